@@ -1,0 +1,163 @@
+/*
+ * ggml-b200.h -- C ABI of the B200-native (sm_100a) Q4_0 x F32 mul_mat.
+ *
+ * Drop-in boundary for ONE path of ggml: GGML_OP_MUL_MAT with a GGML_TYPE_Q4_0 src0 and an F32
+ * src1 (ggml_compute_forward_mul_mat -> ggml_compute_forward_mul_mat_q_f32, reference
+ * ggml.c:11426 / ggml.c:11226).  Plain C linkage, plain pointers and sizes, no C++ or torch
+ * types.  One process drives one GPU (one rank per GPU); a multi-GPU job is N processes that
+ * each upload their row shard and meet in ggml_b200_mul_mat_q4_0_sharded (NCCL all-gather over NVLink).
+ *
+ * Every entry point cites the reference interface it replaces (paths under the reference
+ * tree).  The ggml_tensor-level glue that binds these to the reference's offload seam
+ * (ggml_cuda_compute_forward etc.) is llama.cpp-q_4_0_b200/ggml_glue/ggml-b200-glue.c; see
+ * INTEGRATION.md.
+ *
+ * Error convention: the reference aborts (GGML_ASSERT, ggml.h:204-210; CUDA_CHECK -> exit(1),
+ * ggml-cuda.cu:22-30).  Here every call returns an int status (0 = ok, negative = error, text
+ * via ggml_b200_last_error()) so a harness can skip on a GPU-less host; the glue turns a
+ * non-zero status into the reference's print + abort.  There is NO CPU fallback anywhere.
+ */
+#ifndef GGML_B200_H
+#define GGML_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GGML_B200_OK              0
+#define GGML_B200_ERR_NO_DEVICE  (-1)   /* no CUDA device / driver */
+#define GGML_B200_ERR_ARCH       (-2)   /* device is not sm_100 (the only code in the fatbin) */
+#define GGML_B200_ERR_CUDA       (-3)   /* a CUDA / NCCL call failed, see ggml_b200_last_error */
+#define GGML_B200_ERR_ARG        (-4)   /* shape / alignment / state violates the op contract */
+#define GGML_B200_ERR_STATE      (-5)   /* ggml_b200_init not called, or comm not initialised */
+
+/* weight layouts in HBM */
+#define GGML_B200_LAYOUT_RAW     0      /* the reference's 18-byte block stream, as on disk */
+#define GGML_B200_LAYOUT_PLANES  1      /* split planes: fp16 d[M][K/32] + 16-byte nibbles[M][K/32] */
+
+/* kernel selection for ggml_b200_set_path (0 = choose by n, the default) */
+#define GGML_B200_PATH_AUTO      0
+#define GGML_B200_PATH_GEMV      1      /* dp4a + warp-shuffle kernel (any n, tiled over columns) */
+#define GGML_B200_PATH_GEMM      2      /* TMA + tcgen05 kind::i8 + TMEM kernel */
+
+typedef struct ggml_b200_weight ggml_b200_weight;   /* opaque: one device-resident Q4_0 row shard */
+
+/* ---- life cycle ---------------------------------------------------------------------------
+ * replaces ggml_init_cublas (ggml-cuda.cu:1826-1861, called from ggml_init ggml.c:4282-4286)
+ * and ggml_cuda_set_main_device (ggml-cuda.h:33).  Selects `device`, checks it is sm_100,
+ * creates the stream and the workspace.  Idempotent for the same device. */
+int          ggml_b200_init(int device);
+void         ggml_b200_shutdown(void);
+int          ggml_b200_device_count(void);                 /* <= 0 when no usable GPU */
+const char * ggml_b200_last_error(void);
+int          ggml_b200_sm_count(void);
+
+/* run-time knobs (the reference's equivalents are build-time GGML_CUDA_DMMV_* macros,
+ * ggml-cuda.cu:203-215).  Also read once from the environment at init:
+ * GGML_B200_REPACK=0|1, GGML_B200_GEMM_MIN_N=<n>, GGML_B200_PATH=auto|gemv|gemm */
+void         ggml_b200_set_repack(int on);                 /* layout of FUTURE uploads; default 1 */
+int          ggml_b200_get_repack(void);
+void         ggml_b200_set_gemm_min_n(int n);              /* n >= this takes the tensor-core path */
+int          ggml_b200_get_gemm_min_n(void);
+void         ggml_b200_set_path(int path);
+/* kernel tuning knobs for sweeps ("gemv_threads", "gemv_ctas_per_sm", "gemv_unroll", "gemv_nc",
+ * "gemm_*"); returns GGML_B200_ERR_ARG for an unknown key or a value out of range */
+int          ggml_b200_set_tuning(const char * key, int value);
+void         ggml_b200_set_stream(void * cuda_stream);     /* NULL = the library's own stream */
+void *       ggml_b200_get_stream(void);
+
+/* pinned host memory: mirrors ggml_cuda_host_malloc / ggml_cuda_host_free (ggml-cuda.cu:1884-1905) */
+void *       ggml_b200_host_malloc(size_t size);
+void         ggml_b200_host_free(void * ptr);
+
+/* ---- load-time upload ---------------------------------------------------------------------
+ * replaces ggml_cuda_transform_tensor (ggml-cuda.cu:2766-2809; caller llama.cpp:678-685).
+ * `blocks` = host pointer to the tensor data: M rows of K/32 block_q4_0 (ggml.c:870-875),
+ * row stride nb1 bytes (== 18*K/32 for every tensor ggml creates).  Rows [row_lo, row_hi) are
+ * COPIED to the device (the caller may free `blocks` afterwards, llama.cpp:682-684) and, when
+ * repack is on, re-laid once into the plane layout.  Returns NULL on error. */
+ggml_b200_weight * ggml_b200_upload_q4_0(const void * blocks, int64_t M, int64_t K, size_t nb1,
+                                         int64_t row_lo, int64_t row_hi);
+/* replaces ggml_cuda_free_data (ggml-cuda.cu:2811-2828; caller llama.cpp:241-245) */
+void         ggml_b200_free_weight(ggml_b200_weight * w);
+int64_t      ggml_b200_weight_rows(const ggml_b200_weight * w);   /* row_hi - row_lo */
+int64_t      ggml_b200_weight_row_lo(const ggml_b200_weight * w);
+int64_t      ggml_b200_weight_M(const ggml_b200_weight * w);      /* rows of the whole tensor */
+int64_t      ggml_b200_weight_K(const ggml_b200_weight * w);
+int          ggml_b200_weight_layout(const ggml_b200_weight * w);
+size_t       ggml_b200_weight_device_bytes(const ggml_b200_weight * w);
+/* inverse of the repack: writes this shard's rows back as 18-byte blocks (host pointer,
+ * rows*K/32*18 bytes).  Used by the parity tests to prove the repack is lossless. */
+int          ggml_b200_download_q4_0(const ggml_b200_weight * w, void * blocks_out);
+
+/* ---- kernel 1: activation quantizer -------------------------------------------------------
+ * replaces quantize_row_q8_0 (ggml.c:1122-1280, AVX2 branch :1192-1250 is the contract) as the
+ * op's INIT phase calls it (ggml.c:11353-11367).  x_dev: n rows of K floats, row stride nb11
+ * bytes.  blocks34_dev: n*K/32 reference-format block_q8_0 (34 bytes each, ggml.c:902-907),
+ * byte-identical to the reference's work buffer.  Device pointers. */
+int          ggml_b200_quantize_q8_0(const float * x_dev, int64_t n, int64_t K, size_t nb11,
+                                     void * blocks34_dev);
+
+/* ---- the op -------------------------------------------------------------------------------
+ * replaces ggml_cuda_mul_mat (ggml-cuda.cu:2671-2690) / the COMPUTE phase of
+ * ggml_compute_forward_mul_mat_q_f32 (ggml.c:11373-11411) for this shard's rows:
+ *   y[c*nb1/4 + row_lo + r] = sum_b fp32(dw[r,b]) * fp32(dx[c,b]) * S_b(r,c)      0 <= c < n
+ * x: n rows of K floats (stride nb11 bytes, nb10 == 4 as ggml.c:11279 requires); y: n rows of
+ * M floats (stride nb1 bytes, nb0 == 4, ggml.c:11282) -- the FULL dst; a shard writes only its
+ * own column range [row_lo, row_hi).  Quantizes x on the device (kernel 1), then runs the GEMV
+ * (kernel 2) or the tensor-core GEMM (kernel 3).
+ *   _dev : x and y are device pointers; asynchronous on the current stream.
+ *   _host: x and y are host pointers (what a ggml graph with CPU-resident activations hands
+ *          over); H2D + kernels + D2H + stream sync, complete on return like
+ *          ggml_cuda_op (ggml-cuda.cu:2514-2552). */
+int          ggml_b200_mul_mat_q4_0(const ggml_b200_weight * w, const float * x_dev, int64_t n,
+                                    size_t nb11, float * y_dev, size_t nb1);
+int          ggml_b200_mul_mat_q4_0_host(const ggml_b200_weight * w, const float * x_host, int64_t n,
+                                         size_t nb11, float * y_host, size_t nb1);
+
+/* ---- parity checkpoint --------------------------------------------------------------------
+ * int32 per-block dots S_b = sum_j (q4_j - 8) * q8_j exactly as the kernels form them
+ * (definition: scalar loop ggml.c:2593-2600).  S_dev: [n][rows][K/32] int32, device pointer.
+ * path: GGML_B200_PATH_GEMV or GGML_B200_PATH_GEMM (the same device code as the op, with the
+ * dump store enabled). */
+int          ggml_b200_block_dots_q4_0(const ggml_b200_weight * w, const float * x_dev, int64_t n,
+                                       size_t nb11, int32_t * S_dev, int path);
+
+/* ---- multi-GPU: row shards + all-gather ---------------------------------------------------
+ * replaces the row-split placement and gather of GGML_BACKEND_GPU_SPLIT (ggml_cuda_set_tensor_split
+ * ggml-cuda.cu:1863-1882, slices :2780-2797, gather by cudaMemcpyAsync :2514-2540) with one
+ * rank per GPU and one NCCL all-gather over NVLink.
+ * unique_id: the 128-byte ncclUniqueId, produced on rank 0 by ggml_b200_comm_unique_id and
+ * broadcast by the launcher (torch.distributed, MPI, a file ...). */
+int          ggml_b200_comm_unique_id(void * out128);
+int          ggml_b200_comm_init(int rank, int world, const void * unique_id128);
+void         ggml_b200_comm_shutdown(void);
+int          ggml_b200_comm_rank(void);
+int          ggml_b200_comm_world(void);
+/* the row range rank r of `world` owns for a tensor of M rows (equal shards rounded to
+ * `GGML_B200_SHARD_ALIGN` rows; the reference rounds to its own granularity at
+ * ggml-cuda.cu:2784-2797) */
+#define GGML_B200_SHARD_ALIGN 128
+void         ggml_b200_shard_rows(int64_t M, int rank, int world, int64_t * row_lo, int64_t * row_hi);
+/* mul_mat on this rank's shard + all-gather so that EVERY rank ends with the full y[n][M]
+ * (device pointers; asynchronous on the current stream).  x must already be replicated. */
+int          ggml_b200_mul_mat_q4_0_sharded(const ggml_b200_weight * w, const float * x_dev, int64_t n,
+                                            size_t nb11, float * y_dev, size_t nb1);
+
+/* ---- introspection for bench.py / tests ---------------------------------------------------*/
+/* number of kernels THIS library launched since init (the bench's gpu_launches claim) */
+uint64_t     ggml_b200_launch_count(void);
+/* plain device memory helpers so a ctypes harness needs no other CUDA binding */
+void *       ggml_b200_dev_malloc(size_t size);
+void         ggml_b200_dev_free(void * ptr);
+int          ggml_b200_memcpy_h2d(void * dst_dev, const void * src_host, size_t size);
+int          ggml_b200_memcpy_d2h(void * dst_host, const void * src_dev, size_t size);
+int          ggml_b200_synchronize(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GGML_B200_H */

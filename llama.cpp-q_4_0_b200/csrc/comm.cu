@@ -1,0 +1,166 @@
+// comm.cu -- multi-GPU: row shards + NCCL all-gather over NVLink (one rank per GPU).
+//
+// Replaces the reference's only multi-device mechanism, GGML_BACKEND_GPU_SPLIT: row slices per
+// device (ggml-cuda.cu:2780-2797) gathered with per-column cudaMemcpyAsync (:2514-2540) from a
+// single host thread.  Here every rank owns rows [row_lo,row_hi) of each weight, computes its
+// slab of dst, and one ncclAllGather reassembles dst on every rank.
+//
+// NCCL is bound at run time (dlopen "libnccl.so.2") so the library has no link-time dependency
+// and shares the copy torch already loaded when driven from a torch.distributed launcher.
+#include <dlfcn.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "state.h"
+
+namespace b200 {
+
+typedef struct ncclComm * ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+typedef int ncclResult_t;
+enum { ncclFloat32 = 7 };
+
+struct Nccl {
+    void * lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    const char * (*GetErrorString)(ncclResult_t) = nullptr;
+    ncclComm_t comm = nullptr;
+    int rank = 0, world = 1;
+    float * gather_buf = nullptr; size_t gather_cap = 0;   // [world][n][rows_max]
+    float * slab_buf = nullptr;   size_t slab_cap = 0;     // [n][rows_max] (this rank)
+};
+static Nccl nc;
+
+static int nccl_load() {
+    if (nc.lib) return GGML_B200_OK;
+    const char * names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char * nm : names) { nc.lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL); if (nc.lib) break; }
+    if (!nc.lib) { set_error("cannot dlopen libnccl.so.2: %s", dlerror()); return GGML_B200_ERR_CUDA; }
+#define SYM(field, name) *(void **)(&nc.field) = dlsym(nc.lib, name); if (!nc.field) { set_error("libnccl lacks %s", name); return GGML_B200_ERR_CUDA; }
+    SYM(GetUniqueId, "ncclGetUniqueId")
+    SYM(CommInitRank, "ncclCommInitRank")
+    SYM(CommDestroy, "ncclCommDestroy")
+    SYM(AllGather, "ncclAllGather")
+    SYM(GetErrorString, "ncclGetErrorString")
+#undef SYM
+    return GGML_B200_OK;
+}
+
+#define NK(call)                                                                              \
+    do {                                                                                      \
+        ncclResult_t r_ = (call);                                                             \
+        if (r_ != 0) { set_error("NCCL error %d (%s): %s", r_, nc.GetErrorString(r_), #call); return GGML_B200_ERR_CUDA; } \
+    } while (0)
+
+// gather_buf[r][c][j] (rank r's slab, rows_r(r) wide but stored with stride rows_max) -> y[c][row_lo(r) + j]
+__global__ void scatter_slabs_kernel(const float * __restrict__ gbuf, float * __restrict__ y, long long ldy,
+                                     int n, long long M, int world, long long rows_max) {
+    const long long total = (long long)n * M;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long c = i / M, m = i - c * M;
+        // owner of row m under ggml_b200_shard_rows
+        long long per = ((M + world - 1) / world + GGML_B200_SHARD_ALIGN - 1) / GGML_B200_SHARD_ALIGN * GGML_B200_SHARD_ALIGN;
+        long long r = m / per;
+        if (r >= world) r = world - 1;
+        const long long j = m - r * per;
+        y[c * ldy + m] = gbuf[(r * n + c) * rows_max + j];
+    }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+void ggml_b200_shard_rows(int64_t M, int rank, int world, int64_t * row_lo, int64_t * row_hi) {
+    if (world < 1) world = 1;
+    int64_t per = ((M + world - 1) / world + GGML_B200_SHARD_ALIGN - 1) / GGML_B200_SHARD_ALIGN * GGML_B200_SHARD_ALIGN;
+    int64_t lo = per * rank, hi = per * (rank + 1);
+    if (lo > M) lo = M;
+    if (hi > M) hi = M;
+    if (row_lo) *row_lo = lo;
+    if (row_hi) *row_hi = hi;
+}
+
+int ggml_b200_comm_unique_id(void * out128) {
+    int rc = nccl_load();
+    if (rc) return rc;
+    ncclUniqueId id;
+    NK(nc.GetUniqueId(&id));
+    memcpy(out128, &id, sizeof(id));
+    return GGML_B200_OK;
+}
+
+int ggml_b200_comm_init(int rank, int world, const void * unique_id128) {
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    if (world < 1 || rank < 0 || rank >= world) { set_error("bad rank %d / world %d", rank, world); return GGML_B200_ERR_ARG; }
+    if (nc.comm) { set_error("communicator already initialised"); return GGML_B200_ERR_STATE; }
+    nc.rank = rank; nc.world = world;
+    if (world == 1) return GGML_B200_OK;
+    int rc = nccl_load();
+    if (rc) return rc;
+    ncclUniqueId id;
+    memcpy(&id, unique_id128, sizeof(id));
+    NK(nc.CommInitRank(&nc.comm, world, id, rank));
+    return GGML_B200_OK;
+}
+
+void ggml_b200_comm_shutdown(void) {
+    if (nc.comm) { nc.CommDestroy(nc.comm); nc.comm = nullptr; }
+    if (nc.gather_buf) { cudaFree(nc.gather_buf); nc.gather_buf = nullptr; nc.gather_cap = 0; }
+    if (nc.slab_buf) { cudaFree(nc.slab_buf); nc.slab_buf = nullptr; nc.slab_cap = 0; }
+    nc.rank = 0; nc.world = 1;
+}
+
+int ggml_b200_comm_rank(void) { return nc.rank; }
+int ggml_b200_comm_world(void) { return nc.world; }
+
+int ggml_b200_mul_mat_q4_0_sharded(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y_dev, size_t nb1) {
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    if (!w || !x_dev || !y_dev) { set_error("null argument"); return GGML_B200_ERR_ARG; }
+    if (nc.world == 1) return ggml_b200_mul_mat_q4_0(w, x_dev, n, nb11, y_dev, nb1);
+    if (!nc.comm) { set_error("ggml_b200_comm_init was not called"); return GGML_B200_ERR_STATE; }
+    int64_t lo, hi;
+    ggml_b200_shard_rows(w->M, nc.rank, nc.world, &lo, &hi);
+    if (lo != w->row_lo || hi != w->row_hi) { set_error("weight shard [%lld,%lld) is not rank %d's shard [%lld,%lld)", (long long)w->row_lo, (long long)w->row_hi, nc.rank, (long long)lo, (long long)hi); return GGML_B200_ERR_ARG; }
+    if (n == 0) return GGML_B200_OK;
+    int64_t l0, h0;
+    ggml_b200_shard_rows(w->M, 0, nc.world, &l0, &h0);
+    const int64_t rows_max = h0 - l0;   // rank 0 always holds a full-width shard
+    const size_t slab = (size_t)n * rows_max;
+
+    if (slab * nc.world * 4 > nc.gather_cap) {
+        if (nc.gather_buf) CK(cudaFree(nc.gather_buf));
+        nc.gather_buf = nullptr; nc.gather_cap = 0;
+        CK(cudaMalloc(&nc.gather_buf, slab * nc.world * 4));
+        nc.gather_cap = slab * nc.world * 4;
+    }
+    // n == 1 and every shard full-width: y itself is the gather buffer ([world][rows_max] == [M])
+    const bool in_place = (n == 1) && (rows_max * nc.world == w->M);
+    float * gbuf = in_place ? y_dev : nc.gather_buf;
+    float * mine = gbuf + (size_t)nc.rank * slab;
+    // this rank's slab, dense [n][rows_max]: reuse the op with a fake dst whose column 0 is `mine`
+    int rc = launch_quantize(x_dev, n, w->K, nb11, nullptr);
+    if (rc) return rc;
+    if (w->rows() > 0) {
+        rc = launch_shard(w, mine, rows_max, (int)n);
+        if (rc) return rc;
+    }
+    NK(nc.AllGather(mine, gbuf, slab, ncclFloat32, nc.comm, g.stream));
+    if (!in_place) {
+        const long long total = (long long)n * w->M;
+        const int threads = 256;
+        long long blocks = (total + threads - 1) / threads;
+        if (blocks > g.sm_count * 8) blocks = g.sm_count * 8;
+        scatter_slabs_kernel<<<(unsigned)blocks, threads, 0, g.stream>>>(gbuf, y_dev, (long long)(nb1 / 4), (int)n, w->M, nc.world, rows_max);
+        g.launches++;
+        CK(cudaGetLastError());
+    }
+    return GGML_B200_OK;
+}
+
+}  // extern "C"

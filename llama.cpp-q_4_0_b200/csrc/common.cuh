@@ -1,0 +1,81 @@
+// common.cuh -- shared device helpers and the HBM data layouts of the Q4_0 x F32 mul_mat path.
+//
+// Data layout in HBM (see DESIGN.md "Data layout"):
+//
+//   weights, LAYOUT_PLANES (after the one-time repack of the reference's 18-byte block_q4_0
+//   stream, ggml.c:870-875):
+//       wq : uint4 [rows][nbk]   16 bytes of nibbles per 32-weight block, 16-byte aligned;
+//                                byte j: low nibble = weight j, high nibble = weight j+16
+//                                (ggml.c:942-951) -- the nibble order is NOT changed
+//       wd : half  [rows][nbk]   the block scale d, bit-identical fp16
+//     algorithmic bytes stay 18 per block (0.5625 B/weight).
+//   weights, LAYOUT_RAW: the 18-byte blocks as uploaded, rows contiguous (18*nbk bytes, 4-byte
+//     aligned because nbk is even, ggml.c:2344).
+//
+//   activations after kernel 1 (the device-side replacement of the op's q8_0 work buffer,
+//   ggml.c:11353-11367):
+//       xq  : int8 [n][K]        quants in natural element order (K-major rows: also the B
+//                                operand of the tensor-core GEMM, loadable by TMA)
+//       xds : int2 [n][nbk]      .x = bits of fp32(fp16(d))   .y = -8 * sum_j q8_j   (exact int)
+//     The -8*sum term turns sum (q4-8)*q8 into a dp4a chain over the UNSIGNED nibbles that starts
+//     from xds.y: the integer result S_b is identical (checked bit-exact in tests).
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define QK 32
+#define Q4_0_BLOCK_BYTES 18
+#define Q8_0_BLOCK_BYTES 34
+
+namespace b200 {
+
+__device__ __forceinline__ uint4 ldg_stream_u4(const uint4 * p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::128B.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+
+__device__ __forceinline__ uint32_t ldg_stream_u32(const uint32_t * p) {
+    uint32_t r;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
+    return r;
+}
+
+__device__ __forceinline__ unsigned short ldg_stream_u16(const unsigned short * p) {
+    unsigned short r;
+    asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=h"(r) : "l"(p));
+    return r;
+}
+
+__device__ __forceinline__ float half_bits_to_float(unsigned short h) {
+    return __half2float(__ushort_as_half(h));
+}
+
+// S_b for one block: 16 bytes of nibbles (4 words) against 32 int8 (lo = elements 0..15,
+// hi = elements 16..31), starting from init = -8 * sum(q8).  ggml.c:2593-2600 restated as
+// sum q4*q8 - 8*sum q8 on IDP.4A.
+__device__ __forceinline__ int block_dot_q4_q8(const uint4 q, const uint4 ylo, const uint4 yhi, int init) {
+    int s = init;
+    s = __dp4a((int)(q.x & 0x0F0F0F0Fu), (int)ylo.x, s);
+    s = __dp4a((int)(q.y & 0x0F0F0F0Fu), (int)ylo.y, s);
+    s = __dp4a((int)(q.z & 0x0F0F0F0Fu), (int)ylo.z, s);
+    s = __dp4a((int)(q.w & 0x0F0F0F0Fu), (int)ylo.w, s);
+    s = __dp4a((int)((q.x >> 4) & 0x0F0F0F0Fu), (int)yhi.x, s);
+    s = __dp4a((int)((q.y >> 4) & 0x0F0F0F0Fu), (int)yhi.y, s);
+    s = __dp4a((int)((q.z >> 4) & 0x0F0F0F0Fu), (int)yhi.z, s);
+    s = __dp4a((int)((q.w >> 4) & 0x0F0F0F0Fu), (int)yhi.w, s);
+    return s;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+    v += __shfl_xor_sync(0xffffffffu, v, 16);
+    v += __shfl_xor_sync(0xffffffffu, v, 8);
+    v += __shfl_xor_sync(0xffffffffu, v, 4);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    return v;
+}
+
+}  // namespace b200

@@ -1,0 +1,437 @@
+// ggml-b200.cu -- the C ABI declared in include/ggml-b200.h: init, load-time upload (+ repack),
+// op dispatch, host-buffer path, parity dumps.  One process drives one GPU.
+//
+// Reference seams replaced (paths under the reference tree): ggml_init_cublas
+// (ggml-cuda.cu:1826-1861), ggml_cuda_transform_tensor (:2766-2809), ggml_cuda_free_data
+// (:2811-2828), ggml_cuda_mul_mat / ggml_cuda_op (:2671-2690, :2286-2567) and, behind them,
+// ggml_compute_forward_mul_mat_q_f32 (ggml.c:11226-11424).  Nothing here is a port of those:
+// the reference dequantizes to f32 and calls cuBLAS / a float DMMV kernel; this file quantizes
+// the activations to q8_0 on the device and multiplies in the integer domain like the CPU path.
+//
+// There is NO CPU fallback: without a sm_100 device every compute entry point fails loudly.
+#include "../../include/ggml-b200.h"
+
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+
+#include "common.cuh"
+#include "gemv_q4_0.cuh"
+#include "quantize_q8_0.cuh"
+#include "repack.cuh"
+#include "state.h"
+
+namespace b200 {
+
+Ctx g;
+static std::mutex g_mu;
+
+void set_error(const char * fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g.err, sizeof(g.err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char * what, const char * file, int line) {
+    set_error("CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+    if (getenv("GGML_B200_VERBOSE")) fprintf(stderr, "ggml-b200: %s\n", g.err);
+    return GGML_B200_ERR_CUDA;
+}
+
+int ensure_workspace(int64_t n, int64_t K) {
+    const size_t need_q = (size_t)n * K;
+    const size_t need_ds = (size_t)n * (K / QK) * sizeof(int2);
+    if (need_q > g.xq_cap) {
+        if (g.xq) CK(cudaFree(g.xq));
+        g.xq = nullptr; g.xq_cap = 0;
+        CK(cudaMalloc(&g.xq, need_q));
+        g.xq_cap = need_q;
+    }
+    if (need_ds > g.xds_cap) {
+        if (g.xds) CK(cudaFree(g.xds));
+        g.xds = nullptr; g.xds_cap = 0;
+        CK(cudaMalloc(&g.xds, need_ds));
+        g.xds_cap = need_ds;
+    }
+    return GGML_B200_OK;
+}
+
+static int ensure_stage(void ** p, size_t * cap, size_t need) {
+    if (need > *cap) {
+        if (*p) CK(cudaFree(*p));
+        *p = nullptr; *cap = 0;
+        CK(cudaMalloc(p, need));
+        *cap = need;
+    }
+    return GGML_B200_OK;
+}
+
+// ---- kernel 1 launch ------------------------------------------------------------------------
+int launch_quantize(const float * x_dev, int64_t n, int64_t K, size_t nb11, void * blocks34_dev) {
+    if (n <= 0) return GGML_B200_OK;
+    int rc = ensure_workspace(n, K);
+    if (rc) return rc;
+    const long long total = (long long)n * (K / 8);
+    const int threads = 256;
+    const unsigned blocks = (unsigned)((total + threads - 1) / threads);
+    const bool aligned = (((uintptr_t)x_dev | nb11) & 15) == 0;
+    if (aligned) {
+        if (blocks34_dev) quantize_q8_0_kernel<true, true><<<blocks, threads, 0, g.stream>>>(x_dev, n, (int)K, nb11, g.xq, g.xds, (unsigned char *)blocks34_dev);
+        else              quantize_q8_0_kernel<true, false><<<blocks, threads, 0, g.stream>>>(x_dev, n, (int)K, nb11, g.xq, g.xds, nullptr);
+    } else {
+        if (blocks34_dev) quantize_q8_0_kernel<false, true><<<blocks, threads, 0, g.stream>>>(x_dev, n, (int)K, nb11, g.xq, g.xds, (unsigned char *)blocks34_dev);
+        else              quantize_q8_0_kernel<false, false><<<blocks, threads, 0, g.stream>>>(x_dev, n, (int)K, nb11, g.xq, g.xds, nullptr);
+    }
+    g.launches++;
+    CK(cudaGetLastError());
+    return GGML_B200_OK;
+}
+
+// ---- kernel 2 launch ------------------------------------------------------------------------
+template <int NC, int UNROLL, bool DUMP>
+static int launch_gemv_planes_t(const ggml_b200_weight * w, float * y, long long ldy, int n, int * S) {
+    const int nbk = (int)(w->K / QK);
+    const size_t smem = gemv_smem_bytes(nbk, NC);
+    auto kern = gemv_q4_0_planes_kernel<NC, UNROLL, DUMP>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
+        attr_set = true;
+    }
+    const int grid = g.sm_count * g.tune.gemv_ctas_per_sm;
+    kern<<<grid, g.tune.gemv_threads, smem, g.stream>>>(w->wq, w->wd, g.xq, g.xds, y, (int)w->rows(), nbk, ldy, n, S);
+    g.launches++;
+    CK(cudaGetLastError());
+    return GGML_B200_OK;
+}
+
+template <int NC, bool DUMP>
+static int launch_gemv_raw_t(const ggml_b200_weight * w, float * y, long long ldy, int n, int * S) {
+    const int nbk = (int)(w->K / QK);
+    const size_t smem = gemv_smem_bytes(nbk, NC);
+    auto kern = gemv_q4_0_raw_kernel<NC, DUMP>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
+        attr_set = true;
+    }
+    const int grid = g.sm_count * g.tune.gemv_ctas_per_sm;
+    kern<<<grid, g.tune.gemv_threads, smem, g.stream>>>((const uint32_t *)w->raw, g.xq, g.xds, y, (int)w->rows(), nbk, ldy, n, S);
+    g.launches++;
+    CK(cudaGetLastError());
+    return GGML_B200_OK;
+}
+
+template <bool DUMP>
+static int launch_gemv_any(const ggml_b200_weight * w, float * y, long long ldy, int n, int * S) {
+    const int nbk = (int)(w->K / QK);
+    // columns per pass: as many as n needs (1, 2, 4, 8), capped by the knob and by shared memory
+    int nc = n >= 8 ? 8 : n >= 3 ? 4 : n;
+    if (g.tune.gemv_nc > 0 && nc > g.tune.gemv_nc) nc = g.tune.gemv_nc;
+    while (nc > 1 && gemv_smem_bytes(nbk, nc) > MAX_DYN_SMEM) nc >>= 1;
+    if (gemv_smem_bytes(nbk, nc) > MAX_DYN_SMEM) {
+        set_error("K = %lld needs %zu bytes of shared memory for the staged activations (max %d)",
+                  (long long)w->K, gemv_smem_bytes(nbk, 1), MAX_DYN_SMEM);
+        return GGML_B200_ERR_ARG;
+    }
+    if (w->layout == GGML_B200_LAYOUT_RAW) {
+        switch (nc) {
+            case 1: return launch_gemv_raw_t<1, DUMP>(w, y, ldy, n, S);
+            case 2: return launch_gemv_raw_t<2, DUMP>(w, y, ldy, n, S);
+            case 4: return launch_gemv_raw_t<4, DUMP>(w, y, ldy, n, S);
+            default: return launch_gemv_raw_t<8, DUMP>(w, y, ldy, n, S);
+        }
+    }
+    const int u = g.tune.gemv_unroll;
+    switch (nc) {
+        case 1: return u >= 4 ? launch_gemv_planes_t<1, 4, DUMP>(w, y, ldy, n, S) : u == 2 ? launch_gemv_planes_t<1, 2, DUMP>(w, y, ldy, n, S) : launch_gemv_planes_t<1, 1, DUMP>(w, y, ldy, n, S);
+        case 2: return u >= 4 ? launch_gemv_planes_t<2, 4, DUMP>(w, y, ldy, n, S) : launch_gemv_planes_t<2, 2, DUMP>(w, y, ldy, n, S);
+        case 4: return u >= 4 ? launch_gemv_planes_t<4, 4, DUMP>(w, y, ldy, n, S) : launch_gemv_planes_t<4, 2, DUMP>(w, y, ldy, n, S);
+        default: return launch_gemv_planes_t<8, 2, DUMP>(w, y, ldy, n, S);
+    }
+}
+
+int launch_gemv(const ggml_b200_weight * w, float * y, long long ldy, int n) {
+    return launch_gemv_any<false>(w, y, ldy, n, nullptr);
+}
+
+int launch_gemv_dump(const ggml_b200_weight * w, float * y, long long ldy, int n, int * S) {
+    return launch_gemv_any<true>(w, y, ldy, n, S);
+}
+
+static bool use_gemm(const ggml_b200_weight * w, int64_t n) {
+    if (g.path == GGML_B200_PATH_GEMV) return false;
+    if (!gemm_available(w)) return false;
+    if (g.path == GGML_B200_PATH_GEMM) return true;
+    return n >= g.gemm_min_n;
+}
+
+static int check_op_args(const ggml_b200_weight * w, const void * x, int64_t n, size_t nb11, const void * y, size_t nb1) {
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    if (!w || !x || !y) { set_error("null argument"); return GGML_B200_ERR_ARG; }
+    if (n < 0 || n > INT32_MAX) { set_error("bad n"); return GGML_B200_ERR_ARG; }
+    // ggml.c:11279 (nb10 == sizeof(float)) and :11282-11285 (dense dst rows)
+    if (nb11 < (size_t)w->K * 4 || (nb11 & 3)) { set_error("src1 row stride %zu < K*4 or not a multiple of 4", nb11); return GGML_B200_ERR_ARG; }
+    if (nb1 < (size_t)w->M * 4 || (nb1 & 3)) { set_error("dst row stride %zu < M*4 or not a multiple of 4", nb1); return GGML_B200_ERR_ARG; }
+    return GGML_B200_OK;
+}
+
+int launch_shard(const ggml_b200_weight * w, float * y, long long ldy, int n) {
+    if (use_gemm(w, n)) return launch_gemm(w, y, ldy, n, nullptr);
+    return launch_gemv(w, y, ldy, n);
+}
+
+// x_dev/y_dev device pointers; y_dev addresses the full dst, this shard writes [row_lo,row_hi)
+int mul_mat_dev(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y_dev, size_t nb1) {
+    if (n == 0 || w->rows() == 0) return GGML_B200_OK;
+    int rc = launch_quantize(x_dev, n, w->K, nb11, nullptr);
+    if (rc) return rc;
+    float * y = y_dev + w->row_lo;
+    const long long ldy = (long long)(nb1 / 4);
+    return launch_shard(w, y, ldy, (int)n);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+// =============================================================================================
+extern "C" {
+
+int ggml_b200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char * ggml_b200_last_error(void) { return g.err; }
+int ggml_b200_sm_count(void) { return g.sm_count; }
+
+int ggml_b200_init(int device) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (g.inited && g.device == device) return GGML_B200_OK;
+    if (g.inited) { set_error("already initialised on device %d", g.device); return GGML_B200_ERR_STATE; }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0) {
+        cudaGetLastError();
+        set_error("no CUDA device (%s); this library has no CPU fallback", e == cudaSuccess ? "count 0" : cudaGetErrorString(e));
+        return GGML_B200_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= ndev) { set_error("device %d out of range (0..%d)", device, ndev - 1); return GGML_B200_ERR_ARG; }
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        set_error("device %d is sm_%d%d; this library contains sm_100a code only", device, prop.major, prop.minor);
+        return GGML_B200_ERR_ARCH;
+    }
+    CK(cudaSetDevice(device));
+    g.device = device;
+    g.sm_count = prop.multiProcessorCount;
+    CK(cudaStreamCreateWithFlags(&g.own_stream, cudaStreamNonBlocking));
+    g.stream = g.own_stream;
+    const char * s;
+    if ((s = getenv("GGML_B200_REPACK")))     g.repack = atoi(s) != 0;
+    if ((s = getenv("GGML_B200_GEMM_MIN_N"))) g.gemm_min_n = atoi(s);
+    if ((s = getenv("GGML_B200_PATH")))       g.path = !strcmp(s, "gemv") ? GGML_B200_PATH_GEMV : !strcmp(s, "gemm") ? GGML_B200_PATH_GEMM : GGML_B200_PATH_AUTO;
+    int rc = gemm_init();
+    if (rc) return rc;
+    g.inited = true;
+    return GGML_B200_OK;
+}
+
+void ggml_b200_shutdown(void) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!g.inited) return;
+    ggml_b200_comm_shutdown();
+    cudaStreamSynchronize(g.stream);
+    if (g.xq) cudaFree(g.xq);
+    if (g.xds) cudaFree(g.xds);
+    if (g.xstage) cudaFree(g.xstage);
+    if (g.ystage) cudaFree(g.ystage);
+    gemm_shutdown();
+    if (g.own_stream) cudaStreamDestroy(g.own_stream);
+    const Tune t = g.tune;
+    g = Ctx();
+    g.tune = t;
+}
+
+void   ggml_b200_set_repack(int on) { g.repack = on != 0; }
+int    ggml_b200_get_repack(void) { return g.repack; }
+void   ggml_b200_set_gemm_min_n(int n) { g.gemm_min_n = n; }
+int    ggml_b200_get_gemm_min_n(void) { return g.gemm_min_n; }
+void   ggml_b200_set_path(int path) { g.path = path; }
+void   ggml_b200_set_stream(void * s) { g.stream = s ? (cudaStream_t)s : g.own_stream; }
+void * ggml_b200_get_stream(void) { return (void *)g.stream; }
+uint64_t ggml_b200_launch_count(void) { return g.launches; }
+
+int ggml_b200_set_tuning(const char * key, int value) {
+    if (!strcmp(key, "gemv_threads"))      { if (value < 32 || value > 512 || (value & 31)) return GGML_B200_ERR_ARG; g.tune.gemv_threads = value; }
+    else if (!strcmp(key, "gemv_ctas_per_sm")) { if (value < 1 || value > 16) return GGML_B200_ERR_ARG; g.tune.gemv_ctas_per_sm = value; }
+    else if (!strcmp(key, "gemv_unroll"))  { g.tune.gemv_unroll = value; }
+    else if (!strcmp(key, "gemv_nc"))      { g.tune.gemv_nc = value; }
+    else return gemm_set_tuning(key, value);
+    return GGML_B200_OK;
+}
+
+void * ggml_b200_host_malloc(size_t size) {
+    void * p = nullptr;
+    if (cudaMallocHost(&p, size) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void ggml_b200_host_free(void * p) { if (p) cudaFreeHost(p); }
+
+void * ggml_b200_dev_malloc(size_t size) {
+    void * p = nullptr;
+    if (cudaMalloc(&p, size ? size : 1) != cudaSuccess) { cuda_fail(cudaGetLastError(), "cudaMalloc", __FILE__, __LINE__); return nullptr; }
+    return p;
+}
+void ggml_b200_dev_free(void * p) { if (p) cudaFree(p); }
+int ggml_b200_memcpy_h2d(void * d, const void * s, size_t n) { CK(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, g.stream)); CK(cudaStreamSynchronize(g.stream)); return GGML_B200_OK; }
+int ggml_b200_memcpy_d2h(void * d, const void * s, size_t n) { CK(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, g.stream)); CK(cudaStreamSynchronize(g.stream)); return GGML_B200_OK; }
+int ggml_b200_synchronize(void) { CK(cudaStreamSynchronize(g.stream)); return GGML_B200_OK; }
+
+// ---- upload -----------------------------------------------------------------------------------
+ggml_b200_weight * ggml_b200_upload_q4_0(const void * blocks, int64_t M, int64_t K, size_t nb1, int64_t row_lo, int64_t row_hi) {
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return nullptr; }
+    // ggml.c:2343-2344: n % 32 == 0 and an even number of blocks per row
+    if (!blocks || M <= 0 || K <= 0 || (K % 64) != 0 || K > INT32_MAX) { set_error("bad shape M=%lld K=%lld (K must be a positive multiple of 64)", (long long)M, (long long)K); return nullptr; }
+    const int64_t nbk = K / QK;
+    const size_t row_bytes = (size_t)nbk * Q4_0_BLOCK_BYTES;
+    if (nb1 < row_bytes) { set_error("row stride %zu < %zu", nb1, row_bytes); return nullptr; }
+    if (row_lo < 0 || row_hi < row_lo || row_hi > M) { set_error("bad row range [%lld,%lld) of %lld", (long long)row_lo, (long long)row_hi, (long long)M); return nullptr; }
+
+    ggml_b200_weight * w = new ggml_b200_weight();
+    w->M = M; w->K = K; w->row_lo = row_lo; w->row_hi = row_hi;
+    w->layout = g.repack ? GGML_B200_LAYOUT_PLANES : GGML_B200_LAYOUT_RAW;
+    const int64_t rows = row_hi - row_lo;
+    const size_t raw_bytes = (size_t)rows * row_bytes;
+    if (rows == 0) return w;
+
+    void * raw = nullptr;
+    cudaError_t e = cudaMalloc(&raw, raw_bytes);
+    if (e != cudaSuccess) { cuda_fail(e, "cudaMalloc(raw)", __FILE__, __LINE__); delete w; return nullptr; }
+    const char * src = (const char *)blocks + (size_t)row_lo * nb1;
+    // blocking copy like the reference (ggml-cuda.cu:2797): the caller may free `blocks` on return
+    e = cudaMemcpy2DAsync(raw, row_bytes, src, nb1, row_bytes, (size_t)rows, cudaMemcpyHostToDevice, g.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
+    if (e != cudaSuccess) { cuda_fail(e, "upload copy", __FILE__, __LINE__); cudaFree(raw); delete w; return nullptr; }
+
+    if (w->layout == GGML_B200_LAYOUT_RAW) {
+        w->raw = raw;
+        w->dev_bytes = raw_bytes;
+        return w;
+    }
+    const long long nblocks = (long long)rows * nbk;
+    e = cudaMalloc(&w->wq, (size_t)nblocks * sizeof(uint4));
+    if (e == cudaSuccess) e = cudaMalloc(&w->wd, (size_t)nblocks * sizeof(__half));
+    if (e != cudaSuccess) { cuda_fail(e, "cudaMalloc(planes)", __FILE__, __LINE__); cudaFree(raw); ggml_b200_free_weight(w); return nullptr; }
+    const int threads = 256;
+    repack_q4_0_to_planes_kernel<<<(unsigned)((nblocks + threads - 1) / threads), threads, 0, g.stream>>>((const unsigned short *)raw, w->wq, w->wd, nblocks);
+    g.launches++;
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
+    cudaFree(raw);
+    if (e != cudaSuccess) { cuda_fail(e, "repack", __FILE__, __LINE__); ggml_b200_free_weight(w); return nullptr; }
+    w->dev_bytes = (size_t)nblocks * (sizeof(uint4) + sizeof(__half));
+    if (gemm_prepare_weight(w) != GGML_B200_OK) { ggml_b200_free_weight(w); return nullptr; }
+    return w;
+}
+
+void ggml_b200_free_weight(ggml_b200_weight * w) {
+    if (!w) return;
+    gemm_release_weight(w);
+    if (w->raw) cudaFree(w->raw);
+    if (w->wq) cudaFree(w->wq);
+    if (w->wd) cudaFree(w->wd);
+    delete w;
+}
+
+int64_t ggml_b200_weight_rows(const ggml_b200_weight * w) { return w ? w->rows() : 0; }
+int64_t ggml_b200_weight_row_lo(const ggml_b200_weight * w) { return w ? w->row_lo : 0; }
+int64_t ggml_b200_weight_M(const ggml_b200_weight * w) { return w ? w->M : 0; }
+int64_t ggml_b200_weight_K(const ggml_b200_weight * w) { return w ? w->K : 0; }
+int     ggml_b200_weight_layout(const ggml_b200_weight * w) { return w ? w->layout : -1; }
+size_t  ggml_b200_weight_device_bytes(const ggml_b200_weight * w) { return w ? w->dev_bytes : 0; }
+
+int ggml_b200_download_q4_0(const ggml_b200_weight * w, void * out) {
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    if (!w || !out) { set_error("null argument"); return GGML_B200_ERR_ARG; }
+    const int64_t rows = w->rows();
+    if (rows == 0) return GGML_B200_OK;
+    const long long nblocks = (long long)rows * (w->K / QK);
+    const size_t bytes = (size_t)nblocks * Q4_0_BLOCK_BYTES;
+    if (w->layout == GGML_B200_LAYOUT_RAW) {
+        CK(cudaMemcpyAsync(out, w->raw, bytes, cudaMemcpyDeviceToHost, g.stream));
+        CK(cudaStreamSynchronize(g.stream));
+        return GGML_B200_OK;
+    }
+    void * raw = nullptr;
+    CK(cudaMalloc(&raw, bytes));
+    const int threads = 256;
+    unpack_planes_to_q4_0_kernel<<<(unsigned)((nblocks + threads - 1) / threads), threads, 0, g.stream>>>(w->wq, w->wd, (unsigned short *)raw, nblocks);
+    g.launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, raw, bytes, cudaMemcpyDeviceToHost, g.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
+    cudaFree(raw);
+    if (e != cudaSuccess) return cuda_fail(e, "download", __FILE__, __LINE__);
+    return GGML_B200_OK;
+}
+
+// ---- kernel 1 ---------------------------------------------------------------------------------
+int ggml_b200_quantize_q8_0(const float * x_dev, int64_t n, int64_t K, size_t nb11, void * blocks34_dev) {
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    if (!x_dev || n < 0 || K <= 0 || (K % QK) != 0 || nb11 < (size_t)K * 4 || (nb11 & 3)) { set_error("bad quantize arguments"); return GGML_B200_ERR_ARG; }
+    return launch_quantize(x_dev, n, K, nb11, blocks34_dev);
+}
+
+// ---- the op -----------------------------------------------------------------------------------
+int ggml_b200_mul_mat_q4_0(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y_dev, size_t nb1) {
+    int rc = check_op_args(w, x_dev, n, nb11, y_dev, nb1);
+    if (rc) return rc;
+    return mul_mat_dev(w, x_dev, n, nb11, y_dev, nb1);
+}
+
+int ggml_b200_mul_mat_q4_0_host(const ggml_b200_weight * w, const float * x_host, int64_t n, size_t nb11, float * y_host, size_t nb1) {
+    int rc = check_op_args(w, x_host, n, nb11, y_host, nb1);
+    if (rc) return rc;
+    const int64_t rows = w->rows();
+    if (n == 0 || rows == 0) return GGML_B200_OK;
+    const size_t xrow = (size_t)w->K * 4;
+    rc = ensure_stage((void **)&g.xstage, &g.xstage_cap, (size_t)n * xrow);
+    if (rc) return rc;
+    rc = ensure_stage((void **)&g.ystage, &g.ystage_cap, (size_t)n * rows * 4);
+    if (rc) return rc;
+    if (nb11 == xrow) CK(cudaMemcpyAsync(g.xstage, x_host, (size_t)n * xrow, cudaMemcpyHostToDevice, g.stream));
+    else              CK(cudaMemcpy2DAsync(g.xstage, xrow, x_host, nb11, xrow, (size_t)n, cudaMemcpyHostToDevice, g.stream));
+    rc = launch_quantize(g.xstage, n, w->K, xrow, nullptr);
+    if (rc) return rc;
+    rc = launch_shard(w, g.ystage, rows, (int)n);
+    if (rc) return rc;
+    CK(cudaMemcpy2DAsync(y_host + w->row_lo, nb1, g.ystage, (size_t)rows * 4, (size_t)rows * 4, (size_t)n, cudaMemcpyDeviceToHost, g.stream));
+    CK(cudaStreamSynchronize(g.stream));
+    return GGML_B200_OK;
+}
+
+int ggml_b200_block_dots_q4_0(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, int32_t * S_dev, int path) {
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    if (!w || !x_dev || !S_dev || n < 0 || nb11 < (size_t)w->K * 4 || (nb11 & 3)) { set_error("bad block_dots arguments"); return GGML_B200_ERR_ARG; }
+    if (n == 0 || w->rows() == 0) return GGML_B200_OK;
+    int rc = launch_quantize(x_dev, n, w->K, nb11, nullptr);
+    if (rc) return rc;
+    rc = ensure_stage((void **)&g.ystage, &g.ystage_cap, (size_t)n * w->rows() * 4);
+    if (rc) return rc;
+    if (path == GGML_B200_PATH_GEMM) {
+        if (!gemm_available(w)) { set_error("tensor-core GEMM path not available for this weight (layout %d)", w->layout); return GGML_B200_ERR_ARG; }
+        return launch_gemm(w, g.ystage, w->rows(), (int)n, S_dev);
+    }
+    return launch_gemv_dump(w, g.ystage, w->rows(), (int)n, S_dev);
+}
+
+}  // extern "C"

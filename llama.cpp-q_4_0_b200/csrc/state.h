@@ -1,0 +1,83 @@
+// state.h -- process-wide state shared by the translation units of libggml_b200.so.
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/ggml-b200.h"
+
+// one device-resident Q4_0 row shard (opaque in the C ABI)
+struct ggml_b200_weight {
+    int64_t M = 0, K = 0;            // shape of the WHOLE tensor (ne01, ne00)
+    int64_t row_lo = 0, row_hi = 0;  // rows this shard holds
+    int     layout = GGML_B200_LAYOUT_PLANES;
+    void *  raw = nullptr;           // LAYOUT_RAW: 18-byte blocks, rows contiguous
+    uint4 * wq = nullptr;            // LAYOUT_PLANES: nibbles [rows][nbk]
+    __half * wd = nullptr;           // LAYOUT_PLANES: scales  [rows][nbk]
+    size_t  dev_bytes = 0;
+    void *  gemm = nullptr;          // tensor-core path's per-weight state (TMA descriptors)
+    int64_t rows() const { return row_hi - row_lo; }
+};
+
+namespace b200 {
+
+constexpr int MAX_DYN_SMEM = 227 * 1024;
+
+struct Tune {
+    int gemv_threads = 512;      // threads per CTA of kernel 2
+    int gemv_ctas_per_sm = 2;    // grid = SMs * this
+    int gemv_unroll = 4;         // 16-byte weight loads in flight per lane
+    int gemv_nc = 0;             // cap on columns per pass (0 = by n)
+};
+
+struct Ctx {
+    bool inited = false;
+    int device = -1;
+    int sm_count = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    int repack = 1;
+    int gemm_min_n = 16;
+    int path = GGML_B200_PATH_AUTO;
+    Tune tune;
+    // activation work buffer (device replacement of params->wdata, ggml.c:11354)
+    int8_t * xq = nullptr;  size_t xq_cap = 0;
+    int2 *   xds = nullptr; size_t xds_cap = 0;
+    // staging for the host-pointer entry point
+    float * xstage = nullptr; size_t xstage_cap = 0;
+    float * ystage = nullptr; size_t ystage_cap = 0;
+    uint64_t launches = 0;
+    char err[512] = {0};
+};
+
+extern Ctx g;
+
+void set_error(const char * fmt, ...);
+int  cuda_fail(cudaError_t e, const char * what, const char * file, int line);
+
+#define CK(call)                                                                   \
+    do {                                                                           \
+        cudaError_t e_ = (call);                                                   \
+        if (e_ != cudaSuccess) return ::b200::cuda_fail(e_, #call, __FILE__, __LINE__); \
+    } while (0)
+
+int ensure_workspace(int64_t n, int64_t K);
+int launch_quantize(const float * x_dev, int64_t n, int64_t K, size_t nb11, void * blocks34_dev);
+int launch_gemv(const ggml_b200_weight * w, float * y, long long ldy, int n);
+// kernel 2 or 3 by n, into y (first element of this shard's column 0), activations already quantized
+int launch_shard(const ggml_b200_weight * w, float * y, long long ldy, int n);
+int mul_mat_dev(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y_dev, size_t nb1);
+
+// kernel 3 (gemm_q4_0_tc.cu)
+int  gemm_init();
+void gemm_shutdown();
+int  gemm_set_tuning(const char * key, int value);
+bool gemm_available(const ggml_b200_weight * w);
+int  gemm_prepare_weight(ggml_b200_weight * w);
+void gemm_release_weight(ggml_b200_weight * w);
+// y: first output element of this shard (column 0), ldy in floats; S != nullptr: also dump S_b
+int  launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int * S);
+
+}  // namespace b200
+
+extern "C" int ggml_b200_set_tuning(const char * key, int value);

@@ -1,0 +1,303 @@
+"""ctypes binding of lib/libggml_b200.so (the C ABI in include/ggml-b200.h).
+
+This is harness plumbing for tests/ and bench.py, not the product: the product is the shared
+library, whose host side is C (the reference is C; see ggml_glue/ for the ggml_tensor glue).
+Method names mirror the C entry points, which mirror the reference seams they replace
+(ggml_cuda_transform_tensor -> upload_q4_0, ggml_cuda_mul_mat -> mul_mat_q4_0, ...).
+
+There is no fallback of any kind: if the library is missing, or no sm_100 GPU is present,
+loading / init raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libggml_b200.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "ggml-b200.h")
+
+OK = 0
+ERR_NO_DEVICE, ERR_ARCH, ERR_CUDA, ERR_ARG, ERR_STATE = -1, -2, -3, -4, -5
+LAYOUT_RAW, LAYOUT_PLANES = 0, 1
+PATH_AUTO, PATH_GEMV, PATH_GEMM = 0, 1, 2
+SHARD_ALIGN = 128
+QK = 32
+
+_vp = C.c_void_p
+_i64 = C.c_int64
+_sz = C.c_size_t
+
+
+class B200Error(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"ggml-b200 error {code}: {msg}")
+        self.code = code
+
+
+def _load() -> C.CDLL:
+    if not os.path.exists(LIB_PATH):
+        raise FileNotFoundError(
+            f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU or PyTorch fallback for this path)")
+    L = C.CDLL(LIB_PATH)
+    sig = {
+        "ggml_b200_init": (C.c_int, [C.c_int]),
+        "ggml_b200_shutdown": (None, []),
+        "ggml_b200_device_count": (C.c_int, []),
+        "ggml_b200_last_error": (C.c_char_p, []),
+        "ggml_b200_sm_count": (C.c_int, []),
+        "ggml_b200_set_repack": (None, [C.c_int]),
+        "ggml_b200_get_repack": (C.c_int, []),
+        "ggml_b200_set_gemm_min_n": (None, [C.c_int]),
+        "ggml_b200_get_gemm_min_n": (C.c_int, []),
+        "ggml_b200_set_path": (None, [C.c_int]),
+        "ggml_b200_set_stream": (None, [_vp]),
+        "ggml_b200_get_stream": (_vp, []),
+        "ggml_b200_set_tuning": (C.c_int, [C.c_char_p, C.c_int]),
+        "ggml_b200_host_malloc": (_vp, [_sz]),
+        "ggml_b200_host_free": (None, [_vp]),
+        "ggml_b200_upload_q4_0": (_vp, [_vp, _i64, _i64, _sz, _i64, _i64]),
+        "ggml_b200_free_weight": (None, [_vp]),
+        "ggml_b200_weight_rows": (_i64, [_vp]),
+        "ggml_b200_weight_row_lo": (_i64, [_vp]),
+        "ggml_b200_weight_M": (_i64, [_vp]),
+        "ggml_b200_weight_K": (_i64, [_vp]),
+        "ggml_b200_weight_layout": (C.c_int, [_vp]),
+        "ggml_b200_weight_device_bytes": (_sz, [_vp]),
+        "ggml_b200_download_q4_0": (C.c_int, [_vp, _vp]),
+        "ggml_b200_quantize_q8_0": (C.c_int, [_vp, _i64, _i64, _sz, _vp]),
+        "ggml_b200_mul_mat_q4_0": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
+        "ggml_b200_mul_mat_q4_0_host": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
+        "ggml_b200_block_dots_q4_0": (C.c_int, [_vp, _vp, _i64, _sz, _vp, C.c_int]),
+        "ggml_b200_comm_unique_id": (C.c_int, [_vp]),
+        "ggml_b200_comm_init": (C.c_int, [C.c_int, C.c_int, _vp]),
+        "ggml_b200_comm_shutdown": (None, []),
+        "ggml_b200_comm_rank": (C.c_int, []),
+        "ggml_b200_comm_world": (C.c_int, []),
+        "ggml_b200_shard_rows": (None, [_i64, C.c_int, C.c_int, C.POINTER(_i64), C.POINTER(_i64)]),
+        "ggml_b200_mul_mat_q4_0_sharded": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
+        "ggml_b200_launch_count": (C.c_uint64, []),
+        "ggml_b200_dev_malloc": (_vp, [_sz]),
+        "ggml_b200_dev_free": (None, [_vp]),
+        "ggml_b200_memcpy_h2d": (C.c_int, [_vp, _vp, _sz]),
+        "ggml_b200_memcpy_d2h": (C.c_int, [_vp, _vp, _sz]),
+        "ggml_b200_synchronize": (C.c_int, []),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype = res
+        fn.argtypes = args
+    return L
+
+
+_L = None
+
+
+def lib() -> C.CDLL:
+    global _L
+    if _L is None:
+        _L = _load()
+    return _L
+
+
+def _check(rc: int) -> None:
+    if rc != OK:
+        raise B200Error(rc, lib().ggml_b200_last_error().decode(errors="replace"))
+
+
+def shard_rows(M: int, rank: int, world: int) -> tuple[int, int]:
+    """Row range rank owns (pure host arithmetic; usable without a GPU)."""
+    lo, hi = _i64(), _i64()
+    lib().ggml_b200_shard_rows(M, rank, world, C.byref(lo), C.byref(hi))
+    return lo.value, hi.value
+
+
+def device_count() -> int:
+    return lib().ggml_b200_device_count()
+
+
+def init(device: int = 0) -> None:
+    _check(lib().ggml_b200_init(device))
+
+
+def shutdown() -> None:
+    lib().ggml_b200_shutdown()
+
+
+def set_repack(on: bool) -> None:
+    lib().ggml_b200_set_repack(1 if on else 0)
+
+
+def set_path(path: int) -> None:
+    lib().ggml_b200_set_path(path)
+
+
+def set_gemm_min_n(n: int) -> None:
+    lib().ggml_b200_set_gemm_min_n(n)
+
+
+def set_tuning(key: str, value: int) -> None:
+    _check(lib().ggml_b200_set_tuning(key.encode(), value))
+
+
+def set_stream(handle: int | None) -> None:
+    lib().ggml_b200_set_stream(_vp(handle) if handle else None)
+
+
+def launch_count() -> int:
+    return int(lib().ggml_b200_launch_count())
+
+
+def sm_count() -> int:
+    return lib().ggml_b200_sm_count()
+
+
+def synchronize() -> None:
+    _check(lib().ggml_b200_synchronize())
+
+
+class DevBuf:
+    """A raw device allocation owned by the library's allocator helpers."""
+
+    def __init__(self, nbytes: int):
+        self.nbytes = int(nbytes)
+        self.ptr = lib().ggml_b200_dev_malloc(self.nbytes)
+        if not self.ptr:
+            raise B200Error(ERR_CUDA, lib().ggml_b200_last_error().decode(errors="replace"))
+
+    @classmethod
+    def from_numpy(cls, a: np.ndarray) -> "DevBuf":
+        a = np.ascontiguousarray(a)
+        b = cls(a.nbytes)
+        _check(lib().ggml_b200_memcpy_h2d(b.ptr, a.ctypes.data_as(_vp), a.nbytes))
+        return b
+
+    def to_numpy(self, dtype, shape) -> np.ndarray:
+        out = np.empty(shape, dtype=dtype)
+        assert out.nbytes <= self.nbytes
+        _check(lib().ggml_b200_memcpy_d2h(out.ctypes.data_as(_vp), self.ptr, out.nbytes))
+        return out
+
+    def free(self) -> None:
+        if self.ptr:
+            lib().ggml_b200_dev_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Weight:
+    """A device-resident Q4_0 row shard (ggml_b200_upload_q4_0)."""
+
+    def __init__(self, blocks: np.ndarray, row_lo: int = 0, row_hi: int | None = None):
+        """blocks: uint8 [M][K/32][18] (the reference's block_q4_0 rows, contiguous)."""
+        blocks = np.ascontiguousarray(blocks, dtype=np.uint8)
+        assert blocks.ndim == 3 and blocks.shape[2] == 18
+        M, nbk = blocks.shape[0], blocks.shape[1]
+        self.M, self.K = M, nbk * QK
+        if row_hi is None:
+            row_hi = M
+        self.h = lib().ggml_b200_upload_q4_0(blocks.ctypes.data_as(_vp), M, self.K, nbk * 18, row_lo, row_hi)
+        if not self.h:
+            raise B200Error(ERR_ARG, lib().ggml_b200_last_error().decode(errors="replace"))
+        self.row_lo, self.row_hi = row_lo, row_hi
+
+    @property
+    def rows(self) -> int:
+        return int(lib().ggml_b200_weight_rows(self.h))
+
+    @property
+    def layout(self) -> int:
+        return int(lib().ggml_b200_weight_layout(self.h))
+
+    @property
+    def device_bytes(self) -> int:
+        return int(lib().ggml_b200_weight_device_bytes(self.h))
+
+    def download(self) -> np.ndarray:
+        out = np.empty((self.rows, self.K // QK, 18), dtype=np.uint8)
+        _check(lib().ggml_b200_download_q4_0(self.h, out.ctypes.data_as(_vp)))
+        return out
+
+    def free(self) -> None:
+        if self.h:
+            lib().ggml_b200_free_weight(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def quantize_q8_0(x: np.ndarray) -> np.ndarray:
+    """Kernel 1 on host data: f32 [n][K] -> reference-format blocks uint8 [n][K/32][34]."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    n, K = x.shape
+    xd = DevBuf.from_numpy(x)
+    out = DevBuf(max(1, n * (K // QK) * 34))
+    _check(lib().ggml_b200_quantize_q8_0(xd.ptr, n, K, K * 4, out.ptr))
+    synchronize()
+    res = out.to_numpy(np.uint8, (n, K // QK, 34))
+    xd.free()
+    out.free()
+    return res
+
+
+def mul_mat_host(w: Weight, x: np.ndarray, y: np.ndarray | None = None) -> np.ndarray:
+    """The reference-facing call: host x [n][K] f32 -> host y [n][M] f32 (this shard's columns)."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    n, K = x.shape
+    assert K == w.K
+    if y is None:
+        y = np.zeros((n, w.M), dtype=np.float32)
+    _check(lib().ggml_b200_mul_mat_q4_0_host(w.h, x.ctypes.data_as(_vp), n, K * 4,
+                                             y.ctypes.data_as(_vp), w.M * 4))
+    return y
+
+
+def mul_mat_dev(w: Weight, x_dev_ptr: int, n: int, y_dev_ptr: int, nb11: int | None = None,
+                nb1: int | None = None) -> None:
+    _check(lib().ggml_b200_mul_mat_q4_0(w.h, _vp(x_dev_ptr), n, nb11 or w.K * 4, _vp(y_dev_ptr), nb1 or w.M * 4))
+
+
+def mul_mat_sharded_dev(w: Weight, x_dev_ptr: int, n: int, y_dev_ptr: int) -> None:
+    _check(lib().ggml_b200_mul_mat_q4_0_sharded(w.h, _vp(x_dev_ptr), n, w.K * 4, _vp(y_dev_ptr), w.M * 4))
+
+
+def block_dots(w: Weight, x: np.ndarray, path: int = PATH_GEMV) -> np.ndarray:
+    """int32 S_b [n][rows][K/32] as the chosen kernel forms them."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    n, K = x.shape
+    nbk = K // QK
+    xd = DevBuf.from_numpy(x)
+    S = DevBuf(max(4, n * w.rows * nbk * 4))
+    _check(lib().ggml_b200_block_dots_q4_0(w.h, xd.ptr, n, K * 4, S.ptr, path))
+    synchronize()
+    out = S.to_numpy(np.int32, (n, w.rows, nbk))
+    xd.free()
+    S.free()
+    return out
+
+
+def comm_unique_id() -> bytes:
+    buf = C.create_string_buffer(128)
+    _check(lib().ggml_b200_comm_unique_id(buf))
+    return buf.raw
+
+
+def comm_init(rank: int, world: int, uid: bytes) -> None:
+    buf = C.create_string_buffer(uid, 128)
+    _check(lib().ggml_b200_comm_init(rank, world, buf))
+
+
+def comm_shutdown() -> None:
+    lib().ggml_b200_comm_shutdown()

@@ -1,0 +1,116 @@
+/*
+ * ref_shim.c -- thin C front door onto the UNMODIFIED reference ggml.c (compiled from
+ * /root/reference where it lies; see oracle/Makefile).  TEST INFRASTRUCTURE ONLY.
+ *
+ * Exposes the reference's own static functions through its public test hook
+ * ggml_internal_get_quantize_fn (ggml.h:1533, ggml.c:1712-1715) and the whole operator through
+ * the public graph API (ggml_mul_mat + ggml_build_forward + ggml_graph_compute), the same way
+ * examples/benchmark/benchmark-matmult.cpp:181-190,224 drives it.
+ */
+#include "ggml.h"
+#include <stdlib.h>
+#include <string.h>
+#include <stdio.h>
+
+static int g_inited = 0;
+
+/* ggml_init fills the fp16 table on first call (ggml.c:4245-4252) */
+void ref_init(void) {
+    if (g_inited) return;
+    struct ggml_init_params p = { 1024, NULL, true };
+    struct ggml_context * ctx = ggml_init(p);
+    ggml_free(ctx);
+    g_inited = 1;
+}
+
+float    ref_fp16_to_fp32(uint16_t h) { ref_init(); return ggml_fp16_to_fp32(h); }
+uint16_t ref_fp32_to_fp16(float f)    { ref_init(); return ggml_fp32_to_fp16(f); }
+
+void ref_quantize_row_q4_0(const float * x, void * y, int k) {
+    ref_init();
+    ggml_internal_get_quantize_fn(GGML_TYPE_Q4_0).quantize_row_q(x, y, k);
+}
+
+void ref_dequantize_row_q4_0(const void * x, float * y, int k) {
+    ref_init();
+    ggml_internal_get_quantize_fn(GGML_TYPE_Q4_0).dequantize_row_q(x, y, k);
+}
+
+/* quantize_row_q_dot of Q4_0 == quantize_row_q8_0 (ggml.c:1623), SIMD branch of the build host */
+void ref_quantize_row_q8_0(const float * x, void * y, int k) {
+    ref_init();
+    ggml_internal_get_quantize_fn(GGML_TYPE_Q4_0).quantize_row_q_dot(x, y, k);
+}
+
+void ref_quantize_row_q8_0_reference(const float * x, void * y, int k) {
+    ref_init();
+    ggml_internal_get_quantize_fn(GGML_TYPE_Q8_0).quantize_row_q_reference(x, y, k);
+}
+
+float ref_vec_dot_q4_0_q8_0(int k, const void * x, const void * y) {
+    ref_init();
+    float s = 0.0f;
+    ggml_internal_get_quantize_fn(GGML_TYPE_Q4_0).vec_dot_q(k, &s, x, y);
+    return s;
+}
+
+/* bulk weight quantizer, ggml.c:19157-19178 */
+size_t ref_quantize_q4_0(const float * src, void * dst, int n, int k) {
+    ref_init();
+    int64_t hist[16] = {0};
+    return ggml_quantize_q4_0(src, dst, n, k, hist);
+}
+
+/* ---- whole operator through the graph scheduler ------------------------------------------ */
+struct ref_mm {
+    struct ggml_context * ctx;
+    struct ggml_tensor  * w;
+    struct ggml_tensor  * x;
+    struct ggml_tensor  * y;
+    struct ggml_cgraph    gf;
+    int64_t M, K, n;
+};
+
+/* W: M*K/32 q4_0 blocks, contiguous.  Returns an opaque handle. */
+struct ref_mm * ref_mm_create(int64_t M, int64_t K, int64_t n, const void * W) {
+    ref_init();
+    struct ref_mm * h = (struct ref_mm *)calloc(1, sizeof(*h));
+    const size_t wbytes = (size_t)M * (K / 32) * 18;
+    size_t ctx_size = wbytes + (size_t)n * K * 4 + (size_t)n * M * 4
+                    + (size_t)n * (K / 32) * 34 + (16u << 20);
+    struct ggml_init_params p = { ctx_size, NULL, false };
+    h->ctx = ggml_init(p);
+    if (!h->ctx) { free(h); return NULL; }
+    h->M = M; h->K = K; h->n = n;
+    h->w = ggml_new_tensor_2d(h->ctx, GGML_TYPE_Q4_0, K, M);
+    memcpy(h->w->data, W, wbytes);
+    h->x = ggml_new_tensor_2d(h->ctx, GGML_TYPE_F32, K, n);
+    h->y = ggml_mul_mat(h->ctx, h->w, h->x);
+    h->gf = ggml_build_forward(h->y);
+    return h;
+}
+
+/* X: [n][K] f32 contiguous, Y: [n][M] f32 contiguous */
+void ref_mm_run(struct ref_mm * h, const float * X, float * Y, int n_threads) {
+    memcpy(h->x->data, X, (size_t)h->n * h->K * 4);
+    h->gf.n_threads = n_threads;
+    ggml_graph_compute(h->ctx, &h->gf);
+    memcpy(Y, h->y->data, (size_t)h->n * h->M * 4);
+}
+
+/* compute only (inputs already in place): what the CPU baseline times */
+void ref_mm_compute(struct ref_mm * h, int n_threads) {
+    h->gf.n_threads = n_threads;
+    ggml_graph_compute(h->ctx, &h->gf);
+}
+
+float * ref_mm_x(struct ref_mm * h) { return (float *)h->x->data; }
+float * ref_mm_y(struct ref_mm * h) { return (float *)h->y->data; }
+
+void ref_mm_free(struct ref_mm * h) {
+    if (!h) return;
+    ggml_free(h->ctx);
+    free(h);
+}
+
+int64_t ref_time_us(void) { ref_init(); return ggml_time_us(); }

@@ -1,0 +1,251 @@
+"""GPU parity tests (run with -m gpu on a B200).  Everything goes through the C ABI
+(lib/libggml_b200.so via ctypes); the oracle is only the checker.
+
+Bars (BASELINE.json north_star):
+  * q8_0 activation blocks: bit-exact (34-byte compare)
+  * int32 per-block dots S_b: bit-exact
+  * fp32 outputs: max|dY| / max|Y| per column <= 1e-4, and max|dY| / sum_b|S_b*dw*dx| <= 1e-4
+    (per-element relative error is meaningless on near-zero outputs; only the
+    accumulation order differs from the CPU)
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-4
+
+
+def make_weights(port, ref, M, K, seed=0x5EED0001):
+    wf = port.synthetic(M * K, seed + M * 31 + K, 0.02).reshape(M, K)
+    q = ref.quantize_q4_0_bulk(wf) if ref is not None else port.quantize_q4_0(wf)
+    return q
+
+
+def make_x(port, n, K, seed=0x5EED0002):
+    return port.synthetic(n * K, seed + n, 1.0, 100).reshape(n, K)
+
+
+def oracle_Y(port, ref, W, X, threads=8):
+    """CPU truth: the compiled reference when present (fast, multi-threaded), else the C port."""
+    if ref is not None:
+        return ref.mul_mat(W, X, n_threads=threads)
+    return port.mul_mat(W, X, avx2_order=True)
+
+
+def scale_sum(port, W, X):
+    """sum_b |S_b * dw * dx| per output, the magnitude actually summed (metric ii)."""
+    q8 = port.quantize_q8_0(X)
+    S = port.block_dots_matrix(W, q8).astype(np.float64)                     # [n][M][nbk]
+    dw = W[:, :, :2].copy().view(np.float16).astype(np.float64)[..., 0]      # [M][nbk]
+    dx = q8[:, :, :2].copy().view(np.float16).astype(np.float64)[..., 0]     # [n][nbk]
+    return np.sum(np.abs(S * dw[None] * dx[:, None, :]), axis=-1)            # [n][M]
+
+
+def assert_close(Y, Yref, denom2=None):
+    assert Y.shape == Yref.shape
+    assert np.isfinite(Y).all()
+    d = np.abs(Y.astype(np.float64) - Yref.astype(np.float64))
+    col_max = np.max(np.abs(Yref), axis=1, keepdims=True)
+    col_max[col_max == 0] = 1.0
+    m1 = float(np.max(d / col_max))
+    assert m1 <= TOL, f"max|dY|/max|Y| = {m1:.3e}"
+    if denom2 is not None:
+        dd = np.where(denom2 > 0, denom2, 1.0)
+        m2 = float(np.max(d / dd))
+        assert m2 <= TOL, f"max|dY|/sum|terms| = {m2:.3e}"
+
+
+# ---------------------------------------------------------------------------- kernel 1
+def test_quantize_q8_0_golden_bit_exact(b200, golden):
+    assert np.array_equal(b200.quantize_q8_0(golden["cos_b"][None, :]), golden["cos_b_q8_0"][None])
+    assert np.array_equal(b200.quantize_q8_0(golden["op_X"]), golden["op_q8"])
+
+
+def test_quantize_q8_0_edge_cases_bit_exact(b200, golden):
+    """zero blocks, single non-zero, exact .5 ties (even rounding), amax in last lane, fp16
+    denormal / zero / inf scale, inf input."""
+    got = b200.quantize_q8_0(golden["edge_X"])
+    want = golden["edge_q8"]
+    for i in range(want.shape[0]):
+        assert np.array_equal(got[i], want[i]), f"edge row {i}"
+
+
+@pytest.mark.parametrize("n,K", [(1, 64), (1, 4096), (3, 4544), (7, 11008), (33, 4096), (512, 4096), (2, 18176)])
+def test_quantize_q8_0_random_bit_exact(b200, port, n, K):
+    rng = np.random.default_rng(n * 1000 + K)
+    x = (rng.standard_normal((n, K)) * rng.choice([1e-4, 1.0, 30.0], size=(n, 1))).astype(np.float32)
+    assert np.array_equal(b200.quantize_q8_0(x), port.quantize_q8_0(x))
+
+
+def test_quantize_q8_0_strided_and_unaligned_rows(b200, port):
+    """src1 rows with a byte stride nb11 > K*4 (ggml views) and a base that is only 4-byte aligned."""
+    import ctypes as C
+    n, K, ld = 5, 256, 300
+    big = port.synthetic(n * ld + 1, 99, 1.0)
+    for off in (0, 1):
+        x = np.lib.stride_tricks.as_strided(big[off:], shape=(n, K), strides=(ld * 4, 4))
+        xd = b200.DevBuf.from_numpy(big)
+        out = b200.DevBuf(n * (K // 32) * 34)
+        rc = b200.lib().ggml_b200_quantize_q8_0(C.c_void_p(xd.ptr + 4 * off), n, K, ld * 4, out.ptr)
+        assert rc == 0, b200.lib().ggml_b200_last_error()
+        b200.synchronize()
+        got = out.to_numpy(np.uint8, (n, K // 32, 34))
+        assert np.array_equal(got, port.quantize_q8_0(np.ascontiguousarray(x)))
+
+
+# ---------------------------------------------------------------------------- upload / repack
+@pytest.mark.parametrize("repack", [True, False])
+def test_upload_download_round_trip(b200, port, ref, repack):
+    M, K = 200, 4544
+    W = make_weights(port, ref, M, K)
+    b200.set_repack(repack)
+    try:
+        w = b200.Weight(W)
+        assert w.layout == (b200.LAYOUT_PLANES if repack else b200.LAYOUT_RAW)
+        assert w.device_bytes == M * (K // 32) * 18          # algorithmic bytes unchanged by the repack
+        assert np.array_equal(w.download(), W)
+        ws = b200.Weight(W, 64, 130)                          # a row shard
+        assert ws.rows == 66 and np.array_equal(ws.download(), W[64:130])
+        w.free(); ws.free()
+    finally:
+        b200.set_repack(True)
+
+
+# ---------------------------------------------------------------------------- kernel 2: S_b and Y
+@pytest.mark.parametrize("repack", [True, False])
+@pytest.mark.parametrize("n", [1, 2, 3, 5, 8, 11])
+def test_gemv_block_dots_bit_exact(b200, port, ref, repack, n):
+    M, K = 70, 1088            # ragged: M not a multiple of anything, nbk = 34 (partial lane sweep)
+    W = make_weights(port, ref, M, K)
+    X = make_x(port, n, K)
+    b200.set_repack(repack)
+    try:
+        w = b200.Weight(W)
+        S = b200.block_dots(w, X, b200.PATH_GEMV)
+        w.free()
+    finally:
+        b200.set_repack(True)
+    want = port.block_dots_matrix(W, port.quantize_q8_0(X))
+    assert np.array_equal(S, want)
+
+
+def test_gemv_golden_op(b200, golden, port):
+    b200.set_path(b200.PATH_GEMV)
+    try:
+        w = b200.Weight(golden["op_W"])
+        Y = b200.mul_mat_host(w, golden["op_X"])
+        w.free()
+    finally:
+        b200.set_path(b200.PATH_AUTO)
+    assert_close(Y, golden["op_Y"], scale_sum(port, golden["op_W"], golden["op_X"]))
+
+
+def test_gemv_cos_vectors_of_reference_test(b200, golden):
+    """tests/test-quantize-fns.cpp's own vectors: one row, K = 4096 -> the 4470.44141 dot."""
+    w = b200.Weight(golden["cos_a_q4_0"][None])
+    S = b200.block_dots(w, golden["cos_b"][None], b200.PATH_GEMV)
+    Y = b200.mul_mat_host(w, golden["cos_b"][None])
+    w.free()
+    assert np.array_equal(S[0, 0], golden["cos_S"]) and int(S.sum()) == -1034162
+    assert abs(float(Y[0, 0]) - float(golden["cos_dot"][0])) <= 1e-6 * 4470.44141 * 4
+
+
+@pytest.mark.parametrize("repack", [True, False])
+@pytest.mark.parametrize("M,K,n", [(1, 64, 1), (33, 64, 1), (4096, 4096, 1), (4672, 4544, 1), (1000, 11008, 1),
+                                   (777, 4096, 2), (512, 4544, 4), (300, 18176, 3), (256, 4096, 9)])
+def test_gemv_outputs_vs_oracle(b200, port, ref, repack, M, K, n):
+    W = make_weights(port, ref, M, K)
+    X = make_x(port, n, K)
+    b200.set_repack(repack)
+    b200.set_path(b200.PATH_GEMV)
+    try:
+        w = b200.Weight(W)
+        Y = b200.mul_mat_host(w, X)
+        w.free()
+    finally:
+        b200.set_repack(True)
+        b200.set_path(b200.PATH_AUTO)
+    assert_close(Y, oracle_Y(port, ref, W, X), scale_sum(port, W, X) if M * K * n <= 1 << 24 else None)
+
+
+def test_extreme_scales_and_zero_inputs(b200, port, ref):
+    """all-zero activations -> exact zeros; zero weight blocks; tiny / huge activation scales."""
+    M, K = 64, 512
+    W = make_weights(port, ref, M, K)
+    W[5, 3, :] = 0                                # an all-zero weight block (d = 0, q = 0)
+    w = b200.Weight(W)
+    Y0 = b200.mul_mat_host(w, np.zeros((2, K), np.float32))
+    assert np.array_equal(Y0, np.zeros((2, M), np.float32))
+    for scale in (1e-6, 1e3):
+        X = make_x(port, 2, K) * np.float32(scale)
+        assert_close(b200.mul_mat_host(w, X), oracle_Y(port, ref, W, X), scale_sum(port, W, X))
+    w.free()
+
+
+def test_empty_and_sharded_rows(b200, port, ref):
+    M, K, n = 300, 1024, 2
+    W = make_weights(port, ref, M, K)
+    X = make_x(port, n, K)
+    Yref = oracle_Y(port, ref, W, X)
+    # n = 0 is a no-op
+    w = b200.Weight(W)
+    assert b200.mul_mat_host(w, np.zeros((0, K), np.float32)).shape == (0, M)
+    w.free()
+    # two row shards write disjoint column ranges of the same dst (ggml-cuda.cu:2780-2797 semantics)
+    Y = np.full((n, M), np.nan, np.float32)
+    for lo, hi in ((0, 128), (128, 300)):
+        ws = b200.Weight(W, lo, hi)
+        b200.mul_mat_host(ws, X, Y)
+        ws.free()
+    assert_close(Y, Yref, scale_sum(port, W, X))
+    # an empty shard leaves dst untouched
+    Y2 = np.full((n, M), 7.0, np.float32)
+    we = b200.Weight(W, 300, 300)
+    b200.mul_mat_host(we, X, Y2)
+    we.free()
+    assert np.all(Y2 == 7.0)
+
+
+def test_device_pointer_entry_with_strides(b200, port, ref):
+    """ggml_b200_mul_mat_q4_0 with device pointers and padded src1 / dst rows."""
+    M, K, n = 130, 256, 3
+    ldx, ldy = K + 8, M + 4
+    W = make_weights(port, ref, M, K)
+    X = make_x(port, n, K)
+    Xp = np.zeros((n, ldx), np.float32); Xp[:, :K] = X
+    w = b200.Weight(W)
+    xd = b200.DevBuf.from_numpy(Xp)
+    yd = b200.DevBuf.from_numpy(np.full((n, ldy), -5.0, np.float32))
+    b200.mul_mat_dev(w, xd.ptr, n, yd.ptr, nb11=ldx * 4, nb1=ldy * 4)
+    b200.synchronize()
+    Yp = yd.to_numpy(np.float32, (n, ldy))
+    w.free()
+    assert np.all(Yp[:, M:] == -5.0)
+    assert_close(Yp[:, :M], oracle_Y(port, ref, W, X), scale_sum(port, W, X))
+
+
+def test_linearity_property_full_size(b200, port, ref):
+    """Size-independent property at a BASELINE shape (11008 x 4096): with activations that are
+    exactly representable after quantization (integers * power of two, amax = 127 per block), the
+    op is exact in the q8 domain, so Y(2x) == 2 * Y(x) bit-for-bit."""
+    M, K = 11008, 4096
+    W = make_weights(port, ref, M, K)
+    rng = np.random.default_rng(5)
+    xi = rng.integers(-127, 128, size=(1, K)).astype(np.float32)
+    xi[:, ::32] = 127.0
+    w = b200.Weight(W)
+    Y1 = b200.mul_mat_host(w, xi * np.float32(0.25))
+    Y2 = b200.mul_mat_host(w, xi * np.float32(0.5))
+    w.free()
+    assert np.array_equal((Y1 * np.float32(2)).view(np.uint32), Y2.view(np.uint32))
+    assert_close(Y1, oracle_Y(port, ref, W, xi * np.float32(0.25)))
+
+
+def test_launch_counter_counts_kernels(b200, port, ref):
+    W = make_weights(port, ref, 64, 256)
+    w = b200.Weight(W)
+    c0 = b200.launch_count()
+    b200.mul_mat_host(w, make_x(port, 1, 256))
+    assert b200.launch_count() - c0 == 2          # kernel 1 + kernel 2
+    w.free()
