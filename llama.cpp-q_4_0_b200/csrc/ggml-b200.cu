@@ -189,8 +189,10 @@ int launch_shard(const ggml_b200_weight * w, float * y, long long ldy, int n) {
 // x_dev/y_dev device pointers; y_dev addresses the full dst, this shard writes [row_lo,row_hi)
 int mul_mat_dev(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y_dev, size_t nb1) {
     if (n == 0 || w->rows() == 0) return GGML_B200_OK;
-    int rc = launch_quantize(x_dev, n, w->K, nb11, nullptr);
-    if (rc) return rc;
+    if (!g.tune.skip_quantize) {
+        int rc = launch_quantize(x_dev, n, w->K, nb11, nullptr);
+        if (rc) return rc;
+    }
     float * y = y_dev + w->row_lo;
     const long long ldy = (long long)(nb1 / 4);
     return launch_shard(w, y, ldy, (int)n);
@@ -275,6 +277,7 @@ int ggml_b200_set_tuning(const char * key, int value) {
     else if (!strcmp(key, "gemv_ctas_per_sm")) { if (value < 1 || value > 16) return GGML_B200_ERR_ARG; g.tune.gemv_ctas_per_sm = value; }
     else if (!strcmp(key, "gemv_unroll"))  { g.tune.gemv_unroll = value; }
     else if (!strcmp(key, "gemv_nc"))      { g.tune.gemv_nc = value; }
+    else if (!strcmp(key, "skip_quantize")) { g.tune.skip_quantize = value != 0; }
     else return gemm_set_tuning(key, value);
     return GGML_B200_OK;
 }

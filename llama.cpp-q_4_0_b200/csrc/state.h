@@ -28,6 +28,7 @@ struct Tune {
     int gemv_ctas_per_sm = 2;    // grid = SMs * this
     int gemv_unroll = 4;         // 16-byte weight loads in flight per lane
     int gemv_nc = 0;             // cap on columns per pass (0 = by n)
+    int skip_quantize = 0;       // bench only: reuse the activations quantized by the previous call
 };
 
 struct Ctx {
