@@ -1,0 +1,553 @@
+#!/usr/bin/env python
+"""bench.py -- Q4_0 x F32 mul_mat throughput on B200 (BASELINE.json metric), one JSON line.
+
+A "step" is one pass of the hot path over one synthetic decode matmul set:
+  N = 1 : LLaMA-7B Q4_0 decode matmul set, n = 1 (BASELINE configs[1]): 32 layers x
+          (4x 4096x4096 attn, 2x 11008x4096 FFN up/gate, 1x 4096x11008 FFN down) + 32000x4096
+          output = 225 matmuls, 3.7 GB of Q4_0 weights streamed once per step (>> 126 MB L2).
+  N > 1 : LLaMA-65B decode matmul set (BASELINE configs[4]: 8192x8192, 22016x8192, 8192x22016,
+          + 32000x8192 output), every weight row-sharded over the N ranks
+          (ggml_b200_shard_rows) and every dst re-assembled by an NCCL all-gather over NVLink.
+
+value   = algorithmic bytes of the set (18*M*K/32 + 4*K + 4*M per matmul) / step time,
+          activations already resident in HBM, CUDA-graph replay, CUDA events, max over ranks.
+e2e     = the same metric through the reference-facing call ggml_b200_mul_mat_q4_0_host with
+          pinned HOST buffers: H2D of x and D2H of y inside the timed region for every matmul.
+roofline= the GEMV kernel alone (activations pre-quantized), algorithmic bytes / CUDA-event time,
+          against MEASURED_PEAKS.json hbm_gbs.
+cpu_baseline = the reference's own CPU code (oracle/_ref, ggml_graph_compute with all host
+          threads) on a bounded sample of the same workload.
+`--impl reference` times only that CPU arm and prints it with "impl": "reference".
+"""
+import argparse
+import ctypes as C
+import importlib.util
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "llama.cpp-q_4_0_b200")
+sys.path.insert(0, ROOT)
+
+METRIC = "q4_0_mul_mat_n1_GBps"
+UNIT = "GB/s"
+
+WORKLOADS = {
+    # name: (n_layers, per-layer [(M, K, count)], [(M, K) once])
+    "llama7b_decode_n1": (32, [(4096, 4096, 4), (11008, 4096, 2), (4096, 11008, 1)], [(32000, 4096)]),
+    "llama65b_decode_n1_rowsharded": (80, [(8192, 8192, 4), (22016, 8192, 2), (8192, 22016, 1)], [(32000, 8192)]),
+}
+
+
+def algo_bytes(M, K, n=1):
+    return 18 * M * K // 32 + 4 * K * n + 4 * M * n
+
+
+def matmul_list(workload, layers=None):
+    L, per_layer, once = WORKLOADS[workload]
+    if layers is not None:
+        L = min(L, layers)
+    out = []
+    for _ in range(L):
+        for (M, K, c) in per_layer:
+            out += [(M, K)] * c
+    out += list(once)
+    return out
+
+
+def load_binding():
+    name = "ggml_b200"
+    if name in sys.modules:
+        return sys.modules[name]
+    spec = importlib.util.spec_from_file_location(name, os.path.join(PKG, "ggml_b200.py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def random_q4_0(rng, M, K):
+    """random-init Q4_0 blocks: uniform nibbles, fp16 scale ~ |N(0, 0.02)| * 3 / 8 with random sign
+    (the scale a block of N(0, 0.02) weights gets from d = max / -8, ggml.c:932)."""
+    nbk = K // 32
+    blk = np.empty((M, nbk, 18), dtype=np.uint8)
+    blk[:, :, 2:] = rng.integers(0, 256, size=(M, nbk, 16), dtype=np.uint8)
+    d = (0.02 * (2.0 + np.abs(rng.standard_normal((M, nbk), dtype=np.float32))) / 8.0)
+    d *= rng.choice(np.array([-1.0, 1.0], np.float32), size=(M, nbk))
+    blk[:, :, :2] = d.astype(np.float16).view(np.uint8).reshape(M, nbk, 2)
+    return blk
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, copy bandwidth)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi sampled DURING the timed regions (B200_PROFILING.md recipe)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons, pw = [], None, set(), []
+        for (t, line) in self.rows:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                if t0 <= t <= t1 + 0.1:
+                    sm.append(float(parts[0]))
+                    pw.append(float(parts[2]))
+                mx = float(parts[1])
+            except ValueError:
+                continue
+            if t0 <= t <= t1 + 0.1:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------------- CPU arm
+def cpu_reference_arm(workload, steps, warmup, budget_s=20.0):
+    """The reference's own CPU path (ggml_graph_compute -> ggml_compute_forward_mul_mat_q_f32 ->
+    AVX2 quantize_row_q8_0 + ggml_vec_dot_q4_0_q8_0) from oracle/_ref, all host threads, on a
+    bounded sample: 2 layers of the set + the output matmul, distinct weights per matmul
+    (so the sample, ~0.3-1 GB, does not sit in the CPU's caches).  Falls back to the scalar C port
+    (kind "port", 1 thread, smaller sample) where oracle/_ref is absent."""
+    import oracle
+    R = oracle.ref()
+    cores = os.cpu_count() or 1
+    rng = np.random.default_rng(1234)
+    L, per_layer, once = WORKLOADS[workload]
+    if R is not None:
+        shapes = matmul_list(workload, layers=2)
+        kind = "reference"
+        handles = []
+        for (M, K) in shapes:
+            h = R.Handle(R, random_q4_0(rng, M, K), 1)
+            h.set_x(rng.standard_normal((1, K), dtype=np.float32))
+            handles.append(h)
+        sample_bytes = sum(algo_bytes(M, K) for (M, K) in shapes)
+
+        def one_step():
+            for h in handles:
+                h.compute(cores)
+        sample = (f"2 of {L} layers + output matmul of {workload} ({len(shapes)} matmuls, {sample_bytes / 1e6:.0f} MB), "
+                  f"ggml_graph_compute n_threads={cores}, {'-march=native' if R.native else '-march=x86-64-v3'} build of the unmodified reference")
+    else:
+        P = oracle.port()
+        kind, cores = "port", 1
+        shapes = [(M, K) for (M, K, _) in per_layer]
+        Ws = [random_q4_0(rng, M, K) for (M, K) in shapes]
+        Xs = [rng.standard_normal((1, K), dtype=np.float32) for (_, K) in shapes]
+        sample_bytes = sum(algo_bytes(M, K) for (M, K) in shapes)
+
+        def one_step():
+            for W, X in zip(Ws, Xs):
+                P.mul_mat(W, X, avx2_order=True)
+        sample = f"one matmul per distinct shape of {workload} ({sample_bytes / 1e6:.0f} MB), scalar C port, 1 thread"
+    for _ in range(max(1, min(warmup, 3))):
+        one_step()
+    t_start = time.perf_counter()
+    done = 0
+    times = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        one_step()
+        times.append(time.perf_counter() - t0)
+        done += 1
+        if time.perf_counter() - t_start > budget_s:
+            break
+    mean = float(np.mean(times))
+    if R is not None:
+        for h in handles:
+            h.close()
+    return {"value": sample_bytes / mean / 1e9, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": sample, "steps_timed": done, "ms_per_sample_step": mean * 1e3,
+            "best_value": sample_bytes / float(np.min(times)) / 1e9}
+
+
+def run_reference_impl(args, workload, rank):
+    if rank != 0:
+        return
+    cb = cpu_reference_arm(workload, args.steps, args.warmup, budget_s=60.0)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": cb["steps_timed"], "warmup": min(args.warmup, 3), "ms_per_step": cb["ms_per_sample_step"],
+        "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None,
+        "dtype": "int8 dot (q4_0 x q8_0), fp32 scale+accumulate", "data": "synthetic",
+        "config": {"workload": workload, "n": 1, "note": "reference CPU path; each step is a bounded sample of the workload"},
+        "cpu_baseline": cb,
+        "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------- GPU arm
+class PinnedArray:
+    """numpy view over pinned host memory from ggml_b200_host_malloc (ggml_cuda_host_malloc's mirror)."""
+
+    def __init__(self, mod, shape, dtype=np.float32):
+        self.mod = mod
+        nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self.ptr = mod.lib().ggml_b200_host_malloc(max(nbytes, 16))
+        if not self.ptr:
+            raise RuntimeError("pinned allocation failed")
+        buf = (C.c_char * max(nbytes, 16)).from_address(self.ptr)
+        self.a = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+    def free(self):
+        if self.ptr:
+            self.mod.lib().ggml_b200_host_free(self.ptr)
+            self.ptr = None
+
+
+def run_gpu_arm(args, workload, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+
+    mod = load_binding()
+    torch.cuda.set_device(local_rank)
+    mod.init(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        uid = [mod.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        mod.comm_init(rank, world, uid[0])
+
+    stream = torch.cuda.Stream()
+    mod.set_stream(stream.cuda_stream)
+
+    L, per_layer, once = WORKLOADS[workload]
+    if args.layers:
+        L = min(L, args.layers)
+    rng = np.random.default_rng(20261104 + 7919 * rank)
+
+    # ---- weights: one random-init layer generated on the host, uploaded once per layer so every
+    # layer has its own HBM copy (timing needs distinct addresses, not distinct values)
+    t_setup = time.time()
+    layer_shapes = []
+    for (M, K, c) in per_layer:
+        layer_shapes += [(M, K)] * c
+    host_blocks = {}
+    weights = []        # (Weight, M, K)
+
+    # the C ABI takes the FULL tensor pointer + [row_lo,row_hi); to avoid generating rows this rank
+    # never uploads, hand it a pointer displaced by -row_lo rows (only rows [lo,hi) are read).
+    def upload_shard(M, K, key):
+        lo, hi = mod.shard_rows(M, rank, world)
+        if key not in host_blocks:
+            host_blocks[key] = random_q4_0(rng, max(hi - lo, 1), K)
+        blk = host_blocks[key]
+        nb1 = (K // 32) * 18
+        base = blk.ctypes.data - lo * nb1
+        h = mod.lib().ggml_b200_upload_q4_0(C.c_void_p(base), M, K, nb1, lo, hi)
+        if not h:
+            raise RuntimeError(mod.lib().ggml_b200_last_error().decode())
+        return h
+
+    handles = []
+    for layer in range(L):
+        for i, (M, K) in enumerate(layer_shapes):
+            handles.append((upload_shard(M, K, ("L", i)), M, K))
+    for i, (M, K) in enumerate(once):
+        handles.append((upload_shard(M, K, ("O", i)), M, K))
+    setup_s = time.time() - t_setup
+    total_bytes = sum(algo_bytes(M, K) for (_, M, K) in handles)
+    weight_bytes = sum(18 * M * K // 32 for (_, M, K) in handles)
+
+    # ---- activations: one x per distinct K, one y per distinct M (device resident)
+    Ks = sorted({K for (_, _, K) in handles})
+    Ms = sorted({M for (_, M, _) in handles})
+    xs = {K: torch.from_numpy(rng.standard_normal((1, K), dtype=np.float32)).cuda() for K in Ks}
+    if world > 1:
+        for K in Ks:
+            dist.broadcast(xs[K], src=0)       # x is replicated on every rank
+    ys = {M: torch.zeros((1, M), dtype=torch.float32, device="cuda") for M in Ms}
+    torch.cuda.synchronize()
+    L_ = mod.lib()
+    op = L_.ggml_b200_mul_mat_q4_0_sharded if world > 1 else L_.ggml_b200_mul_mat_q4_0
+
+    def one_step():
+        for (h, M, K) in handles:
+            rc = op(h, C.c_void_p(xs[K].data_ptr()), 1, K * 4, C.c_void_p(ys[M].data_ptr()), M * 4)
+            if rc:
+                raise RuntimeError(L_.ggml_b200_last_error().decode())
+
+    # ---- sanity (outside any timed region): the last matmul of the set against the oracle
+    parity = None
+    if rank == 0 and not args.no_check:
+        import oracle
+        P = oracle.port()
+        hW, M, K = handles[0]
+        with torch.cuda.stream(stream):
+            rc = L_.ggml_b200_mul_mat_q4_0(hW, C.c_void_p(xs[K].data_ptr()), 1, K * 4, C.c_void_p(ys[M].data_ptr()), M * 4)
+        stream.synchronize()
+        lo, hi = mod.shard_rows(M, rank, world)
+        Wh = host_blocks[("L", 0)][: hi - lo]
+        Yo = P.mul_mat(Wh, xs[K].cpu().numpy(), avx2_order=True)
+        Yg = ys[M].cpu().numpy()[:, lo:hi]
+        parity = float(np.max(np.abs(Yg - Yo)) / max(np.max(np.abs(Yo)), 1e-30))
+        if not parity <= 1e-4:
+            raise RuntimeError(f"bench sanity check failed: max|dY|/max|Y| = {parity:.3e}")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- capture one step in a CUDA graph (launch-bound otherwise: 450 short kernels per step)
+    with torch.cuda.stream(stream):
+        for _ in range(2):
+            one_step()
+    stream.synchronize()
+    graph = None
+    launches_per_step = None
+    if not args.no_graph:
+        try:
+            graph = torch.cuda.CUDAGraph()
+            c0 = mod.launch_count()
+            with torch.cuda.graph(graph, stream=stream):
+                mod.set_stream(torch.cuda.current_stream().cuda_stream)
+                one_step()
+            launches_per_step = mod.launch_count() - c0
+            mod.set_stream(stream.cuda_stream)
+        except Exception as e:   # noqa: BLE001
+            if rank == 0:
+                print(f"[bench] CUDA graph capture failed ({e}); timing direct launches", file=sys.stderr)
+            graph = None
+            mod.set_stream(stream.cuda_stream)
+    if launches_per_step is None:
+        c0 = mod.launch_count()
+        with torch.cuda.stream(stream):
+            one_step()
+        stream.synchronize()
+        launches_per_step = mod.launch_count() - c0
+
+    def timed(fn, steps, warmup):
+        with torch.cuda.stream(stream):
+            for _ in range(warmup):
+                fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            for _ in range(steps):
+                fn()
+            e1.record(stream)
+        stream.synchronize()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    step_fn = (lambda: graph.replay()) if graph is not None else one_step
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    t_clock0 = time.time()
+    total_ms = timed(step_fn, args.steps, args.warmup)
+    ms_per_step = total_ms / args.steps
+    value = total_bytes / (ms_per_step * 1e-3) / 1e9
+
+    # ---- roofline leg: the GEMV kernel alone (activations quantized once, quantizer skipped)
+    roof = None
+    if world == 1:
+        mod.set_tuning("skip_quantize", 1)
+        g2 = None
+        try:
+            if graph is not None:
+                g2 = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g2, stream=stream):
+                    mod.set_stream(torch.cuda.current_stream().cuda_stream)
+                    one_step()
+                mod.set_stream(stream.cuda_stream)
+            gemv_ms = timed((lambda: g2.replay()) if g2 is not None else one_step, args.steps, args.warmup) / args.steps
+        finally:
+            mod.set_tuning("skip_quantize", 0)
+            mod.set_stream(stream.cuda_stream)
+        peak, peak_src = peaks()
+        n_launch = len(handles)
+        achieved = total_bytes / (gemv_ms * 1e-3) / 1e9
+        roof = {"kernel": "gemv_q4_0_planes_kernel<1,*>", "bound": "hbm", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "frac_of_nominal_8000": achieved / 8000.0,
+                "peak_source": peak_src, "traffic": None,
+                "launches_per_step": n_launch, "avg_launch_us": gemv_ms * 1e3 / n_launch,
+                "algorithmic_bytes_per_step": total_bytes}
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                roof["traffic"] = json.load(f).get("gemv_dram_bytes_per_launch")
+        except Exception:
+            pass
+
+    # ---- e2e leg: host buffers through the reference-facing call, H2D + D2H inside the timed region
+    e2e = None
+    if world == 1:
+        xh = {K: PinnedArray(mod, (1, K)) for K in Ks}
+        yh = {M: PinnedArray(mod, (1, M)) for M in Ms}
+        for K in Ks:
+            xh[K].a[:] = xs[K].cpu().numpy()
+
+        def one_step_host():
+            for (h, M, K) in handles:
+                rc = L_.ggml_b200_mul_mat_q4_0_host(h, C.c_void_p(xh[K].ptr), 1, K * 4, C.c_void_p(yh[M].ptr), M * 4)
+                if rc:
+                    raise RuntimeError(L_.ggml_b200_last_error().decode())
+        e2e_steps = args.steps if args.e2e_steps is None else args.e2e_steps
+        for _ in range(max(1, min(args.warmup, 3))):
+            one_step_host()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            one_step_host()
+        torch.cuda.synchronize()
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+        e2e = {"value": total_bytes / (e2e_ms * 1e-3) / 1e9, "unit": UNIT,
+               "h2d_bytes_per_step": sum(4 * K for (_, _, K) in handles),
+               "d2h_bytes_per_step": sum(4 * M for (_, M, _) in handles),
+               "ms_per_step": e2e_ms, "steps": e2e_steps,
+               "api": "ggml_b200_mul_mat_q4_0_host (pinned host x/y, synchronous per matmul like the ggml hook)"}
+        # the D2H result of the last matmul must equal the resident path's
+        if not args.no_check:
+            hW, M, K = handles[-1]
+            with torch.cuda.stream(stream):
+                L_.ggml_b200_mul_mat_q4_0(hW, C.c_void_p(xs[K].data_ptr()), 1, K * 4, C.c_void_p(ys[M].data_ptr()), M * 4)
+            stream.synchronize()
+            assert np.array_equal(ys[M].cpu().numpy(), yh[M].a), "e2e result differs from resident result"
+        for p in list(xh.values()) + list(yh.values()):
+            p.free()
+    else:
+        # multi-GPU e2e: x from pinned host -> every rank's HBM, sharded op + all-gather, y back to host
+        xh = {K: PinnedArray(mod, (1, K)) for K in Ks}
+        yh = {M: PinnedArray(mod, (1, M)) for M in Ms}
+        xt = {K: torch.from_numpy(xh[K].a) for K in Ks}
+        yt = {M: torch.from_numpy(yh[M].a) for M in Ms}
+        for K in Ks:
+            xh[K].a[:] = xs[K].cpu().numpy()
+
+        def one_step_host():
+            for (h, M, K) in handles:
+                xs[K].copy_(xt[K], non_blocking=True)
+                rc = op(h, C.c_void_p(xs[K].data_ptr()), 1, K * 4, C.c_void_p(ys[M].data_ptr()), M * 4)
+                if rc:
+                    raise RuntimeError(L_.ggml_b200_last_error().decode())
+                yt[M].copy_(ys[M], non_blocking=True)
+                stream.synchronize()
+        e2e_steps = args.steps if args.e2e_steps is None else args.e2e_steps
+        with torch.cuda.stream(stream):
+            one_step_host()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(e2e_steps):
+                one_step_host()
+        barrier()
+        e2e_ms_t = torch.tensor([(time.perf_counter() - t0) * 1e3 / e2e_steps], dtype=torch.float64, device="cuda")
+        dist.all_reduce(e2e_ms_t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(e2e_ms_t.item())
+        e2e = {"value": total_bytes / (e2e_ms * 1e-3) / 1e9, "unit": UNIT,
+               "h2d_bytes_per_step": sum(4 * K for (_, _, K) in handles) * world,
+               "d2h_bytes_per_step": sum(4 * M for (_, M, _) in handles) * world,
+               "ms_per_step": e2e_ms, "steps": e2e_steps,
+               "api": "pinned host x -> HBM on every rank, ggml_b200_mul_mat_q4_0_sharded, y -> pinned host, per matmul"}
+    t_clock1 = time.time()
+    clocks = sampler.stop(t_clock0, t_clock1) if sampler else None
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu = cpu_reference_arm(workload, 10, 1, budget_s=20.0)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
+            "vs_baseline": None, "dtype": "int8 dot (q4_0 x q8_0, dp4a), fp32 scale+accumulate", "data": "synthetic",
+            "config": {"workload": workload, "n": 1, "layers": L, "matmuls_per_step": len(handles),
+                       "weight_bytes_per_step": weight_bytes, "algorithmic_bytes_per_step": total_bytes,
+                       "l2": "inputs larger than L2: the set's weights (%.2f GB per rank) are streamed once per step" % (weight_bytes / world / 1e9),
+                       "weights": "random-init Q4_0 blocks (one layer generated on the host, a separate HBM copy per layer)",
+                       "layout": "planes (one-time repack at upload)", "cuda_graph": graph is not None,
+                       "parallelism": ("row-sharded x%d + NCCL all-gather per matmul" % world) if world > 1 else "single GPU",
+                       "setup_s": round(setup_s, 2), "sanity_max_rel_err": parity},
+            "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps), "gpu_launches_per_step": int(launches_per_step),
+            "clocks": clocks,
+        }
+        if roof:
+            line["roofline"] = roof
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+
+    for (h, _, _) in handles:
+        L_.ggml_b200_free_weight(h)
+    if world > 1:
+        mod.comm_shutdown()
+        dist.destroy_process_group()
+    mod.shutdown()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
+    ap.add_argument("--layers", type=int, default=None, help="use fewer layers of the set (debug)")
+    ap.add_argument("--e2e-steps", type=int, default=None)
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-check", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world == 1 and args.gpus > 1:
+        # launched without torchrun: re-exec under it
+        port = 29500 + (os.getpid() % 2000)
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", str(port)] + sys.argv
+        sys.exit(subprocess.call(cmd))
+    workload = args.workload or ("llama7b_decode_n1" if args.gpus == 1 else "llama65b_decode_n1_rowsharded")
+    if args.impl == "reference":
+        run_reference_impl(args, workload, rank)
+        return
+    run_gpu_arm(args, workload, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()
