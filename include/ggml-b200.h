@@ -126,6 +126,12 @@ int          ggml_b200_mul_mat_q4_0_host(const ggml_b200_weight * w, const float
 int          ggml_b200_block_dots_q4_0(const ggml_b200_weight * w, const float * x_dev, int64_t n,
                                        size_t nb11, int32_t * S_dev, int path);
 
+/* the same checkpoint for the n = 1 kernel that fuses kernel 1 into kernel 2: the q8_0 blocks its
+ * in-CTA quantizer formed (blocks34_dev: K/32 reference-format blocks, may be NULL) and its S_b
+ * (S_dev: [rows][K/32] int32, may be NULL).  x_dev: one row of K floats. */
+int          ggml_b200_fused_checkpoint_q4_0(const ggml_b200_weight * w, const float * x_dev,
+                                             int32_t * S_dev, void * blocks34_dev);
+
 /* ---- multi-GPU: row shards + all-gather ---------------------------------------------------
  * replaces the row-split placement and gather of GGML_BACKEND_GPU_SPLIT (ggml_cuda_set_tensor_split
  * ggml-cuda.cu:1863-1882, slices :2780-2797, gather by cudaMemcpyAsync :2514-2540) with one

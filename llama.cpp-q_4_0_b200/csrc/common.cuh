@@ -79,3 +79,14 @@ __device__ __forceinline__ float warp_sum(float v) {
 }
 
 }  // namespace b200
+
+// ---- programmatic dependent launch (PDL) ------------------------------------------------------
+// griddepcontrol.launch_dependents: lets the NEXT kernel in the stream start being scheduled as
+// this grid's CTAs retire; griddepcontrol.wait: blocks until every prerequisite grid has fully
+// completed and flushed.  Both are no-ops when the launch carries no programmatic edge.  Weights
+// are never written by a previous kernel, so kernels prefetch them BEFORE the wait and the HBM
+// stream keeps flowing across kernel boundaries.
+namespace b200 {
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+}  // namespace b200

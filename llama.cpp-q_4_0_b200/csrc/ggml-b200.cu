@@ -21,6 +21,7 @@
 
 #include "common.cuh"
 #include "gemv_q4_0.cuh"
+#include "gemv_q4_0_fused.cuh"
 #include "quantize_q8_0.cuh"
 #include "repack.cuh"
 #include "state.h"
@@ -71,6 +72,21 @@ static int ensure_stage(void ** p, size_t * cap, size_t need) {
     return GGML_B200_OK;
 }
 
+// every kernel goes through here: optional programmatic-dependent-launch edge to the previous
+// kernel in the stream (the kernels call griddepcontrol.wait before touching activations)
+template <typename... KArgs, typename... Args>
+static int launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = g.stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = g.tune.pdl ? 1 : 0;
+    CK(cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...));
+    g.launches++;
+    return GGML_B200_OK;
+}
+
 // ---- kernel 1 launch ------------------------------------------------------------------------
 int launch_quantize(const float * x_dev, int64_t n, int64_t K, size_t nb11, void * blocks34_dev) {
     if (n <= 0) return GGML_B200_OK;
@@ -80,16 +96,14 @@ int launch_quantize(const float * x_dev, int64_t n, int64_t K, size_t nb11, void
     const int threads = 256;
     const unsigned blocks = (unsigned)((total + threads - 1) / threads);
     const bool aligned = (((uintptr_t)x_dev | nb11) & 15) == 0;
+    unsigned char * b34 = (unsigned char *)blocks34_dev;
+    const long long nn = n;
     if (aligned) {
-        if (blocks34_dev) quantize_q8_0_kernel<true, true><<<blocks, threads, 0, g.stream>>>(x_dev, n, (int)K, nb11, g.xq, g.xds, (unsigned char *)blocks34_dev);
-        else              quantize_q8_0_kernel<true, false><<<blocks, threads, 0, g.stream>>>(x_dev, n, (int)K, nb11, g.xq, g.xds, nullptr);
-    } else {
-        if (blocks34_dev) quantize_q8_0_kernel<false, true><<<blocks, threads, 0, g.stream>>>(x_dev, n, (int)K, nb11, g.xq, g.xds, (unsigned char *)blocks34_dev);
-        else              quantize_q8_0_kernel<false, false><<<blocks, threads, 0, g.stream>>>(x_dev, n, (int)K, nb11, g.xq, g.xds, nullptr);
+        if (b34) return launch_k(quantize_q8_0_kernel<true, true>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34);
+        return launch_k(quantize_q8_0_kernel<true, false>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34);
     }
-    g.launches++;
-    CK(cudaGetLastError());
-    return GGML_B200_OK;
+    if (b34) return launch_k(quantize_q8_0_kernel<false, true>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34);
+    return launch_k(quantize_q8_0_kernel<false, false>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34);
 }
 
 // ---- kernel 2 launch ------------------------------------------------------------------------
@@ -104,10 +118,7 @@ static int launch_gemv_planes_t(const ggml_b200_weight * w, float * y, long long
         attr_set = true;
     }
     const int grid = g.sm_count * g.tune.gemv_ctas_per_sm;
-    kern<<<grid, g.tune.gemv_threads, smem, g.stream>>>(w->wq, w->wd, g.xq, g.xds, y, (int)w->rows(), nbk, ldy, n, S);
-    g.launches++;
-    CK(cudaGetLastError());
-    return GGML_B200_OK;
+    return launch_k(kern, grid, g.tune.gemv_threads, smem, (const uint4 *)w->wq, (const __half *)w->wd, (const int8_t *)g.xq, (const int2 *)g.xds, y, (int)w->rows(), nbk, ldy, n, S);
 }
 
 template <int NC, bool DUMP>
@@ -121,10 +132,7 @@ static int launch_gemv_raw_t(const ggml_b200_weight * w, float * y, long long ld
         attr_set = true;
     }
     const int grid = g.sm_count * g.tune.gemv_ctas_per_sm;
-    kern<<<grid, g.tune.gemv_threads, smem, g.stream>>>((const uint32_t *)w->raw, g.xq, g.xds, y, (int)w->rows(), nbk, ldy, n, S);
-    g.launches++;
-    CK(cudaGetLastError());
-    return GGML_B200_OK;
+    return launch_k(kern, grid, g.tune.gemv_threads, smem, (const uint32_t *)w->raw, (const int8_t *)g.xq, (const int2 *)g.xds, y, (int)w->rows(), nbk, ldy, n, S);
 }
 
 template <bool DUMP>
@@ -154,6 +162,34 @@ static int launch_gemv_any(const ggml_b200_weight * w, float * y, long long ldy,
         case 4: return u >= 4 ? launch_gemv_planes_t<4, 4, DUMP>(w, y, ldy, n, S) : launch_gemv_planes_t<4, 2, DUMP>(w, y, ldy, n, S);
         default: return launch_gemv_planes_t<8, 2, DUMP>(w, y, ldy, n, S);
     }
+}
+
+// n == 1, plane layout: kernel 1 fused into kernel 2 (one launch per op)
+template <int UNROLL, int MAXT, bool DUMP>
+static int launch_fused_t(const ggml_b200_weight * w, const float * x, float * y, int * S, unsigned char * b34) {
+    const int nbk = (int)(w->K / QK);
+    auto kern = gemv_q4_0_fused_kernel<UNROLL, MAXT, DUMP>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
+        attr_set = true;
+    }
+    int threads = g.tune.fused_threads > MAXT ? MAXT : g.tune.fused_threads;
+    const int grid = g.sm_count * g.tune.fused_ctas_per_sm;
+    const int aligned = (((uintptr_t)x) & 15) == 0;
+    return launch_k(kern, grid, threads, gemv_smem_bytes(nbk, 1), (const uint4 *)w->wq, (const __half *)w->wd, x, y, (int)w->rows(), nbk, aligned, S, b34);
+}
+
+bool fused_ok(const ggml_b200_weight * w, int64_t n) {
+    return n == 1 && g.tune.gemv_fused && !g.tune.skip_quantize && w->layout == GGML_B200_LAYOUT_PLANES &&
+           g.path != GGML_B200_PATH_GEMM && gemv_smem_bytes((int)(w->K / QK), 1) <= (size_t)MAX_DYN_SMEM;
+}
+
+int launch_fused(const ggml_b200_weight * w, const float * x, float * y, int * S, unsigned char * b34) {
+    const bool big = g.tune.fused_threads > 512;
+    if (S || b34) return big ? launch_fused_t<4, 1024, true>(w, x, y, S, b34) : launch_fused_t<4, 512, true>(w, x, y, S, b34);
+    if (g.tune.gemv_unroll >= 4) return big ? launch_fused_t<4, 1024, false>(w, x, y, S, b34) : launch_fused_t<4, 512, false>(w, x, y, S, b34);
+    return big ? launch_fused_t<2, 1024, false>(w, x, y, S, b34) : launch_fused_t<2, 512, false>(w, x, y, S, b34);
 }
 
 int launch_gemv(const ggml_b200_weight * w, float * y, long long ldy, int n) {
@@ -189,6 +225,7 @@ int launch_shard(const ggml_b200_weight * w, float * y, long long ldy, int n) {
 // x_dev/y_dev device pointers; y_dev addresses the full dst, this shard writes [row_lo,row_hi)
 int mul_mat_dev(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y_dev, size_t nb1) {
     if (n == 0 || w->rows() == 0) return GGML_B200_OK;
+    if (fused_ok(w, n)) return launch_fused(w, x_dev, y_dev + w->row_lo, nullptr, nullptr);
     if (!g.tune.skip_quantize) {
         int rc = launch_quantize(x_dev, n, w->K, nb11, nullptr);
         if (rc) return rc;
@@ -256,6 +293,7 @@ void ggml_b200_shutdown(void) {
     if (g.xds) cudaFree(g.xds);
     if (g.xstage) cudaFree(g.xstage);
     if (g.ystage) cudaFree(g.ystage);
+    if (g.sstage) cudaFree(g.sstage);
     gemm_shutdown();
     if (g.own_stream) cudaStreamDestroy(g.own_stream);
     const Tune t = g.tune;
@@ -277,6 +315,10 @@ int ggml_b200_set_tuning(const char * key, int value) {
     else if (!strcmp(key, "gemv_ctas_per_sm")) { if (value < 1 || value > 16) return GGML_B200_ERR_ARG; g.tune.gemv_ctas_per_sm = value; }
     else if (!strcmp(key, "gemv_unroll"))  { g.tune.gemv_unroll = value; }
     else if (!strcmp(key, "gemv_nc"))      { g.tune.gemv_nc = value; }
+    else if (!strcmp(key, "gemv_fused"))   { g.tune.gemv_fused = value != 0; }
+    else if (!strcmp(key, "pdl"))          { g.tune.pdl = value != 0; }
+    else if (!strcmp(key, "fused_threads")) { if (value < 32 || value > 1024 || (value & 31)) return GGML_B200_ERR_ARG; g.tune.fused_threads = value; }
+    else if (!strcmp(key, "fused_ctas_per_sm")) { if (value < 1 || value > 16) return GGML_B200_ERR_ARG; g.tune.fused_ctas_per_sm = value; }
     else if (!strcmp(key, "skip_quantize")) { g.tune.skip_quantize = value != 0; }
     else return gemm_set_tuning(key, value);
     return GGML_B200_OK;
@@ -413,9 +455,13 @@ int ggml_b200_mul_mat_q4_0_host(const ggml_b200_weight * w, const float * x_host
     if (rc) return rc;
     if (nb11 == xrow) CK(cudaMemcpyAsync(g.xstage, x_host, (size_t)n * xrow, cudaMemcpyHostToDevice, g.stream));
     else              CK(cudaMemcpy2DAsync(g.xstage, xrow, x_host, nb11, xrow, (size_t)n, cudaMemcpyHostToDevice, g.stream));
-    rc = launch_quantize(g.xstage, n, w->K, xrow, nullptr);
-    if (rc) return rc;
-    rc = launch_shard(w, g.ystage, rows, (int)n);
+    if (fused_ok(w, n)) {
+        rc = launch_fused(w, g.xstage, g.ystage, nullptr, nullptr);
+    } else {
+        rc = launch_quantize(g.xstage, n, w->K, xrow, nullptr);
+        if (rc) return rc;
+        rc = launch_shard(w, g.ystage, rows, (int)n);
+    }
     if (rc) return rc;
     CK(cudaMemcpy2DAsync(y_host + w->row_lo, nb1, g.ystage, (size_t)rows * 4, (size_t)rows * 4, (size_t)n, cudaMemcpyDeviceToHost, g.stream));
     CK(cudaStreamSynchronize(g.stream));
@@ -426,15 +472,32 @@ int ggml_b200_block_dots_q4_0(const ggml_b200_weight * w, const float * x_dev, i
     if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
     if (!w || !x_dev || !S_dev || n < 0 || nb11 < (size_t)w->K * 4 || (nb11 & 3)) { set_error("bad block_dots arguments"); return GGML_B200_ERR_ARG; }
     if (n == 0 || w->rows() == 0) return GGML_B200_OK;
-    int rc = launch_quantize(x_dev, n, w->K, nb11, nullptr);
+    int rc = ensure_stage((void **)&g.ystage, &g.ystage_cap, (size_t)n * w->rows() * 4);
     if (rc) return rc;
-    rc = ensure_stage((void **)&g.ystage, &g.ystage_cap, (size_t)n * w->rows() * 4);
+    if (path == GGML_B200_PATH_GEMV && fused_ok(w, n)) return launch_fused(w, x_dev, g.ystage, S_dev, nullptr);
+    rc = launch_quantize(x_dev, n, w->K, nb11, nullptr);
     if (rc) return rc;
     if (path == GGML_B200_PATH_GEMM) {
         if (!gemm_available(w)) { set_error("tensor-core GEMM path not available for this weight (layout %d)", w->layout); return GGML_B200_ERR_ARG; }
         return launch_gemm(w, g.ystage, w->rows(), (int)n, S_dev);
     }
     return launch_gemv_dump(w, g.ystage, w->rows(), (int)n, S_dev);
+}
+
+int ggml_b200_fused_checkpoint_q4_0(const ggml_b200_weight * w, const float * x_dev, int32_t * S_dev, void * blocks34_dev) {
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    if (!w || !x_dev) { set_error("null argument"); return GGML_B200_ERR_ARG; }
+    if (w->layout != GGML_B200_LAYOUT_PLANES) { set_error("the fused kernel needs the plane layout"); return GGML_B200_ERR_ARG; }
+    if (w->rows() == 0) return GGML_B200_OK;
+    int rc = ensure_stage((void **)&g.ystage, &g.ystage_cap, (size_t)w->rows() * 4);
+    if (rc) return rc;
+    int * S = S_dev;
+    if (!S) {   // the DUMP kernel always stores S_b
+        rc = ensure_stage((void **)&g.sstage, &g.sstage_cap, (size_t)w->rows() * (w->K / QK) * 4);
+        if (rc) return rc;
+        S = (int *)g.sstage;
+    }
+    return launch_fused(w, x_dev, g.ystage, S, (unsigned char *)blocks34_dev);
 }
 
 }  // extern "C"

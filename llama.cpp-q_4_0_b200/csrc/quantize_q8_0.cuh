@@ -29,6 +29,8 @@ __global__ void __launch_bounds__(256)
 quantize_q8_0_kernel(const float * __restrict__ x, long long n, int K, size_t nb11,
                      int8_t * __restrict__ xq, int2 * __restrict__ xds,
                      unsigned char * __restrict__ blocks34) {
+    pdl_launch_dependents();
+    pdl_wait();   // x may be produced, and xq/xds still be read, by the previous kernel
     const int per_row = K >> 3;
     const long long total = n * (long long)per_row;
     long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;

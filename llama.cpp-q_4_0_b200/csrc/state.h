@@ -28,6 +28,10 @@ struct Tune {
     int gemv_ctas_per_sm = 2;    // grid = SMs * this
     int gemv_unroll = 4;         // 16-byte weight loads in flight per lane
     int gemv_nc = 0;             // cap on columns per pass (0 = by n)
+    int gemv_fused = 1;          // n == 1: quantize inside the GEMV kernel (one launch per op)
+    int fused_threads = 1024;    // threads per CTA of the fused kernel
+    int fused_ctas_per_sm = 1;
+    int pdl = 1;                 // programmatic dependent launch between consecutive kernels
     int skip_quantize = 0;       // bench only: reuse the activations quantized by the previous call
 };
 
@@ -47,6 +51,7 @@ struct Ctx {
     // staging for the host-pointer entry point
     float * xstage = nullptr; size_t xstage_cap = 0;
     float * ystage = nullptr; size_t ystage_cap = 0;
+    void *  sstage = nullptr; size_t sstage_cap = 0;
     uint64_t launches = 0;
     char err[512] = {0};
 };

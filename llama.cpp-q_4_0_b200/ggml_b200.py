@@ -72,6 +72,7 @@ def _load() -> C.CDLL:
         "ggml_b200_mul_mat_q4_0": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
         "ggml_b200_mul_mat_q4_0_host": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
         "ggml_b200_block_dots_q4_0": (C.c_int, [_vp, _vp, _i64, _sz, _vp, C.c_int]),
+        "ggml_b200_fused_checkpoint_q4_0": (C.c_int, [_vp, _vp, _vp, _vp]),
         "ggml_b200_comm_unique_id": (C.c_int, [_vp]),
         "ggml_b200_comm_init": (C.c_int, [C.c_int, C.c_int, _vp]),
         "ggml_b200_comm_shutdown": (None, []),
@@ -285,6 +286,21 @@ def block_dots(w: Weight, x: np.ndarray, path: int = PATH_GEMV) -> np.ndarray:
     out = S.to_numpy(np.int32, (n, w.rows, nbk))
     xd.free()
     S.free()
+    return out
+
+
+def fused_checkpoint(w: Weight, x: np.ndarray) -> tuple[np.ndarray, np.ndarray]:
+    """(q8_0 blocks [K/32][34], S_b [rows][K/32]) as the fused n = 1 kernel forms them."""
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1)
+    nbk = x.size // QK
+    xd = DevBuf.from_numpy(x)
+    S = DevBuf(max(4, w.rows * nbk * 4))
+    B = DevBuf(nbk * 34)
+    _check(lib().ggml_b200_fused_checkpoint_q4_0(w.h, xd.ptr, S.ptr, B.ptr))
+    synchronize()
+    out = (B.to_numpy(np.uint8, (nbk, 34)), S.to_numpy(np.int32, (w.rows, nbk)))
+    for b in (xd, S, B):
+        b.free()
     return out
 
 

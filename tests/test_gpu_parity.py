@@ -247,5 +247,64 @@ def test_launch_counter_counts_kernels(b200, port, ref):
     w = b200.Weight(W)
     c0 = b200.launch_count()
     b200.mul_mat_host(w, make_x(port, 1, 256))
+    assert b200.launch_count() - c0 == 1          # n = 1: kernel 1 is fused into kernel 2
+    c0 = b200.launch_count()
+    b200.mul_mat_host(w, make_x(port, 2, 256))
     assert b200.launch_count() - c0 == 2          # kernel 1 + kernel 2
     w.free()
+
+
+@pytest.mark.parametrize("M,K", [(70, 1088), (4096, 4096), (300, 18176), (1, 64)])
+def test_fused_kernel_checkpoints_bit_exact(b200, port, ref, golden, M, K):
+    """The n = 1 kernel quantizes inside the CTA: its q8_0 blocks and S_b must be the reference's,
+    and its output must equal the unfused two-kernel path bit for bit (same accumulation order)."""
+    W = make_weights(port, ref, M, K)
+    x = make_x(port, 1, K)
+    w = b200.Weight(W)
+    q8, S = b200.fused_checkpoint(w, x)
+    want_q8 = port.quantize_q8_0(x)
+    assert np.array_equal(q8, want_q8[0])
+    assert np.array_equal(S, port.block_dots_matrix(W, want_q8)[0])
+    Yf = b200.mul_mat_host(w, x)
+    b200.set_tuning("gemv_fused", 0)
+    try:
+        Yu = b200.mul_mat_host(w, x)
+    finally:
+        b200.set_tuning("gemv_fused", 1)
+    w.free()
+    assert np.array_equal(Yf.view(np.uint32), Yu.view(np.uint32))
+
+
+def test_fused_kernel_edge_rows(b200, golden, port, ref):
+    """edge activations (ties, zeros, denormal / inf scales) through the fused quantizer."""
+    W = make_weights(port, ref, 8, 64)
+    w = b200.Weight(W)
+    for i, row in enumerate(golden["edge_X"]):
+        q8, _ = b200.fused_checkpoint(w, row)
+        assert np.array_equal(q8, golden["edge_q8"][i]), f"edge row {i}"
+    w.free()
+
+
+@pytest.mark.parametrize("pdl", [0, 1])
+def test_back_to_back_ops_with_and_without_pdl(b200, port, ref, pdl):
+    """Consecutive ops share the activation workspace and overlap their prologues under
+    programmatic dependent launch; results must not depend on it."""
+    M, K = 600, 2048
+    W1, W2 = make_weights(port, ref, M, K, 1), make_weights(port, ref, M, K, 2)
+    w1, w2 = b200.Weight(W1), b200.Weight(W2)
+    b200.set_tuning("pdl", pdl)
+    try:
+        for n in (1, 3):
+            xs = [make_x(port, n, K, 10 + i) for i in range(4)]
+            xd = [b200.DevBuf.from_numpy(x) for x in xs]
+            yd = [b200.DevBuf(n * M * 4) for _ in xs]
+            for rep in range(3):
+                for i in range(4):
+                    b200.mul_mat_dev(w1 if i % 2 == 0 else w2, xd[i].ptr, n, yd[i].ptr)
+            b200.synchronize()
+            for i in range(4):
+                Y = yd[i].to_numpy(np.float32, (n, M))
+                assert_close(Y, oracle_Y(port, ref, W1 if i % 2 == 0 else W2, xs[i]))
+    finally:
+        b200.set_tuning("pdl", 1)
+    w1.free(); w2.free()

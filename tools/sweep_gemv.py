@@ -29,9 +29,11 @@ def main():
     mod.set_stream(stream.cuda_stream)
     rng = np.random.default_rng(1)
     peak, _ = bench.peaks()
-    cfgs = list(itertools.product([256, 512], [1, 2, 4], [1, 2, 4]))
+    # (fused, threads, ctas/SM, unroll, pdl)
+    cfgs = [(1, t, c, u, p) for t in (512, 1024) for c in (1, 2, 4) for u in (2, 4) for p in (0, 1) if t * c <= 2048]
+    cfgs += [(0, 512, 2, 4, p) for p in (0, 1)]
     if quick:
-        cfgs = [(512, 2, 4), (256, 4, 4), (512, 1, 4)]
+        cfgs = [(1, 1024, 1, 4, 1), (1, 1024, 1, 4, 0), (1, 512, 2, 4, 1), (0, 512, 2, 4, 1)]
     results = []
     for (M, K) in (SHAPES[:4] if quick else SHAPES):
         wbytes = 18 * M * K // 32
@@ -44,16 +46,17 @@ def main():
             hs.append(h)
         x = torch.randn(1, K, device="cuda")
         y = torch.zeros(1, M, device="cuda")
-        # quantize once
-        with torch.cuda.stream(stream):
-            L_.ggml_b200_mul_mat_q4_0(hs[0], C.c_void_p(x.data_ptr()), 1, K * 4, C.c_void_p(y.data_ptr()), M * 4)
-        stream.synchronize()
-        mod.set_tuning("skip_quantize", 1)
         best = None
-        for (thr, cps, unr) in cfgs:
-            mod.set_tuning("gemv_threads", thr)
-            mod.set_tuning("gemv_ctas_per_sm", cps)
+        for (fused, thr, cps, unr, pdl) in cfgs:
+            mod.set_tuning("gemv_fused", fused)
+            mod.set_tuning("pdl", pdl)
             mod.set_tuning("gemv_unroll", unr)
+            if fused:
+                mod.set_tuning("fused_threads", thr)
+                mod.set_tuning("fused_ctas_per_sm", cps)
+            else:
+                mod.set_tuning("gemv_threads", thr)
+                mod.set_tuning("gemv_ctas_per_sm", cps)
 
             def step():
                 for h in hs:
@@ -77,14 +80,13 @@ def main():
             stream.synchronize()
             us = e0.elapsed_time(e1) * 1e3 / (reps * copies)
             gbs = bench.algo_bytes(M, K) / us / 1e3
-            r = {"M": M, "K": K, "threads": thr, "ctas_per_sm": cps, "unroll": unr, "us": us, "GBps": gbs, "frac": gbs / peak}
+            r = {"M": M, "K": K, "fused": fused, "threads": thr, "ctas_per_sm": cps, "unroll": unr, "pdl": pdl, "us": us, "GBps": gbs, "frac": gbs / peak}
             results.append(r)
             if best is None or gbs > best["GBps"]:
                 best = r
             del g
-        mod.set_tuning("skip_quantize", 0)
         print(f"{M:6d}x{K:<6d} best {best['GBps']:7.0f} GB/s ({best['frac']*100:5.1f}% of measured) {best['us']:7.2f} us  "
-              f"thr={best['threads']} cps={best['ctas_per_sm']} unroll={best['unroll']}", flush=True)
+              f"fused={best['fused']} thr={best['threads']} cps={best['ctas_per_sm']} unroll={best['unroll']} pdl={best['pdl']}", flush=True)
         for h in hs:
             L_.ggml_b200_free_weight(h)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
