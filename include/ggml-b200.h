@@ -156,6 +156,11 @@ int          ggml_b200_mul_mat_q4_0_sharded(const ggml_b200_weight * w, const fl
 /* ---- introspection for bench.py / tests ---------------------------------------------------*/
 /* number of kernels THIS library launched since init (the bench's gpu_launches claim) */
 uint64_t     ggml_b200_launch_count(void);
+/* per-CTA timeline trace of the n = 1 kernels (profiling aid): records of 8 x u64
+ * {kernel seq, blockIdx | smid << 32, t_start, t_after_dependency_wait, t_after_prologue, t_end, 0, 0}
+ * in globaltimer ns.  trace_end returns the number of records copied to `out`. */
+int          ggml_b200_trace_begin(unsigned int capacity_records);
+int          ggml_b200_trace_end(unsigned long long * out, unsigned int max_records);
 /* plain device memory helpers so a ctypes harness needs no other CUDA binding */
 void *       ggml_b200_dev_malloc(size_t size);
 void         ggml_b200_dev_free(void * ptr);

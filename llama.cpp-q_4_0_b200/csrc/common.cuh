@@ -69,6 +69,27 @@ __device__ __forceinline__ int block_dot_q4_q8(const uint4 q, const uint4 ylo, c
     return s;
 }
 
+// Same S_b with 8 instead of 12 unpack instructions and two independent IDP.4A chains: the high
+// nibbles stay in place (byte = 16*q_hi, read as UNSIGNED by dp4a.u32.s32), so that chain yields
+// 16 * sum(q_hi*q8) exactly and one arithmetic shift restores it.
+__device__ __forceinline__ int dp4a_us(uint32_t a_unsigned, uint32_t b_signed, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a_unsigned), "r"(b_signed), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int block_dot_q4_q8_fast(const uint4 q, const uint4 ylo, const uint4 yhi, int init) {
+    int lo = init, hi = 0;
+    lo = dp4a_us(q.x & 0x0F0F0F0Fu, ylo.x, lo);
+    hi = dp4a_us(q.x & 0xF0F0F0F0u, yhi.x, hi);
+    lo = dp4a_us(q.y & 0x0F0F0F0Fu, ylo.y, lo);
+    hi = dp4a_us(q.y & 0xF0F0F0F0u, yhi.y, hi);
+    lo = dp4a_us(q.z & 0x0F0F0F0Fu, ylo.z, lo);
+    hi = dp4a_us(q.z & 0xF0F0F0F0u, yhi.z, hi);
+    lo = dp4a_us(q.w & 0x0F0F0F0Fu, ylo.w, lo);
+    hi = dp4a_us(q.w & 0xF0F0F0F0u, yhi.w, hi);
+    return lo + (hi >> 4);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
     v += __shfl_xor_sync(0xffffffffu, v, 16);
     v += __shfl_xor_sync(0xffffffffu, v, 8);
@@ -89,4 +110,36 @@ __device__ __forceinline__ float warp_sum(float v) {
 namespace b200 {
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+}  // namespace b200
+
+// ---- optional per-CTA timeline trace (debug / profiling only; off unless ggml_b200_trace_begin) ----
+// record = 8 x u64: {kernel seq, blockIdx | smid << 32, t_start, t_after_wait, t_after_prologue, t_end, 0, 0}
+namespace b200 {
+static __device__ unsigned long long * g_trace = nullptr;   // per translation unit
+static __device__ unsigned int g_trace_cap = 0;
+static __device__ unsigned int g_trace_pos = 0;
+
+__device__ __forceinline__ unsigned long long gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+struct CtaTrace {
+    unsigned long long * rec;
+    __device__ __forceinline__ void begin(unsigned seq) {
+        rec = nullptr;
+        if (g_trace != nullptr) {
+            const unsigned slot = atomicAdd(&g_trace_pos, 1u);
+            if (slot < g_trace_cap) {
+                unsigned smid;
+                asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+                rec = g_trace + (size_t)slot * 8;
+                rec[0] = seq;
+                rec[1] = (unsigned long long)blockIdx.x | ((unsigned long long)smid << 32);
+                rec[2] = gtime();
+            }
+        }
+    }
+    __device__ __forceinline__ void mark(int i) { if (rec) rec[2 + i] = gtime(); }
+};
 }  // namespace b200

@@ -17,34 +17,42 @@
 
 namespace b200 {
 
-template <int UNROLL, int MAXT, bool DUMP>
+template <int UNROLL, int RIF, int MAXT, bool DUMP>
 __global__ void __launch_bounds__(MAXT, (2048 / MAXT) / 2)
 gemv_q4_0_fused_kernel(const uint4 * __restrict__ wq, const __half * __restrict__ wd,
                        const float * __restrict__ x, float * __restrict__ y, int rows, int nbk,
-                       int x_aligned, int * __restrict__ S_out, unsigned char * __restrict__ blocks34) {
+                       int x_aligned, int * __restrict__ S_out, unsigned char * __restrict__ blocks34, unsigned seq) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     GemvSmem<1> s(smem_raw, nbk);
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const int nwarps = blockDim.x >> 5;
+    CtaTrace tr;
+    if (threadIdx.x == 0) tr.begin(seq);
     pdl_launch_dependents();
 
-    // 1. first chunk of this warp's first row
-    int row = blockIdx.x + gridDim.x * warp;
-    uint4 q[UNROLL];
-    unsigned short dh[UNROLL];
-    if (row < rows) {
-        const uint4 * wrow = wq + (size_t)row * nbk;
-        const unsigned short * drow = reinterpret_cast<const unsigned short *>(wd) + (size_t)row * nbk;
+    // 1. first chunk of this warp's first RIF rows (RIF rows in flight per warp)
+    const int rstride = gridDim.x * nwarps;
+    const int row_first = blockIdx.x + gridDim.x * warp;
+    uint4 q[RIF][UNROLL];
+    unsigned short dh[RIF][UNROLL];
 #pragma unroll
-        for (int u = 0; u < UNROLL; u++) {
-            const int b = lane + 32 * u;
-            if (b < nbk) { q[u] = ldg_stream_u4(wrow + b); dh[u] = ldg_stream_u16(drow + b); }
+    for (int r = 0; r < RIF; r++) {
+        const int row = row_first + r * rstride;
+        if (row < rows) {
+            const uint4 * wrow = wq + (size_t)row * nbk;
+            const unsigned short * drow = reinterpret_cast<const unsigned short *>(wd) + (size_t)row * nbk;
+#pragma unroll
+            for (int u = 0; u < UNROLL; u++) {
+                const int b = lane + 32 * u;
+                if (b < nbk) { q[r][u] = ldg_stream_u4(wrow + b); dh[r][u] = ldg_stream_u16(drow + b); }
+            }
         }
     }
 
     // 2. activations (and y) may belong to the previous kernel
     pdl_wait();
+    if (threadIdx.x == 0) tr.mark(1);
 
     // 3. quantize_row_q8_0 into the smem planes; 4 threads per block, 8 floats per thread
     {
@@ -101,19 +109,28 @@ gemv_q4_0_fused_kernel(const uint4 * __restrict__ wq, const __half * __restrict_
         }
     }
     __syncthreads();
+    if (threadIdx.x == 0) tr.mark(2);
 
-    // 4. dot loop
+    // 4. dot loop, RIF rows at a time
     bool prefetched = true;
-    for (; row < rows; row += gridDim.x * nwarps) {
-        const uint4 * wrow = wq + (size_t)row * nbk;
-        const unsigned short * drow = reinterpret_cast<const unsigned short *>(wd) + (size_t)row * nbk;
-        float acc = 0.0f;
+    for (int row0 = row_first; row0 < rows; row0 += RIF * rstride) {
+        float acc[RIF];
+#pragma unroll
+        for (int r = 0; r < RIF; r++) acc[r] = 0.0f;
         for (int b0 = lane; b0 < nbk; b0 += 32 * UNROLL) {
             if (!prefetched) {
 #pragma unroll
-                for (int u = 0; u < UNROLL; u++) {
-                    const int b = b0 + 32 * u;
-                    if (b < nbk) { q[u] = ldg_stream_u4(wrow + b); dh[u] = ldg_stream_u16(drow + b); }
+                for (int r = 0; r < RIF; r++) {
+                    const int row = row0 + r * rstride;
+                    if (row < rows) {
+                        const uint4 * wrow = wq + (size_t)row * nbk;
+                        const unsigned short * drow = reinterpret_cast<const unsigned short *>(wd) + (size_t)row * nbk;
+#pragma unroll
+                        for (int u = 0; u < UNROLL; u++) {
+                            const int b = b0 + 32 * u;
+                            if (b < nbk) { q[r][u] = ldg_stream_u4(wrow + b); dh[r][u] = ldg_stream_u16(drow + b); }
+                        }
+                    }
                 }
             }
             prefetched = false;
@@ -122,15 +139,28 @@ gemv_q4_0_fused_kernel(const uint4 * __restrict__ wq, const __half * __restrict_
                 const int b = b0 + 32 * u;
                 if (b < nbk) {
                     const int2 ds = s.ds[b];
-                    const int sb = block_dot_q4_q8(q[u], s.lo[b], s.hi[b], ds.y);
-                    if (DUMP) S_out[(size_t)row * nbk + b] = sb;
-                    acc = fmaf((float)sb, half_bits_to_float(dh[u]) * __int_as_float(ds.x), acc);
+                    const uint4 ylo = s.lo[b], yhi = s.hi[b];
+                    const float dxf = __int_as_float(ds.x);
+#pragma unroll
+                    for (int r = 0; r < RIF; r++) {
+                        const int row = row0 + r * rstride;
+                        if (row < rows) {
+                            const int sb = block_dot_q4_q8(q[r][u], ylo, yhi, ds.y);
+                            if (DUMP) S_out[(size_t)row * nbk + b] = sb;
+                            acc[r] = fmaf((float)sb, half_bits_to_float(dh[r][u]) * dxf, acc[r]);
+                        }
+                    }
                 }
             }
         }
-        acc = warp_sum(acc);
-        if (lane == 0) y[row] = acc;
+#pragma unroll
+        for (int r = 0; r < RIF; r++) {
+            const int row = row0 + r * rstride;
+            const float t = warp_sum(acc[r]);
+            if (lane == 0 && row < rows) y[row] = t;
+        }
     }
+    if (threadIdx.x == 0) tr.mark(3);
 }
 
 }  // namespace b200

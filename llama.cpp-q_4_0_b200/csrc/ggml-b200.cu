@@ -22,6 +22,7 @@
 #include "common.cuh"
 #include "gemv_q4_0.cuh"
 #include "gemv_q4_0_fused.cuh"
+#include "gemv_q4_0_stream.cuh"
 #include "quantize_q8_0.cuh"
 #include "repack.cuh"
 #include "state.h"
@@ -30,6 +31,8 @@ namespace b200 {
 
 Ctx g;
 static std::mutex g_mu;
+static unsigned long long * h_trace_dev = nullptr;
+static unsigned int h_trace_cap = 0;
 
 void set_error(const char * fmt, ...) {
     va_list ap;
@@ -165,10 +168,10 @@ static int launch_gemv_any(const ggml_b200_weight * w, float * y, long long ldy,
 }
 
 // n == 1, plane layout: kernel 1 fused into kernel 2 (one launch per op)
-template <int UNROLL, int MAXT, bool DUMP>
+template <int UNROLL, int RIF, int MAXT, bool DUMP>
 static int launch_fused_t(const ggml_b200_weight * w, const float * x, float * y, int * S, unsigned char * b34) {
     const int nbk = (int)(w->K / QK);
-    auto kern = gemv_q4_0_fused_kernel<UNROLL, MAXT, DUMP>;
+    auto kern = gemv_q4_0_fused_kernel<UNROLL, RIF, MAXT, DUMP>;
     static bool attr_set = false;
     if (!attr_set) {
         CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
@@ -177,7 +180,43 @@ static int launch_fused_t(const ggml_b200_weight * w, const float * x, float * y
     int threads = g.tune.fused_threads > MAXT ? MAXT : g.tune.fused_threads;
     const int grid = g.sm_count * g.tune.fused_ctas_per_sm;
     const int aligned = (((uintptr_t)x) & 15) == 0;
-    return launch_k(kern, grid, threads, gemv_smem_bytes(nbk, 1), (const uint4 *)w->wq, (const __half *)w->wd, x, y, (int)w->rows(), nbk, aligned, S, b34);
+    return launch_k(kern, grid, threads, gemv_smem_bytes(nbk, 1), (const uint4 *)w->wq, (const __half *)w->wd, x, y, (int)w->rows(), nbk, aligned, S, b34, (unsigned)g.launches);
+}
+
+// n == 1, plane layout: the streaming kernel (bulk-async ring + mbarriers, quantizer fused in)
+template <int NCL, bool DUMP>
+static int launch_stream_t(const ggml_b200_weight * w, const StreamPlan & p, const float * x, float * y, int * S, unsigned char * b34) {
+    auto kern = gemv_q4_0_stream_kernel<NCL, DUMP>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
+        attr_set = true;
+    }
+    const int nbk = (int)(w->K / QK);
+    const int aligned = (((uintptr_t)x) & 15) == 0;
+    int stages = p.stages;
+    if (g.tune.stream_stages > 1 && g.tune.stream_stages < stages && g.tune.stream_stages * p.rs >= STREAM_WARPS / p.wpr) stages = g.tune.stream_stages;
+    const size_t smem = (size_t)stages * p.stage_bytes + 128 + 128 + (size_t)40 * nbk;
+    return launch_k(kern, g.sm_count * g.tune.stream_ctas_per_sm, STREAM_THREADS, smem, (const uint4 *)w->wq, (const __half *)w->wd, x, y,
+                    (int)w->rows(), nbk, p.rs, p.wpr, stages, p.stage_bytes, aligned, S, b34, (unsigned)g.launches);
+}
+
+template <bool DUMP>
+static int launch_stream_d(const ggml_b200_weight * w, const float * x, float * y, int * S, unsigned char * b34) {
+    const StreamPlan p = stream_plan((int)(w->K / QK));
+    switch (p.ncl) {
+        case 1: return launch_stream_t<1, DUMP>(w, p, x, y, S, b34);
+        case 2: return launch_stream_t<2, DUMP>(w, p, x, y, S, b34);
+        case 3: return launch_stream_t<3, DUMP>(w, p, x, y, S, b34);
+        case 4: return launch_stream_t<4, DUMP>(w, p, x, y, S, b34);
+    }
+    set_error("no streaming-kernel instantiation for ncl=%d", p.ncl);
+    return GGML_B200_ERR_ARG;
+}
+
+bool stream_ok(const ggml_b200_weight * w, int64_t n) {
+    return n == 1 && g.tune.gemv_stream && g.tune.gemv_fused && !g.tune.skip_quantize && w->layout == GGML_B200_LAYOUT_PLANES &&
+           g.path != GGML_B200_PATH_GEMM && stream_plan((int)(w->K / QK)).ok;
 }
 
 bool fused_ok(const ggml_b200_weight * w, int64_t n) {
@@ -186,10 +225,16 @@ bool fused_ok(const ggml_b200_weight * w, int64_t n) {
 }
 
 int launch_fused(const ggml_b200_weight * w, const float * x, float * y, int * S, unsigned char * b34) {
+    if (stream_ok(w, 1)) return (S || b34) ? launch_stream_d<true>(w, x, y, S, b34) : launch_stream_d<false>(w, x, y, S, b34);
+    // 1024 x 1 CTA/SM is best up to ~8k rows; beyond, 512 x 2 CTAs/SM (finer row interleave) wins
+    // (profiles/r01_sweep_gemv_v2.log); an explicit fused_threads knob overrides
     const bool big = g.tune.fused_threads > 512;
-    if (S || b34) return big ? launch_fused_t<4, 1024, true>(w, x, y, S, b34) : launch_fused_t<4, 512, true>(w, x, y, S, b34);
-    if (g.tune.gemv_unroll >= 4) return big ? launch_fused_t<4, 1024, false>(w, x, y, S, b34) : launch_fused_t<4, 512, false>(w, x, y, S, b34);
-    return big ? launch_fused_t<2, 1024, false>(w, x, y, S, b34) : launch_fused_t<2, 512, false>(w, x, y, S, b34);
+    const int rif = g.tune.fused_rif;
+    if (S || b34) return big ? launch_fused_t<4, 1, 1024, true>(w, x, y, S, b34) : rif >= 2 ? launch_fused_t<4, 2, 512, true>(w, x, y, S, b34) : launch_fused_t<4, 1, 512, true>(w, x, y, S, b34);
+    if (big) return g.tune.gemv_unroll >= 4 ? launch_fused_t<4, 1, 1024, false>(w, x, y, S, b34) : launch_fused_t<2, 1, 1024, false>(w, x, y, S, b34);
+    if (rif >= 4) return launch_fused_t<2, 4, 512, false>(w, x, y, S, b34);
+    if (rif >= 2) return g.tune.gemv_unroll >= 4 ? launch_fused_t<4, 2, 512, false>(w, x, y, S, b34) : launch_fused_t<2, 2, 512, false>(w, x, y, S, b34);
+    return g.tune.gemv_unroll >= 4 ? launch_fused_t<4, 1, 512, false>(w, x, y, S, b34) : launch_fused_t<2, 1, 512, false>(w, x, y, S, b34);
 }
 
 int launch_gemv(const ggml_b200_weight * w, float * y, long long ldy, int n) {
@@ -315,6 +360,10 @@ int ggml_b200_set_tuning(const char * key, int value) {
     else if (!strcmp(key, "gemv_ctas_per_sm")) { if (value < 1 || value > 16) return GGML_B200_ERR_ARG; g.tune.gemv_ctas_per_sm = value; }
     else if (!strcmp(key, "gemv_unroll"))  { g.tune.gemv_unroll = value; }
     else if (!strcmp(key, "gemv_nc"))      { g.tune.gemv_nc = value; }
+    else if (!strcmp(key, "gemv_stream"))  { g.tune.gemv_stream = value != 0; }
+    else if (!strcmp(key, "stream_stages")) { g.tune.stream_stages = value; }
+    else if (!strcmp(key, "stream_ctas_per_sm")) { if (value < 1 || value > 2) return GGML_B200_ERR_ARG; g.tune.stream_ctas_per_sm = value; }
+    else if (!strcmp(key, "fused_rif"))    { g.tune.fused_rif = value; }
     else if (!strcmp(key, "gemv_fused"))   { g.tune.gemv_fused = value != 0; }
     else if (!strcmp(key, "pdl"))          { g.tune.pdl = value != 0; }
     else if (!strcmp(key, "fused_threads")) { if (value < 32 || value > 1024 || (value & 31)) return GGML_B200_ERR_ARG; g.tune.fused_threads = value; }
@@ -374,7 +423,7 @@ ggml_b200_weight * ggml_b200_upload_q4_0(const void * blocks, int64_t M, int64_t
     }
     const long long nblocks = (long long)rows * nbk;
     e = cudaMalloc(&w->wq, (size_t)nblocks * sizeof(uint4));
-    if (e == cudaSuccess) e = cudaMalloc(&w->wd, (size_t)nblocks * sizeof(__half));
+    if (e == cudaSuccess) e = cudaMalloc(&w->wd, (size_t)nblocks * sizeof(__half) + 16);
     if (e != cudaSuccess) { cuda_fail(e, "cudaMalloc(planes)", __FILE__, __LINE__); cudaFree(raw); ggml_b200_free_weight(w); return nullptr; }
     const int threads = 256;
     repack_q4_0_to_planes_kernel<<<(unsigned)((nblocks + threads - 1) / threads), threads, 0, g.stream>>>((const unsigned short *)raw, w->wq, w->wd, nblocks);
@@ -482,6 +531,36 @@ int ggml_b200_block_dots_q4_0(const ggml_b200_weight * w, const float * x_dev, i
         return launch_gemm(w, g.ystage, w->rows(), (int)n, S_dev);
     }
     return launch_gemv_dump(w, g.ystage, w->rows(), (int)n, S_dev);
+}
+
+// per-CTA timeline trace of the n = 1 kernels (profiling aid; see common.cuh CtaTrace)
+int ggml_b200_trace_begin(unsigned int capacity) {
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    CK(cudaStreamSynchronize(g.stream));
+    if (h_trace_dev) { cudaFree(h_trace_dev); h_trace_dev = nullptr; }
+    CK(cudaMalloc(&h_trace_dev, (size_t)capacity * 64));
+    CK(cudaMemset(h_trace_dev, 0, (size_t)capacity * 64));
+    h_trace_cap = capacity;
+    unsigned int zero = 0;
+    CK(cudaMemcpyToSymbol(g_trace_cap, &capacity, sizeof(capacity)));
+    CK(cudaMemcpyToSymbol(g_trace_pos, &zero, sizeof(zero)));
+    CK(cudaMemcpyToSymbol(g_trace, &h_trace_dev, sizeof(h_trace_dev)));
+    return GGML_B200_OK;
+}
+
+int ggml_b200_trace_end(unsigned long long * out, unsigned int max_records) {
+    if (!h_trace_dev) return 0;
+    cudaDeviceSynchronize();
+    unsigned long long * null_ptr = nullptr;
+    unsigned int pos = 0;
+    cudaMemcpyFromSymbol(&pos, g_trace_pos, sizeof(pos));
+    cudaMemcpyToSymbol(g_trace, &null_ptr, sizeof(null_ptr));
+    if (pos > h_trace_cap) pos = h_trace_cap;
+    if (pos > max_records) pos = max_records;
+    cudaMemcpy(out, h_trace_dev, (size_t)pos * 64, cudaMemcpyDeviceToHost);
+    cudaFree(h_trace_dev);
+    h_trace_dev = nullptr;
+    return (int)pos;
 }
 
 int ggml_b200_fused_checkpoint_q4_0(const ggml_b200_weight * w, const float * x_dev, int32_t * S_dev, void * blocks34_dev) {

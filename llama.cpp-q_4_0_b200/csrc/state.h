@@ -28,6 +28,10 @@ struct Tune {
     int gemv_ctas_per_sm = 2;    // grid = SMs * this
     int gemv_unroll = 4;         // 16-byte weight loads in flight per lane
     int gemv_nc = 0;             // cap on columns per pass (0 = by n)
+    int fused_rif = 1;           // rows in flight per warp of the fused kernel
+    int gemv_stream = 0;         // n == 1: bulk-async smem ring kernel (gemv_q4_0_stream.cuh)
+    int stream_stages = 0;       // cap on the ring depth (0 = as many as fit in 96 KB)
+    int stream_ctas_per_sm = 1;
     int gemv_fused = 1;          // n == 1: quantize inside the GEMV kernel (one launch per op)
     int fused_threads = 1024;    // threads per CTA of the fused kernel
     int fused_ctas_per_sm = 1;

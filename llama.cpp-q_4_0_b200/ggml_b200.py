@@ -81,6 +81,8 @@ def _load() -> C.CDLL:
         "ggml_b200_shard_rows": (None, [_i64, C.c_int, C.c_int, C.POINTER(_i64), C.POINTER(_i64)]),
         "ggml_b200_mul_mat_q4_0_sharded": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
         "ggml_b200_launch_count": (C.c_uint64, []),
+        "ggml_b200_trace_begin": (C.c_int, [C.c_uint]),
+        "ggml_b200_trace_end": (C.c_int, [_vp, C.c_uint]),
         "ggml_b200_dev_malloc": (_vp, [_sz]),
         "ggml_b200_dev_free": (None, [_vp]),
         "ggml_b200_memcpy_h2d": (C.c_int, [_vp, _vp, _sz]),

@@ -254,7 +254,8 @@ def test_launch_counter_counts_kernels(b200, port, ref):
     w.free()
 
 
-@pytest.mark.parametrize("M,K", [(70, 1088), (4096, 4096), (300, 18176), (1, 64)])
+@pytest.mark.parametrize("M,K", [(70, 1088), (4096, 4096), (300, 18176), (1, 64), (149, 4544), (1000, 11008),
+                                 (500, 22016), (297, 8192), (2000, 256), (40, 24576 + 64)])
 def test_fused_kernel_checkpoints_bit_exact(b200, port, ref, golden, M, K):
     """The n = 1 kernel quantizes inside the CTA: its q8_0 blocks and S_b must be the reference's,
     and its output must equal the unfused two-kernel path bit for bit (same accumulation order)."""
@@ -265,14 +266,22 @@ def test_fused_kernel_checkpoints_bit_exact(b200, port, ref, golden, M, K):
     want_q8 = port.quantize_q8_0(x)
     assert np.array_equal(q8, want_q8[0])
     assert np.array_equal(S, port.block_dots_matrix(W, want_q8)[0])
-    Yf = b200.mul_mat_host(w, x)
-    b200.set_tuning("gemv_fused", 0)
+    Ys = b200.mul_mat_host(w, x)                      # streaming kernel (default for n = 1)
+    b200.set_tuning("gemv_stream", 0)
     try:
-        Yu = b200.mul_mat_host(w, x)
+        q8r, Sr = b200.fused_checkpoint(w, x)          # register-streaming fused kernel
+        Yf = b200.mul_mat_host(w, x)
+        b200.set_tuning("gemv_fused", 0)
+        Yu = b200.mul_mat_host(w, x)                  # kernel 1 + kernel 2 as two launches
     finally:
         b200.set_tuning("gemv_fused", 1)
+        b200.set_tuning("gemv_stream", 1)
     w.free()
-    assert np.array_equal(Yf.view(np.uint32), Yu.view(np.uint32))
+    assert np.array_equal(q8r, want_q8[0]) and np.array_equal(Sr, S)
+    assert np.array_equal(Yf.view(np.uint32), Yu.view(np.uint32))   # same accumulation order
+    Yo = oracle_Y(port, ref, W, x)
+    assert_close(Ys, Yo, scale_sum(port, W, x) if M * K <= 1 << 24 else None)
+    assert_close(Yf, Yo)
 
 
 def test_fused_kernel_edge_rows(b200, golden, port, ref):

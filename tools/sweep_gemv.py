@@ -29,11 +29,21 @@ def main():
     mod.set_stream(stream.cuda_stream)
     rng = np.random.default_rng(1)
     peak, _ = bench.peaks()
-    # (fused, threads, ctas/SM, unroll, pdl)
-    cfgs = [(1, t, c, u, p) for t in (512, 1024) for c in (1, 2, 4) for u in (2, 4) for p in (0, 1) if t * c <= 2048]
-    cfgs += [(0, 512, 2, 4, p) for p in (0, 1)]
+    base = dict(gemv_fused=1, gemv_stream=0, pdl=1, gemv_unroll=4, fused_threads=1024, fused_ctas_per_sm=1, fused_rif=1)
+    cfgs = []
+    for pdl in (1, 0):
+        cfgs.append(dict(base, pdl=pdl))
+        cfgs.append(dict(base, pdl=pdl, fused_threads=512, fused_ctas_per_sm=2))
+        cfgs.append(dict(base, pdl=pdl, fused_threads=512, fused_ctas_per_sm=1, fused_rif=2))
+        cfgs.append(dict(base, pdl=pdl, fused_threads=512, fused_ctas_per_sm=1, fused_rif=2, gemv_unroll=2))
+        cfgs.append(dict(base, pdl=pdl, fused_threads=512, fused_ctas_per_sm=1, fused_rif=4, gemv_unroll=2))
+        cfgs.append(dict(base, pdl=pdl, fused_threads=512, fused_ctas_per_sm=2, fused_rif=2))
+        cfgs.append(dict(base, pdl=pdl, fused_threads=256, fused_ctas_per_sm=2, fused_rif=2))
+        cfgs.append(dict(base, pdl=pdl, fused_threads=256, fused_ctas_per_sm=2, fused_rif=4, gemv_unroll=2))
+        cfgs.append(dict(base, pdl=pdl, gemv_stream=1))
+    cfgs.append(dict(base, gemv_fused=0))
     if quick:
-        cfgs = [(1, 1024, 1, 4, 1), (1, 1024, 1, 4, 0), (1, 512, 2, 4, 1), (0, 512, 2, 4, 1)]
+        cfgs = cfgs[:3]
     results = []
     for (M, K) in (SHAPES[:4] if quick else SHAPES):
         wbytes = 18 * M * K // 32
@@ -47,16 +57,9 @@ def main():
         x = torch.randn(1, K, device="cuda")
         y = torch.zeros(1, M, device="cuda")
         best = None
-        for (fused, thr, cps, unr, pdl) in cfgs:
-            mod.set_tuning("gemv_fused", fused)
-            mod.set_tuning("pdl", pdl)
-            mod.set_tuning("gemv_unroll", unr)
-            if fused:
-                mod.set_tuning("fused_threads", thr)
-                mod.set_tuning("fused_ctas_per_sm", cps)
-            else:
-                mod.set_tuning("gemv_threads", thr)
-                mod.set_tuning("gemv_ctas_per_sm", cps)
+        for cfg in cfgs:
+            for k_, v_ in cfg.items():
+                mod.set_tuning(k_, v_)
 
             def step():
                 for h in hs:
@@ -80,13 +83,15 @@ def main():
             stream.synchronize()
             us = e0.elapsed_time(e1) * 1e3 / (reps * copies)
             gbs = bench.algo_bytes(M, K) / us / 1e3
-            r = {"M": M, "K": K, "fused": fused, "threads": thr, "ctas_per_sm": cps, "unroll": unr, "pdl": pdl, "us": us, "GBps": gbs, "frac": gbs / peak}
+            r = dict(cfg, M=M, K=K, us=us, GBps=gbs, frac=gbs / peak)
             results.append(r)
             if best is None or gbs > best["GBps"]:
                 best = r
             del g
         print(f"{M:6d}x{K:<6d} best {best['GBps']:7.0f} GB/s ({best['frac']*100:5.1f}% of measured) {best['us']:7.2f} us  "
-              f"fused={best['fused']} thr={best['threads']} cps={best['ctas_per_sm']} unroll={best['unroll']} pdl={best['pdl']}", flush=True)
+              + " ".join(f"{k_}={v_}" for k_, v_ in best.items() if k_ in base and base[k_] != v_), flush=True)
+        for r_ in sorted([x_ for x_ in results if x_["M"] == M and x_["K"] == K], key=lambda x_: x_["us"])[:6]:
+            print("        %7.2f us  " % r_["us"] + " ".join(f"{k_}={v_}" for k_, v_ in r_.items() if k_ in base and base[k_] != v_), flush=True)
         for h in hs:
             L_.ggml_b200_free_weight(h)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
