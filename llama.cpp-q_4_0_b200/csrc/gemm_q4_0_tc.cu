@@ -1,15 +1,109 @@
-// gemm_q4_0_tc.cu -- kernel 3: prefill GEMM (TMA + tcgen05 kind::i8 + TMEM).  [stub until built]
+// gemm_q4_0_tc.cu -- host side of kernel 3 (gemm_q4_0_tc.cuh): TMA tensor maps, launch, tuning.
+//
+// cuTensorMapEncodeTiled is fetched through cudaGetDriverEntryPoint so the library keeps no
+// link-time dependency on libcuda (it must load, and export its ABI, on a GPU-less build host).
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <string.h>
+
+#include "gemm_q4_0_tc.cuh"
 #include "state.h"
 
 namespace b200 {
-int  gemm_init() { return GGML_B200_OK; }
-void gemm_shutdown() {}
-int  gemm_set_tuning(const char *, int) { return GGML_B200_ERR_ARG; }
-bool gemm_available(const ggml_b200_weight *) { return false; }
-int  gemm_prepare_weight(ggml_b200_weight *) { return GGML_B200_OK; }
-void gemm_release_weight(ggml_b200_weight *) {}
-int  launch_gemm(const ggml_b200_weight *, float *, long long, int, int *) {
-    set_error("tensor-core GEMM path not built");
-    return GGML_B200_ERR_STATE;
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+static bool g_gemm_ready = false;
+
+struct GemmWeight {
+    CUtensorMap tm_nib;
+};
+
+static int encode_2d(CUtensorMap * tm, CUtensorMapDataType dt, void * base, uint64_t inner, uint64_t outer,
+                     uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer, CUtensorMapSwizzle sw) {
+    const cuuint64_t dims[2] = {inner, outer};
+    const cuuint64_t strides[1] = {row_stride_bytes};
+    const cuuint32_t box[2] = {box_inner, box_outer};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(tm, dt, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed (%d): inner %llu outer %llu stride %llu box %ux%u", (int)r,
+                  (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)row_stride_bytes, box_inner, box_outer);
+        return GGML_B200_ERR_CUDA;
+    }
+    return GGML_B200_OK;
 }
+
+int gemm_init() {
+    void * fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || fn == nullptr) {
+        cudaGetLastError();
+        set_error("cuTensorMapEncodeTiled is not available from the driver");
+        return GGML_B200_ERR_CUDA;
+    }
+    g_encode = (EncodeTiledFn)fn;
+    CK(cudaFuncSetAttribute(gemm_q4_0_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(gemm_q4_0_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+    g_gemm_ready = true;
+    return GGML_B200_OK;
+}
+
+void gemm_shutdown() { g_gemm_ready = false; }
+
+int gemm_set_tuning(const char *, int) { return GGML_B200_ERR_ARG; }
+
+bool gemm_available(const ggml_b200_weight * w) {
+    return g_gemm_ready && w && w->layout == GGML_B200_LAYOUT_PLANES && w->gemm != nullptr;
+}
+
+int gemm_prepare_weight(ggml_b200_weight * w) {
+    if (!g_gemm_ready || w->layout != GGML_B200_LAYOUT_PLANES || w->rows() == 0) return GGML_B200_OK;
+    GemmWeight * gw = new GemmWeight();
+    const uint64_t nbk = (uint64_t)(w->K / QK);
+    // nibble plane as bytes: [rows][nbk * 16], box = 4 blocks (64 B) x 128 rows, no swizzle
+    int rc = encode_2d(&gw->tm_nib, CU_TENSOR_MAP_DATA_TYPE_UINT8, w->wq, nbk * 16, (uint64_t)w->rows(), nbk * 16,
+                       GEMM_KB * 16, GEMM_BM, CU_TENSOR_MAP_SWIZZLE_NONE);
+    if (rc) { delete gw; return rc; }
+    w->gemm = gw;
+    return GGML_B200_OK;
+}
+
+void gemm_release_weight(ggml_b200_weight * w) {
+    if (w->gemm) { delete (GemmWeight *)w->gemm; w->gemm = nullptr; }
+}
+
+int launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int * S) {
+    if (!gemm_available(w)) { set_error("tensor-core GEMM path not available for this weight"); return GGML_B200_ERR_STATE; }
+    if (!g.xdT || g.xdT_n_pad < n) { set_error("activation scales were not laid out for the GEMM path"); return GGML_B200_ERR_STATE; }
+    const GemmWeight * gw = (const GemmWeight *)w->gemm;
+    const uint64_t K = (uint64_t)w->K, nbk = K / QK;
+    CUtensorMap tm_xq, tm_xd;
+    // activations int8 [n][K], box = 128 K-bytes x 128 columns, 128-byte swizzle (UMMA K-major SW128)
+    int rc = encode_2d(&tm_xq, CU_TENSOR_MAP_DATA_TYPE_UINT8, g.xq, K, (uint64_t)n, K, GEMM_KB * 32, GEMM_BN, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+    // activation scales block-major [nbk][n_pad] f32, box = 128 columns x 4 blocks
+    rc = encode_2d(&tm_xd, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, g.xdT, (uint64_t)g.xdT_n_pad, nbk, (uint64_t)g.xdT_n_pad * 4,
+                   GEMM_BN, GEMM_KB, CU_TENSOR_MAP_SWIZZLE_NONE);
+    if (rc) return rc;
+
+    const dim3 grid((unsigned)((w->rows() + GEMM_BM - 1) / GEMM_BM), (unsigned)((n + GEMM_BN - 1) / GEMM_BN));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = dim3(GEMM_THREADS); cfg.dynamicSmemBytes = GEMM_SMEM_BYTES; cfg.stream = g.stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = g.tune.pdl ? 1 : 0;
+    const __half * wd = w->wd;
+    const int rows = (int)w->rows(), nbk_i = (int)nbk;
+    if (S) CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<true>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S));
+    else   CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S));
+    g.launches++;
+    return GGML_B200_OK;
+}
+
 }  // namespace b200

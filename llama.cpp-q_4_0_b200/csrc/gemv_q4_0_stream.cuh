@@ -26,6 +26,7 @@
 // Roofline: HBM; algorithmic bytes per launch 18*M*K/32 + 4*K + 4*M.
 #pragma once
 #include "common.cuh"
+#include "ptx.cuh"
 #include "quantize_q8_0.cuh"
 
 namespace b200 {
@@ -68,33 +69,6 @@ __host__ inline StreamPlan stream_plan(int nbk) {
     // ring + barriers (2 * 8 * 8 B) + reduction scratch (2 parities * 8 warps * 4 B, padded)
     p.smem = (size_t)p.stages * p.stage_bytes + 128 + 128 + (size_t)40 * nbk;
     return p;
-}
-
-// ---- mbarrier / bulk-copy PTX ---------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
-}
-// global -> shared bulk copy through the TMA engine; size and both addresses 16-byte multiples
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void * src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 
 template <int NCL, bool DUMP>

@@ -101,12 +101,26 @@ int launch_quantize(const float * x_dev, int64_t n, int64_t K, size_t nb11, void
     const bool aligned = (((uintptr_t)x_dev | nb11) & 15) == 0;
     unsigned char * b34 = (unsigned char *)blocks34_dev;
     const long long nn = n;
-    if (aligned) {
-        if (b34) return launch_k(quantize_q8_0_kernel<true, true>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34);
-        return launch_k(quantize_q8_0_kernel<true, false>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34);
+    // the GEMM path also wants the scales block-major ([K/32][n_pad] floats)
+    float * xdT = nullptr;
+    const long long n_pad = (n + 3) & ~3ll;
+    if (n >= 2 && g.path != GGML_B200_PATH_GEMV) {
+        const size_t need = (size_t)(K / QK) * n_pad * sizeof(float);
+        if (need > g.xdT_cap) {
+            if (g.xdT) CK(cudaFree(g.xdT));
+            g.xdT = nullptr; g.xdT_cap = 0;
+            CK(cudaMalloc(&g.xdT, need));
+            g.xdT_cap = need;
+        }
+        xdT = g.xdT;
     }
-    if (b34) return launch_k(quantize_q8_0_kernel<false, true>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34);
-    return launch_k(quantize_q8_0_kernel<false, false>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34);
+    g.xdT_n_pad = n_pad;
+    if (aligned) {
+        if (b34) return launch_k(quantize_q8_0_kernel<true, true>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34, xdT, n_pad);
+        return launch_k(quantize_q8_0_kernel<true, false>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34, xdT, n_pad);
+    }
+    if (b34) return launch_k(quantize_q8_0_kernel<false, true>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34, xdT, n_pad);
+    return launch_k(quantize_q8_0_kernel<false, false>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34, xdT, n_pad);
 }
 
 // ---- kernel 2 launch ------------------------------------------------------------------------
@@ -336,6 +350,7 @@ void ggml_b200_shutdown(void) {
     cudaStreamSynchronize(g.stream);
     if (g.xq) cudaFree(g.xq);
     if (g.xds) cudaFree(g.xds);
+    if (g.xdT) cudaFree(g.xdT);
     if (g.xstage) cudaFree(g.xstage);
     if (g.ystage) cudaFree(g.ystage);
     if (g.sstage) cudaFree(g.sstage);

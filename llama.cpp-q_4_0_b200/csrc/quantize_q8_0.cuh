@@ -28,7 +28,8 @@ template <bool ALIGNED, bool WRITE_BLOCKS34>
 __global__ void __launch_bounds__(256)
 quantize_q8_0_kernel(const float * __restrict__ x, long long n, int K, size_t nb11,
                      int8_t * __restrict__ xq, int2 * __restrict__ xds,
-                     unsigned char * __restrict__ blocks34) {
+                     unsigned char * __restrict__ blocks34,
+                     float * __restrict__ xdT, long long n_pad) {
     pdl_launch_dependents();
     pdl_wait();   // x may be produced, and xq/xds still be read, by the previous kernel
     const int per_row = K >> 3;
@@ -79,6 +80,8 @@ quantize_q8_0_kernel(const float * __restrict__ x, long long n, int K, size_t nb
     *reinterpret_cast<uint2 *>(xq + row * (long long)K + 8 * j) = make_uint2(w0, w1);
     if ((j & 3) == 0) {
         xds[row * nbk + b] = make_int2(__float_as_int(__half2float(dh)), -8 * sum);
+        // block-major copy of the scales for the tensor-core GEMM's epilogue: xdT[b][row]
+        if (xdT != nullptr) xdT[(long long)b * n_pad + row] = __half2float(dh);
     }
     if (WRITE_BLOCKS34) {
         unsigned char * blk = blocks34 + (row * nbk + b) * (long long)Q8_0_BLOCK_BYTES;

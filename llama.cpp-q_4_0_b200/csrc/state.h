@@ -46,12 +46,13 @@ struct Ctx {
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
     int repack = 1;
-    int gemm_min_n = 16;
+    int gemm_min_n = 32;
     int path = GGML_B200_PATH_AUTO;
     Tune tune;
     // activation work buffer (device replacement of params->wdata, ggml.c:11354)
     int8_t * xq = nullptr;  size_t xq_cap = 0;
     int2 *   xds = nullptr; size_t xds_cap = 0;
+    float *  xdT = nullptr; size_t xdT_cap = 0; long long xdT_n_pad = 0;   // scales block-major, GEMM epilogue
     // staging for the host-pointer entry point
     float * xstage = nullptr; size_t xstage_cap = 0;
     float * ystage = nullptr; size_t ystage_cap = 0;

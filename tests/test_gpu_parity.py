@@ -317,3 +317,79 @@ def test_back_to_back_ops_with_and_without_pdl(b200, port, ref, pdl):
     finally:
         b200.set_tuning("pdl", 1)
     w1.free(); w2.free()
+
+
+# ---------------------------------------------------------------------------- kernel 3: tcgen05 GEMM
+@pytest.mark.parametrize("M,K,n", [(128, 128, 128), (128, 256, 128), (256, 1024, 64), (300, 1088, 200), (70, 64, 5),
+                                   (129, 4544, 130), (512, 4096, 512)])
+def test_gemm_block_dots_bit_exact(b200, port, ref, M, K, n):
+    """int32 S_b out of TMEM (tcgen05.mma kind::i8, one MMA per Q4_0 block) vs the scalar definition
+    (ggml.c:2593-2600): ragged M (TMA zero-fill rows), ragged n, K tail (K/32 not a multiple of 4)."""
+    W = make_weights(port, ref, M, K)
+    X = make_x(port, n, K)
+    w = b200.Weight(W)
+    S = b200.block_dots(w, X, b200.PATH_GEMM)
+    w.free()
+    want = port.block_dots_matrix(W, port.quantize_q8_0(X))
+    assert np.array_equal(S, want)
+
+
+@pytest.mark.parametrize("M,K,n", [(128, 128, 128), (300, 1088, 200), (4096, 4096, 512), (4672, 4544, 130),
+                                   (1000, 11008, 64), (256, 18176, 33), (2048, 8192, 512)])
+def test_gemm_outputs_vs_oracle(b200, port, ref, M, K, n):
+    W = make_weights(port, ref, M, K)
+    X = make_x(port, n, K)
+    b200.set_path(b200.PATH_GEMM)
+    try:
+        w = b200.Weight(W)
+        Y = b200.mul_mat_host(w, X)
+        w.free()
+    finally:
+        b200.set_path(b200.PATH_AUTO)
+    assert_close(Y, oracle_Y(port, ref, W, X, threads=16), scale_sum(port, W, X) if M * K * n <= 1 << 26 else None)
+
+
+def test_gemm_golden_op_and_gemv_agree(b200, golden, port):
+    """The golden op (reference ggml_graph_compute output) through the tensor-core path, and the two
+    device paths against each other on the same inputs."""
+    w = b200.Weight(golden["op_W"])
+    b200.set_path(b200.PATH_GEMM)
+    try:
+        Yg = b200.mul_mat_host(w, golden["op_X"])
+        b200.set_path(b200.PATH_GEMV)
+        Yv = b200.mul_mat_host(w, golden["op_X"])
+    finally:
+        b200.set_path(b200.PATH_AUTO)
+    w.free()
+    den = scale_sum(port, golden["op_W"], golden["op_X"])
+    assert_close(Yg, golden["op_Y"], den)
+    assert_close(Yg, Yv, den)
+
+
+def test_auto_dispatch_by_n(b200, port, ref):
+    """n >= gemm_min_n takes kernel 3 (1 quantize + 1 GEMM launch), below it the GEMV path."""
+    M, K = 256, 512
+    W = make_weights(port, ref, M, K)
+    w = b200.Weight(W)
+    nmin = b200.lib().ggml_b200_get_gemm_min_n()
+    for n in (nmin - 1, nmin, 3 * nmin + 1):
+        X = make_x(port, n, K)
+        Y = b200.mul_mat_host(w, X)
+        assert_close(Y, oracle_Y(port, ref, W, X), scale_sum(port, W, X))
+    w.free()
+
+
+def test_gemm_sharded_rows_disjoint(b200, port, ref):
+    M, K, n = 512, 1024, 96
+    W = make_weights(port, ref, M, K)
+    X = make_x(port, n, K)
+    Y = np.full((n, M), np.nan, np.float32)
+    b200.set_path(b200.PATH_GEMM)
+    try:
+        for lo, hi in ((0, 128), (128, 384), (384, 512)):
+            ws = b200.Weight(W, lo, hi)
+            b200.mul_mat_host(ws, X, Y)
+            ws.free()
+    finally:
+        b200.set_path(b200.PATH_AUTO)
+    assert_close(Y, oracle_Y(port, ref, W, X), scale_sum(port, W, X))
