@@ -161,6 +161,9 @@ uint64_t     ggml_b200_launch_count(void);
  * in globaltimer ns.  trace_end returns the number of records copied to `out`. */
 int          ggml_b200_trace_begin(unsigned int capacity_records);
 int          ggml_b200_trace_end(unsigned long long * out, unsigned int max_records);
+/* kernel 3 timeline (profiling aid): after ggml_b200_set_tuning("gemm_trace", 1), CTA (0,0) of every GEMM
+ * launch stamps clock64 at its pipeline hand-offs; out = 4 roles (TMA, MMA, epilogue warp 0, unpack) x 2048 */
+int          ggml_b200_gemm_trace_read(long long * out, int count);
 /* plain device memory helpers so a ctypes harness needs no other CUDA binding */
 void *       ggml_b200_dev_malloc(size_t size);
 void         ggml_b200_dev_free(void * ptr);

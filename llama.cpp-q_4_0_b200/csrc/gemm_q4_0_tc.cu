@@ -47,15 +47,30 @@ int gemm_init() {
         return GGML_B200_ERR_CUDA;
     }
     g_encode = (EncodeTiledFn)fn;
-    CK(cudaFuncSetAttribute(gemm_q4_0_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
-    CK(cudaFuncSetAttribute(gemm_q4_0_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(gemm_q4_0_tc_kernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(gemm_q4_0_tc_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(gemm_q4_0_tc_kernel<false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(gemm_q4_0_tc_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(gemm_q4_0_tc_kernel<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
     g_gemm_ready = true;
     return GGML_B200_OK;
 }
 
 void gemm_shutdown() { g_gemm_ready = false; }
 
-int gemm_set_tuning(const char *, int) { return GGML_B200_ERR_ARG; }
+// "gemm_bias": 1 = the constant-tile MMA + denormal-read epilogue (no int->float instruction), 0 = the
+// 1.5*2^23 integer-add epilogue (gemm_q4_0_tc.cuh)
+static int g_gemm_bias = 1;
+long long * g_gemm_trace = nullptr;   // debug timeline buffer (tools/trace_gemm.py)
+int gemm_set_tuning(const char * key, int value) {
+    if (!strcmp(key, "gemm_bias")) { g_gemm_bias = value != 0; return GGML_B200_OK; }
+    if (!strcmp(key, "gemm_trace")) {   // value != 0: allocate and arm the 4 x 2048 clock64 timeline buffer
+        if (g_gemm_trace) { cudaFree(g_gemm_trace); g_gemm_trace = nullptr; }
+        if (value) { CK(cudaMalloc(&g_gemm_trace, 4 * 2048 * 8)); CK(cudaMemset(g_gemm_trace, 0, 4 * 2048 * 8)); }
+        return GGML_B200_OK;
+    }
+    return GGML_B200_ERR_ARG;
+}
 
 bool gemm_available(const ggml_b200_weight * w) {
     return g_gemm_ready && w && w->layout == GGML_B200_LAYOUT_PLANES && w->gemm != nullptr;
@@ -100,10 +115,27 @@ int launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int
     cfg.attrs = attr; cfg.numAttrs = g.tune.pdl ? 1 : 0;
     const __half * wd = w->wd;
     const int rows = (int)w->rows(), nbk_i = (int)nbk;
-    if (S) CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<true>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S));
-    else   CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S));
+    if (g_gemm_trace && !S) {
+        CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<false, true, true>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace));
+    } else if (g_gemm_bias) {
+        if (S) CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<true, true, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace));
+        else   CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<false, true, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace));
+    } else {
+        if (S) CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<true, false, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace));
+        else   CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<false, false, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace));
+    }
     g.launches++;
     return GGML_B200_OK;
 }
 
 }  // namespace b200
+
+// debug: copy the kernel-3 timeline (armed with set_tuning("gemm_trace", 1)) to the host: 4 roles x 2048 clock64 stamps
+extern "C" int ggml_b200_gemm_trace_read(long long * out, int count) {
+    if (!b200::g_gemm_trace) { b200::set_error("gemm trace not armed"); return GGML_B200_ERR_STATE; }
+    if (count > 4 * 2048) count = 4 * 2048;
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaMemcpy(out, b200::g_gemm_trace, (size_t)count * 8, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return b200::cuda_fail(e, "trace read", __FILE__, __LINE__);
+    return GGML_B200_OK;
+}

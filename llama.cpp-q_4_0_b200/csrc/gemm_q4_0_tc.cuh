@@ -6,21 +6,32 @@
 //     Y[c][m] = sum_b fp32(dw[m,b]) * fp32(dx[c,b]) * S_b[m,c],  S_b = sum_j (q4_j - 8) * q8_j
 // One `tcgen05.mma.kind::i8` (M = 128 weight rows, N = 128 activation columns, K = 32 = one
 // Q4_0 block) forms the 128x128 int32 S_b exactly in TMEM; because every block has its own
-// fp16 x fp16 scale pair the int32 accumulator cannot run across blocks, so each MMA targets a
-// fresh TMEM buffer (4-deep ring) and the epilogue warps fold S_b * dw * dx into fp32 registers.
+// fp16 x fp16 scale pair the int32 accumulator cannot run across blocks, so each block's MMA
+// targets a fresh TMEM buffer (4-deep ring) and the epilogue warps fold S_b * dw * dx into fp32
+// registers.  That epilogue (2 FP32 multiply-adds per S_b element on the CUDA cores), not the
+// tensor pipe, is the bound of this formulation: 128x128 elements per block at 128 packed
+// FMA lanes per clock per SM = 256 clk against 64 clk of MMA (see DESIGN.md "Kernel 3").
 //
-// CTA = one 128 (rows) x 128 (columns) output tile, 16 warps:
-//   warp 0      TMA producer: per k-stage (4 blocks = 128 K-bytes) loads the 128x64 B nibble tile
+// CTA = one 128 (rows) x 128 (columns) output tile, 20 warps (640 threads x 96 registers):
+//   warp 18     TMA producer: per k-stage (4 blocks = 128 K-bytes) loads the 128x64 B nibble tile
 //               (plane layout), the 128x128 B int8 activation tile (SWIZZLE_128B, K-major) and the
 //               4x128 block-major activation scales, each into its own mbarrier ring
-//   warp 1      TMEM allocator + MMA issuer (one thread): 4 MMAs per stage, tcgen05.commit per MMA
-//   warps 4-7   unpack: nibbles -> signed int8 (q - 8), written K-major with the 128-byte swizzle
-//               the UMMA descriptor expects; (x + 0x78) ^ 0x80 per byte = x - 8 without carries
-//   warps 8-15  epilogue: tcgen05.ld of S_b, exact int->float by the 1.5*2^23 bias trick folded
-//               into an FMA with dw, second FMA with dx into 64 fp32 accumulators per thread;
-//               warps 8-11 own columns 0-63, warps 12-15 columns 64-127 of the same 128 TMEM lanes
-// Roofline: the north star judges it against the dense int8 tensor peak; the practical bound is the
-// epilogue (2 FMA-pipe ops + 1 ALU op per S_b element), not the tensor pipe.
+//   warp 19     TMEM allocator + MMA issuer (one thread): per block one MMA (+ one constant-tile
+//               MMA that adds 32768 to every S_b when BIAS), tcgen05.commit per block
+//   warps 16-17 unpack: nibbles -> signed int8 (q - 8), written K-major with the 128-byte swizzle
+//               the UMMA descriptor expects; (x + 0x78) ^ 0x80 per byte = x - 8 without carries.
+//               8 (row, block) items per thread and k-stage, loads batched ahead of the expansion.
+//               The same threads stage the items' weight scales (fp16 -> fp32) for the epilogue.
+//   warps 0-15  epilogue: warp = (TMEM lane quadrant, 32-column group).  tcgen05.ld of S_b, then
+//               per pair of columns two packed FMAs (fma.rn.f32x2): t = rn(S_b * dw), acc += t * dx.
+//               int -> float without a conversion instruction:
+//                 BIAS = false: f = int_as_float(S_b + 0x4B400000) = 1.5*2^23 + S_b (one IADD), and
+//                               t = fma(f, dw, -1.5*2^23*dw) = rn(S_b * dw) exactly;
+//                 BIAS = true : the constant-tile MMA made the accumulator S_b + 32768 >= 0, whose
+//                               bits read as a float are the DENORMAL (S_b + 32768) * 2^-149, exact;
+//                               t' = fma(f, dw*2^100, -2^-134 * dw*2^100) = rn(S_b * dw) * 2^-49, the
+//                               accumulators run scaled by 2^-49 and are rescaled once at the end.
+//               Same fp32 operation order either way: y = sum_b rn(rn(S_b*dw) * dx + acc).
 #pragma once
 #include <cuda.h>
 
@@ -36,18 +47,30 @@ constexpr int GEMM_NS_RAW = 4;          // nibble-tile ring
 constexpr int GEMM_NS_OP = 4;           // int8 operand ring (A unpacked + B)
 constexpr int GEMM_NS_X = 8;            // activation-scale ring
 constexpr int GEMM_NS_D = 4;            // TMEM accumulator ring (4 x 128 columns = 512)
-constexpr int GEMM_THREADS = 512;
-constexpr int GEMM_UNPACK_WARP0 = 4, GEMM_EPI_WARP0 = 8;
+constexpr int GEMM_THREADS = 640;
+// Warp roles, lowest id first.  The SM's warp schedulers favour the HIGHEST warp id among eligible warps, so the
+// producers sit on top: the single MMA-issuing thread and the TMA thread must never queue behind 16 warps of FMAs
+// (measured: with the issuer as warp 1 every block cost it ~400 clk of issue-slot starvation).
+constexpr int GEMM_EPI_WARP0 = 4, GEMM_EPI_WARPS = 16, GEMM_UNPACK_WARP0 = 2, GEMM_UNPACK_WARPS = 2;
+constexpr int GEMM_TMA_WARP = 0, GEMM_MMA_WARP = 1;
+constexpr int GEMM_UNPACK_ROWS = GEMM_BM / (GEMM_UNPACK_WARPS * 8);   // rows per unpack thread (8)
+// 640 threads x 96 registers (65536 / 640 = 102 -> 96): the epilogue (32 accumulators + 32 S_b + operands)
+// fits without spills, so no setmaxnreg re-split is needed.
 
 constexpr int GEMM_RAW_BYTES = GEMM_BM * GEMM_KB * 16;          // 8 KB
 constexpr int GEMM_A_BYTES = GEMM_BM * GEMM_KB * 32;            // 16 KB
 constexpr int GEMM_B_BYTES = GEMM_BN * GEMM_KB * 32;            // 16 KB
-constexpr int GEMM_X_BYTES = GEMM_KB * GEMM_BN * 4;             // 2 KB
+constexpr int GEMM_DW_STRIDE = 136;     // floats per block row of staged weight scales (== 8 mod 32: conflict-free stores)
+constexpr int GEMM_XD_BYTES = GEMM_KB * GEMM_BN * 4;            // 2 KB   activation scales [4][128] f32 (TMA)
+constexpr int GEMM_DW_BYTES = GEMM_KB * GEMM_DW_STRIDE * 4;     // 2176 B weight scales [4][136] f32 (unpack warps)
+constexpr int GEMM_X_BYTES = GEMM_XD_BYTES + GEMM_DW_BYTES;     // 4224 B (33 * 128)
 constexpr int GEMM_SMEM_OP = 0;                                                    // 1024-aligned
-constexpr int GEMM_SMEM_RAW = GEMM_SMEM_OP + GEMM_NS_OP * (GEMM_A_BYTES + GEMM_B_BYTES);
+constexpr int GEMM_SMEM_CONST = GEMM_SMEM_OP + GEMM_NS_OP * (GEMM_A_BYTES + GEMM_B_BYTES);   // 16 KB of bytes = 32
+constexpr int GEMM_SMEM_RAW = GEMM_SMEM_CONST + GEMM_A_BYTES;
 constexpr int GEMM_SMEM_X = GEMM_SMEM_RAW + GEMM_NS_RAW * GEMM_RAW_BYTES;
 constexpr int GEMM_SMEM_BAR = GEMM_SMEM_X + GEMM_NS_X * GEMM_X_BYTES;
-constexpr int GEMM_SMEM_BYTES = GEMM_SMEM_BAR + 512 + 1024;                        // + alignment slack
+constexpr int GEMM_SMEM_BYTES = GEMM_SMEM_BAR + 512;
+static_assert(GEMM_SMEM_BYTES <= 227 * 1024, "shared memory budget");
 
 struct GemmBars {   // byte offsets of the mbarriers inside the barrier block
     static constexpr int raw_full = 0, raw_empty = 8 * GEMM_NS_RAW;
@@ -64,17 +87,21 @@ __device__ __forceinline__ void unpack_q4_word(uint32_t w, uint32_t & lo, uint32
     hi = (((w >> 4) & 0x0F0F0F0Fu) + 0x78787878u) ^ 0x80808080u;
 }
 
-template <bool DUMP>
+// TRACE: CTA (0,0) stamps clock64 at its pipeline hand-offs into trc (tools/trace_gemm.py); compiled out otherwise
+template <bool DUMP, bool BIAS, bool TRACE>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_q4_0_tc_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble plane  [rows][nbk*16 B], box 64 B x 128
                     const __grid_constant__ CUtensorMap tm_xq,    // activations   [n][K] int8,      box 128 B x 128, SW128
                     const __grid_constant__ CUtensorMap tm_xd,    // act. scales   [nbk][n_pad] f32, box 128 x 4
                     const __half * __restrict__ wd,               // weight scales [rows][nbk]
                     float * __restrict__ y, long long ldy, int rows, int n, int nbk,
-                    int * __restrict__ S_out) {
-    extern __shared__ unsigned char smem_unaligned[];
-    unsigned char * smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_unaligned) + 1023) & ~(uintptr_t)1023);
+                    int * __restrict__ S_out, long long * __restrict__ trc) {
+#define GEMM_TR(role, idx) do { if (TRACE && trc != nullptr && blockIdx.x == 0 && blockIdx.y == 0) trc[(role) * 2048 + (idx)] = clock64(); } while (0)
+    // no static shared memory in this kernel: the dynamic window starts 1024-byte aligned (checked below),
+    // which the 128-byte swizzle atoms need; a computed alignment would be rematerialised all over the epilogue
+    extern __shared__ __align__(1024) unsigned char smem[];
     const uint32_t sbase = smem_u32(smem);
+    if ((sbase & 1023u) != 0) __trap();
     const uint32_t bars = sbase + GEMM_SMEM_BAR;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = blockIdx.x * GEMM_BM;       // first weight row of the tile
@@ -82,16 +109,22 @@ gemm_q4_0_tc_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble plan
     const int nstages = (nbk + GEMM_KB - 1) / GEMM_KB;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < GEMM_NS_RAW; i++) { mbar_init(bars + GemmBars::raw_full + 8 * i, 1); mbar_init(bars + GemmBars::raw_empty + 8 * i, 4); }
-        for (int i = 0; i < GEMM_NS_OP; i++)  { mbar_init(bars + GemmBars::op_full + 8 * i, 1 + 4); mbar_init(bars + GemmBars::op_empty + 8 * i, 1); }
-        for (int i = 0; i < GEMM_NS_X; i++)   { mbar_init(bars + GemmBars::x_full + 8 * i, 1); mbar_init(bars + GemmBars::x_empty + 8 * i, 8); }
-        for (int i = 0; i < GEMM_NS_D; i++)   { mbar_init(bars + GemmBars::d_full + 8 * i, 1); mbar_init(bars + GemmBars::d_empty + 8 * i, 8); }
+        for (int i = 0; i < GEMM_NS_RAW; i++) { mbar_init(bars + GemmBars::raw_full + 8 * i, 1); mbar_init(bars + GemmBars::raw_empty + 8 * i, GEMM_UNPACK_WARPS); }
+        for (int i = 0; i < GEMM_NS_OP; i++)  { mbar_init(bars + GemmBars::op_full + 8 * i, 1 + GEMM_UNPACK_WARPS); mbar_init(bars + GemmBars::op_empty + 8 * i, 1); }
+        for (int i = 0; i < GEMM_NS_X; i++)   { mbar_init(bars + GemmBars::x_full + 8 * i, 1 + GEMM_UNPACK_WARPS); mbar_init(bars + GemmBars::x_empty + 8 * i, GEMM_EPI_WARPS); }
+        for (int i = 0; i < GEMM_NS_D; i++)   { mbar_init(bars + GemmBars::d_full + 8 * i, 1); mbar_init(bars + GemmBars::d_empty + 8 * i, GEMM_EPI_WARPS); }
         mbar_fence_init();
         tma_prefetch_desc(&tm_nib); tma_prefetch_desc(&tm_xq); tma_prefetch_desc(&tm_xd);
     }
-    if (warp == 1) {
+    if (warp == GEMM_MMA_WARP) {
         tmem_alloc(bars + GemmBars::tmem_slot, 512);
         tmem_relinquish();
+    }
+    if (BIAS) {
+        // constant operand tile: every byte = 32, so a K = 32 MMA of it with itself adds 32*32*32 = 32768
+        uint4 * cst = reinterpret_cast<uint4 *>(smem + GEMM_SMEM_CONST);
+        for (int i = threadIdx.x; i < GEMM_A_BYTES / 16; i += GEMM_THREADS) cst[i] = make_uint4(0x20202020u, 0x20202020u, 0x20202020u, 0x20202020u);
+        fence_proxy_async_smem();
     }
     tc_fence_before_sync();
     __syncthreads();
@@ -100,31 +133,35 @@ gemm_q4_0_tc_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble plan
     pdl_wait();   // the quantized activations come from the previous kernel
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(smem + GEMM_SMEM_BAR + GemmBars::tmem_slot);
 
-    if (warp == 0) {
-        // ===== TMA producer =====
-        if (lane == 0) {
+    if (warp < GEMM_EPI_WARP0) {
+      if (warp < GEMM_UNPACK_WARP0) {
+        if (warp == GEMM_TMA_WARP && lane == 0) {
+            // ===== TMA producer =====
             for (int s = 0; s < nstages; s++) {
                 const int sr = s % GEMM_NS_RAW, so = s % GEMM_NS_OP, sx = s % GEMM_NS_X;
                 if (s >= GEMM_NS_RAW) mbar_wait(bars + GemmBars::raw_empty + 8 * sr, ((s / GEMM_NS_RAW) - 1) & 1);
+                GEMM_TR(0, 3 * s);
                 mbar_expect_tx(bars + GemmBars::raw_full + 8 * sr, GEMM_RAW_BYTES);
                 tma_load_2d(sbase + GEMM_SMEM_RAW + sr * GEMM_RAW_BYTES, &tm_nib, s * GEMM_KB * 16, m0, bars + GemmBars::raw_full + 8 * sr);
-                if (s >= GEMM_NS_X) mbar_wait(bars + GemmBars::x_empty + 8 * sx, ((s / GEMM_NS_X) - 1) & 1);
-                mbar_expect_tx(bars + GemmBars::x_full + 8 * sx, GEMM_X_BYTES);
-                tma_load_2d(sbase + GEMM_SMEM_X + sx * GEMM_X_BYTES, &tm_xd, c0, s * GEMM_KB, bars + GemmBars::x_full + 8 * sx);
                 if (s >= GEMM_NS_OP) mbar_wait(bars + GemmBars::op_empty + 8 * so, ((s / GEMM_NS_OP) - 1) & 1);
                 mbar_expect_tx(bars + GemmBars::op_full + 8 * so, GEMM_B_BYTES);
                 tma_load_2d(sbase + GEMM_SMEM_OP + so * (GEMM_A_BYTES + GEMM_B_BYTES) + GEMM_A_BYTES, &tm_xq, s * GEMM_KB * 32, c0,
                             bars + GemmBars::op_full + 8 * so);
+                GEMM_TR(0, 3 * s + 1);
+                if (s >= GEMM_NS_X) mbar_wait(bars + GemmBars::x_empty + 8 * sx, ((s / GEMM_NS_X) - 1) & 1);
+                GEMM_TR(0, 3 * s + 2);
+                mbar_expect_tx(bars + GemmBars::x_full + 8 * sx, GEMM_XD_BYTES);
+                tma_load_2d(sbase + GEMM_SMEM_X + sx * GEMM_X_BYTES, &tm_xd, c0, s * GEMM_KB, bars + GemmBars::x_full + 8 * sx);
             }
-        }
-    } else if (warp == 1) {
-        // ===== MMA issuer =====
-        if (lane == 0) {
+        } else if (warp == GEMM_MMA_WARP && lane == 0) {
+            // ===== MMA issuer =====
             const uint32_t idesc = umma_idesc_i8(GEMM_BM, GEMM_BN);
+            const uint64_t cdesc = umma_desc_k_sw128(sbase + GEMM_SMEM_CONST);
             int blk = 0;
             for (int s = 0; s < nstages; s++) {
                 const int so = s % GEMM_NS_OP;
                 mbar_wait(bars + GemmBars::op_full + 8 * so, (s / GEMM_NS_OP) & 1);
+                GEMM_TR(1, 512 + s);
                 tc_fence_after_sync();
                 const uint32_t a_addr = sbase + GEMM_SMEM_OP + so * (GEMM_A_BYTES + GEMM_B_BYTES);
                 const uint32_t b_addr = a_addr + GEMM_A_BYTES;
@@ -132,135 +169,185 @@ gemm_q4_0_tc_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble plan
                 for (int j = 0; j < nb; j++, blk++) {
                     const int d = blk % GEMM_NS_D;
                     if (blk >= GEMM_NS_D) mbar_wait(bars + GemmBars::d_empty + 8 * d, ((blk / GEMM_NS_D) - 1) & 1);
+                    GEMM_TR(1, blk);
                     tc_fence_after_sync();
                     mma_i8_ss(tmem_base + d * GEMM_BN, umma_desc_k_sw128(a_addr + j * 32), umma_desc_k_sw128(b_addr + j * 32), idesc, 0u);
+                    if (BIAS) mma_i8_ss(tmem_base + d * GEMM_BN, cdesc, cdesc, idesc, 1u);
                     mma_commit(bars + GemmBars::d_full + 8 * d);
                 }
                 mma_commit(bars + GemmBars::op_empty + 8 * so);   // operands of this stage are free again
             }
         }
-    } else if (warp >= GEMM_UNPACK_WARP0 && warp < GEMM_EPI_WARP0) {
+      } else {
         // ===== unpack: nibble tile -> K-major int8 A tile with the 128-byte swizzle =====
-        const int t = threadIdx.x - GEMM_UNPACK_WARP0 * 32;      // 0..127
+        // 64 threads x 8 (row, block) items per k-stage; all 8 shared-memory loads are issued before the
+        // first is expanded so the two warps run at issue rate, not at LDS + ALU-chain latency
+        const int t = threadIdx.x - GEMM_UNPACK_WARP0 * 32;      // 0..63
         const int j = t & 3;                                       // block within the stage
-        for (int s = 0; s < nstages; s++) {
-            const int sr = s % GEMM_NS_RAW, so = s % GEMM_NS_OP;
-            mbar_wait(bars + GemmBars::raw_full + 8 * sr, (s / GEMM_NS_RAW) & 1);
-            if (s >= GEMM_NS_OP) mbar_wait(bars + GemmBars::op_empty + 8 * so, ((s / GEMM_NS_OP) - 1) & 1);
-            const unsigned char * raw = smem + GEMM_SMEM_RAW + sr * GEMM_RAW_BYTES;
-            unsigned char * a = smem + GEMM_SMEM_OP + so * (GEMM_A_BYTES + GEMM_B_BYTES);
+        constexpr int RSTEP = GEMM_UNPACK_WARPS * 8;              // tile rows between this thread's items (16)
+        // the same threads stage the weight scales of their items (fp16 -> fp32, x 2^100 when BIAS) for the
+        // epilogue; the global loads run one k-stage ahead
+        const unsigned short * wd16 = reinterpret_cast<const unsigned short *>(wd);
+        const float dscale = BIAS ? 1.2676506002282294e30f : 1.0f;
+        unsigned short dnext[GEMM_UNPACK_ROWS];
 #pragma unroll
-            for (int i = 0; i < 4; i++) {
-                const int r = (t >> 2) + 32 * i;                  // tile row
-                const uint4 q = *reinterpret_cast<const uint4 *>(raw + r * 64 + j * 16);
+        for (int i = 0; i < GEMM_UNPACK_ROWS; i++) {
+            const int m = m0 + (t >> 2) + RSTEP * i;
+            dnext[i] = (m < rows && j < nbk) ? ldg_stream_u16(wd16 + (size_t)m * nbk + j) : (unsigned short)0;
+        }
+        for (int s = 0; s < nstages; s++) {
+            const int sr = s % GEMM_NS_RAW, so = s % GEMM_NS_OP, sx = s % GEMM_NS_X;
+            if (t == 0) GEMM_TR(3, 4 * s);
+            mbar_wait(bars + GemmBars::raw_full + 8 * sr, (s / GEMM_NS_RAW) & 1);
+            if (t == 0) GEMM_TR(3, 4 * s + 1);
+            const uint32_t raw = sbase + GEMM_SMEM_RAW + sr * GEMM_RAW_BYTES + (t >> 2) * 64 + j * 16;
+            uint4 q[GEMM_UNPACK_ROWS];
+#pragma unroll
+            for (int i = 0; i < GEMM_UNPACK_ROWS; i++) q[i] = lds_u32x4(raw + RSTEP * i * 64);
+            if (s >= GEMM_NS_OP) mbar_wait(bars + GemmBars::op_empty + 8 * so, ((s / GEMM_NS_OP) - 1) & 1);
+            if (s >= GEMM_NS_X) mbar_wait(bars + GemmBars::x_empty + 8 * sx, ((s / GEMM_NS_X) - 1) & 1);
+            if (t == 0) GEMM_TR(3, 4 * s + 2);
+            const uint32_t a = sbase + GEMM_SMEM_OP + so * (GEMM_A_BYTES + GEMM_B_BYTES);
+            const uint32_t dws = sbase + GEMM_SMEM_X + sx * GEMM_X_BYTES + GEMM_XD_BYTES;
+#pragma unroll
+            for (int i = 0; i < GEMM_UNPACK_ROWS; i++)
+                sts_f32(dws + (j * GEMM_DW_STRIDE + (t >> 2) + RSTEP * i) * 4, half_bits_to_float(dnext[i]) * dscale);
+            if (s + 1 < nstages) {
+                const int b = (s + 1) * GEMM_KB + j;
+#pragma unroll
+                for (int i = 0; i < GEMM_UNPACK_ROWS; i++) {
+                    const int m = m0 + (t >> 2) + RSTEP * i;
+                    dnext[i] = (m < rows && b < nbk) ? ldg_stream_u16(wd16 + (size_t)m * nbk + b) : (unsigned short)0;
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < GEMM_UNPACK_ROWS; i++) {
+                const int r = (t >> 2) + RSTEP * i;               // tile row
                 uint4 lo, hi;
-                unpack_q4_word(q.x, lo.x, hi.x);
-                unpack_q4_word(q.y, lo.y, hi.y);
-                unpack_q4_word(q.z, lo.z, hi.z);
-                unpack_q4_word(q.w, lo.w, hi.w);
+                unpack_q4_word(q[i].x, lo.x, hi.x);
+                unpack_q4_word(q[i].y, lo.y, hi.y);
+                unpack_q4_word(q[i].z, lo.z, hi.z);
+                unpack_q4_word(q[i].w, lo.w, hi.w);
                 // K bytes [32j, 32j+16) = elements 0..15 (low nibbles), [32j+16, 32j+32) = elements 16..31
-                unsigned char * row = a + r * 128;
-                *reinterpret_cast<uint4 *>(row + (((2 * j) ^ (r & 7)) << 4)) = lo;
-                *reinterpret_cast<uint4 *>(row + (((2 * j + 1) ^ (r & 7)) << 4)) = hi;
+                const uint32_t row = a + r * 128;
+                sts_u32x4(row + (((2 * j) ^ (r & 7)) << 4), lo);
+                sts_u32x4(row + (((2 * j + 1) ^ (r & 7)) << 4), hi);
             }
             fence_proxy_async_smem();      // generic-proxy stores -> tensor-core (async proxy) reads
             __syncwarp();
+            if (t == 0) GEMM_TR(3, 4 * s + 3);
             if (lane == 0) {
                 mbar_arrive(bars + GemmBars::op_full + 8 * so);
                 mbar_arrive(bars + GemmBars::raw_empty + 8 * sr);
+                mbar_arrive(bars + GemmBars::x_full + 8 * sx);
             }
         }
-    } else if (warp >= GEMM_EPI_WARP0) {
+      }
+    } else {
         // ===== epilogue: S_b (TMEM) * dw * dx -> fp32 accumulators =====
-        const int ew = warp - GEMM_EPI_WARP0;          // 0..7
+        const int ew = warp - GEMM_EPI_WARP0;          // 0..15 (GEMM_EPI_WARP0 is a multiple of 4)
         const int quad = ew & 3;                        // TMEM lane quadrant (== warp % 4)
-        const int half = ew >> 2;                       // column half: 0 -> 0..63, 1 -> 64..127
+        const int cg = ew >> 2;                         // 32-column group
         const int m = m0 + quad * 32 + lane;            // this thread's weight row
         const bool row_ok = m < rows;
-        const unsigned short * drow = reinterpret_cast<const unsigned short *>(wd) + (size_t)(row_ok ? m : 0) * nbk;
-        const uint32_t t_lane = tmem_base + ((uint32_t)(quad * 32) << 16) + half * 64;
-        const float MAGIC = 12582912.0f;                // 1.5 * 2^23: int_as_float(S + bits(MAGIC)) == MAGIC + S exactly
-
-        float acc[64];
+        const bool cols_live = c0 + cg * 32 < n;        // warp-uniform: any real column in this group?
+        const uint32_t t_lane = tmem_base + ((uint32_t)(quad * 32) << 16) + cg * 32;
+        // BIAS: accumulator bits = denormal (S_b + 32768) * 2^-149;  2^-134 = 32768 * 2^-149
+        const float NEG_OFFSET = BIAS ? -__int_as_float(32768) : -12582912.0f;
+        uint64_t acc[16];
 #pragma unroll
-        for (int i = 0; i < 64; i++) acc[i] = 0.0f;
+        for (int i = 0; i < 16; i++) acc[i] = 0ull;
 
-        unsigned short dnext[GEMM_KB];
-#pragma unroll
-        for (int jj = 0; jj < GEMM_KB; jj++) dnext[jj] = (row_ok && jj < nbk) ? ldg_stream_u16(drow + jj) : (unsigned short)0;
-
-        int blk = 0;
+        // block j of a stage always lands in accumulator buffer j (GEMM_KB == GEMM_NS_D), so every
+        // barrier / TMEM / shared address below is a per-stage base plus a compile-time offset
+        static_assert(GEMM_KB == GEMM_NS_D, "block j of a k-stage uses TMEM buffer j");
+        int sx = 0;
+        uint32_t xph = 0;
         for (int s = 0; s < nstages; s++) {
-            const int sx = s % GEMM_NS_X;
-            unsigned short dcur[GEMM_KB];
-#pragma unroll
-            for (int jj = 0; jj < GEMM_KB; jj++) dcur[jj] = dnext[jj];
-            if (s + 1 < nstages) {
-#pragma unroll
-                for (int jj = 0; jj < GEMM_KB; jj++) {
-                    const int b = (s + 1) * GEMM_KB + jj;
-                    dnext[jj] = (row_ok && b < nbk) ? ldg_stream_u16(drow + b) : (unsigned short)0;
-                }
-            }
-            mbar_wait(bars + GemmBars::x_full + 8 * sx, (s / GEMM_NS_X) & 1);
-            const float * xs = reinterpret_cast<const float *>(smem + GEMM_SMEM_X + sx * GEMM_X_BYTES) + half * 64;
+            const uint32_t dph = s & 1;
+            const uint32_t slot = sbase + GEMM_SMEM_X + sx * GEMM_X_BYTES;
+            const uint32_t xs = slot + cg * 32 * 4;
+            const uint32_t dws = slot + GEMM_XD_BYTES + (quad * 32 + lane) * 4;
+            mbar_wait(bars + GemmBars::x_full + 8 * sx, xph);
             const int nb = min(GEMM_KB, nbk - s * GEMM_KB);
-#pragma unroll
+#pragma unroll 1
             for (int jj = 0; jj < GEMM_KB; jj++) {
                 if (jj < nb) {
-                    const int d = blk % GEMM_NS_D;
-                    mbar_wait(bars + GemmBars::d_full + 8 * d, (blk / GEMM_NS_D) & 1);
+                    if (ew == 0 && lane == 0) GEMM_TR(2, 8 * (s * GEMM_KB + jj));
+                    mbar_wait(bars + GemmBars::d_full + 8 * jj, dph);
+                    if (ew == 0 && lane == 0) GEMM_TR(2, 8 * (s * GEMM_KB + jj) + 1);
                     tc_fence_after_sync();
-                    const float dw = half_bits_to_float(dcur[jj]);
-                    const float nc = -MAGIC * dw;                         // exact: dw has 11 significant bits
-                    const float * xrow = xs + jj * GEMM_BN;
+                    if (cols_live) {
+                        const float dw = lds_f32(dws + jj * GEMM_DW_STRIDE * 4);
+                        const float nc = NEG_OFFSET * dw;                 // exact: dw has 11 significant bits
+                        const uint64_t dw2 = pack_f32x2(dw, dw), nc2 = pack_f32x2(nc, nc);
+                        // two halves of 16 columns: 16 live S_b registers instead of 32 keeps the thread under
+                        // 96 registers without address rematerialisation or accumulator copies
 #pragma unroll
-                    for (int ch = 0; ch < 2; ch++) {
-                        uint32_t sreg[32];
-                        tmem_ld_32x32(t_lane + d * GEMM_BN + ch * 32, sreg);
-                        tmem_ld_wait();
-                        if (ch == 1) {
-                            // both halves of this thread's 64 columns are in registers: free the buffer
-                            tc_fence_before_sync();
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive(bars + GemmBars::d_empty + 8 * d);
-                        }
-#pragma unroll
-                        for (int i = 0; i < 32; i += 4) {
-                            const float4 dx4 = *reinterpret_cast<const float4 *>(xrow + ch * 32 + i);   // warp-uniform broadcast
-                            const float dxv[4] = {dx4.x, dx4.y, dx4.z, dx4.w};
-#pragma unroll
-                            for (int k = 0; k < 4; k++) {
-                                const int sb = (int)sreg[i + k];
-                                if (DUMP) {
-                                    const int c = c0 + half * 64 + ch * 32 + i + k;
-                                    if (row_ok && c < n) S_out[((size_t)c * rows + m) * nbk + (s * GEMM_KB + jj)] = sb;
-                                }
-                                const float f = __int_as_float(sb + 0x4B400000);      // MAGIC + S_b, exact
-                                const float tt = fmaf(f, dw, nc);                     // == rn(S_b * dw)
-                                acc[ch * 32 + i + k] = fmaf(tt, dxv[k], acc[ch * 32 + i + k]);
+                        for (int h = 0; h < 2; h++) {
+                            uint32_t sreg[16];
+                            tmem_ld_32x16(t_lane + jj * GEMM_BN + h * 16, sreg);
+                            tmem_ld_wait();
+                            if (ew == 0 && lane == 0) GEMM_TR(2, 8 * (s * GEMM_KB + jj) + 2 + 2 * h);
+                            if (h == 1) {
+                                // this warp's slice of the buffer is in registers: hand it back to the MMA issuer
+                                tc_fence_before_sync();
+                                __syncwarp();
+                                if (lane == 0) mbar_arrive(bars + GemmBars::d_empty + 8 * jj);
                             }
+#pragma unroll
+                            for (int i = 0; i < 16; i += 4) {
+                                const float4 dx4 = lds_f32x4(xs + (jj * GEMM_BN + h * 16 + i) * 4);   // warp-uniform broadcast
+                                uint32_t f0 = sreg[i], f1 = sreg[i + 1], f2 = sreg[i + 2], f3 = sreg[i + 3];
+                                if (DUMP) {
+                                    const int c = c0 + cg * 32 + h * 16 + i;
+                                    const int off = BIAS ? 32768 : 0;
+                                    if (row_ok) {
+                                        int * dst = S_out + ((size_t)c * rows + m) * nbk + (s * GEMM_KB + jj);
+                                        const size_t cs = (size_t)rows * nbk;
+                                        if (c < n)     dst[0] = (int)f0 - off;
+                                        if (c + 1 < n) dst[cs] = (int)f1 - off;
+                                        if (c + 2 < n) dst[2 * cs] = (int)f2 - off;
+                                        if (c + 3 < n) dst[3 * cs] = (int)f3 - off;
+                                    }
+                                }
+                                if (!BIAS) { f0 += 0x4B400000u; f1 += 0x4B400000u; f2 += 0x4B400000u; f3 += 0x4B400000u; }
+                                const uint64_t t01 = fma_f32x2(pack_u32x2(f0, f1), dw2, nc2);   // == rn(S_b * dw) (x 2^-49 when BIAS)
+                                const uint64_t t23 = fma_f32x2(pack_u32x2(f2, f3), dw2, nc2);
+                                fma_acc_f32x2(acc[(h * 16 + i) / 2], t01, pack_f32x2(dx4.x, dx4.y));
+                                fma_acc_f32x2(acc[(h * 16 + i) / 2 + 1], t23, pack_f32x2(dx4.z, dx4.w));
+                            }
+                            if (ew == 0 && lane == 0) GEMM_TR(2, 8 * (s * GEMM_KB + jj) + 3 + 2 * h);
                         }
+                    } else {
+                        // no real column in this group: only keep the buffer ring moving
+                        tc_fence_before_sync();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(bars + GemmBars::d_empty + 8 * jj);
                     }
-                    blk++;
                 }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(bars + GemmBars::x_empty + 8 * sx);
+            if (++sx == GEMM_NS_X) { sx = 0; xph ^= 1; }
         }
         // store: for a fixed column the 32 lanes of a warp hold 32 consecutive rows -> 128-byte stores
-        if (row_ok) {
+        if (row_ok && cols_live) {
+            const float rescale = BIAS ? 562949953421312.0f : 1.0f;   // 2^49
 #pragma unroll
-            for (int i = 0; i < 64; i++) {
-                const int c = c0 + half * 64 + i;
-                if (c < n) y[(size_t)c * ldy + m] = acc[i];
+            for (int i = 0; i < 16; i++) {
+                float a0, a1;
+                unpack_f32x2(acc[i], a0, a1);
+                const int c = c0 + cg * 32 + 2 * i;
+                if (c < n)     y[(size_t)c * ldy + m] = a0 * rescale;
+                if (c + 1 < n) y[(size_t)(c + 1) * ldy + m] = a1 * rescale;
             }
         }
     }
 
     tc_fence_before_sync();
     __syncthreads();
-    if (warp == 1) {
+    if (warp == GEMM_MMA_WARP) {
         tc_fence_after_sync();
         tmem_dealloc(tmem_base, 512);
     }

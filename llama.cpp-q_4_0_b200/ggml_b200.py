@@ -83,6 +83,7 @@ def _load() -> C.CDLL:
         "ggml_b200_launch_count": (C.c_uint64, []),
         "ggml_b200_trace_begin": (C.c_int, [C.c_uint]),
         "ggml_b200_trace_end": (C.c_int, [_vp, C.c_uint]),
+        "ggml_b200_gemm_trace_read": (C.c_int, [_vp, C.c_int]),
         "ggml_b200_dev_malloc": (_vp, [_sz]),
         "ggml_b200_dev_free": (None, [_vp]),
         "ggml_b200_memcpy_h2d": (C.c_int, [_vp, _vp, _sz]),

@@ -1,0 +1,48 @@
+"""Small ncu target (GPU box): a few launches of each hot kernel through the C ABI on BASELINE
+shapes -- the fused n = 1 GEMV on 4096x4096 and 11008x4096, and kernel 1 + the tcgen05 GEMM at
+n = 512 on 4096x4096 and 11008x4096.  Kept short because `ncu --set full` replays each launch
+~40 times.  Not part of the product."""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+
+
+def main():
+    mod = bench.load_binding()
+    mod.init(0)
+    L_ = mod.lib()
+    ns = (1, 512)
+    if "--gemm-only" in sys.argv:
+        ns = (512,)
+    if "--gemv-only" in sys.argv:
+        ns = (1,)
+    for kv in sys.argv[1:]:
+        if "=" in kv:
+            k, v = kv.split("=")
+            mod.set_tuning(k, int(v))
+    rng = np.random.default_rng(3)
+    for (M, K) in [(4096, 4096), (11008, 4096)]:
+        blk = bench.random_q4_0(rng, M, K)
+        w = mod.Weight(blk)
+        for n in ns:
+            x = mod.DevBuf.from_numpy(rng.standard_normal((n, K), dtype=np.float32))
+            y = mod.DevBuf(n * M * 4)
+            for _ in range(3):
+                rc = L_.ggml_b200_mul_mat_q4_0(w.h, C.c_void_p(x.ptr), n, K * 4, C.c_void_p(y.ptr), M * 4)
+                assert rc == 0, L_.ggml_b200_last_error()
+            mod.synchronize()
+            x.free()
+            y.free()
+        w.free()
+    mod.shutdown()
+    print("ncu target done")
+
+
+if __name__ == "__main__":
+    main()
