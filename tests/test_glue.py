@@ -1,0 +1,101 @@
+"""The drop-in seam itself: the UNMODIFIED reference ggml.c built with -DGGML_USE_CUBLAS, linked against
+llama.cpp-q_4_0_b200/ggml_glue/ggml-b200-glue.c + libggml_b200.so instead of the reference's ggml-cuda.o
+(ggml_glue/Makefile).  The tests drive the reference's own public graph API (ggml_mul_mat + ggml_graph_compute,
+tests/glue/graph_driver.c) with the weight tagged GGML_BACKEND_GPU, i.e. exactly what llama.cpp's loader and
+eval do for an offloaded layer (llama.cpp:678-685, :1573), and compare with the same library's CPU path.
+
+The prebuilt library travels to the GPU box; where neither it nor /root/reference exists the tests skip."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import PKG, ROOT, load_binding
+
+GLUE_SO = os.path.join(PKG, "ggml_glue", "_build", "libggml_b200_glue_ref.so")
+
+
+def _glue():
+    if not os.path.exists(GLUE_SO):
+        pytest.skip("ggml_glue/_build/libggml_b200_glue_ref.so not built (needs /root/reference at build time)")
+    load_binding().lib()   # libggml_b200.so first, so both bindings share one copy of the library state
+    G = C.CDLL(GLUE_SO)
+    G.glue_graph_mul_mat.restype = C.c_int
+    G.glue_graph_mul_mat.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int]
+    return G
+
+
+def _run(G, W, wtype, M, K, X, offload, threads=4):
+    n = X.shape[0]
+    Y = np.zeros((n, M), np.float32)
+    Wc = np.ascontiguousarray(W)
+    Xc = np.ascontiguousarray(X, dtype=np.float32)
+    rc = G.glue_graph_mul_mat(Wc.ctypes.data_as(C.c_void_p), wtype, M, K, Xc.ctypes.data_as(C.c_void_p), n,
+                              Y.ctypes.data_as(C.c_void_p), threads, offload)
+    assert rc == 0
+    return Y
+
+
+def test_glue_defines_every_symbol_of_the_reference_header():
+    """Link compatibility: every function the reference declares in ggml-cuda.h is exported by the glue."""
+    G = _glue()
+    names = ["ggml_init_cublas", "ggml_cuda_set_tensor_split", "ggml_cuda_mul", "ggml_cuda_can_mul_mat",
+             "ggml_cuda_mul_mat_get_wsize", "ggml_cuda_mul_mat", "ggml_cuda_host_malloc", "ggml_cuda_host_free",
+             "ggml_cuda_transform_tensor", "ggml_cuda_free_data", "ggml_cuda_assign_buffers",
+             "ggml_cuda_assign_buffers_no_scratch", "ggml_cuda_assign_buffers_force_inplace", "ggml_cuda_set_main_device",
+             "ggml_cuda_set_scratch_size", "ggml_cuda_free_scratch", "ggml_cuda_compute_forward"]
+    ref_header = "/root/reference/ggml-cuda.h"
+    if os.path.exists(ref_header):   # in the build container: take the list from the header itself
+        text = open(ref_header).read()
+        names = sorted(set(re.findall(r"\b(ggml_(?:cuda|init)_[a-z0-9_]+)\s*\(", text)))
+        assert len(names) >= 17
+    missing = [n for n in names if not hasattr(G, n)]
+    assert not missing, missing
+    assert G.glue_cpu_has_cublas() == 1      # the reference really was compiled with its offload seam live
+
+
+def test_cpu_path_of_the_seam_build_matches_the_oracle(port):
+    """offload = 0: the -DGGML_USE_CUBLAS build must still compute the reference CPU result (hook returns false)."""
+    G = _glue()
+    M, K, n = 96, 256, 3
+    W = port.quantize_q4_0(port.synthetic(M * K, 11, 0.02).reshape(M, K))
+    X = port.synthetic(n * K, 12, 1.0, 100).reshape(n, K)
+    Y = _run(G, W, 0, M, K, X, offload=0)
+    Yo = port.mul_mat(W, X, avx2_order=True)
+    assert np.max(np.abs(Y - Yo)) <= 1e-4 * np.max(np.abs(Yo))
+
+
+def test_tensors_off_the_path_stay_on_the_cpu(port):
+    """A loader may tag any tensor GGML_BACKEND_GPU (llama.cpp tags the norm weights of offloaded layers).  Types
+    this back-end does not take are kept on the host and re-tagged CPU, so the graph still computes the CPU result."""
+    G = _glue()
+    M, K, n = 64, 128, 2
+    Wf = port.synthetic(M * K, 21, 0.05).reshape(M, K).astype(np.float32)
+    X = port.synthetic(n * K, 22, 1.0).reshape(n, K)
+    Y0 = _run(G, Wf, 1, M, K, X, offload=0)
+    Y1 = _run(G, Wf, 1, M, K, X, offload=1)
+    assert np.array_equal(Y0, Y1)
+    assert np.allclose(Y0, X.astype(np.float64) @ Wf.astype(np.float64).T, rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,K,n,offload", [(512, 1024, 1, 1), (4096, 4096, 1, 1), (300, 1088, 7, 1), (1000, 4544, 130, 2),
+                                           (4096, 4096, 512, 1)])
+def test_reference_graph_runs_the_op_on_the_gpu(b200, port, ref, M, K, n, offload):
+    """The reference graph API end to end: weight uploaded by ggml_cuda_transform_tensor, op taken by
+    ggml_cuda_compute_forward inside ggml_graph_compute, result in dst->data; vs the same build's CPU path."""
+    G = _glue()
+    wf = port.synthetic(M * K, 31 + M + K, 0.02).reshape(M, K)
+    W = ref.quantize_q4_0_bulk(wf) if ref is not None else port.quantize_q4_0(wf)
+    X = port.synthetic(n * K, 32 + n, 1.0, 100).reshape(n, K)
+    before = b200.launch_count()
+    Yg = _run(G, W, 0, M, K, X, offload=offload)
+    launched = b200.launch_count() - before
+    assert G.glue_ready() == 1
+    assert launched >= 2, "the op did not reach the CUDA kernels"      # repack at upload + at least one op kernel
+    Yc = _run(G, W, 0, M, K, X, offload=0, threads=8)
+    d = np.abs(Yg.astype(np.float64) - Yc)
+    colmax = np.max(np.abs(Yc), axis=1, keepdims=True)
+    assert float(np.max(d / colmax)) <= 1e-4
