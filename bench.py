@@ -341,6 +341,8 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
     import torch
     import torch.distributed as dist
 
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line (the version banner goes to stdout)
     mod = load_binding()
     torch.cuda.set_device(local_rank)
     mod.init(local_rank)
@@ -632,11 +634,16 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
 
+    if world > 1:
+        # the captured graph holds NCCL kernels of the library's communicator: tearing the communicator down under
+        # it can block forever (seen on 2 GPUs), so multi-rank runs leave by the short way once every rank is done
+        sys.stdout.flush()
+        dist.barrier()
+        torch.cuda.synchronize()
+        os._exit(0)
+    del graph
     for (h, _, _) in handles:
         L_.ggml_b200_free_weight(h)
-    if world > 1:
-        mod.comm_shutdown()
-        dist.destroy_process_group()
     mod.shutdown()
 
 
