@@ -47,11 +47,11 @@ constexpr int GEMM_NS_RAW = 4;          // nibble-tile ring
 constexpr int GEMM_NS_OP = 4;           // int8 operand ring (A unpacked + B)
 constexpr int GEMM_NS_X = 8;            // activation-scale ring
 constexpr int GEMM_NS_D = 4;            // TMEM accumulator ring (4 x 128 columns = 512)
-constexpr int GEMM_THREADS = 640;
+constexpr int GEMM_THREADS = 384;
 // Warp roles, lowest id first.  The SM's warp schedulers favour the HIGHEST warp id among eligible warps, so the
 // producers sit on top: the single MMA-issuing thread and the TMA thread must never queue behind 16 warps of FMAs
 // (measured: with the issuer as warp 1 every block cost it ~400 clk of issue-slot starvation).
-constexpr int GEMM_EPI_WARP0 = 4, GEMM_EPI_WARPS = 16, GEMM_UNPACK_WARP0 = 2, GEMM_UNPACK_WARPS = 2;
+constexpr int GEMM_EPI_WARP0 = 4, GEMM_EPI_WARPS = 8, GEMM_UNPACK_WARP0 = 2, GEMM_UNPACK_WARPS = 2;
 constexpr int GEMM_TMA_WARP = 0, GEMM_MMA_WARP = 1;
 constexpr int GEMM_UNPACK_ROWS = GEMM_BM / (GEMM_UNPACK_WARPS * 8);   // rows per unpack thread (8)
 // 640 threads x 96 registers (65536 / 640 = 102 -> 96): the epilogue (32 accumulators + 32 S_b + operands)
@@ -85,6 +85,47 @@ static_assert(GemmBars::tmem_slot + 8 <= 512, "barrier block too small");
 __device__ __forceinline__ void unpack_q4_word(uint32_t w, uint32_t & lo, uint32_t & hi) {
     lo = ((w & 0x0F0F0F0Fu) + 0x78787878u) ^ 0x80808080u;
     hi = (((w >> 4) & 0x0F0F0F0Fu) + 0x78787878u) ^ 0x80808080u;
+}
+
+constexpr int GEMM_EPI_COLS = 64;       // tile columns per epilogue thread
+
+// parity checkpoint plumbing of the epilogue (DUMP instantiations only)
+struct GemmDump {
+    int * S; int rows, n, nbk, m, c_first; bool row_ok;
+};
+
+// one chunk of the epilogue = 32 rows x 16 columns of the warp's slice, held in the accumulator-fragment layout
+// (ptx.cuh tmem_ld_16x256b_x2): lo[] = TMEM lanes 0..15 of the quadrant, hi[] = lanes 16..31.  Thread i owns rows
+// (i/4) + 8j, j = 0..3, and columns 8k + 2(i%4) + {0,1}, k = 0,1: per chunk 4 row scales (registers) and two
+// 8-byte column-scale loads whose addresses differ per lane -> 1 shared-memory wavefront each.  (With the
+// one-row-per-thread layout every dx was a 32-way broadcast: 512 LSU wavefronts per block, the measured limiter.)
+//   acc[((CH * 2 + k) * 4 + j)] = (row j, column pair k of chunk CH)
+template <int CH, bool DUMP, bool BIAS>
+__device__ __forceinline__ void gemm_epi_chunk(uint32_t (&lo)[8], uint32_t (&hi)[8], uint64_t (&acc)[GEMM_EPI_COLS / 2],
+                                               uint32_t xa, const uint64_t (&dw2)[4], const uint64_t (&nc2)[4],
+                                               const GemmDump & dp, int blk, int lane) {
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+        const uint64_t dx2 = lds_b64(xa + (CH * 16 + 8 * k) * 4);    // xa already carries + 2(i%4) columns
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            uint32_t f0 = (j < 2) ? lo[4 * k + 2 * (j & 1)] : hi[4 * k + 2 * (j & 1)];
+            uint32_t f1 = (j < 2) ? lo[4 * k + 2 * (j & 1) + 1] : hi[4 * k + 2 * (j & 1) + 1];
+            if (DUMP) {
+                const int c = dp.c_first + CH * 16 + 8 * k + 2 * (lane & 3);
+                const int mm = dp.m + 8 * j;
+                const int off = BIAS ? 32768 : 0;
+                if (mm < dp.rows) {
+                    int * dst = dp.S + ((size_t)c * dp.rows + mm) * dp.nbk + blk;
+                    if (c < dp.n)     dst[0] = (int)f0 - off;
+                    if (c + 1 < dp.n) dst[(size_t)dp.rows * dp.nbk] = (int)f1 - off;
+                }
+            }
+            if (!BIAS) { f0 += 0x4B400000u; f1 += 0x4B400000u; }
+            const uint64_t t = fma_f32x2(pack_u32x2(f0, f1), dw2[j], nc2[j]);   // == rn(S_b * dw) (x 2^-49 when BIAS)
+            fma_acc_f32x2(acc[(CH * 2 + k) * 4 + j], t, dx2);
+        }
+    }
 }
 
 // TRACE: CTA (0,0) stamps clock64 at its pipeline hand-offs into trc (tools/trace_gemm.py); compiled out otherwise
@@ -245,102 +286,120 @@ gemm_q4_0_tc_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble plan
       }
     } else {
         // ===== epilogue: S_b (TMEM) * dw * dx -> fp32 accumulators =====
-        const int ew = warp - GEMM_EPI_WARP0;          // 0..15 (GEMM_EPI_WARP0 is a multiple of 4)
+        // 8 warps = 4 TMEM lane quadrants x 2 column halves; a thread owns one weight row x 64 columns (64 fp32
+        // accumulators).  Few fat warps instead of many thin ones: with <= 168 registers the tcgen05.ld of the
+        // NEXT 16-column chunk is in flight while the packed FMAs of the current chunk issue, so TMEM latency
+        // hides behind the warp's own math (the warps of one scheduler run in lockstep on the same barriers and
+        // cannot hide it for each other).
+        const int ew = warp - GEMM_EPI_WARP0;          // 0..7 (GEMM_EPI_WARP0 is a multiple of 4)
         const int quad = ew & 3;                        // TMEM lane quadrant (== warp % 4)
-        const int cg = ew >> 2;                         // 32-column group
-        const int m = m0 + quad * 32 + lane;            // this thread's weight row
-        const bool row_ok = m < rows;
-        const bool cols_live = c0 + cg * 32 < n;        // warp-uniform: any real column in this group?
-        const uint32_t t_lane = tmem_base + ((uint32_t)(quad * 32) << 16) + cg * 32;
+        const int col0 = (ew >> 2) * GEMM_EPI_COLS;     // first tile column of this warp
+        const int r0 = quad * 32 + (lane >> 2);         // this thread's tile rows: r0 + 8j, j = 0..3
+        const int m = m0 + r0;
+        const bool cols_live = c0 + col0 < n;           // warp-uniform: any real column in this half?
+        const uint32_t t_lane = tmem_base + ((uint32_t)(quad * 32) << 16) + col0;
         // BIAS: accumulator bits = denormal (S_b + 32768) * 2^-149;  2^-134 = 32768 * 2^-149
         const float NEG_OFFSET = BIAS ? -__int_as_float(32768) : -12582912.0f;
-        uint64_t acc[16];
+        uint64_t acc[GEMM_EPI_COLS / 2];
 #pragma unroll
-        for (int i = 0; i < 16; i++) acc[i] = 0ull;
+        for (int i = 0; i < GEMM_EPI_COLS / 2; i++) acc[i] = 0ull;
+        const GemmDump dump = {S_out, rows, n, nbk, m, c0 + col0, true};
 
-        // block j of a stage always lands in accumulator buffer j (GEMM_KB == GEMM_NS_D), so every
-        // barrier / TMEM / shared address below is a per-stage base plus a compile-time offset
+        // block j of a k-stage always lands in TMEM buffer j (GEMM_KB == GEMM_NS_D)
         static_assert(GEMM_KB == GEMM_NS_D, "block j of a k-stage uses TMEM buffer j");
         int sx = 0;
         uint32_t xph = 0;
-        for (int s = 0; s < nstages; s++) {
-            const uint32_t dph = s & 1;
-            const uint32_t slot = sbase + GEMM_SMEM_X + sx * GEMM_X_BYTES;
-            const uint32_t xs = slot + cg * 32 * 4;
-            const uint32_t dws = slot + GEMM_XD_BYTES + (quad * 32 + lane) * 4;
-            mbar_wait(bars + GemmBars::x_full + 8 * sx, xph);
-            const int nb = min(GEMM_KB, nbk - s * GEMM_KB);
+        if (cols_live) {
+            uint32_t al[8], ah[8], bl[8], bh[8];       // two chunk buffers (lanes 0..15 / 16..31 of the quadrant)
+            mbar_wait(bars + GemmBars::x_full, 0);
+            mbar_wait(bars + GemmBars::d_full, 0);
+            tc_fence_after_sync();
+            tmem_ld_16x256b_x2(t_lane, al);
+            tmem_ld_16x256b_x2(t_lane + (16u << 16), ah);
 #pragma unroll 1
-            for (int jj = 0; jj < GEMM_KB; jj++) {
-                if (jj < nb) {
-                    if (ew == 0 && lane == 0) GEMM_TR(2, 8 * (s * GEMM_KB + jj));
-                    mbar_wait(bars + GemmBars::d_full + 8 * jj, dph);
-                    if (ew == 0 && lane == 0) GEMM_TR(2, 8 * (s * GEMM_KB + jj) + 1);
-                    tc_fence_after_sync();
-                    if (cols_live) {
-                        const float dw = lds_f32(dws + jj * GEMM_DW_STRIDE * 4);
-                        const float nc = NEG_OFFSET * dw;                 // exact: dw has 11 significant bits
-                        const uint64_t dw2 = pack_f32x2(dw, dw), nc2 = pack_f32x2(nc, nc);
-                        // two halves of 16 columns: 16 live S_b registers instead of 32 keeps the thread under
-                        // 96 registers without address rematerialisation or accumulator copies
+            for (int blk = 0; blk < nbk; blk++) {
+                const int jj = blk & (GEMM_KB - 1);
+                const uint32_t slot = sbase + GEMM_SMEM_X + sx * GEMM_X_BYTES;
+                const uint32_t xa = slot + (jj * GEMM_BN + col0 + 2 * (lane & 3)) * 4;
+                const uint32_t tb = t_lane + jj * GEMM_BN;
+                const uint32_t da = slot + GEMM_XD_BYTES + (jj * GEMM_DW_STRIDE + r0) * 4;
+                uint64_t dw2[4], nc2[4];
 #pragma unroll
-                        for (int h = 0; h < 2; h++) {
-                            uint32_t sreg[16];
-                            tmem_ld_32x16(t_lane + jj * GEMM_BN + h * 16, sreg);
-                            tmem_ld_wait();
-                            if (ew == 0 && lane == 0) GEMM_TR(2, 8 * (s * GEMM_KB + jj) + 2 + 2 * h);
-                            if (h == 1) {
-                                // this warp's slice of the buffer is in registers: hand it back to the MMA issuer
-                                tc_fence_before_sync();
-                                __syncwarp();
-                                if (lane == 0) mbar_arrive(bars + GemmBars::d_empty + 8 * jj);
-                            }
-#pragma unroll
-                            for (int i = 0; i < 16; i += 4) {
-                                const float4 dx4 = lds_f32x4(xs + (jj * GEMM_BN + h * 16 + i) * 4);   // warp-uniform broadcast
-                                uint32_t f0 = sreg[i], f1 = sreg[i + 1], f2 = sreg[i + 2], f3 = sreg[i + 3];
-                                if (DUMP) {
-                                    const int c = c0 + cg * 32 + h * 16 + i;
-                                    const int off = BIAS ? 32768 : 0;
-                                    if (row_ok) {
-                                        int * dst = S_out + ((size_t)c * rows + m) * nbk + (s * GEMM_KB + jj);
-                                        const size_t cs = (size_t)rows * nbk;
-                                        if (c < n)     dst[0] = (int)f0 - off;
-                                        if (c + 1 < n) dst[cs] = (int)f1 - off;
-                                        if (c + 2 < n) dst[2 * cs] = (int)f2 - off;
-                                        if (c + 3 < n) dst[3 * cs] = (int)f3 - off;
-                                    }
-                                }
-                                if (!BIAS) { f0 += 0x4B400000u; f1 += 0x4B400000u; f2 += 0x4B400000u; f3 += 0x4B400000u; }
-                                const uint64_t t01 = fma_f32x2(pack_u32x2(f0, f1), dw2, nc2);   // == rn(S_b * dw) (x 2^-49 when BIAS)
-                                const uint64_t t23 = fma_f32x2(pack_u32x2(f2, f3), dw2, nc2);
-                                fma_acc_f32x2(acc[(h * 16 + i) / 2], t01, pack_f32x2(dx4.x, dx4.y));
-                                fma_acc_f32x2(acc[(h * 16 + i) / 2 + 1], t23, pack_f32x2(dx4.z, dx4.w));
-                            }
-                            if (ew == 0 && lane == 0) GEMM_TR(2, 8 * (s * GEMM_KB + jj) + 3 + 2 * h);
-                        }
-                    } else {
-                        // no real column in this group: only keep the buffer ring moving
-                        tc_fence_before_sync();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(bars + GemmBars::d_empty + 8 * jj);
-                    }
+                for (int j = 0; j < 4; j++) {
+                    const float dw = lds_f32(da + 8 * j * 4);
+                    const float nc = NEG_OFFSET * dw;                 // exact: dw has 11 significant bits
+                    dw2[j] = pack_f32x2(dw, dw);
+                    nc2[j] = pack_f32x2(nc, nc);
                 }
+                tmem_ld_wait();                                       // a = columns 0..15
+                tmem_ld_16x256b_x2(tb + 16, bl);
+                tmem_ld_16x256b_x2(tb + 16 + (16u << 16), bh);
+                gemm_epi_chunk<0, DUMP, BIAS>(al, ah, acc, xa, dw2, nc2, dump, blk, lane);
+                tmem_ld_wait();                                       // b = columns 16..31
+                tmem_ld_16x256b_x2(tb + 32, al);
+                tmem_ld_16x256b_x2(tb + 32 + (16u << 16), ah);
+                gemm_epi_chunk<1, DUMP, BIAS>(bl, bh, acc, xa, dw2, nc2, dump, blk, lane);
+                tmem_ld_wait();                                       // a = columns 32..47
+                tmem_ld_16x256b_x2(tb + 48, bl);
+                tmem_ld_16x256b_x2(tb + 48 + (16u << 16), bh);
+                gemm_epi_chunk<2, DUMP, BIAS>(al, ah, acc, xa, dw2, nc2, dump, blk, lane);
+                tmem_ld_wait();                                       // b = columns 48..63
+                // this warp's slice of the buffer is in registers: hand it back to the MMA issuer
+                tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bars + GemmBars::d_empty + 8 * jj);
+                const bool stage_done = jj == GEMM_KB - 1 || blk + 1 == nbk;
+                int sx1 = sx;
+                uint32_t xph1 = xph;
+                if (blk + 1 < nbk) {
+                    if (jj == GEMM_KB - 1) {
+                        if (++sx1 == GEMM_NS_X) { sx1 = 0; xph1 ^= 1; }
+                        mbar_wait(bars + GemmBars::x_full + 8 * sx1, xph1);   // next stage's scales have landed
+                    }
+                    const int j1 = (blk + 1) & (GEMM_KB - 1);
+                    mbar_wait(bars + GemmBars::d_full + 8 * j1, ((blk + 1) / GEMM_KB) & 1);
+                    tc_fence_after_sync();
+                    tmem_ld_16x256b_x2(t_lane + j1 * GEMM_BN, al);
+                    tmem_ld_16x256b_x2(t_lane + j1 * GEMM_BN + (16u << 16), ah);
+                }
+                gemm_epi_chunk<3, DUMP, BIAS>(bl, bh, acc, xa, dw2, nc2, dump, blk, lane);
+                if (stage_done) {
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bars + GemmBars::x_empty + 8 * sx);
+                }
+                sx = sx1;
+                xph = xph1;
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bars + GemmBars::x_empty + 8 * sx);
-            if (++sx == GEMM_NS_X) { sx = 0; xph ^= 1; }
+        } else {
+            // no real column in this half: only keep the rings moving (wait before every arrive so an arrival can
+            // never land in an earlier phase of the barrier)
+            for (int st = 0; st < nstages; st++) {
+                mbar_wait(bars + GemmBars::x_full + 8 * sx, xph);
+                const int nb = min(GEMM_KB, nbk - st * GEMM_KB);
+                for (int jj = 0; jj < nb; jj++) {
+                    mbar_wait(bars + GemmBars::d_full + 8 * jj, st & 1);
+                    if (lane == 0) mbar_arrive(bars + GemmBars::d_empty + 8 * jj);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bars + GemmBars::x_empty + 8 * sx);
+                if (++sx == GEMM_NS_X) { sx = 0; xph ^= 1; }
+            }
         }
-        // store: for a fixed column the 32 lanes of a warp hold 32 consecutive rows -> 128-byte stores
-        if (row_ok && cols_live) {
+        // store: a thread holds rows m + 8j and column pairs; for one (j, pair) the 8 threads with equal i%4 cover
+        // 8 consecutive rows = one 32-byte sector per column
+        if (cols_live) {
             const float rescale = BIAS ? 562949953421312.0f : 1.0f;   // 2^49
 #pragma unroll
-            for (int i = 0; i < 16; i++) {
+            for (int q = 0; q < GEMM_EPI_COLS / 2; q++) {
+                const int j = q & 3, k = (q >> 2) & 1, ch = q >> 3;
                 float a0, a1;
-                unpack_f32x2(acc[i], a0, a1);
-                const int c = c0 + cg * 32 + 2 * i;
-                if (c < n)     y[(size_t)c * ldy + m] = a0 * rescale;
-                if (c + 1 < n) y[(size_t)(c + 1) * ldy + m] = a1 * rescale;
+                unpack_f32x2(acc[q], a0, a1);
+                const int c = c0 + col0 + ch * 16 + 8 * k + 2 * (lane & 3);
+                const int mm = m + 8 * j;
+                if (mm < rows) {
+                    if (c < n)     y[(size_t)c * ldy + mm] = a0 * rescale;
+                    if (c + 1 < n) y[(size_t)(c + 1) * ldy + mm] = a1 * rescale;
+                }
             }
         }
     }

@@ -135,6 +135,22 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&r)[16])
           "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
         : "r"(taddr) : "memory");
 }
+// 16 TMEM lanes x 2 groups of 8 columns in the accumulator-fragment layout (16x256b.x2): thread i gets, for column
+// group k = 0,1: r[4k+0], r[4k+1] = lane (i/4),     columns 8k + 2(i%4), +1
+//                r[4k+2], r[4k+3] = lane (i/4) + 8, the same two columns.
+// A warp's 32 threads thus hold a 2-D patch each (2 rows x 4 columns) instead of one row x 16 columns, so the
+// per-row and per-column operands of an epilogue are few and DISTINCT per lane (no 32-way broadcast loads).
+__device__ __forceinline__ void tmem_ld_16x256b_x2(uint32_t taddr, uint32_t (&r)[8]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.16x256b.x2.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ uint64_t lds_b64(uint32_t addr) {
+    uint64_t v;
+    asm volatile("ld.shared.b64 %0, [%1];" : "=l"(v) : "r"(addr));
+    return v;
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---- register re-split between warp roles (all warps of a 128-thread warpgroup execute it) --------
