@@ -440,6 +440,8 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
+    barrier()      # rank 0 spent time in the CPU check; peers must not sit in a gather kernel waiting for it
+
     # ---- capture one step in a CUDA graph (launch-bound otherwise: 450 short kernels per step)
     with torch.cuda.stream(stream):
         for _ in range(2):
@@ -621,7 +623,7 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
                        "weights": "random-init Q4_0 blocks (one layer generated on the host, a separate HBM copy per layer)",
                        "layout": "planes (one-time repack at upload)", "cuda_graph": graph is not None,
                        "fused_quantize": not args.unfused, "pdl": not args.no_pdl, "tune": args.tune,
-                       "parallelism": ("row-sharded x%d + NCCL all-gather per matmul" % world) if world > 1 else "single GPU",
+                       "parallelism": ("row-sharded x%d + peer-to-peer gather kernel per matmul (NVLink stores + flags; NCCL only for n > 1)" % world) if world > 1 else "single GPU",
                        "setup_s": round(setup_s, 2), "sanity_max_rel_err": parity},
             "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps), "gpu_launches_per_step": int(launches_per_step),
             "clocks": clocks,

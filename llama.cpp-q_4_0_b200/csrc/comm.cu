@@ -9,6 +9,7 @@
 // and shares the copy torch already loaded when driven from a torch.distributed launcher.
 #include <dlfcn.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "state.h"
@@ -19,6 +20,82 @@ typedef struct ncclComm * ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 typedef int ncclResult_t;
 enum { ncclFloat32 = 7 };
+
+// ---- n = 1 gather without a collective library call ------------------------------------------------
+// An NCCL all-gather of a few KB costs ~12 us per matmul, several times the GEMV it follows.  Here every rank
+// owns an "arena" in its HBM, exported with cudaIpcGetMemHandle and mapped by every peer at comm_init:
+//     [2 halves][P2P_MAX_M] 8-byte words   (bits of y[m], op number), double-buffered by the op number's parity
+//     [P2P_MAX_WORLD] op counters          one per peer, touched only by the owning rank
+// The GEMV writes this rank's rows straight into the caller's dst.  One small kernel follows it, one CTA per
+// peer: CTA p stores this rank's rows into p's arena, every word carrying the op number next to the value
+// (8-byte words are single-copy atomic, so a word whose number matches IS the datum: no fence, no separate
+// flag, no round trip -- one NVLink one-way latency per op), then polls this rank's arena for p's rows and
+// writes them to dst.  A peer can run at most one op ahead (its next op needs this rank's next slab), so two
+// halves are enough.  Op numbers live on the device: a captured CUDA graph replays correctly.  Ranks are
+// separate GPUs driven by separate processes, so the poll cannot starve the peer it waits for.
+constexpr int P2P_MAX_WORLD = 8;
+constexpr int P2P_MAX_M = 65536;
+constexpr size_t P2P_CTR_OFF = (size_t)2 * P2P_MAX_M * 8;
+constexpr size_t P2P_ARENA_BYTES = P2P_CTR_OFF + 256;
+
+struct P2PPeers { unsigned char * arena[P2P_MAX_WORLD]; };
+
+__device__ __forceinline__ void st_sys_b64x2(unsigned long long * p, unsigned long long a, unsigned long long b) {
+    asm volatile("st.relaxed.sys.global.v2.b64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
+}
+__device__ __forceinline__ void st_sys_b64(unsigned long long * p, unsigned long long a) {
+    asm volatile("st.relaxed.sys.global.b64 [%0], %1;" ::"l"(p), "l"(a) : "memory");
+}
+__device__ __forceinline__ void ld_sys_b64x2(const unsigned long long * p, unsigned long long & a, unsigned long long & b) {
+    asm volatile("ld.relaxed.sys.global.v2.b64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_sys_b64(const unsigned long long * p) {
+    unsigned long long a;
+    asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(a) : "l"(p) : "memory");
+    return a;
+}
+__device__ __forceinline__ unsigned long long p2p_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+constexpr unsigned long long P2P_TIMEOUT_NS = 60000000000ull;   // a peer that never arrives: trap, do not hang
+
+// grid = world - 1 CTAs; per = rows of a full shard (ggml_b200_shard_rows), y = the whole dst column
+__global__ void __launch_bounds__(1024)
+p2p_gather_kernel(const __grid_constant__ P2PPeers peers, int me, int world, float * __restrict__ y, int M, int per) {
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");     // this rank's rows come from the GEMV just before
+    const int p = (int)blockIdx.x < me ? (int)blockIdx.x : (int)blockIdx.x + 1;
+    __shared__ unsigned s_seq;
+    if (threadIdx.x == 0) s_seq = ++reinterpret_cast<unsigned *>(peers.arena[me] + P2P_CTR_OFF)[p];
+    __syncthreads();
+    const unsigned long long tag = (unsigned long long)s_seq << 32;
+    const size_t half = (size_t)(s_seq & 1u) * P2P_MAX_M;
+    const int lo_me = min(me * per, M), n_me = min(lo_me + per, M) - lo_me;
+    const int lo_p = min(p * per, M), n_p = min(lo_p + per, M) - lo_p;
+    // 1. my rows -> p's arena (lo_* are multiples of 128, so word pairs are 16-byte aligned)
+    unsigned long long * out = reinterpret_cast<unsigned long long *>(peers.arena[p]) + half + lo_me;
+    const float * mine = y + lo_me;
+    for (int i = threadIdx.x * 2; i + 1 < n_me; i += blockDim.x * 2)
+        st_sys_b64x2(out + i, tag | __float_as_uint(mine[i]), tag | __float_as_uint(mine[i + 1]));
+    if ((n_me & 1) && threadIdx.x == 0) st_sys_b64(out + n_me - 1, tag | __float_as_uint(mine[n_me - 1]));
+    // 2. p's rows <- my arena, as they land
+    const unsigned long long * in = reinterpret_cast<const unsigned long long *>(peers.arena[me]) + half + lo_p;
+    float * theirs = y + lo_p;
+    const unsigned long long t0 = p2p_now();
+    for (int i = threadIdx.x * 2; i + 1 < n_p; i += blockDim.x * 2) {
+        unsigned long long a, b;
+        for (;;) {
+            ld_sys_b64x2(in + i, a, b);
+            if ((a >> 32) == s_seq && (b >> 32) == s_seq) break;
+            if (p2p_now() - t0 > P2P_TIMEOUT_NS) __trap();
+        }
+        theirs[i] = __uint_as_float((unsigned)a);
+        theirs[i + 1] = __uint_as_float((unsigned)b);
+    }
+    if ((n_p & 1) && threadIdx.x == 0) {
+        unsigned long long a;
+        while (((a = ld_sys_b64(in + n_p - 1)) >> 32) != s_seq) if (p2p_now() - t0 > P2P_TIMEOUT_NS) __trap();
+        theirs[n_p - 1] = __uint_as_float((unsigned)a);
+    }
+}
 
 struct Nccl {
     void * lib = nullptr;
@@ -31,8 +108,13 @@ struct Nccl {
     int rank = 0, world = 1;
     float * gather_buf = nullptr; size_t gather_cap = 0;   // [world][n][rows_max]
     float * slab_buf = nullptr;   size_t slab_cap = 0;     // [n][rows_max] (this rank)
+    // n = 1 fast path: peer-to-peer gather over NVLink (see p2p_gather_kernel)
+    unsigned char * arena = nullptr;                       // this rank's IPC-exported arena
+    P2PPeers peers;                                        // every rank's arena as mapped in this process
+    bool p2p_ok = false;
 };
 static Nccl nc;
+static int g_p2p_enabled = 1;   // tuning key "p2p_gather"
 
 static int nccl_load() {
     if (nc.lib) return GGML_B200_OK;
@@ -68,6 +150,71 @@ __global__ void scatter_slabs_kernel(const float * __restrict__ gbuf, float * __
         const long long j = m - r * per;
         y[c * ldy + m] = gbuf[(r * n + c) * rows_max + j];
     }
+}
+
+void comm_set_p2p(int on) { g_p2p_enabled = on != 0; }
+
+// Export this rank's arena, learn everybody's handle through the communicator, map the peers.
+// Any failure leaves p2p_ok false and the NCCL gather in charge.
+static int p2p_setup() {
+    nc.p2p_ok = false;
+    if (nc.world > P2P_MAX_WORLD) return GGML_B200_OK;
+    const char * env = getenv("GGML_B200_P2P");
+    if (env && atoi(env) == 0) return GGML_B200_OK;
+    CK(cudaMalloc(&nc.arena, P2P_ARENA_BYTES));
+    CK(cudaMemset(nc.arena, 0, P2P_ARENA_BYTES));
+    cudaIpcMemHandle_t mine;
+    cudaIpcMemHandle_t all[P2P_MAX_WORLD];
+    int ok = cudaIpcGetMemHandle(&mine, nc.arena) == cudaSuccess;
+    if (!ok) { cudaGetLastError(); memset(&mine, 0, sizeof(mine)); }
+    // handles (+ an "I could export" byte) travel through one all-gather
+    constexpr size_t REC = sizeof(cudaIpcMemHandle_t) + 16;
+    unsigned char * dev = nullptr;
+    CK(cudaMalloc(&dev, REC * (nc.world + 1)));
+    unsigned char rec[REC] = {0};
+    memcpy(rec, &mine, sizeof(mine));
+    rec[sizeof(mine)] = (unsigned char)ok;
+    CK(cudaMemcpyAsync(dev + REC * nc.world, rec, REC, cudaMemcpyHostToDevice, g.stream));
+    NK(nc.AllGather(dev + REC * nc.world, dev, REC / 4, ncclFloat32, nc.comm, g.stream));
+    unsigned char host[REC * P2P_MAX_WORLD];
+    CK(cudaMemcpyAsync(host, dev, REC * nc.world, cudaMemcpyDeviceToHost, g.stream));
+    CK(cudaStreamSynchronize(g.stream));
+    CK(cudaFree(dev));
+    int all_ok = 1;
+    for (int r = 0; r < nc.world; r++) { memcpy(&all[r], host + REC * r, sizeof(all[r])); all_ok &= host[REC * r + sizeof(all[r])]; }
+    int mapped = all_ok;
+    for (int r = 0; r < P2P_MAX_WORLD; r++) nc.peers.arena[r] = nullptr;
+    nc.peers.arena[nc.rank] = nc.arena;
+    for (int r = 0; r < nc.world && mapped; r++) {
+        if (r == nc.rank) continue;
+        void * p = nullptr;
+        if (cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); mapped = 0; break; }
+        nc.peers.arena[r] = (unsigned char *)p;
+    }
+    // every rank must agree, or one would wait for flags nobody raises
+    int * flag_dev = nullptr;
+    CK(cudaMalloc(&flag_dev, 4 * (nc.world + 1)));
+    float f = mapped ? 1.0f : 0.0f;
+    CK(cudaMemcpyAsync(flag_dev + nc.world, &f, 4, cudaMemcpyHostToDevice, g.stream));
+    NK(nc.AllGather(flag_dev + nc.world, flag_dev, 1, ncclFloat32, nc.comm, g.stream));
+    float fl[P2P_MAX_WORLD];
+    CK(cudaMemcpyAsync(fl, flag_dev, 4 * nc.world, cudaMemcpyDeviceToHost, g.stream));
+    CK(cudaStreamSynchronize(g.stream));
+    CK(cudaFree(flag_dev));
+    bool agree = true;
+    for (int r = 0; r < nc.world; r++) agree = agree && fl[r] == 1.0f;
+    nc.p2p_ok = agree;
+    if (getenv("GGML_B200_VERBOSE")) fprintf(stderr, "ggml_b200: rank %d peer-to-peer gather %s\n", nc.rank, agree ? "on" : "off (NCCL gather)");
+    return GGML_B200_OK;
+}
+
+static void p2p_teardown() {
+    for (int r = 0; r < P2P_MAX_WORLD; r++) {
+        if (nc.peers.arena[r] && r != nc.rank) cudaIpcCloseMemHandle(nc.peers.arena[r]);
+        nc.peers.arena[r] = nullptr;
+    }
+    if (nc.arena) { cudaFree(nc.arena); nc.arena = nullptr; }
+    nc.p2p_ok = false;
 }
 
 }  // namespace b200
@@ -106,10 +253,12 @@ int ggml_b200_comm_init(int rank, int world, const void * unique_id128) {
     ncclUniqueId id;
     memcpy(&id, unique_id128, sizeof(id));
     NK(nc.CommInitRank(&nc.comm, world, id, rank));
-    return GGML_B200_OK;
+    return p2p_setup();
 }
 
 void ggml_b200_comm_shutdown(void) {
+    if (nc.comm) cudaDeviceSynchronize();   // peers may still be storing into this arena
+    p2p_teardown();
     if (nc.comm) { nc.CommDestroy(nc.comm); nc.comm = nullptr; }
     if (nc.gather_buf) { cudaFree(nc.gather_buf); nc.gather_buf = nullptr; nc.gather_cap = 0; }
     if (nc.slab_buf) { cudaFree(nc.slab_buf); nc.slab_buf = nullptr; nc.slab_cap = 0; }
@@ -133,6 +282,21 @@ int ggml_b200_mul_mat_q4_0_sharded(const ggml_b200_weight * w, const float * x_d
     const int64_t rows_max = h0 - l0;   // rank 0 always holds a full-width shard
     const size_t slab = (size_t)n * rows_max;
 
+    if (n == 1 && nc.p2p_ok && g_p2p_enabled && w->M <= P2P_MAX_M) {
+        // GEMV straight into dst[lo,hi), then one kernel that trades rows with every peer over NVLink
+        int rc = launch_slab(w, x_dev, 1, nb11, y_dev + lo, rows_max);
+        if (rc) return rc;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = nc.world - 1; cfg.blockDim = 1024; cfg.stream = g.stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr; cfg.numAttrs = g.tune.pdl ? 1 : 0;
+        CK(cudaLaunchKernelEx(&cfg, p2p_gather_kernel, nc.peers, nc.rank, nc.world, y_dev, (int)w->M, (int)rows_max));
+        g.launches++;
+        return GGML_B200_OK;
+    }
+
     if (slab * nc.world * 4 > nc.gather_cap) {
         if (nc.gather_buf) CK(cudaFree(nc.gather_buf));
         nc.gather_buf = nullptr; nc.gather_cap = 0;
@@ -144,12 +308,8 @@ int ggml_b200_mul_mat_q4_0_sharded(const ggml_b200_weight * w, const float * x_d
     float * gbuf = in_place ? y_dev : nc.gather_buf;
     float * mine = gbuf + (size_t)nc.rank * slab;
     // this rank's slab, dense [n][rows_max]: reuse the op with a fake dst whose column 0 is `mine`
-    int rc = launch_quantize(x_dev, n, w->K, nb11, nullptr);
+    int rc = launch_slab(w, x_dev, n, nb11, mine, rows_max);
     if (rc) return rc;
-    if (w->rows() > 0) {
-        rc = launch_shard(w, mine, rows_max, (int)n);
-        if (rc) return rc;
-    }
     NK(nc.AllGather(mine, gbuf, slab, ncclFloat32, nc.comm, g.stream));
     if (!in_place) {
         const long long total = (long long)n * w->M;

@@ -281,6 +281,17 @@ int launch_shard(const ggml_b200_weight * w, float * y, long long ldy, int n) {
     return launch_gemv(w, y, ldy, n);
 }
 
+// this shard's slab of dst, dense: y = first element of column 0, ldy floats between columns
+int launch_slab(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y, long long ldy) {
+    if (n == 0 || w->rows() == 0) return GGML_B200_OK;
+    if (fused_ok(w, n)) return launch_fused(w, x_dev, y, nullptr, nullptr);
+    if (!g.tune.skip_quantize) {
+        int rc = launch_quantize(x_dev, n, w->K, nb11, nullptr);
+        if (rc) return rc;
+    }
+    return launch_shard(w, y, ldy, (int)n);
+}
+
 // x_dev/y_dev device pointers; y_dev addresses the full dst, this shard writes [row_lo,row_hi)
 int mul_mat_dev(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y_dev, size_t nb1) {
     if (n == 0 || w->rows() == 0) return GGML_B200_OK;
@@ -384,6 +395,7 @@ int ggml_b200_set_tuning(const char * key, int value) {
     else if (!strcmp(key, "fused_threads")) { if (value < 32 || value > 1024 || (value & 31)) return GGML_B200_ERR_ARG; g.tune.fused_threads = value; }
     else if (!strcmp(key, "fused_ctas_per_sm")) { if (value < 1 || value > 16) return GGML_B200_ERR_ARG; g.tune.fused_ctas_per_sm = value; }
     else if (!strcmp(key, "skip_quantize")) { g.tune.skip_quantize = value != 0; }
+    else if (!strcmp(key, "p2p_gather"))   { comm_set_p2p(value); }
     else return gemm_set_tuning(key, value);
     return GGML_B200_OK;
 }

@@ -77,6 +77,8 @@ int launch_quantize(const float * x_dev, int64_t n, int64_t K, size_t nb11, void
 int launch_gemv(const ggml_b200_weight * w, float * y, long long ldy, int n);
 // kernel 2 or 3 by n, into y (first element of this shard's column 0), activations already quantized
 int launch_shard(const ggml_b200_weight * w, float * y, long long ldy, int n);
+int launch_slab(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y, long long ldy);
+void comm_set_p2p(int on);
 int mul_mat_dev(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y_dev, size_t nb1);
 
 // kernel 3 (gemm_q4_0_tc.cu)

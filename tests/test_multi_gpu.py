@@ -1,0 +1,32 @@
+"""Row-sharded op on real GPUs (skipped on a one-GPU box): ggml_b200_mul_mat_q4_0_sharded -- the peer-to-peer gather
+kernel (n = 1) and the NCCL all-gather (n > 1) -- must equal the single-GPU op bit for bit on every rank, under
+back-to-back queuing and CUDA-graph replay.  The work is done by tools/check_sharded.py under torchrun, one
+process per GPU, as the library is meant to be driven (reference mechanism: GGML_BACKEND_GPU_SPLIT,
+ggml-cuda.cu:2780-2797)."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _gpus():
+    try:
+        import torch
+        return torch.cuda.device_count() if torch.cuda.is_available() else 0
+    except Exception:   # noqa: BLE001
+        return 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_sharded_equals_single_gpu(world):
+    if _gpus() < world:
+        pytest.skip(f"needs {world} GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29600 + world), os.path.join(ROOT, "tools", "check_sharded.py")]
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "CHECK_SHARDED OK" in r.stdout
