@@ -59,7 +59,7 @@ constexpr unsigned long long P2P_TIMEOUT_NS = 60000000000ull;   // a peer that n
 
 // grid = world - 1 CTAs; per = rows of a full shard (ggml_b200_shard_rows), y = the whole dst column
 __global__ void __launch_bounds__(1024)
-p2p_gather_kernel(const __grid_constant__ P2PPeers peers, int me, int world, float * __restrict__ y, int M, int per) {
+p2p_gather_kernel(const __grid_constant__ P2PPeers peers, int me, int world, float * __restrict__ y, int M, int per, int mode) {
     asm volatile("griddepcontrol.launch_dependents;");
     asm volatile("griddepcontrol.wait;" ::: "memory");     // this rank's rows come from the GEMV just before
     const int p = (int)blockIdx.x < me ? (int)blockIdx.x : (int)blockIdx.x + 1;
@@ -70,12 +70,15 @@ p2p_gather_kernel(const __grid_constant__ P2PPeers peers, int me, int world, flo
     const size_t half = (size_t)(s_seq & 1u) * P2P_MAX_M;
     const int lo_me = min(me * per, M), n_me = min(lo_me + per, M) - lo_me;
     const int lo_p = min(p * per, M), n_p = min(lo_p + per, M) - lo_p;
+    // mode (tuning key p2p_gather): 1 = the protocol; 3 = no poll, 4 = no store, no poll (timing experiments only)
+    if (mode == 4) return;
     // 1. my rows -> p's arena (lo_* are multiples of 128, so word pairs are 16-byte aligned)
     unsigned long long * out = reinterpret_cast<unsigned long long *>(peers.arena[p]) + half + lo_me;
     const float * mine = y + lo_me;
     for (int i = threadIdx.x * 2; i + 1 < n_me; i += blockDim.x * 2)
         st_sys_b64x2(out + i, tag | __float_as_uint(mine[i]), tag | __float_as_uint(mine[i + 1]));
     if ((n_me & 1) && threadIdx.x == 0) st_sys_b64(out + n_me - 1, tag | __float_as_uint(mine[n_me - 1]));
+    if (mode == 3) return;
     // 2. p's rows <- my arena, as they land
     const unsigned long long * in = reinterpret_cast<const unsigned long long *>(peers.arena[me]) + half + lo_p;
     float * theirs = y + lo_p;
@@ -152,7 +155,7 @@ __global__ void scatter_slabs_kernel(const float * __restrict__ gbuf, float * __
     }
 }
 
-void comm_set_p2p(int on) { g_p2p_enabled = on != 0; }
+void comm_set_p2p(int on) { g_p2p_enabled = on; }
 
 // Export this rank's arena, learn everybody's handle through the communicator, map the peers.
 // Any failure leaves p2p_ok false and the NCCL gather in charge.
@@ -286,13 +289,14 @@ int ggml_b200_mul_mat_q4_0_sharded(const ggml_b200_weight * w, const float * x_d
         // GEMV straight into dst[lo,hi), then one kernel that trades rows with every peer over NVLink
         int rc = launch_slab(w, x_dev, 1, nb11, y_dev + lo, rows_max);
         if (rc) return rc;
+        if (g_p2p_enabled == 2) return GGML_B200_OK;    // timing experiment: this rank's rows only
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = nc.world - 1; cfg.blockDim = 1024; cfg.stream = g.stream;
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         attr[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = attr; cfg.numAttrs = g.tune.pdl ? 1 : 0;
-        CK(cudaLaunchKernelEx(&cfg, p2p_gather_kernel, nc.peers, nc.rank, nc.world, y_dev, (int)w->M, (int)rows_max));
+        CK(cudaLaunchKernelEx(&cfg, p2p_gather_kernel, nc.peers, nc.rank, nc.world, y_dev, (int)w->M, (int)rows_max, g_p2p_enabled));
         g.launches++;
         return GGML_B200_OK;
     }
