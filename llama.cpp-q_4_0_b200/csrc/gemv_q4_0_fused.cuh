@@ -17,45 +17,11 @@
 
 namespace b200 {
 
-template <int UNROLL, int RIF, int MAXT, bool DUMP>
-__global__ void __launch_bounds__(MAXT, (2048 / MAXT) / 2)
-gemv_q4_0_fused_kernel(const uint4 * __restrict__ wq, const __half * __restrict__ wd,
-                       const float * __restrict__ x, float * __restrict__ y, int rows, int nbk,
-                       int x_aligned, int * __restrict__ S_out, unsigned char * __restrict__ blocks34, unsigned seq) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    GemvSmem<1> s(smem_raw, nbk);
-    const int lane = threadIdx.x & 31;
-    const int warp = threadIdx.x >> 5;
-    const int nwarps = blockDim.x >> 5;
-    CtaTrace tr;
-    if (threadIdx.x == 0) tr.begin(seq);
-    pdl_launch_dependents();
-
-    // 1. first chunk of this warp's first RIF rows (RIF rows in flight per warp)
-    const int rstride = gridDim.x * nwarps;
-    const int row_first = blockIdx.x + gridDim.x * warp;
-    uint4 q[RIF][UNROLL];
-    unsigned short dh[RIF][UNROLL];
-#pragma unroll
-    for (int r = 0; r < RIF; r++) {
-        const int row = row_first + r * rstride;
-        if (row < rows) {
-            const uint4 * wrow = wq + (size_t)row * nbk;
-            const unsigned short * drow = reinterpret_cast<const unsigned short *>(wd) + (size_t)row * nbk;
-#pragma unroll
-            for (int u = 0; u < UNROLL; u++) {
-                const int b = lane + 32 * u;
-                if (b < nbk) { q[r][u] = ldg_stream_u4(wrow + b); dh[r][u] = ldg_stream_u16(drow + b); }
-            }
-        }
-    }
-
-    // 2. activations (and y) may belong to the previous kernel
-    pdl_wait();
-    if (threadIdx.x == 0) tr.mark(1);
-
-    // 3. quantize_row_q8_0 into the smem planes; 4 threads per block, 8 floats per thread
-    {
+// kernel 1 inside a CTA: quantize_row_q8_0 (AVX2 contract, ggml.c:1192-1250) of the whole activation row into the
+// shared-memory planes the dot loops read; 4 threads per block, 8 floats per thread.  Caller syncs the CTA.
+template <bool DUMP>
+__device__ __forceinline__ void quantize_x_to_smem(GemvSmem<1> & s, const float * __restrict__ x, int nbk, int x_aligned,
+                                                   int warp, int lane, unsigned char * __restrict__ blocks34) {
         const int total = nbk * 4;
         uint32_t * lo32 = reinterpret_cast<uint32_t *>(s.lo);
         uint32_t * hi32 = reinterpret_cast<uint32_t *>(s.hi);
@@ -107,7 +73,47 @@ gemv_q4_0_fused_kernel(const uint4 * __restrict__ wq, const __half * __restrict_
                 }
             }
         }
+}
+
+template <int UNROLL, int RIF, int MAXT, bool DUMP>
+__global__ void __launch_bounds__(MAXT, (2048 / MAXT) / 2)
+gemv_q4_0_fused_kernel(const uint4 * __restrict__ wq, const __half * __restrict__ wd,
+                       const float * __restrict__ x, float * __restrict__ y, int rows, int nbk,
+                       int x_aligned, int * __restrict__ S_out, unsigned char * __restrict__ blocks34, unsigned seq) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    GemvSmem<1> s(smem_raw, nbk);
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int nwarps = blockDim.x >> 5;
+    CtaTrace tr;
+    if (threadIdx.x == 0) tr.begin(seq);
+    pdl_launch_dependents();
+
+    // 1. first chunk of this warp's first RIF rows (RIF rows in flight per warp)
+    const int rstride = gridDim.x * nwarps;
+    const int row_first = blockIdx.x + gridDim.x * warp;
+    uint4 q[RIF][UNROLL];
+    unsigned short dh[RIF][UNROLL];
+#pragma unroll
+    for (int r = 0; r < RIF; r++) {
+        const int row = row_first + r * rstride;
+        if (row < rows) {
+            const uint4 * wrow = wq + (size_t)row * nbk;
+            const unsigned short * drow = reinterpret_cast<const unsigned short *>(wd) + (size_t)row * nbk;
+#pragma unroll
+            for (int u = 0; u < UNROLL; u++) {
+                const int b = lane + 32 * u;
+                if (b < nbk) { q[r][u] = ldg_stream_u4(wrow + b); dh[r][u] = ldg_stream_u16(drow + b); }
+            }
+        }
     }
+
+    // 2. activations (and y) may belong to the previous kernel
+    pdl_wait();
+    if (threadIdx.x == 0) tr.mark(1);
+
+    // 3. quantize_row_q8_0 into the smem planes
+    quantize_x_to_smem<DUMP>(s, x, nbk, x_aligned, warp, lane, blocks34);
     __syncthreads();
     if (threadIdx.x == 0) tr.mark(2);
 

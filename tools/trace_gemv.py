@@ -66,8 +66,9 @@ def main():
         hs.append(h)
     x = torch.randn(1, K, device="cuda")
     y = torch.zeros(1, M, device="cuda")
-    cfgs = [("fused 512x1 rif2 pdl", dict(gemv_stream=0, fused_threads=512, fused_ctas_per_sm=1, fused_rif=2, pdl=1)),
-            ("fused 256x2 rif2 pdl", dict(gemv_stream=0, fused_threads=256, fused_ctas_per_sm=2, fused_rif=2, pdl=1)),
+    cfgs = [("stream x1 pdl", dict(gemv_stream=1, stream_ctas_per_sm=1, pdl=1)),
+            ("stream x2 pdl", dict(gemv_stream=1, stream_ctas_per_sm=2, pdl=1)),
+            ("fused 512x1 rif2 pdl", dict(gemv_stream=0, fused_threads=512, fused_ctas_per_sm=1, fused_rif=2, pdl=1)),
             ("fused 1024x1 pdl", dict(gemv_stream=0, fused_threads=1024, fused_ctas_per_sm=1, fused_rif=1, pdl=1))]
     for label, t in cfgs:
         for k, v in t.items():
