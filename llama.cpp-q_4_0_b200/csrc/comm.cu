@@ -12,6 +12,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include "p2p.cuh"
 #include "state.h"
 
 namespace b200 {
@@ -21,83 +22,26 @@ typedef struct { char internal[128]; } ncclUniqueId;
 typedef int ncclResult_t;
 enum { ncclFloat32 = 7 };
 
-// ---- n = 1 gather without a collective library call ------------------------------------------------
-// An NCCL all-gather of a few KB costs ~12 us per matmul, several times the GEMV it follows.  Here every rank
-// owns an "arena" in its HBM, exported with cudaIpcGetMemHandle and mapped by every peer at comm_init:
-//     [2 halves][P2P_MAX_M] 8-byte words   (bits of y[m], op number), double-buffered by the op number's parity
-//     [P2P_MAX_WORLD] op counters          one per peer, touched only by the owning rank
-// The GEMV writes this rank's rows straight into the caller's dst.  One small kernel follows it, one CTA per
-// peer: CTA p stores this rank's rows into p's arena, every word carrying the op number next to the value
-// (8-byte words are single-copy atomic, so a word whose number matches IS the datum: no fence, no separate
-// flag, no round trip -- one NVLink one-way latency per op), then polls this rank's arena for p's rows and
-// writes them to dst.  A peer can run at most one op ahead (its next op needs this rank's next slab), so two
-// halves are enough.  Op numbers live on the device: a captured CUDA graph replays correctly.  Ranks are
-// separate GPUs driven by separate processes, so the poll cannot starve the peer it waits for.
-constexpr int P2P_MAX_WORLD = 8;
-constexpr int P2P_MAX_M = 65536;
-constexpr size_t P2P_CTR_OFF = (size_t)2 * P2P_MAX_M * 8;
-constexpr size_t P2P_ARENA_BYTES = P2P_CTR_OFF + 256;
+// ---- n = 1 gather without a collective library call (protocol: p2p.cuh) -----------------------------------
+// Stand-alone form, used after a GEMV that could not take the fused kernel (gemv_q4_0_p2p.cuh): this rank's rows
+// are already in y; a few CTAs send them to every peer and collect the peers' rows.
+// mode (tuning key p2p_gather): 1 = the protocol; 3 = no poll, 4 = no store, no poll (timing experiments only)
+constexpr int P2P_GATHER_CTAS = 8;
 
-struct P2PPeers { unsigned char * arena[P2P_MAX_WORLD]; };
-
-__device__ __forceinline__ void st_sys_b64x2(unsigned long long * p, unsigned long long a, unsigned long long b) {
-    asm volatile("st.relaxed.sys.global.v2.b64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
-}
-__device__ __forceinline__ void st_sys_b64(unsigned long long * p, unsigned long long a) {
-    asm volatile("st.relaxed.sys.global.b64 [%0], %1;" ::"l"(p), "l"(a) : "memory");
-}
-__device__ __forceinline__ void ld_sys_b64x2(const unsigned long long * p, unsigned long long & a, unsigned long long & b) {
-    asm volatile("ld.relaxed.sys.global.v2.b64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
-}
-__device__ __forceinline__ unsigned long long ld_sys_b64(const unsigned long long * p) {
-    unsigned long long a;
-    asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(a) : "l"(p) : "memory");
-    return a;
-}
-__device__ __forceinline__ unsigned long long p2p_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
-constexpr unsigned long long P2P_TIMEOUT_NS = 60000000000ull;   // a peer that never arrives: trap, do not hang
-
-// grid = world - 1 CTAs; per = rows of a full shard (ggml_b200_shard_rows), y = the whole dst column
 __global__ void __launch_bounds__(1024)
-p2p_gather_kernel(const __grid_constant__ P2PPeers peers, int me, int world, float * __restrict__ y, int M, int per, int mode) {
+p2p_gather_kernel(const __grid_constant__ P2PExchange ex, float * __restrict__ y, int mode) {
     asm volatile("griddepcontrol.launch_dependents;");
     asm volatile("griddepcontrol.wait;" ::: "memory");     // this rank's rows come from the GEMV just before
-    const int p = (int)blockIdx.x < me ? (int)blockIdx.x : (int)blockIdx.x + 1;
     __shared__ unsigned s_seq;
-    if (threadIdx.x == 0) s_seq = ++reinterpret_cast<unsigned *>(peers.arena[me] + P2P_CTR_OFF)[p];
+    if (threadIdx.x == 0) s_seq = p2p_op_number(ex);
     __syncthreads();
-    const unsigned long long tag = (unsigned long long)s_seq << 32;
-    const size_t half = (size_t)(s_seq & 1u) * P2P_MAX_M;
-    const int lo_me = min(me * per, M), n_me = min(lo_me + per, M) - lo_me;
-    const int lo_p = min(p * per, M), n_p = min(lo_p + per, M) - lo_p;
-    // mode (tuning key p2p_gather): 1 = the protocol; 3 = no poll, 4 = no store, no poll (timing experiments only)
-    if (mode == 4) return;
-    // 1. my rows -> p's arena (lo_* are multiples of 128, so word pairs are 16-byte aligned)
-    unsigned long long * out = reinterpret_cast<unsigned long long *>(peers.arena[p]) + half + lo_me;
-    const float * mine = y + lo_me;
-    for (int i = threadIdx.x * 2; i + 1 < n_me; i += blockDim.x * 2)
-        st_sys_b64x2(out + i, tag | __float_as_uint(mine[i]), tag | __float_as_uint(mine[i + 1]));
-    if ((n_me & 1) && threadIdx.x == 0) st_sys_b64(out + n_me - 1, tag | __float_as_uint(mine[n_me - 1]));
-    if (mode == 3) return;
-    // 2. p's rows <- my arena, as they land
-    const unsigned long long * in = reinterpret_cast<const unsigned long long *>(peers.arena[me]) + half + lo_p;
-    float * theirs = y + lo_p;
-    const unsigned long long t0 = p2p_now();
-    for (int i = threadIdx.x * 2; i + 1 < n_p; i += blockDim.x * 2) {
-        unsigned long long a, b;
-        for (;;) {
-            ld_sys_b64x2(in + i, a, b);
-            if ((a >> 32) == s_seq && (b >> 32) == s_seq) break;
-            if (p2p_now() - t0 > P2P_TIMEOUT_NS) __trap();
-        }
-        theirs[i] = __uint_as_float((unsigned)a);
-        theirs[i + 1] = __uint_as_float((unsigned)b);
-    }
-    if ((n_p & 1) && threadIdx.x == 0) {
-        unsigned long long a;
-        while (((a = ld_sys_b64(in + n_p - 1)) >> 32) != s_seq) if (p2p_now() - t0 > P2P_TIMEOUT_NS) __trap();
-        theirs[n_p - 1] = __uint_as_float((unsigned)a);
-    }
+    const unsigned seq = s_seq;
+    int lo_me, n_me, j0, j1;
+    p2p_rows_of(ex, ex.me, lo_me, n_me);
+    p2p_cta_slice(n_me, j0, j1);
+    if (mode != 4) p2p_send(ex, seq, y + lo_me + j0, lo_me + j0, j1 - j0);
+    if (mode == 1) p2p_receive(ex, seq, y);
+    p2p_cta_done(ex, seq);
 }
 
 struct Nccl {
@@ -286,17 +230,21 @@ int ggml_b200_mul_mat_q4_0_sharded(const ggml_b200_weight * w, const float * x_d
     const size_t slab = (size_t)n * rows_max;
 
     if (n == 1 && nc.p2p_ok && g_p2p_enabled && w->M <= P2P_MAX_M) {
-        // GEMV straight into dst[lo,hi), then one kernel that trades rows with every peer over NVLink
+        P2PExchange ex;
+        ex.peers = nc.peers; ex.me = nc.rank; ex.world = nc.world; ex.per = (int)rows_max; ex.M = (int)w->M;
+        // one kernel: GEMV of this rank's rows + delivery to every peer + collection of theirs
+        if (g_p2p_enabled == 1 && fused_p2p_ok(w)) return launch_fused_p2p(w, x_dev, nb11, y_dev, ex);
+        // otherwise GEMV straight into dst[lo,hi), then the stand-alone exchange kernel
         int rc = launch_slab(w, x_dev, 1, nb11, y_dev + lo, rows_max);
         if (rc) return rc;
         if (g_p2p_enabled == 2) return GGML_B200_OK;    // timing experiment: this rank's rows only
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = nc.world - 1; cfg.blockDim = 1024; cfg.stream = g.stream;
+        cfg.gridDim = P2P_GATHER_CTAS; cfg.blockDim = 1024; cfg.stream = g.stream;
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         attr[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = attr; cfg.numAttrs = g.tune.pdl ? 1 : 0;
-        CK(cudaLaunchKernelEx(&cfg, p2p_gather_kernel, nc.peers, nc.rank, nc.world, y_dev, (int)w->M, (int)rows_max, g_p2p_enabled));
+        CK(cudaLaunchKernelEx(&cfg, p2p_gather_kernel, ex, y_dev, g_p2p_enabled == 5 ? 1 : g_p2p_enabled));
         g.launches++;
         return GGML_B200_OK;
     }

@@ -22,6 +22,7 @@
 #include "common.cuh"
 #include "gemv_q4_0.cuh"
 #include "gemv_q4_0_fused.cuh"
+#include "gemv_q4_0_p2p.cuh"
 #include "gemv_q4_0_stream.cuh"
 #include "quantize_q8_0.cuh"
 #include "repack.cuh"
@@ -279,6 +280,26 @@ static int check_op_args(const ggml_b200_weight * w, const void * x, int64_t n, 
 int launch_shard(const ggml_b200_weight * w, float * y, long long ldy, int n) {
     if (use_gemm(w, n)) return launch_gemm(w, y, ldy, n, nullptr);
     return launch_gemv(w, y, ldy, n);
+}
+
+// n == 1 row shard, gather fused in (multi-GPU; comm.cu decides when)
+bool fused_p2p_ok(const ggml_b200_weight * w) {
+    return g.tune.gemv_fused && !g.tune.skip_quantize && (w->layout == GGML_B200_LAYOUT_PLANES || w->rows() == 0) && g.path != GGML_B200_PATH_GEMM &&
+           gemv_p2p_smem_bytes((int)(w->K / QK), (int)w->rows(), g.sm_count) <= (size_t)MAX_DYN_SMEM - 1024;
+}
+
+int launch_fused_p2p(const ggml_b200_weight * w, const float * x_dev, size_t nb11, float * y_dev, const P2PExchange & ex) {
+    (void)nb11;   // n == 1: a single activation row
+    const int nbk = (int)(w->K / QK);
+    auto kern = gemv_q4_0_fused_p2p_kernel<4, 1024>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM - 1024));   // the kernel has static smem too
+        attr_set = true;
+    }
+    const int aligned = (((uintptr_t)x_dev) & 15) == 0;
+    return launch_k(kern, g.sm_count, 1024, gemv_p2p_smem_bytes(nbk, (int)w->rows(), g.sm_count), (const uint4 *)w->wq, (const __half *)w->wd, x_dev, y_dev,
+                    (int)w->rows(), nbk, aligned, (unsigned)g.launches, ex);
 }
 
 // this shard's slab of dst, dense: y = first element of column 0, ldy floats between columns

@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #include "../../include/ggml-b200.h"
+#include "p2p.cuh"
 
 // one device-resident Q4_0 row shard (opaque in the C ABI)
 struct ggml_b200_weight {
@@ -79,6 +80,9 @@ int launch_gemv(const ggml_b200_weight * w, float * y, long long ldy, int n);
 int launch_shard(const ggml_b200_weight * w, float * y, long long ldy, int n);
 int launch_slab(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y, long long ldy);
 void comm_set_p2p(int on);
+// n = 1 row shard with the multi-GPU exchange fused in (gemv_q4_0_p2p.cuh); y_dev = the whole dst column
+bool fused_p2p_ok(const ggml_b200_weight * w);
+int launch_fused_p2p(const ggml_b200_weight * w, const float * x_dev, size_t nb11, float * y_dev, const P2PExchange & ex);
 int mul_mat_dev(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y_dev, size_t nb1);
 
 // kernel 3 (gemm_q4_0_tc.cu)

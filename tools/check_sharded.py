@@ -4,7 +4,8 @@
         tools/check_sharded.py
 
 For each shape every rank uploads (a) the full weight and (b) its row shard.  The sharded op -- peer-to-peer
-gather kernel (n = 1) and NCCL all-gather (n > 1, or p2p_gather=0) -- must reproduce the single-GPU op of the
+exchange over NVLink (n = 1: fused into the GEMV, or as a stand-alone kernel with p2p_gather=5) and NCCL
+all-gather (n > 1, or p2p_gather=0) -- must reproduce the single-GPU op of the
 same library bit for bit on EVERY rank, also when 300 ops are queued back to back without a host sync (the
 flag/parity protocol of p2p_gather_kernel) and when the sequence is replayed from a CUDA graph.  Prints one
 "CHECK_SHARDED OK" line from rank 0, exits non-zero on any mismatch.  The kernels of the single-GPU op are
@@ -79,7 +80,8 @@ def main():
                 bad = int((y != y_ref).sum().item())
                 failures.append(f"rank {rank} {label} M={M} K={K} n={n}: {bad} of {n * M} differ")
 
-    run_case(1, 1, "p2p")
+    run_case(1, 1, "p2p-fused")
+    run_case(1, 5, "p2p-gather")
     run_case(1, 0, "nccl")
     run_case(7, 1, "nccl-n7")
     run_case(64, 1, "nccl-gemm")
@@ -100,8 +102,11 @@ def main():
     t0 = time.time()
     for i in range(reps):
         src = bufs[i] if i % 8 else x0
+        if i % 5 == 3:
+            mod.set_tuning("p2p_gather", 5)                  # mix in the stand-alone exchange kernel: one op numbering
         if L.ggml_b200_mul_mat_q4_0_sharded(ws.h, C.c_void_p(src.data_ptr()), 1, K * 4, C.c_void_p(bufs[i + 1].data_ptr()), M * 4):
             raise RuntimeError(err())
+        mod.set_tuning("p2p_gather", 1)
     mod.synchronize()
     dt = (time.time() - t0) / reps * 1e6
     bad_ops = sum(0 if torch.equal(bufs[i + 1], bufs_ref[i + 1]) else 1 for i in range(reps))
