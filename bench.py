@@ -412,9 +412,30 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
     L_ = mod.lib()
     op = L_.ggml_b200_mul_mat_q4_0_sharded if world > 1 else L_.ggml_b200_mul_mat_q4_0
 
+    # Buffers as the model graph has them (llama.cpp:1394-1504): wq, wk, wv read the same normed row; wo reads the
+    # attention output; w3, w1 read the same normed row; w2 reads the gated product; every matmul has its own dst.
+    src_group = ["attn_in", "attn_in", "attn_in", "attn_out", "ffn_in", "ffn_in", "ffn_mid"]
+    assert len(layer_shapes) == len(src_group)
+    xg = {}
+    yg = {}
+    ops = []
+    for idx, (h, M, K) in enumerate(handles):
+        pos = idx % len(layer_shapes) if idx < L * len(layer_shapes) else len(layer_shapes) + (idx - L * len(layer_shapes))
+        grp = src_group[pos] if pos < len(src_group) else "out_in"
+        if grp not in xg:
+            xg[grp] = xs[K].clone()
+        if pos not in yg:
+            yg[pos] = torch.zeros((1, M), dtype=torch.float32, device="cuda")
+        assert xg[grp].shape[1] == K and yg[pos].shape[1] == M
+        ops.append((h, M, K, xg[grp].data_ptr(), yg[pos].data_ptr()))
+    torch.cuda.synchronize()
+    if world == 1 and not args.no_overlap:
+        # this process owns the stream: nothing but library ops sits between two matmuls that share src1
+        mod.set_tuning("overlap_same_src", 1)
+
     def one_step():
-        for (h, M, K) in handles:
-            rc = op(h, C.c_void_p(xs[K].data_ptr()), 1, K * 4, C.c_void_p(ys[M].data_ptr()), M * 4)
+        for (h, M, K, xp, yp) in ops:
+            rc = op(h, C.c_void_p(xp), 1, K * 4, C.c_void_p(yp), M * 4)
             if rc:
                 raise RuntimeError(L_.ggml_b200_last_error().decode())
 
@@ -622,7 +643,8 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
                        "l2": "inputs larger than L2: the set's weights (%.2f GB per rank) are streamed once per step" % (weight_bytes / world / 1e9),
                        "weights": "random-init Q4_0 blocks (one layer generated on the host, a separate HBM copy per layer)",
                        "layout": "planes (one-time repack at upload)", "cuda_graph": graph is not None,
-                       "fused_quantize": not args.unfused, "pdl": not args.no_pdl, "tune": args.tune,
+                       "fused_quantize": not args.unfused, "pdl": not args.no_pdl,
+                       "same_src1_overlap": (world == 1 and not args.no_overlap), "tune": args.tune,
                        "parallelism": ("row-sharded x%d + peer-to-peer gather kernel per matmul (NVLink stores + flags; NCCL only for n > 1)" % world) if world > 1 else "single GPU",
                        "setup_s": round(setup_s, 2), "sanity_max_rel_err": parity},
             "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps), "gpu_launches_per_step": int(launches_per_step),
@@ -661,6 +683,7 @@ def main():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--unfused", action="store_true", help="kernel 1 + kernel 2 as separate launches")
     ap.add_argument("--no-pdl", action="store_true")
+    ap.add_argument("--no-overlap", action="store_true", help="every matmul waits for the previous one even when they only share src1")
     ap.add_argument("--tune", action="append", default=[], help="key=value for ggml_b200_set_tuning")
     ap.add_argument("--no-check", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

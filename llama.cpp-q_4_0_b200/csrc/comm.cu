@@ -30,8 +30,8 @@ constexpr int P2P_GATHER_CTAS = 8;
 
 __global__ void __launch_bounds__(1024)
 p2p_gather_kernel(const __grid_constant__ P2PExchange ex, float * __restrict__ y, int mode) {
-    asm volatile("griddepcontrol.launch_dependents;");
     asm volatile("griddepcontrol.wait;" ::: "memory");     // this rank's rows come from the GEMV just before
+    asm volatile("griddepcontrol.launch_dependents;");
     __shared__ unsigned s_seq;
     if (threadIdx.x == 0) s_seq = p2p_op_number(ex);
     __syncthreads();

@@ -170,8 +170,8 @@ gemm_q4_0_tc_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble plan
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
-    pdl_launch_dependents();
     pdl_wait();   // the quantized activations come from the previous kernel
+    pdl_launch_dependents();   // after the wait: see gemv_q4_0_fused.cuh (independent ops)
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(smem + GEMM_SMEM_BAR + GemmBars::tmem_slot);
 
     if (warp < GEMM_EPI_WARP0) {

@@ -67,8 +67,8 @@ gemv_q4_0_planes_kernel(const uint4 * __restrict__ wq, const __half * __restrict
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const int nwarps = blockDim.x >> 5;
-    pdl_launch_dependents();
     pdl_wait();   // the quantized activations come from the previous kernel
+    pdl_launch_dependents();   // after the wait: see gemv_q4_0_fused.cuh (independent ops)
 
     for (int col0 = 0; col0 < n; col0 += NC) {
         const int ncols = min(NC, n - col0);
@@ -137,8 +137,8 @@ gemv_q4_0_raw_kernel(const uint32_t * __restrict__ wraw,
     const int nwarps = blockDim.x >> 5;
     const int npairs = nbk >> 1;
     const size_t row_words = (size_t)nbk * Q4_0_BLOCK_BYTES / 4;
-    pdl_launch_dependents();
     pdl_wait();
+    pdl_launch_dependents();   // after the wait: see gemv_q4_0_fused.cuh (independent ops)
 
     for (int col0 = 0; col0 < n; col0 += NC) {
         const int ncols = min(NC, n - col0);

@@ -5,7 +5,7 @@
 // straight into the shared-memory planes the dot loop reads (the 4*K bytes of x come from L2), so
 // the op is ONE kernel: no q8 round trip through HBM and no second launch.  Order inside a CTA:
 //   1. every warp issues the 16-byte weight loads of its first row          (no dependency)
-//   2. griddepcontrol.wait                                                   (x may be produced
+//   2. griddepcontrol.wait, then griddepcontrol.launch_dependents            (x may be produced
 //      by the previous kernel; weights never are)
 //   3. quantize x -> smem planes (quantize_row_q8_0 contract, ggml.c:1192-1250), __syncthreads
 //   4. dot loop over the CTA's rows (row = cta + grid * slot), warp-shuffle reduce, store y
@@ -79,7 +79,8 @@ template <int UNROLL, int RIF, int MAXT, bool DUMP>
 __global__ void __launch_bounds__(MAXT, (2048 / MAXT) / 2)
 gemv_q4_0_fused_kernel(const uint4 * __restrict__ wq, const __half * __restrict__ wd,
                        const float * __restrict__ x, float * __restrict__ y, int rows, int nbk,
-                       int x_aligned, int * __restrict__ S_out, unsigned char * __restrict__ blocks34, unsigned seq) {
+                       int x_aligned, int * __restrict__ S_out, unsigned char * __restrict__ blocks34, unsigned seq,
+                       int independent) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     GemvSmem<1> s(smem_raw, nbk);
     const int lane = threadIdx.x & 31;
@@ -87,7 +88,12 @@ gemv_q4_0_fused_kernel(const uint4 * __restrict__ wq, const __half * __restrict_
     const int nwarps = blockDim.x >> 5;
     CtaTrace tr;
     if (threadIdx.x == 0) tr.begin(seq);
-    pdl_launch_dependents();
+    // `independent`: the host established that this op reads the same x as the library's previous op on this
+    // stream and writes rows nobody in flight touches (wq/wk/wv, w1/w3).  It then need not wait for that kernel:
+    // everything older is complete, because every kernel of this library releases its dependents only AFTER its
+    // own dependency wait.  It waits at its END instead, so that its completion still implies the completion of
+    // everything before it (a later kernel's griddepcontrol.wait only covers its immediate predecessor).
+    if (independent) pdl_launch_dependents();
 
     // 1. first chunk of this warp's first RIF rows (RIF rows in flight per warp)
     const int rstride = gridDim.x * nwarps;
@@ -109,7 +115,7 @@ gemv_q4_0_fused_kernel(const uint4 * __restrict__ wq, const __half * __restrict_
     }
 
     // 2. activations (and y) may belong to the previous kernel
-    pdl_wait();
+    if (!independent) { pdl_wait(); pdl_launch_dependents(); }
     if (threadIdx.x == 0) tr.mark(1);
 
     // 3. quantize_row_q8_0 into the smem planes
@@ -167,6 +173,7 @@ gemv_q4_0_fused_kernel(const uint4 * __restrict__ wq, const __half * __restrict_
         }
     }
     if (threadIdx.x == 0) tr.mark(3);
+    if (independent) pdl_wait();
 }
 
 }  // namespace b200

@@ -40,7 +40,6 @@ gemv_q4_0_fused_p2p_kernel(const uint4 * __restrict__ wq, const __half * __restr
     const int nwarps = blockDim.x >> 5;
     CtaTrace tr;
     if (threadIdx.x == 0) tr.begin(seq_trace);
-    pdl_launch_dependents();
 
     // this CTA's contiguous slice of the shard
     int j0, j1;
@@ -63,6 +62,7 @@ gemv_q4_0_fused_p2p_kernel(const uint4 * __restrict__ wq, const __half * __restr
 
     // 2. x, dst and the op counter may belong to the previous kernel
     pdl_wait();
+    pdl_launch_dependents();   // after the wait: see gemv_q4_0_fused.cuh (independent ops)
     unsigned seq_ld = 0;
     if (threadIdx.x == 0) { tr.mark(1); seq_ld = p2p_op_number(ex); }   // in flight under the quantizer
 

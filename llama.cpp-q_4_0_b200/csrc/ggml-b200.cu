@@ -182,6 +182,34 @@ static int launch_gemv_any(const ggml_b200_weight * w, float * y, long long ldy,
     }
 }
 
+// ---- independent consecutive ops (tuning key overlap_same_src) -------------------------------------------
+// A decode graph multiplies the same activation row by several weights in a row (wq/wk/wv, w1/w3).  Stream order
+// makes each wait for the one before although they share nothing but the read-only x.  With the key set the CALLER
+// promises that nothing but this library's ops is enqueued on the stream between two ops with the same src1
+// pointer; the library then lets such an op start without waiting for its predecessor (gemv_q4_0_fused.cuh) when
+// its dst overlaps neither x nor the dst of any op of the current run.
+static bool ranges_overlap(const float * a_lo, const float * a_hi, const float * b_lo, const float * b_hi) { return a_lo < b_hi && b_lo < a_hi; }
+
+static int independent_of_run(const ggml_b200_weight * w, const float * x, const float * y) {
+    auto & r = g.run;
+    if (!g.tune.overlap_same_src || !g.tune.pdl || r.count == 0 || r.count >= 8) return 0;
+    if (r.x != x || r.K != w->K || r.stream != g.stream || r.launches_after != g.launches) return 0;
+    const float * y_hi = y + w->rows();
+    if (ranges_overlap(y, y_hi, x, x + w->K)) return 0;
+    for (int i = 0; i < r.count; i++) if (ranges_overlap(y, y_hi, r.y_lo[i], r.y_hi[i])) return 0;
+    return 1;
+}
+
+static void run_append(const ggml_b200_weight * w, const float * x, const float * y, int independent) {
+    auto & r = g.run;
+    if (!independent) { r.count = 0; r.x = x; r.K = w->K; r.stream = g.stream; r.head = w; }
+    else { w->run_member = true; if (r.head) r.head->run_member = true; }   // next pass: both take the half-SM kernel
+    // an op whose dst overlaps x ends the run: the next reader of x must wait for it
+    if (ranges_overlap(y, y + w->rows(), x, x + w->K)) { r.count = 0; r.x = nullptr; return; }
+    r.y_lo[r.count] = y; r.y_hi[r.count] = y + w->rows(); r.count++;
+    r.launches_after = g.launches;
+}
+
 // n == 1, plane layout: kernel 1 fused into kernel 2 (one launch per op)
 template <int UNROLL, int RIF, int MAXT, bool DUMP>
 static int launch_fused_t(const ggml_b200_weight * w, const float * x, float * y, int * S, unsigned char * b34) {
@@ -195,7 +223,11 @@ static int launch_fused_t(const ggml_b200_weight * w, const float * x, float * y
     int threads = g.tune.fused_threads > MAXT ? MAXT : g.tune.fused_threads;
     const int grid = g.sm_count * g.tune.fused_ctas_per_sm;
     const int aligned = (((uintptr_t)x) & 15) == 0;
-    return launch_k(kern, grid, threads, gemv_smem_bytes(nbk, 1), (const uint4 *)w->wq, (const __half *)w->wd, x, y, (int)w->rows(), nbk, aligned, S, b34, (unsigned)g.launches);
+    const int independent = (S || b34) ? 0 : independent_of_run(w, x, y);
+    int rc = launch_k(kern, grid, threads, gemv_smem_bytes(nbk, 1), (const uint4 *)w->wq, (const __half *)w->wd, x, y, (int)w->rows(), nbk, aligned, S, b34, (unsigned)g.launches,
+                      independent);
+    if (rc == GGML_B200_OK && !(S || b34)) run_append(w, x, y, independent);
+    return rc;
 }
 
 // n == 1, plane layout: the streaming kernel (bulk-async ring + mbarriers, quantizer fused in)
@@ -243,8 +275,11 @@ int launch_fused(const ggml_b200_weight * w, const float * x, float * y, int * S
     if (stream_ok(w, 1)) return (S || b34) ? launch_stream_d<true>(w, x, y, S, b34) : launch_stream_d<false>(w, x, y, S, b34);
     // 1024 x 1 CTA/SM is best up to ~8k rows; beyond, 512 x 2 CTAs/SM (finer row interleave) wins
     // (profiles/r01_sweep_gemv_v2.log); an explicit fused_threads knob overrides
-    const bool big = g.tune.fused_threads > 512;
-    const int rif = g.tune.fused_rif;
+    // members of a same-src1 run take 512 threads (half an SM) with two rows in flight per warp, so that the run's
+    // kernels, which do not wait for each other, are resident together and overlap end to end
+    const bool member = g.tune.overlap_same_src && g.tune.pdl && w->run_member && !(S || b34);
+    const bool big = !member && g.tune.fused_threads > 512;
+    const int rif = member ? 2 : g.tune.fused_rif;
     if (S || b34) return big ? launch_fused_t<4, 1, 1024, true>(w, x, y, S, b34) : rif >= 2 ? launch_fused_t<4, 2, 512, true>(w, x, y, S, b34) : launch_fused_t<4, 1, 512, true>(w, x, y, S, b34);
     if (big) return g.tune.gemv_unroll >= 4 ? launch_fused_t<4, 1, 1024, false>(w, x, y, S, b34) : launch_fused_t<2, 1, 1024, false>(w, x, y, S, b34);
     if (rif >= 4) return launch_fused_t<2, 4, 512, false>(w, x, y, S, b34);
@@ -416,6 +451,7 @@ int ggml_b200_set_tuning(const char * key, int value) {
     else if (!strcmp(key, "fused_threads")) { if (value < 32 || value > 1024 || (value & 31)) return GGML_B200_ERR_ARG; g.tune.fused_threads = value; }
     else if (!strcmp(key, "fused_ctas_per_sm")) { if (value < 1 || value > 16) return GGML_B200_ERR_ARG; g.tune.fused_ctas_per_sm = value; }
     else if (!strcmp(key, "skip_quantize")) { g.tune.skip_quantize = value != 0; }
+    else if (!strcmp(key, "overlap_same_src")) { g.tune.overlap_same_src = value != 0; g.run.count = 0; }
     else if (!strcmp(key, "p2p_gather"))   { comm_set_p2p(value); }
     else return gemm_set_tuning(key, value);
     return GGML_B200_OK;
@@ -487,6 +523,7 @@ ggml_b200_weight * ggml_b200_upload_q4_0(const void * blocks, int64_t M, int64_t
 
 void ggml_b200_free_weight(ggml_b200_weight * w) {
     if (!w) return;
+    if (g.run.head == w) { g.run.head = nullptr; g.run.count = 0; }
     gemm_release_weight(w);
     if (w->raw) cudaFree(w->raw);
     if (w->wq) cudaFree(w->wq);

@@ -30,8 +30,8 @@ quantize_q8_0_kernel(const float * __restrict__ x, long long n, int K, size_t nb
                      int8_t * __restrict__ xq, int2 * __restrict__ xds,
                      unsigned char * __restrict__ blocks34,
                      float * __restrict__ xdT, long long n_pad) {
-    pdl_launch_dependents();
     pdl_wait();   // x may be produced, and xq/xds still be read, by the previous kernel
+    pdl_launch_dependents();   // after the wait: see gemv_q4_0_fused.cuh (independent ops)
     const int per_row = K >> 3;
     const long long total = n * (long long)per_row;
     long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;

@@ -17,6 +17,7 @@ struct ggml_b200_weight {
     __half * wd = nullptr;           // LAYOUT_PLANES: scales  [rows][nbk]
     size_t  dev_bytes = 0;
     void *  gemm = nullptr;          // tensor-core path's per-weight state (TMA descriptors)
+    mutable bool run_member = false; // seen in a run of n = 1 ops sharing src1 (overlap_same_src): gets the half-SM kernel
     int64_t rows() const { return row_hi - row_lo; }
 };
 
@@ -37,6 +38,7 @@ struct Tune {
     int fused_threads = 1024;    // threads per CTA of the fused kernel
     int fused_ctas_per_sm = 1;
     int pdl = 1;                 // programmatic dependent launch between consecutive kernels
+    int overlap_same_src = 0;    // n == 1: an op that reads the same x as the previous one does not wait for it (caller owns the stream)
     int skip_quantize = 0;       // bench only: reuse the activations quantized by the previous call
 };
 
@@ -59,6 +61,9 @@ struct Ctx {
     float * ystage = nullptr; size_t ystage_cap = 0;
     void *  sstage = nullptr; size_t sstage_cap = 0;
     uint64_t launches = 0;
+    // the run of n = 1 fused launches that read the same x (overlap_same_src): the ops still possibly in flight
+    struct { const float * x = nullptr; int64_t K = 0; cudaStream_t stream = nullptr; uint64_t launches_after = 0;
+             int count = 0; const float * y_lo[8]; const float * y_hi[8]; const ggml_b200_weight * head = nullptr; } run;
     char err[512] = {0};
 };
 

@@ -319,6 +319,47 @@ def test_back_to_back_ops_with_and_without_pdl(b200, port, ref, pdl):
     w1.free(); w2.free()
 
 
+def test_same_src1_ops_overlap_without_changing_results(b200, port, ref):
+    """overlap_same_src: ops that read the same x (wq/wk/wv, w1/w3) start without waiting for each other; an op
+    that consumes one of their results, reuses a dst, or writes x must still see stream order.  A decode-like chain
+    (3 independent ops -> op on the first result -> 2 independent ops -> op that overwrites x) is run 40 times back
+    to back with and without the key; every buffer must be bit-identical, and correct against the oracle."""
+    K = M = 1024
+    Ws = [make_weights(port, ref, M, K, 30 + i) for i in range(7)]
+    ws = [b200.Weight(W) for W in Ws]
+    x0 = make_x(port, 1, K, 77)
+
+    def run(overlap):
+        b200.set_tuning("overlap_same_src", overlap)
+        xd = b200.DevBuf.from_numpy(x0)
+        yd = [b200.DevBuf(M * 4) for _ in range(7)]
+        for rep in range(40):
+            for i in (0, 1, 2):
+                b200.mul_mat_dev(ws[i], xd.ptr, 1, yd[i].ptr)         # same src1, distinct dst: may overlap
+            b200.mul_mat_dev(ws[3], yd[0].ptr, 1, yd[3].ptr)          # reads a result of the run: must wait
+            for i in (4, 5):
+                b200.mul_mat_dev(ws[i], yd[3].ptr, 1, yd[i].ptr)      # a new run on another x
+            b200.mul_mat_dev(ws[5], yd[3].ptr, 1, yd[5].ptr)          # same dst again: must not overlap its twin
+            b200.mul_mat_dev(ws[6], yd[4].ptr, 1, yd[6].ptr)
+        b200.synchronize()
+        out = [y.to_numpy(np.float32, (1, M)) for y in yd]
+        return out
+
+    try:
+        serial = run(0)
+        overlapped = run(1)
+    finally:
+        b200.set_tuning("overlap_same_src", 0)
+    for i in range(7):
+        assert np.array_equal(serial[i], overlapped[i]), f"buffer {i} differs with overlap_same_src"
+    for i in (0, 1, 2):
+        assert_close(serial[i], oracle_Y(port, ref, Ws[i], x0))
+    assert_close(serial[3], oracle_Y(port, ref, Ws[3], serial[0]))
+    assert_close(serial[6], oracle_Y(port, ref, Ws[6], serial[4]))
+    for w in ws:
+        w.free()
+
+
 # ---------------------------------------------------------------------------- kernel 3: tcgen05 GEMM
 @pytest.mark.parametrize("M,K,n", [(128, 128, 128), (128, 256, 128), (256, 1024, 64), (300, 1088, 200), (70, 64, 5),
                                    (129, 4544, 130), (512, 4096, 512)])

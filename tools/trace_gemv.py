@@ -13,9 +13,11 @@ import bench  # noqa: E402
 
 
 def run(mod, L_, stream, hs, x, y, M, K, label, nk=12):
+    ys = [torch.zeros_like(y) for _ in range(nk)]        # distinct dst per op: same-src1 ops may overlap
+
     def step():
-        for h in hs[:nk]:
-            L_.ggml_b200_mul_mat_q4_0(h, C.c_void_p(x.data_ptr()), 1, K * 4, C.c_void_p(y.data_ptr()), M * 4)
+        for i, h in enumerate(hs[:nk]):
+            L_.ggml_b200_mul_mat_q4_0(h, C.c_void_p(x.data_ptr()), 1, K * 4, C.c_void_p(ys[i].data_ptr()), M * 4)
     with torch.cuda.stream(stream):
         step()
     stream.synchronize()
@@ -51,7 +53,7 @@ def run(mod, L_, stream, hs, x, y, M, K, label, nk=12):
 
 def main():
     M, K = 4096, 4096
-    if len(sys.argv) > 2:
+    if len(sys.argv) > 2 and sys.argv[1].isdigit():
         M, K = int(sys.argv[1]), int(sys.argv[2])
     mod = bench.load_binding()
     mod.init(0)
@@ -69,7 +71,11 @@ def main():
     cfgs = [("stream x1 pdl", dict(gemv_stream=1, stream_ctas_per_sm=1, pdl=1)),
             ("stream x2 pdl", dict(gemv_stream=1, stream_ctas_per_sm=2, pdl=1)),
             ("fused 512x1 rif2 pdl", dict(gemv_stream=0, fused_threads=512, fused_ctas_per_sm=1, fused_rif=2, pdl=1)),
-            ("fused 1024x1 pdl", dict(gemv_stream=0, fused_threads=1024, fused_ctas_per_sm=1, fused_rif=1, pdl=1))]
+            ("fused 1024x1 pdl", dict(gemv_stream=0, fused_threads=1024, fused_ctas_per_sm=1, fused_rif=1, pdl=1)),
+            ("fused 1024x1 pdl overlap_same_src", dict(gemv_stream=0, fused_threads=1024, fused_ctas_per_sm=1, fused_rif=1, pdl=1, overlap_same_src=1))]
+    cfgs.append(("fused 512x1 rif2 pdl overlap_same_src", dict(gemv_stream=0, fused_threads=512, fused_ctas_per_sm=1, fused_rif=2, pdl=1, overlap_same_src=1)))
+    if "--overlap-only" in sys.argv:
+        cfgs = cfgs[-1:]
     for label, t in cfgs:
         for k, v in t.items():
             mod.set_tuning(k, v)
