@@ -17,12 +17,14 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <chrono>
 #include <mutex>
 
 #include "common.cuh"
 #include "gemv_q4_0.cuh"
 #include "gemv_q4_0_fused.cuh"
 #include "gemv_q4_0_p2p.cuh"
+#include "gemv_q4_0_hostio.cuh"
 #include "gemv_q4_0_stream.cuh"
 #include "quantize_q8_0.cuh"
 #include "repack.cuh"
@@ -410,6 +412,10 @@ int ggml_b200_init(int device) {
     return GGML_B200_OK;
 }
 
+// GGML_B200_VERBOSE: where the host path's time goes (ns totals), printed at shutdown
+static struct { uint64_t ops, copy_in, launch, spin, copy_out; } g_hio_stats = {};
+static void hostio_release();
+
 void ggml_b200_shutdown(void) {
     std::lock_guard<std::mutex> lk(g_mu);
     if (!g.inited) return;
@@ -421,6 +427,15 @@ void ggml_b200_shutdown(void) {
     if (g.xstage) cudaFree(g.xstage);
     if (g.ystage) cudaFree(g.ystage);
     if (g.sstage) cudaFree(g.sstage);
+    if (getenv("GGML_B200_VERBOSE") && g_hio_stats.ops) {
+        const double n = (double)g_hio_stats.ops * 1e3;
+        unsigned long long prof[4] = {0, 0, 0, 0};
+        if (g.hio.counters) cudaMemcpy(prof, (const char *)g.hio.counters + 16, sizeof(prof), cudaMemcpyDeviceToHost);
+        fprintf(stderr, "ggml_b200: host path kernel: start -> x published %.2f us, -> all rows stored to the host %.2f us\n", prof[1] / n, prof[2] / n);
+        fprintf(stderr, "ggml_b200: host path, %llu ops: copy-in %.2f us, launch %.2f us, wait %.2f us, copy-out %.2f us per op\n",
+                (unsigned long long)g_hio_stats.ops, g_hio_stats.copy_in / n, g_hio_stats.launch / n, g_hio_stats.spin / n, g_hio_stats.copy_out / n);
+    }
+    hostio_release();
     gemm_shutdown();
     if (g.own_stream) cudaStreamDestroy(g.own_stream);
     const Tune t = g.tune;
@@ -451,6 +466,7 @@ int ggml_b200_set_tuning(const char * key, int value) {
     else if (!strcmp(key, "fused_threads")) { if (value < 32 || value > 1024 || (value & 31)) return GGML_B200_ERR_ARG; g.tune.fused_threads = value; }
     else if (!strcmp(key, "fused_ctas_per_sm")) { if (value < 1 || value > 16) return GGML_B200_ERR_ARG; g.tune.fused_ctas_per_sm = value; }
     else if (!strcmp(key, "skip_quantize")) { g.tune.skip_quantize = value != 0; }
+    else if (!strcmp(key, "host_fast"))    { g.tune.host_fast = value != 0; }
     else if (!strcmp(key, "overlap_same_src")) { g.tune.overlap_same_src = value != 0; g.run.count = 0; }
     else if (!strcmp(key, "p2p_gather"))   { comm_set_p2p(value); }
     else return gemm_set_tuning(key, value);
@@ -577,11 +593,93 @@ int ggml_b200_mul_mat_q4_0(const ggml_b200_weight * w, const float * x_dev, int6
     return mul_mat_dev(w, x_dev, n, nb11, y_dev, nb1);
 }
 
+// ---- n = 1 host entry point: one launch, no driver copies, no stream sync (gemv_q4_0_hostio.cuh) -----------
+static int hostio_grow_mapped(float ** p, size_t * cap, size_t need) {
+    if (need <= *cap) return GGML_B200_OK;
+    if (*p) { CK(cudaStreamSynchronize(g.stream)); CK(cudaFreeHost(*p)); *p = nullptr; *cap = 0; }
+    need = (need + 65535) & ~(size_t)65535;
+    CK(cudaHostAlloc((void **)p, need, cudaHostAllocMapped | cudaHostAllocPortable));
+    *cap = need;
+    return GGML_B200_OK;
+}
+
+static void hostio_release() {
+    auto & h = g.hio;
+    if (h.hx) cudaFreeHost(h.hx);
+    if (h.hy) cudaFreeHost(h.hy);
+    if (h.hdone) cudaFreeHost(h.hdone);
+    if (h.xdev) cudaFree(h.xdev);
+    if (h.ydev) cudaFree(h.ydev);
+    if (h.counters) cudaFree(h.counters);
+    h.hx = h.hy = h.xdev = h.ydev = nullptr; h.hdone = h.counters = nullptr;
+    h.hx_cap = h.hy_cap = h.xdev_cap = h.ydev_cap = 0; h.seq = 0;
+}
+
+static inline uint64_t now_ns() { return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+static bool hostio_ok(const ggml_b200_weight * w, int64_t n) { return g.tune.host_fast && fused_ok(w, n) && !stream_ok(w, n); }
+
+static int mul_mat_hostio(const ggml_b200_weight * w, const float * x_host, float * y_host) {
+    auto & h = g.hio;
+    const int64_t rows = w->rows();
+    const int nbk = (int)(w->K / QK);
+    int rc;
+    if ((rc = hostio_grow_mapped(&h.hx, &h.hx_cap, (size_t)w->K * 4))) return rc;
+    if ((rc = hostio_grow_mapped(&h.hy, &h.hy_cap, (size_t)rows * 4))) return rc;
+    if ((rc = ensure_stage((void **)&h.xdev, &h.xdev_cap, (size_t)w->K * 4))) return rc;
+    if (!h.counters) {
+        CK(cudaMalloc((void **)&h.counters, 64));
+        CK(cudaMemsetAsync(h.counters, 0, 64, g.stream));
+        CK(cudaHostAlloc((void **)&h.hdone, 64, cudaHostAllocMapped | cudaHostAllocPortable));
+        *h.hdone = 0;
+        h.seq = 0;
+    }
+    const uint64_t ts0 = now_ns();
+    memcpy(h.hx, x_host, (size_t)w->K * 4);
+    const uint64_t ts1 = now_ns();
+    HostIO io;
+    CK(cudaHostGetDevicePointer((void **)&io.x_host, h.hx, 0));
+    CK(cudaHostGetDevicePointer((void **)&io.y_host, h.hy, 0));
+    CK(cudaHostGetDevicePointer((void **)&io.done_host, h.hdone, 0));
+    io.x_dev = h.xdev; io.counters = h.counters; io.seq = ++h.seq;
+    static const int verbose = getenv("GGML_B200_VERBOSE") != nullptr;
+    io.profile = verbose;
+    auto kern = gemv_q4_0_hostio_kernel<4, 1024>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM - 1024));
+        attr_set = true;
+    }
+    rc = launch_k(kern, g.sm_count, 1024, gemv_smem_bytes(nbk, 1) + (size_t)((rows + g.sm_count - 1) / g.sm_count) * 4 + 16, (const uint4 *)w->wq, (const __half *)w->wd, (int)rows, nbk, io);
+    if (rc) { h.seq--; return rc; }
+    // spin on the completion word; look at the stream now and then so that a faulted kernel is reported, not awaited
+    volatile unsigned * done = h.hdone;
+    const uint64_t ts2 = now_ns();
+    const auto t0 = std::chrono::steady_clock::now();
+    unsigned spins = 0;
+    while (*done != io.seq) {
+        if ((++spins & 0xFFFF) == 0) {
+            const cudaError_t e = cudaStreamQuery(g.stream);
+            if (e != cudaSuccess && e != cudaErrorNotReady) return cuda_fail(e, "host-path kernel", __FILE__, __LINE__);
+            if (std::chrono::steady_clock::now() - t0 > std::chrono::seconds(20)) { set_error("host-path kernel did not complete in 20 s"); return GGML_B200_ERR_CUDA; }
+        }
+#if defined(__x86_64__)
+        __builtin_ia32_pause();
+#endif
+    }
+    const uint64_t ts3 = now_ns();
+    memcpy(y_host + w->row_lo, h.hy, (size_t)rows * 4);
+    const uint64_t ts4 = now_ns();
+    g_hio_stats.ops++; g_hio_stats.copy_in += ts1 - ts0; g_hio_stats.launch += ts2 - ts1; g_hio_stats.spin += ts3 - ts2; g_hio_stats.copy_out += ts4 - ts3;
+    return GGML_B200_OK;
+}
+
 int ggml_b200_mul_mat_q4_0_host(const ggml_b200_weight * w, const float * x_host, int64_t n, size_t nb11, float * y_host, size_t nb1) {
     int rc = check_op_args(w, x_host, n, nb11, y_host, nb1);
     if (rc) return rc;
     const int64_t rows = w->rows();
     if (n == 0 || rows == 0) return GGML_B200_OK;
+    if (n == 1 && hostio_ok(w, n)) return mul_mat_hostio(w, x_host, y_host);
     const size_t xrow = (size_t)w->K * 4;
     rc = ensure_stage((void **)&g.xstage, &g.xstage_cap, (size_t)n * xrow);
     if (rc) return rc;

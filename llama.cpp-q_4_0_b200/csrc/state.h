@@ -39,6 +39,7 @@ struct Tune {
     int fused_ctas_per_sm = 1;
     int pdl = 1;                 // programmatic dependent launch between consecutive kernels
     int overlap_same_src = 0;    // n == 1: an op that reads the same x as the previous one does not wait for it (caller owns the stream)
+    int host_fast = 1;           // n == 1 host entry: single-launch path with mapped staging rows and a completion word
     int skip_quantize = 0;       // bench only: reuse the activations quantized by the previous call
 };
 
@@ -60,6 +61,10 @@ struct Ctx {
     float * xstage = nullptr; size_t xstage_cap = 0;
     float * ystage = nullptr; size_t ystage_cap = 0;
     void *  sstage = nullptr; size_t sstage_cap = 0;
+    // n = 1 host entry point without driver copies or stream syncs (gemv_q4_0_hostio.cuh)
+    struct { float * hx = nullptr; size_t hx_cap = 0; float * hy = nullptr; size_t hy_cap = 0; unsigned * hdone = nullptr;
+             float * xdev = nullptr; size_t xdev_cap = 0; float * ydev = nullptr; size_t ydev_cap = 0; unsigned * counters = nullptr;
+             unsigned seq = 0; } hio;
     uint64_t launches = 0;
     // the run of n = 1 fused launches that read the same x (overlap_same_src): the ops still possibly in flight
     struct { const float * x = nullptr; int64_t K = 0; cudaStream_t stream = nullptr; uint64_t launches_after = 0;
