@@ -75,7 +75,7 @@ void         ggml_b200_host_free(void * ptr);
 
 /* ---- load-time upload ---------------------------------------------------------------------
  * replaces ggml_cuda_transform_tensor (ggml-cuda.cu:2766-2809; caller llama.cpp:678-685).
- * `blocks` = host pointer to the tensor data: M rows of K/32 block_q4_0 (ggml.c:870-875),
+ * `blocks` = host (or device) pointer to the tensor data: M rows of K/32 block_q4_0 (ggml.c:870-875),
  * row stride nb1 bytes (== 18*K/32 for every tensor ggml creates).  Rows [row_lo, row_hi) are
  * COPIED to the device (the caller may free `blocks` afterwards, llama.cpp:682-684) and, when
  * repack is on, re-laid once into the plane layout.  Returns NULL on error. */
@@ -92,6 +92,20 @@ size_t       ggml_b200_weight_device_bytes(const ggml_b200_weight * w);
 /* inverse of the repack: writes this shard's rows back as 18-byte blocks (host pointer,
  * rows*K/32*18 bytes).  Used by the parity tests to prove the repack is lossless. */
 int          ggml_b200_download_q4_0(const ggml_b200_weight * w, void * blocks_out);
+
+/* ---- weight-side Q4_0 codec on the device ---------------------------------------
+ * replaces quantize_row_q4_0 / quantize_row_q4_0_reference (ggml.c:918-957; bulk form ggml_quantize_q4_0
+ * :19157-19178, threaded caller llama.cpp:2452-2505): x_dev = nrows rows of K floats, row stride nb1 bytes;
+ * blocks_dev receives nrows*K/32 block_q4_0 (18 bytes each, rows dense).  Bit-identical to the reference, ties
+ * and sign of d included.  The blocks may be handed to ggml_b200_upload_q4_0, which accepts device pointers too. */
+int          ggml_b200_quantize_q4_0(const float * x_dev, int64_t nrows, int64_t K, size_t nb1, void * blocks_dev);
+/* replaces dequantize_row_q4_0 (ggml.c:1500-1518): nblocks 18-byte blocks -> 32*nblocks floats */
+int          ggml_b200_dequantize_q4_0(const void * blocks_dev, int64_t nblocks, float * y_dev);
+/* replaces ggml_compute_forward_get_rows_q for a Q4_0 src0 (ggml.c:11868-11890; token embeddings,
+ * llama.cpp:1358): y_dev row i (row stride nb1 bytes, >= 4*K) = dequantized row ids_dev[i] of the tensor.
+ * ids are int32 rows of the WHOLE tensor; GGML_B200_ERR_ARG if one is outside this shard. */
+int          ggml_b200_get_rows_q4_0(const ggml_b200_weight * w, const int32_t * ids_dev, int64_t n,
+                                     float * y_dev, size_t nb1);
 
 /* ---- kernel 1: activation quantizer -------------------------------------------------------
  * replaces quantize_row_q8_0 (ggml.c:1122-1280, AVX2 branch :1192-1250 is the contract) as the

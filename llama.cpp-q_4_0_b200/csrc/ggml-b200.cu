@@ -28,6 +28,7 @@
 #include "gemv_q4_0_stream.cuh"
 #include "quantize_q8_0.cuh"
 #include "repack.cuh"
+#include "codec_q4_0.cuh"
 #include "state.h"
 
 namespace b200 {
@@ -512,7 +513,7 @@ ggml_b200_weight * ggml_b200_upload_q4_0(const void * blocks, int64_t M, int64_t
     if (e != cudaSuccess) { cuda_fail(e, "cudaMalloc(raw)", __FILE__, __LINE__); delete w; return nullptr; }
     const char * src = (const char *)blocks + (size_t)row_lo * nb1;
     // blocking copy like the reference (ggml-cuda.cu:2797): the caller may free `blocks` on return
-    e = cudaMemcpy2DAsync(raw, row_bytes, src, nb1, row_bytes, (size_t)rows, cudaMemcpyHostToDevice, g.stream);
+    e = cudaMemcpy2DAsync(raw, row_bytes, src, nb1, row_bytes, (size_t)rows, cudaMemcpyDefault, g.stream);   // host or device source
     if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
     if (e != cudaSuccess) { cuda_fail(e, "upload copy", __FILE__, __LINE__); cudaFree(raw); delete w; return nullptr; }
 
@@ -576,6 +577,56 @@ int ggml_b200_download_q4_0(const ggml_b200_weight * w, void * out) {
     if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
     cudaFree(raw);
     if (e != cudaSuccess) return cuda_fail(e, "download", __FILE__, __LINE__);
+    return GGML_B200_OK;
+}
+
+// ---- weight-side codec (codec_q4_0.cuh) -----------------------------------------------------------
+static unsigned codec_grid(long long threads_needed) {
+    long long blocks = (threads_needed + 255) / 256;
+    const long long cap = (long long)g.sm_count * 16;
+    return (unsigned)(blocks < 1 ? 1 : blocks > cap ? cap : blocks);
+}
+
+int ggml_b200_quantize_q4_0(const float * x_dev, int64_t nrows, int64_t K, size_t nb1, void * blocks_dev) {
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    if (!x_dev || !blocks_dev || nrows < 0 || K <= 0 || (K % QK) != 0 || K > INT32_MAX || nb1 < (size_t)K * 4 || (nb1 & 3)) { set_error("bad quantize_q4_0 arguments"); return GGML_B200_ERR_ARG; }
+    if (nrows == 0) return GGML_B200_OK;
+    quantize_q4_0_kernel<<<codec_grid(nrows * (K / QK) * 4), 256, 0, g.stream>>>(x_dev, nrows, (int)K, nb1, (unsigned short *)blocks_dev);
+    g.launches++;
+    CK(cudaGetLastError());
+    return GGML_B200_OK;
+}
+
+int ggml_b200_dequantize_q4_0(const void * blocks_dev, int64_t nblocks, float * y_dev) {
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    if (!blocks_dev || !y_dev || nblocks < 0) { set_error("bad dequantize_q4_0 arguments"); return GGML_B200_ERR_ARG; }
+    if (nblocks == 0) return GGML_B200_OK;
+    dequantize_q4_0_kernel<<<codec_grid(nblocks * 8), 256, 0, g.stream>>>((const unsigned short *)blocks_dev, nblocks, y_dev);
+    g.launches++;
+    CK(cudaGetLastError());
+    return GGML_B200_OK;
+}
+
+int ggml_b200_get_rows_q4_0(const ggml_b200_weight * w, const int32_t * ids_dev, int64_t n, float * y_dev, size_t nb1) {
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    if (!w || !ids_dev || !y_dev || n < 0 || nb1 < (size_t)w->K * 4 || (nb1 & 3)) { set_error("bad get_rows arguments"); return GGML_B200_ERR_ARG; }
+    if (n == 0) return GGML_B200_OK;
+    int rc = ensure_stage(&g.sstage, &g.sstage_cap, 16);
+    if (rc) return rc;
+    int * bad = (int *)g.sstage;
+    CK(cudaMemsetAsync(bad, 0, 4, g.stream));
+    const int nbk = (int)(w->K / QK);
+    const unsigned grid = codec_grid(n * nbk * 8);
+    if (w->layout == GGML_B200_LAYOUT_PLANES)
+        get_rows_q4_0_kernel<true><<<grid, 256, 0, g.stream>>>(nullptr, w->wq, w->wd, ids_dev, n, nbk, w->row_lo, w->rows(), y_dev, (long long)(nb1 / 4), bad);
+    else
+        get_rows_q4_0_kernel<false><<<grid, 256, 0, g.stream>>>((const unsigned short *)w->raw, nullptr, nullptr, ids_dev, n, nbk, w->row_lo, w->rows(), y_dev, (long long)(nb1 / 4), bad);
+    g.launches++;
+    CK(cudaGetLastError());
+    int h_bad = 0;
+    CK(cudaMemcpyAsync(&h_bad, bad, 4, cudaMemcpyDeviceToHost, g.stream));
+    CK(cudaStreamSynchronize(g.stream));
+    if (h_bad) { set_error("get_rows: a row id is outside this shard [%lld,%lld)", (long long)w->row_lo, (long long)w->row_hi); return GGML_B200_ERR_ARG; }
     return GGML_B200_OK;
 }
 

@@ -69,6 +69,9 @@ def _load() -> C.CDLL:
         "ggml_b200_weight_device_bytes": (_sz, [_vp]),
         "ggml_b200_download_q4_0": (C.c_int, [_vp, _vp]),
         "ggml_b200_quantize_q8_0": (C.c_int, [_vp, _i64, _i64, _sz, _vp]),
+        "ggml_b200_quantize_q4_0": (C.c_int, [_vp, _i64, _i64, _sz, _vp]),
+        "ggml_b200_dequantize_q4_0": (C.c_int, [_vp, _i64, _vp]),
+        "ggml_b200_get_rows_q4_0": (C.c_int, [_vp, _vp, _i64, _vp, _sz]),
         "ggml_b200_mul_mat_q4_0": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
         "ggml_b200_mul_mat_q4_0_host": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
         "ggml_b200_block_dots_q4_0": (C.c_int, [_vp, _vp, _i64, _sz, _vp, C.c_int]),
@@ -252,6 +255,47 @@ def quantize_q8_0(x: np.ndarray) -> np.ndarray:
     synchronize()
     res = out.to_numpy(np.uint8, (n, K // QK, 34))
     xd.free()
+    out.free()
+    return res
+
+
+def quantize_q4_0(x: np.ndarray) -> np.ndarray:
+    """Weight quantizer on host data: f32 [M][K] -> reference-format blocks uint8 [M][K/32][18]."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    M, K = x.shape
+    xd = DevBuf.from_numpy(x)
+    out = DevBuf(max(1, M * (K // QK) * 18))
+    _check(lib().ggml_b200_quantize_q4_0(xd.ptr, M, K, K * 4, out.ptr))
+    synchronize()
+    res = out.to_numpy(np.uint8, (M, K // QK, 18))
+    xd.free()
+    out.free()
+    return res
+
+
+def dequantize_q4_0(blocks: np.ndarray) -> np.ndarray:
+    """uint8 [..., 18] blocks -> f32 [nblocks*32]."""
+    blocks = np.ascontiguousarray(blocks, dtype=np.uint8)
+    nblk = blocks.size // 18
+    bd = DevBuf.from_numpy(blocks)
+    out = DevBuf(max(1, nblk * QK * 4))
+    _check(lib().ggml_b200_dequantize_q4_0(bd.ptr, nblk, out.ptr))
+    synchronize()
+    res = out.to_numpy(np.float32, (nblk * QK,))
+    bd.free()
+    out.free()
+    return res
+
+
+def get_rows(w: Weight, ids: np.ndarray) -> np.ndarray:
+    """Rows `ids` of an uploaded Q4_0 tensor, dequantized: f32 [len(ids)][K]."""
+    ids = np.ascontiguousarray(ids, dtype=np.int32)
+    idd = DevBuf.from_numpy(ids) if ids.size else DevBuf(4)
+    out = DevBuf(max(1, ids.size * w.K * 4))
+    _check(lib().ggml_b200_get_rows_q4_0(w.h, idd.ptr, ids.size, out.ptr, w.K * 4))
+    synchronize()
+    res = out.to_numpy(np.float32, (ids.size, w.K))
+    idd.free()
     out.free()
     return res
 

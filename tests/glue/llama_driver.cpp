@@ -1,0 +1,35 @@
+// llama_driver.cpp -- test driver over the reference's PUBLIC llama.h API (llama_init_from_file, llama_eval,
+// llama_get_logits): loads a model file with the reference's unmodified loader, evaluates a prompt (n > 1) and then
+// one more token (n = 1), returns both logit vectors.  Built twice by ggml_glue/Makefile: against the plain CPU
+// reference (the truth) and against the reference compiled -DGGML_USE_CUBLAS + ggml-b200-glue.c + libggml_b200.so
+// (the drop-in).  Test infrastructure only.
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "llama.h"
+
+extern "C" int tiny_llama_run(const char * path, int n_gpu_layers, const int * tokens, int n_prompt, int next_token,
+                              int n_threads, float * logits_prompt, float * logits_decode, int n_vocab_expected) {
+    static bool backend = false;
+    if (!backend) { llama_init_backend(false); backend = true; }
+    llama_context_params p = llama_context_default_params();
+    p.n_ctx = 128;
+    p.n_batch = 64;
+    p.n_gpu_layers = n_gpu_layers;
+    p.seed = 1;
+    p.use_mmap = false;
+    p.f16_kv = true;
+    llama_context * ctx = llama_init_from_file(path, p);
+    if (!ctx) return -1;
+    const int nv = llama_n_vocab(ctx);
+    if (nv != n_vocab_expected) { llama_free(ctx); return -2; }
+    std::vector<llama_token> toks(tokens, tokens + n_prompt);
+    if (llama_eval(ctx, toks.data(), n_prompt, 0, n_threads) != 0) { llama_free(ctx); return -3; }
+    memcpy(logits_prompt, llama_get_logits(ctx), sizeof(float) * nv);
+    llama_token t = next_token;
+    if (llama_eval(ctx, &t, 1, n_prompt, n_threads) != 0) { llama_free(ctx); return -4; }
+    memcpy(logits_decode, llama_get_logits(ctx), sizeof(float) * nv);
+    llama_free(ctx);
+    return 0;
+}

@@ -61,6 +61,21 @@ def main():
     out["edge_X"] = e
     out["edge_q8"] = R.quantize_q8_0(e)
     out["edge_q8_scalar_reference"] = R.quantize_q8_0(e, scalar_reference=True)
+    # 3b. edge rows for the WEIGHT quantizer (ggml.c:918-957): ties between +a and -a in both orders decide the sign
+    # of d, an all-zero block gives d = -0.0, the max element lands on q = 0 and its mirror on 16 -> clamped to 15
+    w = np.zeros((8, 64), np.float32)
+    w[0, :32] = [1.5, -1.5] + [0.25] * 30;  w[0, 32:] = [-1.5, 1.5] + [-0.25] * 30        # +a first / -a first
+    w[1, 5] = 2.0; w[1, 40] = -2.0                                                          # mirrors across the nibble halves
+    w[2] = P.synthetic(64, 0x31, 1e-7)                                                      # d below fp16 denormals
+    w[3] = P.synthetic(64, 0x32, 4e5)                                                       # d overflows fp16
+    w[4] = P.synthetic(64, 0x33, 0.02); w[4, 31] = 0.3; w[4, 63] = -0.3                     # max in the last lane
+    w[5] = np.linspace(-1.0, 1.0, 64, dtype=np.float32)                                     # many .5 boundaries
+    w[6, :32] = np.arange(32, dtype=np.float32) / 31.0 * 8.0 - 4.0; w[6, 32:] = -w[6, :32]
+    w[7] = P.cos_data(64, 2.0)
+    out["edge_W"] = w
+    out["edge_W_q4_0"] = R.quantize_q4_0_bulk(w)
+    assert np.array_equal(out["edge_W_q4_0"], P.quantize_q4_0(w))
+    out["edge_W_dequant"] = R.dequantize_q4_0(out["edge_W_q4_0"])
     # 4. fp16 conversion table (65536 halves -> f32 bits) and a sample of f32 -> fp16
     out["fp16_to_fp32_bits"] = np.array([np.float32(R.fp16_to_fp32(h)).view(np.uint32) for h in range(65536)], np.uint32)
     fs = np.concatenate([P.synthetic(4096, 0x21, 1.0), P.synthetic(2048, 0x22, 1e-5), P.synthetic(2048, 0x23, 3e4),

@@ -99,3 +99,80 @@ def test_reference_graph_runs_the_op_on_the_gpu(b200, port, ref, M, K, n, offloa
     d = np.abs(Yg.astype(np.float64) - Yc)
     colmax = np.max(np.abs(Yc), axis=1, keepdims=True)
     assert float(np.max(d / colmax)) <= 1e-4
+
+
+# ---------------------------------------------------------------------------- whole model through the seam
+LLAMA_CPU_SO = os.path.join(PKG, "ggml_glue", "_build", "libllama_ref_cpu.so")
+LLAMA_B200_SO = os.path.join(PKG, "ggml_glue", "_build", "libllama_b200.so")
+
+
+def _tiny_llama_logits(tmp_path, lib, ngl, n_prompt, model):
+    import subprocess
+    import sys
+    out = str(tmp_path / (os.path.basename(lib) + ".%d.%d.npy" % (ngl, n_prompt)))
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "glue", "run_tiny_llama.py"), lib, model, str(ngl), str(n_prompt), out],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    return np.load(out), r.stderr
+
+
+def _tiny_model(tmp_path, n_layer=26):
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests", "glue"))
+    import make_tiny_llama
+    if not (os.path.exists(LLAMA_CPU_SO) and os.path.exists(LLAMA_B200_SO)):
+        pytest.skip("ggml_glue/_build/libllama_*.so not built (needs /root/reference at build time)")
+    return make_tiny_llama.write_model(str(tmp_path / ("tiny_llama_q4_0_%d.bin" % n_layer)), hp=dict(make_tiny_llama.HP, n_layer=n_layer))
+
+
+def test_tiny_llama_through_the_seam_without_a_gpu_is_the_cpu_reference(tmp_path):
+    """The reference's unmodified llama.cpp loader + graph (llama_init_from_file, llama_eval), built
+    -DGGML_USE_CUBLAS over the glue: on a host without a B200 nothing is offloaded and the logits are bit-identical
+    to the plain CPU build.  (On the GPU box this test is not selected; the GPU twin is below.)"""
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("GPU present: covered by the gpu-marked twin")
+    except ImportError:
+        pass
+    model = _tiny_model(tmp_path)
+    cpu, _ = _tiny_llama_logits(tmp_path, LLAMA_CPU_SO, 0, 40, model)
+    seam, _ = _tiny_llama_logits(tmp_path, LLAMA_B200_SO, 99, 40, model)
+    assert np.isfinite(cpu).all() and np.abs(cpu).max() > 1.0
+    assert np.array_equal(cpu, seam)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_prompt", [5, 40])
+def test_tiny_llama_offloaded_to_b200_matches_cpu_reference(tmp_path, n_prompt):
+    """Drop-in at model level: a 26-layer LLaMA (Q4_0 weights, the reference's file format) loaded by the reference's
+    unmodified loader with -ngl 99; all 183 Q4_0 matmuls per eval run on the B200 (prompt: n = 5 -> GEMV columns,
+    n = 40 -> tcgen05 GEMM; decode: n = 1 -> the one-launch host path), everything else on the reference CPU code.
+    Every matmul agrees with the CPU to ~1e-7 (tests/test_gpu_parity.py), but a model re-quantizes its activations
+    to int8 before every matmul, so a last-bit difference can move a rounding boundary and come back as one q8 step
+    (0.8 % of a block's amax); over 26 layers that is the reference's own build-to-build spread: its scalar
+    (-march=x86-64) and AVX2 builds differ by 1.8e-2 .. 2.6e-2 of the largest logit on this very model (measured in
+    the build container).  Bar: <= 3e-2 of the largest logit, cosine >= 0.9995, same arg-max token."""
+    model = _tiny_model(tmp_path)
+    cpu, _ = _tiny_llama_logits(tmp_path, LLAMA_CPU_SO, 0, n_prompt, model)
+    gpu, log = _tiny_llama_logits(tmp_path, LLAMA_B200_SO, 99, n_prompt, model)
+    assert "offloaded" in log
+    for i in range(2):
+        scale = float(np.abs(cpu[i]).max())
+        err = float(np.abs(cpu[i] - gpu[i]).max()) / scale
+        cos = float(np.dot(cpu[i], gpu[i]) / (np.linalg.norm(cpu[i]) * np.linalg.norm(gpu[i])))
+        assert err <= 3e-2 and cos >= 0.9995, f"eval {i}: max|dlogit|/max|logit| = {err:.3e}, cosine = {cos:.6f}"
+        assert int(cpu[i].argmax()) == int(gpu[i].argmax())
+
+
+@pytest.mark.gpu
+def test_shallow_llama_offloaded_to_b200_is_tight(tmp_path):
+    """The same through a 1-layer model, where no error has room to be re-quantized and amplified: 8 offloaded
+    matmuls per eval; logits within 1e-3 of the largest logit of the CPU reference."""
+    model = _tiny_model(tmp_path, n_layer=1)
+    cpu, _ = _tiny_llama_logits(tmp_path, LLAMA_CPU_SO, 0, 40, model)
+    gpu, _ = _tiny_llama_logits(tmp_path, LLAMA_B200_SO, 99, 40, model)
+    for i in range(2):
+        err = float(np.abs(cpu[i] - gpu[i]).max()) / float(np.abs(cpu[i]).max())
+        assert err <= 1e-3, f"eval {i}: max|dlogit|/max|logit| = {err:.3e}"
+        assert int(cpu[i].argmax()) == int(gpu[i].argmax())

@@ -360,6 +360,91 @@ def test_same_src1_ops_overlap_without_changing_results(b200, port, ref):
         w.free()
 
 
+# ---------------------------------------------------------------------------- weight-side codec
+def test_quantize_q4_0_golden_and_edges_bit_exact(b200, golden):
+    """quantize_row_q4_0 (ggml.c:918-957) on the device: the reference test's cos vector and the edge rows (sign of d
+    decided by the FIRST element of largest |x|, -0.0 scale of a zero block, clamp to 15) byte for byte."""
+    q = b200.quantize_q4_0(golden["cos_a"].reshape(1, -1))
+    assert np.array_equal(q.reshape(-1, 18), golden["cos_a_q4_0"].reshape(-1, 18))
+    assert q[0, 0, 0] == 0x33 and q[0, 0, 1] == 0xB4 and list(q[0, 0, 2:6]) == [0xF0, 0xA4, 0x3B, 0x0F]   # SURVEY 8c
+    e = b200.quantize_q4_0(golden["edge_W"])
+    assert np.array_equal(e, golden["edge_W_q4_0"])
+
+
+@pytest.mark.parametrize("M,K", [(1, 64), (7, 4096), (300, 4544), (33, 11008)])
+def test_quantize_q4_0_random_bit_exact(b200, port, ref, M, K):
+    wf = port.synthetic(M * K, 0xABC + M + K, 0.02, 50).reshape(M, K)
+    want = ref.quantize_q4_0_bulk(wf) if ref is not None else port.quantize_q4_0(wf)
+    assert np.array_equal(b200.quantize_q4_0(wf), want)
+
+
+def test_quantize_q4_0_strided_rows_and_device_upload(b200, port, ref):
+    """Row stride > 4*K, and the on-device path f32 -> blocks -> weight handle without a host round trip."""
+    M, K = 70, 1088
+    wide = port.synthetic(M * (K + 24), 0x77, 0.02).reshape(M, K + 24)
+    xd = b200.DevBuf.from_numpy(wide)
+    out = b200.DevBuf(M * (K // 32) * 18)
+    b200._check(b200.lib().ggml_b200_quantize_q4_0(xd.ptr + 16, M, K, (K + 24) * 4, out.ptr))   # rows start 4 floats in
+    b200.synchronize()
+    got = out.to_numpy(np.uint8, (M, K // 32, 18))
+    want = port.quantize_q4_0(np.ascontiguousarray(wide[:, 4:4 + K]))
+    assert np.array_equal(got, want)
+    h = b200.lib().ggml_b200_upload_q4_0(out.ptr, M, K, (K // 32) * 18, 0, M)                     # device pointer in
+    assert h
+    back = np.empty((M, K // 32, 18), np.uint8)
+    b200._check(b200.lib().ggml_b200_download_q4_0(h, back.ctypes.data))
+    assert np.array_equal(back, want)
+    x = make_x(port, 1, K, 5)
+    y = np.zeros((1, M), np.float32)
+    b200._check(b200.lib().ggml_b200_mul_mat_q4_0_host(h, x.ctypes.data, 1, K * 4, y.ctypes.data, M * 4))
+    assert_close(y, oracle_Y(port, ref, want, x))
+    b200.lib().ggml_b200_free_weight(h)
+
+
+def assert_same_floats(a, b):
+    """Bit-equal, except that any NaN matches any NaN (0 * inf: x86 yields 0xFFC00000, the GPU 0x7FFFFFFF)."""
+    a, b = np.asarray(a, np.float32).reshape(-1), np.asarray(b, np.float32).reshape(-1)
+    na, nb = np.isnan(a), np.isnan(b)
+    assert np.array_equal(na, nb)
+    assert np.array_equal(a.view(np.uint32)[~na], b.view(np.uint32)[~nb])
+
+
+def test_dequantize_q4_0_bit_exact(b200, golden, port):
+    """dequantize_row_q4_0 (ggml.c:1500-1518): exact, including the quantize -> dequantize round trip error bound of
+    the reference's own test (tests/test-quantize-fns.cpp:16,129: rmse <= 0.002 on the cos vector)."""
+    got = b200.dequantize_q4_0(golden["cos_a_q4_0"])
+    assert np.array_equal(got.view(np.uint32), golden["cos_a_dequant"].reshape(-1).view(np.uint32))
+    assert_same_floats(b200.dequantize_q4_0(golden["edge_W_q4_0"]), golden["edge_W_dequant"])       # row 3: d = inf, (8-8)*inf = NaN
+    n = got.size    # array_rmse of the reference test is sqrt(sum d^2) / n (tests/test-quantize-fns.cpp:33-41)
+    err = float(np.sqrt(np.sum((got.astype(np.float64) - golden["cos_a"].astype(np.float64)) ** 2))) / n
+    assert err <= 0.002 and abs(err - 0.001121) < 2e-6      # SURVEY 8c: "q4_0 abs err 0.001121"
+    W = port.quantize_q4_0(port.synthetic(50 * 2048, 0x99, 0.02).reshape(50, 2048))
+    assert np.array_equal(b200.dequantize_q4_0(W).view(np.uint32), port.dequantize_q4_0(W).reshape(-1).view(np.uint32))
+
+
+@pytest.mark.parametrize("repack", [True, False])
+def test_get_rows_q4_0(b200, port, repack):
+    """get_rows on a Q4_0 tensor (ggml.c:11868-11890; the token-embedding lookup) from both HBM layouts, full tensor
+    and a row shard; an id outside the shard is refused."""
+    M, K = 400, 1088
+    W = port.quantize_q4_0(port.synthetic(M * K, 0x55, 0.02).reshape(M, K))
+    full = port.dequantize_q4_0(W).reshape(M, K)
+    b200.set_repack(repack)
+    try:
+        w = b200.Weight(W)
+        ids = np.array([0, 399, 17, 17, 256, 3], np.int32)
+        assert np.array_equal(b200.get_rows(w, ids).view(np.uint32), full[ids].view(np.uint32))
+        assert b200.get_rows(w, np.zeros(0, np.int32)).shape == (0, K)
+        ws = b200.Weight(W, 128, 256)
+        ids2 = np.array([128, 255, 200], np.int32)
+        assert np.array_equal(b200.get_rows(ws, ids2).view(np.uint32), full[ids2].view(np.uint32))
+        with pytest.raises(b200.B200Error):
+            b200.get_rows(ws, np.array([100], np.int32))
+        w.free(); ws.free()
+    finally:
+        b200.set_repack(True)
+
+
 # ---------------------------------------------------------------------------- kernel 3: tcgen05 GEMM
 @pytest.mark.parametrize("M,K,n", [(128, 128, 128), (128, 256, 128), (256, 1024, 64), (300, 1088, 200), (70, 64, 5),
                                    (129, 4544, 130), (512, 4096, 512)])
