@@ -62,7 +62,7 @@ struct Ctx {
     float * ystage = nullptr; size_t ystage_cap = 0;
     void *  sstage = nullptr; size_t sstage_cap = 0;
     // n = 1 host entry point without driver copies or stream syncs (gemv_q4_0_hostio.cuh)
-    struct { float * hx = nullptr; size_t hx_cap = 0; float * hy = nullptr; size_t hy_cap = 0; unsigned * hdone = nullptr;
+    struct { float * hx = nullptr; size_t hx_cap = 0; float * hy = nullptr; size_t hy_cap = 0;
              float * xdev = nullptr; size_t xdev_cap = 0; float * ydev = nullptr; size_t ydev_cap = 0; unsigned * counters = nullptr;
              unsigned seq = 0; } hio;
     uint64_t launches = 0;
