@@ -45,6 +45,16 @@ WORKLOADS = {
 }
 
 
+def gemm_traffic():
+    """DRAM bytes of one 4096x4096 n=512 launch of kernel 3 from the committed ncu capture (profiles/traffic.json)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            d = json.load(f)
+        return {"bytes_per_launch_4096x4096_n512": d["gemm_dram_bytes_4096x4096_n512"], "algorithmic_read_bytes": 18 * 4096 * 4096 // 32 + 512 * 4096 + 512 * 128 * 4}
+    except Exception:   # noqa: BLE001
+        return None
+
+
 def algo_bytes(M, K, n=1):
     return 18 * M * K // 32 + 4 * K * n + 4 * M * n
 
@@ -329,7 +339,7 @@ def prefill_leg(mod, stream, rng, steps, warmup, n=512):
                 "api": "ggml_b200_mul_mat_q4_0_host (pinned host x/y)"},
         "roofline": {"kernel": "gemm_q4_0_tc_kernel (TMA + nibble unpack + tcgen05.mma kind::i8 + TMEM + scale epilogue)",
                      "bound": "tensor", "achieved": tops_gemm, "peak": 2 * bf16, "unit": "TOP/s", "frac": tops_gemm / (2 * bf16),
-                     "frac_of_nominal_4500": tops_gemm / 4500.0, "peak_source": src, "traffic": None,
+                     "frac_of_nominal_4500": tops_gemm / 4500.0, "peak_source": src, "traffic": gemm_traffic(),
                      "ms_per_pass_kernel3": ms_gemm,
                      "note": "the per-block fp16 x fp16 scale epilogue (2 fp32 FMA per int32 S_b on the CUDA cores) bounds this "
                              "formulation at 64/256 = 25% of the tensor rate with 128x128 tiles; see DESIGN.md kernel 3"},
