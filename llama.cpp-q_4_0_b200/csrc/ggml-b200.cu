@@ -206,7 +206,7 @@ static int independent_of_run(const ggml_b200_weight * w, const float * x, const
 static void run_append(const ggml_b200_weight * w, const float * x, const float * y, int independent) {
     auto & r = g.run;
     if (!independent) { r.count = 0; r.x = x; r.K = w->K; r.stream = g.stream; r.head = w; }
-    else { w->run_member = true; if (r.head) { r.head->run_member = true; if (r.count == 1) r.head->run_head = true; } }   // next pass: both take the half-SM kernel
+    else { w->run_member = true; if (r.head) r.head->run_member = true; }   // next pass: both take the half-SM kernel
     // an op whose dst overlaps x ends the run: the next reader of x must wait for it
     if (ranges_overlap(y, y + w->rows(), x, x + w->K)) { r.count = 0; r.x = nullptr; return; }
     r.y_lo[r.count] = y; r.y_hi[r.count] = y + w->rows(); r.count++;
@@ -280,7 +280,7 @@ int launch_fused(const ggml_b200_weight * w, const float * x, float * y, int * S
     // (profiles/r01_sweep_gemv_v2.log); an explicit fused_threads knob overrides
     // members of a same-src1 run take 512 threads (half an SM) with two rows in flight per warp, so that the run's
     // kernels, which do not wait for each other, are resident together and overlap end to end
-    const bool member = g.tune.overlap_same_src && g.tune.pdl && w->run_member && !(S || b34) && !(g.tune.run_head_big && w->run_head);
+    const bool member = g.tune.overlap_same_src && g.tune.pdl && w->run_member && !(S || b34);
     const bool big = !member && g.tune.fused_threads > 512;
     const int rif = member ? 2 : g.tune.fused_rif;
     if (S || b34) return big ? launch_fused_t<4, 1, 1024, true>(w, x, y, S, b34) : rif >= 2 ? launch_fused_t<4, 2, 512, true>(w, x, y, S, b34) : launch_fused_t<4, 1, 512, true>(w, x, y, S, b34);
@@ -468,7 +468,6 @@ int ggml_b200_set_tuning(const char * key, int value) {
     else if (!strcmp(key, "fused_ctas_per_sm")) { if (value < 1 || value > 16) return GGML_B200_ERR_ARG; g.tune.fused_ctas_per_sm = value; }
     else if (!strcmp(key, "skip_quantize")) { g.tune.skip_quantize = value != 0; }
     else if (!strcmp(key, "host_fast"))    { g.tune.host_fast = value != 0; }
-    else if (!strcmp(key, "run_head_big")) { g.tune.run_head_big = value != 0; }
     else if (!strcmp(key, "overlap_same_src")) { g.tune.overlap_same_src = value != 0; g.run.count = 0; }
     else if (!strcmp(key, "p2p_gather"))   { comm_set_p2p(value); }
     else return gemm_set_tuning(key, value);

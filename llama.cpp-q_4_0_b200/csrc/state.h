@@ -17,7 +17,6 @@ struct ggml_b200_weight {
     __half * wd = nullptr;           // LAYOUT_PLANES: scales  [rows][nbk]
     size_t  dev_bytes = 0;
     void *  gemm = nullptr;          // tensor-core path's per-weight state (TMA descriptors)
-    mutable bool run_head = false;   // ... as the first op of such a run
     mutable bool run_member = false; // seen in a run of n = 1 ops sharing src1 (overlap_same_src): gets the half-SM kernel
     int64_t rows() const { return row_hi - row_lo; }
 };
@@ -39,7 +38,6 @@ struct Tune {
     int fused_threads = 1024;    // threads per CTA of the fused kernel
     int fused_ctas_per_sm = 1;
     int pdl = 1;                 // programmatic dependent launch between consecutive kernels
-    int run_head_big = 0;        // overlap_same_src: the first op of a run keeps the 1024-thread kernel
     int overlap_same_src = 0;    // n == 1: an op that reads the same x as the previous one does not wait for it (caller owns the stream)
     int host_fast = 1;           // n == 1 host entry: single-launch path with mapped staging rows and a completion word
     int skip_quantize = 0;       // bench only: reuse the activations quantized by the previous call
