@@ -31,14 +31,20 @@ def main():
         blk = bench.random_q4_0(rng, M, K)
         w = mod.Weight(blk)
         for n in ns:
-            x = mod.DevBuf.from_numpy(rng.standard_normal((n, K), dtype=np.float32))
-            y = mod.DevBuf(n * M * 4)
-            for _ in range(3):
-                rc = L_.ggml_b200_mul_mat_q4_0(w.h, C.c_void_p(x.ptr), n, K * 4, C.c_void_p(y.ptr), M * 4)
-                assert rc == 0, L_.ggml_b200_last_error()
+            xh = rng.standard_normal((n, K), dtype=np.float32)
+            x = mod.DevBuf.from_numpy(xh)
+            ys = [mod.DevBuf(n * M * 4) for _ in range(3)]
+            for _ in range(2):          # distinct dst per call: with overlap_same_src=1 the second pass runs as a same-src1 run
+                for y in ys:
+                    rc = L_.ggml_b200_mul_mat_q4_0(w.h, C.c_void_p(x.ptr), n, K * 4, C.c_void_p(y.ptr), M * 4)
+                    assert rc == 0, L_.ggml_b200_last_error()
             mod.synchronize()
+            if n == 1 and "--host" in sys.argv:      # the one-launch host entry point (gemv_q4_0_hostio_kernel)
+                for _ in range(2):
+                    mod.mul_mat_host(w, xh)
             x.free()
-            y.free()
+            for y in ys:
+                y.free()
         w.free()
     mod.shutdown()
     print("ncu target done")
