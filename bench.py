@@ -439,7 +439,7 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
         assert xg[grp].shape[1] == K and yg[pos].shape[1] == M
         ops.append((h, M, K, xg[grp].data_ptr(), yg[pos].data_ptr()))
     torch.cuda.synchronize()
-    if world == 1 and not args.no_overlap:
+    if not args.no_overlap:
         # this process owns the stream: nothing but library ops sits between two matmuls that share src1
         mod.set_tuning("overlap_same_src", 1)
 
@@ -654,7 +654,7 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
                        "weights": "random-init Q4_0 blocks (one layer generated on the host, a separate HBM copy per layer)",
                        "layout": "planes (one-time repack at upload)", "cuda_graph": graph is not None,
                        "fused_quantize": not args.unfused, "pdl": not args.no_pdl,
-                       "same_src1_overlap": (world == 1 and not args.no_overlap), "tune": args.tune,
+                       "same_src1_overlap": not args.no_overlap, "tune": args.tune,
                        "parallelism": ("row-sharded x%d + peer-to-peer gather kernel per matmul (NVLink stores + flags; NCCL only for n > 1)" % world) if world > 1 else "single GPU",
                        "setup_s": round(setup_s, 2), "sanity_max_rel_err": parity},
             "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps), "gpu_launches_per_step": int(launches_per_step),

@@ -31,9 +31,8 @@ constexpr int P2P_GATHER_CTAS = 8;
 __global__ void __launch_bounds__(1024)
 p2p_gather_kernel(const __grid_constant__ P2PExchange ex, float * __restrict__ y, int mode) {
     asm volatile("griddepcontrol.wait;" ::: "memory");     // this rank's rows come from the GEMV just before
-    asm volatile("griddepcontrol.launch_dependents;");
     __shared__ unsigned s_seq;
-    if (threadIdx.x == 0) s_seq = p2p_op_number(ex);
+    if (threadIdx.x == 0) { s_seq = p2p_counter(ex) + P2P_MAX_RUN; p2p_head_publish_and_release(ex, s_seq); }   // always a dependent op
     __syncthreads();
     const unsigned seq = s_seq;
     int lo_me, n_me, j0, j1;
@@ -41,7 +40,6 @@ p2p_gather_kernel(const __grid_constant__ P2PExchange ex, float * __restrict__ y
     p2p_cta_slice(n_me, j0, j1);
     if (mode != 4) p2p_send(ex, seq, y + lo_me + j0, lo_me + j0, j1 - j0);
     if (mode == 1) p2p_receive(ex, seq, y);
-    p2p_cta_done(ex, seq);
 }
 
 struct Nccl {

@@ -27,10 +27,11 @@ __host__ __device__ inline size_t gemv_p2p_smem_bytes(int nbk, int rows, int gri
 }
 
 template <int UNROLL, int MAXT>
-__global__ void __launch_bounds__(MAXT, 1)
+__global__ void __launch_bounds__(MAXT, MAXT <= 512 ? 2 : 1)
 gemv_q4_0_fused_p2p_kernel(const uint4 * __restrict__ wq, const __half * __restrict__ wd,
                            const float * __restrict__ x, float * __restrict__ y /* whole dst column */,
-                           int rows, int nbk, int x_aligned, unsigned seq_trace, const __grid_constant__ P2PExchange ex) {
+                           int rows, int nbk, int x_aligned, unsigned seq_trace, const __grid_constant__ P2PExchange ex,
+                           int run_index /* 0: dependent op; j > 0: j-th op that only shares src1 with its predecessors */) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     GemvSmem<1> s(smem_raw, nbk);
     float * yres = reinterpret_cast<float *>(smem_raw + gemv_smem_bytes(nbk, 1));
@@ -40,16 +41,22 @@ gemv_q4_0_fused_p2p_kernel(const uint4 * __restrict__ wq, const __half * __restr
     const int nwarps = blockDim.x >> 5;
     CtaTrace tr;
     if (threadIdx.x == 0) tr.begin(seq_trace);
+    if (run_index && threadIdx.x == 0) pdl_launch_dependents();      // independent of the previous op (gemv_q4_0_fused.cuh): no wait at the top
+    unsigned seq_ld = 0;
+    if (threadIdx.x == 0) seq_ld = p2p_counter(ex) + (run_index ? (unsigned)run_index : (unsigned)P2P_MAX_RUN);   // stable before the wait (p2p.cuh)
 
     // this CTA's contiguous slice of the shard
     int j0, j1;
     p2p_cta_slice(rows, j0, j1);
     const unsigned short * wd16 = reinterpret_cast<const unsigned short *>(wd);
 
-    // 1. first row of this warp (weights are never produced by the previous kernel)
+    // 1. first row of this warp (weights are never produced by the previous kernel).  Warp 0 of a dependent op
+    // holds back: its thread 0 publishes the op number behind a __threadfence right after the wait, and a fence
+    // with weight loads in flight would stall on them.
     uint4 q[UNROLL];
     unsigned short dh[UNROLL];
-    {
+    bool prefetched = run_index != 0 || warp != 0;
+    if (prefetched) {
         const int row = j0 + warp;
         if (row < j1) {
 #pragma unroll
@@ -60,11 +67,12 @@ gemv_q4_0_fused_p2p_kernel(const uint4 * __restrict__ wq, const __half * __restr
         }
     }
 
-    // 2. x, dst and the op counter may belong to the previous kernel
-    pdl_wait();
-    pdl_launch_dependents();   // after the wait: see gemv_q4_0_fused.cuh (independent ops)
-    unsigned seq_ld = 0;
-    if (threadIdx.x == 0) { tr.mark(1); seq_ld = p2p_op_number(ex); }   // in flight under the quantizer
+    // 2. x and dst may belong to the previous kernel.  A dependent op publishes its op number for the followers of
+    // its run and releases its dependents right after the wait.
+    if (!run_index) {
+        pdl_wait();
+        if (threadIdx.x == 0) { tr.mark(1); p2p_head_publish_and_release(ex, seq_ld); }
+    }
 
     // 3. quantize_row_q8_0 into the smem planes
     quantize_x_to_smem<false>(s, x, nbk, x_aligned, warp, lane, nullptr);
@@ -76,7 +84,6 @@ gemv_q4_0_fused_p2p_kernel(const uint4 * __restrict__ wq, const __half * __restr
     p2p_rows_of(ex, ex.me, lo_me, n_me);
 
     // 4. dot loop over the slice
-    bool prefetched = true;
     for (int row = j0 + warp; row < j1; row += nwarps) {
         float acc = 0.0f;
         for (int b0 = lane; b0 < nbk; b0 += 32 * UNROLL) {
@@ -106,8 +113,8 @@ gemv_q4_0_fused_p2p_kernel(const uint4 * __restrict__ wq, const __half * __restr
     // 5. slice -> every peer; peers' rows -> dst
     p2p_send(ex, seq, yres, lo_me + j0, j1 - j0);
     p2p_receive(ex, seq, y);
-    p2p_cta_done(ex, seq);
     if (threadIdx.x == 0) tr.mark(3);
+    if (run_index) pdl_wait();                   // completion of this op must imply completion of its predecessors
 }
 
 }  // namespace b200

@@ -193,23 +193,22 @@ static int launch_gemv_any(const ggml_b200_weight * w, float * y, long long ldy,
 // its dst overlaps neither x nor the dst of any op of the current run.
 static bool ranges_overlap(const float * a_lo, const float * a_hi, const float * b_lo, const float * b_hi) { return a_lo < b_hi && b_lo < a_hi; }
 
-static int independent_of_run(const ggml_b200_weight * w, const float * x, const float * y) {
+static int independent_of_run(const ggml_b200_weight * w, const float * x, const float * y, const float * y_hi, int max_run = 8) {
     auto & r = g.run;
-    if (!g.tune.overlap_same_src || !g.tune.pdl || r.count == 0 || r.count >= 8) return 0;
+    if (!g.tune.overlap_same_src || !g.tune.pdl || r.count == 0 || r.count >= max_run) return 0;
     if (r.x != x || r.K != w->K || r.stream != g.stream || r.launches_after != g.launches) return 0;
-    const float * y_hi = y + w->rows();
     if (ranges_overlap(y, y_hi, x, x + w->K)) return 0;
     for (int i = 0; i < r.count; i++) if (ranges_overlap(y, y_hi, r.y_lo[i], r.y_hi[i])) return 0;
     return 1;
 }
 
-static void run_append(const ggml_b200_weight * w, const float * x, const float * y, int independent) {
+static void run_append(const ggml_b200_weight * w, const float * x, const float * y, const float * y_hi, int independent) {
     auto & r = g.run;
     if (!independent) { r.count = 0; r.x = x; r.K = w->K; r.stream = g.stream; r.head = w; }
     else { w->run_member = true; if (r.head) r.head->run_member = true; }   // next pass: both take the half-SM kernel
     // an op whose dst overlaps x ends the run: the next reader of x must wait for it
-    if (ranges_overlap(y, y + w->rows(), x, x + w->K)) { r.count = 0; r.x = nullptr; return; }
-    r.y_lo[r.count] = y; r.y_hi[r.count] = y + w->rows(); r.count++;
+    if (ranges_overlap(y, y_hi, x, x + w->K)) { r.count = 0; r.x = nullptr; return; }
+    r.y_lo[r.count] = y; r.y_hi[r.count] = y_hi; r.count++;
     r.launches_after = g.launches;
 }
 
@@ -226,10 +225,10 @@ static int launch_fused_t(const ggml_b200_weight * w, const float * x, float * y
     int threads = g.tune.fused_threads > MAXT ? MAXT : g.tune.fused_threads;
     const int grid = g.sm_count * g.tune.fused_ctas_per_sm;
     const int aligned = (((uintptr_t)x) & 15) == 0;
-    const int independent = (S || b34) ? 0 : independent_of_run(w, x, y);
+    const int independent = (S || b34) ? 0 : independent_of_run(w, x, y, y + w->rows());
     int rc = launch_k(kern, grid, threads, gemv_smem_bytes(nbk, 1), (const uint4 *)w->wq, (const __half *)w->wd, x, y, (int)w->rows(), nbk, aligned, S, b34, (unsigned)g.launches,
                       independent);
-    if (rc == GGML_B200_OK && !(S || b34)) run_append(w, x, y, independent);
+    if (rc == GGML_B200_OK && !(S || b34)) run_append(w, x, y, y + w->rows(), independent);
     return rc;
 }
 
@@ -326,18 +325,31 @@ bool fused_p2p_ok(const ggml_b200_weight * w) {
            gemv_p2p_smem_bytes((int)(w->K / QK), (int)w->rows(), g.sm_count) <= (size_t)MAX_DYN_SMEM - 1024;
 }
 
-int launch_fused_p2p(const ggml_b200_weight * w, const float * x_dev, size_t nb11, float * y_dev, const P2PExchange & ex) {
-    (void)nb11;   // n == 1: a single activation row
+template <int MAXT>
+static int launch_fused_p2p_t(const ggml_b200_weight * w, const float * x_dev, float * y_dev, const P2PExchange & ex, int run_index) {
     const int nbk = (int)(w->K / QK);
-    auto kern = gemv_q4_0_fused_p2p_kernel<4, 1024>;
+    auto kern = gemv_q4_0_fused_p2p_kernel<4, MAXT>;
     static bool attr_set = false;
     if (!attr_set) {
         CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM - 1024));   // the kernel has static smem too
         attr_set = true;
     }
     const int aligned = (((uintptr_t)x_dev) & 15) == 0;
-    return launch_k(kern, g.sm_count, 1024, gemv_p2p_smem_bytes(nbk, (int)w->rows(), g.sm_count), (const uint4 *)w->wq, (const __half *)w->wd, x_dev, y_dev,
-                    (int)w->rows(), nbk, aligned, (unsigned)g.launches, ex);
+    return launch_k(kern, g.sm_count, MAXT, gemv_p2p_smem_bytes(nbk, (int)w->rows(), g.sm_count), (const uint4 *)w->wq, (const __half *)w->wd, x_dev, y_dev,
+                    (int)w->rows(), nbk, aligned, (unsigned)g.launches, ex, run_index);
+}
+
+int launch_fused_p2p(const ggml_b200_weight * w, const float * x_dev, size_t nb11, float * y_dev, const P2PExchange & ex) {
+    (void)nb11;   // n == 1: a single activation row
+    // ops that only share src1 with their predecessors (wq/wk/wv, w3/w1) neither wait for them nor for their
+    // exchange: position in the run = op-number offset (p2p.cuh); members of a run take the half-SM variant so
+    // that the next op computes while this one waits for its peers
+    const int independent = independent_of_run(w, x_dev, y_dev, y_dev + w->M, P2P_MAX_RUN);
+    const int run_index = independent ? g.run.count : 0;
+    const bool member = g.tune.overlap_same_src && g.tune.pdl && w->run_member;
+    const int rc = member ? launch_fused_p2p_t<512>(w, x_dev, y_dev, ex, run_index) : launch_fused_p2p_t<1024>(w, x_dev, y_dev, ex, run_index);
+    if (rc == GGML_B200_OK) run_append(w, x_dev, y_dev, y_dev + w->M, independent);
+    return rc;
 }
 
 // this shard's slab of dst, dense: y = first element of column 0, ldy floats between columns

@@ -3,16 +3,22 @@
 //
 // An NCCL all-gather of a few KB costs ~12 us per matmul, several times the GEMV it follows.  Instead every rank
 // owns an "arena" in its HBM, exported with cudaIpcGetMemHandle and mapped by every peer at comm_init:
-//     [2 halves][P2P_MAX_M] 8-byte words   (bits of y[m], op number), double-buffered by the op number's parity
-//     P2P_CTR_SLOTS op counters            one per CTA index, touched only by the owning rank
+//     [P2P_REGIONS][P2P_MAX_M] 8-byte words (bits of y[m], op number); op s uses region s % P2P_REGIONS
+//     P2P_CTR_SLOTS op counters             one per CTA index, touched only by the owning rank
 // A rank stores its rows into every peer's arena with each word carrying the op number next to the value: 8-byte
 // words are single-copy atomic, so a word whose number matches IS the datum -- no fence, no separate flag, no
 // round trip, one NVLink one-way latency per op.  It then polls its own arena for the peers' rows.
-//   * A peer can run at most one op ahead (its next op needs this rank's next rows), so two halves are enough.
+//   * A peer can run ahead by at most one run of independent ops (<= P2P_MAX_RUN; the op after a run needs this
+//     rank's rows of every op of the run), so P2P_REGIONS > P2P_MAX_RUN regions never collide.
 //   * Op numbers live on the device, so a captured CUDA graph replays correctly, and every rank numbers its ops
-//     identically (same op sequence).  CTA b reads slot b after the dependency wait and, when done, writes the
-//     new number to slots b, b + grid, b + 2 grid, ...: every launch leaves ALL slots equal, whatever its grid,
-//     without atomics or fences (the next reader is a later kernel).
+//     identically (same op sequence).  Only DEPENDENT ops (heads of runs) write the counters: CTA b reads ctr[b]
+//     BEFORE its dependency wait (the value is stable: the previous head wrote it before it released anything),
+//     and after the wait one thread stores number = old + P2P_MAX_RUN to ctr[b, b + grid, ...], fences, and only
+//     then releases the dependents (griddepcontrol.launch_dependents counts per CTA as soon as ONE thread issues
+//     it: tools/ubench/pdl_trigger.cu).  An op that runs independently of its predecessor (same src1: wq/wk/wv)
+//     does not wait; the host tells it its position j in the run and it takes ctr[b] + j, which the head stored
+//     before this launch could be scheduled.  Heads always advance by P2P_MAX_RUN, whatever the run's length, so
+//     numbers never repeat even when a captured graph is replayed after a different history.
 //   * Ranks are separate GPUs driven by separate processes: a poll cannot starve the peer it waits for.
 #pragma once
 #include <stdint.h>
@@ -21,8 +27,10 @@ namespace b200 {
 
 constexpr int P2P_MAX_WORLD = 8;
 constexpr int P2P_MAX_M = 65536;
+constexpr int P2P_REGIONS = 8;
+constexpr int P2P_MAX_RUN = 4;                                 // ops of one same-src1 run that may be in flight together
 constexpr int P2P_CTR_SLOTS = 256;                             // >= any grid that takes part
-constexpr size_t P2P_CTR_OFF = (size_t)2 * P2P_MAX_M * 8;
+constexpr size_t P2P_CTR_OFF = (size_t)P2P_REGIONS * P2P_MAX_M * 8;
 constexpr size_t P2P_ARENA_BYTES = P2P_CTR_OFF + P2P_CTR_SLOTS * 4;
 constexpr unsigned long long P2P_TIMEOUT_NS = 60000000000ull;  // a peer that never arrives: trap, do not hang
 
@@ -48,15 +56,17 @@ __device__ __forceinline__ unsigned long long p2p_now() { unsigned long long t; 
 
 __device__ __forceinline__ unsigned * p2p_ctr(const P2PExchange & e) { return reinterpret_cast<unsigned *>(e.peers.arena[e.me] + P2P_CTR_OFF); }
 
-// op number of the launch this CTA belongs to; call after the dependency wait
-__device__ __forceinline__ unsigned p2p_op_number(const P2PExchange & e) {
-    return reinterpret_cast<volatile unsigned *>(p2p_ctr(e))[blockIdx.x % P2P_CTR_SLOTS] + 1u;
+// the counter as this CTA sees it: a head may read it BEFORE its dependency wait, a follower any time
+__device__ __forceinline__ unsigned p2p_counter(const P2PExchange & e) {
+    return reinterpret_cast<volatile unsigned *>(p2p_ctr(e))[blockIdx.x % P2P_CTR_SLOTS];
 }
-
-// call with every thread of the CTA when it has finished sending and receiving
-__device__ __forceinline__ void p2p_cta_done(const P2PExchange & e, unsigned seq) {
-    const unsigned slot = blockIdx.x + gridDim.x * threadIdx.x;
-    if (slot < (unsigned)P2P_CTR_SLOTS) p2p_ctr(e)[slot] = seq;
+// head, ONE thread, after the dependency wait: store the run's number, make it visible, release the dependents.
+// No other thread of the CTA may issue griddepcontrol.launch_dependents.
+__device__ __forceinline__ void p2p_head_publish_and_release(const P2PExchange & e, unsigned seq) {
+    volatile unsigned * ctr = reinterpret_cast<volatile unsigned *>(p2p_ctr(e));
+    for (unsigned slot = blockIdx.x; slot < (unsigned)P2P_CTR_SLOTS; slot += gridDim.x) ctr[slot] = seq;
+    __threadfence();
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 
 // rows [lo, lo+n) of rank r
@@ -75,7 +85,7 @@ __device__ __forceinline__ void p2p_cta_slice(int n, int & j0, int & j1) {
 // send vals[0..cnt) = y[lo_me + j0 ...] to every peer (all threads of the CTA; consecutive threads -> consecutive words)
 __device__ __forceinline__ void p2p_send(const P2PExchange & e, unsigned seq, const float * vals, int first_row, int cnt) {
     const unsigned long long tag = (unsigned long long)seq << 32;
-    const size_t half = (size_t)(seq & 1u) * P2P_MAX_M;
+    const size_t half = (size_t)(seq % P2P_REGIONS) * P2P_MAX_M;
     const int total = (e.world - 1) * cnt;
     for (int i = threadIdx.x; i < total; i += blockDim.x) {
         const int pi = i / cnt, j = i - pi * cnt;
@@ -86,7 +96,7 @@ __device__ __forceinline__ void p2p_send(const P2PExchange & e, unsigned seq, co
 
 // receive this CTA's slice of every peer's rows into y as they land
 __device__ __forceinline__ void p2p_receive(const P2PExchange & e, unsigned seq, float * __restrict__ y) {
-    const size_t half = (size_t)(seq & 1u) * P2P_MAX_M;
+    const size_t half = (size_t)(seq % P2P_REGIONS) * P2P_MAX_M;
     const unsigned long long * in = reinterpret_cast<const unsigned long long *>(e.peers.arena[e.me]) + half;
     const int rs = (e.per + gridDim.x - 1) / gridDim.x;        // slice length of a full shard
     const int total = (e.world - 1) * rs;

@@ -144,6 +144,75 @@ def main():
         failures.append(f"rank {rank} graph: {e}")
         mod.set_stream(stream.cuda_stream)
 
+    # ---- same-src1 runs (overlap_same_src): wq/wk/wv-like triples and w3/w1-like pairs do not wait for each other nor
+    # for each other's exchange; a consumer of their results must still see all of them.  60 rounds back to back,
+    # eagerly and from a CUDA graph, against the same sequence on the unsharded weights.
+    run_us = None
+    (wf0, ws0, M0, K0), (wf1, ws1, M1, K1) = weights[0], weights[1]          # 4096x4096 and 11008x4096
+    rounds = 60
+
+    def make_bufs():
+        return {k: torch.zeros((1, m), dtype=torch.float32, device="cuda") for k, m in
+                (("a", M0), ("b", M0), ("c", M0), ("d", M0), ("e", M1), ("f", M1), ("g", M0))}
+
+    def sequence(fn, w0, w1, B):
+        for r in range(rounds):
+            xin = x0 if r % 3 == 0 else B["g"]
+            for k in ("a", "b", "c"):
+                fn(w0, xin, K0, B[k], M0)                       # run of three on xin
+            fn(w0, B["b"], K0, B["d"], M0)                      # consumes a member of the run
+            for k in ("e", "f"):
+                fn(w1, B["d"], K0, B[k], M1)                    # run of two
+            fn(w0, B["c"], K0, B["g"], M0)                      # feeds the next round
+
+    def op_full(w, x, K, y, M):
+        assert L.ggml_b200_mul_mat_q4_0(w.h, C.c_void_p(x.data_ptr()), 1, K * 4, C.c_void_p(y.data_ptr()), M * 4) == 0, err()
+
+    def op_shard(w, x, K, y, M):
+        assert L.ggml_b200_mul_mat_q4_0_sharded(w.h, C.c_void_p(x.data_ptr()), 1, K * 4, C.c_void_p(y.data_ptr()), M * 4) == 0, err()
+
+    Bref, Bsh = make_bufs(), make_bufs()
+    torch.cuda.synchronize()
+    sequence(op_full, wf0, wf1, Bref)
+    mod.synchronize()
+    mod.set_tuning("overlap_same_src", 1)
+    try:
+        for attempt in range(2):                                # second pass: run members are known, half-SM kernels
+            for b_ in Bsh.values():
+                b_.zero_()
+            torch.cuda.synchronize()
+            dist.barrier()
+            sequence(op_shard, ws0, ws1, Bsh)
+            mod.synchronize()
+            for k in Bref:
+                if not torch.equal(Bsh[k], Bref[k]):
+                    failures.append(f"rank {rank} same-src runs, pass {attempt}: buffer {k} differs")
+        g2 = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g2, stream=stream):
+            mod.set_stream(torch.cuda.current_stream().cuda_stream)
+            sequence(op_shard, ws0, ws1, Bsh)
+        mod.set_stream(stream.cuda_stream)
+        for rep in range(3):
+            for b_ in Bsh.values():
+                b_.zero_()
+            torch.cuda.synchronize()
+            dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            with torch.cuda.stream(stream):
+                e0.record(stream)
+                g2.replay()
+                e1.record(stream)
+            stream.synchronize()
+            run_us = e0.elapsed_time(e1) * 1e3 / (rounds * 7)
+            for k in Bref:
+                if not torch.equal(Bsh[k], Bref[k]):
+                    failures.append(f"rank {rank} same-src runs, graph replay {rep}: buffer {k} differs")
+        del g2
+    except Exception as e:   # noqa: BLE001
+        failures.append(f"rank {rank} same-src runs: {e}")
+        mod.set_stream(stream.cuda_stream)
+    mod.set_tuning("overlap_same_src", 0)
+
     # NCCL per-op time on the same chain for the log
     mod.set_tuning("p2p_gather", 0)
     dist.barrier()
@@ -162,7 +231,8 @@ def main():
         for f in flat:
             print("FAIL", f)
         print(f"CHECK_SHARDED {'OK' if not flat else 'FAILED'} world={world} shapes={len(shapes)} "
-              f"chain_us_per_op p2p={dt:.1f} (graph {graph_us if graph_us is None else round(graph_us, 2)}) nccl={dt_nccl:.1f}")
+              f"chain_us_per_op p2p={dt:.1f} (graph {graph_us if graph_us is None else round(graph_us, 2)}) nccl={dt_nccl:.1f} "
+              f"same-src-runs graph us/op={run_us if run_us is None else round(run_us, 2)}")
     sys.stdout.flush()
     dist.barrier()
     torch.cuda.synchronize()
