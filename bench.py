@@ -269,10 +269,19 @@ def prefill_leg(mod, stream, rng, steps, warmup, n=512):
     Ms = sorted({M for (_, M, _) in handles})
     xs = {K: torch.randn(n, K, device="cuda") for K in Ks}
     ys = {M: torch.zeros(n, M, device="cuda") for M in Ms}
+    # device-resident leg: buffers as the model graph has them (wq, wk, wv share the normed rows; w3, w1 too; every
+    # matmul has its own dst), so same-src1 ops may reuse the quantized activations and overlap (overlap_same_src)
+    groups = ["attn_in", "attn_in", "attn_in", "attn_out", "ffn_in", "ffn_in", "ffn_mid", "out_in"]
+    assert len(handles) == len(groups)
+    xg, dev_ops = {}, []
+    for (h, M, K), grp in zip(handles, groups):
+        if grp not in xg:
+            xg[grp] = xs[K].clone()
+        dev_ops.append((h, M, K, xg[grp], torch.zeros(n, M, device="cuda")))
 
     def one_pass():
-        for (h, M, K) in handles:
-            rc = L_.ggml_b200_mul_mat_q4_0(h, C.c_void_p(xs[K].data_ptr()), n, K * 4, C.c_void_p(ys[M].data_ptr()), M * 4)
+        for (h, M, K, xb, yb) in dev_ops:
+            rc = L_.ggml_b200_mul_mat_q4_0(h, C.c_void_p(xb.data_ptr()), n, K * 4, C.c_void_p(yb.data_ptr()), M * 4)
             if rc:
                 raise RuntimeError(L_.ggml_b200_last_error().decode())
     c0 = mod.launch_count()

@@ -92,7 +92,7 @@ void gemm_release_weight(ggml_b200_weight * w) {
     if (w->gemm) { delete (GemmWeight *)w->gemm; w->gemm = nullptr; }
 }
 
-int launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int * S) {
+int launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int * S, int independent) {
     if (!gemm_available(w)) { set_error("tensor-core GEMM path not available for this weight"); return GGML_B200_ERR_STATE; }
     if (!g.xdT || g.xdT_n_pad < n) { set_error("activation scales were not laid out for the GEMM path"); return GGML_B200_ERR_STATE; }
     const GemmWeight * gw = (const GemmWeight *)w->gemm;
@@ -116,13 +116,13 @@ int launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int
     const __half * wd = w->wd;
     const int rows = (int)w->rows(), nbk_i = (int)nbk;
     if (g_gemm_trace && !S) {
-        CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<false, true, true>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace));
+        CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<false, true, true>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
     } else if (g_gemm_bias) {
-        if (S) CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<true, true, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace));
-        else   CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<false, true, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace));
+        if (S) CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<true, true, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
+        else   CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<false, true, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
     } else {
-        if (S) CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<true, false, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace));
-        else   CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<false, false, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace));
+        if (S) CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<true, false, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
+        else   CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<false, false, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
     }
     g.launches++;
     return GGML_B200_OK;

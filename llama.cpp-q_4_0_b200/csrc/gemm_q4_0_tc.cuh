@@ -136,7 +136,8 @@ gemm_q4_0_tc_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble plan
                     const __grid_constant__ CUtensorMap tm_xd,    // act. scales   [nbk][n_pad] f32, box 128 x 4
                     const __half * __restrict__ wd,               // weight scales [rows][nbk]
                     float * __restrict__ y, long long ldy, int rows, int n, int nbk,
-                    int * __restrict__ S_out, long long * __restrict__ trc) {
+                    int * __restrict__ S_out, long long * __restrict__ trc,
+                    int independent /* reads the activations its predecessor read, writes its own dst: no wait at the top */) {
 #define GEMM_TR(role, idx) do { if (TRACE && trc != nullptr && blockIdx.x == 0 && blockIdx.y == 0) trc[(role) * 2048 + (idx)] = clock64(); } while (0)
     // no static shared memory in this kernel: the dynamic window starts 1024-byte aligned (checked below),
     // which the 128-byte swizzle atoms need; a computed alignment would be rematerialised all over the epilogue
@@ -170,7 +171,10 @@ gemm_q4_0_tc_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble plan
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
-    pdl_wait();   // the quantized activations come from the previous kernel
+    // the quantized activations come from the previous kernel -- unless this op only shares them with its predecessor
+    // (wq/wk/wv, w3/w1 of one layer; the host skipped kernel 1): then its tiles fill the SMs the predecessor's last wave
+    // leaves idle, and it waits at its END so that its completion still implies the predecessor's
+    if (!independent) pdl_wait();
     pdl_launch_dependents();   // after the wait: see gemv_q4_0_fused.cuh (independent ops)
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(smem + GEMM_SMEM_BAR + GemmBars::tmem_slot);
 
@@ -410,6 +414,7 @@ gemm_q4_0_tc_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble plan
         tc_fence_after_sync();
         tmem_dealloc(tmem_base, 512);
     }
+    if (independent) pdl_wait();
 }
 
 }  // namespace b200

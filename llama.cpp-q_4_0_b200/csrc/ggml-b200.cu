@@ -367,13 +367,27 @@ int launch_slab(const ggml_b200_weight * w, const float * x_dev, int64_t n, size
 int mul_mat_dev(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y_dev, size_t nb1) {
     if (n == 0 || w->rows() == 0) return GGML_B200_OK;
     if (fused_ok(w, n)) return launch_fused(w, x_dev, y_dev + w->row_lo, nullptr, nullptr);
-    if (!g.tune.skip_quantize) {
+    float * y = y_dev + w->row_lo;
+    const long long ldy = (long long)(nb1 / 4);
+    // n > 1, same src1 as the previous op of this library on this stream, dst disjoint (overlap_same_src contract,
+    // see independent_of_run): kernel 1 already ran for this x -- reuse its output, and let the GEMM start without
+    // waiting for its predecessor
+    const float * y_hi = y + (n - 1) * ldy + w->rows();
+    auto & r = g.runN;
+    bool same = g.tune.overlap_same_src && g.tune.pdl && r.count > 0 && r.count < 8 && r.x == x_dev && r.n == n && r.K == w->K && r.nb11 == nb11 &&
+                r.stream == g.stream && r.launches_after == g.launches && !ranges_overlap(y, y_hi, x_dev, (const float *)((const char *)x_dev + n * nb11));
+    for (int i = 0; same && i < r.count; i++) same = !ranges_overlap(y, y_hi, r.y_lo[i], r.y_hi[i]);
+    if (!same && !g.tune.skip_quantize) {
         int rc = launch_quantize(x_dev, n, w->K, nb11, nullptr);
         if (rc) return rc;
     }
-    float * y = y_dev + w->row_lo;
-    const long long ldy = (long long)(nb1 / 4);
-    return launch_shard(w, y, ldy, (int)n);
+    const int rc = use_gemm(w, n) ? launch_gemm(w, y, ldy, (int)n, nullptr, same ? 1 : 0) : launch_gemv(w, y, ldy, (int)n);
+    if (rc) return rc;
+    if (!same) { r.count = 0; r.x = x_dev; r.n = n; r.K = w->K; r.nb11 = nb11; r.stream = g.stream; }
+    if (ranges_overlap(y, y_hi, x_dev, (const float *)((const char *)x_dev + n * nb11))) { r.count = 0; r.x = nullptr; return GGML_B200_OK; }
+    r.y_lo[r.count] = y; r.y_hi[r.count] = y_hi; r.count++;
+    r.launches_after = g.launches;
+    return GGML_B200_OK;
 }
 
 }  // namespace b200
@@ -480,7 +494,7 @@ int ggml_b200_set_tuning(const char * key, int value) {
     else if (!strcmp(key, "fused_ctas_per_sm")) { if (value < 1 || value > 16) return GGML_B200_ERR_ARG; g.tune.fused_ctas_per_sm = value; }
     else if (!strcmp(key, "skip_quantize")) { g.tune.skip_quantize = value != 0; }
     else if (!strcmp(key, "host_fast"))    { g.tune.host_fast = value != 0; }
-    else if (!strcmp(key, "overlap_same_src")) { g.tune.overlap_same_src = value != 0; g.run.count = 0; }
+    else if (!strcmp(key, "overlap_same_src")) { g.tune.overlap_same_src = value != 0; g.run.count = 0; g.runN.count = 0; }
     else if (!strcmp(key, "p2p_gather"))   { comm_set_p2p(value); }
     else return gemm_set_tuning(key, value);
     return GGML_B200_OK;

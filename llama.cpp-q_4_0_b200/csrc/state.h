@@ -69,6 +69,9 @@ struct Ctx {
     // the run of n = 1 fused launches that read the same x (overlap_same_src): the ops still possibly in flight
     struct { const float * x = nullptr; int64_t K = 0; cudaStream_t stream = nullptr; uint64_t launches_after = 0;
              int count = 0; const float * y_lo[8]; const float * y_hi[8]; const ggml_b200_weight * head = nullptr; } run;
+    // the same for n > 1: ops that share src1 reuse the quantized activations of the run's first op
+    struct { const float * x = nullptr; int64_t K = 0, n = 0; size_t nb11 = 0; cudaStream_t stream = nullptr; uint64_t launches_after = 0;
+             int count = 0; const float * y_lo[8]; const float * y_hi[8]; } runN;
     char err[512] = {0};
 };
 
@@ -103,7 +106,7 @@ bool gemm_available(const ggml_b200_weight * w);
 int  gemm_prepare_weight(ggml_b200_weight * w);
 void gemm_release_weight(ggml_b200_weight * w);
 // y: first output element of this shard (column 0), ldy in floats; S != nullptr: also dump S_b
-int  launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int * S);
+int  launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int * S, int independent = 0);
 
 }  // namespace b200
 

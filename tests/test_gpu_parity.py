@@ -360,6 +360,44 @@ def test_same_src1_ops_overlap_without_changing_results(b200, port, ref):
         w.free()
 
 
+@pytest.mark.parametrize("n", [5, 48, 200])
+def test_same_src1_batched_ops_reuse_quantized_activations(b200, port, ref, n):
+    """n > 1 with overlap_same_src: ops that share src1 skip kernel 1 (the activations of the run's first op are
+    reused) and, on the tensor-core path, start without waiting for their predecessor.  Same chain as the n = 1
+    test, run back to back with and without the key: bit-identical buffers, correct against the oracle."""
+    K = M = 1024
+    Ws = [make_weights(port, ref, M, K, 60 + i) for i in range(5)]
+    ws = [b200.Weight(W) for W in Ws]
+    x0 = make_x(port, n, K, 91)
+
+    def run(overlap):
+        b200.set_tuning("overlap_same_src", overlap)
+        xd = b200.DevBuf.from_numpy(x0)
+        yd = [b200.DevBuf(n * M * 4) for _ in range(5)]
+        for rep in range(10):
+            for i in (0, 1, 2):
+                b200.mul_mat_dev(ws[i], xd.ptr, n, yd[i].ptr)         # same src1, distinct dst
+            b200.mul_mat_dev(ws[3], yd[1].ptr, n, yd[3].ptr)          # consumes a member: new x, must re-quantize
+            b200.mul_mat_dev(ws[4], yd[1].ptr, n, yd[4].ptr)          # same src1 as the previous op
+            b200.mul_mat_dev(ws[4], yd[1].ptr, n, yd[4].ptr)          # same dst again: no overlap with its twin
+        b200.synchronize()
+        return [y.to_numpy(np.float32, (n, M)) for y in yd]
+
+    try:
+        serial = run(0)
+        overlapped = run(1)
+    finally:
+        b200.set_tuning("overlap_same_src", 0)
+    for i in range(5):
+        assert np.array_equal(serial[i], overlapped[i]), f"buffer {i} differs with overlap_same_src"
+    for i in (0, 1, 2):
+        assert_close(serial[i], oracle_Y(port, ref, Ws[i], x0))
+    assert_close(serial[3], oracle_Y(port, ref, Ws[3], serial[1]))
+    assert_close(serial[4], oracle_Y(port, ref, Ws[4], serial[1]))
+    for w in ws:
+        w.free()
+
+
 # ---------------------------------------------------------------------------- weight-side codec (SURVEY 8f-3)
 def test_quantize_q4_0_golden_and_edges_bit_exact(b200, golden):
     """quantize_row_q4_0 (ggml.c:918-957) on the device: the reference test's cos vector and the edge rows (sign of d
