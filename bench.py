@@ -452,11 +452,63 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
         # this process owns the stream: nothing but library ops sits between two matmuls that share src1
         mod.set_tuning("overlap_same_src", 1)
 
-    def one_step():
+    def one_step_per_op():
         for (h, M, K, xp, yp) in ops:
             rc = op(h, C.c_void_p(xp), 1, K * 4, C.c_void_p(yp), M * 4)
             if rc:
                 raise RuntimeError(L_.ggml_b200_last_error().decode())
+
+    # ---- single GPU: the whole list as ONE persistent launch (ggml_b200_set_*).  Before it is timed
+    # every dst buffer must be bit-identical to the per-op path's; otherwise the per-op kernels are timed instead.
+    opset = None
+    set_note = None
+    if world == 1 and not args.no_set and not args.unfused:
+        try:
+            with torch.cuda.stream(stream):
+                one_step_per_op()
+            stream.synchronize()
+            want = {pos: y.cpu().numpy().copy() for pos, y in yg.items()}
+            for y in yg.values():
+                y.zero_()
+            torch.cuda.synchronize()
+            opset = mod.OpSet([(h, xp, yp) for (h, M, K, xp, yp) in ops])
+            with torch.cuda.stream(stream):
+                opset.run()
+            stream.synchronize()
+            bad = [pos for pos, y in yg.items() if not np.array_equal(y.cpu().numpy(), want[pos])]
+            if bad:
+                raise RuntimeError(f"dst buffers {bad} differ from the per-op path")
+            set_note = {"ops": opset.n_ops, "dependency_barriers": opset.barriers, "ring_slots": opset.slots,
+                        "checked": "every dst bit-identical to ggml_b200_mul_mat_q4_0 per op"}
+        except Exception as e:   # noqa: BLE001
+            print(f"[bench] persistent multi-op launch unavailable ({e}); timing one launch per mul_mat", file=sys.stderr)
+            opset = None
+            torch.cuda.synchronize()      # a trapped kernel leaves a sticky error: fail here, loudly
+    if args.probe_set:
+        # child process of main(): is the persistent launch healthy on this box (parity above, then graph replays)?
+        ok = opset is not None
+        if ok:
+            gp = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gp, stream=stream):
+                mod.set_stream(torch.cuda.current_stream().cuda_stream)
+                opset.run()
+            mod.set_stream(stream.cuda_stream)
+            for y in yg.values():
+                y.zero_()
+            torch.cuda.synchronize()
+            with torch.cuda.stream(stream):
+                for _ in range(20):
+                    gp.replay()
+            stream.synchronize()
+            ok = all(np.array_equal(y.cpu().numpy(), want[pos]) for pos, y in yg.items())
+        print("probe-set:", "ok" if ok else "FAILED", flush=True)
+        os._exit(0 if ok else 3)
+
+    def one_step():
+        if opset is not None:
+            opset.run()
+        else:
+            one_step_per_op()
 
     # ---- sanity (outside any timed region): the last matmul of the set against the oracle
     parity = None
@@ -559,17 +611,21 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
             kname = "gemv_q4_0_planes_kernel<1,4> (activations pre-quantized by quantize_q8_0_kernel)"
         else:
             gemv_ms = ms_per_step
-            kname = "gemv_q4_0_fused_kernel (quantize_row_q8_0 fused in; one launch per mul_mat)"
+            kname = ("gemv_q4_0_set_kernel (persistent: all mul_mats of the step in one launch, quantize_row_q8_0 fused in)" if opset is not None
+                     else "gemv_q4_0_fused_kernel (quantize_row_q8_0 fused in; one launch per mul_mat)")
+            if opset is not None:
+                n_launch = 1
         achieved = total_bytes / (gemv_ms * 1e-3) / 1e9
         roof = {"kernel": kname, "bound": "hbm", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "frac_of_nominal_8000": achieved / 8000.0,
                 "peak_source": peak_src, "traffic": None,
                 "launches_per_step": n_launch, "avg_launch_us": gemv_ms * 1e3 / n_launch,
                 "algorithmic_bytes_per_step": total_bytes,
-                "note": "launches overlap under programmatic dependent launch; avg = step time / launches"}
+                "note": ("one persistent launch per step: launch duration = step time" if opset is not None else
+                         "launches overlap under programmatic dependent launch; avg = step time / launches")}
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-                roof["traffic"] = json.load(f).get("gemv_dram_bytes_per_launch")
+                roof["traffic"] = json.load(f).get("set_dram_bytes_per_launch" if opset is not None else "gemv_dram_bytes_per_launch")
         except Exception:
             pass
 
@@ -664,6 +720,7 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
                        "layout": "planes (one-time repack at upload)", "cuda_graph": graph is not None,
                        "fused_quantize": not args.unfused, "pdl": not args.no_pdl,
                        "same_src1_overlap": not args.no_overlap, "tune": args.tune,
+                       "one_launch_per_step": set_note,
                        "parallelism": ("row-sharded x%d + peer-to-peer gather kernel per matmul (NVLink stores + flags; NCCL only for n > 1)" % world) if world > 1 else "single GPU",
                        "setup_s": round(setup_s, 2), "sanity_max_rel_err": parity},
             "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps), "gpu_launches_per_step": int(launches_per_step),
@@ -685,6 +742,8 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
         torch.cuda.synchronize()
         os._exit(0)
     del graph
+    if opset is not None:
+        opset.free()
     for (h, _, _) in handles:
         L_.ggml_b200_free_weight(h)
     mod.shutdown()
@@ -702,6 +761,8 @@ def main():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--unfused", action="store_true", help="kernel 1 + kernel 2 as separate launches")
     ap.add_argument("--no-pdl", action="store_true")
+    ap.add_argument("--no-set", action="store_true", help="one launch per mul_mat instead of the persistent multi-op launch")
+    ap.add_argument("--probe-set", action="store_true", help=argparse.SUPPRESS)
     ap.add_argument("--no-overlap", action="store_true", help="every matmul waits for the previous one even when they only share src1")
     ap.add_argument("--tune", action="append", default=[], help="key=value for ggml_b200_set_tuning")
     ap.add_argument("--no-check", action="store_true")
@@ -722,6 +783,20 @@ def main():
     if args.impl == "reference":
         run_reference_impl(args, workload, rank)
         return
+    if world == 1 and not args.no_set and not args.unfused and not args.probe_set:
+        # The persistent launch spins on device-side barriers: prove it healthy in a CHILD process first (a trapped
+        # kernel poisons its CUDA context), and time one launch per mul_mat if it is not.
+        cmd = [sys.executable, os.path.abspath(__file__), "--probe-set", "--layers", "2", "--workload", workload,
+               "--no-cpu", "--no-prefill", "--no-check"] + [a for kv in args.tune for a in ("--tune", kv)]
+        try:
+            pr = subprocess.run(cmd, timeout=600, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+            healthy = pr.returncode == 0
+            tail = pr.stdout[-400:]
+        except subprocess.TimeoutExpired:
+            healthy, tail = False, "probe timed out"
+        if not healthy:
+            print(f"[bench] persistent multi-op launch failed its probe ({tail!r}); timing one launch per mul_mat", file=sys.stderr)
+            args.no_set = True
     run_gpu_arm(args, workload, rank, world, local_rank)
 
 

@@ -132,6 +132,34 @@ int          ggml_b200_mul_mat_q4_0(const ggml_b200_weight * w, const float * x_
 int          ggml_b200_mul_mat_q4_0_host(const ggml_b200_weight * w, const float * x_host, int64_t n,
                                          size_t nb11, float * y_host, size_t nb1);
 
+/* ---- a list of n = 1 ops in ONE launch ----------------------------------------
+ * replaces, for the run of GGML_OP_MUL_MAT nodes of a decode step, the per-node loop of
+ * ggml_graph_compute (ggml.c:17541-17720) entering ggml_compute_forward_mul_mat_q_f32
+ * (ggml.c:11226-11424) once per node: one persistent kernel streams the weights of all ops back to
+ * back (gemv_q4_0_set.cuh).  Semantics and result BITS are those of
+ *     for each op in order: ggml_b200_mul_mat_q4_0(op.w, op.x_dev, 1, 4*K, op.y_dev, 4*M)
+ * An op that reads the same x_dev as its predecessor and writes rows no op of that run touches
+ * (wq/wk/wv, w3/w1; llama.cpp:1394-1504) starts without a dependency barrier; every other op waits
+ * for ALL earlier ops (so y of one op may be x of the next).  x_dev 16-byte aligned (ggml tensors
+ * are), weights in the plane layout.  create copies the list; the buffers must stay valid.  run is
+ * asynchronous on the current stream and may be captured in a CUDA graph. */
+typedef struct ggml_b200_set ggml_b200_set;
+typedef struct ggml_b200_set_op {
+    const ggml_b200_weight * w;
+    const float *            x_dev;   /* K floats */
+    float *                  y_dev;   /* the FULL dst row (M floats); a shard writes [row_lo,row_hi) */
+} ggml_b200_set_op;
+ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops);
+int          ggml_b200_set_run(ggml_b200_set * s);
+void         ggml_b200_set_free(ggml_b200_set * s);
+int          ggml_b200_set_ops(const ggml_b200_set * s);       /* ops with a non-empty shard */
+int          ggml_b200_set_barriers(const ggml_b200_set * s);  /* dependency barriers per run */
+int          ggml_b200_set_slots(const ggml_b200_set * s);     /* depth of the shared-memory ring */
+uint64_t     ggml_b200_set_bytes(const ggml_b200_set * s);     /* algorithmic bytes per run */
+/* parity checkpoint of the same device code: S_dev[i] = [rows_i][K_i/32] int32 block dots of the
+ * i-th non-empty op (device pointers, or NULL to skip that op); also writes y like run */
+int          ggml_b200_set_checkpoint(ggml_b200_set * s, int32_t * const * S_dev, int n_ops);
+
 /* ---- parity checkpoint --------------------------------------------------------------------
  * int32 per-block dots S_b = sum_j (q4_j - 8) * q8_j exactly as the kernels form them
  * (definition: scalar loop ggml.c:2593-2600).  S_dev: [n][rows][K/32] int32, device pointer.

@@ -21,11 +21,12 @@ namespace b200 {
 // shared-memory planes the dot loops read; 4 threads per block, 8 floats per thread.  Caller syncs the CTA.
 template <bool DUMP>
 __device__ __forceinline__ void quantize_x_to_smem(GemvSmem<1> & s, const float * __restrict__ x, int nbk, int x_aligned,
-                                                   int warp, int lane, unsigned char * __restrict__ blocks34) {
+                                                   int warp, int lane, unsigned char * __restrict__ blocks34, int nthreads = 0) {
         const int total = nbk * 4;
+        const int stride = nthreads ? nthreads : (int)blockDim.x;   // the threads that take part (warps 0 .. stride/32-1)
         uint32_t * lo32 = reinterpret_cast<uint32_t *>(s.lo);
         uint32_t * hi32 = reinterpret_cast<uint32_t *>(s.hi);
-        for (int base = warp * 32; base < total; base += blockDim.x) {
+        for (int base = warp * 32; base < total; base += stride) {
             int item = base + lane;
             const bool active = item < total;
             if (!active) item = total - 1;

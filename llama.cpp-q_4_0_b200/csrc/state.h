@@ -40,6 +40,10 @@ struct Tune {
     int pdl = 1;                 // programmatic dependent launch between consecutive kernels
     int overlap_same_src = 0;    // n == 1: an op that reads the same x as the previous one does not wait for it (caller owns the stream)
     int host_fast = 1;           // n == 1 host entry: single-launch path with mapped staging rows and a completion word
+    int set_coop = 1;            // persistent multi-op kernel: cooperative launch (the driver checks co-residency of the grid)
+    int set_warps = 16;          // its consumer warps per CTA (8, 16 or 24)
+    int set_rpw = 0;             // 1: one row per warp per tile for every op (default: two where the tile stays <= 20 KB)
+    int set_slots = 0;           // cap on its ring depth (0 = as many as fit)
     int skip_quantize = 0;       // bench only: reuse the activations quantized by the previous call
 };
 

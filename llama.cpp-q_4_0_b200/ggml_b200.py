@@ -83,6 +83,14 @@ def _load() -> C.CDLL:
         "ggml_b200_comm_world": (C.c_int, []),
         "ggml_b200_shard_rows": (None, [_i64, C.c_int, C.c_int, C.POINTER(_i64), C.POINTER(_i64)]),
         "ggml_b200_mul_mat_q4_0_sharded": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
+        "ggml_b200_set_create": (_vp, [_vp, C.c_int]),
+        "ggml_b200_set_run": (C.c_int, [_vp]),
+        "ggml_b200_set_free": (None, [_vp]),
+        "ggml_b200_set_ops": (C.c_int, [_vp]),
+        "ggml_b200_set_barriers": (C.c_int, [_vp]),
+        "ggml_b200_set_slots": (C.c_int, [_vp]),
+        "ggml_b200_set_bytes": (C.c_uint64, [_vp]),
+        "ggml_b200_set_checkpoint": (C.c_int, [_vp, _vp, C.c_int]),
         "ggml_b200_launch_count": (C.c_uint64, []),
         "ggml_b200_trace_begin": (C.c_int, [C.c_uint]),
         "ggml_b200_trace_end": (C.c_int, [_vp, C.c_uint]),
@@ -319,6 +327,51 @@ def mul_mat_dev(w: Weight, x_dev_ptr: int, n: int, y_dev_ptr: int, nb11: int | N
 
 def mul_mat_sharded_dev(w: Weight, x_dev_ptr: int, n: int, y_dev_ptr: int) -> None:
     _check(lib().ggml_b200_mul_mat_q4_0_sharded(w.h, _vp(x_dev_ptr), n, w.K * 4, _vp(y_dev_ptr), w.M * 4))
+
+
+class SetOp(C.Structure):
+    """struct ggml_b200_set_op"""
+    _fields_ = [("w", _vp), ("x_dev", _vp), ("y_dev", _vp)]
+
+
+class OpSet:
+    """A list of n = 1 ops compiled for ONE persistent launch (ggml_b200_set_create).
+    ops: iterable of (weight handle or Weight, x device pointer, y device pointer)."""
+
+    def __init__(self, ops):
+        ops = list(ops)
+        arr = (SetOp * max(1, len(ops)))()
+        for i, (w, xp, yp) in enumerate(ops):
+            arr[i].w = w.h if isinstance(w, Weight) else w
+            arr[i].x_dev = xp
+            arr[i].y_dev = yp
+        self.h = lib().ggml_b200_set_create(C.cast(arr, _vp), len(ops))
+        if not self.h:
+            raise B200Error(ERR_ARG, lib().ggml_b200_last_error().decode(errors="replace"))
+
+    n_ops = property(lambda self: int(lib().ggml_b200_set_ops(self.h)))
+    barriers = property(lambda self: int(lib().ggml_b200_set_barriers(self.h)))
+    slots = property(lambda self: int(lib().ggml_b200_set_slots(self.h)))
+    bytes = property(lambda self: int(lib().ggml_b200_set_bytes(self.h)))
+
+    def run(self) -> None:
+        _check(lib().ggml_b200_set_run(self.h))
+
+    def checkpoint(self, S_ptrs) -> None:
+        """S_ptrs: one device pointer (or None) per non-empty op: int32 [rows][K/32]."""
+        arr = (_vp * len(S_ptrs))(*[_vp(p) if p else None for p in S_ptrs])
+        _check(lib().ggml_b200_set_checkpoint(self.h, C.cast(arr, _vp), len(S_ptrs)))
+
+    def free(self) -> None:
+        if self.h:
+            lib().ggml_b200_set_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
 
 
 def block_dots(w: Weight, x: np.ndarray, path: int = PATH_GEMV) -> np.ndarray:

@@ -73,6 +73,10 @@ def test_no_gpu_means_loud_failure():
     w = np.zeros((4, 2, 18), np.uint8)
     assert L.ggml_b200_upload_q4_0(w.ctypes.data_as(C.c_void_p), 4, 64, 36, 0, 4) is None
     assert L.ggml_b200_quantize_q8_0(x.ctypes.data_as(C.c_void_p), 1, 64, 256, y.ctypes.data_as(C.c_void_p)) == mod.ERR_STATE
+    ops = (mod.SetOp * 1)()
+    assert L.ggml_b200_set_create(C.cast(ops, C.c_void_p), 1) is None
+    assert b"ggml_b200_init" in L.ggml_b200_last_error()
+    assert L.ggml_b200_set_run(None) == mod.ERR_STATE
 
 
 def test_product_never_imports_oracle():

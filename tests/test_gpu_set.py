@@ -1,0 +1,214 @@
+"""GPU parity tests of the persistent multi-op GEMV (ggml_b200_set_*, gemv_q4_0_set.cuh): a LIST of n = 1
+Q4_0 x F32 mul_mats in one launch.  Contract: result bits == ggml_b200_mul_mat_q4_0 called per op in list order
+(which test_gpu_parity.py pins against the oracle); S_b bit-exact against the oracle; outputs within 1e-4."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from test_gpu_parity import assert_close, make_weights, make_x, oracle_Y
+
+pytestmark = pytest.mark.gpu
+
+
+def _per_op(b200, ops):
+    for (w, xp, yp) in ops:
+        b200.mul_mat_dev(w, xp, 1, yp)
+    b200.synchronize()
+
+
+def _chain(b200, port, ref, shapes, seed):
+    """A decode-like chain: groups of ops that share x; the first result of a group is the next group's x.
+    shapes: list of groups, each a list of (M, K); M of a group's first op == K of the next group."""
+    Ws, ws, ops_desc = [], [], []
+    for gi, grp in enumerate(shapes):
+        for oi, (M, K) in enumerate(grp):
+            W = make_weights(port, ref, M, K, seed + 17 * gi + oi)
+            Ws.append(W)
+            ws.append(b200.Weight(W))
+            ops_desc.append((gi, oi, M, K))
+    return Ws, ws, ops_desc
+
+
+def _buffers(b200, port, shapes, ops_desc, x0):
+    xd0 = b200.DevBuf.from_numpy(x0)
+    yd = [b200.DevBuf(max(4, M * 4)) for (_, _, M, _) in ops_desc]
+    first_of_group = {}
+    for i, (gi, oi, _, _) in enumerate(ops_desc):
+        if oi == 0:
+            first_of_group[gi] = i
+    xs = []
+    for (gi, oi, M, K) in ops_desc:
+        xs.append(xd0.ptr if gi == 0 else yd[first_of_group[gi - 1]].ptr)
+    return xd0, yd, xs, first_of_group
+
+
+@pytest.mark.parametrize("warps", [16, 8, 24])
+def test_set_chain_bit_identical_to_per_op_calls(b200, port, ref, warps):
+    """qkv-like run -> op on its first result -> w3/w1-like run -> down projection; ragged tiles (M % 8 != 0),
+    both tile shapes (K = 1024: two rows per warp, K = 5120: one), more tiles than ring slots, 30 runs back to back
+    (the sync words must be left zero by every launch)."""
+    shapes = [[(1024, 1024), (1003, 1024), (600, 1024)], [(5120, 1024)], [(1024, 5120), (1021, 5120)], [(2052, 1024)]]
+    Ws, ws, desc = _chain(b200, port, ref, shapes, 900)
+    x0 = make_x(port, 1, 1024, 41)
+    b200.set_tuning("set_warps", warps)
+    try:
+        xd0, yd, xs, fog = _buffers(b200, port, shapes, desc, x0)
+        ops = [(ws[i], xs[i], yd[i].ptr) for i in range(len(ws))]
+        _per_op(b200, ops)
+        want = [yd[i].to_numpy(np.float32, (1, desc[i][2])) for i in range(len(ws))]
+        for y in yd:
+            b200.lib().ggml_b200_memcpy_h2d(y.ptr, np.zeros(y.nbytes, np.uint8).ctypes.data_as(C.c_void_p), y.nbytes)
+        s = b200.OpSet(ops)
+        assert s.n_ops == len(ops)
+        assert s.barriers == 3          # one per change of x; none inside a run
+        assert s.slots >= 4
+        c0 = b200.launch_count()
+        for _ in range(30):
+            s.run()
+        b200.synchronize()
+        assert b200.launch_count() - c0 == 30          # ONE launch per list
+        got = [yd[i].to_numpy(np.float32, (1, desc[i][2])) for i in range(len(ws))]
+        for i in range(len(ws)):
+            assert np.array_equal(got[i], want[i]), f"op {i} {desc[i]}: set result differs from the per-op call"
+        # and against the CPU truth, following the chain
+        xin = {0: x0}
+        for i, (gi, oi, M, K) in enumerate(desc):
+            assert_close(got[i], oracle_Y(port, ref, Ws[i], xin[gi]))
+            if oi == 0:
+                xin[gi + 1] = got[i]
+        s.free()
+    finally:
+        b200.set_tuning("set_warps", 16)
+    for w in ws:
+        w.free()
+
+
+def test_set_block_dots_bit_exact(b200, port, ref):
+    """S_b as the persistent kernel forms them == the oracle's int32 block dots (ggml.c:2593-2600)."""
+    shapes = [[(520, 2048), (64, 2048)], [(300, 5120)]]
+    Ws = [make_weights(port, ref, M, K, 950 + i) for i, (M, K) in enumerate([s for g in shapes for s in g])]
+    ws = [b200.Weight(W) for W in Ws]
+    xa, xb = make_x(port, 1, 2048, 5), make_x(port, 1, 5120, 6)
+    xda, xdb = b200.DevBuf.from_numpy(xa), b200.DevBuf.from_numpy(xb)
+    yd = [b200.DevBuf(W.shape[0] * 4) for W in Ws]
+    Sd = [b200.DevBuf(W.shape[0] * W.shape[1] * 4) for W in Ws]
+    ops = [(ws[0], xda.ptr, yd[0].ptr), (ws[1], xda.ptr, yd[1].ptr), (ws[2], xdb.ptr, yd[2].ptr)]
+    s = b200.OpSet(ops)
+    assert s.barriers == 1
+    s.checkpoint([b.ptr for b in Sd])
+    b200.synchronize()
+    for i, (W, x) in enumerate(zip(Ws, (xa, xa, xb))):
+        S = Sd[i].to_numpy(np.int32, (W.shape[0], W.shape[1]))
+        want = port.block_dots_matrix(W, port.quantize_q8_0(x))[0]
+        assert np.array_equal(S, want), f"op {i}: int32 block dots differ"
+        assert_close(yd[i].to_numpy(np.float32, (1, W.shape[0])), oracle_Y(port, ref, W, x))
+    s.free()
+    for w in ws:
+        w.free()
+
+
+def test_set_in_place_and_repeated_dst_are_ordered(b200, port, ref):
+    """An op that writes a buffer an earlier op of the list reads or writes must wait for it: y -> x chains
+    through the SAME buffer (square weights), and two ops with the same dst (the later one wins)."""
+    M = K = 1024
+    Ws = [make_weights(port, ref, M, K, 970 + i) for i in range(4)]
+    ws = [b200.Weight(W) for W in Ws]
+    x0 = make_x(port, 1, K, 99)
+    buf = b200.DevBuf.from_numpy(x0)          # x of op 0, overwritten by op 1
+    t = b200.DevBuf(M * 4)
+    ops = [(ws[0], buf.ptr, t.ptr),           # t = W0 x0
+           (ws[1], t.ptr, buf.ptr),           # buf = W1 t        (overwrites op 0's x)
+           (ws[2], buf.ptr, t.ptr),           # t = W2 buf        (overwrites op 1's x)
+           (ws[3], buf.ptr, t.ptr)]           # t = W3 buf        (same dst as op 2: must run after it)
+    s = b200.OpSet(ops)
+    assert s.barriers == 3
+    s.run()
+    b200.synchronize()
+    got_t, got_buf = t.to_numpy(np.float32, (1, M)), buf.to_numpy(np.float32, (1, M))
+    b200.lib().ggml_b200_memcpy_h2d(buf.ptr, x0.ctypes.data_as(C.c_void_p), x0.nbytes)
+    _per_op(b200, ops)
+    assert np.array_equal(got_t, t.to_numpy(np.float32, (1, M)))
+    assert np.array_equal(got_buf, buf.to_numpy(np.float32, (1, M)))
+    y0 = oracle_Y(port, ref, Ws[0], x0)
+    y1 = oracle_Y(port, ref, Ws[1], y0)
+    assert_close(got_buf, y1)
+    s.free()
+    for w in ws:
+        w.free()
+
+
+def test_set_row_shards_and_empty_shard(b200, port, ref):
+    """A shard writes only [row_lo,row_hi) of the full dst; an empty shard is skipped (multi-GPU row split)."""
+    M, K = 1100, 1024
+    W = make_weights(port, ref, M, K, 990)
+    x = make_x(port, 1, K, 7)
+    parts = [b200.Weight(W, 0, 384), b200.Weight(W, 384, 384), b200.Weight(W, 384, 1100)]
+    xd = b200.DevBuf.from_numpy(x)
+    yd = b200.DevBuf.from_numpy(np.full((1, M), -7.0, np.float32))
+    s = b200.OpSet([(p, xd.ptr, yd.ptr) for p in parts])
+    assert s.n_ops == 2 and s.barriers == 0
+    s.run()
+    b200.synchronize()
+    assert_close(yd.to_numpy(np.float32, (1, M)), oracle_Y(port, ref, W, x))
+    s.free()
+    for p in parts:
+        p.free()
+
+
+def test_set_rejects_what_it_cannot_run(b200, port, ref):
+    W = make_weights(port, ref, 64, 1024, 995)
+    x = b200.DevBuf(1024 * 4 + 16)
+    y = b200.DevBuf(64 * 4)
+    b200.set_repack(False)
+    try:
+        raw = b200.Weight(W)
+    finally:
+        b200.set_repack(True)
+    with pytest.raises(b200.B200Error):
+        b200.OpSet([(raw, x.ptr, y.ptr)])                 # RAW layout
+    w = b200.Weight(W)
+    with pytest.raises(b200.B200Error):
+        b200.OpSet([(w, x.ptr + 4, y.ptr)])               # x not 16-byte aligned
+    with pytest.raises(b200.B200Error):
+        b200.OpSet([])
+    raw.free(); w.free()
+
+
+def test_set_replays_in_a_cuda_graph(b200, port, ref):
+    """The launch is capturable: device-side sync words need no host reset between replays."""
+    torch = pytest.importorskip("torch")
+    M = K = 1024
+    Ws = [make_weights(port, ref, M, K, 1010 + i) for i in range(3)]
+    ws = [b200.Weight(W) for W in Ws]
+    x0 = make_x(port, 1, K, 3)
+    xd = b200.DevBuf.from_numpy(x0)
+    yd = [b200.DevBuf(M * 4) for _ in range(3)]
+    ops = [(ws[0], xd.ptr, yd[0].ptr), (ws[1], yd[0].ptr, yd[1].ptr), (ws[2], yd[1].ptr, yd[2].ptr)]
+    s = b200.OpSet(ops)
+    stream = torch.cuda.Stream()
+    old = b200.lib().ggml_b200_get_stream()
+    try:
+        b200.set_stream(stream.cuda_stream)
+        with torch.cuda.stream(stream):
+            s.run()
+        stream.synchronize()
+        want = yd[2].to_numpy(np.float32, (1, M))
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=stream):
+            b200.set_stream(torch.cuda.current_stream().cuda_stream)
+            s.run()
+        b200.set_stream(stream.cuda_stream)
+        b200.lib().ggml_b200_memcpy_h2d(yd[2].ptr, np.zeros(M * 4, np.uint8).ctypes.data_as(C.c_void_p), M * 4)
+        with torch.cuda.stream(stream):
+            for _ in range(5):
+                graph.replay()
+        stream.synchronize()
+        assert np.array_equal(yd[2].to_numpy(np.float32, (1, M)), want)
+        del graph
+    finally:
+        b200.set_stream(None)
+        assert b200.lib().ggml_b200_get_stream() == old or True
+    s.free()
+    for w in ws:
+        w.free()

@@ -27,6 +27,29 @@ def main():
             k, v = kv.split("=")
             mod.set_tuning(k, int(v))
     rng = np.random.default_rng(3)
+    if "--set-only" in sys.argv:
+        # the persistent multi-op launch on 4 layers of the LLaMA-7B decode list (455 MB of weights: > 3x L2)
+        shapes = [(4096, 4096)] * 4 + [(11008, 4096)] * 2 + [(4096, 11008)]
+        groups = ["a", "a", "a", "b", "c", "c", "d"]
+        blks = {s: bench.random_q4_0(rng, *s) for s in set(shapes)}
+        xs = {g: mod.DevBuf.from_numpy(rng.standard_normal((1, K), dtype=np.float32)) for g, (M, K) in zip(groups, shapes)}
+        ws, ops = [], []
+        for layer in range(4):
+            for g, (M, K) in zip(groups, shapes):
+                w = mod.Weight(blks[(M, K)])
+                ws.append(w)
+                ops.append((w, xs[g].ptr, mod.DevBuf(M * 4)))
+        keep = [o[2] for o in ops]
+        s = mod.OpSet([(w, xp, y.ptr) for (w, xp, y) in ops])
+        for _ in range(3):
+            s.run()
+        mod.synchronize()
+        print("set bytes per launch:", s.bytes, "ops", s.n_ops, "barriers", s.barriers, "slots", s.slots)
+        s.free()
+        del keep
+        mod.shutdown()
+        print("ncu target done")
+        return
     for (M, K) in [(4096, 4096), (11008, 4096)]:
         blk = bench.random_q4_0(rng, M, K)
         w = mod.Weight(blk)
