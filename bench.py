@@ -82,16 +82,49 @@ def load_binding():
     return mod
 
 
-def random_q4_0(rng, M, K):
+def random_q4_0(rng, M, K, scale=0.02):
     """random-init Q4_0 blocks: uniform nibbles, fp16 scale ~ |N(0, 0.02)| * 3 / 8 with random sign
-    (the scale a block of N(0, 0.02) weights gets from d = max / -8, ggml.c:932)."""
+    (the scale a block of N(0, 0.02) weights gets from d = max / -8, ggml.c:932).  scale = 0.6 / sqrt(K) gives a
+    matmul of gain ~1, so that a chain of 129 of them (chain_ops) stays in fp32 range."""
     nbk = K // 32
     blk = np.empty((M, nbk, 18), dtype=np.uint8)
     blk[:, :, 2:] = rng.integers(0, 256, size=(M, nbk, 16), dtype=np.uint8)
-    d = (0.02 * (2.0 + np.abs(rng.standard_normal((M, nbk), dtype=np.float32))) / 8.0)
+    d = (scale * (2.0 + np.abs(rng.standard_normal((M, nbk), dtype=np.float32))) / 8.0)
     d *= rng.choice(np.array([-1.0, 1.0], np.float32), size=(M, nbk))
     blk[:, :, :2] = d.astype(np.float16).view(np.uint8).reshape(M, nbk, 2)
     return blk
+
+
+def chain_ops(torch, handles, layer_shapes, L, x0=None):
+    """The decode list chained as the model chains it (llama.cpp:1394-1504 without the element-wise ops between the
+    matmuls): wq, wk, wv read the layer input; wo reads wq's result; w3, w1 read wo's; w2 reads w1's; the next layer reads
+    w2's; the output matmul reads the last layer's.  Every matmul has its own dst.  Works for any per-layer shape list
+    [(M, K)] * 7 laid out (attn x4, up/gate x2, down x1).  Returns ([(handle, x_ptr, y_ptr, y_tensor)], input tensor -- keep it alive)."""
+    assert len(layer_shapes) == 7
+    ops = []
+    first = handles[0]
+    h_in = x0 if x0 is not None else torch.randn((1, first[2]), dtype=torch.float32, device="cuda")
+    cur = h_in
+    n_layer_ops = L * 7
+    for idx, (h, M, K) in enumerate(handles):
+        y = torch.zeros((1, M), dtype=torch.float32, device="cuda")
+        if idx < n_layer_ops:
+            pos = idx % 7
+            if pos == 0:
+                layer_in = cur
+            src = {0: layer_in, 1: layer_in, 2: layer_in}.get(pos)
+            if pos == 3:
+                src = ops[idx - 3][3]          # wq's result
+            elif pos in (4, 5):
+                src = ops[idx - (pos - 3)][3]  # wo's result
+            elif pos == 6:
+                src = ops[idx - 1][3]          # w1's result (the second of the up/gate pair)
+                cur = y
+        else:
+            src = cur
+        assert src.shape[1] == K, (idx, src.shape, K)
+        ops.append((h, src.data_ptr(), y.data_ptr(), y))
+    return ops, h_in
 
 
 def peaks():
@@ -475,11 +508,23 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
             with torch.cuda.stream(stream):
                 opset.run()
             stream.synchronize()
-            bad = [pos for pos, y in yg.items() if not np.array_equal(y.cpu().numpy(), want[pos])]
-            if bad:
-                raise RuntimeError(f"dst buffers {bad} differ from the per-op path")
+            def set_check():
+                """K <= 4096: bits of the per-op kernel; K > 4096: four warp partials per row in a fixed order."""
+                exact = 0
+                for pos, y in yg.items():
+                    got = y.cpu().numpy()
+                    if np.array_equal(got, want[pos]):
+                        exact += 1
+                        continue
+                    K_pos = next(K for (h, M, K, xp, yp) in ops if yp == y.data_ptr())
+                    err = float(np.max(np.abs(got - want[pos])) / max(float(np.max(np.abs(want[pos]))), 1e-30))
+                    if K_pos <= 4096 or not err <= 1e-5:
+                        raise RuntimeError(f"dst buffer {pos} (K = {K_pos}) differs from the per-op path: max|dY|/max|Y| = {err:.3e}")
+                return exact
+            n_exact = set_check()
             set_note = {"ops": opset.n_ops, "dependency_barriers": opset.barriers, "ring_slots": opset.slots,
-                        "checked": "every dst bit-identical to ggml_b200_mul_mat_q4_0 per op"}
+                        "checked": f"{n_exact}/{len(yg)} dst buffers bit-identical to ggml_b200_mul_mat_q4_0 per op (all with K <= 4096), "
+                                   "the others within 1e-5 of max|y| (fixed-order four-warp sums)"}
         except Exception as e:   # noqa: BLE001
             print(f"[bench] persistent multi-op launch unavailable ({e}); timing one launch per mul_mat", file=sys.stderr)
             opset = None
@@ -500,7 +545,11 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
                 for _ in range(20):
                     gp.replay()
             stream.synchronize()
-            ok = all(np.array_equal(y.cpu().numpy(), want[pos]) for pos, y in yg.items())
+            try:
+                set_check()
+            except RuntimeError as e:
+                print(e, flush=True)
+                ok = False
         print("probe-set:", "ok" if ok else "FAILED", flush=True)
         os._exit(0 if ok else 3)
 

@@ -138,9 +138,10 @@ int          ggml_b200_mul_mat_q4_0_host(const ggml_b200_weight * w, const float
  * (ggml.c:11226-11424) once per node: one persistent kernel streams the weights of all ops back to
  * back (gemv_q4_0_set.cuh).  Semantics and result BITS are those of
  *     for each op in order: ggml_b200_mul_mat_q4_0(op.w, op.x_dev, 1, 4*K, op.y_dev, 4*M)
- * An op that reads the same x_dev as its predecessor and writes rows no op of that run touches
- * (wq/wk/wv, w3/w1; llama.cpp:1394-1504) starts without a dependency barrier; every other op waits
- * for ALL earlier ops (so y of one op may be x of the next).  x_dev 16-byte aligned (ggml tensors
+ * Ordering follows the DATA hazards between the ops: ops that share x_dev run back to back
+ * (wq/wk/wv, w3/w1; llama.cpp:1394-1504); an op whose x_dev is exactly the dst of one earlier op
+ * waits for that op's rows only (they travel as tagged words, no barrier); any other overlap of an
+ * op's x or dst with an earlier op's x or dst puts a grid-wide barrier in front of it.  x_dev 16-byte aligned (ggml tensors
  * are), weights in the plane layout.  create copies the list; the buffers must stay valid.  run is
  * asynchronous on the current stream and may be captured in a CUDA graph. */
 typedef struct ggml_b200_set ggml_b200_set;
@@ -153,12 +154,18 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops);
 int          ggml_b200_set_run(ggml_b200_set * s);
 void         ggml_b200_set_free(ggml_b200_set * s);
 int          ggml_b200_set_ops(const ggml_b200_set * s);       /* ops with a non-empty shard */
-int          ggml_b200_set_barriers(const ggml_b200_set * s);  /* dependency barriers per run */
+int          ggml_b200_set_barriers(const ggml_b200_set * s);  /* grid-wide dependency barriers per launch */
+int          ggml_b200_set_linked_runs(const ggml_b200_set * s); /* runs whose x is read from its producer op's tagged rows */
 int          ggml_b200_set_slots(const ggml_b200_set * s);     /* depth of the shared-memory ring */
 uint64_t     ggml_b200_set_bytes(const ggml_b200_set * s);     /* algorithmic bytes per run */
 /* parity checkpoint of the same device code: S_dev[i] = [rows_i][K_i/32] int32 block dots of the
  * i-th non-empty op (device pointers, or NULL to skip that op); also writes y like run */
 int          ggml_b200_set_checkpoint(ggml_b200_set * s, int32_t * const * S_dev, int n_ops);
+/* profiling aid: one synchronous run of an instrumented build of the same kernel; out_host[cta*16 + i] = clock64
+ * totals {whole kernel, a consumer warp waiting for weights, in dependency barriers, quantizing x, the producer
+ * waiting for a free ring slot, that warp from data ready to y stored, its tiles, 0, and of the barriers: CTA
+ * sync, release, polling, acquire fence, 0...}.  Returns the number of CTAs written (<= max_ctas) or an error. */
+int          ggml_b200_set_profile(ggml_b200_set * s, long long * out_host, int max_ctas);
 
 /* ---- parity checkpoint --------------------------------------------------------------------
  * int32 per-block dots S_b = sum_j (q4_j - 8) * q8_j exactly as the kernels form them

@@ -10,38 +10,52 @@
 //     Weights are immutable, so the producer never waits for an op to finish: while the consumers sit in a
 //     dependency barrier or quantize the next x, up to ~190 KB per SM (28 MB per GPU) of the NEXT ops' weights
 //     are already in flight, and HBM never idles across op boundaries;
-//   * W consumer warps in groups of 4; slot j belongs to group j % NG.  A tile is R = 4*RPW consecutive weight rows
-//     (nibble plane rows + scale plane rows, both contiguous in the plane layout); warp i of the group owns rows
-//     i*RPW .. i*RPW+RPW-1 of the tile, lane l owns blocks l, l+32, ... of its rows: the arithmetic, its order and
-//     therefore the result bits are those of gemv_q4_0_fused_kernel (S_b exact on IDP.4A, per-lane fmaf chain
-//     over b, xor-shuffle tree);
+//   * W consumer warps in groups of 4; slot j belongs to group j % NG.  A tile is R consecutive weight rows
+//     (nibble plane rows + scale plane rows, both contiguous in the plane layout):
+//       K <= 4096 (WPR = 1): R = 8, warp i of the group owns rows 2i, 2i+1, lane l owns blocks l, l+32, ... of them
+//                            -- the arithmetic, its order and therefore the result BITS are those of
+//                            gemv_q4_0_fused_kernel (S_b exact on IDP.4A, per-lane fmaf chain over b, xor-shuffle tree);
+//       K >  4096 (WPR = 4): R = 4, the group's 128 lanes share every row (lane t owns blocks t, t+128, ...), the
+//                            four warp partials are added in a fixed order (deterministic; S_b exact; fp32 order
+//                            differs from the per-op kernel like every GPU order differs from the CPU's);
+//     in both shapes a lane's slice of the quantized x (<= 6 blocks) lives in REGISTERS for the whole run of ops
+//     that share x, so shared memory carries the weights only (18 B written by the TMA engine + 18 B read per
+//     block): the consumers were bound by the shared-memory pipe when x was re-read per row (v1, 40 B more per
+//     block and row pair; profiles/r01_set_sweep_v1.log);
 //   * tiles are dealt round-robin over the CTAs CONTINUING across ops, so the per-op remainder does not idle SMs;
 //   * ops that read the same x as their predecessor and write rows nobody of the run touches (wq/wk/wv, w3/w1)
 //     run back to back; every other op starts with a grid-wide barrier (all its predecessors complete, results
-//     visible) and a re-quantization of x into the shared-memory planes (quantize_row_q8_0 contract,
-//     ggml.c:1192-1250, same code as the fused kernel).  Semantics == calling ggml_b200_mul_mat_q4_0 per op in order.
+//     visible) and a re-quantization of x (quantize_row_q8_0 contract, ggml.c:1192-1250, same arithmetic as the
+//     fused kernel).  Semantics == calling ggml_b200_mul_mat_q4_0 per op in order.
 // Roofline: HBM; algorithmic bytes per launch = sum over ops of 18*M*K/32 + 4*K + 4*M.
 #pragma once
 #include "common.cuh"
 #include "gemv_q4_0.cuh"
-#include "gemv_q4_0_fused.cuh"
 #include "ptx.cuh"
+#include "quantize_q8_0.cuh"
 
 namespace b200 {
 
-constexpr int SET_WPG = 4;            // consumer warps per group (= rows of a tile / RPW)
+constexpr int SET_WPG = 4;            // consumer warps per group
 constexpr int SET_MAX_SLOTS = 16;
+constexpr int SET_MAX_GROUPS = 6;
+constexpr int SET_RED_BYTES = 2 * SET_MAX_GROUPS * 16 * 4;   // cross-warp partials: [parity][group][row 4][warp 4] floats
+constexpr int SET_BAR_BYTES = 2 * SET_MAX_SLOTS * 8;
+constexpr int SET_MAX_NBK_WPR1 = 128; // blocks per row a single warp keeps x for (4 per lane)
+constexpr int SET_MAX_NBK = 768;      // 6 per lane of a 4-warp team (K <= 24576)
 
 enum { SET_OP_BARRIER = 1, SET_OP_QUANT = 2 };
 
-struct SetOp {                        // 64 bytes, device resident, read-only during the launch
+struct SetOp {                        // 80 bytes, device resident, read-only during the launch
     const uint4 * wq;                 // nibble plane of this shard [rows][nbk]
     const unsigned short * wd;        // scale plane [rows][nbk] (fp16 bits)
     const float * x;                  // K floats, 16-byte aligned
     float * y;                        // first output row of this shard
     int * S;                          // parity checkpoint: [rows][nbk] int32 block dots, or nullptr
+    unsigned long long * ytag;        // this op's rows as tagged words (launch number << 32 | bits of y), when a later op of the list reads them as x
+    const unsigned long long * xtag;  // ... the tagged rows this op's x is read from, or nullptr: plain x
     int rows, nbk;
-    int rpw;                          // rows per warp per tile (1 or 2); tile = 4*rpw rows
+    int tile_rows;                    // R: 8 (nbk <= 128) or 4
     int ntiles;
     int first_mod;                    // (tiles of all earlier ops) % grid: CTA c takes tiles (c - first_mod) mod grid, + grid, ...
     int flags;                        // SET_OP_BARRIER | SET_OP_QUANT
@@ -50,15 +64,42 @@ struct SetOp {                        // 64 bytes, device resident, read-only du
 struct SetSync {                      // device resident, zero between launches
     unsigned arrived;                 // dependency barriers: monotonically counted arrivals of this launch
     unsigned done;                    // CTAs that finished the list; the last one re-zeroes both words
+    unsigned epoch;                   // launches completed: launch number e = epoch + 1 tags the staging words
+    unsigned pad;
 };
 
-__device__ __forceinline__ unsigned ld_acquire_gpu_u32(const unsigned * p) {
+__device__ __forceinline__ void st_relaxed_gpu_b64(unsigned long long * p, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.b64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_gpu_b64(const unsigned long long * p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.b64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void ld_relaxed_gpu_v2b64(const unsigned long long * p, unsigned long long & a, unsigned long long & b) {
+    asm volatile("ld.relaxed.gpu.global.v2.b64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+
+__device__ __forceinline__ unsigned ld_relaxed_gpu_u32(const unsigned * p) {
     unsigned v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
 __device__ __forceinline__ void red_release_gpu_add_u32(unsigned * p, unsigned v) {
     asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+
+// the producer's wait for a free slot: it is usually a long wait (the ring is full most of the time), and a hot
+// try_wait loop would take issue slots from the consumer warps of its scheduler
+__device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity) {
+    unsigned long long t0 = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        __nanosleep(128);
+        const unsigned long long t1 = gtime();
+        if (t0 == 0) t0 = t1;
+        if (t1 - t0 > 10000000000ull) __trap();
+    }
 }
 
 template <int NCONS>
@@ -66,150 +107,421 @@ __device__ __forceinline__ void set_consumer_sync() {
     asm volatile("bar.sync 1, %0;" ::"n"(NCONS) : "memory");
 }
 
-// all consumer threads of every CTA; `target` = arrivals that complete this barrier
-template <int NCONS>
-__device__ __forceinline__ void set_grid_barrier(SetSync * sync, unsigned target) {
-    set_consumer_sync<NCONS>();       // this CTA's y stores of the finished ops are issued
+// All consumer threads of every CTA; `target` = arrivals that complete this barrier.  One release (the CTA's y
+// stores, ordered before thread 0 by the CTA barrier, become visible before the count), relaxed polls, one
+// acquire fence: every GPU-scope fence costs an L2 round trip under a saturated memory system, so there are
+// exactly two on the critical path.
+template <int NCONS, bool PROF>
+__device__ __forceinline__ void set_grid_barrier(SetSync * sync, unsigned target, long long * tp) {
+    long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+    if (PROF) c0 = clock64();
+    set_consumer_sync<NCONS>();
     if (threadIdx.x == 0) {
-        __threadfence();
+        if (PROF) c1 = clock64();
         red_release_gpu_add_u32(&sync->arrived, 1u);
+        if (PROF) c2 = clock64();
         unsigned long long t0 = 0;
-        while ((int)(ld_acquire_gpu_u32(&sync->arrived) - target) < 0) {
+        while ((int)(ld_relaxed_gpu_u32(&sync->arrived) - target) < 0) {
             const unsigned long long t1 = gtime();
             if (t0 == 0) t0 = t1;
             if (t1 - t0 > 10000000000ull) __trap();   // a CTA of the grid is not resident / died: fail, do not hang
         }
-        __threadfence();
+        if (PROF) c3 = clock64();
+        fence_acq_rel_gpu();
+        if (PROF) { tp[0] += c1 - c0; tp[1] += c2 - c1; tp[2] += c3 - c2; tp[3] += clock64() - c3; }
     }
     set_consumer_sync<NCONS>();
 }
 
-template <int RPW, bool DUMP>
-__device__ __forceinline__ void set_tile_rows(const unsigned char * __restrict__ nib, const unsigned char * __restrict__ sc,
-                                              const GemvSmem<1> & xs, int nbk, int lane, int nvalid, float * __restrict__ yrow,
-                                              int * __restrict__ Srow, uint32_t empty_bar) {
-    float acc[RPW];
+// kernel 1 inside the CTA (quantize_row_q8_0, AVX2 contract ggml.c:1192-1250; arithmetic of quantize_x_to_smem):
+// 4 threads per block, 8 floats per thread, up to 3 items per thread with all their loads issued first.  x may have
+// been written by other SMs during this launch: ld.global.cg.
+// 8 consecutive elements of x out of tagged words: a word whose upper half is this launch's number IS the datum
+// (8-byte accesses are single-copy atomic), so the reader needs neither a flag nor a fence -- one L2 round trip
+// after the producer's store has landed.
+__device__ __forceinline__ void set_load_tagged8(const unsigned long long * __restrict__ w, unsigned long long tag, float (&v)[8]) {
+    unsigned long long t0 = 0;
+    for (;;) {
+        // all eight words per poll: the poll that finds them complete has already fetched them (no second round trip)
+        unsigned long long a[8];
 #pragma unroll
-    for (int k = 0; k < RPW; k++) acc[k] = 0.0f;
-#pragma unroll 2
-    for (int b = lane; b < nbk; b += 32) {
-        const int2 ds = xs.ds[b];
-        const uint4 ylo = xs.lo[b], yhi = xs.hi[b];
-        const float dxf = __int_as_float(ds.x);
+        for (int i = 0; i < 4; i++) ld_relaxed_gpu_v2b64(w + 2 * i, a[2 * i], a[2 * i + 1]);
+        unsigned long long bad = 0;
 #pragma unroll
-        for (int k = 0; k < RPW; k++) {
-            const uint4 q = *reinterpret_cast<const uint4 *>(nib + ((size_t)k * nbk + b) * 16);
-            const unsigned short dh = *reinterpret_cast<const unsigned short *>(sc + ((size_t)k * nbk + b) * 2);
-            const int sb = block_dot_q4_q8_fast(q, ylo, yhi, ds.y);
-            if (DUMP) { if (Srow != nullptr && k < nvalid) Srow[(size_t)k * nbk + b] = sb; }
-            acc[k] = fmaf((float)sb, half_bits_to_float(dh) * dxf, acc[k]);
-        }
-    }
-    // the slot's bytes of this warp's rows are in registers: hand the slot back before the reduction
-    __syncwarp();
-    if (lane == 0) mbar_arrive(empty_bar);
-#pragma unroll
-    for (int k = 0; k < RPW; k++) {
-        const float t = warp_sum(acc[k]);
-        if (lane == 0 && k < nvalid) yrow[k] = t;
+        for (int i = 0; i < 8; i++) { bad |= a[i] ^ tag; v[i] = __uint_as_float((unsigned)a[i]); }
+        if ((bad >> 32) == 0) return;
+        __nanosleep(20);
+        const unsigned long long t1 = gtime();
+        if (t0 == 0) t0 = t1;
+        if (t1 - t0 > 10000000000ull) __trap();      // the producer rows never arrive: fail, do not hang
     }
 }
 
-template <int W, bool DUMP>
+template <int NCONS>
+__device__ __forceinline__ void set_quantize_x(GemvSmem<1> & s, const float * __restrict__ x, const unsigned long long * __restrict__ xtag,
+                                               unsigned long long tag, int nbk, int tid) {
+    const int total = nbk * 4;
+    uint32_t * lo32 = reinterpret_cast<uint32_t *>(s.lo);
+    uint32_t * hi32 = reinterpret_cast<uint32_t *>(s.hi);
+    for (int base = 0; base < total; base += 3 * NCONS) {
+        float4 a[3], c[3];
+#pragma unroll
+        for (int p = 0; p < 3; p++) {
+            int item = base + p * NCONS + tid;
+            if (item >= total) item = total - 1;
+            a[p] = make_float4(0.f, 0.f, 0.f, 0.f); c[p] = a[p];
+            if (xtag == nullptr) {
+                a[p] = __ldcg(reinterpret_cast<const float4 *>(x + 8 * item));
+                c[p] = __ldcg(reinterpret_cast<const float4 *>(x + 8 * item) + 1);
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < 3; p++) {
+            const int item = base + p * NCONS + tid;
+            if (base + p * NCONS >= total) break;                       // warp-uniform (NCONS and total are multiples of 4; see below)
+            const bool active = item < total;
+            float v[8] = {a[p].x, a[p].y, a[p].z, a[p].w, c[p].x, c[p].y, c[p].z, c[p].w};
+            if (xtag != nullptr) set_load_tagged8(xtag + 8 * (active ? item : total - 1), tag, v);      // (one item at a time: the wait is here)
+            float amax = 0.0f;
+#pragma unroll
+            for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v[i]));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+            const float d  = __fdiv_rn(amax, 127.0f);
+            const float id = (amax != 0.0f) ? __fdiv_rn(127.0f, amax) : 0.0f;
+            const __half dhalf = __float2half_rn(d);
+            int qq[8];
+            int sum = 0;
+#pragma unroll
+            for (int i = 0; i < 8; i++) { qq[i] = q8_round(v[i], id); sum += qq[i]; }
+            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+            const uint32_t w0 = (uint32_t)(qq[0] & 0xFF) | ((uint32_t)(qq[1] & 0xFF) << 8) |
+                                ((uint32_t)(qq[2] & 0xFF) << 16) | ((uint32_t)(qq[3] & 0xFF) << 24);
+            const uint32_t w1 = (uint32_t)(qq[4] & 0xFF) | ((uint32_t)(qq[5] & 0xFF) << 8) |
+                                ((uint32_t)(qq[6] & 0xFF) << 16) | ((uint32_t)(qq[7] & 0xFF) << 24);
+            if (active) {
+                const int b = item >> 2, part = item & 3;
+                uint32_t * dst = (part & 2) ? hi32 : lo32;
+                *reinterpret_cast<uint2 *>(dst + 4 * b + 2 * (part & 1)) = make_uint2(w0, w1);
+                if (part == 0) s.ds[b] = make_int2(__float_as_int(__half2float(dhalf)), -8 * sum);
+            }
+        }
+    }
+}
+
+// what a consumer needs of an op; loaded one op AHEAD (an L2 round trip under a saturated memory system costs
+// ~0.7 us, and the ops of a list are walked serially)
+struct SetOpC {
+    const float * x;
+    float * y;
+    int * S;
+    unsigned long long * ytag;
+    const unsigned long long * xtag;
+    int rows, nbk, ntiles, first_mod, flags;
+};
+// the same, 48 bytes, as staged in shared memory at kernel start when the list fits (SET_MAX_TABLE_BYTES): the
+// consumers then walk the list without touching global memory at all
+struct __align__(16) SetOpS {
+    const float * x;
+    float * y;
+    unsigned long long * ytag;
+    const unsigned long long * xtag;
+    int rows, nbk, ntiles, fm_flags;   // first_mod | flags << 16
+};
+constexpr int SET_MAX_TABLE_BYTES = 32 * 1024;
+
+template <bool DUMP>
+__device__ __forceinline__ SetOpC set_load_op(const SetOp * __restrict__ ops, const SetOpS * tbl, int o) {
+    SetOpC r;
+    if (tbl != nullptr) {
+        const SetOpS t = tbl[o];
+        r.x = t.x; r.y = t.y; r.ytag = t.ytag; r.xtag = t.xtag; r.rows = t.rows; r.nbk = t.nbk; r.ntiles = t.ntiles;
+        r.first_mod = t.fm_flags & 0xFFFF; r.flags = t.fm_flags >> 16;
+        r.S = DUMP ? ops[o].S : nullptr;
+        return r;
+    }
+    const SetOp * p = ops + o;
+    r.x = p->x; r.y = p->y; r.S = DUMP ? p->S : nullptr; r.ytag = p->ytag; r.xtag = p->xtag;
+    r.rows = p->rows; r.nbk = p->nbk; r.ntiles = p->ntiles; r.first_mod = p->first_mod; r.flags = p->flags;
+    return r;
+}
+
+struct SetCtx {
+    const SetOp * ops;
+    const SetOpS * tbl;
+    int nops;
+    unsigned char * ring;
+    float * red;
+    uint32_t full0, empty0;
+    int nslots, slot_bytes;
+    int G, group, wig, lane;
+    unsigned long long tag;           // launch number << 32
+};
+
+// ring position of the CTA's next tile: slot index and the parity of its current use
+struct SetRing {
+    int s, phase;
+    __device__ __forceinline__ void next(int nslots) { if (++s == nslots) { s = 0; phase ^= 1; } }
+};
+
+// One run of ops that share x, for one consumer warp.  WPR warps cooperate on a row; a lane keeps the quantized x of
+// its NCL blocks in registers.  Returns the index of the op that starts the next run.
+// `op` = descriptor of op o on entry, of the returned op on exit (when there is one).
+template <int NG, int WPR, int NCL, bool DUMP, bool PROF>
+__device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<1> & xs, int o, SetOpC & op, int & j, SetRing & rp,
+                                               unsigned & ntile_team, long long & t_full, long long & t_comp, long long & n_tiles) {
+    constexpr int RPT = WPR == 1 ? 2 : 4;               // rows of a tile per team
+    constexpr int R = (SET_WPG / WPR) * RPT;            // 8 or 4
+    constexpr int STRIDE = 32 * WPR;
+    const int tl = WPR == 1 ? c.lane : c.wig * 32 + c.lane;
+    const int nbk = op.nbk;
+    uint4 xlo[NCL], xhi[NCL];
+    float dx[NCL];
+    int s8[NCL];
+#pragma unroll
+    for (int u = 0; u < NCL; u++) {
+        const int b = tl + STRIDE * u;
+        xlo[u] = make_uint4(0, 0, 0, 0); xhi[u] = make_uint4(0, 0, 0, 0); dx[u] = 0.0f; s8[u] = 0;
+        if (b < nbk) {
+            xlo[u] = xs.lo[b]; xhi[u] = xs.hi[b];
+            const int2 ds = xs.ds[b];
+            dx[u] = __int_as_float(ds.x); s8[u] = ds.y;
+        }
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(NG * SET_WPG * 32) : "memory");   // the planes may be overwritten by whoever finishes this run first
+    for (;;) {
+        int first = (int)blockIdx.x - op.first_mod;
+        if (first < 0) first += c.G;
+        for (int t = first; t < op.ntiles; t += c.G, j++, rp.next(c.nslots)) {
+            if (j % NG != c.group) continue;
+            const int rit = WPR == 1 ? c.wig * RPT : 0;           // first row of this team inside the tile
+            const int row0 = t * R + rit;
+            const int nvalid = min(RPT, op.rows - row0);
+            const unsigned char * slot = c.ring + (size_t)rp.s * c.slot_bytes;
+            const unsigned char * nib = slot + (size_t)rit * nbk * 16;
+            const unsigned char * sc = slot + (size_t)R * nbk * 16 + (size_t)rit * nbk * 2;
+            const uint32_t full = c.full0 + 8 * rp.s, empty = c.empty0 + 8 * rp.s;
+            long long tf0 = 0;
+            if (PROF) tf0 = clock64();
+            mbar_wait(full, rp.phase);
+            long long tc0 = 0;
+            if (PROF) { tc0 = clock64(); t_full += tc0 - tf0; n_tiles++; }
+            if (nvalid <= 0) {            // ragged last tile (WPR == 1 only): nothing for this warp, still release the slot
+                if (c.lane == 0) mbar_arrive(empty);
+                continue;
+            }
+            float acc[RPT];
+#pragma unroll
+            for (int r = 0; r < RPT; r++) acc[r] = 0.0f;
+#pragma unroll
+            for (int u = 0; u < NCL; u++) {
+                const int b = tl + STRIDE * u;
+                if (b < nbk) {
+                    uint4 q[RPT];
+                    unsigned short dh[RPT];
+#pragma unroll
+                    for (int r = 0; r < RPT; r++) {
+                        q[r] = *reinterpret_cast<const uint4 *>(nib + ((size_t)r * nbk + b) * 16);
+                        dh[r] = *reinterpret_cast<const unsigned short *>(sc + ((size_t)r * nbk + b) * 2);
+                    }
+#pragma unroll
+                    for (int r = 0; r < RPT; r++) {
+                        const int sb = block_dot_q4_q8_fast(q[r], xlo[u], xhi[u], s8[u]);
+                        if (DUMP) { if (op.S != nullptr && r < nvalid) op.S[(size_t)(row0 + r) * nbk + b] = sb; }
+                        acc[r] = fmaf((float)sb, half_bits_to_float(dh[r]) * dx[u], acc[r]);
+                    }
+                }
+            }
+            // the slot's bytes of this warp are in registers: hand the slot back before the reduction
+            __syncwarp();
+            if (c.lane == 0) mbar_arrive(empty);
+#pragma unroll
+            for (int r = 0; r < RPT; r++) acc[r] = warp_sum(acc[r]);
+            if (WPR == 1) {
+                if (c.lane == 0) {
+#pragma unroll
+                    for (int r = 0; r < RPT; r++) if (r < nvalid) {
+                        op.y[row0 + r] = acc[r];
+                        if (op.ytag != nullptr) st_relaxed_gpu_b64(op.ytag + row0 + r, c.tag | __float_as_uint(acc[r]));
+                    }
+                }
+            } else {
+                // four warp partials per row, added in a fixed order by the group's first warp
+                float * red = c.red + ((ntile_team & 1u) * SET_MAX_GROUPS + c.group) * 16;
+                if (c.lane == 0) {
+#pragma unroll
+                    for (int r = 0; r < RPT; r++) red[r * 4 + c.wig] = acc[r];
+                }
+                asm volatile("bar.sync %0, 128;" ::"r"(2 + c.group) : "memory");
+                if (c.wig == 0 && c.lane < nvalid) {
+                    const float4 p = *reinterpret_cast<const float4 *>(red + c.lane * 4);
+                    const float v = ((p.x + p.y) + p.z) + p.w;
+                    op.y[row0 + c.lane] = v;
+                    if (op.ytag != nullptr) st_relaxed_gpu_b64(op.ytag + row0 + c.lane, c.tag | __float_as_uint(v));
+                }
+                ntile_team++;
+            }
+            if (PROF) t_comp += clock64() - tc0;
+        }
+        o++;
+        if (o >= c.nops) break;
+        op = set_load_op<DUMP>(c.ops, c.tbl, o);      // shared-memory table (lists beyond SET_MAX_TABLE_BYTES: an L2 round trip per op)
+        if (op.flags & SET_OP_QUANT) break;
+    }
+    return o;
+}
+
+// PROF (profiling aid, ggml_b200_set_profile): clock64 totals per CTA -> prof[cta*8 + ..] =
+// {whole kernel, consumer warp 0 waiting for full slots, in dependency barriers, quantizing x, producer waiting for empty slots}
+template <int W, bool DUMP, bool PROF>
 __global__ void __launch_bounds__(W * 32 + 32, 1)
 gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restrict__ sync, int nslots, int slot_bytes,
-                     int x_bytes, unsigned seq) {
+                     int x_bytes, int tbl_bytes, int max_fly, unsigned seq, long long * __restrict__ prof) {
     constexpr int NCONS = W * 32;
     constexpr int NG = W / SET_WPG;
+    static_assert(NG <= SET_MAX_GROUPS, "named barriers 2 .. 2+NG-1 and the partials buffer are sized for 6 groups");
     extern __shared__ __align__(128) unsigned char smem[];
-    // [x planes: x_bytes][full barriers 16 x 8][empty barriers 16 x 8][ring: nslots x slot_bytes]
+    // [x planes: x_bytes][full barriers 16 x 8][empty barriers 16 x 8][team partials][op table: tbl_bytes][ring: nslots x slot_bytes]
     GemvSmem<1> xs(smem, x_bytes / 40);
     uint64_t * bars = reinterpret_cast<uint64_t *>(smem + x_bytes);
-    unsigned char * ring = smem + x_bytes + 2 * SET_MAX_SLOTS * 8;
+    SetOpS * tbl = tbl_bytes ? reinterpret_cast<SetOpS *>(smem + x_bytes + SET_BAR_BYTES + SET_RED_BYTES) : nullptr;
+    unsigned char * ring = smem + x_bytes + SET_BAR_BYTES + SET_RED_BYTES + tbl_bytes;
     const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + SET_MAX_SLOTS);
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int warp = tid >> 5;
     const int G = gridDim.x;
 
+    __shared__ unsigned s_launch;
     if (tid == 0) {
         for (int s = 0; s < nslots; s++) {
             mbar_init(full0 + 8 * s, 1);
             mbar_init(empty0 + 8 * s, SET_WPG);
         }
         mbar_fence_init();
+        s_launch = ld_relaxed_gpu_u32(&sync->epoch) + 1u;     // stable: the last CTA of the previous launch wrote it
+    }
+    if (tbl != nullptr) {
+        for (int i = tid; i < nops; i += blockDim.x) {
+            const SetOp * p = ops + i;
+            SetOpS t;
+            t.x = p->x; t.y = p->y; t.ytag = p->ytag; t.xtag = p->xtag; t.rows = p->rows; t.nbk = p->nbk; t.ntiles = p->ntiles; t.fm_flags = p->first_mod | (p->flags << 16);
+            tbl[i] = t;
+        }
     }
     __syncthreads();
     CtaTrace tr;
     if (tid == 0) tr.begin(seq);
+    long long t_begin = 0, t_full = 0, t_bar = 0, t_quant = 0, t_empty = 0, t_comp = 0, n_tiles = 0, t_run = 0;
+    if (PROF) t_begin = clock64();
 
     if (warp == W) {
         // ===== producer: streams this CTA's tiles of every op, in list order, through the ring =====
         if (lane == 0) {
-            int j = 0;
+            SetRing rp = {0, 0};
+            // At most max_fly copies in flight: the TMA engine's requests and the CTA's ordinary loads (dependency
+            // polls, x) leave the SM through the same queue, and a load issued behind 8 x 18 KB of bulk requests
+            // waits ~2400 clk for its turn (measured: profiles/r01_experiments.md).  `lag` trails the issue position by
+            // max_fly slots; the copy issued there must have landed before the next one goes out.
+            SetRing lag = {0, 0};
+            int issued = 0;
+            bool wrapped = false;
+            SetOp op = ops[0];
             for (int o = 0; o < nops; o++) {
-                const SetOp op = ops[o];
-                const int R = SET_WPG * op.rpw;
+                SetOp nxt = op;
+                if (o + 1 < nops) nxt = ops[o + 1];
+                const int R = op.tile_rows;
                 const unsigned char * nib_base = reinterpret_cast<const unsigned char *>(op.wq);
                 const unsigned char * sc_base = reinterpret_cast<const unsigned char *>(op.wd);
                 int first = (int)blockIdx.x - op.first_mod;
                 if (first < 0) first += G;
-                for (int t = first; t < op.ntiles; t += G, j++) {
-                    const int s = j % nslots;
-                    if (j >= nslots) mbar_wait(empty0 + 8 * s, ((j / nslots) - 1) & 1);
+                for (int t = first; t < op.ntiles; t += G) {
+                    if (wrapped) {
+                        long long t0 = 0;
+                        if (PROF) t0 = clock64();
+                        mbar_wait_backoff(empty0 + 8 * rp.s, rp.phase ^ 1);      // the consumers released the slot's previous use
+                        if (PROF) t_empty += clock64() - t0;
+                    }
+                    if (issued >= max_fly) {
+                        mbar_wait_backoff(full0 + 8 * lag.s, lag.phase);
+                        lag.next(nslots);
+                    }
+                    issued++;
                     const int row0 = t * R;
                     const int nr = min(R, op.rows - row0);
                     const uint32_t nib_sz = (uint32_t)nr * op.nbk * 16;
                     const uint32_t sc_sz = ((uint32_t)nr * op.nbk * 2 + 15u) & ~15u;   // the scale plane is allocated with 16 B of slack
-                    const uint32_t dst = smem_u32(ring + (size_t)s * slot_bytes);
-                    mbar_expect_tx(full0 + 8 * s, nib_sz + sc_sz);
-                    bulk_g2s(dst, nib_base + (size_t)row0 * op.nbk * 16, nib_sz, full0 + 8 * s);
-                    bulk_g2s(dst + (uint32_t)R * op.nbk * 16, sc_base + (size_t)row0 * op.nbk * 2, sc_sz, full0 + 8 * s);
+                    const uint32_t dst = smem_u32(ring + (size_t)rp.s * slot_bytes);
+                    const uint32_t full = full0 + 8 * rp.s;
+                    mbar_expect_tx(full, nib_sz + sc_sz);
+                    bulk_g2s(dst, nib_base + (size_t)row0 * op.nbk * 16, nib_sz, full);
+                    bulk_g2s(dst + (uint32_t)R * op.nbk * 16, sc_base + (size_t)row0 * op.nbk * 2, sc_sz, full);
+                    if (++rp.s == nslots) { rp.s = 0; rp.phase ^= 1; wrapped = true; }
                 }
+                op = nxt;
             }
+            if (PROF) prof[blockIdx.x * 16 + 4] = t_empty;
         }
         return;
     }
 
     // ===== consumers =====
-    const int group = warp / SET_WPG;
-    const int wig = warp - group * SET_WPG;
+    SetCtx c;
+    c.ops = ops; c.tbl = tbl; c.nops = nops; c.ring = ring; c.red = reinterpret_cast<float *>(smem + x_bytes + SET_BAR_BYTES);
+    c.full0 = full0; c.empty0 = empty0; c.nslots = nslots; c.slot_bytes = slot_bytes;
+    c.G = G; c.group = warp / SET_WPG; c.wig = warp % SET_WPG; c.lane = lane;
+    c.tag = (unsigned long long)s_launch << 32;
+    SetRing rp = {0, 0};
     int j = 0;
-    unsigned nbar = 0;
-    for (int o = 0; o < nops; o++) {
-        const SetOp op = ops[o];
-        if (op.flags & SET_OP_BARRIER) {
+    unsigned nbar = 0, ntile_team = 0;
+    SetOpC op = set_load_op<DUMP>(ops, tbl, 0);
+    long long tp[4] = {0, 0, 0, 0};
+    for (int o = 0; o < nops;) {
+        // Every run starts with an op that (re)quantizes x.  Where the host found a hazard it cannot express as
+        // "x is the dst of ONE earlier op" the run waits for everything before it (grid barrier); otherwise x is
+        // either untouched by the list (plain loads) or read out of its producer's tagged words, which is the wait.
+        const int flags = op.flags;
+        const int nbk = op.nbk;
+        const float * x = op.x;
+        long long tq0 = 0;
+        if (PROF) tq0 = clock64();
+        if (flags & SET_OP_BARRIER) {
             nbar++;
-            set_grid_barrier<NCONS>(sync, nbar * (unsigned)G);
+            set_grid_barrier<NCONS, PROF>(sync, nbar * (unsigned)G, tp);
         }
-        if (op.flags & SET_OP_QUANT) {
-            if (!(op.flags & SET_OP_BARRIER)) set_consumer_sync<NCONS>();   // everybody is done with the old planes
-            // x may have been written by other SMs during this launch: L2-coherent loads (mode 2)
-            quantize_x_to_smem<false>(xs, op.x, op.nbk, 2, warp, lane, nullptr, NCONS);
-            set_consumer_sync<NCONS>();
+        if (PROF) { const long long t1 = clock64(); t_bar += t1 - tq0; tq0 = t1; }
+        // the planes are free: every warp passed the CTA barrier that follows its register load of the previous run
+        set_quantize_x<NCONS>(xs, x, op.xtag, c.tag, nbk, tid);
+        set_consumer_sync<NCONS>();
+        long long tr0 = 0;
+        if (PROF) { tr0 = clock64(); t_quant += tr0 - tq0; }
+        if (nbk <= SET_MAX_NBK_WPR1) {
+            if (nbk <= 32)       o = set_consume_run<NG, 1, 1, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
+            else if (nbk <= 64)  o = set_consume_run<NG, 1, 2, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
+            else if (nbk <= 96)  o = set_consume_run<NG, 1, 3, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
+            else                 o = set_consume_run<NG, 1, 4, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
+        } else {
+            if (nbk <= 256)      o = set_consume_run<NG, 4, 2, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
+            else if (nbk <= 384) o = set_consume_run<NG, 4, 3, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
+            else if (nbk <= 512) o = set_consume_run<NG, 4, 4, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
+            else                 o = set_consume_run<NG, 4, 6, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
         }
-        const int R = SET_WPG * op.rpw;
-        int first = (int)blockIdx.x - op.first_mod;
-        if (first < 0) first += G;
-        for (int t = first; t < op.ntiles; t += G, j++) {
-            if (j % NG != group) continue;
-            const int s = j % nslots;
-            const int row0 = t * R + wig * op.rpw;
-            const int nvalid = min(op.rpw, op.rows - row0);
-            const unsigned char * slot = ring + (size_t)s * slot_bytes;
-            const unsigned char * nib = slot + (size_t)wig * op.rpw * op.nbk * 16;
-            const unsigned char * sc = slot + (size_t)R * op.nbk * 16 + (size_t)wig * op.rpw * op.nbk * 2;
-            mbar_wait(full0 + 8 * s, (j / nslots) & 1);
-            if (nvalid <= 0) {            // ragged last tile: nothing for this warp, still release the slot
-                if (lane == 0) mbar_arrive(empty0 + 8 * s);
-                continue;
-            }
-            int * Srow = (DUMP && op.S != nullptr) ? op.S + (size_t)row0 * op.nbk : nullptr;
-            if (op.rpw == 2) set_tile_rows<2, DUMP>(nib, sc, xs, op.nbk, lane, nvalid, op.y + row0, Srow, empty0 + 8 * s);
-            else             set_tile_rows<1, DUMP>(nib, sc, xs, op.nbk, lane, nvalid, op.y + row0, Srow, empty0 + 8 * s);
-        }
+        if (PROF) t_run += clock64() - tr0;
     }
     if (tid == 0) tr.mark(3);
+    if (PROF) {
+        if (tid == 0) {
+            prof[blockIdx.x * 16 + 0] = clock64() - t_begin;
+            prof[blockIdx.x * 16 + 1] = t_full;
+            prof[blockIdx.x * 16 + 2] = t_bar;
+            prof[blockIdx.x * 16 + 3] = t_quant;
+            prof[blockIdx.x * 16 + 5] = t_comp;
+            prof[blockIdx.x * 16 + 6] = n_tiles;
+            prof[blockIdx.x * 16 + 7] = t_run;
+            for (int i = 0; i < 4; i++) prof[blockIdx.x * 16 + 8 + i] = tp[i];
+        }
+    }
 
     // leave the sync words zero for the next launch: the last CTA to finish has seen every barrier complete
     set_consumer_sync<NCONS>();
@@ -219,6 +531,7 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
         if (old == (unsigned)G - 1u) {
             atomicExch(&sync->arrived, 0u);
             atomicExch(&sync->done, 0u);
+            atomicExch(&sync->epoch, s_launch);
         }
     }
 }

@@ -496,8 +496,11 @@ int ggml_b200_set_tuning(const char * key, int value) {
     else if (!strcmp(key, "host_fast"))    { g.tune.host_fast = value != 0; }
     else if (!strcmp(key, "overlap_same_src")) { g.tune.overlap_same_src = value != 0; g.run.count = 0; g.runN.count = 0; }
     else if (!strcmp(key, "set_coop"))     { g.tune.set_coop = value != 0; }
-    else if (!strcmp(key, "set_warps"))    { if (value != 8 && value != 16 && value != 24) return GGML_B200_ERR_ARG; g.tune.set_warps = value; }
-    else if (!strcmp(key, "set_rpw"))      { g.tune.set_rpw = value; }
+    else if (!strcmp(key, "set_warps"))    { if (value != 8 && value != 12 && value != 16 && value != 20) return GGML_B200_ERR_ARG; g.tune.set_warps = value; }
+    else if (!strcmp(key, "set_unsafe_no_barriers")) { g.tune.set_unsafe_no_barriers = value != 0; }
+    else if (!strcmp(key, "set_link"))     { g.tune.set_link = value != 0; }
+    else if (!strcmp(key, "set_fly"))      { g.tune.set_fly = value; }
+    else if (!strcmp(key, "set_table"))    { g.tune.set_table = value != 0; }
     else if (!strcmp(key, "set_slots"))    { g.tune.set_slots = value; }
     else if (!strcmp(key, "p2p_gather"))   { comm_set_p2p(value); }
     else return gemm_set_tuning(key, value);

@@ -19,7 +19,9 @@ struct ggml_b200_set {
     b200::SetOp * dev_ops = nullptr;
     b200::SetOp * dev_ops_dump = nullptr;   // scratch table for the checkpoint launch
     b200::SetSync * sync = nullptr;
-    int nslots = 0, slot_bytes = 0, x_bytes = 0;
+    unsigned long long * staging = nullptr;   // tagged dst rows of the ops a later op reads as x
+    int linked_runs = 0;
+    int nslots = 0, slot_bytes = 0, x_bytes = 0, tbl_bytes = 0;
     size_t smem = 0;
     int barriers = 0;
     int warps = 16;
@@ -31,12 +33,12 @@ namespace b200 {
 
 static bool set_ranges_overlap(const float * a_lo, const float * a_hi, const float * b_lo, const float * b_hi) { return a_lo < b_hi && b_lo < a_hi; }
 
-template <int W, bool DUMP>
-static int set_launch_t(const ggml_b200_set * s, const SetOp * table) {
-    auto kern = gemv_q4_0_set_kernel<W, DUMP>;
+template <int W, bool DUMP, bool PROF>
+static int set_launch_t(const ggml_b200_set * s, const SetOp * table, long long * prof) {
+    auto kern = gemv_q4_0_set_kernel<W, DUMP, PROF>;
     static bool attr_set = false;
     if (!attr_set) {
-        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM - 1024));   // the kernel has a little static shared memory too
         attr_set = true;
     }
     cudaLaunchConfig_t cfg = {};
@@ -47,17 +49,18 @@ static int set_launch_t(const ggml_b200_set * s, const SetOp * table) {
     attr[0].id = cudaLaunchAttributeCooperative;
     attr[0].val.cooperative = 1;
     cfg.attrs = attr; cfg.numAttrs = g.tune.set_coop ? 1 : 0;
-    CK(cudaLaunchKernelEx(&cfg, kern, table, (int)s->host_ops.size(), s->sync, s->nslots, s->slot_bytes, s->x_bytes, (unsigned)g.launches));
+    CK(cudaLaunchKernelEx(&cfg, kern, table, (int)s->host_ops.size(), s->sync, s->nslots, s->slot_bytes, s->x_bytes, s->tbl_bytes, g.tune.set_fly > 0 ? g.tune.set_fly : 1 << 30, (unsigned)g.launches, prof));
     g.launches++;
     return GGML_B200_OK;
 }
 
-template <bool DUMP>
-static int set_launch(const ggml_b200_set * s, const SetOp * table) {
+template <bool DUMP, bool PROF>
+static int set_launch(const ggml_b200_set * s, const SetOp * table, long long * prof = nullptr) {
     switch (s->warps) {
-        case 8:  return set_launch_t<8, DUMP>(s, table);
-        case 24: return set_launch_t<24, DUMP>(s, table);
-        default: return set_launch_t<16, DUMP>(s, table);
+        case 8:  return set_launch_t<8, DUMP, PROF>(s, table, prof);
+        case 12: return set_launch_t<12, DUMP, PROF>(s, table, prof);
+        case 20: return set_launch_t<20, DUMP, PROF>(s, table, prof);
+        default: return set_launch_t<16, DUMP, PROF>(s, table, prof);
     }
 }
 
@@ -76,9 +79,16 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
     const int NG = s->warps / SET_WPG;
     int nbk_max = 0;
     long long tiles = 0;
-    // the current run of mutually independent ops (same x, disjoint dst): same rule as overlap_same_src
-    const float * run_x = nullptr; int64_t run_K = 0;
-    std::vector<std::pair<const float *, const float *>> run_y;
+    // Hazards between the ops of the list (the list must behave like the ops run one after the other):
+    //   * x of an op is exactly the dst of ONE earlier op still "live" (no barrier since)  -> the run reads x out of that
+    //     op's tagged staging rows (gemv_q4_0_set.cuh): the wait is per word, no barrier;
+    //   * x overlaps live dsts in any other way, or dst overlaps a live x or dst (WAR / WAW)  -> grid barrier first;
+    //   * otherwise x is not produced inside the list (or was before the last barrier): plain loads.
+    // Ops that share x with the head of the current run and need no barrier join it (no re-quantization).
+    struct Range { const float * lo, * hi; int op; bool whole; };
+    std::vector<Range> live_x, live_y;
+    std::vector<int> link_of;             // per host op: index of the host op whose staging rows its x is read from, or -1
+    const float * run_x = nullptr; int64_t run_K = 0; int run_link = -1;
     for (int i = 0; i < n_ops; i++) {
         const ggml_b200_weight * w = ops[i].w;
         const float * x = ops[i].x_dev;
@@ -92,20 +102,37 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
         SetOp o = {};
         o.wq = w->wq; o.wd = reinterpret_cast<const unsigned short *>(w->wd); o.x = x; o.y = y + w->row_lo; o.S = nullptr;
         o.rows = (int)w->rows(); o.nbk = (int)(w->K / QK);
-        o.rpw = (g.tune.set_rpw == 1 || 8 * o.nbk * 18 > 20 * 1024) ? 1 : 2;
-        const int R = SET_WPG * o.rpw;
+        if (o.nbk > SET_MAX_NBK) { set_error("set op %d: K = %lld > %d is beyond the persistent kernel's register plan; use ggml_b200_mul_mat_q4_0", i, (long long)w->K, SET_MAX_NBK * QK); delete s; return nullptr; }
+        o.tile_rows = o.nbk <= SET_MAX_NBK_WPR1 ? 8 : 4;
+        const int R = o.tile_rows;
         o.ntiles = (o.rows + R - 1) / R;
         o.first_mod = (int)(tiles % s->grid);
         tiles += o.ntiles;
         const float * y_lo = o.y, * y_hi = o.y + o.rows;
-        bool independent = !s->host_ops.empty() && run_x == x && run_K == w->K;
-        for (size_t k = 0; independent && k < run_y.size(); k++) independent = !set_ranges_overlap(y_lo, y_hi, run_y[k].first, run_y[k].second);
-        if (!independent) {
-            o.flags = SET_OP_QUANT | (s->host_ops.empty() ? 0 : SET_OP_BARRIER);
-            if (o.flags & SET_OP_BARRIER) s->barriers++;
-            run_x = x; run_K = w->K; run_y.clear();
+        const float * x_hi = x + w->K;
+        bool barrier = false;
+        for (const Range & r : live_x) if (set_ranges_overlap(y_lo, y_hi, r.lo, r.hi)) barrier = true;      // WAR
+        for (const Range & r : live_y) if (set_ranges_overlap(y_lo, y_hi, r.lo, r.hi)) barrier = true;      // WAW
+        int link = -1, writers = 0;
+        for (const Range & r : live_y) {
+            if (!set_ranges_overlap(x, x_hi, r.lo, r.hi)) continue;
+            writers++;
+            if (r.lo == x && r.hi == x_hi && r.whole) link = r.op; else barrier = true;                   // RAW
         }
-        run_y.push_back({y_lo, y_hi});
+        if (writers > 1 || (link >= 0 && !g.tune.set_link)) barrier = true;
+        if (barrier) { live_x.clear(); live_y.clear(); link = -1; }
+        const bool same_run = !s->host_ops.empty() && !barrier && run_x == x && run_K == w->K && run_link == link;
+        if (!same_run) {
+            const bool bar = barrier && !s->host_ops.empty() && !g.tune.set_unsafe_no_barriers;
+            o.flags = SET_OP_QUANT | (bar ? SET_OP_BARRIER : 0);
+            if (bar) s->barriers++;
+            if (link >= 0) s->linked_runs++;
+            run_x = x; run_K = w->K; run_link = link;
+        }
+        link_of.push_back(same_run ? -1 : link);
+        const int me = (int)s->host_ops.size();
+        live_x.push_back({x, x_hi, me, false});
+        live_y.push_back({y_lo, y_hi, me, w->row_lo == 0 && w->row_hi == w->M});
         if (o.nbk > nbk_max) nbk_max = o.nbk;
         const int stage = R * o.nbk * 16 + ((R * o.nbk * 2 + 15) & ~15);
         if (stage > s->slot_bytes) s->slot_bytes = stage;
@@ -114,7 +141,10 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
     if (s->host_ops.empty()) { set_error("every op of the set has an empty row shard"); delete s; return nullptr; }
     s->slot_bytes = (s->slot_bytes + 127) & ~127;
     s->x_bytes = 40 * nbk_max;
-    const long long ring = (long long)MAX_DYN_SMEM - s->x_bytes - 2 * SET_MAX_SLOTS * 8 - 128;
+    s->tbl_bytes = (int)((s->host_ops.size() * sizeof(SetOpS) + 127) & ~(size_t)127);
+    if (s->tbl_bytes > SET_MAX_TABLE_BYTES || g.tune.set_table == 0) s->tbl_bytes = 0;      // long list: descriptors stay in global memory
+    for (const SetOp & o : s->host_ops) if (o.first_mod > 0xFFFF) s->tbl_bytes = 0;
+    const long long ring = (long long)MAX_DYN_SMEM - 1024 - s->x_bytes - SET_BAR_BYTES - SET_RED_BYTES - s->tbl_bytes - 128;
     s->nslots = (int)(ring / s->slot_bytes);
     if (s->nslots > SET_MAX_SLOTS) s->nslots = SET_MAX_SLOTS;
     if (g.tune.set_slots > 0 && g.tune.set_slots < s->nslots) s->nslots = g.tune.set_slots;
@@ -123,7 +153,22 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
         delete s; return nullptr;
     }
     (void)NG;
-    s->smem = (size_t)s->x_bytes + 2 * SET_MAX_SLOTS * 8 + (size_t)s->nslots * s->slot_bytes;
+    s->smem = (size_t)s->x_bytes + SET_BAR_BYTES + SET_RED_BYTES + s->tbl_bytes + (size_t)s->nslots * s->slot_bytes;
+    {
+        size_t words = 0;
+        std::vector<long long> off(s->host_ops.size(), -1);
+        for (size_t i = 0; i < link_of.size(); i++) {
+            const int k = link_of[i];
+            if (k >= 0 && off[k] < 0) { off[k] = (long long)words; words += ((size_t)s->host_ops[k].rows + 7) & ~(size_t)7; }
+        }
+        if (words) {
+            cudaError_t e2 = cudaMalloc(&s->staging, words * 8);
+            if (e2 == cudaSuccess) e2 = cudaMemset(s->staging, 0, words * 8);      // launch numbers start at 1
+            if (e2 != cudaSuccess) { cuda_fail(e2, "set_create staging", __FILE__, __LINE__); ggml_b200_set_free(s); return nullptr; }
+            for (size_t i = 0; i < s->host_ops.size(); i++) if (off[i] >= 0) s->host_ops[i].ytag = s->staging + off[i];
+            for (size_t i = 0; i < link_of.size(); i++) if (link_of[i] >= 0) s->host_ops[i].xtag = s->staging + off[link_of[i]];
+        }
+    }
     cudaError_t e = cudaMalloc(&s->dev_ops, s->host_ops.size() * sizeof(SetOp));
     if (e == cudaSuccess) e = cudaMalloc(&s->sync, sizeof(SetSync));
     if (e == cudaSuccess) e = cudaMemcpy(s->dev_ops, s->host_ops.data(), s->host_ops.size() * sizeof(SetOp), cudaMemcpyHostToDevice);
@@ -137,13 +182,14 @@ void ggml_b200_set_free(ggml_b200_set * s) {
     if (s->dev_ops) cudaFree(s->dev_ops);
     if (s->dev_ops_dump) cudaFree(s->dev_ops_dump);
     if (s->sync) cudaFree(s->sync);
+    if (s->staging) cudaFree(s->staging);
     delete s;
 }
 
 int ggml_b200_set_run(ggml_b200_set * s) {
     if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
     if (!s) { set_error("null set"); return GGML_B200_ERR_ARG; }
-    return set_launch<false>(s, s->dev_ops);
+    return set_launch<false, false>(s, s->dev_ops);
 }
 
 int ggml_b200_set_checkpoint(ggml_b200_set * s, int32_t * const * S_dev, int n_ops) {
@@ -154,10 +200,29 @@ int ggml_b200_set_checkpoint(ggml_b200_set * s, int32_t * const * S_dev, int n_o
     if (!s->dev_ops_dump) CK(cudaMalloc(&s->dev_ops_dump, t.size() * sizeof(SetOp)));
     CK(cudaMemcpyAsync(s->dev_ops_dump, t.data(), t.size() * sizeof(SetOp), cudaMemcpyHostToDevice, g.stream));
     CK(cudaStreamSynchronize(g.stream));   // t is a local
-    return set_launch<true>(s, s->dev_ops_dump);
+    return set_launch<true, false>(s, s->dev_ops_dump);
+}
+
+int ggml_b200_set_profile(ggml_b200_set * s, long long * out_host, int max_ctas) {
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    if (!s || !out_host || max_ctas <= 0) { set_error("bad set_profile arguments"); return GGML_B200_ERR_ARG; }
+    long long * dev = nullptr;
+    const size_t bytes = (size_t)s->grid * 16 * sizeof(long long);
+    CK(cudaMalloc(&dev, bytes));
+    cudaError_t e = cudaMemsetAsync(dev, 0, bytes, g.stream);
+    int rc = e == cudaSuccess ? set_launch<false, true>(s, s->dev_ops, dev) : cuda_fail(e, "memset", __FILE__, __LINE__);
+    const int n = max_ctas < s->grid ? max_ctas : s->grid;
+    if (rc == GGML_B200_OK) {
+        e = cudaMemcpyAsync(out_host, dev, (size_t)n * 16 * sizeof(long long), cudaMemcpyDeviceToHost, g.stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
+        if (e != cudaSuccess) rc = cuda_fail(e, "set_profile", __FILE__, __LINE__);
+    }
+    cudaFree(dev);
+    return rc == GGML_B200_OK ? n : rc;
 }
 
 int      ggml_b200_set_barriers(const ggml_b200_set * s) { return s ? s->barriers : -1; }
+int      ggml_b200_set_linked_runs(const ggml_b200_set * s) { return s ? s->linked_runs : -1; }
 int      ggml_b200_set_ops(const ggml_b200_set * s) { return s ? (int)s->host_ops.size() : -1; }
 int      ggml_b200_set_slots(const ggml_b200_set * s) { return s ? s->nslots : -1; }
 uint64_t ggml_b200_set_bytes(const ggml_b200_set * s) { return s ? s->bytes : 0; }

@@ -89,8 +89,10 @@ def _load() -> C.CDLL:
         "ggml_b200_set_ops": (C.c_int, [_vp]),
         "ggml_b200_set_barriers": (C.c_int, [_vp]),
         "ggml_b200_set_slots": (C.c_int, [_vp]),
+        "ggml_b200_set_linked_runs": (C.c_int, [_vp]),
         "ggml_b200_set_bytes": (C.c_uint64, [_vp]),
         "ggml_b200_set_checkpoint": (C.c_int, [_vp, _vp, C.c_int]),
+        "ggml_b200_set_profile": (C.c_int, [_vp, _vp, C.c_int]),
         "ggml_b200_launch_count": (C.c_uint64, []),
         "ggml_b200_trace_begin": (C.c_int, [C.c_uint]),
         "ggml_b200_trace_end": (C.c_int, [_vp, C.c_uint]),
@@ -352,6 +354,7 @@ class OpSet:
     n_ops = property(lambda self: int(lib().ggml_b200_set_ops(self.h)))
     barriers = property(lambda self: int(lib().ggml_b200_set_barriers(self.h)))
     slots = property(lambda self: int(lib().ggml_b200_set_slots(self.h)))
+    linked_runs = property(lambda self: int(lib().ggml_b200_set_linked_runs(self.h)))
     bytes = property(lambda self: int(lib().ggml_b200_set_bytes(self.h)))
 
     def run(self) -> None:
@@ -361,6 +364,14 @@ class OpSet:
         """S_ptrs: one device pointer (or None) per non-empty op: int32 [rows][K/32]."""
         arr = (_vp * len(S_ptrs))(*[_vp(p) if p else None for p in S_ptrs])
         _check(lib().ggml_b200_set_checkpoint(self.h, C.cast(arr, _vp), len(S_ptrs)))
+
+    def profile(self) -> np.ndarray:
+        """int64 [ctas][16] clock totals of one instrumented run (see ggml_b200_set_profile)."""
+        out = np.zeros((sm_count(), 16), dtype=np.int64)
+        n = lib().ggml_b200_set_profile(self.h, out.ctypes.data_as(_vp), out.shape[0])
+        if n < 0:
+            _check(n)
+        return out[:n]
 
     def free(self) -> None:
         if self.h:
