@@ -810,7 +810,9 @@ def main():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--unfused", action="store_true", help="kernel 1 + kernel 2 as separate launches")
     ap.add_argument("--no-pdl", action="store_true")
-    ap.add_argument("--no-set", action="store_true", help="one launch per mul_mat instead of the persistent multi-op launch")
+    ap.add_argument("--set", dest="no_set", action="store_false", default=True,
+                    help="time the persistent multi-op launch (ggml_b200_set_*) instead of one launch per mul_mat; off by default: "
+                         "on a dependent list it is not faster yet (profiles/r01_set_sweep_*.log, tools/sweep_set.py)")
     ap.add_argument("--probe-set", action="store_true", help=argparse.SUPPRESS)
     ap.add_argument("--no-overlap", action="store_true", help="every matmul waits for the previous one even when they only share src1")
     ap.add_argument("--tune", action="append", default=[], help="key=value for ggml_b200_set_tuning")

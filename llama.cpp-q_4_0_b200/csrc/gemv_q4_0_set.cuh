@@ -270,7 +270,7 @@ struct SetRing {
 // `op` = descriptor of op o on entry, of the returned op on exit (when there is one).
 template <int NG, int WPR, int NCL, bool DUMP, bool PROF>
 __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<1> & xs, int o, SetOpC & op, int & j, SetRing & rp,
-                                               unsigned & ntile_team, long long & t_full, long long & t_comp, long long & n_tiles) {
+                                               unsigned & ntile_team, long long & t_full, long long & t_comp, long long & n_tiles, long long * tx) {
     constexpr int RPT = WPR == 1 ? 2 : 4;               // rows of a tile per team
     constexpr int R = (SET_WPG / WPR) * RPT;            // 8 or 4
     constexpr int STRIDE = 32 * WPR;
@@ -293,7 +293,10 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
     for (;;) {
         int first = (int)blockIdx.x - op.first_mod;
         if (first < 0) first += c.G;
+        long long tl0 = 0;
+        if (PROF) tl0 = clock64();
         for (int t = first; t < op.ntiles; t += c.G, j++, rp.next(c.nslots)) {
+            if (PROF) { const long long now = clock64(); tx[0] += now - tl0; tl0 = now; tx[1]++; }      // since the previous iteration's last stamp
             if (j % NG != c.group) continue;
             const int rit = WPR == 1 ? c.wig * RPT : 0;           // first row of this team inside the tile
             const int row0 = t * R + rit;
@@ -362,11 +365,13 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
                 }
                 ntile_team++;
             }
-            if (PROF) t_comp += clock64() - tc0;
+            if (PROF) { tl0 = clock64(); t_comp += tl0 - tc0; }
         }
+        if (PROF) { const long long now = clock64(); tx[2] += now - tl0; tl0 = now; }
         o++;
         if (o >= c.nops) break;
         op = set_load_op<DUMP>(c.ops, c.tbl, o);      // shared-memory table (lists beyond SET_MAX_TABLE_BYTES: an L2 round trip per op)
+        if (PROF) tx[3] += clock64() - tl0;
         if (op.flags & SET_OP_QUANT) break;
     }
     return o;
@@ -374,7 +379,8 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
 
 // PROF (profiling aid, ggml_b200_set_profile): clock64 totals per CTA -> prof[cta*8 + ..] =
 // {whole kernel, consumer warp 0 waiting for full slots, in dependency barriers, quantizing x, producer waiting for empty slots}
-template <int W, bool DUMP, bool PROF>
+// BIG: also the 6-blocks-per-lane plan (K > 16384); the kernel without it needs fewer registers
+template <int W, bool DUMP, bool PROF, bool BIG>
 __global__ void __launch_bounds__(W * 32 + 32, 1)
 gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restrict__ sync, int nslots, int slot_bytes,
                      int x_bytes, int tbl_bytes, int max_fly, unsigned seq, long long * __restrict__ prof) {
@@ -477,6 +483,7 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
     unsigned nbar = 0, ntile_team = 0;
     SetOpC op = set_load_op<DUMP>(ops, tbl, 0);
     long long tp[4] = {0, 0, 0, 0};
+    long long tx[4] = {0, 0, 0, 0};
     for (int o = 0; o < nops;) {
         // Every run starts with an op that (re)quantizes x.  Where the host found a hazard it cannot express as
         // "x is the dst of ONE earlier op" the run waits for everything before it (grid barrier); otherwise x is
@@ -497,15 +504,15 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
         long long tr0 = 0;
         if (PROF) { tr0 = clock64(); t_quant += tr0 - tq0; }
         if (nbk <= SET_MAX_NBK_WPR1) {
-            if (nbk <= 32)       o = set_consume_run<NG, 1, 1, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
-            else if (nbk <= 64)  o = set_consume_run<NG, 1, 2, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
-            else if (nbk <= 96)  o = set_consume_run<NG, 1, 3, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
-            else                 o = set_consume_run<NG, 1, 4, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
+            if (nbk <= 32)       o = set_consume_run<NG, 1, 1, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx);
+            else if (nbk <= 64)  o = set_consume_run<NG, 1, 2, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx);
+            else if (nbk <= 96)  o = set_consume_run<NG, 1, 3, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx);
+            else                 o = set_consume_run<NG, 1, 4, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx);
         } else {
-            if (nbk <= 256)      o = set_consume_run<NG, 4, 2, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
-            else if (nbk <= 384) o = set_consume_run<NG, 4, 3, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
-            else if (nbk <= 512) o = set_consume_run<NG, 4, 4, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
-            else                 o = set_consume_run<NG, 4, 6, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles);
+            if (nbk <= 256)      o = set_consume_run<NG, 4, 2, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx);
+            else if (nbk <= 384) o = set_consume_run<NG, 4, 3, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx);
+            else if (nbk <= 512 || !BIG) o = set_consume_run<NG, 4, 4, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx);
+            else { if constexpr (BIG) o = set_consume_run<NG, 4, 6, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx); }
         }
         if (PROF) t_run += clock64() - tr0;
     }
@@ -520,6 +527,7 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
             prof[blockIdx.x * 16 + 6] = n_tiles;
             prof[blockIdx.x * 16 + 7] = t_run;
             for (int i = 0; i < 4; i++) prof[blockIdx.x * 16 + 8 + i] = tp[i];
+            for (int i = 0; i < 4; i++) prof[blockIdx.x * 16 + 12 + i] = tx[i];
         }
     }
 

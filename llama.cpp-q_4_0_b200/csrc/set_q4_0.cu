@@ -21,6 +21,7 @@ struct ggml_b200_set {
     b200::SetSync * sync = nullptr;
     unsigned long long * staging = nullptr;   // tagged dst rows of the ops a later op reads as x
     int linked_runs = 0;
+    bool big = false;                       // some op has K > 16384: the kernel build with the 6-blocks-per-lane plan
     int nslots = 0, slot_bytes = 0, x_bytes = 0, tbl_bytes = 0;
     size_t smem = 0;
     int barriers = 0;
@@ -33,9 +34,9 @@ namespace b200 {
 
 static bool set_ranges_overlap(const float * a_lo, const float * a_hi, const float * b_lo, const float * b_hi) { return a_lo < b_hi && b_lo < a_hi; }
 
-template <int W, bool DUMP, bool PROF>
-static int set_launch_t(const ggml_b200_set * s, const SetOp * table, long long * prof) {
-    auto kern = gemv_q4_0_set_kernel<W, DUMP, PROF>;
+template <int W, bool DUMP, bool PROF, bool BIG>
+static int set_launch_tb(const ggml_b200_set * s, const SetOp * table, long long * prof) {
+    auto kern = gemv_q4_0_set_kernel<W, DUMP, PROF, BIG>;
     static bool attr_set = false;
     if (!attr_set) {
         CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM - 1024));   // the kernel has a little static shared memory too
@@ -52,6 +53,11 @@ static int set_launch_t(const ggml_b200_set * s, const SetOp * table, long long 
     CK(cudaLaunchKernelEx(&cfg, kern, table, (int)s->host_ops.size(), s->sync, s->nslots, s->slot_bytes, s->x_bytes, s->tbl_bytes, g.tune.set_fly > 0 ? g.tune.set_fly : 1 << 30, (unsigned)g.launches, prof));
     g.launches++;
     return GGML_B200_OK;
+}
+
+template <int W, bool DUMP, bool PROF>
+static int set_launch_t(const ggml_b200_set * s, const SetOp * table, long long * prof) {
+    return s->big ? set_launch_tb<W, DUMP, PROF, true>(s, table, prof) : set_launch_tb<W, DUMP, PROF, false>(s, table, prof);
 }
 
 template <bool DUMP, bool PROF>
@@ -141,6 +147,7 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
     if (s->host_ops.empty()) { set_error("every op of the set has an empty row shard"); delete s; return nullptr; }
     s->slot_bytes = (s->slot_bytes + 127) & ~127;
     s->x_bytes = 40 * nbk_max;
+    s->big = nbk_max > 512;
     s->tbl_bytes = (int)((s->host_ops.size() * sizeof(SetOpS) + 127) & ~(size_t)127);
     if (s->tbl_bytes > SET_MAX_TABLE_BYTES || g.tune.set_table == 0) s->tbl_bytes = 0;      // long list: descriptors stay in global memory
     for (const SetOp & o : s->host_ops) if (o.first_mod > 0xFFFF) s->tbl_bytes = 0;

@@ -110,7 +110,7 @@ def main():
         parts.append(f"warp 0: {prof[:, 6].mean():.0f} tiles, {(prof[:, 5] / np.maximum(prof[:, 6], 1)).mean():.0f} clk from data ready to y stored per tile "
                      f"({100 * (prof[:, 5] / tot).mean():.1f}% of the kernel)")
         parts.append(f"in the tile loops {100 * (prof[:, 7] / tot).mean():.1f}%")
-        parts.append(f"run prologue (x to registers) {100 * (prof[:, 14] / tot).mean():.1f}%, own-tile setup {100 * (prof[:, 13] / tot).mean():.1f}%, loop iterations {prof[:, 15].mean():.0f}")
+        parts.append(f"loop: top-of-iteration gaps {100 * (prof[:, 12] / tot).mean():.1f}% over {prof[:, 13].mean():.0f} iterations, after last tile of an op {100 * (prof[:, 14] / tot).mean():.1f}%, next-op descriptor {100 * (prof[:, 15] / tot).mean():.1f}%")
         nb_ = max(s.barriers, 1)
         parts.append("per barrier clk: CTA sync %.0f, release %.0f, poll %.0f, acquire %.0f" % tuple(prof[:, 8 + i].mean() / nb_ for i in range(4)))
         print("    profile: " + "; ".join(parts), flush=True)
