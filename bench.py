@@ -583,6 +583,41 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
 
     barrier()      # rank 0 spent time in the CPU check; peers must not sit in a gather kernel waiting for it
 
+    # ---- the persistent launch is timed only where it is the faster of the two paths on this list; both numbers are
+    # reported (config.one_launch_per_step).  NOTE on what the list is: every matmul reads an activation buffer that no
+    # matmul of the list writes (the model's element-wise ops sit between them and are not part of this set), so the
+    # only data hazards are the dst buffers the layers reuse.  One launch per mul_mat serialises on stream order
+    # (except ops that share src1); the persistent launch orders by those hazards.  On a list CHAINED like the model
+    # (x of an op = dst of an earlier one) it is the slower path: tools/sweep_set.py, profiles/r01_set_sweep_v3*.log.
+    if opset is not None:
+        def quick(fn, n=30):
+            with torch.cuda.stream(stream):
+                for _ in range(3):
+                    fn()
+            stream.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            with torch.cuda.stream(stream):
+                e0.record(stream)
+                for _ in range(n):
+                    fn()
+                e1.record(stream)
+            stream.synchronize()
+            return e0.elapsed_time(e1) / n
+        g_po = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g_po, stream=stream):
+            mod.set_stream(torch.cuda.current_stream().cuda_stream)
+            one_step_per_op()
+        mod.set_stream(stream.cuda_stream)
+        ms_po, ms_set = quick(g_po.replay), quick(opset.run)
+        del g_po
+        set_note["ms_per_step_one_launch_per_step"] = ms_set
+        set_note["ms_per_step_one_launch_per_mul_mat"] = ms_po
+        set_note["GBps_one_launch_per_mul_mat"] = total_bytes / (ms_po * 1e-3) / 1e9
+        set_note["timed_path"] = "one launch per step" if ms_set < ms_po else "one launch per mul_mat (faster here)"
+        if not ms_set < ms_po:
+            opset.free()
+            opset = None
+
     # ---- capture one step in a CUDA graph (launch-bound otherwise: 450 short kernels per step)
     with torch.cuda.stream(stream):
         for _ in range(2):
@@ -810,10 +845,12 @@ def main():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--unfused", action="store_true", help="kernel 1 + kernel 2 as separate launches")
     ap.add_argument("--no-pdl", action="store_true")
-    ap.add_argument("--set", dest="no_set", action="store_false", default=True,
-                    help="time the persistent multi-op launch (ggml_b200_set_*) instead of one launch per mul_mat; off by default: "
-                         "on a dependent list it is not faster yet (profiles/r01_set_sweep_*.log, tools/sweep_set.py)")
+    ap.add_argument("--no-set", action="store_true",
+                    help="never time the persistent multi-op launch (ggml_b200_set_*); by default it is probed in a child process, "
+                         "checked against the per-op path and timed when it is the faster of the two on this list")
+    ap.add_argument("--set", action="store_true", help=argparse.SUPPRESS)      # (the default now; kept for old command lines)
     ap.add_argument("--probe-set", action="store_true", help=argparse.SUPPRESS)
+    ap.add_argument("--no-probe", action="store_true", help="skip the child-process health probe of the persistent launch (profiler runs)")
     ap.add_argument("--no-overlap", action="store_true", help="every matmul waits for the previous one even when they only share src1")
     ap.add_argument("--tune", action="append", default=[], help="key=value for ggml_b200_set_tuning")
     ap.add_argument("--no-check", action="store_true")
@@ -834,10 +871,10 @@ def main():
     if args.impl == "reference":
         run_reference_impl(args, workload, rank)
         return
-    if world == 1 and not args.no_set and not args.unfused and not args.probe_set:
+    if world == 1 and not args.no_set and not args.unfused and not args.probe_set and not args.no_probe:
         # The persistent launch spins on device-side barriers: prove it healthy in a CHILD process first (a trapped
         # kernel poisons its CUDA context), and time one launch per mul_mat if it is not.
-        cmd = [sys.executable, os.path.abspath(__file__), "--probe-set", "--layers", "2", "--workload", workload,
+        cmd = [sys.executable, os.path.abspath(__file__), "--probe-set", "--set", "--layers", "2", "--workload", workload,
                "--no-cpu", "--no-prefill", "--no-check"] + [a for kv in args.tune for a in ("--tune", kv)]
         try:
             pr = subprocess.run(cmd, timeout=600, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
