@@ -44,7 +44,7 @@ constexpr int SET_BAR_BYTES = 2 * SET_MAX_SLOTS * 8;
 constexpr int SET_MAX_NBK_WPR1 = 128; // blocks per row a single warp keeps x for (4 per lane)
 constexpr int SET_MAX_NBK = 768;      // 6 per lane of a 4-warp team (K <= 24576)
 
-enum { SET_OP_BARRIER = 1, SET_OP_QUANT = 2 };
+enum { SET_OP_BARRIER = 1, SET_OP_QUANT = 2, SET_OP_XEXT = 4 };   // XEXT: no op of the list writes x (it may be cached / fetched early)
 
 struct SetOp {                        // 80 bytes, device resident, read-only during the launch
     const uint4 * wq;                 // nibble plane of this shard [rows][nbk]
@@ -159,7 +159,7 @@ __device__ __forceinline__ void set_load_tagged8(const unsigned long long * __re
 
 template <int NCONS>
 __device__ __forceinline__ void set_quantize_x(GemvSmem<1> & s, const float * __restrict__ x, const unsigned long long * __restrict__ xtag,
-                                               unsigned long long tag, int nbk, int tid) {
+                                               unsigned long long tag, int nbk, int tid, bool ext) {
     const int total = nbk * 4;
     uint32_t * lo32 = reinterpret_cast<uint32_t *>(s.lo);
     uint32_t * hi32 = reinterpret_cast<uint32_t *>(s.hi);
@@ -171,8 +171,13 @@ __device__ __forceinline__ void set_quantize_x(GemvSmem<1> & s, const float * __
             if (item >= total) item = total - 1;
             a[p] = make_float4(0.f, 0.f, 0.f, 0.f); c[p] = a[p];
             if (xtag == nullptr) {
-                a[p] = __ldcg(reinterpret_cast<const float4 *>(x + 8 * item));
-                c[p] = __ldcg(reinterpret_cast<const float4 *>(x + 8 * item) + 1);
+                if (ext) {       // immutable during the launch: L1 may hold it (prefetched there during the previous run)
+                    a[p] = __ldca(reinterpret_cast<const float4 *>(x + 8 * item));
+                    c[p] = __ldca(reinterpret_cast<const float4 *>(x + 8 * item) + 1);
+                } else {
+                    a[p] = __ldcg(reinterpret_cast<const float4 *>(x + 8 * item));
+                    c[p] = __ldcg(reinterpret_cast<const float4 *>(x + 8 * item) + 1);
+                }
             }
         }
 #pragma unroll
@@ -279,11 +284,13 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
     uint4 xlo[NCL], xhi[NCL];
     float dx[NCL];
     int s8[NCL];
+    unsigned vmask = 0;                                 // bit u: this lane's u-th block exists in the row
 #pragma unroll
     for (int u = 0; u < NCL; u++) {
         const int b = tl + STRIDE * u;
         xlo[u] = make_uint4(0, 0, 0, 0); xhi[u] = make_uint4(0, 0, 0, 0); dx[u] = 0.0f; s8[u] = 0;
         if (b < nbk) {
+            vmask |= 1u << u;
             xlo[u] = xs.lo[b]; xhi[u] = xs.hi[b];
             const int2 ds = xs.ds[b];
             dx[u] = __int_as_float(ds.x); s8[u] = ds.y;
@@ -317,23 +324,26 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
             float acc[RPT];
 #pragma unroll
             for (int r = 0; r < RPT; r++) acc[r] = 0.0f;
+            // Straight-line over the lane's NCL blocks: a lane whose block index is past the row re-reads the row's last
+            // block (valid shared memory, finite or not) and only its final accumulate is predicated off, so there
+            // is no branch between the 2*NCL*RPT loads and the dots and the scheduler can overlap all of them.
 #pragma unroll
             for (int u = 0; u < NCL; u++) {
                 const int b = tl + STRIDE * u;
-                if (b < nbk) {
-                    uint4 q[RPT];
-                    unsigned short dh[RPT];
+                const int ba = min(b, nbk - 1);
+                uint4 q[RPT];
+                unsigned short dh[RPT];
 #pragma unroll
-                    for (int r = 0; r < RPT; r++) {
-                        q[r] = *reinterpret_cast<const uint4 *>(nib + ((size_t)r * nbk + b) * 16);
-                        dh[r] = *reinterpret_cast<const unsigned short *>(sc + ((size_t)r * nbk + b) * 2);
-                    }
+                for (int r = 0; r < RPT; r++) {
+                    q[r] = *reinterpret_cast<const uint4 *>(nib + ((size_t)r * nbk + ba) * 16);
+                    dh[r] = *reinterpret_cast<const unsigned short *>(sc + ((size_t)r * nbk + ba) * 2);
+                }
 #pragma unroll
-                    for (int r = 0; r < RPT; r++) {
-                        const int sb = block_dot_q4_q8_fast(q[r], xlo[u], xhi[u], s8[u]);
-                        if (DUMP) { if (op.S != nullptr && r < nvalid) op.S[(size_t)(row0 + r) * nbk + b] = sb; }
-                        acc[r] = fmaf((float)sb, half_bits_to_float(dh[r]) * dx[u], acc[r]);
-                    }
+                for (int r = 0; r < RPT; r++) {
+                    const int sb = block_dot_q4_q8_fast(q[r], xlo[u], xhi[u], s8[u]);
+                    if (DUMP) { if (op.S != nullptr && r < nvalid && b < nbk) op.S[(size_t)(row0 + r) * nbk + b] = sb; }
+                    const float t = fmaf((float)sb, half_bits_to_float(dh[r]) * dx[u], acc[r]);
+                    if ((vmask >> u) & 1u) acc[r] = t;
                 }
             }
             // the slot's bytes of this warp are in registers: hand the slot back before the reduction
@@ -499,8 +509,22 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
         }
         if (PROF) { const long long t1 = clock64(); t_bar += t1 - tq0; tq0 = t1; }
         // the planes are free: every warp passed the CTA barrier that follows its register load of the previous run
-        set_quantize_x<NCONS>(xs, x, op.xtag, c.tag, nbk, tid);
+        set_quantize_x<NCONS>(xs, x, op.xtag, c.tag, nbk, tid, (flags & SET_OP_XEXT) != 0);
         set_consumer_sync<NCONS>();
+        // x of the NEXT run, when nothing in the list writes it and no barrier (whose fence drops L1) precedes it: ask L1
+        // for it now, so that the loads at the next change of x do not pay an L2 round trip (~1 100 clk under load)
+        if (tbl != nullptr) {
+            int n = o + 1;
+            while (n < nops && !((tbl[n].fm_flags >> 16) & SET_OP_QUANT)) n++;
+            if (n < nops) {
+                const int fl = tbl[n].fm_flags >> 16;
+                if ((fl & SET_OP_XEXT) && !(fl & SET_OP_BARRIER)) {
+                    const float * xn = tbl[n].x;
+                    const int total_n = tbl[n].nbk * 4;
+                    for (int item = tid; item < total_n; item += NCONS) asm volatile("prefetch.global.L1 [%0];" ::"l"(xn + 8 * item));
+                }
+            }
+        }
         long long tr0 = 0;
         if (PROF) { tr0 = clock64(); t_quant += tr0 - tq0; }
         if (nbk <= SET_MAX_NBK_WPR1) {

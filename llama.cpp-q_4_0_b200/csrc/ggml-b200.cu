@@ -500,6 +500,7 @@ int ggml_b200_set_tuning(const char * key, int value) {
     else if (!strcmp(key, "set_unsafe_no_barriers")) { g.tune.set_unsafe_no_barriers = value != 0; }
     else if (!strcmp(key, "set_link"))     { g.tune.set_link = value != 0; }
     else if (!strcmp(key, "set_fly"))      { g.tune.set_fly = value; }
+    else if (!strcmp(key, "set_xext"))     { g.tune.set_xext = value != 0; }
     else if (!strcmp(key, "set_table"))    { g.tune.set_table = value != 0; }
     else if (!strcmp(key, "set_slots"))    { g.tune.set_slots = value; }
     else if (!strcmp(key, "p2p_gather"))   { comm_set_p2p(value); }

@@ -161,6 +161,13 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
     }
     (void)NG;
     s->smem = (size_t)s->x_bytes + SET_BAR_BYTES + SET_RED_BYTES + s->tbl_bytes + (size_t)s->nslots * s->slot_bytes;
+    // x that no op of the list writes: the kernel may cache it and fetch it ahead of the run that needs it
+    for (SetOp & o : s->host_ops) {
+        if (!(o.flags & SET_OP_QUANT) || !g.tune.set_xext) continue;
+        bool written = false;
+        for (const SetOp & q : s->host_ops) if (set_ranges_overlap(o.x, o.x + (size_t)o.nbk * QK, q.y, q.y + q.rows)) written = true;
+        if (!written) o.flags |= SET_OP_XEXT;
+    }
     {
         size_t words = 0;
         std::vector<long long> off(s->host_ops.size(), -1);

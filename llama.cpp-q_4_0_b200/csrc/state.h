@@ -41,10 +41,11 @@ struct Tune {
     int overlap_same_src = 0;    // n == 1: an op that reads the same x as the previous one does not wait for it (caller owns the stream)
     int host_fast = 1;           // n == 1 host entry: single-launch path with mapped staging rows and a completion word
     int set_coop = 1;            // persistent multi-op kernel: cooperative launch (the driver checks co-residency of the grid)
-    int set_warps = 8;           // its consumer warps per CTA (8, 12, 16 or 20)
+    int set_warps = 12;          // its consumer warps per CTA (8, 12, 16 or 20)
     int set_unsafe_no_barriers = 0;   // MEASUREMENT ONLY: drop the dependency barriers (results are wrong when ops depend on each other)
     int set_link = 1;            // x that is exactly the dst of one earlier op is read from that op's tagged rows (0: grid barrier instead)
     int set_fly = 0;             // bulk copies in flight per CTA (0 = as many as the ring has free slots)
+    int set_xext = 1;            // x that nothing in the list writes is loaded through L1 and prefetched one run ahead
     int set_table = 1;           // stage the op descriptors in shared memory when the list fits
     int set_slots = 0;           // cap on its ring depth (0 = as many as fit)
     int skip_quantize = 0;       // bench only: reuse the activations quantized by the previous call

@@ -85,7 +85,7 @@ def test_set_chain_bit_identical_to_per_op_calls(b200, port, ref, warps, shapes,
                 xin[gi + 1] = got[i]
         s.free()
     finally:
-        b200.set_tuning("set_warps", 8)
+        b200.set_tuning("set_warps", 12)
     for w in ws:
         w.free()
 
