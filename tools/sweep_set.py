@@ -19,6 +19,8 @@ def main():
     ap.add_argument("--workload", default="llama7b_decode_n1")
     ap.add_argument("--configs", default="16:0,12:0,8:0,16:0:bar,16:0:nb",
                     help="warps:slots[:nb]; nb = without dependency barriers (NOT the op semantics: streaming ceiling of the kernel only)")
+    ap.add_argument("--bench-list", action="store_true",
+                    help="buffers as bench.py has them (x from outside the list, one dst per position in the layer, reused by every layer) instead of the chained list")
     args = ap.parse_args()
     import torch
     mod = bench.load_binding()
@@ -43,7 +45,19 @@ def main():
     total = sum(bench.algo_bytes(M, K) for (_, M, K) in handles)
     # the list as the model chains it (llama.cpp:1394-1504 minus the element-wise ops): wq/wk/wv read the layer input,
     # wo reads wq's result, w3/w1 read wo's, w2 reads w1's, the next layer reads w2's; every matmul has its own dst
-    ops, h_in = bench.chain_ops(torch, handles, shapes, L)
+    if args.bench_list:
+        grp_of = [0, 0, 0, 1, 2, 2, 3]
+        xg, ygb, ops = {}, {}, []
+        for idx, (h, M, K) in enumerate(handles):
+            pos = idx % 7 if idx < L * 7 else 7 + idx - L * 7
+            g_ = grp_of[pos] if pos < 7 else 4
+            if g_ not in xg:
+                xg[g_] = torch.from_numpy(rng.standard_normal((1, K), dtype=np.float32)).cuda()
+            if pos not in ygb:
+                ygb[pos] = torch.zeros((1, M), dtype=torch.float32, device="cuda")
+            ops.append((h, xg[g_].data_ptr(), ygb[pos].data_ptr(), ygb[pos]))
+    else:
+        ops, h_in = bench.chain_ops(torch, handles, shapes, L)
     torch.cuda.synchronize()
     print(f"list: {len(ops)} ops, {total / 1e9:.3f} GB algorithmic per run", flush=True)
 
@@ -70,7 +84,7 @@ def main():
     with torch.cuda.stream(stream):
         per_op(); per_op()
     stream.synchronize()
-    yg = {i: t for i, (w, xp, yp, t) in enumerate(ops)}
+    yg = {yp: t for (w, xp, yp, t) in ops}
     ops = [(w, xp, yp) for (w, xp, yp, t) in ops]
     want = {p: y.cpu().numpy().copy() for p, y in yg.items()}
     g = torch.cuda.CUDAGraph()
