@@ -44,7 +44,10 @@ constexpr int SET_BAR_BYTES = 2 * SET_MAX_SLOTS * 8;
 constexpr int SET_MAX_NBK_WPR1 = 128; // blocks per row a single warp keeps x for (4 per lane)
 constexpr int SET_MAX_NBK = 768;      // 6 per lane of a 4-warp team (K <= 24576)
 
-enum { SET_OP_BARRIER = 1, SET_OP_QUANT = 2, SET_OP_XEXT = 4 };   // XEXT: no op of the list writes x (it may be cached / fetched early)
+enum { SET_OP_BARRIER = 1, SET_OP_QUANT = 2, SET_OP_XEXT = 4 };
+// flags bits 8..14: how many dependency barriers every consumer warp arrives at when it has finished this op
+constexpr int SET_OP_ARRIVE_SHIFT = 8, SET_OP_ARRIVE_MASK = 0x7F;
+//   // XEXT: no op of the list writes x (it may be cached / fetched early)
 
 struct SetOp {                        // 80 bytes, device resident, read-only during the launch
     const uint4 * wq;                 // nibble plane of this shard [rows][nbk]
@@ -107,30 +110,39 @@ __device__ __forceinline__ void set_consumer_sync() {
     asm volatile("bar.sync 1, %0;" ::"n"(NCONS) : "memory");
 }
 
-// All consumer threads of every CTA; `target` = arrivals that complete this barrier.  One release (the CTA's y
-// stores, ordered before thread 0 by the CTA barrier, become visible before the count), relaxed polls, one
-// acquire fence: every GPU-scope fence costs an L2 round trip under a saturated memory system, so there are
-// exactly two on the critical path.
-template <int NCONS, bool PROF>
-__device__ __forceinline__ void set_grid_barrier(SetSync * sync, unsigned target, long long * tp) {
-    long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;
-    if (PROF) c0 = clock64();
-    set_consumer_sync<NCONS>();
-    if (threadIdx.x == 0) {
-        if (PROF) c1 = clock64();
-        red_release_gpu_add_u32(&sync->arrived, 1u);
-        if (PROF) c2 = clock64();
-        unsigned long long t0 = 0;
-        while ((int)(ld_relaxed_gpu_u32(&sync->arrived) - target) < 0) {
-            const unsigned long long t1 = gtime();
-            if (t0 == 0) t0 = t1;
-            if (t1 - t0 > 10000000000ull) __trap();   // a CTA of the grid is not resident / died: fail, do not hang
-        }
-        if (PROF) c3 = clock64();
-        fence_acq_rel_gpu();
-        if (PROF) { tp[0] += c1 - c0; tp[1] += c2 - c1; tp[2] += c3 - c2; tp[3] += clock64() - c3; }
+// Dependency barrier, split in two.  ARRIVE: a consumer warp that has finished the last op the waiting run conflicts
+// with counts itself in shared memory (CTA-scope release: its y stores -- lane 0's, or the lanes' before the
+// __syncwarp -- are ordered before the count); when all warps of the CTA have, the sentinel adds the CTA to the
+// grid-wide counter with a GPU-scope release, which by cumulativity covers those stores.  No consumer thread ever
+// executes a GPU-scope fence or atomic.  WAIT (thread 0 of the CTA, at the head of the run): relaxed polls until every
+// consumer warp of the grid has arrived, then one acquire fence; the CTA barrier that follows the quantization of x
+// hands the result to the other threads.  The arrival point is usually several ops before the wait (a layer's wq
+// against the next layer's wq: four ops), so the poll finds the count complete and a barrier costs two L2 round
+// trips of one thread that has nothing else to do (set_barrier_wait below) instead of a grid-wide rendezvous.
+__device__ __forceinline__ void set_barrier_arrive(uint32_t done_local, int lane) {
+    __syncwarp();
+    if (lane == 0) asm volatile("red.release.cta.shared.add.u32 [%0], 1;" ::"r"(done_local) : "memory");
+}
+// WAIT, by the CTA's sentinel thread (a warp of its own with nothing else to do, so the two L2 round trips -- the poll
+// that finds the count complete and the acquire fence -- are off the consumers' path): it walks the list ahead of the
+// consumers and publishes the number of barriers it has seen complete in shared memory.
+__device__ __forceinline__ void set_barrier_wait(const unsigned * cnt, unsigned target) {
+    unsigned long long t0 = 0;
+    while (ld_relaxed_gpu_u32(cnt) < target) {
+        __nanosleep(100);
+        const unsigned long long t1 = gtime();
+        if (t0 == 0) t0 = t1;
+        if (t1 - t0 > 10000000000ull) __trap();   // a CTA of the grid is not resident / died: fail, do not hang
     }
-    set_consumer_sync<NCONS>();
+    fence_acq_rel_gpu();
+}
+__device__ __forceinline__ void st_release_cta_shared_u32(uint32_t addr, unsigned v) {
+    asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_cta_shared_u32(uint32_t addr) {
+    unsigned v;
+    asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
 }
 
 // kernel 1 inside the CTA (quantize_row_q8_0, AVX2 contract ggml.c:1192-1250; arithmetic of quantize_x_to_smem):
@@ -262,6 +274,7 @@ struct SetCtx {
     int nslots, slot_bytes;
     int G, group, wig, lane;
     unsigned long long tag;           // launch number << 32
+    uint32_t done_local;              // shared-memory count of consumer warps past the ops that barriers wait for
 };
 
 // ring position of the CTA's next tile: slot index and the parity of its current use
@@ -314,6 +327,13 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
             const uint32_t full = c.full0 + 8 * rp.s, empty = c.empty0 + 8 * rp.s;
             long long tf0 = 0;
             if (PROF) tf0 = clock64();
+            // A parity wait can only tell the current phase of a barrier from the one before it.  The slot's previous use
+            // may belong to ANOTHER group and its copy may still be in flight although later copies have landed (bulk
+            // copies complete in any order): `full` would then be one phase behind what this warp assumes and the wait
+            // would fall through on the phase before that.  The previous use having been RELEASED (its `empty` phase;
+            // that wait cannot alias: this tile's predecessors were issued after the use before that was released)
+            // pins `full` to the phase waited for.  (The two tests must not be overlapped: issued back to back they failed.)
+            if (j >= c.nslots) mbar_wait(empty, rp.phase ^ 1);
             mbar_wait(full, rp.phase);
             long long tc0 = 0;
             if (PROF) { tc0 = clock64(); t_full += tc0 - tf0; n_tiles++; }
@@ -378,6 +398,10 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
             if (PROF) { tl0 = clock64(); t_comp += tl0 - tc0; }
         }
         if (PROF) { const long long now = clock64(); tx[2] += now - tl0; tl0 = now; }
+        {
+            const int narr = (op.flags >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK;
+            if (narr) set_barrier_arrive(c.done_local, c.lane);      // a later run waits for this op (and everything before it)
+        }
         o++;
         if (o >= c.nops) break;
         op = set_load_op<DUMP>(c.ops, c.tbl, o);      // shared-memory table (lists beyond SET_MAX_TABLE_BYTES: an L2 round trip per op)
@@ -391,7 +415,7 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
 // {whole kernel, consumer warp 0 waiting for full slots, in dependency barriers, quantizing x, producer waiting for empty slots}
 // BIG: also the 6-blocks-per-lane plan (K > 16384); the kernel without it needs fewer registers
 template <int W, bool DUMP, bool PROF, bool BIG>
-__global__ void __launch_bounds__(W * 32 + 32, 1)
+__global__ void __launch_bounds__(W * 32 + 96, 1)
 gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restrict__ sync, int nslots, int slot_bytes,
                      int x_bytes, int tbl_bytes, int max_fly, unsigned seq, long long * __restrict__ prof) {
     constexpr int NCONS = W * 32;
@@ -409,8 +433,16 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
     const int warp = tid >> 5;
     const int G = gridDim.x;
 
+    // one arrival counter per barrier behind the sync words: a CTA may be several arrival points ahead of another, so a
+    // single running count would not say WHO has arrived
+    unsigned * bar_cnt = reinterpret_cast<unsigned *>(sync + 1);
     __shared__ unsigned s_launch;
+    __shared__ unsigned s_bar_passed;                         // dependency barriers the sentinel has seen complete
+    __shared__ unsigned s_done_local;
+    const uint32_t bar_passed = smem_u32(&s_bar_passed), done_local = smem_u32(&s_done_local);
     if (tid == 0) {
+        s_bar_passed = 0u;
+        s_done_local = 0u;
         for (int s = 0; s < nslots; s++) {
             mbar_init(full0 + 8 * s, 1);
             mbar_init(empty0 + 8 * s, SET_WPG);
@@ -482,12 +514,51 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
         return;
     }
 
+    if (warp == W + 1) {
+        // ===== wait sentinel: waits for the list's dependency barriers, in order, as far ahead of the consumers as the
+        // arrivals allow; publishes how many it has seen complete =====
+        if (lane == 0) {
+            unsigned k = 0;
+            for (int o = 0; o < nops; o++) {
+                const int fl = tbl != nullptr ? (tbl[o].fm_flags >> 16) : ops[o].flags;
+                if (!(fl & SET_OP_BARRIER)) continue;
+                k++;
+                set_barrier_wait(bar_cnt + (k - 1), (unsigned)G);
+                st_release_cta_shared_u32(bar_passed, k);
+            }
+        }
+        return;
+    }
+    if (warp == W + 2) {
+        // ===== arrive sentinel: when every consumer warp of this CTA is past an op that barriers wait for, the CTA
+        // arrives at them (a thread of its own: the release must not sit behind the other sentinel's polls) =====
+        if (lane == 0) {
+            unsigned ev = 0, kb = 0;
+            for (int o = 0; o < nops; o++) {
+                const int fl = tbl != nullptr ? (tbl[o].fm_flags >> 16) : ops[o].flags;
+                const int narr = (fl >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK;
+                if (!narr) continue;
+                ev++;
+                unsigned long long t0 = 0;
+                while ((int)(ld_acquire_cta_shared_u32(done_local) - ev * (unsigned)W) < 0) {
+                    __nanosleep(64);
+                    const unsigned long long t1 = gtime();
+                    if (t0 == 0) t0 = t1;
+                    if (t1 - t0 > 10000000000ull) __trap();
+                }
+                for (int i = 0; i < narr; i++) red_release_gpu_add_u32(bar_cnt + kb++, 1u);      // barriers are numbered in the order of their arrival points
+            }
+        }
+        return;
+    }
+
     // ===== consumers =====
     SetCtx c;
     c.ops = ops; c.tbl = tbl; c.nops = nops; c.ring = ring; c.red = reinterpret_cast<float *>(smem + x_bytes + SET_BAR_BYTES);
     c.full0 = full0; c.empty0 = empty0; c.nslots = nslots; c.slot_bytes = slot_bytes;
     c.G = G; c.group = warp / SET_WPG; c.wig = warp % SET_WPG; c.lane = lane;
     c.tag = (unsigned long long)s_launch << 32;
+    c.done_local = done_local;
     SetRing rp = {0, 0};
     int j = 0;
     unsigned nbar = 0, ntile_team = 0;
@@ -503,22 +574,25 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
         const float * x = op.x;
         long long tq0 = 0;
         if (PROF) tq0 = clock64();
+        const bool ext = (flags & SET_OP_XEXT) != 0;
         if (flags & SET_OP_BARRIER) {
+            // every thread sees for itself that the sentinel has passed this barrier (normally long ago: the arrival
+            // point lies ops back); x that an op of the list writes and this run's y stores come after it
             nbar++;
-            set_grid_barrier<NCONS, PROF>(sync, nbar * (unsigned)G, tp);
+            while ((int)(ld_acquire_cta_shared_u32(bar_passed) - nbar) < 0) { }
         }
         if (PROF) { const long long t1 = clock64(); t_bar += t1 - tq0; tq0 = t1; }
         // the planes are free: every warp passed the CTA barrier that follows its register load of the previous run
-        set_quantize_x<NCONS>(xs, x, op.xtag, c.tag, nbk, tid, (flags & SET_OP_XEXT) != 0);
+        set_quantize_x<NCONS>(xs, x, op.xtag, c.tag, nbk, tid, ext);
         set_consumer_sync<NCONS>();
-        // x of the NEXT run, when nothing in the list writes it and no barrier (whose fence drops L1) precedes it: ask L1
+        // x of the NEXT run, when nothing in the list writes it: ask L1
         // for it now, so that the loads at the next change of x do not pay an L2 round trip (~1 100 clk under load)
         if (tbl != nullptr) {
             int n = o + 1;
             while (n < nops && !((tbl[n].fm_flags >> 16) & SET_OP_QUANT)) n++;
             if (n < nops) {
                 const int fl = tbl[n].fm_flags >> 16;
-                if ((fl & SET_OP_XEXT) && !(fl & SET_OP_BARRIER)) {
+                if (fl & SET_OP_XEXT) {
                     const float * xn = tbl[n].x;
                     const int total_n = tbl[n].nbk * 4;
                     for (int item = tid; item < total_n; item += NCONS) asm volatile("prefetch.global.L1 [%0];" ::"l"(xn + 8 * item));
@@ -561,7 +635,7 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
         __threadfence();
         const unsigned old = atomicAdd(&sync->done, 1u);
         if (old == (unsigned)G - 1u) {
-            atomicExch(&sync->arrived, 0u);
+            for (unsigned i = 0; i < nbar; i++) atomicExch(bar_cnt + i, 0u);      // (every arrival has been observed: all barriers passed everywhere)
             atomicExch(&sync->done, 0u);
             atomicExch(&sync->epoch, s_launch);
         }

@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 #include <string.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "common.cuh"
@@ -43,7 +44,7 @@ static int set_launch_tb(const ggml_b200_set * s, const SetOp * table, long long
         attr_set = true;
     }
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)s->grid); cfg.blockDim = dim3(W * 32 + 32); cfg.dynamicSmemBytes = s->smem; cfg.stream = g.stream;
+    cfg.gridDim = dim3((unsigned)s->grid); cfg.blockDim = dim3(W * 32 + 96); cfg.dynamicSmemBytes = s->smem; cfg.stream = g.stream;
     // every CTA of the grid must be resident at once (dependency barriers spin on peers): cooperative launch makes
     // the driver check that instead of trusting it
     cudaLaunchAttribute attr[1];
@@ -95,6 +96,7 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
     std::vector<Range> live_x, live_y;
     std::vector<int> link_of;             // per host op: index of the host op whose staging rows its x is read from, or -1
     const float * run_x = nullptr; int64_t run_K = 0; int run_link = -1;
+    int arrive_mono = -1;
     for (int i = 0; i < n_ops; i++) {
         const ggml_b200_weight * w = ops[i].w;
         const float * x = ops[i].x_dev;
@@ -116,22 +118,59 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
         tiles += o.ntiles;
         const float * y_lo = o.y, * y_hi = o.y + o.rows;
         const float * x_hi = x + w->K;
+        // hazards of list entry j against the ops still live: does it need a barrier, behind which op, is its x one op's dst
+        auto hazards = [&](int j, bool & bar_, int & after_, int & link_) {
+            const ggml_b200_weight * wj = ops[j].w;
+            const float * xj = ops[j].x_dev, * xj_hi = xj + wj->K;
+            const float * yj_lo = ops[j].y_dev + wj->row_lo, * yj_hi = ops[j].y_dev + wj->row_hi;
+            for (const Range & r : live_x) if (set_ranges_overlap(yj_lo, yj_hi, r.lo, r.hi)) { bar_ = true; after_ = std::max(after_, r.op); }      // WAR
+            for (const Range & r : live_y) if (set_ranges_overlap(yj_lo, yj_hi, r.lo, r.hi)) { bar_ = true; after_ = std::max(after_, r.op); }      // WAW
+            int writers = 0, last_writer = -1;
+            link_ = -1;
+            for (const Range & r : live_y) {
+                if (!set_ranges_overlap(xj, xj_hi, r.lo, r.hi)) continue;
+                writers++;
+                last_writer = std::max(last_writer, r.op);
+                if (r.lo == xj && r.hi == xj_hi && r.whole) link_ = r.op; else bar_ = true;                   // RAW
+            }
+            if (writers > 1 || (link_ >= 0 && !g.tune.set_link)) bar_ = true;
+            if (bar_) after_ = std::max(after_, last_writer);
+        };
         bool barrier = false;
-        for (const Range & r : live_x) if (set_ranges_overlap(y_lo, y_hi, r.lo, r.hi)) barrier = true;      // WAR
-        for (const Range & r : live_y) if (set_ranges_overlap(y_lo, y_hi, r.lo, r.hi)) barrier = true;      // WAW
-        int link = -1, writers = 0;
-        for (const Range & r : live_y) {
-            if (!set_ranges_overlap(x, x_hi, r.lo, r.hi)) continue;
-            writers++;
-            if (r.lo == x && r.hi == x_hi && r.whole) link = r.op; else barrier = true;                   // RAW
+        int after = -1;                       // last earlier op this one conflicts with
+        int link = -1;
+        hazards(i, barrier, after, link);
+        if (barrier) {
+            // Split barrier: every warp ARRIVES when it has finished the last op this run conflicts with and WAITS here,
+            // usually several ops later, when the count is long complete.  Arrival points are kept monotonic so that one
+            // counter serves all barriers; ops after the arrival point stay live (the barrier says nothing about them).
+            // The ops that will share this run's x wait here too (a barrier of their own would split the run), and ops up
+            // to `set_barrier_slack` before the head are waited for as well: they have long finished (the wait stays
+            // free) and whatever later conflicts with them needs no barrier of its own.
+            for (int j = i + 1; j < n_ops && ops[j].w && ops[j].x_dev == x && ops[j].y_dev && ops[j].w->K == w->K; j++) {
+                if (ops[j].w->rows() == 0) continue;
+                bool b2 = false; int l2 = -1;
+                hazards(j, b2, after, l2);
+            }
+            const int prev = (int)s->host_ops.size() - 1;
+            after = std::max(std::max(after, arrive_mono), prev - std::max(g.tune.set_barrier_slack, 0));
+            if (after > prev || !g.tune.set_split_barrier) after = prev;
+            while (after >= 0 && after + 1 < (int)s->host_ops.size() && ((s->host_ops[after].flags >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK) >= SET_OP_ARRIVE_MASK) after++;
+            arrive_mono = after;
+            auto dead = [&](const Range & r) { return r.op <= after; };
+            live_x.erase(std::remove_if(live_x.begin(), live_x.end(), dead), live_x.end());
+            live_y.erase(std::remove_if(live_y.begin(), live_y.end(), dead), live_y.end());
+            link = -1;
         }
-        if (writers > 1 || (link >= 0 && !g.tune.set_link)) barrier = true;
-        if (barrier) { live_x.clear(); live_y.clear(); link = -1; }
         const bool same_run = !s->host_ops.empty() && !barrier && run_x == x && run_K == w->K && run_link == link;
         if (!same_run) {
             const bool bar = barrier && !s->host_ops.empty() && !g.tune.set_unsafe_no_barriers;
             o.flags = SET_OP_QUANT | (bar ? SET_OP_BARRIER : 0);
-            if (bar) s->barriers++;
+            if (bar) {
+                s->barriers++;
+                if (((s->host_ops[after].flags >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK) >= SET_OP_ARRIVE_MASK) { set_error("set op %d: too many dependency barriers behind one op", i); delete s; return nullptr; }
+                s->host_ops[after].flags += 1 << SET_OP_ARRIVE_SHIFT;
+            }
             if (link >= 0) s->linked_runs++;
             run_x = x; run_K = w->K; run_link = link;
         }
@@ -154,12 +193,15 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
     const long long ring = (long long)MAX_DYN_SMEM - 1024 - s->x_bytes - SET_BAR_BYTES - SET_RED_BYTES - s->tbl_bytes - 128;
     s->nslots = (int)(ring / s->slot_bytes);
     if (s->nslots > SET_MAX_SLOTS) s->nslots = SET_MAX_SLOTS;
-    if (g.tune.set_slots > 0 && g.tune.set_slots < s->nslots) s->nslots = g.tune.set_slots;
+    // Measured (profiles/r01_set_sweep_v5_slots.log, LLaMA-7B list, 12 warps): 3 slots 832 us, 4: 757, 5: 793, 6: 801, 8: 802 -- a ring
+    // one slot deeper than the number of consumer groups keeps the stream busy, and what the ring does not take stays L1
+    // (x of the next run is prefetched there).  set_slots overrides.
+    if (g.tune.set_slots > 0) { if (g.tune.set_slots < s->nslots) s->nslots = g.tune.set_slots; }
+    else if (s->nslots > NG + 1) s->nslots = NG + 1;
     if (s->nslots < 2) {
         set_error("K = %d: a 4-row tile (%d B) does not fit the shared-memory ring twice; use ggml_b200_mul_mat_q4_0 per op", nbk_max * QK, s->slot_bytes);
         delete s; return nullptr;
     }
-    (void)NG;
     s->smem = (size_t)s->x_bytes + SET_BAR_BYTES + SET_RED_BYTES + s->tbl_bytes + (size_t)s->nslots * s->slot_bytes;
     // x that no op of the list writes: the kernel may cache it and fetch it ahead of the run that needs it
     for (SetOp & o : s->host_ops) {
@@ -184,9 +226,9 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
         }
     }
     cudaError_t e = cudaMalloc(&s->dev_ops, s->host_ops.size() * sizeof(SetOp));
-    if (e == cudaSuccess) e = cudaMalloc(&s->sync, sizeof(SetSync));
+    if (e == cudaSuccess) e = cudaMalloc(&s->sync, sizeof(SetSync) + 4 * (size_t)(s->barriers + 1));      // + one arrival counter per barrier
     if (e == cudaSuccess) e = cudaMemcpy(s->dev_ops, s->host_ops.data(), s->host_ops.size() * sizeof(SetOp), cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = cudaMemset(s->sync, 0, sizeof(SetSync));
+    if (e == cudaSuccess) e = cudaMemset(s->sync, 0, sizeof(SetSync) + 4 * (size_t)(s->barriers + 1));
     if (e != cudaSuccess) { cuda_fail(e, "set_create", __FILE__, __LINE__); ggml_b200_set_free(s); return nullptr; }
     return s;
 }

@@ -45,6 +45,8 @@ struct Tune {
     int set_unsafe_no_barriers = 0;   // MEASUREMENT ONLY: drop the dependency barriers (results are wrong when ops depend on each other)
     int set_link = 1;            // x that is exactly the dst of one earlier op is read from that op's tagged rows (0: grid barrier instead)
     int set_fly = 0;             // bulk copies in flight per CTA (0 = as many as the ring has free slots)
+    int set_split_barrier = 1;   // dependency barriers: arrive after the last conflicting op, wait at the run that needs it (0: arrive right before the wait)
+    int set_barrier_slack = 1 << 20;   // a dependency barrier also waits for everything up to this many ops before its run (default: only for what the run conflicts with, i.e. arrive as early as possible)
     int set_xext = 1;            // x that nothing in the list writes is loaded through L1 and prefetched one run ahead
     int set_table = 1;           // stage the op descriptors in shared memory when the list fits
     int set_slots = 0;           // cap on its ring depth (0 = as many as fit)

@@ -67,7 +67,7 @@ def test_set_chain_bit_identical_to_per_op_calls(b200, port, ref, warps, shapes,
         s = b200.OpSet(ops)
         assert s.n_ops == len(ops)
         assert s.barriers == 0 and s.linked_runs == len(shapes) - 1     # every change of x is "the dst of one earlier op"
-        assert s.slots >= 4
+        assert s.slots >= 3             # one more than the consumer groups (8 warps = 2 groups) or what fits
         c0 = b200.launch_count()
         for _ in range(30):
             s.run()
@@ -221,4 +221,101 @@ def test_set_replays_in_a_cuda_graph(b200, port, ref):
         assert b200.lib().ggml_b200_get_stream() == old or True
     s.free()
     for w in ws:
+        w.free()
+
+
+@pytest.mark.parametrize("warps,slots", [(12, 0), (12, 4), (8, 3), (16, 5), (12, 8)])
+def test_set_tight_ring_many_tiles_per_cta(b200, port, ref, warps, slots):
+    """Regression: with a ring one slot deeper than the consumer groups, a group's next tile lives in the slot another
+    group is still being served from; a bulk copy that lands before an older one must not let the parity wait fall
+    through on the phase before (K = 8192: four warps per row, 14 tiles per CTA, natural ring depth; launch failure
+    before the fix).  30 launches back to back, results against the oracle and bit-identical from launch to launch."""
+    M, K = 2048, 8192
+    Ws = [make_weights(port, ref, M, K, 1100 + i) for i in range(4)]
+    ws = [b200.Weight(W) for W in Ws]
+    x = make_x(port, 1, K, 77)
+    xd = b200.DevBuf.from_numpy(x)
+    yd = [b200.DevBuf(M * 4) for _ in range(4)]
+    b200.set_tuning("set_warps", warps)
+    b200.set_tuning("set_slots", slots)
+    try:
+        s = b200.OpSet([(ws[i], xd.ptr, yd[i].ptr) for i in range(4)])
+        assert s.barriers == 0 and s.linked_runs == 0
+        s.run()
+        b200.synchronize()
+        first = [y.to_numpy(np.float32, (1, M)) for y in yd]
+        for _ in range(30):
+            s.run()
+        b200.synchronize()
+        for i in range(4):
+            got = yd[i].to_numpy(np.float32, (1, M))
+            assert np.array_equal(got, first[i])
+            assert_close(got, oracle_Y(port, ref, Ws[i], x))
+        s.free()
+    finally:
+        b200.set_tuning("set_warps", 12)
+        b200.set_tuning("set_slots", 0)
+    for w in ws:
+        w.free()
+
+
+def test_set_reused_dst_buffers_layer_after_layer(b200, port, ref):
+    """The decode graph's buffer pattern: x comes from outside the list, every position of a layer has one dst that the
+    next layer overwrites (write-after-write).  The barriers are split -- a CTA arrives when it has finished the op the
+    later run conflicts with and the wait happens ops later -- and the last writer must win, launch after launch."""
+    M = K = 1024
+    L, P = 6, 4                                    # layers x positions; positions 0,1 share x
+    Ws = [make_weights(port, ref, M + 8 * (i % P), K, 1200 + i) for i in range(L * P)]
+    ws = [b200.Weight(W) for W in Ws]
+    xh = [make_x(port, 1, K, 300 + g) for g in range(3)]
+    xd = [b200.DevBuf.from_numpy(x) for x in xh]
+    grp = [0, 0, 1, 2]
+    yd = [b200.DevBuf((M + 8 * p) * 4) for p in range(P)]
+    ops = [(ws[i], xd[grp[i % P]].ptr, yd[i % P].ptr) for i in range(L * P)]
+    s = b200.OpSet(ops)
+    assert s.linked_runs == 0 and 0 < s.barriers <= 3 * (L - 1) + 1
+    for _ in range(20):
+        s.run()
+    b200.synchronize()
+    for p in range(P):
+        i = (L - 1) * P + p
+        assert_close(yd[p].to_numpy(np.float32, (1, M + 8 * p)), oracle_Y(port, ref, Ws[i], xh[grp[p]]))
+    got = [yd[p].to_numpy(np.float32, (1, M + 8 * p)) for p in range(P)]
+    _per_op(b200, ops)
+    for p in range(P):
+        assert np.array_equal(got[p], yd[p].to_numpy(np.float32, (1, M + 8 * p)))
+    s.free()
+    for w in ws:
+        w.free()
+
+
+def test_set_x_written_by_two_row_shards_waits_for_both(b200, port, ref):
+    """x of the last op is the dst of TWO earlier ops (row shards of one matrix): not a single producer, so the run
+    waits at a barrier whose arrival point is the later shard; an unrelated op sits between them and the reader."""
+    M, K = 1024, 1024
+    W0 = make_weights(port, ref, M, K, 1300)
+    W1 = make_weights(port, ref, 520, K, 1301)
+    W2 = make_weights(port, ref, 777, M, 1302)
+    x0 = make_x(port, 1, K, 5)
+    xd = b200.DevBuf.from_numpy(x0)
+    y0 = b200.DevBuf(M * 4)
+    y1 = b200.DevBuf(520 * 4)
+    y2 = b200.DevBuf(777 * 4)
+    parts = [b200.Weight(W0, 0, 400), b200.Weight(W0, 400, M)]
+    w1, w2 = b200.Weight(W1), b200.Weight(W2)
+    ops = [(parts[0], xd.ptr, y0.ptr), (parts[1], xd.ptr, y0.ptr), (w1, xd.ptr, y1.ptr), (w2, y0.ptr, y2.ptr)]
+    s = b200.OpSet(ops)
+    assert s.barriers == 1 and s.linked_runs == 0
+    for _ in range(10):
+        s.run()
+    b200.synchronize()
+    h = oracle_Y(port, ref, W0, x0)
+    assert_close(y0.to_numpy(np.float32, (1, M)), h)
+    assert_close(y1.to_numpy(np.float32, (1, 520)), oracle_Y(port, ref, W1, x0))
+    got = y2.to_numpy(np.float32, (1, 777))
+    assert_close(got, oracle_Y(port, ref, W2, y0.to_numpy(np.float32, (1, M))))
+    _per_op(b200, ops)
+    assert np.array_equal(got, y2.to_numpy(np.float32, (1, 777)))
+    s.free()
+    for w in parts + [w1, w2]:
         w.free()

@@ -21,6 +21,8 @@ def main():
                     help="warps:slots[:nb]; nb = without dependency barriers (NOT the op semantics: streaming ceiling of the kernel only)")
     ap.add_argument("--bench-list", action="store_true",
                     help="buffers as bench.py has them (x from outside the list, one dst per position in the layer, reused by every layer) instead of the chained list")
+    ap.add_argument("--own-dst", action="store_true", help="with --bench-list: a dst per op (no write-after-write barriers)")
+    ap.add_argument("--one-x", action="store_true", help="with --bench-list: one x per K (runs change only where K changes)")
     args = ap.parse_args()
     import torch
     mod = bench.load_binding()
@@ -51,6 +53,10 @@ def main():
         for idx, (h, M, K) in enumerate(handles):
             pos = idx % 7 if idx < L * 7 else 7 + idx - L * 7
             g_ = grp_of[pos] if pos < 7 else 4
+            if args.one_x:
+                g_ = K
+            if args.own_dst:
+                pos = idx
             if g_ not in xg:
                 xg[g_] = torch.from_numpy(rng.standard_normal((1, K), dtype=np.float32)).cuda()
             if pos not in ygb:
@@ -100,6 +106,10 @@ def main():
         warps, slots = int(parts_[0]), int(parts_[1])
         fly = [int(v[3:]) for v in parts_[2:] if v.startswith("fly")]
         parts_ = [v for v in parts_ if not v.startswith("fly")]
+        mod.set_tuning("set_split_barrier", 0 if "ns" in parts_ else 1)
+        slack = [int(v[1:]) for v in parts_[2:] if v[0] == "s" and v[1:].isdigit()]
+        mod.set_tuning("set_barrier_slack", slack[0] if slack else (1 << 20))
+        parts_ = [v for v in parts_ if v != "ns" and not (v[0] == "s" and v[1:].isdigit())]
         mod.set_tuning("set_fly", fly[0] if fly else 0)
         mod.set_tuning("set_unsafe_no_barriers", 1 if parts_[2:] == ["nb"] else 0)
         mod.set_tuning("set_link", 0 if parts_[2:] in (["bar"], ["nb"]) else 1)
