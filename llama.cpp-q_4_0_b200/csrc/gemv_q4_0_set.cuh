@@ -37,6 +37,8 @@
 namespace b200 {
 
 constexpr int SET_WPG = 4;            // consumer warps per group
+constexpr int SET_XWARPS = 2;         // warps that quantize the NEXT run's x while the consumers work on this one
+constexpr int SET_EXTRA_THREADS = 32 /* producer */ + 32 /* sentinel */ + 32 * SET_XWARPS;
 constexpr int SET_MAX_SLOTS = 16;
 constexpr int SET_MAX_GROUPS = 6;
 constexpr int SET_RED_BYTES = 2 * SET_MAX_GROUPS * 16 * 4;   // cross-warp partials: [parity][group][row 4][warp 4] floats
@@ -227,6 +229,34 @@ __device__ __forceinline__ void set_quantize_x(GemvSmem<1> & s, const float * __
     }
 }
 
+// The same arithmetic with ONE thread per 32-element block (x warps: few threads, off the consumers' path): no
+// shuffles, the two divisions once per block instead of once per quarter block.  Plain x only (not tagged words).
+template <int NT>
+__device__ __forceinline__ void set_quantize_x_blocks(GemvSmem<1> & s, const float * __restrict__ x, int nbk, int t, bool ext) {
+    for (int b = t; b < nbk; b += NT) {
+        const float4 * p = reinterpret_cast<const float4 *>(x + 32 * b);
+        float4 f[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) f[i] = ext ? __ldca(p + i) : __ldcg(p + i);
+        float amax = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 8; i++) amax = fmaxf(fmaxf(fmaxf(amax, fabsf(f[i].x)), fmaxf(fabsf(f[i].y), fabsf(f[i].z))), fabsf(f[i].w));
+        const float d  = __fdiv_rn(amax, 127.0f);
+        const float id = (amax != 0.0f) ? __fdiv_rn(127.0f, amax) : 0.0f;
+        uint32_t w[8];
+        int sum = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const int q0 = q8_round(f[i].x, id), q1 = q8_round(f[i].y, id), q2 = q8_round(f[i].z, id), q3 = q8_round(f[i].w, id);
+            sum += (q0 + q1) + (q2 + q3);
+            w[i] = (uint32_t)(q0 & 0xFF) | ((uint32_t)(q1 & 0xFF) << 8) | ((uint32_t)(q2 & 0xFF) << 16) | ((uint32_t)(q3 & 0xFF) << 24);
+        }
+        s.lo[b] = make_uint4(w[0], w[1], w[2], w[3]);
+        s.hi[b] = make_uint4(w[4], w[5], w[6], w[7]);
+        s.ds[b] = make_int2(__float_as_int(__half2float(__float2half_rn(d))), -8 * sum);
+    }
+}
+
 // what a consumer needs of an op; loaded one op AHEAD (an L2 round trip under a saturated memory system costs
 // ~0.7 us, and the ops of a list are walked serially)
 struct SetOpC {
@@ -274,6 +304,7 @@ struct SetCtx {
     int nslots, slot_bytes;
     int G, group, wig, lane;
     unsigned long long tag;           // launch number << 32
+    uint32_t xempty;                  // mbarrier: every consumer warp has the run's x in registers (the planes are free)
     uint32_t done_local;              // shared-memory count of consumer warps past the ops that barriers wait for
 };
 
@@ -309,7 +340,8 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
             dx[u] = __int_as_float(ds.x); s8[u] = ds.y;
         }
     }
-    asm volatile("bar.sync 1, %0;" ::"n"(NG * SET_WPG * 32) : "memory");   // the planes may be overwritten by whoever finishes this run first
+    __syncwarp();
+    if (c.lane == 0) mbar_arrive(c.xempty);           // the planes may now be refilled with the next run's x (x warps)
     for (;;) {
         int first = (int)blockIdx.x - op.first_mod;
         if (first < 0) first += c.G;
@@ -415,7 +447,7 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
 // {whole kernel, consumer warp 0 waiting for full slots, in dependency barriers, quantizing x, producer waiting for empty slots}
 // BIG: also the 6-blocks-per-lane plan (K > 16384); the kernel without it needs fewer registers
 template <int W, bool DUMP, bool PROF, bool BIG>
-__global__ void __launch_bounds__(W * 32 + 96, 1)
+__global__ void __launch_bounds__(W * 32 + SET_EXTRA_THREADS, 1)
 gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restrict__ sync, int nslots, int slot_bytes,
                      int x_bytes, int tbl_bytes, int max_fly, unsigned seq, long long * __restrict__ prof) {
     constexpr int NCONS = W * 32;
@@ -439,10 +471,14 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
     __shared__ unsigned s_launch;
     __shared__ unsigned s_bar_passed;                         // dependency barriers the sentinel has seen complete
     __shared__ unsigned s_done_local;
+    __shared__ __align__(8) uint64_t s_xbar[2];
+    const uint32_t xfull = smem_u32(&s_xbar[0]), xempty = smem_u32(&s_xbar[1]);
     const uint32_t bar_passed = smem_u32(&s_bar_passed), done_local = smem_u32(&s_done_local);
     if (tid == 0) {
         s_bar_passed = 0u;
         s_done_local = 0u;
+        mbar_init(xfull, 1);       // the x warps filled the planes with a run's quantized x (or handed them over: tagged x)
+        mbar_init(xempty, W);      // every consumer warp copied the run's x to registers
         for (int s = 0; s < nslots; s++) {
             mbar_init(full0 + 8 * s, 1);
             mbar_init(empty0 + 8 * s, SET_WPG);
@@ -515,39 +551,67 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
     }
 
     if (warp == W + 1) {
-        // ===== wait sentinel: waits for the list's dependency barriers, in order, as far ahead of the consumers as the
-        // arrivals allow; publishes how many it has seen complete =====
+        // ===== sentinel (one thread, never blocks on one duty while the other is due) =====
+        //  arrive: when every consumer warp of this CTA is past an op that barriers wait for, the CTA arrives at them;
+        //  wait:   polls the list's barriers, in order, as far ahead of the consumers as the arrivals allow, and
+        //          publishes how many it has seen complete.
         if (lane == 0) {
-            unsigned k = 0;
-            for (int o = 0; o < nops; o++) {
-                const int fl = tbl != nullptr ? (tbl[o].fm_flags >> 16) : ops[o].flags;
-                if (!(fl & SET_OP_BARRIER)) continue;
-                k++;
-                set_barrier_wait(bar_cnt + (k - 1), (unsigned)G);
-                st_release_cta_shared_u32(bar_passed, k);
+            int oa = 0, ow = 0;                 // list positions of the next arrival point / the next barrier head
+            unsigned ev = 0, kb = 0, k = 0;
+            unsigned long long t0 = 0;
+            auto flags_of = [&](int o) { return tbl != nullptr ? (tbl[o].fm_flags >> 16) : ops[o].flags; };
+            while (oa < nops && !((flags_of(oa) >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK)) oa++;
+            while (ow < nops && !(flags_of(ow) & SET_OP_BARRIER)) ow++;
+            while (oa < nops || ow < nops) {
+                bool progress = false;
+                if (oa < nops && (int)(ld_acquire_cta_shared_u32(done_local) - (ev + 1) * (unsigned)W) >= 0) {
+                    const int narr = (flags_of(oa) >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK;
+                    for (int i = 0; i < narr; i++) red_release_gpu_add_u32(bar_cnt + kb++, 1u);      // barriers are numbered in the order of their arrival points
+                    ev++;
+                    oa++;
+                    while (oa < nops && !((flags_of(oa) >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK)) oa++;
+                    progress = true;
+                }
+                if (ow < nops && ld_relaxed_gpu_u32(bar_cnt + k) >= (unsigned)G) {
+                    fence_acq_rel_gpu();
+                    k++;
+                    st_release_cta_shared_u32(bar_passed, k);
+                    ow++;
+                    while (ow < nops && !(flags_of(ow) & SET_OP_BARRIER)) ow++;
+                    progress = true;
+                }
+                if (progress) { t0 = 0; continue; }
+                __nanosleep(64);
+                const unsigned long long t1 = gtime();
+                if (t0 == 0) t0 = t1;
+                if (t1 - t0 > 10000000000ull) __trap();   // a CTA of the grid is not resident / died: fail, do not hang
             }
         }
         return;
     }
-    if (warp == W + 2) {
-        // ===== arrive sentinel: when every consumer warp of this CTA is past an op that barriers wait for, the CTA
-        // arrives at them (a thread of its own: the release must not sit behind the other sentinel's polls) =====
-        if (lane == 0) {
-            unsigned ev = 0, kb = 0;
-            for (int o = 0; o < nops; o++) {
-                const int fl = tbl != nullptr ? (tbl[o].fm_flags >> 16) : ops[o].flags;
-                const int narr = (fl >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK;
-                if (!narr) continue;
-                ev++;
-                unsigned long long t0 = 0;
-                while ((int)(ld_acquire_cta_shared_u32(done_local) - ev * (unsigned)W) < 0) {
-                    __nanosleep(64);
-                    const unsigned long long t1 = gtime();
-                    if (t0 == 0) t0 = t1;
-                    if (t1 - t0 > 10000000000ull) __trap();
-                }
-                for (int i = 0; i < narr; i++) red_release_gpu_add_u32(bar_cnt + kb++, 1u);      // barriers are numbered in the order of their arrival points
+    if (warp > W + 1) {
+        // ===== x warps: kernel 1 (quantize_row_q8_0) of every run, one run AHEAD of the consumers =====
+        // The consumers keep a run's x in registers, so the planes are free as soon as every warp has copied them: the
+        // next run's x is quantized into them during this run's tiles, and a change of x costs a consumer warp one
+        // shared-memory wait and the register load -- no CTA-wide rendezvous, no L2 round trip, no quantization.  Runs
+        // whose x is another op's result (tagged words) are left to the consumers: all of them poll and quantize, which
+        // is the shorter critical path; the x warps only hand the planes over.
+        constexpr int NX = SET_XWARPS * 32;
+        const int xt = tid - (W + 2) * 32;
+        unsigned r = 0, kx = 0;
+        for (int o = 0; o < nops; o++) {
+            const SetOpC op = set_load_op<false>(ops, tbl, o);
+            if (!(op.flags & SET_OP_QUANT)) continue;
+            if (r > 0) mbar_wait_backoff(xempty, (r - 1) & 1u);
+            if (op.flags & SET_OP_BARRIER) {
+                kx++;
+                // x that an op of the list writes may only be read behind the run's barrier
+                if (!(op.flags & SET_OP_XEXT)) while ((int)(ld_acquire_cta_shared_u32(bar_passed) - kx) < 0) __nanosleep(64);
             }
+            if (op.xtag == nullptr) set_quantize_x_blocks<NX>(xs, op.x, op.nbk, xt, (op.flags & SET_OP_XEXT) != 0);
+            asm volatile("bar.sync 15, %0;" ::"n"(NX) : "memory");
+            if (xt == 0) mbar_arrive(xfull);
+            r++;
         }
         return;
     }
@@ -559,9 +623,10 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
     c.G = G; c.group = warp / SET_WPG; c.wig = warp % SET_WPG; c.lane = lane;
     c.tag = (unsigned long long)s_launch << 32;
     c.done_local = done_local;
+    c.xempty = xempty;
     SetRing rp = {0, 0};
     int j = 0;
-    unsigned nbar = 0, ntile_team = 0;
+    unsigned nbar = 0, ntile_team = 0, nrun = 0;
     SetOpC op = set_load_op<DUMP>(ops, tbl, 0);
     long long tp[4] = {0, 0, 0, 0};
     long long tx[4] = {0, 0, 0, 0};
@@ -574,30 +639,20 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
         const float * x = op.x;
         long long tq0 = 0;
         if (PROF) tq0 = clock64();
-        const bool ext = (flags & SET_OP_XEXT) != 0;
         if (flags & SET_OP_BARRIER) {
             // every thread sees for itself that the sentinel has passed this barrier (normally long ago: the arrival
-            // point lies ops back); x that an op of the list writes and this run's y stores come after it
+            // point lies ops back); this run's y stores (and reads of x that the list writes) come after it
             nbar++;
             while ((int)(ld_acquire_cta_shared_u32(bar_passed) - nbar) < 0) { }
         }
         if (PROF) { const long long t1 = clock64(); t_bar += t1 - tq0; tq0 = t1; }
-        // the planes are free: every warp passed the CTA barrier that follows its register load of the previous run
-        set_quantize_x<NCONS>(xs, x, op.xtag, c.tag, nbk, tid, ext);
-        set_consumer_sync<NCONS>();
-        // x of the NEXT run, when nothing in the list writes it: ask L1
-        // for it now, so that the loads at the next change of x do not pay an L2 round trip (~1 100 clk under load)
-        if (tbl != nullptr) {
-            int n = o + 1;
-            while (n < nops && !((tbl[n].fm_flags >> 16) & SET_OP_QUANT)) n++;
-            if (n < nops) {
-                const int fl = tbl[n].fm_flags >> 16;
-                if (fl & SET_OP_XEXT) {
-                    const float * xn = tbl[n].x;
-                    const int total_n = tbl[n].nbk * 4;
-                    for (int item = tid; item < total_n; item += NCONS) asm volatile("prefetch.global.L1 [%0];" ::"l"(xn + 8 * item));
-                }
-            }
+        // the x warps have the run's quantized x in the planes (they started on it when the previous run's x went to
+        // registers) -- or, for x that is another op's result, have handed the free planes over
+        mbar_wait(xfull, nrun & 1u);
+        nrun++;
+        if (op.xtag != nullptr) {
+            set_quantize_x<NCONS>(xs, x, op.xtag, c.tag, nbk, tid, false);
+            set_consumer_sync<NCONS>();
         }
         long long tr0 = 0;
         if (PROF) { tr0 = clock64(); t_quant += tr0 - tq0; }

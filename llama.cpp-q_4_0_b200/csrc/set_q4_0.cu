@@ -44,7 +44,7 @@ static int set_launch_tb(const ggml_b200_set * s, const SetOp * table, long long
         attr_set = true;
     }
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)s->grid); cfg.blockDim = dim3(W * 32 + 96); cfg.dynamicSmemBytes = s->smem; cfg.stream = g.stream;
+    cfg.gridDim = dim3((unsigned)s->grid); cfg.blockDim = dim3(W * 32 + SET_EXTRA_THREADS); cfg.dynamicSmemBytes = s->smem; cfg.stream = g.stream;
     // every CTA of the grid must be resident at once (dependency barriers spin on peers): cooperative launch makes
     // the driver check that instead of trusting it
     cudaLaunchAttribute attr[1];
