@@ -319,3 +319,32 @@ def test_set_x_written_by_two_row_shards_waits_for_both(b200, port, ref):
     s.free()
     for w in parts + [w1, w2]:
         w.free()
+
+
+def test_set_long_list_walks_the_table_in_global_memory(b200, port, ref):
+    """More ops than the shared-memory op table holds (32 KB / 48 B): consumers, producer, sentinel and x warps read
+    the descriptors from global memory.  800 small ops on three weights, three x, four dst buffers reused round-robin
+    (write-after-write barriers all along); the last writer of every dst must win."""
+    shapes = [(72, 1024), (64, 2048), (40, 1024)]
+    Ws = [make_weights(port, ref, M, K, 1400 + i) for i, (M, K) in enumerate(shapes)]
+    ws = [b200.Weight(W) for W in Ws]
+    xh = {1024: make_x(port, 1, 1024, 11), 2048: make_x(port, 1, 2048, 12)}
+    xd = {K: b200.DevBuf.from_numpy(x) for K, x in xh.items()}
+    yd = [b200.DevBuf(72 * 4) for _ in range(4)]
+    ops, last = [], {}
+    for i in range(800):
+        k = (i * 7 + i // 5) % 3
+        d = i % 4
+        ops.append((ws[k], xd[shapes[k][1]].ptr, yd[d].ptr))
+        last[d] = k
+    s = b200.OpSet(ops)
+    assert s.n_ops == 800 and s.barriers > 0
+    for _ in range(5):
+        s.run()
+    b200.synchronize()
+    for d, k in last.items():
+        M, K = shapes[k]
+        assert_close(yd[d].to_numpy(np.float32, (1, 72))[:, :M], oracle_Y(port, ref, Ws[k], xh[K]))
+    s.free()
+    for w in ws:
+        w.free()
