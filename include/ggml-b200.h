@@ -64,7 +64,7 @@ void         ggml_b200_set_gemm_min_n(int n);              /* n >= this takes th
 int          ggml_b200_get_gemm_min_n(void);
 void         ggml_b200_set_path(int path);
 /* kernel tuning knobs for sweeps ("gemv_threads", "gemv_ctas_per_sm", "gemv_unroll", "gemv_nc",
- * "gemm_*"); returns GGML_B200_ERR_ARG for an unknown key or a value out of range */
+ * "gemm_*", "set_*"); returns GGML_B200_ERR_ARG for an unknown key or a value out of range */
 int          ggml_b200_set_tuning(const char * key, int value);
 void         ggml_b200_set_stream(void * cuda_stream);     /* NULL = the library's own stream */
 void *       ggml_b200_get_stream(void);
@@ -141,8 +141,12 @@ int          ggml_b200_mul_mat_q4_0_host(const ggml_b200_weight * w, const float
  * Ordering follows the DATA hazards between the ops: ops that share x_dev run back to back
  * (wq/wk/wv, w3/w1; llama.cpp:1394-1504); an op whose x_dev is exactly the dst of one earlier op
  * waits for that op's rows only (they travel as tagged words, no barrier); any other overlap of an
- * op's x or dst with an earlier op's x or dst puts a grid-wide barrier in front of it.  x_dev 16-byte aligned (ggml tensors
- * are), weights in the plane layout.  create copies the list; the buffers must stay valid.  run is
+ * op's x or dst with an earlier op's x or dst is a grid-wide dependency barrier, split in two: every
+ * CTA arrives when it has finished the last op the run conflicts with, and the wait sits at the head
+ * of the run (ops later, normally long satisfied).  x_dev 16-byte aligned (ggml tensors are), weights
+ * in the plane layout.  Tuning keys (ggml_b200_set_tuning): "set_warps" consumer warps per CTA
+ * (8/12/16/20, default 12), "set_slots" ring depth (0 = consumer groups + 1), "set_link" 0 = barriers
+ * instead of tagged words, "set_split_barrier" 0 = arrive right before the wait, "set_barrier_slack".  create copies the list; the buffers must stay valid.  run is
  * asynchronous on the current stream and may be captured in a CUDA graph. */
 typedef struct ggml_b200_set ggml_b200_set;
 typedef struct ggml_b200_set_op {
@@ -163,8 +167,8 @@ uint64_t     ggml_b200_set_bytes(const ggml_b200_set * s);     /* algorithmic by
 int          ggml_b200_set_checkpoint(ggml_b200_set * s, int32_t * const * S_dev, int n_ops);
 /* profiling aid: one synchronous run of an instrumented build of the same kernel; out_host[cta*16 + i] = clock64
  * totals {whole kernel, a consumer warp waiting for weights, in dependency barriers, quantizing x, the producer
- * waiting for a free ring slot, that warp from data ready to y stored, its tiles, 0, and of the barriers: CTA
- * sync, release, polling, acquire fence, 0...}.  Returns the number of CTAs written (<= max_ctas) or an error. */
+ * waiting for a free ring slot, that warp from data ready to y stored, its tiles, in the tile loops, 0 x 4 (the
+ * barrier's pieces moved to the sentinel thread), loop bookkeeping x 4}.  Returns the number of CTAs written (<= max_ctas) or an error. */
 int          ggml_b200_set_profile(ggml_b200_set * s, long long * out_host, int max_ctas);
 
 /* ---- parity checkpoint --------------------------------------------------------------------

@@ -120,24 +120,14 @@ __device__ __forceinline__ void set_consumer_sync() {
 // consumer warp of the grid has arrived, then one acquire fence; the CTA barrier that follows the quantization of x
 // hands the result to the other threads.  The arrival point is usually several ops before the wait (a layer's wq
 // against the next layer's wq: four ops), so the poll finds the count complete and a barrier costs two L2 round
-// trips of one thread that has nothing else to do (set_barrier_wait below) instead of a grid-wide rendezvous.
+// trips of one thread that has nothing else to do (the sentinel) instead of a grid-wide rendezvous.
 __device__ __forceinline__ void set_barrier_arrive(uint32_t done_local, int lane) {
     __syncwarp();
     if (lane == 0) asm volatile("red.release.cta.shared.add.u32 [%0], 1;" ::"r"(done_local) : "memory");
 }
-// WAIT, by the CTA's sentinel thread (a warp of its own with nothing else to do, so the two L2 round trips -- the poll
-// that finds the count complete and the acquire fence -- are off the consumers' path): it walks the list ahead of the
-// consumers and publishes the number of barriers it has seen complete in shared memory.
-__device__ __forceinline__ void set_barrier_wait(const unsigned * cnt, unsigned target) {
-    unsigned long long t0 = 0;
-    while (ld_relaxed_gpu_u32(cnt) < target) {
-        __nanosleep(100);
-        const unsigned long long t1 = gtime();
-        if (t0 == 0) t0 = t1;
-        if (t1 - t0 > 10000000000ull) __trap();   // a CTA of the grid is not resident / died: fail, do not hang
-    }
-    fence_acq_rel_gpu();
-}
+// WAIT, by the CTA's sentinel thread (a warp of its own, so the two L2 round trips -- the poll that finds the count
+// complete and the acquire fence -- are off the consumers' path): it polls the barriers in list order ahead of the
+// consumers and publishes the number it has seen complete in shared memory (kernel body, `warp == W + 1`).
 __device__ __forceinline__ void st_release_cta_shared_u32(uint32_t addr, unsigned v) {
     asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }

@@ -127,7 +127,7 @@ def main():
         s.profile()
         prof = s.profile().astype(np.float64)
         tot = prof[:, 0]
-        names = ["kernel clk", "consumer waits for weights", "dependency barriers", "quantize x", "producer waits for a slot"]
+        names = ["kernel clk", "consumer waits for weights", "dependency barriers", "waiting for x (x warps; tagged x: poll + quantize)", "producer waits for a slot"]
         parts = [f"{names[0]} mean {tot.mean():.0f} max {tot.max():.0f}"]
         for i in range(1, 5):
             parts.append(f"{names[i]} {100 * (prof[:, i] / tot).mean():.1f}% (max {100 * (prof[:, i] / tot).max():.1f}%)")
@@ -136,7 +136,6 @@ def main():
         parts.append(f"in the tile loops {100 * (prof[:, 7] / tot).mean():.1f}%")
         parts.append(f"loop: top-of-iteration gaps {100 * (prof[:, 12] / tot).mean():.1f}% over {prof[:, 13].mean():.0f} iterations, after last tile of an op {100 * (prof[:, 14] / tot).mean():.1f}%, next-op descriptor {100 * (prof[:, 15] / tot).mean():.1f}%")
         nb_ = max(s.barriers, 1)
-        parts.append("per barrier clk: CTA sync %.0f, release %.0f, poll %.0f, acquire %.0f" % tuple(prof[:, 8 + i].mean() / nb_ for i in range(4)))
         print("    profile: " + "; ".join(parts), flush=True)
         s.free()
     mod.shutdown()
