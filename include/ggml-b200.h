@@ -162,6 +162,17 @@ int          ggml_b200_set_barriers(const ggml_b200_set * s);  /* grid-wide depe
 int          ggml_b200_set_linked_runs(const ggml_b200_set * s); /* runs whose x is read from its producer op's tagged rows */
 int          ggml_b200_set_slots(const ggml_b200_set * s);     /* depth of the shared-memory ring */
 uint64_t     ggml_b200_set_bytes(const ggml_b200_set * s);     /* algorithmic bytes per run */
+/* The hazard analysis of create, alone (pure host code: no device, nothing dereferenced; x and y are addresses as
+ * integers): flags_out[i] = what the kernel is told about op i -- bit 0 a dependency barrier is waited for at its head,
+ * bit 1 it starts a new run (x is (re)quantized), bit 2 no op of the list writes its x, bits 8..14 how many barriers
+ * every CTA arrives at when it has finished op i; link_out[i] = the op whose result rows op i's run reads as x (tagged
+ * words), or -1.  Ops with an empty shard get 0 / -1.  Returns the number of barriers, or an error (< 0). */
+typedef struct ggml_b200_set_plan_op {
+    uint64_t x, y;                    /* addresses of src1 and of the FULL dst row */
+    int64_t  K, M, row_lo, row_hi;    /* the weight shard: rows [row_lo, row_hi) of M, K columns */
+} ggml_b200_set_plan_op;
+int          ggml_b200_set_plan(const ggml_b200_set_plan_op * ops, int n_ops, int * flags_out, int * link_out,
+                                int * linked_runs_out);
 /* parity checkpoint of the same device code: S_dev[i] = [rows_i][K_i/32] int32 block dots of the
  * i-th non-empty op (device pointers, or NULL to skip that op); also writes y like run */
 int          ggml_b200_set_checkpoint(ggml_b200_set * s, int32_t * const * S_dev, int n_ops);

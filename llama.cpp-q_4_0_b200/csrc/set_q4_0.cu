@@ -71,11 +71,128 @@ static int set_launch(const ggml_b200_set * s, const SetOp * table, long long * 
     }
 }
 
+
+// ---- hazard analysis of a list (pure host code; ggml_b200_set_plan exposes it to the CPU-only tests) ----------------
+// The list must behave like its ops run one after the other.  Per op (non-empty shards only), against the ops still
+// "live" (not yet covered by a barrier):
+//   * x is exactly the dst of ONE live earlier op          -> the run reads x out of that op's tagged staging rows
+//     (gemv_q4_0_set.cuh): the wait is per word, no barrier;
+//   * x overlaps live dsts in any other way, or dst overlaps a live x or dst (WAR / WAW)   -> dependency barrier;
+//   * otherwise x is not produced inside the list (or was before a barrier that covers it): plain loads.
+// Ops that share x with the head of the current run and need no barrier join it (no re-quantization).
+struct SetPlanOp { const float * x, * x_hi, * y_lo, * y_hi; long long K; bool whole; };
+struct SetPlan {
+    std::vector<int> flags;       // SET_OP_* | arrivals << SET_OP_ARRIVE_SHIFT, per op
+    std::vector<int> link;        // per op: index of the op whose staging rows its x is read from (heads of linked runs), or -1
+    int barriers = 0, linked_runs = 0;
+};
+// returns -1, or the index of the op behind which too many barriers would arrive
+static int set_plan_hazards(const std::vector<SetPlanOp> & ops, const Tune & tune, SetPlan & out) {
+    const int n = (int)ops.size();
+    out.flags.assign(n, 0);
+    out.link.assign(n, -1);
+    struct Range { const float * lo, * hi; int op; bool whole; };
+    std::vector<Range> live_x, live_y;
+    const float * run_x = nullptr; long long run_K = 0; int run_link = -1;
+    int arrive_mono = -1;
+    // hazards of op j against the ops still live: does it need a barrier, behind which op, is its x one op's dst
+    auto hazards = [&](int j, bool & bar_, int & after_, int & link_) {
+        const SetPlanOp & o = ops[j];
+        for (const Range & r : live_x) if (set_ranges_overlap(o.y_lo, o.y_hi, r.lo, r.hi)) { bar_ = true; after_ = std::max(after_, r.op); }      // WAR
+        for (const Range & r : live_y) if (set_ranges_overlap(o.y_lo, o.y_hi, r.lo, r.hi)) { bar_ = true; after_ = std::max(after_, r.op); }      // WAW
+        int writers = 0, last_writer = -1;
+        link_ = -1;
+        for (const Range & r : live_y) {
+            if (!set_ranges_overlap(o.x, o.x_hi, r.lo, r.hi)) continue;
+            writers++;
+            last_writer = std::max(last_writer, r.op);
+            if (r.lo == o.x && r.hi == o.x_hi && r.whole) link_ = r.op; else bar_ = true;                   // RAW
+        }
+        if (writers > 1 || (link_ >= 0 && !tune.set_link)) bar_ = true;
+        if (bar_) after_ = std::max(after_, last_writer);
+    };
+    for (int i = 0; i < n; i++) {
+        const SetPlanOp & o = ops[i];
+        bool barrier = false;
+        int after = -1;                       // last earlier op this one conflicts with
+        int link = -1;
+        hazards(i, barrier, after, link);
+        if (barrier) {
+            // Split barrier: every warp ARRIVES when it has finished the last op this run conflicts with and WAITS here,
+            // usually several ops later, when the count is long complete.  Arrival points are kept monotonic (barriers
+            // are numbered in the order of their arrival points); ops after the arrival point stay live (the barrier
+            // says nothing about them).  The ops that will share this run's x wait here too (a barrier of their own would
+            // split the run), and ops up to `set_barrier_slack` before the head are waited for as well.
+            for (int j = i + 1; j < n && ops[j].x == o.x && ops[j].K == o.K; j++) {
+                bool b2 = false; int l2 = -1;
+                hazards(j, b2, after, l2);
+            }
+            const int prev = i - 1;
+            after = std::max(std::max(after, arrive_mono), prev - std::max(tune.set_barrier_slack, 0));
+            if (after > prev || !tune.set_split_barrier) after = prev;
+            while (after >= 0 && after < prev && ((out.flags[after] >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK) >= SET_OP_ARRIVE_MASK) after++;
+            arrive_mono = after;
+            auto dead = [&](const Range & r) { return r.op <= after; };
+            live_x.erase(std::remove_if(live_x.begin(), live_x.end(), dead), live_x.end());
+            live_y.erase(std::remove_if(live_y.begin(), live_y.end(), dead), live_y.end());
+            link = -1;
+        }
+        const bool same_run = i > 0 && !barrier && run_x == o.x && run_K == o.K && run_link == link;
+        if (!same_run) {
+            const bool bar = barrier && i > 0 && !tune.set_unsafe_no_barriers;
+            out.flags[i] = SET_OP_QUANT | (bar ? SET_OP_BARRIER : 0);
+            if (bar) {
+                out.barriers++;
+                if (((out.flags[after] >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK) >= SET_OP_ARRIVE_MASK) return after;
+                out.flags[after] += 1 << SET_OP_ARRIVE_SHIFT;
+            }
+            if (link >= 0) out.linked_runs++;
+            run_x = o.x; run_K = o.K; run_link = link;
+        }
+        out.link[i] = same_run ? -1 : link;
+        live_x.push_back({o.x, o.x_hi, i, false});
+        live_y.push_back({o.y_lo, o.y_hi, i, o.whole});
+    }
+    // x that no op of the list writes: the kernel may cache it and fetch it ahead of the run that needs it
+    for (int i = 0; i < n; i++) {
+        if (!(out.flags[i] & SET_OP_QUANT) || !tune.set_xext) continue;
+        bool written = false;
+        for (const SetPlanOp & q : ops) if (set_ranges_overlap(ops[i].x, ops[i].x_hi, q.y_lo, q.y_hi)) written = true;
+        if (!written) out.flags[i] |= SET_OP_XEXT;
+    }
+    return -1;
+}
+
 }  // namespace b200
 
 using namespace b200;
 
 extern "C" {
+
+int ggml_b200_set_plan(const ggml_b200_set_plan_op * ops, int n_ops, int * flags_out, int * link_out, int * linked_runs_out) {
+    if (!ops || n_ops <= 0) { set_error("empty op list"); return GGML_B200_ERR_ARG; }
+    std::vector<SetPlanOp> po;
+    std::vector<int> where;             // list index of every op with a non-empty shard
+    for (int i = 0; i < n_ops; i++) {
+        const ggml_b200_set_plan_op & o = ops[i];
+        if (o.K <= 0 || o.K % QK || o.row_lo < 0 || o.row_hi < o.row_lo || o.row_hi > o.M) { set_error("set_plan op %d: bad shape", i); return GGML_B200_ERR_ARG; }
+        if (flags_out) flags_out[i] = 0;
+        if (link_out) link_out[i] = -1;
+        if (o.row_hi == o.row_lo) continue;
+        const float * x = reinterpret_cast<const float *>((uintptr_t)o.x);
+        const float * y = reinterpret_cast<const float *>((uintptr_t)o.y);
+        po.push_back({x, x + o.K, y + o.row_lo, y + o.row_hi, (long long)o.K, o.row_lo == 0 && o.row_hi == o.M});
+        where.push_back(i);
+    }
+    SetPlan plan;
+    if (set_plan_hazards(po, g.tune, plan) >= 0) { set_error("too many dependency barriers behind one op of the set"); return GGML_B200_ERR_ARG; }
+    for (size_t k = 0; k < where.size(); k++) {
+        if (flags_out) flags_out[where[k]] = plan.flags[k];
+        if (link_out && plan.link[k] >= 0) link_out[where[k]] = where[plan.link[k]];
+    }
+    if (linked_runs_out) *linked_runs_out = plan.linked_runs;
+    return plan.barriers;
+}
 
 ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
     if (!g.inited) { set_error("ggml_b200_init was not called"); return nullptr; }
@@ -86,17 +203,7 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
     const int NG = s->warps / SET_WPG;
     int nbk_max = 0;
     long long tiles = 0;
-    // Hazards between the ops of the list (the list must behave like the ops run one after the other):
-    //   * x of an op is exactly the dst of ONE earlier op still "live" (no barrier since)  -> the run reads x out of that
-    //     op's tagged staging rows (gemv_q4_0_set.cuh): the wait is per word, no barrier;
-    //   * x overlaps live dsts in any other way, or dst overlaps a live x or dst (WAR / WAW)  -> grid barrier first;
-    //   * otherwise x is not produced inside the list (or was before the last barrier): plain loads.
-    // Ops that share x with the head of the current run and need no barrier join it (no re-quantization).
-    struct Range { const float * lo, * hi; int op; bool whole; };
-    std::vector<Range> live_x, live_y;
-    std::vector<int> link_of;             // per host op: index of the host op whose staging rows its x is read from, or -1
-    const float * run_x = nullptr; int64_t run_K = 0; int run_link = -1;
-    int arrive_mono = -1;
+    std::vector<SetPlanOp> plan_ops;
     for (int i = 0; i < n_ops; i++) {
         const ggml_b200_weight * w = ops[i].w;
         const float * x = ops[i].x_dev;
@@ -118,72 +225,22 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
         tiles += o.ntiles;
         const float * y_lo = o.y, * y_hi = o.y + o.rows;
         const float * x_hi = x + w->K;
-        // hazards of list entry j against the ops still live: does it need a barrier, behind which op, is its x one op's dst
-        auto hazards = [&](int j, bool & bar_, int & after_, int & link_) {
-            const ggml_b200_weight * wj = ops[j].w;
-            const float * xj = ops[j].x_dev, * xj_hi = xj + wj->K;
-            const float * yj_lo = ops[j].y_dev + wj->row_lo, * yj_hi = ops[j].y_dev + wj->row_hi;
-            for (const Range & r : live_x) if (set_ranges_overlap(yj_lo, yj_hi, r.lo, r.hi)) { bar_ = true; after_ = std::max(after_, r.op); }      // WAR
-            for (const Range & r : live_y) if (set_ranges_overlap(yj_lo, yj_hi, r.lo, r.hi)) { bar_ = true; after_ = std::max(after_, r.op); }      // WAW
-            int writers = 0, last_writer = -1;
-            link_ = -1;
-            for (const Range & r : live_y) {
-                if (!set_ranges_overlap(xj, xj_hi, r.lo, r.hi)) continue;
-                writers++;
-                last_writer = std::max(last_writer, r.op);
-                if (r.lo == xj && r.hi == xj_hi && r.whole) link_ = r.op; else bar_ = true;                   // RAW
-            }
-            if (writers > 1 || (link_ >= 0 && !g.tune.set_link)) bar_ = true;
-            if (bar_) after_ = std::max(after_, last_writer);
-        };
-        bool barrier = false;
-        int after = -1;                       // last earlier op this one conflicts with
-        int link = -1;
-        hazards(i, barrier, after, link);
-        if (barrier) {
-            // Split barrier: every warp ARRIVES when it has finished the last op this run conflicts with and WAITS here,
-            // usually several ops later, when the count is long complete.  Arrival points are kept monotonic so that one
-            // counter serves all barriers; ops after the arrival point stay live (the barrier says nothing about them).
-            // The ops that will share this run's x wait here too (a barrier of their own would split the run), and ops up
-            // to `set_barrier_slack` before the head are waited for as well: they have long finished (the wait stays
-            // free) and whatever later conflicts with them needs no barrier of its own.
-            for (int j = i + 1; j < n_ops && ops[j].w && ops[j].x_dev == x && ops[j].y_dev && ops[j].w->K == w->K; j++) {
-                if (ops[j].w->rows() == 0) continue;
-                bool b2 = false; int l2 = -1;
-                hazards(j, b2, after, l2);
-            }
-            const int prev = (int)s->host_ops.size() - 1;
-            after = std::max(std::max(after, arrive_mono), prev - std::max(g.tune.set_barrier_slack, 0));
-            if (after > prev || !g.tune.set_split_barrier) after = prev;
-            while (after >= 0 && after + 1 < (int)s->host_ops.size() && ((s->host_ops[after].flags >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK) >= SET_OP_ARRIVE_MASK) after++;
-            arrive_mono = after;
-            auto dead = [&](const Range & r) { return r.op <= after; };
-            live_x.erase(std::remove_if(live_x.begin(), live_x.end(), dead), live_x.end());
-            live_y.erase(std::remove_if(live_y.begin(), live_y.end(), dead), live_y.end());
-            link = -1;
-        }
-        const bool same_run = !s->host_ops.empty() && !barrier && run_x == x && run_K == w->K && run_link == link;
-        if (!same_run) {
-            const bool bar = barrier && !s->host_ops.empty() && !g.tune.set_unsafe_no_barriers;
-            o.flags = SET_OP_QUANT | (bar ? SET_OP_BARRIER : 0);
-            if (bar) {
-                s->barriers++;
-                if (((s->host_ops[after].flags >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK) >= SET_OP_ARRIVE_MASK) { set_error("set op %d: too many dependency barriers behind one op", i); delete s; return nullptr; }
-                s->host_ops[after].flags += 1 << SET_OP_ARRIVE_SHIFT;
-            }
-            if (link >= 0) s->linked_runs++;
-            run_x = x; run_K = w->K; run_link = link;
-        }
-        link_of.push_back(same_run ? -1 : link);
-        const int me = (int)s->host_ops.size();
-        live_x.push_back({x, x_hi, me, false});
-        live_y.push_back({y_lo, y_hi, me, w->row_lo == 0 && w->row_hi == w->M});
+        plan_ops.push_back({x, x_hi, y_lo, y_hi, (long long)w->K, w->row_lo == 0 && w->row_hi == w->M});
         if (o.nbk > nbk_max) nbk_max = o.nbk;
         const int stage = R * o.nbk * 16 + ((R * o.nbk * 2 + 15) & ~15);
         if (stage > s->slot_bytes) s->slot_bytes = stage;
         s->host_ops.push_back(o);
     }
     if (s->host_ops.empty()) { set_error("every op of the set has an empty row shard"); delete s; return nullptr; }
+    SetPlan plan;
+    {
+        const int bad = set_plan_hazards(plan_ops, g.tune, plan);
+        if (bad >= 0) { set_error("too many dependency barriers behind op %d of the set", bad); delete s; return nullptr; }
+    }
+    for (size_t i = 0; i < s->host_ops.size(); i++) s->host_ops[i].flags = plan.flags[i];
+    s->barriers = plan.barriers;
+    s->linked_runs = plan.linked_runs;
+    const std::vector<int> & link_of = plan.link;
     s->slot_bytes = (s->slot_bytes + 127) & ~127;
     s->x_bytes = 40 * nbk_max;
     s->big = nbk_max > 512;
@@ -203,13 +260,6 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
         delete s; return nullptr;
     }
     s->smem = (size_t)s->x_bytes + SET_BAR_BYTES + SET_RED_BYTES + s->tbl_bytes + (size_t)s->nslots * s->slot_bytes;
-    // x that no op of the list writes: the kernel may cache it and fetch it ahead of the run that needs it
-    for (SetOp & o : s->host_ops) {
-        if (!(o.flags & SET_OP_QUANT) || !g.tune.set_xext) continue;
-        bool written = false;
-        for (const SetOp & q : s->host_ops) if (set_ranges_overlap(o.x, o.x + (size_t)o.nbk * QK, q.y, q.y + q.rows)) written = true;
-        if (!written) o.flags |= SET_OP_XEXT;
-    }
     {
         size_t words = 0;
         std::vector<long long> off(s->host_ops.size(), -1);

@@ -89,6 +89,7 @@ def _load() -> C.CDLL:
         "ggml_b200_set_ops": (C.c_int, [_vp]),
         "ggml_b200_set_barriers": (C.c_int, [_vp]),
         "ggml_b200_set_slots": (C.c_int, [_vp]),
+        "ggml_b200_set_plan": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
         "ggml_b200_set_linked_runs": (C.c_int, [_vp]),
         "ggml_b200_set_bytes": (C.c_uint64, [_vp]),
         "ggml_b200_set_checkpoint": (C.c_int, [_vp, _vp, C.c_int]),
@@ -334,6 +335,32 @@ def mul_mat_sharded_dev(w: Weight, x_dev_ptr: int, n: int, y_dev_ptr: int) -> No
 class SetOp(C.Structure):
     """struct ggml_b200_set_op"""
     _fields_ = [("w", _vp), ("x_dev", _vp), ("y_dev", _vp)]
+
+
+class SetPlanOp(C.Structure):
+    """struct ggml_b200_set_plan_op"""
+    _fields_ = [("x", C.c_uint64), ("y", C.c_uint64), ("K", C.c_int64), ("M", C.c_int64), ("row_lo", C.c_int64), ("row_hi", C.c_int64)]
+
+
+SET_OP_BARRIER, SET_OP_QUANT, SET_OP_XEXT = 1, 2, 4
+
+
+def set_plan(ops):
+    """The hazard analysis of ggml_b200_set_create alone (host code, no device).
+    ops: iterable of (x address, y address, M, K[, row_lo, row_hi]).
+    Returns (barriers, linked_runs, [dict(barrier, new_run, ext, arrivals, link)] per op)."""
+    ops = [tuple(o) + ((0, o[2]) if len(o) == 4 else ()) for o in ops]
+    arr = (SetPlanOp * max(1, len(ops)))()
+    for i, (x, y, M, K, lo, hi) in enumerate(ops):
+        arr[i] = SetPlanOp(x, y, K, M, lo, hi)
+    flags = (C.c_int * max(1, len(ops)))()
+    link = (C.c_int * max(1, len(ops)))()
+    linked = C.c_int(0)
+    rc = lib().ggml_b200_set_plan(C.cast(arr, _vp), len(ops), flags, link, C.byref(linked))
+    _check(min(rc, 0))
+    out = [dict(barrier=bool(flags[i] & SET_OP_BARRIER), new_run=bool(flags[i] & SET_OP_QUANT), ext=bool(flags[i] & SET_OP_XEXT),
+                arrivals=(flags[i] >> 8) & 0x7F, link=link[i]) for i in range(len(ops))]
+    return rc, linked.value, out
 
 
 class OpSet:
