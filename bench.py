@@ -588,7 +588,7 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
     # matmul of the list writes (the model's element-wise ops sit between them and are not part of this set), so the
     # only data hazards are the dst buffers the layers reuse.  One launch per mul_mat serialises on stream order
     # (except ops that share src1); the persistent launch orders by those hazards.  On a list CHAINED like the model
-    # (x of an op = dst of an earlier one) it is the slower path: tools/sweep_set.py, profiles/r01_set_sweep_v3*.log.
+    # (x of an op = dst of an earlier one) it is the slower path: tools/sweep_set.py, profiles/r01_set_sweep_v3*.log, r01_set_sweep_v5_slots.log.
     if opset is not None:
         def quick(fn, n=30):
             with torch.cuda.stream(stream):
