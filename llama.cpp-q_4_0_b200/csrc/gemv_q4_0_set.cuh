@@ -7,9 +7,9 @@
 //   * grid = one CTA per SM, resident for the whole list (cooperative launch);
 //   * ONE producer thread per CTA walks the CTA's tiles of ALL ops in list order and copies them with
 //     cp.async.bulk (TMA engine, UBLKCP) into a shared-memory ring of NS slots, completion on an mbarrier per slot.
-//     Weights are immutable, so the producer never waits for an op to finish: while the consumers sit in a
-//     dependency barrier or quantize the next x, up to ~190 KB per SM (28 MB per GPU) of the NEXT ops' weights
-//     are already in flight, and HBM never idles across op boundaries;
+//     Weights are immutable, so the producer never waits for an op to finish: while consumers wait on a dependency
+//     or change x, the NEXT ops' weights are already in flight, and HBM never idles across op boundaries.  Ring
+//     depth = consumer groups + 1 (measured best; what the ring does not take stays L1);
 //   * W consumer warps in groups of 4; slot j belongs to group j % NG.  A tile is R consecutive weight rows
 //     (nibble plane rows + scale plane rows, both contiguous in the plane layout):
 //       K <= 4096 (WPR = 1): R = 8, warp i of the group owns rows 2i, 2i+1, lane l owns blocks l, l+32, ... of them
@@ -23,10 +23,14 @@
 //     block): the consumers were bound by the shared-memory pipe when x was re-read per row (v1, 40 B more per
 //     block and row pair; profiles/r01_set_sweep_v1.log);
 //   * tiles are dealt round-robin over the CTAs CONTINUING across ops, so the per-op remainder does not idle SMs;
-//   * ops that read the same x as their predecessor and write rows nobody of the run touches (wq/wk/wv, w3/w1)
-//     run back to back; every other op starts with a grid-wide barrier (all its predecessors complete, results
-//     visible) and a re-quantization of x (quantize_row_q8_0 contract, ggml.c:1192-1250, same arithmetic as the
-//     fused kernel).  Semantics == calling ggml_b200_mul_mat_q4_0 per op in order.
+//   * ops that read the same x as their predecessor (wq/wk/wv, w3/w1) form a RUN and go back to back.  A change of x
+//     costs a consumer warp one shared-memory wait: two x warps quantize the next run's x (quantize_row_q8_0 contract,
+//     ggml.c:1192-1250, same arithmetic as the fused kernel) into the planes while the consumers work from registers;
+//   * ordering follows the data hazards the host found (set_q4_0.cu, set_plan_hazards): x that is exactly one earlier
+//     op's dst is read out of that op's tagged 8-byte words (the wait is per word); any other overlap is a split
+//     dependency barrier -- CTAs arrive when they have finished the last conflicting op, a sentinel thread per CTA
+//     forwards arrivals and waits ahead of the consumers.  Semantics == calling ggml_b200_mul_mat_q4_0 per op in order.
+//   * warps of a CTA: W consumers, 1 producer, 1 sentinel, SET_XWARPS x warps.
 // Roofline: HBM; algorithmic bytes per launch = sum over ops of 18*M*K/32 + 4*K + 4*M.
 #pragma once
 #include "common.cuh"
@@ -49,7 +53,7 @@ constexpr int SET_MAX_NBK = 768;      // 6 per lane of a 4-warp team (K <= 24576
 enum { SET_OP_BARRIER = 1, SET_OP_QUANT = 2, SET_OP_XEXT = 4 };
 // flags bits 8..14: how many dependency barriers every consumer warp arrives at when it has finished this op
 constexpr int SET_OP_ARRIVE_SHIFT = 8, SET_OP_ARRIVE_MASK = 0x7F;
-//   // XEXT: no op of the list writes x (it may be cached / fetched early)
+// XEXT: no op of the list writes x (it may be cached / fetched early)
 
 struct SetOp {                        // 80 bytes, device resident, read-only during the launch
     const uint4 * wq;                 // nibble plane of this shard [rows][nbk]
