@@ -443,13 +443,15 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
 template <int W, bool DUMP, bool PROF, bool BIG>
 __global__ void __launch_bounds__(W * 32 + SET_EXTRA_THREADS, 1)
 gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restrict__ sync, int nslots, int slot_bytes,
-                     int x_bytes, int tbl_bytes, int max_fly, unsigned seq, long long * __restrict__ prof) {
+                     int x_bytes, int x_bufs, int tbl_bytes, int max_fly, unsigned seq, long long * __restrict__ prof) {
     constexpr int NCONS = W * 32;
     constexpr int NG = W / SET_WPG;
     static_assert(NG <= SET_MAX_GROUPS, "named barriers 2 .. 2+NG-1 and the partials buffer are sized for 6 groups");
     extern __shared__ __align__(128) unsigned char smem[];
     // [x planes: x_bytes][full barriers 16 x 8][empty barriers 16 x 8][team partials][op table: tbl_bytes][ring: nslots x slot_bytes]
-    GemvSmem<1> xs(smem, x_bytes / 40);
+    // x_bufs = 2: the x warps may be a whole run ahead (they fill one buffer while the consumers still copy the other)
+    const int x_per = x_bytes / x_bufs;
+    GemvSmem<1> xs0(smem, x_per / 40), xs1(smem + (x_bufs > 1 ? x_per : 0), x_per / 40);
     uint64_t * bars = reinterpret_cast<uint64_t *>(smem + x_bytes);
     SetOpS * tbl = tbl_bytes ? reinterpret_cast<SetOpS *>(smem + x_bytes + SET_BAR_BYTES + SET_RED_BYTES) : nullptr;
     unsigned char * ring = smem + x_bytes + SET_BAR_BYTES + SET_RED_BYTES + tbl_bytes;
@@ -465,14 +467,16 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
     __shared__ unsigned s_launch;
     __shared__ unsigned s_bar_passed;                         // dependency barriers the sentinel has seen complete
     __shared__ unsigned s_done_local;
-    __shared__ __align__(8) uint64_t s_xbar[2];
-    const uint32_t xfull = smem_u32(&s_xbar[0]), xempty = smem_u32(&s_xbar[1]);
+    __shared__ __align__(8) uint64_t s_xbar[4];      // per x buffer: full [0..1], empty [2..3]
+    const uint32_t xfull0 = smem_u32(&s_xbar[0]), xempty0 = smem_u32(&s_xbar[2]);
     const uint32_t bar_passed = smem_u32(&s_bar_passed), done_local = smem_u32(&s_done_local);
     if (tid == 0) {
         s_bar_passed = 0u;
         s_done_local = 0u;
-        mbar_init(xfull, 1);       // the x warps filled the planes with a run's quantized x (or handed them over: tagged x)
-        mbar_init(xempty, W);      // every consumer warp copied the run's x to registers
+        for (int b = 0; b < 2; b++) {
+            mbar_init(xfull0 + 8 * b, 1);       // the x warps filled the planes with a run's quantized x (or handed them over: tagged x)
+            mbar_init(xempty0 + 8 * b, W);      // every consumer warp copied the run's x to registers
+        }
         for (int s = 0; s < nslots; s++) {
             mbar_init(full0 + 8 * s, 1);
             mbar_init(empty0 + 8 * s, SET_WPG);
@@ -596,15 +600,16 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
         for (int o = 0; o < nops; o++) {
             const SetOpC op = set_load_op<false>(ops, tbl, o);
             if (!(op.flags & SET_OP_QUANT)) continue;
-            if (r > 0) mbar_wait_backoff(xempty, (r - 1) & 1u);
+            const unsigned b = x_bufs > 1 ? (r & 1u) : 0u, u = x_bufs > 1 ? (r >> 1) : r;      // buffer, and its how-manieth use
+            if (u > 0) mbar_wait_backoff(xempty0 + 8 * b, (u - 1) & 1u);
             if (op.flags & SET_OP_BARRIER) {
                 kx++;
                 // x that an op of the list writes may only be read behind the run's barrier
                 if (!(op.flags & SET_OP_XEXT)) while ((int)(ld_acquire_cta_shared_u32(bar_passed) - kx) < 0) __nanosleep(64);
             }
-            if (op.xtag == nullptr) set_quantize_x_blocks<NX>(xs, op.x, op.nbk, xt, (op.flags & SET_OP_XEXT) != 0);
+            if (op.xtag == nullptr) set_quantize_x_blocks<NX>(b ? xs1 : xs0, op.x, op.nbk, xt, (op.flags & SET_OP_XEXT) != 0);
             asm volatile("bar.sync 15, %0;" ::"n"(NX) : "memory");
-            if (xt == 0) mbar_arrive(xfull);
+            if (xt == 0) mbar_arrive(xfull0 + 8 * b);
             r++;
         }
         return;
@@ -617,7 +622,7 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
     c.G = G; c.group = warp / SET_WPG; c.wig = warp % SET_WPG; c.lane = lane;
     c.tag = (unsigned long long)s_launch << 32;
     c.done_local = done_local;
-    c.xempty = xempty;
+    c.xempty = xempty0;
     SetRing rp = {0, 0};
     int j = 0;
     unsigned nbar = 0, ntile_team = 0, nrun = 0;
@@ -642,8 +647,11 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
         if (PROF) { const long long t1 = clock64(); t_bar += t1 - tq0; tq0 = t1; }
         // the x warps have the run's quantized x in the planes (they started on it when the previous run's x went to
         // registers) -- or, for x that is another op's result, have handed the free planes over
-        mbar_wait(xfull, nrun & 1u);
+        const unsigned xb = x_bufs > 1 ? (nrun & 1u) : 0u, xu = x_bufs > 1 ? (nrun >> 1) : nrun;
+        mbar_wait(xfull0 + 8 * xb, xu & 1u);
         nrun++;
+        GemvSmem<1> & xs = xb ? xs1 : xs0;
+        c.xempty = xempty0 + 8 * xb;
         if (op.xtag != nullptr) {
             set_quantize_x<NCONS>(xs, x, op.xtag, c.tag, nbk, tid, false);
             set_consumer_sync<NCONS>();

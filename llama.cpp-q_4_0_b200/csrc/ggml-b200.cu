@@ -502,6 +502,7 @@ int ggml_b200_set_tuning(const char * key, int value) {
     else if (!strcmp(key, "set_fly"))      { g.tune.set_fly = value; }
     else if (!strcmp(key, "set_xext"))     { g.tune.set_xext = value != 0; }
     else if (!strcmp(key, "set_barrier_slack")) { g.tune.set_barrier_slack = value; }
+    else if (!strcmp(key, "set_xbufs"))    { if (value < 1 || value > 2) return GGML_B200_ERR_ARG; g.tune.set_xbufs = value; }
     else if (!strcmp(key, "set_split_barrier")) { g.tune.set_split_barrier = value != 0; }
     else if (!strcmp(key, "set_table"))    { g.tune.set_table = value != 0; }
     else if (!strcmp(key, "set_slots"))    { g.tune.set_slots = value; }

@@ -23,7 +23,7 @@ struct ggml_b200_set {
     unsigned long long * staging = nullptr;   // tagged dst rows of the ops a later op reads as x
     int linked_runs = 0;
     bool big = false;                       // some op has K > 16384: the kernel build with the 6-blocks-per-lane plan
-    int nslots = 0, slot_bytes = 0, x_bytes = 0, tbl_bytes = 0;
+    int nslots = 0, slot_bytes = 0, x_bytes = 0, x_bufs = 1, tbl_bytes = 0;      // x_bytes: all x buffers together
     size_t smem = 0;
     int barriers = 0;
     int warps = 16;
@@ -51,7 +51,7 @@ static int set_launch_tb(const ggml_b200_set * s, const SetOp * table, long long
     attr[0].id = cudaLaunchAttributeCooperative;
     attr[0].val.cooperative = 1;
     cfg.attrs = attr; cfg.numAttrs = g.tune.set_coop ? 1 : 0;
-    CK(cudaLaunchKernelEx(&cfg, kern, table, (int)s->host_ops.size(), s->sync, s->nslots, s->slot_bytes, s->x_bytes, s->tbl_bytes, g.tune.set_fly > 0 ? g.tune.set_fly : 1 << 30, (unsigned)g.launches, prof));
+    CK(cudaLaunchKernelEx(&cfg, kern, table, (int)s->host_ops.size(), s->sync, s->nslots, s->slot_bytes, s->x_bytes, s->x_bufs, s->tbl_bytes, g.tune.set_fly > 0 ? g.tune.set_fly : 1 << 30, (unsigned)g.launches, prof));
     g.launches++;
     return GGML_B200_OK;
 }
@@ -242,19 +242,25 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
     s->linked_runs = plan.linked_runs;
     const std::vector<int> & link_of = plan.link;
     s->slot_bytes = (s->slot_bytes + 127) & ~127;
-    s->x_bytes = 40 * nbk_max;
+    s->x_bytes = (40 * nbk_max + 127) & ~127;      // per buffer; everything behind it stays 128-byte aligned
     s->big = nbk_max > 512;
     s->tbl_bytes = (int)((s->host_ops.size() * sizeof(SetOpS) + 127) & ~(size_t)127);
     if (s->tbl_bytes > SET_MAX_TABLE_BYTES || g.tune.set_table == 0) s->tbl_bytes = 0;      // long list: descriptors stay in global memory
     for (const SetOp & o : s->host_ops) if (o.first_mod > 0xFFFF) s->tbl_bytes = 0;
-    const long long ring = (long long)MAX_DYN_SMEM - 1024 - s->x_bytes - SET_BAR_BYTES - SET_RED_BYTES - s->tbl_bytes - 128;
-    s->nslots = (int)(ring / s->slot_bytes);
-    if (s->nslots > SET_MAX_SLOTS) s->nslots = SET_MAX_SLOTS;
-    // Measured (profiles/r01_set_sweep_v5_slots.log, LLaMA-7B list, 12 warps): 3 slots 832 us, 4: 757, 5: 793, 6: 801, 8: 802 -- a ring
-    // one slot deeper than the number of consumer groups keeps the stream busy, and what the ring does not take stays L1
-    // (x of the next run is prefetched there).  set_slots overrides.
-    if (g.tune.set_slots > 0) { if (g.tune.set_slots < s->nslots) s->nslots = g.tune.set_slots; }
-    else if (s->nslots > NG + 1) s->nslots = NG + 1;
+    // ring depth: what fits, capped.  Measured (profiles/r01_set_sweep_v5_slots.log, LLaMA-7B list, 12 warps): 3 slots 832 us,
+    // 4: 757, 5: 793, 6: 801, 8: 802 -- a ring one slot deeper than the number of consumer groups keeps the stream busy, and
+    // what the ring does not take stays L1.  set_slots overrides.  A second x buffer (the x warps a whole run ahead)
+    // is taken when it does not cost the ring a slot.
+    auto depth = [&](int bufs) {
+        const long long ring = (long long)MAX_DYN_SMEM - 1024 - (long long)s->x_bytes * bufs - SET_BAR_BYTES - SET_RED_BYTES - s->tbl_bytes - 128;
+        int n = (int)(ring / s->slot_bytes);
+        if (n > SET_MAX_SLOTS) n = SET_MAX_SLOTS;
+        if (g.tune.set_slots > 0) { if (g.tune.set_slots < n) n = g.tune.set_slots; }
+        else if (n > NG + 1) n = NG + 1;
+        return n;
+    };
+    s->nslots = depth(1);
+    if (g.tune.set_xbufs > 1 && depth(2) == s->nslots) { s->x_bufs = 2; s->x_bytes *= 2; }
     if (s->nslots < 2) {
         set_error("K = %d: a 4-row tile (%d B) does not fit the shared-memory ring twice; use ggml_b200_mul_mat_q4_0 per op", nbk_max * QK, s->slot_bytes);
         delete s; return nullptr;

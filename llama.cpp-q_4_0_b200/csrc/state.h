@@ -47,6 +47,7 @@ struct Tune {
     int set_fly = 0;             // bulk copies in flight per CTA (0 = as many as the ring has free slots)
     int set_split_barrier = 1;   // dependency barriers: arrive after the last conflicting op, wait at the run that needs it (0: arrive right before the wait)
     int set_barrier_slack = 1 << 20;   // a dependency barrier also waits for everything up to this many ops before its run (default: only for what the run conflicts with, i.e. arrive as early as possible)
+    int set_xbufs = 2;           // quantized-x buffers in shared memory (2: the x warps may be a whole run ahead)
     int set_xext = 1;            // x that nothing in the list writes may be read before the run's barrier and through L1
     int set_table = 1;           // stage the op descriptors in shared memory when the list fits
     int set_slots = 0;           // cap on its ring depth (0 = as many as fit)
