@@ -97,3 +97,30 @@ def test_bad_arguments_are_rejected(b200):
         b200.set_plan([])
     with pytest.raises(b200.B200Error):
         b200.set_plan([(X0, Y[0], 64, 1000)])            # K not a multiple of 32
+
+
+def test_tuning_keys_change_the_plan_not_the_semantics(b200):
+    chain = [(X0, Y[0], 1024, 1024), (X0, Y[1], 1024, 1024), (Y[0], Y[2], 2048, 1024), (Y[2], Y[3], 512, 2048)]
+    layer = [(X0, Y[0], 256, 1024), (X1, Y[1], 256, 1024), (X2, Y[2], 256, 1024)]
+    try:
+        b200.set_tuning("set_link", 0)                      # no tagged words: every dependency is a barrier
+        nb, linked, p = b200.set_plan(chain)
+        assert linked == 0 and nb == 2 and [o["barrier"] for o in p] == [False, False, True, True]
+        assert [i for i, o in enumerate(p) for _ in range(o["arrivals"])] == [0, 2]      # behind the producer, not behind op 1
+        b200.set_tuning("set_link", 1)
+        b200.set_tuning("set_split_barrier", 0)             # arrive right before the wait: the classic grid barrier
+        nb, linked, p = b200.set_plan(layer * 3)
+        waits = [i for i, o in enumerate(p) if o["barrier"]]
+        arr = [i for i, o in enumerate(p) for _ in range(o["arrivals"])]
+        assert arr == [w - 1 for w in waits]
+        # a full barrier covers everything before it: one per layer instead of one per run
+        assert waits == [3, 6]
+        b200.set_tuning("set_split_barrier", 1)
+        nb, linked, p = b200.set_plan(layer * 3)
+        assert [i for i, o in enumerate(p) if o["barrier"]] == [3, 4, 5, 6, 7, 8]
+        assert [i for i, o in enumerate(p) for _ in range(o["arrivals"])] == [0, 1, 2, 3, 4, 5]
+        b200.set_tuning("set_xext", 0)
+        assert not any(o["ext"] for o in b200.set_plan(layer)[2])
+    finally:
+        for k, v in (("set_link", 1), ("set_split_barrier", 1), ("set_xext", 1)):
+            b200.set_tuning(k, v)
