@@ -161,6 +161,7 @@ int          ggml_b200_set_ops(const ggml_b200_set * s);       /* ops with a non
 int          ggml_b200_set_barriers(const ggml_b200_set * s);  /* grid-wide dependency barriers per launch */
 int          ggml_b200_set_linked_runs(const ggml_b200_set * s); /* runs whose x is read from its producer op's tagged rows */
 int          ggml_b200_set_slots(const ggml_b200_set * s);     /* depth of the shared-memory ring */
+int          ggml_b200_set_warps(const ggml_b200_set * s);     /* consumer warps per CTA ("set_warps", fewer when the ring is shallower than the groups) */
 uint64_t     ggml_b200_set_bytes(const ggml_b200_set * s);     /* algorithmic bytes per run */
 /* The hazard analysis of create, alone (pure host code: no device, nothing dereferenced; x and y are addresses as
  * integers): flags_out[i] = what the kernel is told about op i -- bit 0 a dependency barrier is waited for at its head,

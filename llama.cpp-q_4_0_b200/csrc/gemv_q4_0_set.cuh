@@ -359,6 +359,8 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
             // would fall through on the phase before that.  The previous use having been RELEASED (its `empty` phase;
             // that wait cannot alias: this tile's predecessors were issued after the use before that was released)
             // pins `full` to the phase waited for.  (The two tests must not be overlapped: issued back to back they failed.)
+            // Needs nslots >= NG, which the host guarantees: this group's previous tile j - NG is then not older than the
+            // slot's previous use j - nslots, so that use has been issued, i.e. the one before it released.
             if (j >= c.nslots) mbar_wait(empty, rp.phase ^ 1);
             mbar_wait(full, rp.phase);
             long long tc0 = 0;

@@ -200,7 +200,7 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
     ggml_b200_set * s = new ggml_b200_set();
     s->grid = g.sm_count;
     s->warps = g.tune.set_warps;
-    const int NG = s->warps / SET_WPG;
+    int NG = s->warps / SET_WPG;
     int nbk_max = 0;
     long long tiles = 0;
     std::vector<SetPlanOp> plan_ops;
@@ -260,6 +260,14 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
         return n;
     };
     s->nslots = depth(1);
+    // The ring must be at least as deep as there are consumer groups: the kernel's parity waits are alias-free only if a
+    // group's previous tile was issued after the previous use of its next slot (gemv_q4_0_set.cuh, tile loop) -- and a
+    // group without a slot of its own would idle anyway.  Huge K with 16 or 20 warps: fewer consumer warps.
+    if (s->nslots >= 2 && s->nslots < NG) {
+        s->warps = SET_WPG * s->nslots;
+        NG = s->nslots;
+        s->nslots = depth(1);
+    }
     if (g.tune.set_xbufs > 1 && depth(2) == s->nslots) { s->x_bufs = 2; s->x_bytes *= 2; }
     if (s->nslots < 2) {
         set_error("K = %d: a 4-row tile (%d B) does not fit the shared-memory ring twice; use ggml_b200_mul_mat_q4_0 per op", nbk_max * QK, s->slot_bytes);
@@ -337,6 +345,7 @@ int      ggml_b200_set_barriers(const ggml_b200_set * s) { return s ? s->barrier
 int      ggml_b200_set_linked_runs(const ggml_b200_set * s) { return s ? s->linked_runs : -1; }
 int      ggml_b200_set_ops(const ggml_b200_set * s) { return s ? (int)s->host_ops.size() : -1; }
 int      ggml_b200_set_slots(const ggml_b200_set * s) { return s ? s->nslots : -1; }
+int      ggml_b200_set_warps(const ggml_b200_set * s) { return s ? s->warps : -1; }
 uint64_t ggml_b200_set_bytes(const ggml_b200_set * s) { return s ? s->bytes : 0; }
 
 }  // extern "C"

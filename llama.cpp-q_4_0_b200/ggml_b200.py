@@ -89,6 +89,7 @@ def _load() -> C.CDLL:
         "ggml_b200_set_ops": (C.c_int, [_vp]),
         "ggml_b200_set_barriers": (C.c_int, [_vp]),
         "ggml_b200_set_slots": (C.c_int, [_vp]),
+        "ggml_b200_set_warps": (C.c_int, [_vp]),
         "ggml_b200_set_plan": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
         "ggml_b200_set_linked_runs": (C.c_int, [_vp]),
         "ggml_b200_set_bytes": (C.c_uint64, [_vp]),
@@ -381,6 +382,7 @@ class OpSet:
     n_ops = property(lambda self: int(lib().ggml_b200_set_ops(self.h)))
     barriers = property(lambda self: int(lib().ggml_b200_set_barriers(self.h)))
     slots = property(lambda self: int(lib().ggml_b200_set_slots(self.h)))
+    warps = property(lambda self: int(lib().ggml_b200_set_warps(self.h)))
     linked_runs = property(lambda self: int(lib().ggml_b200_set_linked_runs(self.h)))
     bytes = property(lambda self: int(lib().ggml_b200_set_bytes(self.h)))
 

@@ -348,3 +348,29 @@ def test_set_long_list_walks_the_table_in_global_memory(b200, port, ref):
     s.free()
     for w in ws:
         w.free()
+
+
+def test_set_ring_never_shallower_than_the_consumer_groups(b200, port, ref):
+    """K = 22016 with 20 consumer warps: four 49.5 KB slots fit, five groups were asked for.  The parity waits of the
+    tile loop need ring depth >= groups, so create takes 16 warps; many tiles per CTA, results against the oracle."""
+    M, K = 600, 22016
+    Ws = [make_weights(port, ref, M, K, 1500 + i) for i in range(3)]
+    ws = [b200.Weight(W) for W in Ws]
+    x = make_x(port, 1, K, 21)
+    xd = b200.DevBuf.from_numpy(x)
+    yd = [b200.DevBuf(M * 4) for _ in range(12)]
+    b200.set_tuning("set_warps", 20)
+    try:
+        s = b200.OpSet([(ws[i % 3], xd.ptr, yd[i].ptr) for i in range(12)])     # 12 x 150 tiles over 148 CTAs
+        assert s.slots >= 2 and s.warps == 4 * s.slots and s.warps < 20
+        for _ in range(10):
+            s.run()
+        b200.synchronize()
+        want = [oracle_Y(port, ref, W, x) for W in Ws]
+        for i in range(12):
+            assert_close(yd[i].to_numpy(np.float32, (1, M)), want[i % 3])
+        s.free()
+    finally:
+        b200.set_tuning("set_warps", 12)
+    for w in ws:
+        w.free()
