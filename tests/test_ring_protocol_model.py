@@ -1,0 +1,92 @@
+"""A model of the persistent kernel's weight ring (gemv_q4_0_set.cuh: producer thread, NG consumer groups, `full` /
+`empty` mbarriers per slot, parity waits) under an adversarial scheduler -- bulk copies land in ANY order, groups run at
+any relative speed.  It pins the protocol's two conditions, both found the hard way on the GPU (launch failures with
+12 warps / 4 slots, DESIGN.md kernel 2s):
+  * before waiting on `full`, a consumer waits for the slot's previous use to have been released (`empty`);
+  * the ring is at least as deep as there are consumer groups (ggml_b200_set_create guarantees it).
+A parity wait can only tell an mbarrier's current phase from the one before it; without these a wait falls through
+one phase early and the group consumes a slot that still holds (or is receiving) another tile."""
+import random
+
+import pytest
+
+
+class Mbar:
+    """mbarrier with one arrival per phase; try_wait.parity(P) is true when the phase with parity P is the most
+    recently COMPLETED one, i.e. the current (incomplete) phase has the other parity."""
+
+    def __init__(self):
+        self.phase = 0
+
+    def arrive(self):
+        self.phase += 1
+
+    def try_wait(self, parity):
+        return (self.phase & 1) != parity
+
+
+def run(ns, ng, tiles, seed, wait_released=True):
+    """Returns None when every tile was consumed from a slot holding exactly that tile, else a description."""
+    rng = random.Random(seed)
+    full = [Mbar() for _ in range(ns)]
+    empty = [Mbar() for _ in range(ns)]
+    content = [None] * ns
+    issued = 0
+    in_flight = []
+    nxt = list(range(ng))                 # next tile of every group
+    done = 0
+    for _ in range(100 * tiles + 1000):
+        acts = []
+        if issued < tiles:
+            s, use = issued % ns, issued // ns
+            if use == 0 or empty[s].try_wait((use - 1) & 1):
+                acts.append(("issue",))
+        for j in in_flight:
+            acts.append(("land", j))
+        for g in range(ng):
+            j = nxt[g]
+            if j >= tiles:
+                continue
+            s, use = j % ns, j // ns
+            if wait_released and use > 0 and not empty[s].try_wait((use - 1) & 1):
+                continue
+            if full[s].try_wait(use & 1):
+                acts.append(("consume", g))
+        if not acts:
+            return None if done == tiles else f"deadlock after {done} tiles"
+        a = rng.choice(acts)
+        if a[0] == "issue":
+            in_flight.append(issued)
+            issued += 1
+        elif a[0] == "land":
+            j = a[1]
+            in_flight.remove(j)
+            content[j % ns] = j
+            full[j % ns].arrive()
+        else:
+            g = a[1]
+            j = nxt[g]
+            if content[j % ns] != j:
+                return f"group {g} consumed slot {j % ns} for tile {j} while it held tile {content[j % ns]}"
+            empty[j % ns].arrive()
+            nxt[g] += ng
+            done += 1
+    return "no progress"
+
+
+@pytest.mark.parametrize("ns,ng", [(4, 3), (3, 2), (8, 3), (5, 4), (3, 3), (4, 4), (4, 2), (7, 3), (16, 5)])
+def test_protocol_holds_when_ring_is_at_least_as_deep_as_the_groups(ns, ng):
+    for seed in range(300):
+        assert run(ns, ng, 60, seed) is None, (ns, ng, seed)
+
+
+@pytest.mark.parametrize("ns,ng", [(4, 3), (3, 2)])
+def test_without_the_released_wait_the_parity_wait_falls_through(ns, ng):
+    """the configurations that failed on the GPU: ring depth = groups + 1"""
+    assert any(run(ns, ng, 60, seed, wait_released=False) is not None for seed in range(300))
+
+
+@pytest.mark.parametrize("ns,ng", [(3, 4), (2, 3), (4, 5)])
+def test_a_ring_shallower_than_the_groups_is_not_safe_even_with_it(ns, ng):
+    """why ggml_b200_set_create lowers the consumer warps instead"""
+    assert any(run(ns, ng, 60, seed) is not None for seed in range(500))
