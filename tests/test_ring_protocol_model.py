@@ -90,3 +90,47 @@ def test_without_the_released_wait_the_parity_wait_falls_through(ns, ng):
 def test_a_ring_shallower_than_the_groups_is_not_safe_even_with_it(ns, ng):
     """why ggml_b200_set_create lowers the consumer warps instead"""
     assert any(run(ns, ng, 60, seed) is not None for seed in range(500))
+
+
+# ---- split dependency barriers: why every barrier has its own arrival counter -----------------------------------
+def run_barriers(n_cta, arrive_at, wait_at, n_ops, seed, per_barrier):
+    """CTAs walk ops 0..n_ops-1 at any relative speed.  Barrier k: a CTA arrives when it has finished op arrive_at[k]
+    and must not start op wait_at[k] before EVERY CTA has finished op arrive_at[k].  Returns a violation or None."""
+    rng = random.Random(seed)
+    pos = [0] * n_cta                     # next op of every CTA
+    single = 0
+    cnt = [0] * len(arrive_at)
+    for _ in range(100 * n_cta * n_ops):
+        movable = []
+        for c in range(n_cta):
+            o = pos[c]
+            if o >= n_ops:
+                continue
+            blocked = False
+            for k, w in enumerate(wait_at):
+                if w == o:
+                    ok = cnt[k] >= n_cta if per_barrier else single >= (k + 1) * n_cta
+                    if not ok:
+                        blocked = True
+                    elif min(pos) <= arrive_at[k]:
+                        return f"CTA {c} passed barrier {k} while a CTA was still at op {min(pos)} <= {arrive_at[k]}"
+            if not blocked:
+                movable.append(c)
+        if not movable:
+            return None if min(pos) >= n_ops else "deadlock"
+        c = rng.choice(movable)
+        o = pos[c]
+        pos[c] += 1                       # op o finished
+        for k, a in enumerate(arrive_at):
+            if a == o:
+                cnt[k] += 1
+                single += 1
+    return "no progress"
+
+
+def test_per_barrier_counters_hold_and_one_running_counter_does_not():
+    # the decode list's pattern: arrival points early (several before the first wait), waits ops later
+    arrive_at, wait_at, n_ops = [2, 3, 5, 6], [7, 10, 11, 13], 14
+    for seed in range(300):
+        assert run_barriers(4, arrive_at, wait_at, n_ops, seed, per_barrier=True) is None
+    assert any(run_barriers(4, arrive_at, wait_at, n_ops, seed, per_barrier=False) is not None for seed in range(300))
