@@ -214,9 +214,14 @@ int ggml_b200_comm_rank(void) { return nc.rank; }
 int ggml_b200_comm_world(void) { return nc.world; }
 
 int ggml_b200_mul_mat_q4_0_sharded(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y_dev, size_t nb1) {
+    B200_API_LOCK;
     if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
     if (!w || !x_dev || !y_dev) { set_error("null argument"); return GGML_B200_ERR_ARG; }
     if (nc.world == 1) return ggml_b200_mul_mat_q4_0(w, x_dev, n, nb11, y_dev, nb1);
+    // the op contract of the single-GPU entry (ggml.c:11279-11285): n, src1 and dst row strides
+    if (n < 0 || n > INT32_MAX) { set_error("bad n"); return GGML_B200_ERR_ARG; }
+    if (nb11 < (size_t)w->K * 4 || (nb11 & 3)) { set_error("src1 row stride %zu < K*4 or not a multiple of 4", nb11); return GGML_B200_ERR_ARG; }
+    if (nb1 < (size_t)w->M * 4 || (nb1 & 3)) { set_error("dst row stride %zu < M*4 or not a multiple of 4", nb1); return GGML_B200_ERR_ARG; }
     if (!nc.comm) { set_error("ggml_b200_comm_init was not called"); return GGML_B200_ERR_STATE; }
     int64_t lo, hi;
     ggml_b200_shard_rows(w->M, nc.rank, nc.world, &lo, &hi);

@@ -33,12 +33,12 @@ __device__ __forceinline__ void quantize_x_to_smem(GemvSmem<1> & s, const float 
             const float * src = x + 8 * item;
             float v[8];
             if (x_aligned) {   // 2: x was written by other SMs during this kernel -> L2-coherent loads
-                const float4 a = x_aligned == 2 ? __ldcg(reinterpret_cast<const float4 *>(src)) : __ldg(reinterpret_cast<const float4 *>(src));
-                const float4 c = x_aligned == 2 ? __ldcg(reinterpret_cast<const float4 *>(src) + 1) : __ldg(reinterpret_cast<const float4 *>(src) + 1);
+                const float4 a = __ldcg(reinterpret_cast<const float4 *>(src));
+                const float4 c = __ldcg(reinterpret_cast<const float4 *>(src) + 1);
                 v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = c.x; v[5] = c.y; v[6] = c.z; v[7] = c.w;
             } else {
 #pragma unroll
-                for (int i = 0; i < 8; i++) v[i] = __ldg(src + i);
+                for (int i = 0; i < 8; i++) v[i] = __ldcg(src + i);
             }
             float amax = 0.0f;
 #pragma unroll

@@ -125,9 +125,13 @@ __device__ __forceinline__ void set_consumer_sync() {
 // hands the result to the other threads.  The arrival point is usually several ops before the wait (a layer's wq
 // against the next layer's wq: four ops), so the poll finds the count complete and a barrier costs two L2 round
 // trips of one thread that has nothing else to do (the sentinel) instead of a grid-wide rendezvous.
-__device__ __forceinline__ void set_barrier_arrive(uint32_t done_local, int lane) {
+// Each consumer warp publishes ITS OWN monotone count of arrival points passed (one shared word per warp): warps of
+// different groups are coupled only through the ring and may be several arrival points apart, so a single CTA-wide
+// count would let two fast groups (2-4 arrival points ahead on lists with less than a tile per CTA and op) stand in
+// for a slow one.  The sentinel forwards arrival e only when the MINIMUM over all W warps has reached it.
+__device__ __forceinline__ void set_barrier_arrive(uint32_t arr_slot, unsigned count, int lane) {
     __syncwarp();
-    if (lane == 0) asm volatile("red.release.cta.shared.add.u32 [%0], 1;" ::"r"(done_local) : "memory");
+    if (lane == 0) asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(arr_slot), "r"(count) : "memory");
 }
 // WAIT, by the CTA's sentinel thread (a warp of its own, so the two L2 round trips -- the poll that finds the count
 // complete and the acquire fence -- are off the consumers' path): it polls the barriers in list order ahead of the
@@ -299,7 +303,7 @@ struct SetCtx {
     int G, group, wig, lane;
     unsigned long long tag;           // launch number << 32
     uint32_t xempty;                  // mbarrier: every consumer warp has the run's x in registers (the planes are free)
-    uint32_t done_local;              // shared-memory count of consumer warps past the ops that barriers wait for
+    uint32_t arr_slot;                // this warp's shared-memory word: arrival points it has passed
 };
 
 // ring position of the CTA's next tile: slot index and the parity of its current use
@@ -313,7 +317,7 @@ struct SetRing {
 // `op` = descriptor of op o on entry, of the returned op on exit (when there is one).
 template <int NG, int WPR, int NCL, bool DUMP, bool PROF>
 __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<1> & xs, int o, SetOpC & op, int & j, SetRing & rp,
-                                               unsigned & ntile_team, long long & t_full, long long & t_comp, long long & n_tiles, long long * tx) {
+                                               unsigned & ntile_team, unsigned & narrived, long long & t_full, long long & t_comp, long long & n_tiles, long long * tx) {
     constexpr int RPT = WPR == 1 ? 2 : 4;               // rows of a tile per team
     constexpr int R = (SET_WPG / WPR) * RPT;            // 8 or 4
     constexpr int STRIDE = 32 * WPR;
@@ -428,7 +432,7 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
         if (PROF) { const long long now = clock64(); tx[2] += now - tl0; tl0 = now; }
         {
             const int narr = (op.flags >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK;
-            if (narr) set_barrier_arrive(c.done_local, c.lane);      // a later run waits for this op (and everything before it)
+            if (narr) set_barrier_arrive(c.arr_slot, ++narrived, c.lane);      // a later run waits for this op (and everything before it)
         }
         o++;
         if (o >= c.nops) break;
@@ -468,13 +472,13 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
     unsigned * bar_cnt = reinterpret_cast<unsigned *>(sync + 1);
     __shared__ unsigned s_launch;
     __shared__ unsigned s_bar_passed;                         // dependency barriers the sentinel has seen complete
-    __shared__ unsigned s_done_local;
+    __shared__ unsigned s_arrived[W];                         // per consumer warp: arrival points passed
     __shared__ __align__(8) uint64_t s_xbar[4];      // per x buffer: full [0..1], empty [2..3]
     const uint32_t xfull0 = smem_u32(&s_xbar[0]), xempty0 = smem_u32(&s_xbar[2]);
-    const uint32_t bar_passed = smem_u32(&s_bar_passed), done_local = smem_u32(&s_done_local);
+    const uint32_t bar_passed = smem_u32(&s_bar_passed), arrived0 = smem_u32(&s_arrived[0]);
+    if (tid < W) s_arrived[tid] = 0u;
     if (tid == 0) {
         s_bar_passed = 0u;
-        s_done_local = 0u;
         for (int b = 0; b < 2; b++) {
             mbar_init(xfull0 + 8 * b, 1);       // the x warps filled the planes with a run's quantized x (or handed them over: tagged x)
             mbar_init(xempty0 + 8 * b, W);      // every consumer warp copied the run's x to registers
@@ -564,7 +568,9 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
             while (ow < nops && !(flags_of(ow) & SET_OP_BARRIER)) ow++;
             while (oa < nops || ow < nops) {
                 bool progress = false;
-                if (oa < nops && (int)(ld_acquire_cta_shared_u32(done_local) - (ev + 1) * (unsigned)W) >= 0) {
+                bool all_arrived = oa < nops;
+                for (int w = 0; all_arrived && w < W; w++) all_arrived = (int)(ld_acquire_cta_shared_u32(arrived0 + 4 * w) - (ev + 1)) >= 0;
+                if (all_arrived) {
                     const int narr = (flags_of(oa) >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK;
                     for (int i = 0; i < narr; i++) red_release_gpu_add_u32(bar_cnt + kb++, 1u);      // barriers are numbered in the order of their arrival points
                     ev++;
@@ -604,11 +610,12 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
             if (!(op.flags & SET_OP_QUANT)) continue;
             const unsigned b = x_bufs > 1 ? (r & 1u) : 0u, u = x_bufs > 1 ? (r >> 1) : r;      // buffer, and its how-manieth use
             if (u > 0) mbar_wait_backoff(xempty0 + 8 * b, (u - 1) & 1u);
-            if (op.flags & SET_OP_BARRIER) {
-                kx++;
-                // x that an op of the list writes may only be read behind the run's barrier
-                if (!(op.flags & SET_OP_XEXT)) while ((int)(ld_acquire_cta_shared_u32(bar_passed) - kx) < 0) __nanosleep(64);
-            }
+            if (op.flags & SET_OP_BARRIER) kx++;
+            // x that an op of the list writes may only be read behind every barrier up to this run: the hazard analysis
+            // drops an op from the live sets once a barrier covers it, so a LATER run that reads its dst carries no flag
+            // of its own -- the consumers are behind that barrier by program order, the x warps (up to two runs ahead,
+            // and not held by barrier heads whose own x is external) must check the count themselves
+            if (!(op.flags & SET_OP_XEXT) && op.xtag == nullptr) while ((int)(ld_acquire_cta_shared_u32(bar_passed) - kx) < 0) __nanosleep(64);
             if (op.xtag == nullptr) set_quantize_x_blocks<NX>(b ? xs1 : xs0, op.x, op.nbk, xt, (op.flags & SET_OP_XEXT) != 0);
             asm volatile("bar.sync 15, %0;" ::"n"(NX) : "memory");
             if (xt == 0) mbar_arrive(xfull0 + 8 * b);
@@ -623,11 +630,11 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
     c.full0 = full0; c.empty0 = empty0; c.nslots = nslots; c.slot_bytes = slot_bytes;
     c.G = G; c.group = warp / SET_WPG; c.wig = warp % SET_WPG; c.lane = lane;
     c.tag = (unsigned long long)s_launch << 32;
-    c.done_local = done_local;
+    c.arr_slot = arrived0 + 4 * warp;
     c.xempty = xempty0;
     SetRing rp = {0, 0};
     int j = 0;
-    unsigned nbar = 0, ntile_team = 0, nrun = 0;
+    unsigned nbar = 0, ntile_team = 0, nrun = 0, narrived = 0;
     SetOpC op = set_load_op<DUMP>(ops, tbl, 0);
     long long tp[4] = {0, 0, 0, 0};
     long long tx[4] = {0, 0, 0, 0};
@@ -661,15 +668,15 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
         long long tr0 = 0;
         if (PROF) { tr0 = clock64(); t_quant += tr0 - tq0; }
         if (nbk <= SET_MAX_NBK_WPR1) {
-            if (nbk <= 32)       o = set_consume_run<NG, 1, 1, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx);
-            else if (nbk <= 64)  o = set_consume_run<NG, 1, 2, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx);
-            else if (nbk <= 96)  o = set_consume_run<NG, 1, 3, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx);
-            else                 o = set_consume_run<NG, 1, 4, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx);
+            if (nbk <= 32)       o = set_consume_run<NG, 1, 1, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
+            else if (nbk <= 64)  o = set_consume_run<NG, 1, 2, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
+            else if (nbk <= 96)  o = set_consume_run<NG, 1, 3, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
+            else                 o = set_consume_run<NG, 1, 4, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
         } else {
-            if (nbk <= 256)      o = set_consume_run<NG, 4, 2, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx);
-            else if (nbk <= 384) o = set_consume_run<NG, 4, 3, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx);
-            else if (nbk <= 512 || !BIG) o = set_consume_run<NG, 4, 4, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx);
-            else { if constexpr (BIG) o = set_consume_run<NG, 4, 6, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, t_full, t_comp, n_tiles, tx); }
+            if (nbk <= 256)      o = set_consume_run<NG, 4, 2, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
+            else if (nbk <= 384) o = set_consume_run<NG, 4, 3, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
+            else if (nbk <= 512 || !BIG) o = set_consume_run<NG, 4, 4, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
+            else { if constexpr (BIG) o = set_consume_run<NG, 4, 6, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx); }
         }
         if (PROF) t_run += clock64() - tr0;
     }

@@ -25,7 +25,6 @@
 #include "gemv_q4_0_fused.cuh"
 #include "gemv_q4_0_p2p.cuh"
 #include "gemv_q4_0_hostio.cuh"
-#include "gemv_q4_0_stream.cuh"
 #include "quantize_q8_0.cuh"
 #include "repack.cuh"
 #include "codec_q4_0.cuh"
@@ -34,6 +33,8 @@
 namespace b200 {
 
 Ctx g;
+std::recursive_mutex g_api_mu;
+unsigned g_init_epoch = 0;
 static std::mutex g_mu;
 static unsigned long long * h_trace_dev = nullptr;
 static unsigned int h_trace_cap = 0;
@@ -133,11 +134,7 @@ static int launch_gemv_planes_t(const ggml_b200_weight * w, float * y, long long
     const int nbk = (int)(w->K / QK);
     const size_t smem = gemv_smem_bytes(nbk, NC);
     auto kern = gemv_q4_0_planes_kernel<NC, UNROLL, DUMP>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
-        attr_set = true;
-    }
+    B200_SET_SMEM_ATTR(kern, MAX_DYN_SMEM);
     const int grid = g.sm_count * g.tune.gemv_ctas_per_sm;
     return launch_k(kern, grid, g.tune.gemv_threads, smem, (const uint4 *)w->wq, (const __half *)w->wd, (const int8_t *)g.xq, (const int2 *)g.xds, y, (int)w->rows(), nbk, ldy, n, S);
 }
@@ -147,11 +144,7 @@ static int launch_gemv_raw_t(const ggml_b200_weight * w, float * y, long long ld
     const int nbk = (int)(w->K / QK);
     const size_t smem = gemv_smem_bytes(nbk, NC);
     auto kern = gemv_q4_0_raw_kernel<NC, DUMP>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
-        attr_set = true;
-    }
+    B200_SET_SMEM_ATTR(kern, MAX_DYN_SMEM);
     const int grid = g.sm_count * g.tune.gemv_ctas_per_sm;
     return launch_k(kern, grid, g.tune.gemv_threads, smem, (const uint32_t *)w->raw, (const int8_t *)g.xq, (const int2 *)g.xds, y, (int)w->rows(), nbk, ldy, n, S);
 }
@@ -217,11 +210,7 @@ template <int UNROLL, int RIF, int MAXT, bool DUMP>
 static int launch_fused_t(const ggml_b200_weight * w, const float * x, float * y, int * S, unsigned char * b34) {
     const int nbk = (int)(w->K / QK);
     auto kern = gemv_q4_0_fused_kernel<UNROLL, RIF, MAXT, DUMP>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
-        attr_set = true;
-    }
+    B200_SET_SMEM_ATTR(kern, MAX_DYN_SMEM);
     int threads = g.tune.fused_threads > MAXT ? MAXT : g.tune.fused_threads;
     const int grid = g.sm_count * g.tune.fused_ctas_per_sm;
     const int aligned = (((uintptr_t)x) & 15) == 0;
@@ -232,49 +221,12 @@ static int launch_fused_t(const ggml_b200_weight * w, const float * x, float * y
     return rc;
 }
 
-// n == 1, plane layout: the streaming kernel (bulk-async ring + mbarriers, quantizer fused in)
-template <int NCL, bool DUMP>
-static int launch_stream_t(const ggml_b200_weight * w, const StreamPlan & p, const float * x, float * y, int * S, unsigned char * b34) {
-    auto kern = gemv_q4_0_stream_kernel<NCL, DUMP>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM));
-        attr_set = true;
-    }
-    const int nbk = (int)(w->K / QK);
-    const int aligned = (((uintptr_t)x) & 15) == 0;
-    int stages = p.stages;
-    if (g.tune.stream_stages > 1 && g.tune.stream_stages < stages && g.tune.stream_stages * p.rs >= STREAM_WARPS / p.wpr) stages = g.tune.stream_stages;
-    const size_t smem = (size_t)stages * p.stage_bytes + 128 + 128 + (size_t)40 * nbk;
-    return launch_k(kern, g.sm_count * g.tune.stream_ctas_per_sm, STREAM_THREADS, smem, (const uint4 *)w->wq, (const __half *)w->wd, x, y,
-                    (int)w->rows(), nbk, p.rs, p.wpr, stages, p.stage_bytes, aligned, S, b34, (unsigned)g.launches);
-}
-
-template <bool DUMP>
-static int launch_stream_d(const ggml_b200_weight * w, const float * x, float * y, int * S, unsigned char * b34) {
-    const StreamPlan p = stream_plan((int)(w->K / QK));
-    switch (p.ncl) {
-        case 1: return launch_stream_t<1, DUMP>(w, p, x, y, S, b34);
-        case 2: return launch_stream_t<2, DUMP>(w, p, x, y, S, b34);
-        case 3: return launch_stream_t<3, DUMP>(w, p, x, y, S, b34);
-        case 4: return launch_stream_t<4, DUMP>(w, p, x, y, S, b34);
-    }
-    set_error("no streaming-kernel instantiation for ncl=%d", p.ncl);
-    return GGML_B200_ERR_ARG;
-}
-
-bool stream_ok(const ggml_b200_weight * w, int64_t n) {
-    return n == 1 && g.tune.gemv_stream && g.tune.gemv_fused && !g.tune.skip_quantize && w->layout == GGML_B200_LAYOUT_PLANES &&
-           g.path != GGML_B200_PATH_GEMM && stream_plan((int)(w->K / QK)).ok;
-}
-
 bool fused_ok(const ggml_b200_weight * w, int64_t n) {
     return n == 1 && g.tune.gemv_fused && !g.tune.skip_quantize && w->layout == GGML_B200_LAYOUT_PLANES &&
            g.path != GGML_B200_PATH_GEMM && gemv_smem_bytes((int)(w->K / QK), 1) <= (size_t)MAX_DYN_SMEM;
 }
 
 int launch_fused(const ggml_b200_weight * w, const float * x, float * y, int * S, unsigned char * b34) {
-    if (stream_ok(w, 1)) return (S || b34) ? launch_stream_d<true>(w, x, y, S, b34) : launch_stream_d<false>(w, x, y, S, b34);
     // 1024 x 1 CTA/SM is best up to ~8k rows; beyond, 512 x 2 CTAs/SM (finer row interleave) wins
     // (profiles/r01_sweep_gemv_v2.log); an explicit fused_threads knob overrides
     // members of a same-src1 run take 512 threads (half an SM) with two rows in flight per warp, so that the run's
@@ -329,11 +281,7 @@ template <int MAXT>
 static int launch_fused_p2p_t(const ggml_b200_weight * w, const float * x_dev, float * y_dev, const P2PExchange & ex, int run_index) {
     const int nbk = (int)(w->K / QK);
     auto kern = gemv_q4_0_fused_p2p_kernel<4, MAXT>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM - 1024));   // the kernel has static smem too
-        attr_set = true;
-    }
+    B200_SET_SMEM_ATTR(kern, MAX_DYN_SMEM - 1024);
     const int aligned = (((uintptr_t)x_dev) & 15) == 0;
     return launch_k(kern, g.sm_count, MAXT, gemv_p2p_smem_bytes(nbk, (int)w->rows(), g.sm_count), (const uint4 *)w->wq, (const __half *)w->wd, x_dev, y_dev,
                     (int)w->rows(), nbk, aligned, (unsigned)g.launches, ex, run_index);
@@ -435,6 +383,7 @@ int ggml_b200_init(int device) {
     if ((s = getenv("GGML_B200_PATH")))       g.path = !strcmp(s, "gemv") ? GGML_B200_PATH_GEMV : !strcmp(s, "gemm") ? GGML_B200_PATH_GEMM : GGML_B200_PATH_AUTO;
     int rc = gemm_init();
     if (rc) return rc;
+    g_init_epoch++;
     g.inited = true;
     return GGML_B200_OK;
 }
@@ -480,13 +429,11 @@ void * ggml_b200_get_stream(void) { return (void *)g.stream; }
 uint64_t ggml_b200_launch_count(void) { return g.launches; }
 
 int ggml_b200_set_tuning(const char * key, int value) {
+    B200_API_LOCK;
     if (!strcmp(key, "gemv_threads"))      { if (value < 32 || value > 512 || (value & 31)) return GGML_B200_ERR_ARG; g.tune.gemv_threads = value; }
     else if (!strcmp(key, "gemv_ctas_per_sm")) { if (value < 1 || value > 16) return GGML_B200_ERR_ARG; g.tune.gemv_ctas_per_sm = value; }
     else if (!strcmp(key, "gemv_unroll"))  { g.tune.gemv_unroll = value; }
     else if (!strcmp(key, "gemv_nc"))      { g.tune.gemv_nc = value; }
-    else if (!strcmp(key, "gemv_stream"))  { g.tune.gemv_stream = value != 0; }
-    else if (!strcmp(key, "stream_stages")) { g.tune.stream_stages = value; }
-    else if (!strcmp(key, "stream_ctas_per_sm")) { if (value < 1 || value > 2) return GGML_B200_ERR_ARG; g.tune.stream_ctas_per_sm = value; }
     else if (!strcmp(key, "fused_rif"))    { g.tune.fused_rif = value; }
     else if (!strcmp(key, "gemv_fused"))   { g.tune.gemv_fused = value != 0; }
     else if (!strcmp(key, "pdl"))          { g.tune.pdl = value != 0; }
@@ -497,7 +444,6 @@ int ggml_b200_set_tuning(const char * key, int value) {
     else if (!strcmp(key, "overlap_same_src")) { g.tune.overlap_same_src = value != 0; g.run.count = 0; g.runN.count = 0; }
     else if (!strcmp(key, "set_coop"))     { g.tune.set_coop = value != 0; }
     else if (!strcmp(key, "set_warps"))    { if (value != 8 && value != 12 && value != 16 && value != 20) return GGML_B200_ERR_ARG; g.tune.set_warps = value; }
-    else if (!strcmp(key, "set_unsafe_no_barriers")) { g.tune.set_unsafe_no_barriers = value != 0; }
     else if (!strcmp(key, "set_link"))     { g.tune.set_link = value != 0; }
     else if (!strcmp(key, "set_fly"))      { g.tune.set_fly = value; }
     else if (!strcmp(key, "set_xext"))     { g.tune.set_xext = value != 0; }
@@ -530,6 +476,7 @@ int ggml_b200_synchronize(void) { CK(cudaStreamSynchronize(g.stream)); return GG
 
 // ---- upload -----------------------------------------------------------------------------------
 ggml_b200_weight * ggml_b200_upload_q4_0(const void * blocks, int64_t M, int64_t K, size_t nb1, int64_t row_lo, int64_t row_hi) {
+    B200_API_LOCK;
     if (!g.inited) { set_error("ggml_b200_init was not called"); return nullptr; }
     // ggml.c:2343-2344: n % 32 == 0 and an even number of blocks per row
     if (!blocks || M <= 0 || K <= 0 || (K % 64) != 0 || K > INT32_MAX) { set_error("bad shape M=%lld K=%lld (K must be a positive multiple of 64)", (long long)M, (long long)K); return nullptr; }
@@ -576,6 +523,7 @@ ggml_b200_weight * ggml_b200_upload_q4_0(const void * blocks, int64_t M, int64_t
 }
 
 void ggml_b200_free_weight(ggml_b200_weight * w) {
+    B200_API_LOCK;
     if (!w) return;
     if (g.run.head == w) { g.run.head = nullptr; g.run.count = 0; }
     gemm_release_weight(w);
@@ -593,6 +541,7 @@ int     ggml_b200_weight_layout(const ggml_b200_weight * w) { return w ? w->layo
 size_t  ggml_b200_weight_device_bytes(const ggml_b200_weight * w) { return w ? w->dev_bytes : 0; }
 
 int ggml_b200_download_q4_0(const ggml_b200_weight * w, void * out) {
+    B200_API_LOCK;
     if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
     if (!w || !out) { set_error("null argument"); return GGML_B200_ERR_ARG; }
     const int64_t rows = w->rows();
@@ -625,6 +574,7 @@ static unsigned codec_grid(long long threads_needed) {
 }
 
 int ggml_b200_quantize_q4_0(const float * x_dev, int64_t nrows, int64_t K, size_t nb1, void * blocks_dev) {
+    B200_API_LOCK;
     if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
     if (!x_dev || !blocks_dev || nrows < 0 || K <= 0 || (K % QK) != 0 || K > INT32_MAX || nb1 < (size_t)K * 4 || (nb1 & 3)) { set_error("bad quantize_q4_0 arguments"); return GGML_B200_ERR_ARG; }
     if (nrows == 0) return GGML_B200_OK;
@@ -635,6 +585,7 @@ int ggml_b200_quantize_q4_0(const float * x_dev, int64_t nrows, int64_t K, size_
 }
 
 int ggml_b200_dequantize_q4_0(const void * blocks_dev, int64_t nblocks, float * y_dev) {
+    B200_API_LOCK;
     if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
     if (!blocks_dev || !y_dev || nblocks < 0) { set_error("bad dequantize_q4_0 arguments"); return GGML_B200_ERR_ARG; }
     if (nblocks == 0) return GGML_B200_OK;
@@ -645,6 +596,7 @@ int ggml_b200_dequantize_q4_0(const void * blocks_dev, int64_t nblocks, float * 
 }
 
 int ggml_b200_get_rows_q4_0(const ggml_b200_weight * w, const int32_t * ids_dev, int64_t n, float * y_dev, size_t nb1) {
+    B200_API_LOCK;
     if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
     if (!w || !ids_dev || !y_dev || n < 0 || nb1 < (size_t)w->K * 4 || (nb1 & 3)) { set_error("bad get_rows arguments"); return GGML_B200_ERR_ARG; }
     if (n == 0) return GGML_B200_OK;
@@ -669,6 +621,7 @@ int ggml_b200_get_rows_q4_0(const ggml_b200_weight * w, const int32_t * ids_dev,
 
 // ---- kernel 1 ---------------------------------------------------------------------------------
 int ggml_b200_quantize_q8_0(const float * x_dev, int64_t n, int64_t K, size_t nb11, void * blocks34_dev) {
+    B200_API_LOCK;
     if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
     if (!x_dev || n < 0 || K <= 0 || (K % QK) != 0 || nb11 < (size_t)K * 4 || (nb11 & 3)) { set_error("bad quantize arguments"); return GGML_B200_ERR_ARG; }
     return launch_quantize(x_dev, n, K, nb11, blocks34_dev);
@@ -676,6 +629,7 @@ int ggml_b200_quantize_q8_0(const float * x_dev, int64_t n, int64_t K, size_t nb
 
 // ---- the op -----------------------------------------------------------------------------------
 int ggml_b200_mul_mat_q4_0(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y_dev, size_t nb1) {
+    B200_API_LOCK;
     int rc = check_op_args(w, x_dev, n, nb11, y_dev, nb1);
     if (rc) return rc;
     return mul_mat_dev(w, x_dev, n, nb11, y_dev, nb1);
@@ -705,7 +659,12 @@ static void hostio_release() {
 
 static inline uint64_t now_ns() { return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
-static bool hostio_ok(const ggml_b200_weight * w, int64_t n) { return g.tune.host_fast && fused_ok(w, n) && !stream_ok(w, n); }
+static size_t hostio_smem(const ggml_b200_weight * w) {
+    return gemv_smem_bytes((int)(w->K / QK), 1) + (size_t)((w->rows() + g.sm_count - 1) / g.sm_count) * 4 + 16;
+}
+// (the kernel has a little static shared memory: its attribute is capped at MAX_DYN_SMEM - 1024; what does not fit
+// takes the staged cudaMemcpyAsync path below)
+static bool hostio_ok(const ggml_b200_weight * w, int64_t n) { return g.tune.host_fast && fused_ok(w, n) && hostio_smem(w) <= (size_t)MAX_DYN_SMEM - 1024; }
 
 static int mul_mat_hostio(const ggml_b200_weight * w, const float * x_host, float * y_host) {
     auto & h = g.hio;
@@ -729,10 +688,9 @@ static int mul_mat_hostio(const ggml_b200_weight * w, const float * x_host, floa
     io.x_dev = h.xdev; io.counters = h.counters; io.seq = ++h.seq;
     static const int verbose = getenv("GGML_B200_VERBOSE") != nullptr;
     io.profile = verbose;
-    const size_t smem = gemv_smem_bytes(nbk, 1) + (size_t)((rows + g.sm_count - 1) / g.sm_count) * 4 + 16;
+    const size_t smem = hostio_smem(w);
     auto kern = gemv_q4_0_hostio_kernel<4, 1024>;
-    static bool attr_set = false;
-    if (!attr_set) { CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM - 1024)); attr_set = true; }
+    B200_SET_SMEM_ATTR(kern, MAX_DYN_SMEM - 1024);
     rc = launch_k(kern, g.sm_count, 1024, smem, (const uint4 *)w->wq, (const __half *)w->wd, (int)rows, nbk, io);
     if (rc) { h.seq--; return rc; }
     // copy y out as it lands: a word is valid once it carries this op's number.  Look at the stream now and then
@@ -772,6 +730,7 @@ static int mul_mat_hostio(const ggml_b200_weight * w, const float * x_host, floa
 }
 
 int ggml_b200_mul_mat_q4_0_host(const ggml_b200_weight * w, const float * x_host, int64_t n, size_t nb11, float * y_host, size_t nb1) {
+    B200_API_LOCK;
     int rc = check_op_args(w, x_host, n, nb11, y_host, nb1);
     if (rc) return rc;
     const int64_t rows = w->rows();
@@ -798,6 +757,7 @@ int ggml_b200_mul_mat_q4_0_host(const ggml_b200_weight * w, const float * x_host
 }
 
 int ggml_b200_block_dots_q4_0(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, int32_t * S_dev, int path) {
+    B200_API_LOCK;
     if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
     if (!w || !x_dev || !S_dev || n < 0 || nb11 < (size_t)w->K * 4 || (nb11 & 3)) { set_error("bad block_dots arguments"); return GGML_B200_ERR_ARG; }
     if (n == 0 || w->rows() == 0) return GGML_B200_OK;
@@ -844,6 +804,7 @@ int ggml_b200_trace_end(unsigned long long * out, unsigned int max_records) {
 }
 
 int ggml_b200_fused_checkpoint_q4_0(const ggml_b200_weight * w, const float * x_dev, int32_t * S_dev, void * blocks34_dev) {
+    B200_API_LOCK;
     if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
     if (!w || !x_dev) { set_error("null argument"); return GGML_B200_ERR_ARG; }
     if (w->layout != GGML_B200_LAYOUT_PLANES) { set_error("the fused kernel needs the plane layout"); return GGML_B200_ERR_ARG; }

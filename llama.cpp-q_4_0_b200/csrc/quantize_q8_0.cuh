@@ -43,13 +43,13 @@ quantize_q8_0_kernel(const float * __restrict__ x, long long n, int K, size_t nb
     const float * src = reinterpret_cast<const float *>(reinterpret_cast<const char *>(x) + row * nb11) + 8 * j;
     float v[8];
     if (ALIGNED) {
-        const float4 a = __ldg(reinterpret_cast<const float4 *>(src));
-        const float4 b = __ldg(reinterpret_cast<const float4 *>(src) + 1);
+        const float4 a = __ldcg(reinterpret_cast<const float4 *>(src));
+        const float4 b = __ldcg(reinterpret_cast<const float4 *>(src) + 1);
         v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
         v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
     } else {
 #pragma unroll
-        for (int i = 0; i < 8; i++) v[i] = __ldg(src + i);
+        for (int i = 0; i < 8; i++) v[i] = __ldcg(src + i);
     }
 
     float amax = 0.0f;

@@ -38,11 +38,7 @@ static bool set_ranges_overlap(const float * a_lo, const float * a_hi, const flo
 template <int W, bool DUMP, bool PROF, bool BIG>
 static int set_launch_tb(const ggml_b200_set * s, const SetOp * table, long long * prof) {
     auto kern = gemv_q4_0_set_kernel<W, DUMP, PROF, BIG>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_DYN_SMEM - 1024));   // the kernel has a little static shared memory too
-        attr_set = true;
-    }
+    B200_SET_SMEM_ATTR(kern, MAX_DYN_SMEM - 1024);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)s->grid); cfg.blockDim = dim3(W * 32 + SET_EXTRA_THREADS); cfg.dynamicSmemBytes = s->smem; cfg.stream = g.stream;
     // every CTA of the grid must be resident at once (dependency barriers spin on peers): cooperative launch makes
@@ -139,7 +135,7 @@ static int set_plan_hazards(const std::vector<SetPlanOp> & ops, const Tune & tun
         }
         const bool same_run = i > 0 && !barrier && run_x == o.x && run_K == o.K && run_link == link;
         if (!same_run) {
-            const bool bar = barrier && i > 0 && !tune.set_unsafe_no_barriers;
+            const bool bar = barrier && i > 0;
             out.flags[i] = SET_OP_QUANT | (bar ? SET_OP_BARRIER : 0);
             if (bar) {
                 out.barriers++;
@@ -195,6 +191,7 @@ int ggml_b200_set_plan(const ggml_b200_set_plan_op * ops, int n_ops, int * flags
 }
 
 ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
+    B200_API_LOCK;
     if (!g.inited) { set_error("ggml_b200_init was not called"); return nullptr; }
     if (!ops || n_ops <= 0) { set_error("empty op list"); return nullptr; }
     ggml_b200_set * s = new ggml_b200_set();
@@ -298,6 +295,7 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
 }
 
 void ggml_b200_set_free(ggml_b200_set * s) {
+    B200_API_LOCK;
     if (!s) return;
     if (s->dev_ops) cudaFree(s->dev_ops);
     if (s->dev_ops_dump) cudaFree(s->dev_ops_dump);
@@ -307,12 +305,14 @@ void ggml_b200_set_free(ggml_b200_set * s) {
 }
 
 int ggml_b200_set_run(ggml_b200_set * s) {
+    B200_API_LOCK;
     if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
     if (!s) { set_error("null set"); return GGML_B200_ERR_ARG; }
     return set_launch<false, false>(s, s->dev_ops);
 }
 
 int ggml_b200_set_checkpoint(ggml_b200_set * s, int32_t * const * S_dev, int n_ops) {
+    B200_API_LOCK;
     if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
     if (!s || !S_dev || n_ops != (int)s->host_ops.size()) { set_error("set_checkpoint: need one S pointer per non-empty op (%d)", s ? (int)s->host_ops.size() : 0); return GGML_B200_ERR_ARG; }
     std::vector<SetOp> t = s->host_ops;
@@ -324,6 +324,7 @@ int ggml_b200_set_checkpoint(ggml_b200_set * s, int32_t * const * S_dev, int n_o
 }
 
 int ggml_b200_set_profile(ggml_b200_set * s, long long * out_host, int max_ctas) {
+    B200_API_LOCK;
     if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
     if (!s || !out_host || max_ctas <= 0) { set_error("bad set_profile arguments"); return GGML_B200_ERR_ARG; }
     long long * dev = nullptr;

@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
+
 #include "../../include/ggml-b200.h"
 #include "p2p.cuh"
 
@@ -31,9 +33,6 @@ struct Tune {
     int gemv_unroll = 4;         // 16-byte weight loads in flight per lane
     int gemv_nc = 0;             // cap on columns per pass (0 = by n)
     int fused_rif = 1;           // rows in flight per warp of the fused kernel
-    int gemv_stream = 0;         // n == 1: bulk-async smem ring kernel (gemv_q4_0_stream.cuh)
-    int stream_stages = 0;       // cap on the ring depth (0 = as many as fit in 96 KB)
-    int stream_ctas_per_sm = 1;
     int gemv_fused = 1;          // n == 1: quantize inside the GEMV kernel (one launch per op)
     int fused_threads = 1024;    // threads per CTA of the fused kernel
     int fused_ctas_per_sm = 1;
@@ -42,7 +41,6 @@ struct Tune {
     int host_fast = 1;           // n == 1 host entry: single-launch path with mapped staging rows and a completion word
     int set_coop = 1;            // persistent multi-op kernel: cooperative launch (the driver checks co-residency of the grid)
     int set_warps = 12;          // its consumer warps per CTA (8, 12, 16 or 20)
-    int set_unsafe_no_barriers = 0;   // MEASUREMENT ONLY: drop the dependency barriers (results are wrong when ops depend on each other)
     int set_link = 1;            // x that is exactly the dst of one earlier op is read from that op's tagged rows (0: grid barrier instead)
     int set_fly = 0;             // bulk copies in flight per CTA (0 = as many as the ring has free slots)
     int set_split_barrier = 1;   // dependency barriers: arrive after the last conflicting op, wait at the run that needs it (0: arrive right before the wait)
@@ -87,6 +85,20 @@ struct Ctx {
 };
 
 extern Ctx g;
+// One process = one device = one Ctx: the public entry points that touch it (workspaces, the same-src1 run records, the
+// staging rows) are serialised by this lock, so two host threads calling the C ABI cannot corrupt each other.
+extern std::recursive_mutex g_api_mu;
+#define B200_API_LOCK std::lock_guard<std::recursive_mutex> api_lock_(::b200::g_api_mu)
+// kernels' dynamic-shared-memory attributes are per device: set again after ggml_b200_shutdown() + init on another one
+extern unsigned g_init_epoch;
+#define B200_SET_SMEM_ATTR(kern, bytes)                                                                    \
+    do {                                                                                                   \
+        static unsigned seen_ = 0;                                                                         \
+        if (seen_ != ::b200::g_init_epoch) {                                                               \
+            CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)));    \
+            seen_ = ::b200::g_init_epoch;                                                                  \
+        }                                                                                                  \
+    } while (0)
 
 void set_error(const char * fmt, ...);
 int  cuda_fail(cudaError_t e, const char * what, const char * file, int line);

@@ -135,8 +135,11 @@ void ggml_cuda_free_data(struct ggml_tensor * tensor) {
  * The reference also grabs large CPU-resident matmuls and uploads them per call; this back-end only takes
  * weights that were uploaded at load time. */
 bool ggml_cuda_can_mul_mat(const struct ggml_tensor * src0, const struct ggml_tensor * src1, struct ggml_tensor * dst) {
+    /* 2-D only (every Q4_0 weight of the models is; a batched src1 falls through to the CPU code instead of aborting),
+     * K a multiple of 64 (ggml.c:2343-2344) */
     return g_ready && weight_of(src0) != NULL && src0->type == GGML_TYPE_Q4_0 && src1->type == GGML_TYPE_F32 &&
-           dst->type == GGML_TYPE_F32 && src1->backend == GGML_BACKEND_CPU && dst->backend == GGML_BACKEND_CPU;
+           dst->type == GGML_TYPE_F32 && src1->backend == GGML_BACKEND_CPU && dst->backend == GGML_BACKEND_CPU &&
+           src0->ne[2] == 1 && src0->ne[3] == 1 && src1->ne[2] == 1 && src1->ne[3] == 1 && src0->ne[0] % 64 == 0;
 }
 
 size_t ggml_cuda_mul_mat_get_wsize(const struct ggml_tensor * src0, const struct ggml_tensor * src1, struct ggml_tensor * dst) {

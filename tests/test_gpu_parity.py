@@ -266,16 +266,16 @@ def test_fused_kernel_checkpoints_bit_exact(b200, port, ref, golden, M, K):
     want_q8 = port.quantize_q8_0(x)
     assert np.array_equal(q8, want_q8[0])
     assert np.array_equal(S, port.block_dots_matrix(W, want_q8)[0])
-    Ys = b200.mul_mat_host(w, x)                      # streaming kernel (default for n = 1)
-    b200.set_tuning("gemv_stream", 0)
+    Ys = b200.mul_mat_host(w, x)                      # the one-launch host entry point (gemv_q4_0_hostio.cuh)
     try:
-        q8r, Sr = b200.fused_checkpoint(w, x)          # register-streaming fused kernel
-        Yf = b200.mul_mat_host(w, x)
+        q8r, Sr = b200.fused_checkpoint(w, x)
+        b200.set_tuning("host_fast", 0)
+        Yf = b200.mul_mat_host(w, x)                  # fused kernel behind staged copies
         b200.set_tuning("gemv_fused", 0)
         Yu = b200.mul_mat_host(w, x)                  # kernel 1 + kernel 2 as two launches
     finally:
         b200.set_tuning("gemv_fused", 1)
-        b200.set_tuning("gemv_stream", 1)
+        b200.set_tuning("host_fast", 1)
     w.free()
     assert np.array_equal(q8r, want_q8[0]) and np.array_equal(Sr, S)
     assert np.array_equal(Yf.view(np.uint32), Yu.view(np.uint32))   # same accumulation order

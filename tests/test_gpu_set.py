@@ -374,3 +374,89 @@ def test_set_ring_never_shallower_than_the_consumer_groups(b200, port, ref):
         b200.set_tuning("set_warps", 12)
     for w in ws:
         w.free()
+
+
+@pytest.mark.parametrize("warps", [8, 12, 16])
+def test_set_many_tiny_ops_barrier_after_each(b200, port, ref, warps):
+    """Advisor r1 (high): with about one tile or fewer per CTA and op, consumer groups without a tile walk straight
+    through the arrival points; a CTA-wide arrival COUNT let two fast groups stand in for a slow one and released a
+    barrier before every writer had stored.  The arrival is now per warp (minimum over the CTA's warps).  120 ops of
+    8-300 rows (1-38 tiles over 148 CTAs): even ops write one of four scratch buffers round-robin (write-after-write
+    barriers), odd ops read a scratch buffer written earlier through a partial overlap (read-after-write barriers).
+    Every odd op's result and the final scratch contents are compared with the per-op path, 6 launches."""
+    K = 1024
+    rows = [24, 300, 64, 152, 40, 96, 8, 256]
+    Ws = [make_weights(port, ref, M, K, 1600 + i) for i, M in enumerate(rows)]
+    ws = [b200.Weight(W) for W in Ws]
+    x0 = make_x(port, 1, K, 31)
+    xd = b200.DevBuf.from_numpy(x0)
+    init = [np.ascontiguousarray(make_x(port, 1, K + 16, 77 + j).reshape(-1)) for j in range(4)]
+    scratch = [b200.DevBuf.from_numpy(v) for v in init]          # dst of the even ops; first K floats = x of the odd ops
+    outs = [b200.DevBuf(300 * 4) for _ in range(120)]
+    ops = []
+    for i in range(120):
+        k = (5 * i + i // 7) % len(rows)
+        if i % 2 == 0:
+            ops.append((ws[k], xd.ptr, scratch[(i // 2) % 4].ptr))
+        else:
+            ops.append((ws[k], scratch[((i // 2) + 2) % 4].ptr, outs[i].ptr))
+
+    def reset():
+        for sb, v in zip(scratch, init):
+            b200.lib().ggml_b200_memcpy_h2d(sb.ptr, v.ctypes.data_as(C.c_void_p), v.nbytes)
+
+    b200.set_tuning("set_warps", warps)
+    try:
+        s = b200.OpSet(ops)
+        assert s.barriers >= 50 and s.linked_runs == 0
+        reset()
+        _per_op(b200, ops)
+        want = [o.to_numpy(np.float32, (300,)).copy() for o in outs]
+        want_s = [sb.to_numpy(np.float32, (K + 16,)).copy() for sb in scratch]
+        for rep in range(6):
+            reset()
+            for o in outs:
+                b200.lib().ggml_b200_memcpy_h2d(o.ptr, np.zeros(300, np.float32).ctypes.data_as(C.c_void_p), 1200)
+            s.run()
+            b200.synchronize()
+            for i in range(1, 120, 2):
+                M = rows[(5 * i + i // 7) % len(rows)]
+                assert np.array_equal(outs[i].to_numpy(np.float32, (300,))[:M], want[i][:M]), f"rep {rep}: op {i} read its x before the writer was done"
+            for j, sb in enumerate(scratch):
+                assert np.array_equal(sb.to_numpy(np.float32, (K + 16,)), want_s[j]), f"rep {rep}: scratch {j}: the wrong writer won"
+        s.free()
+    finally:
+        b200.set_tuning("set_warps", 12)
+    for w in ws:
+        w.free()
+
+
+def test_set_x_of_an_op_a_barrier_already_covers(b200, port, ref):
+    """Advisor r1 (medium): op3 reads the dst of op0, but a write-after-write barrier between them (op2 rewrites op1's
+    dst; its own x is external) already covers op0, so the hazard analysis gives op3's run no flag of its own.  The x
+    warps run up to two runs ahead of the consumers and used to wait only at barrier heads with non-external x: they
+    could quantize y_A before the barrier that guarantees it.  Big op0 (slow to finish), tiny ops behind it."""
+    K = 1024
+    W0 = make_weights(port, ref, 1024, K, 1700)       # y_A, K floats: the x of op3
+    W1 = make_weights(port, ref, 64, K, 1701)
+    W2 = make_weights(port, ref, 64, K, 1702)
+    W3 = make_weights(port, ref, 200, 1024, 1703)
+    ws = [b200.Weight(W) for W in (W0, W1, W2, W3)]
+    x0, x1 = make_x(port, 1, K, 41), make_x(port, 1, K, 42)
+    xd0, xd1 = b200.DevBuf.from_numpy(x0), b200.DevBuf.from_numpy(x1)
+    yA, yB, yC = b200.DevBuf(1024 * 4), b200.DevBuf(64 * 4), b200.DevBuf(200 * 4)
+    ops = [(ws[0], xd0.ptr, yA.ptr), (ws[1], xd0.ptr, yB.ptr), (ws[2], xd1.ptr, yB.ptr), (ws[3], yA.ptr, yC.ptr)]
+    s = b200.OpSet(ops)
+    assert s.barriers == 1 and s.linked_runs == 0      # the WAW barrier covers op0; op3's run has no flag of its own
+    want_A = oracle_Y(port, ref, W0, x0)
+    for rep in range(20):
+        b200.lib().ggml_b200_memcpy_h2d(yA.ptr, np.full(1024, 1e30, np.float32).ctypes.data_as(C.c_void_p), 4096)   # stale x would be loud
+        s.run()
+        b200.synchronize()
+        got_A = yA.to_numpy(np.float32, (1, 1024))
+        assert_close(got_A, want_A)
+        assert_close(yC.to_numpy(np.float32, (1, 200)), oracle_Y(port, ref, W3, got_A))
+        assert_close(yB.to_numpy(np.float32, (1, 64)), oracle_Y(port, ref, W2, x1))
+    s.free()
+    for w in ws:
+        w.free()

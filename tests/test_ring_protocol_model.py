@@ -134,3 +134,47 @@ def test_per_barrier_counters_hold_and_one_running_counter_does_not():
     for seed in range(300):
         assert run_barriers(4, arrive_at, wait_at, n_ops, seed, per_barrier=True) is None
     assert any(run_barriers(4, arrive_at, wait_at, n_ops, seed, per_barrier=False) is not None for seed in range(300))
+
+
+# ---- inside a CTA: why the arrival is counted per WARP (advisor r1) ---------------------------------------------------
+def run_cta_arrivals(n_groups, warps_per_group, ops_with_tile, arrive_ops, max_skew, seed, per_warp):
+    """One CTA.  Group g has a tile only in the ops of ops_with_tile[g]; a warp that has no tile in an op walks through
+    it.  Every warp arrives (counts itself) at the ops in arrive_ops.  The sentinel forwards arrival e when
+      per_warp:  min over warps of (arrival points passed) >= e + 1
+      else:      the CTA-wide sum of arrivals >= (e + 1) * W          (the round-1 code)
+    Warps of different groups are coupled only by the ring: a warp may be at most max_skew ops ahead of the slowest.
+    Returns a violation (arrival e forwarded while some warp has not finished op arrive_ops[e]) or None."""
+    rng = random.Random(seed)
+    W = n_groups * warps_per_group
+    n_ops = max(arrive_ops) + 2
+    pos = [0] * W                         # ops finished per warp
+    arrived = [0] * W
+    forwarded = 0
+    for _ in range(200 * W * n_ops):
+        while forwarded < len(arrive_ops):
+            ok = min(arrived) >= forwarded + 1 if per_warp else sum(arrived) >= (forwarded + 1) * W
+            if not ok:
+                break
+            if min(pos) <= arrive_ops[forwarded]:
+                return f"arrival {forwarded} forwarded while a warp is still at op {min(pos)} <= {arrive_ops[forwarded]}"
+            forwarded += 1
+        movable = [w for w in range(W) if pos[w] < n_ops and pos[w] - min(pos) < max_skew]
+        if not movable:
+            return None
+        # a group with a tile in its current op is slow (it waits for the bulk copy); empty-handed groups run ahead
+        fast = [w for w in movable if pos[w] not in ops_with_tile[w // warps_per_group]]
+        w = rng.choice(fast if fast and rng.random() < 0.9 else movable)
+        if pos[w] in arrive_ops:
+            arrived[w] += 1
+        pos[w] += 1
+    return None
+
+
+def test_arrivals_counted_per_warp_hold_and_a_cta_wide_count_does_not():
+    # 3 groups x 4 warps (W = 12); group 0 holds the only tile of op 0, the others have none in ops 0..3;
+    # every op is an arrival point; the ring lets a group run 4 ops ahead: 8 warps x 2 arrivals = 16 >= 12
+    tiles = [{0}, set(), set()]
+    arrive_ops = [0, 1, 2, 3]
+    for seed in range(300):
+        assert run_cta_arrivals(3, 4, tiles, arrive_ops, 4, seed, per_warp=True) is None
+    assert any(run_cta_arrivals(3, 4, tiles, arrive_ops, 4, seed, per_warp=False) is not None for seed in range(300))

@@ -50,11 +50,10 @@ def main():
         hs = [L_.ggml_b200_upload_q4_0(blk.ctypes.data_as(C.c_void_p), M, K, (K // 32) * 18, 0, M) for _ in range(min(ncopies, 64))]
         x = torch.randn(1, K, device="cuda")
         y = torch.zeros(1, M, device="cuda")
-        for label, t in [("fused1024 pdl", dict(gemv_fused=1, gemv_stream=0, fused_threads=1024, fused_ctas_per_sm=1, fused_rif=1, pdl=1)),
-                         ("fused1024 nopdl", dict(gemv_fused=1, gemv_stream=0, fused_threads=1024, fused_ctas_per_sm=1, fused_rif=1, pdl=0)),
-                         ("fused512x1rif2 pdl", dict(gemv_fused=1, gemv_stream=0, fused_threads=512, fused_ctas_per_sm=1, fused_rif=2, pdl=1)),
-                         ("stream pdl", dict(gemv_fused=1, gemv_stream=1, pdl=1)),
-                         ("unfused pdl", dict(gemv_fused=0, gemv_stream=0, pdl=1))]:
+        for label, t in [("fused1024 pdl", dict(gemv_fused=1, fused_threads=1024, fused_ctas_per_sm=1, fused_rif=1, pdl=1)),
+                         ("fused1024 nopdl", dict(gemv_fused=1, fused_threads=1024, fused_ctas_per_sm=1, fused_rif=1, pdl=0)),
+                         ("fused512x1rif2 pdl", dict(gemv_fused=1, fused_threads=512, fused_ctas_per_sm=1, fused_rif=2, pdl=1)),
+                         ("unfused pdl", dict(gemv_fused=0, pdl=1))]:
             for k, v in t.items():
                 mod.set_tuning(k, v)
             cold = timeit(mod, L_, stream, hs, x, y, M, K, len(hs))

@@ -29,7 +29,7 @@ def main():
     mod.set_stream(stream.cuda_stream)
     rng = np.random.default_rng(1)
     peak, _ = bench.peaks()
-    base = dict(gemv_fused=1, gemv_stream=0, pdl=1, gemv_unroll=4, fused_threads=1024, fused_ctas_per_sm=1, fused_rif=1)
+    base = dict(gemv_fused=1, pdl=1, gemv_unroll=4, fused_threads=1024, fused_ctas_per_sm=1, fused_rif=1)
     cfgs = []
     for pdl in (1, 0):
         cfgs.append(dict(base, pdl=pdl))
@@ -40,7 +40,6 @@ def main():
         cfgs.append(dict(base, pdl=pdl, fused_threads=512, fused_ctas_per_sm=2, fused_rif=2))
         cfgs.append(dict(base, pdl=pdl, fused_threads=256, fused_ctas_per_sm=2, fused_rif=2))
         cfgs.append(dict(base, pdl=pdl, fused_threads=256, fused_ctas_per_sm=2, fused_rif=4, gemv_unroll=2))
-        cfgs.append(dict(base, pdl=pdl, gemv_stream=1))
     cfgs.append(dict(base, gemv_fused=0))
     if quick:
         cfgs = cfgs[:3]

@@ -111,7 +111,6 @@ def main():
         mod.set_tuning("set_barrier_slack", slack[0] if slack else (1 << 20))
         parts_ = [v for v in parts_ if v != "ns" and not (v[0] == "s" and v[1:].isdigit())]
         mod.set_tuning("set_fly", fly[0] if fly else 0)
-        mod.set_tuning("set_unsafe_no_barriers", 1 if parts_[2:] == ["nb"] else 0)
         mod.set_tuning("set_link", 0 if parts_[2:] in (["bar"], ["nb"]) else 1)
         mod.set_tuning("set_warps", warps)
         mod.set_tuning("set_slots", slots)

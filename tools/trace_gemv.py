@@ -68,12 +68,10 @@ def main():
         hs.append(h)
     x = torch.randn(1, K, device="cuda")
     y = torch.zeros(1, M, device="cuda")
-    cfgs = [("stream x1 pdl", dict(gemv_stream=1, stream_ctas_per_sm=1, pdl=1)),
-            ("stream x2 pdl", dict(gemv_stream=1, stream_ctas_per_sm=2, pdl=1)),
-            ("fused 512x1 rif2 pdl", dict(gemv_stream=0, fused_threads=512, fused_ctas_per_sm=1, fused_rif=2, pdl=1)),
-            ("fused 1024x1 pdl", dict(gemv_stream=0, fused_threads=1024, fused_ctas_per_sm=1, fused_rif=1, pdl=1)),
-            ("fused 1024x1 pdl overlap_same_src", dict(gemv_stream=0, fused_threads=1024, fused_ctas_per_sm=1, fused_rif=1, pdl=1, overlap_same_src=1))]
-    cfgs.append(("fused 512x1 rif2 pdl overlap_same_src", dict(gemv_stream=0, fused_threads=512, fused_ctas_per_sm=1, fused_rif=2, pdl=1, overlap_same_src=1)))
+    cfgs = [("fused 512x1 rif2 pdl", dict(fused_threads=512, fused_ctas_per_sm=1, fused_rif=2, pdl=1)),
+            ("fused 1024x1 pdl", dict(fused_threads=1024, fused_ctas_per_sm=1, fused_rif=1, pdl=1)),
+            ("fused 1024x1 pdl overlap_same_src", dict(fused_threads=1024, fused_ctas_per_sm=1, fused_rif=1, pdl=1, overlap_same_src=1))]
+    cfgs.append(("fused 512x1 rif2 pdl overlap_same_src", dict(fused_threads=512, fused_ctas_per_sm=1, fused_rif=2, pdl=1, overlap_same_src=1)))
     if "--overlap-only" in sys.argv:
         cfgs = cfgs[-1:]
     for label, t in cfgs:
