@@ -131,6 +131,17 @@ int          ggml_b200_mul_mat_q4_0(const ggml_b200_weight * w, const float * x_
                                     size_t nb11, float * y_dev, size_t nb1);
 int          ggml_b200_mul_mat_q4_0_host(const ggml_b200_weight * w, const float * x_host, int64_t n,
                                          size_t nb11, float * y_host, size_t nb1);
+/* The _dev op WITHOUT ANY ALLOCATION.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, dispatch and result bits as ggml_b200_mul_mat_q4_0; the quantized activations (kernel 1's output)
+ * go to a file-scope `static __device__` array instead of the growing workspace, and no cudaMalloc / cudaFree /
+ * allocating library routine is called.  Limit: n * K <= ggml_b200_static_max_elems() = 4 Mi activations per call
+ * (e.g. n = 512 at K = 8192, n = 1024 at K = 4096; the array is 6 MiB and every GPU that loads the library holds it
+ * until exit); larger calls return GGML_B200_ERR_ARG.  All calls share the array and it keeps the last call's
+ * contents; calls that overlap on the GPU (different streams) race on it -- serialise them. */
+int          ggml_b200_mul_mat_q4_0_static(const ggml_b200_weight * w, const float * x_dev, int64_t n,
+                                           size_t nb11, float * y_dev, size_t nb1);
+size_t       ggml_b200_static_max_elems(void);
 
 /* ---- a list of n = 1 ops in ONE launch ----------------------------------------
  * replaces, for the run of GGML_OP_MUL_MAT nodes of a decode step, the per-node loop of

@@ -635,6 +635,21 @@ int ggml_b200_mul_mat_q4_0(const ggml_b200_weight * w, const float * x_dev, int6
     return mul_mat_dev(w, x_dev, n, nb11, y_dev, nb1);
 }
 
+// ---- the op without any allocation (no counterpart in the reference) ----------------------
+// ggml_b200_mul_mat_q4_0 keeps the quantized activations (kernel 1's output: xq, xds, xdT) in a workspace that grows
+// with cudaMalloc.  Callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid it)
+// get the same op with that scratch in a file-scope device array of fixed size.  Every GPU that loads the library
+// holds the array until exit.  All calls share it and it keeps the last call's contents (nothing in it must start at
+// zero: kernel 1 writes every byte kernels 2/3 read, padded scale columns only feed columns that are never stored);
+// calls that overlap on the GPU (two streams) race on it.
+constexpr size_t STATIC_MAX_ELEMS = (size_t)4 << 20;                  // n * K of one call
+constexpr size_t STATIC_XQ_BYTES = STATIC_MAX_ELEMS;                  // int8 [n][K]
+constexpr size_t STATIC_XDS_BYTES = STATIC_MAX_ELEMS / 4;             // int2 [n][K/32]
+constexpr size_t STATIC_XDT_BYTES = (size_t)1 << 20;                  // float [K/32][n_pad], n_pad <= n + 3
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_XQ_BYTES + STATIC_XDS_BYTES + STATIC_XDT_BYTES];
+static unsigned char * g_static_ptr = nullptr;        // DEVICE address of the array on g.device (the symbol's name is only a host-side stand-in)
+static unsigned g_static_epoch = 0;
+
 // ---- n = 1 host entry point: one launch, no driver copies, no stream sync (gemv_q4_0_hostio.cuh) -----------
 static int hostio_grow_mapped(float ** p, size_t * cap, size_t need) {
     if (need <= *cap) return GGML_B200_OK;
@@ -754,6 +769,40 @@ int ggml_b200_mul_mat_q4_0_host(const ggml_b200_weight * w, const float * x_host
     CK(cudaMemcpy2DAsync(y_host + w->row_lo, nb1, g.ystage, (size_t)rows * 4, (size_t)rows * 4, (size_t)n, cudaMemcpyDeviceToHost, g.stream));
     CK(cudaStreamSynchronize(g.stream));
     return GGML_B200_OK;
+}
+
+size_t ggml_b200_static_max_elems(void) { return STATIC_MAX_ELEMS; }
+
+int ggml_b200_mul_mat_q4_0_static(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y_dev, size_t nb1) {
+    B200_API_LOCK;
+    int rc = check_op_args(w, x_dev, n, nb11, y_dev, nb1);
+    if (rc) return rc;
+    if (n == 0 || w->rows() == 0) return GGML_B200_OK;
+    const uint64_t elems = (uint64_t)n * (uint64_t)w->K;
+    const uint64_t n_pad = ((uint64_t)n + 3) & ~3ull;
+    if (elems > STATIC_MAX_ELEMS || (uint64_t)(w->K / QK) * n_pad * 4 > STATIC_XDT_BYTES) {
+        set_error("ggml_b200_mul_mat_q4_0_static: n * K = %llu activations exceed the static scratch (max %llu); use ggml_b200_mul_mat_q4_0",
+                  (unsigned long long)elems, (unsigned long long)STATIC_MAX_ELEMS);
+        return GGML_B200_ERR_ARG;
+    }
+    if (g_static_epoch != g_init_epoch) {             // set-up, once per device (per init), with that device current
+        CK(cudaSetDevice(g.device));
+        void * p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_static_scratch));
+        g_static_ptr = (unsigned char *)p;
+        g_static_epoch = g_init_epoch;
+    }
+    // run the unchanged dispatch with the workspace pointing at the static array: sized above, so nothing grows
+    struct Saved { int8_t * xq; size_t xq_cap; int2 * xds; size_t xds_cap; float * xdT; size_t xdT_cap; long long n_pad; } sv =
+        {g.xq, g.xq_cap, g.xds, g.xds_cap, g.xdT, g.xdT_cap, g.xdT_n_pad};
+    g.xq = (int8_t *)g_static_ptr;                                          g.xq_cap = STATIC_XQ_BYTES;
+    g.xds = (int2 *)(g_static_ptr + STATIC_XQ_BYTES);                       g.xds_cap = STATIC_XDS_BYTES;
+    g.xdT = (float *)(g_static_ptr + STATIC_XQ_BYTES + STATIC_XDS_BYTES);   g.xdT_cap = STATIC_XDT_BYTES;
+    g.runN.count = 0;      // "same src1 as the previous op": its quantized activations live in the other workspace
+    rc = mul_mat_dev(w, x_dev, n, nb11, y_dev, nb1);
+    g.runN.count = 0;
+    g.xq = sv.xq; g.xq_cap = sv.xq_cap; g.xds = sv.xds; g.xds_cap = sv.xds_cap; g.xdT = sv.xdT; g.xdT_cap = sv.xdT_cap; g.xdT_n_pad = sv.n_pad;
+    return rc;
 }
 
 int ggml_b200_block_dots_q4_0(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, int32_t * S_dev, int path) {

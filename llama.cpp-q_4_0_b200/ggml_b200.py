@@ -74,6 +74,8 @@ def _load() -> C.CDLL:
         "ggml_b200_get_rows_q4_0": (C.c_int, [_vp, _vp, _i64, _vp, _sz]),
         "ggml_b200_mul_mat_q4_0": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
         "ggml_b200_mul_mat_q4_0_host": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
+        "ggml_b200_mul_mat_q4_0_static": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
+        "ggml_b200_static_max_elems": (_sz, []),
         "ggml_b200_block_dots_q4_0": (C.c_int, [_vp, _vp, _i64, _sz, _vp, C.c_int]),
         "ggml_b200_fused_checkpoint_q4_0": (C.c_int, [_vp, _vp, _vp, _vp]),
         "ggml_b200_comm_unique_id": (C.c_int, [_vp]),
