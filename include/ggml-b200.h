@@ -166,6 +166,15 @@ typedef struct ggml_b200_set_op {
     float *                  y_dev;   /* the FULL dst row (M floats); a shard writes [row_lo,row_hi) */
 } ggml_b200_set_op;
 ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops);
+/* The same list on row shards, one rank per GPU (replaces, for a decode step, GGML_BACKEND_GPU_SPLIT's per-op
+ * row slices + per-column cudaMemcpyAsync gather, ggml-cuda.cu:2353-2552): COLLECTIVE over the communicator of
+ * ggml_b200_comm_init -- every rank passes the same list with its own shards (ggml_b200_shard_rows) and its own
+ * replicated x / full-size dst buffers.  One persistent launch per rank and step; the exchange is INSIDE it: a
+ * finished row goes to this rank's dst and, as a tagged 8-byte word, into every rank's arena over NVLink; runs whose
+ * x is another op's dst read the gathered vector from the arena; a gather warp per CTA completes every dst on every
+ * rank (the contract of ggml_b200_mul_mat_q4_0_sharded).  No NCCL call and no launch per mul_mat.  With a world of 1
+ * it is ggml_b200_set_create.  Every rank must call run the same number of times. */
+ggml_b200_set * ggml_b200_set_create_sharded(const ggml_b200_set_op * ops, int n_ops);
 int          ggml_b200_set_run(ggml_b200_set * s);
 void         ggml_b200_set_free(ggml_b200_set * s);
 int          ggml_b200_set_ops(const ggml_b200_set * s);       /* ops with a non-empty shard */

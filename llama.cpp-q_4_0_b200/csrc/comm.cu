@@ -153,6 +153,41 @@ static int p2p_setup() {
     return GGML_B200_OK;
 }
 
+bool comm_p2p_ready() { return nc.comm != nullptr && nc.p2p_ok; }
+
+int comm_share(void * local, void ** mapped) {
+    for (int r = 0; r < P2P_MAX_WORLD; r++) mapped[r] = nullptr;
+    mapped[nc.rank] = local;
+    if (nc.world == 1) return GGML_B200_OK;
+    if (!comm_p2p_ready()) { set_error("peer access is not set up"); return GGML_B200_ERR_STATE; }
+    cudaIpcMemHandle_t mine;
+    CK(cudaIpcGetMemHandle(&mine, local));
+    constexpr size_t REC = sizeof(cudaIpcMemHandle_t);
+    static_assert(REC % 4 == 0, "handles travel as floats");
+    unsigned char * dev = nullptr;
+    CK(cudaMalloc(&dev, REC * (nc.world + 1)));
+    CK(cudaMemcpyAsync(dev + REC * nc.world, &mine, REC, cudaMemcpyHostToDevice, g.stream));
+    NK(nc.AllGather(dev + REC * nc.world, dev, REC / 4, ncclFloat32, nc.comm, g.stream));
+    cudaIpcMemHandle_t all[P2P_MAX_WORLD];
+    CK(cudaMemcpyAsync(all, dev, REC * nc.world, cudaMemcpyDeviceToHost, g.stream));
+    CK(cudaStreamSynchronize(g.stream));
+    CK(cudaFree(dev));
+    for (int r = 0; r < nc.world; r++) {
+        if (r == nc.rank) continue;
+        void * p = nullptr;
+        CK(cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess));
+        mapped[r] = p;
+    }
+    return GGML_B200_OK;
+}
+
+void comm_unshare(void ** mapped) {
+    for (int r = 0; r < P2P_MAX_WORLD; r++) {
+        if (mapped[r] && r != nc.rank) cudaIpcCloseMemHandle(mapped[r]);
+        mapped[r] = nullptr;
+    }
+}
+
 static void p2p_teardown() {
     for (int r = 0; r < P2P_MAX_WORLD; r++) {
         if (nc.peers.arena[r] && r != nc.rank) cudaIpcCloseMemHandle(nc.peers.arena[r]);

@@ -35,6 +35,7 @@
 #pragma once
 #include "common.cuh"
 #include "gemv_q4_0.cuh"
+#include "p2p.cuh"
 #include "ptx.cuh"
 #include "quantize_q8_0.cuh"
 
@@ -43,6 +44,8 @@ namespace b200 {
 constexpr int SET_WPG = 4;            // consumer warps per group
 constexpr int SET_XWARPS = 2;         // warps that quantize the NEXT run's x while the consumers work on this one
 constexpr int SET_EXTRA_THREADS = 32 /* producer */ + 32 /* sentinel */ + 32 * SET_XWARPS;
+// multi-GPU lists: the second x warp becomes the gather warp (copies the peers' rows into dst), so the CTA keeps its
+// 512 threads / 128 registers (one more warp would round the register budget down to 96 and spill the tile loop)
 constexpr int SET_MAX_SLOTS = 16;
 constexpr int SET_MAX_GROUPS = 6;
 constexpr int SET_RED_BYTES = 2 * SET_MAX_GROUPS * 16 * 4;   // cross-warp partials: [parity][group][row 4][warp 4] floats
@@ -50,7 +53,9 @@ constexpr int SET_BAR_BYTES = 2 * SET_MAX_SLOTS * 8;
 constexpr int SET_MAX_NBK_WPR1 = 128; // blocks per row a single warp keeps x for (4 per lane)
 constexpr int SET_MAX_NBK = 768;      // 6 per lane of a 4-warp team (K <= 24576)
 
-enum { SET_OP_BARRIER = 1, SET_OP_QUANT = 2, SET_OP_XEXT = 4 };
+enum { SET_OP_BARRIER = 1, SET_OP_QUANT = 2, SET_OP_XEXT = 4, SET_OP_ARRIVE_GATHER = 1 << 15 };
+// ARRIVE_GATHER (multi-GPU lists): a barrier that arrives behind this op also waits until the peers' rows of every op
+// up to it are in dst (a later run reads such a dst with plain loads)
 // flags bits 8..14: how many dependency barriers every consumer warp arrives at when it has finished this op
 constexpr int SET_OP_ARRIVE_SHIFT = 8, SET_OP_ARRIVE_MASK = 0x7F;
 // XEXT: no op of the list writes x (it may be cached / fetched early)
@@ -68,6 +73,25 @@ struct SetOp {                        // 80 bytes, device resident, read-only du
     int ntiles;
     int first_mod;                    // (tiles of all earlier ops) % grid: CTA c takes tiles (c - first_mod) mod grid, + grid, ...
     int flags;                        // SET_OP_BARRIER | SET_OP_QUANT
+    // multi-GPU lists (row shards, SetGather below): the whole tensor has gM rows, this shard starts at grow0; ytag then
+    // points at this shard's first row inside this rank's ARENA (parity 0) and every peer has the same layout
+    int gM, grow0;
+};
+
+// Multi-GPU lists: one rank per GPU runs the same list on its row shards (ggml_b200_set_create_sharded).  Every rank
+// owns an arena [2 launch parities][sum of the ops' M] of tagged 8-byte words (launch number << 32 | bits of y),
+// exported over CUDA IPC and mapped by every peer.  A consumer warp that finishes a row stores it into its own dst AND
+// as a tagged word into EVERY rank's arena (NVLink stores, one lane per rank); 8-byte words are single-copy atomic, so a
+// word whose number matches IS the datum: no fence, no flag, no collective call.  A run whose x is another op's dst
+// reads the whole gathered vector out of the local arena (the linked-run mechanism of the single-GPU list), and one
+// gather warp per CTA copies the peers' rows into dst as they land, so that every op ends with the full dst on every
+// rank -- the contract of ggml_b200_mul_mat_q4_0_sharded, with NO launch and NO exchange step per mul_mat.
+// The arena is double-buffered by launch parity: a peer can be at most one launch ahead (it cannot finish launch e + 1
+// without this rank's rows of launch e + 1, which are produced after this rank's launch e has completed).
+struct SetGather {
+    unsigned long long * arena[P2P_MAX_WORLD];   // every rank's arena as mapped here; arena[me] = this rank's
+    long long stride;                            // words per parity
+    int me, world;
 };
 
 struct SetSync {                      // device resident, zero between launches
@@ -282,7 +306,7 @@ __device__ __forceinline__ SetOpC set_load_op(const SetOp * __restrict__ ops, co
     if (tbl != nullptr) {
         const SetOpS t = tbl[o];
         r.x = t.x; r.y = t.y; r.ytag = t.ytag; r.xtag = t.xtag; r.rows = t.rows; r.nbk = t.nbk; r.ntiles = t.ntiles;
-        r.first_mod = t.fm_flags & 0xFFFF; r.flags = t.fm_flags >> 16;
+        r.first_mod = t.fm_flags & 0xFFFF; r.flags = (int)((unsigned)t.fm_flags >> 16);
         r.S = DUMP ? ops[o].S : nullptr;
         return r;
     }
@@ -304,6 +328,8 @@ struct SetCtx {
     unsigned long long tag;           // launch number << 32
     uint32_t xempty;                  // mbarrier: every consumer warp has the run's x in registers (the planes are free)
     uint32_t arr_slot;                // this warp's shared-memory word: arrival points it has passed
+    const SetGather * gth;            // multi-GPU lists: the ranks' arenas (else nullptr)
+    long long gpar;                   // word offset of this launch's parity inside an arena
 };
 
 // ring position of the CTA's next tile: slot index and the parity of its current use
@@ -315,7 +341,7 @@ struct SetRing {
 // One run of ops that share x, for one consumer warp.  WPR warps cooperate on a row; a lane keeps the quantized x of
 // its NCL blocks in registers.  Returns the index of the op that starts the next run.
 // `op` = descriptor of op o on entry, of the returned op on exit (when there is one).
-template <int NG, int WPR, int NCL, bool DUMP, bool PROF>
+template <int NG, int WPR, int NCL, bool DUMP, bool PROF, bool GATHER>
 __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<1> & xs, int o, SetOpC & op, int & j, SetRing & rp,
                                                unsigned & ntile_team, unsigned & narrived, long long & t_full, long long & t_comp, long long & n_tiles, long long * tx) {
     constexpr int RPT = WPR == 1 ? 2 : 4;               // rows of a tile per team
@@ -404,7 +430,18 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
 #pragma unroll
             for (int r = 0; r < RPT; r++) acc[r] = warp_sum(acc[r]);
             if (WPR == 1) {
-                if (c.lane == 0) {
+                if (GATHER) {
+                    // every lane holds the sums (xor-shuffle tree): lane p < world sends the rows to rank p's arena
+                    if (c.lane < c.gth->world) {
+                        unsigned long long * dst = c.gth->arena[c.lane] + (op.ytag - c.gth->arena[c.gth->me]) + c.gpar + row0;
+#pragma unroll
+                        for (int r = 0; r < RPT; r++) if (r < nvalid) st_sys_b64(dst + r, c.tag | __float_as_uint(acc[r]));
+                    }
+                    if (c.lane == 0) {
+#pragma unroll
+                        for (int r = 0; r < RPT; r++) if (r < nvalid) op.y[row0 + r] = acc[r];
+                    }
+                } else if (c.lane == 0) {
 #pragma unroll
                     for (int r = 0; r < RPT; r++) if (r < nvalid) {
                         op.y[row0 + r] = acc[r];
@@ -419,7 +456,16 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
                     for (int r = 0; r < RPT; r++) red[r * 4 + c.wig] = acc[r];
                 }
                 asm volatile("bar.sync %0, 128;" ::"r"(2 + c.group) : "memory");
-                if (c.wig == 0 && c.lane < nvalid) {
+                if (GATHER) {
+                    // lane l of the group's first warp: row l % 4 to rank l / 4
+                    if (c.wig == 0 && (c.lane & 3) < nvalid && (c.lane >> 2) < c.gth->world) {
+                        const int r = c.lane & 3, pr = c.lane >> 2;
+                        const float4 p = *reinterpret_cast<const float4 *>(red + r * 4);
+                        const float v = ((p.x + p.y) + p.z) + p.w;
+                        st_sys_b64(c.gth->arena[pr] + (op.ytag - c.gth->arena[c.gth->me]) + c.gpar + row0 + r, c.tag | __float_as_uint(v));
+                        if (pr == 0) op.y[row0 + r] = v;
+                    }
+                } else if (c.wig == 0 && c.lane < nvalid) {
                     const float4 p = *reinterpret_cast<const float4 *>(red + c.lane * 4);
                     const float v = ((p.x + p.y) + p.z) + p.w;
                     op.y[row0 + c.lane] = v;
@@ -446,10 +492,11 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
 // PROF (profiling aid, ggml_b200_set_profile): clock64 totals per CTA -> prof[cta*8 + ..] =
 // {whole kernel, consumer warp 0 waiting for full slots, in dependency barriers, quantizing x, producer waiting for empty slots}
 // BIG: also the 6-blocks-per-lane plan (K > 16384); the kernel without it needs fewer registers
-template <int W, bool DUMP, bool PROF, bool BIG>
+template <int W, bool DUMP, bool PROF, bool BIG, bool GATHER>
 __global__ void __launch_bounds__(W * 32 + SET_EXTRA_THREADS, 1)
 gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restrict__ sync, int nslots, int slot_bytes,
-                     int x_bytes, int x_bufs, int tbl_bytes, int max_fly, unsigned seq, long long * __restrict__ prof) {
+                     int x_bytes, int x_bufs, int tbl_bytes, int max_fly, unsigned seq, long long * __restrict__ prof,
+                     const __grid_constant__ SetGather gth) {
     constexpr int NCONS = W * 32;
     constexpr int NG = W / SET_WPG;
     static_assert(NG <= SET_MAX_GROUPS, "named barriers 2 .. 2+NG-1 and the partials buffer are sized for 6 groups");
@@ -473,12 +520,14 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
     __shared__ unsigned s_launch;
     __shared__ unsigned s_bar_passed;                         // dependency barriers the sentinel has seen complete
     __shared__ unsigned s_arrived[W];                         // per consumer warp: arrival points passed
+    __shared__ unsigned s_gathered;                           // multi-GPU lists: ops whose peer rows this CTA's gather warp has copied into dst
     __shared__ __align__(8) uint64_t s_xbar[4];      // per x buffer: full [0..1], empty [2..3]
     const uint32_t xfull0 = smem_u32(&s_xbar[0]), xempty0 = smem_u32(&s_xbar[2]);
     const uint32_t bar_passed = smem_u32(&s_bar_passed), arrived0 = smem_u32(&s_arrived[0]);
     if (tid < W) s_arrived[tid] = 0u;
     if (tid == 0) {
         s_bar_passed = 0u;
+        s_gathered = 0u;
         for (int b = 0; b < 2; b++) {
             mbar_init(xfull0 + 8 * b, 1);       // the x warps filled the planes with a run's quantized x (or handed them over: tagged x)
             mbar_init(xempty0 + 8 * b, W);      // every consumer warp copied the run's x to registers
@@ -563,13 +612,15 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
             int oa = 0, ow = 0;                 // list positions of the next arrival point / the next barrier head
             unsigned ev = 0, kb = 0, k = 0;
             unsigned long long t0 = 0;
-            auto flags_of = [&](int o) { return tbl != nullptr ? (tbl[o].fm_flags >> 16) : ops[o].flags; };
+            auto flags_of = [&](int o) { return tbl != nullptr ? (int)((unsigned)tbl[o].fm_flags >> 16) : ops[o].flags; };
             while (oa < nops && !((flags_of(oa) >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK)) oa++;
             while (ow < nops && !(flags_of(ow) & SET_OP_BARRIER)) ow++;
             while (oa < nops || ow < nops) {
                 bool progress = false;
                 bool all_arrived = oa < nops;
                 for (int w = 0; all_arrived && w < W; w++) all_arrived = (int)(ld_acquire_cta_shared_u32(arrived0 + 4 * w) - (ev + 1)) >= 0;
+                if (GATHER && all_arrived && (flags_of(oa) & SET_OP_ARRIVE_GATHER))
+                    all_arrived = (int)(ld_acquire_cta_shared_u32(smem_u32(&s_gathered)) - (unsigned)(oa + 1)) >= 0;
                 if (all_arrived) {
                     const int narr = (flags_of(oa) >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK;
                     for (int i = 0; i < narr; i++) red_release_gpu_add_u32(bar_cnt + kb++, 1u);      // barriers are numbered in the order of their arrival points
@@ -595,14 +646,15 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
         }
         return;
     }
-    if (warp > W + 1) {
+    constexpr int XW = GATHER ? SET_XWARPS - 1 : SET_XWARPS;
+    if (warp > W + 1 && warp < W + 2 + XW) {
         // ===== x warps: kernel 1 (quantize_row_q8_0) of every run, one run AHEAD of the consumers =====
         // The consumers keep a run's x in registers, so the planes are free as soon as every warp has copied them: the
         // next run's x is quantized into them during this run's tiles, and a change of x costs a consumer warp one
         // shared-memory wait and the register load -- no CTA-wide rendezvous, no L2 round trip, no quantization.  Runs
         // whose x is another op's result (tagged words) are left to the consumers: all of them poll and quantize, which
         // is the shorter critical path; the x warps only hand the planes over.
-        constexpr int NX = SET_XWARPS * 32;
+        constexpr int NX = XW * 32;
         const int xt = tid - (W + 2) * 32;
         unsigned r = 0, kx = 0;
         for (int o = 0; o < nops; o++) {
@@ -624,6 +676,58 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
         return;
     }
 
+    if (GATHER && warp == W + 2 + XW) {
+        // ===== gather warp (multi-GPU lists): the peers' rows of every op, out of this rank's arena into dst =====
+        // In list order; this CTA takes a fixed slice of every op's rows, so the same thread handles the same address
+        // of a dst buffer that several ops reuse (program order = list order).  Dst buffers that an EARLIER op still
+        // reads as x or writes are protected by the list's barriers: the warp waits for every barrier up to the op.
+        const unsigned launch = s_launch;
+        const unsigned long long * mine = gth.arena[gth.me] + (long long)(launch & 1u) * gth.stride;
+        unsigned kg = 0;
+        unsigned long long t0 = 0;
+        for (int o = 0; o < nops; o++) {
+            const SetOp * p = ops + o;
+            const int flags = p->flags;
+            if (flags & SET_OP_BARRIER) {
+                kg++;
+                while ((int)(ld_acquire_cta_shared_u32(bar_passed) - kg) < 0) __nanosleep(64);
+            }
+            const int M = p->gM, lo_me = p->grow0, hi_me = p->grow0 + p->rows;
+            const unsigned long long * src = mine + (p->ytag - gth.arena[gth.me]) - lo_me;      // row 0 of the whole tensor
+            float * yfull = p->y - lo_me;
+            const int per_cta = (M + G - 1) / G;
+            const int m0 = min((int)blockIdx.x * per_cta, M), m1 = min(m0 + per_cta, M);
+            for (int base = m0; base < m1; base += 128) {
+                unsigned long long a[4];
+                bool need[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int m = base + 32 * u + lane;
+                    need[u] = m < m1 && (m < lo_me || m >= hi_me);
+                    a[u] = 0;
+                }
+                for (;;) {
+                    bool again = false;
+#pragma unroll
+                    for (int u = 0; u < 4; u++) if (need[u] && (unsigned)(a[u] >> 32) != launch) a[u] = ld_sys_b64(src + base + 32 * u + lane);
+#pragma unroll
+                    for (int u = 0; u < 4; u++) again |= need[u] && (unsigned)(a[u] >> 32) != launch;
+                    if (!again) break;
+                    __nanosleep(200);
+                    const unsigned long long t1 = gtime();
+                    if (t0 == 0) t0 = t1;
+                    if (t1 - t0 > P2P_TIMEOUT_NS) __trap();      // a peer never delivered: fail, do not hang
+                }
+                t0 = 0;
+#pragma unroll
+                for (int u = 0; u < 4; u++) if (need[u]) yfull[base + 32 * u + lane] = __uint_as_float((unsigned)a[u]);
+            }
+            __syncwarp();
+            if (lane == 0) st_release_cta_shared_u32(smem_u32(&s_gathered), (unsigned)(o + 1));
+        }
+        return;
+    }
+
     // ===== consumers =====
     SetCtx c;
     c.ops = ops; c.tbl = tbl; c.nops = nops; c.ring = ring; c.red = reinterpret_cast<float *>(smem + x_bytes + SET_BAR_BYTES);
@@ -631,6 +735,8 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
     c.G = G; c.group = warp / SET_WPG; c.wig = warp % SET_WPG; c.lane = lane;
     c.tag = (unsigned long long)s_launch << 32;
     c.arr_slot = arrived0 + 4 * warp;
+    c.gth = GATHER ? &gth : nullptr;
+    c.gpar = GATHER ? (long long)(s_launch & 1u) * gth.stride : 0;
     c.xempty = xempty0;
     SetRing rp = {0, 0};
     int j = 0;
@@ -662,21 +768,21 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
         GemvSmem<1> & xs = xb ? xs1 : xs0;
         c.xempty = xempty0 + 8 * xb;
         if (op.xtag != nullptr) {
-            set_quantize_x<NCONS>(xs, x, op.xtag, c.tag, nbk, tid, false);
+            set_quantize_x<NCONS>(xs, x, op.xtag + c.gpar, c.tag, nbk, tid, false);
             set_consumer_sync<NCONS>();
         }
         long long tr0 = 0;
         if (PROF) { tr0 = clock64(); t_quant += tr0 - tq0; }
         if (nbk <= SET_MAX_NBK_WPR1) {
-            if (nbk <= 32)       o = set_consume_run<NG, 1, 1, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
-            else if (nbk <= 64)  o = set_consume_run<NG, 1, 2, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
-            else if (nbk <= 96)  o = set_consume_run<NG, 1, 3, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
-            else                 o = set_consume_run<NG, 1, 4, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
+            if (nbk <= 32)       o = set_consume_run<NG, 1, 1, DUMP, PROF, GATHER>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
+            else if (nbk <= 64)  o = set_consume_run<NG, 1, 2, DUMP, PROF, GATHER>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
+            else if (nbk <= 96)  o = set_consume_run<NG, 1, 3, DUMP, PROF, GATHER>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
+            else                 o = set_consume_run<NG, 1, 4, DUMP, PROF, GATHER>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
         } else {
-            if (nbk <= 256)      o = set_consume_run<NG, 4, 2, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
-            else if (nbk <= 384) o = set_consume_run<NG, 4, 3, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
-            else if (nbk <= 512 || !BIG) o = set_consume_run<NG, 4, 4, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
-            else { if constexpr (BIG) o = set_consume_run<NG, 4, 6, DUMP, PROF>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx); }
+            if (nbk <= 256)      o = set_consume_run<NG, 4, 2, DUMP, PROF, GATHER>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
+            else if (nbk <= 384) o = set_consume_run<NG, 4, 3, DUMP, PROF, GATHER>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
+            else if (nbk <= 512 || !BIG) o = set_consume_run<NG, 4, 4, DUMP, PROF, GATHER>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx);
+            else { if constexpr (BIG) o = set_consume_run<NG, 4, 6, DUMP, PROF, GATHER>(c, xs, o, op, j, rp, ntile_team, narrived, t_full, t_comp, n_tiles, tx); }
         }
         if (PROF) t_run += clock64() - tr0;
     }

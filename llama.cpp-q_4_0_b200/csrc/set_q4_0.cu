@@ -29,15 +29,20 @@ struct ggml_b200_set {
     int warps = 16;
     int grid = 0;
     uint64_t bytes = 0;                     // algorithmic bytes of one run
+    // multi-GPU list (ggml_b200_set_create_sharded): this rank's arena and the peers' as mapped here
+    bool gathered = false;
+    unsigned long long * arena = nullptr;
+    void * mapped[b200::P2P_MAX_WORLD] = {nullptr};
+    b200::SetGather gth = {};
 };
 
 namespace b200 {
 
 static bool set_ranges_overlap(const float * a_lo, const float * a_hi, const float * b_lo, const float * b_hi) { return a_lo < b_hi && b_lo < a_hi; }
 
-template <int W, bool DUMP, bool PROF, bool BIG>
+template <int W, bool DUMP, bool PROF, bool BIG, bool GATHER = false>
 static int set_launch_tb(const ggml_b200_set * s, const SetOp * table, long long * prof) {
-    auto kern = gemv_q4_0_set_kernel<W, DUMP, PROF, BIG>;
+    auto kern = gemv_q4_0_set_kernel<W, DUMP, PROF, BIG, GATHER>;
     B200_SET_SMEM_ATTR(kern, MAX_DYN_SMEM - 1024);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)s->grid); cfg.blockDim = dim3(W * 32 + SET_EXTRA_THREADS); cfg.dynamicSmemBytes = s->smem; cfg.stream = g.stream;
@@ -47,13 +52,17 @@ static int set_launch_tb(const ggml_b200_set * s, const SetOp * table, long long
     attr[0].id = cudaLaunchAttributeCooperative;
     attr[0].val.cooperative = 1;
     cfg.attrs = attr; cfg.numAttrs = g.tune.set_coop ? 1 : 0;
-    CK(cudaLaunchKernelEx(&cfg, kern, table, (int)s->host_ops.size(), s->sync, s->nslots, s->slot_bytes, s->x_bytes, s->x_bufs, s->tbl_bytes, g.tune.set_fly > 0 ? g.tune.set_fly : 1 << 30, (unsigned)g.launches, prof));
+    CK(cudaLaunchKernelEx(&cfg, kern, table, (int)s->host_ops.size(), s->sync, s->nslots, s->slot_bytes, s->x_bytes, s->x_bufs, s->tbl_bytes, g.tune.set_fly > 0 ? g.tune.set_fly : 1 << 30, (unsigned)g.launches, prof, s->gth));
     g.launches++;
     return GGML_B200_OK;
 }
 
 template <int W, bool DUMP, bool PROF>
 static int set_launch_t(const ggml_b200_set * s, const SetOp * table, long long * prof) {
+    if constexpr (!DUMP && !PROF) {
+        if (s->gathered) return s->big ? set_launch_tb<W, false, false, true, true>(s, table, prof) : set_launch_tb<W, false, false, false, true>(s, table, prof);
+    }
+    if (s->gathered) { set_error("checkpoint / profile launches are single-GPU only"); return GGML_B200_ERR_ARG; }
     return s->big ? set_launch_tb<W, DUMP, PROF, true>(s, table, prof) : set_launch_tb<W, DUMP, PROF, false>(s, table, prof);
 }
 
@@ -92,6 +101,7 @@ static int set_plan_hazards(const std::vector<SetPlanOp> & ops, const Tune & tun
     const float * run_x = nullptr; long long run_K = 0; int run_link = -1;
     int arrive_mono = -1;
     // hazards of op j against the ops still live: does it need a barrier, behind which op, is its x one op's dst
+    bool raw_bar = false;                  // the barrier being planned orders a read of x behind its writers (not only WAR / WAW)
     auto hazards = [&](int j, bool & bar_, int & after_, int & link_) {
         const SetPlanOp & o = ops[j];
         for (const Range & r : live_x) if (set_ranges_overlap(o.y_lo, o.y_hi, r.lo, r.hi)) { bar_ = true; after_ = std::max(after_, r.op); }      // WAR
@@ -102,9 +112,9 @@ static int set_plan_hazards(const std::vector<SetPlanOp> & ops, const Tune & tun
             if (!set_ranges_overlap(o.x, o.x_hi, r.lo, r.hi)) continue;
             writers++;
             last_writer = std::max(last_writer, r.op);
-            if (r.lo == o.x && r.hi == o.x_hi && r.whole) link_ = r.op; else bar_ = true;                   // RAW
+            if (r.lo == o.x && r.hi == o.x_hi && r.whole) link_ = r.op; else { bar_ = true; raw_bar = true; }      // RAW
         }
-        if (writers > 1 || (link_ >= 0 && !tune.set_link)) bar_ = true;
+        if (writers > 1 || (link_ >= 0 && !tune.set_link)) { bar_ = true; raw_bar = true; }
         if (bar_) after_ = std::max(after_, last_writer);
     };
     for (int i = 0; i < n; i++) {
@@ -112,6 +122,7 @@ static int set_plan_hazards(const std::vector<SetPlanOp> & ops, const Tune & tun
         bool barrier = false;
         int after = -1;                       // last earlier op this one conflicts with
         int link = -1;
+        raw_bar = false;
         hazards(i, barrier, after, link);
         if (barrier) {
             // Split barrier: every warp ARRIVES when it has finished the last op this run conflicts with and WAITS here,
@@ -128,6 +139,7 @@ static int set_plan_hazards(const std::vector<SetPlanOp> & ops, const Tune & tun
             if (after > prev || !tune.set_split_barrier) after = prev;
             while (after >= 0 && after < prev && ((out.flags[after] >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK) >= SET_OP_ARRIVE_MASK) after++;
             arrive_mono = after;
+            if (link >= 0) raw_bar = true;        // x IS one op's dst, but the run reads it with plain loads behind this barrier
             auto dead = [&](const Range & r) { return r.op <= after; };
             live_x.erase(std::remove_if(live_x.begin(), live_x.end(), dead), live_x.end());
             live_y.erase(std::remove_if(live_y.begin(), live_y.end(), dead), live_y.end());
@@ -141,6 +153,7 @@ static int set_plan_hazards(const std::vector<SetPlanOp> & ops, const Tune & tun
                 out.barriers++;
                 if (((out.flags[after] >> SET_OP_ARRIVE_SHIFT) & SET_OP_ARRIVE_MASK) >= SET_OP_ARRIVE_MASK) return after;
                 out.flags[after] += 1 << SET_OP_ARRIVE_SHIFT;
+                if (raw_bar) out.flags[after] |= SET_OP_ARRIVE_GATHER;      // (multi-GPU lists: the peers' rows must be in dst too)
             }
             if (link >= 0) out.linked_runs++;
             run_x = o.x; run_K = o.K; run_link = link;
@@ -190,8 +203,7 @@ int ggml_b200_set_plan(const ggml_b200_set_plan_op * ops, int n_ops, int * flags
     return plan.barriers;
 }
 
-ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
-    B200_API_LOCK;
+static ggml_b200_set * set_create_impl(const ggml_b200_set_op * ops, int n_ops, bool gathered) {
     if (!g.inited) { set_error("ggml_b200_init was not called"); return nullptr; }
     if (!ops || n_ops <= 0) { set_error("empty op list"); return nullptr; }
     ggml_b200_set * s = new ggml_b200_set();
@@ -210,9 +222,10 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
         if (((uintptr_t)x & 15) || ((uintptr_t)y & 3)) { set_error("set op %d: x must be 16-byte aligned (ggml tensors are, GGML_MEM_ALIGN)", i); delete s; return nullptr; }
         if (set_ranges_overlap(y + w->row_lo, y + w->row_hi, x, x + w->K)) { set_error("set op %d: dst overlaps src1 (ggml never does that: dst is a fresh tensor, ggml.c:11226)", i); delete s; return nullptr; }
         s->bytes += (uint64_t)(18 * (w->rows() * (w->K / QK)) + 4 * w->K + 4 * w->rows());
-        if (w->rows() == 0) continue;
+        if (w->rows() == 0 && !gathered) continue;      // (a multi-GPU list keeps it: the peers' rows are still gathered into dst)
         SetOp o = {};
         o.wq = w->wq; o.wd = reinterpret_cast<const unsigned short *>(w->wd); o.x = x; o.y = y + w->row_lo; o.S = nullptr;
+        o.gM = (int)w->M; o.grow0 = (int)w->row_lo;
         o.rows = (int)w->rows(); o.nbk = (int)(w->K / QK);
         if (o.nbk > SET_MAX_NBK) { set_error("set op %d: K = %lld > %d is beyond the persistent kernel's register plan; use ggml_b200_mul_mat_q4_0", i, (long long)w->K, SET_MAX_NBK * QK); delete s; return nullptr; }
         o.tile_rows = o.nbk <= SET_MAX_NBK_WPR1 ? 8 : 4;
@@ -222,7 +235,8 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
         tiles += o.ntiles;
         const float * y_lo = o.y, * y_hi = o.y + o.rows;
         const float * x_hi = x + w->K;
-        plan_ops.push_back({x, x_hi, y_lo, y_hi, (long long)w->K, w->row_lo == 0 && w->row_hi == w->M});
+        if (gathered) plan_ops.push_back({x, x_hi, y, y + w->M, (long long)w->K, true});      // every rank ends up with the whole dst
+        else plan_ops.push_back({x, x_hi, y_lo, y_hi, (long long)w->K, w->row_lo == 0 && w->row_hi == w->M});
         if (o.nbk > nbk_max) nbk_max = o.nbk;
         const int stage = R * o.nbk * 16 + ((R * o.nbk * 2 + 15) & ~15);
         if (stage > s->slot_bytes) s->slot_bytes = stage;
@@ -271,7 +285,23 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
         delete s; return nullptr;
     }
     s->smem = (size_t)s->x_bytes + SET_BAR_BYTES + SET_RED_BYTES + s->tbl_bytes + (size_t)s->nslots * s->slot_bytes;
-    {
+    if (gathered) {
+        // arena: [2 parities][sum of M, each padded to 8 words]; every rank computes the same layout from the same list
+        s->gathered = true;
+        size_t words = 0;
+        std::vector<size_t> goff(s->host_ops.size());
+        for (size_t i = 0; i < s->host_ops.size(); i++) { goff[i] = words; words += ((size_t)s->host_ops[i].gM + 7) & ~(size_t)7; }
+        cudaError_t e2 = cudaMalloc(&s->arena, 2 * words * 8);
+        if (e2 == cudaSuccess) e2 = cudaMemset(s->arena, 0, 2 * words * 8);      // launch numbers start at 1
+        if (e2 != cudaSuccess) { cuda_fail(e2, "set_create arena", __FILE__, __LINE__); ggml_b200_set_free(s); return nullptr; }
+        if (comm_share(s->arena, s->mapped) != GGML_B200_OK) { ggml_b200_set_free(s); return nullptr; }
+        s->gth.stride = (long long)words; s->gth.me = ggml_b200_comm_rank(); s->gth.world = ggml_b200_comm_world();
+        for (int r = 0; r < P2P_MAX_WORLD; r++) s->gth.arena[r] = (unsigned long long *)s->mapped[r];
+        for (size_t i = 0; i < s->host_ops.size(); i++) {
+            s->host_ops[i].ytag = s->arena + goff[i] + s->host_ops[i].grow0;                 // this shard's first row (parity 0)
+            if (link_of[i] >= 0) s->host_ops[i].xtag = s->arena + goff[link_of[i]];           // the whole gathered vector
+        }
+    } else {
         size_t words = 0;
         std::vector<long long> off(s->host_ops.size(), -1);
         for (size_t i = 0; i < link_of.size(); i++) {
@@ -297,11 +327,28 @@ ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
 void ggml_b200_set_free(ggml_b200_set * s) {
     B200_API_LOCK;
     if (!s) return;
+    if (s->gathered) {
+        cudaDeviceSynchronize();       // this rank's last launch has seen every peer's rows; peers may only be as far
+        comm_unshare(s->mapped);
+        if (s->arena) cudaFree(s->arena);
+    }
     if (s->dev_ops) cudaFree(s->dev_ops);
     if (s->dev_ops_dump) cudaFree(s->dev_ops_dump);
     if (s->sync) cudaFree(s->sync);
     if (s->staging) cudaFree(s->staging);
     delete s;
+}
+
+ggml_b200_set * ggml_b200_set_create(const ggml_b200_set_op * ops, int n_ops) {
+    B200_API_LOCK;
+    return set_create_impl(ops, n_ops, false);
+}
+
+ggml_b200_set * ggml_b200_set_create_sharded(const ggml_b200_set_op * ops, int n_ops) {
+    B200_API_LOCK;
+    if (ggml_b200_comm_world() <= 1) return set_create_impl(ops, n_ops, false);
+    if (!comm_p2p_ready()) { set_error("set_create_sharded: the peers' memory is not mapped (ggml_b200_comm_init failed to set up peer access)"); return nullptr; }
+    return set_create_impl(ops, n_ops, true);
 }
 
 int ggml_b200_set_run(ggml_b200_set * s) {

@@ -116,6 +116,11 @@ int launch_gemv(const ggml_b200_weight * w, float * y, long long ldy, int n);
 int launch_shard(const ggml_b200_weight * w, float * y, long long ldy, int n);
 int launch_slab(const ggml_b200_weight * w, const float * x_dev, int64_t n, size_t nb11, float * y, long long ldy);
 void comm_set_p2p(int on);
+// collective over the communicator: export `local` (a cudaMalloc'd block) over CUDA IPC and map every peer's block;
+// mapped[me] = local.  comm_unshare closes the peers' mappings.
+bool comm_p2p_ready();
+int  comm_share(void * local, void ** mapped /* [P2P_MAX_WORLD] */);
+void comm_unshare(void ** mapped);
 // n = 1 row shard with the multi-GPU exchange fused in (gemv_q4_0_p2p.cuh); y_dev = the whole dst column
 bool fused_p2p_ok(const ggml_b200_weight * w);
 int launch_fused_p2p(const ggml_b200_weight * w, const float * x_dev, size_t nb11, float * y_dev, const P2PExchange & ex);

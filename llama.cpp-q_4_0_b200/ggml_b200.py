@@ -86,6 +86,7 @@ def _load() -> C.CDLL:
         "ggml_b200_shard_rows": (None, [_i64, C.c_int, C.c_int, C.POINTER(_i64), C.POINTER(_i64)]),
         "ggml_b200_mul_mat_q4_0_sharded": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
         "ggml_b200_set_create": (_vp, [_vp, C.c_int]),
+        "ggml_b200_set_create_sharded": (_vp, [_vp, C.c_int]),
         "ggml_b200_set_run": (C.c_int, [_vp]),
         "ggml_b200_set_free": (None, [_vp]),
         "ggml_b200_set_ops": (C.c_int, [_vp]),
@@ -370,14 +371,15 @@ class OpSet:
     """A list of n = 1 ops compiled for ONE persistent launch (ggml_b200_set_create).
     ops: iterable of (weight handle or Weight, x device pointer, y device pointer)."""
 
-    def __init__(self, ops):
+    def __init__(self, ops, sharded=False):
+        """sharded: collective over the ranks of comm_init (ggml_b200_set_create_sharded): row shards, full dst on every rank"""
         ops = list(ops)
         arr = (SetOp * max(1, len(ops)))()
         for i, (w, xp, yp) in enumerate(ops):
             arr[i].w = w.h if isinstance(w, Weight) else w
             arr[i].x_dev = xp
             arr[i].y_dev = yp
-        self.h = lib().ggml_b200_set_create(C.cast(arr, _vp), len(ops))
+        self.h = (lib().ggml_b200_set_create_sharded if sharded else lib().ggml_b200_set_create)(C.cast(arr, _vp), len(ops))
         if not self.h:
             raise B200Error(ERR_ARG, lib().ggml_b200_last_error().decode(errors="replace"))
 

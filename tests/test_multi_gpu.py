@@ -30,3 +30,17 @@ def test_sharded_equals_single_gpu(world):
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "CHECK_SHARDED OK" in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 8])
+def test_sharded_persistent_list_equals_single_gpu(world):
+    """ggml_b200_set_create_sharded: one persistent launch per rank with the exchange inside it (tools/check_sharded_set.py):
+    the LLaMA-65B shapes, bit-identical to the single-GPU launch on every rank, within 1e-4 of the oracle on rank 0."""
+    if _gpus() < world:
+        pytest.skip(f"needs {world} GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29700 + world), os.path.join(ROOT, "tools", "check_sharded_set.py")]
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "CHECK_SHARDED_SET OK" in r.stdout
