@@ -42,6 +42,18 @@ WORKLOADS = {
     # name: (n_layers, per-layer [(M, K, count)], [(M, K) once])
     "llama7b_decode_n1": (32, [(4096, 4096, 4), (11008, 4096, 2), (4096, 11008, 1)], [(32000, 4096)]),
     "llama65b_decode_n1_rowsharded": (80, [(8192, 8192, 4), (22016, 8192, 2), (8192, 22016, 1)], [(32000, 8192)]),
+    # BASELINE configs[3] (arch/falcon/falcon.cpp:997-1025): fused QKV 4672x4544, FFN up 18176x4544 (both read the layer
+    # norm's row), attention output 4544x4544, FFN down 4544x18176; lm_head 65024x4544
+    "falcon7b_decode_n1": (32, [(4672, 4544, 1), (18176, 4544, 1), (4544, 4544, 1), (4544, 18176, 1)], [(65024, 4544)]),
+    # BASELINE configs[0]: one 4096x4096 op, as tests/test-quantize-perf.cpp sizes it; 48 HBM copies (453 MB > 2x L2) cycled
+    "single_4096_n1": (48, [(4096, 4096, 1)], []),
+}
+# which activation buffer every matmul of a layer reads (ops that share one form a same-src1 run)
+SRC_GROUPS = {
+    "llama7b_decode_n1": ["attn_in", "attn_in", "attn_in", "attn_out", "ffn_in", "ffn_in", "ffn_mid"],
+    "llama65b_decode_n1_rowsharded": ["attn_in", "attn_in", "attn_in", "attn_out", "ffn_in", "ffn_in", "ffn_mid"],
+    "falcon7b_decode_n1": ["ln_out", "ln_out", "attn_out", "ffn_mid"],
+    "single_4096_n1": ["x"],
 }
 
 
@@ -185,7 +197,7 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------------- CPU arm
-def cpu_reference_arm(workload, steps, warmup, budget_s=20.0):
+def cpu_reference_arm(workload, steps, warmup, budget_s=20.0, sample_layers=None):
     """The reference's own CPU path (ggml_graph_compute -> ggml_compute_forward_mul_mat_q_f32 ->
     AVX2 quantize_row_q8_0 + ggml_vec_dot_q4_0_q8_0) from oracle/_ref, all host threads, on a
     bounded sample: 2 layers of the set + the output matmul, distinct weights per matmul
@@ -196,21 +208,43 @@ def cpu_reference_arm(workload, steps, warmup, budget_s=20.0):
     cores = os.cpu_count() or 1
     rng = np.random.default_rng(1234)
     L, per_layer, once = WORKLOADS[workload]
+    sweep = None
     if R is not None:
-        shapes = matmul_list(workload, layers=2)
+        # sample_layers None: as much of the workload as fits (a distinct host copy of the weights per matmul, 8 GB of RAM)
+        full = matmul_list(workload)
+        nl = sum(c for (_, _, c) in per_layer)
+        per_layer_bytes = sum(18 * M * K // 32 * c for (M, K, c) in per_layer)
+        # (and the reference allows 64 live ggml contexts, ggml.c GGML_MAX_CONTEXTS: one per matmul handle here)
+        lay = sample_layers if sample_layers else max(1, min(L, int(8e9 // per_layer_bytes), (56 - len(once)) // nl))
+        shapes = matmul_list(workload, layers=lay)
         kind = "reference"
         handles = []
+        base = {}
         for (M, K) in shapes:
-            h = R.Handle(R, random_q4_0(rng, M, K), 1)
+            if (M, K) not in base:
+                base[(M, K)] = random_q4_0(rng, M, K)
+            h = R.Handle(R, base[(M, K)], 1)          # (the handle copies the blocks into its own ggml context: distinct memory per matmul)
             h.set_x(rng.standard_normal((1, K), dtype=np.float32))
             handles.append(h)
         sample_bytes = sum(algo_bytes(M, K) for (M, K) in shapes)
+        # n_threads: the best of {8, 16, 32, all} on this box (more threads than memory channels can use got SLOWER in round 1)
+        sweep = {}
+        for th in thread_counts():
+            for h in handles:
+                h.compute(th)
+            t0 = time.perf_counter()
+            for h in handles:
+                h.compute(th)
+            sweep[str(th)] = sample_bytes / (time.perf_counter() - t0) / 1e9
+        cores = int(max(sweep, key=sweep.get))
 
         def one_step():
             for h in handles:
                 h.compute(cores)
-        sample = (f"2 of {L} layers + output matmul of {workload} ({len(shapes)} matmuls, {sample_bytes / 1e6:.0f} MB), "
-                  f"ggml_graph_compute n_threads={cores}, {'-march=native' if R.native else '-march=x86-64-v3'} build of the unmodified reference")
+        whole = len(shapes) == len(full)
+        sample = ((f"the whole workload ({len(shapes)} matmuls, {sample_bytes / 1e6:.0f} MB)" if whole else
+                   f"{lay} of {L} layers + output matmul of {workload} ({len(shapes)} matmuls, {sample_bytes / 1e6:.0f} MB)") +
+                  f", ggml_graph_compute n_threads={cores} (best of the sweep), {'-march=native' if R.native else '-march=x86-64-v3'} build of the unmodified reference")
     else:
         P = oracle.port()
         kind, cores = "port", 1
@@ -223,7 +257,7 @@ def cpu_reference_arm(workload, steps, warmup, budget_s=20.0):
             for W, X in zip(Ws, Xs):
                 P.mul_mat(W, X, avx2_order=True)
         sample = f"one matmul per distinct shape of {workload} ({sample_bytes / 1e6:.0f} MB), scalar C port, 1 thread"
-    for _ in range(max(1, min(warmup, 3))):
+    for _ in range(max(1, warmup)):
         one_step()
     t_start = time.perf_counter()
     done = 0
@@ -240,17 +274,17 @@ def cpu_reference_arm(workload, steps, warmup, budget_s=20.0):
         for h in handles:
             h.close()
     return {"value": sample_bytes / mean / 1e9, "unit": UNIT, "cores": cores, "kind": kind,
-            "sample": sample, "steps_timed": done, "ms_per_sample_step": mean * 1e3,
+            "sample": sample, "steps_timed": done, "ms_per_sample_step": mean * 1e3, "GBps_by_n_threads": sweep,
             "best_value": sample_bytes / float(np.min(times)) / 1e9}
 
 
 def run_reference_impl(args, workload, rank):
     if rank != 0:
         return
-    cb = cpu_reference_arm(workload, args.steps, args.warmup, budget_s=60.0)
+    cb = cpu_reference_arm(workload, args.steps, args.warmup, budget_s=90.0)
     line = {
         "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
-        "steps": cb["steps_timed"], "warmup": min(args.warmup, 3), "ms_per_step": cb["ms_per_sample_step"],
+        "steps": cb["steps_timed"], "warmup": args.warmup, "ms_per_step": cb["ms_per_sample_step"],
         "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None,
         "dtype": "int8 dot (q4_0 x q8_0), fp32 scale+accumulate", "data": "synthetic",
         "config": {"workload": workload, "n": 1, "note": "reference CPU path; each step is a bounded sample of the workload"},
@@ -280,17 +314,194 @@ class PinnedArray:
             self.ptr = None
 
 
+def decode_list_leg(mod, stream, rng, workload, steps, warmup, layers=None, check=True):
+    """One GPU, n = 1: the matmul list of `workload` (buffers as the model graph has them: SRC_GROUPS, one dst per layer
+    position reused by every layer) as ONE persistent launch per step (ggml_b200_set_run) and as one launch per mul_mat
+    (CUDA graph).  CUDA events on the launching stream; every layer has its own HBM copy of the weights.  One op of each
+    distinct shape is checked against the oracle first.  Returns a dict for the JSON line."""
+    import torch
+    L_ = mod.lib()
+    L, per_layer, once = WORKLOADS[workload]
+    if layers:
+        L = min(L, layers)
+    layer_shapes = [(M, K) for (M, K, c) in per_layer for _ in range(c)]
+    groups = SRC_GROUPS[workload]
+    host = {}
+    handles = []
+
+    def up(M, K):
+        if (M, K) not in host:
+            host[(M, K)] = random_q4_0(rng, M, K)
+        h = L_.ggml_b200_upload_q4_0(host[(M, K)].ctypes.data_as(C.c_void_p), M, K, (K // 32) * 18, 0, M)
+        if not h:
+            raise RuntimeError(L_.ggml_b200_last_error().decode())
+        return h
+    for _ in range(L):
+        for (M, K) in layer_shapes:
+            handles.append((up(M, K), M, K))
+    for (M, K) in once:
+        handles.append((up(M, K), M, K))
+    xg, yg, ops = {}, {}, []
+    for idx, (h, M, K) in enumerate(handles):
+        pos = idx % len(layer_shapes) if idx < L * len(layer_shapes) else len(layer_shapes) + idx - L * len(layer_shapes)
+        grp = groups[pos] if pos < len(groups) else "out_in"
+        if grp not in xg:
+            xg[grp] = torch.from_numpy(rng.standard_normal((1, K), dtype=np.float32)).cuda()
+        if pos not in yg:
+            yg[pos] = torch.zeros((1, M), dtype=torch.float32, device="cuda")
+        ops.append((h, M, K, xg[grp], yg[pos]))
+    total_bytes = sum(algo_bytes(M, K) for (_, M, K) in handles)
+    opset = mod.OpSet([(h, x.data_ptr(), y.data_ptr()) for (h, M, K, x, y) in ops])
+
+    def per_op():
+        for (h, M, K, x, y) in ops:
+            rc = L_.ggml_b200_mul_mat_q4_0(h, C.c_void_p(x.data_ptr()), 1, K * 4, C.c_void_p(y.data_ptr()), M * 4)
+            if rc:
+                raise RuntimeError(L_.ggml_b200_last_error().decode())
+    errs = {}
+    if check:
+        import oracle
+        R, P = oracle.ref(), oracle.port()
+        with torch.cuda.stream(stream):
+            opset.run()
+        stream.synchronize()
+        seen = set()
+        for (h, M, K, x, y) in reversed(ops):          # the last writer of every dst
+            if (M, K) in seen:
+                continue
+            seen.add((M, K))
+            W = host[(M, K)]
+            xn = x.cpu().numpy()
+            want = R.mul_mat(W, xn, n_threads=min(16, os.cpu_count() or 1)) if R is not None else P.mul_mat(W, xn, avx2_order=True)
+            e = float(np.max(np.abs(y.cpu().numpy() - want)) / max(float(np.max(np.abs(want))), 1e-30))
+            errs[f"{M}x{K}"] = e
+            if not e <= 1e-4:
+                raise RuntimeError(f"{workload}: {M}x{K} differs from the oracle: max|dY|/max|Y| = {e:.3e}")
+
+    def timed(fn):
+        with torch.cuda.stream(stream):
+            for _ in range(max(3, warmup)):
+                fn()
+        stream.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            for _ in range(steps):
+                fn()
+            e1.record(stream)
+        stream.synchronize()
+        return e0.elapsed_time(e1) / steps
+    ms_set = timed(opset.run)
+    mod.set_tuning("overlap_same_src", 1)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=stream):
+        mod.set_stream(torch.cuda.current_stream().cuda_stream)
+        per_op()
+    mod.set_stream(stream.cuda_stream)
+    ms_po = timed(g.replay)
+    del g
+    peak, peak_src = peaks()
+    out = {"workload": workload, "n": 1, "layers": L, "matmuls_per_step": len(handles), "algorithmic_bytes_per_step": total_bytes,
+           "GBps": total_bytes / (ms_set * 1e-3) / 1e9, "ms_per_step": ms_set, "frac_of_measured_hbm_peak": total_bytes / (ms_set * 1e-3) / 1e9 / peak,
+           "kernel": "gemv_q4_0_set_kernel (one persistent launch per step)",
+           "one_launch_per_mul_mat": {"GBps": total_bytes / (ms_po * 1e-3) / 1e9, "ms_per_step": ms_po, "us_per_mul_mat": ms_po * 1e3 / len(handles),
+                                      "frac_of_measured_hbm_peak": total_bytes / (ms_po * 1e-3) / 1e9 / peak},
+           "dependency_barriers": opset.barriers, "timing": "CUDA events, %d steps after %d warm-ups; weights %.2f GB (>> L2) streamed once per step" % (steps, max(3, warmup), total_bytes / 1e9),
+           "oracle_max_rel_err": errs}
+    opset.free()
+    for (h, _, _) in handles:
+        L_.ggml_b200_free_weight(h)
+    del xg, yg, ops
+    torch.cuda.empty_cache()
+    return out
+
+
+def single_4096_cpu(threads_list):
+    """BASELINE configs[0] on the host: the reference's single-thread vec_dot_q GB/s by the tests/test-quantize-perf.cpp
+    method (warm-ups, best of 10 passes) and ggml_graph_compute of one 4096x4096 n = 1 mul_mat over the thread counts."""
+    import oracle
+    R = oracle.ref()
+    if R is None:
+        return None
+    rng = np.random.default_rng(5)
+    M = K = 4096
+    Ws = [random_q4_0(rng, M, K) for _ in range(8)]                  # 75 MB: alternated to defeat the caches (benchmark-matmult.cpp:192-202)
+    x = rng.standard_normal((1, K), dtype=np.float32)
+    q8 = R.quantize_q8_0(x)[0]
+    out = {"shape": [M, K], "method": "tests/test-quantize-perf.cpp:85-108 (5 warm-ups, best of 10), weights as stored: 18 B per block"}
+    t = R.time_vec_dot(Ws[0][:16], q8, 5, 10)
+    out["vec_dot_q_1thread_cache_resident_GBps"] = 16 * (K // 32) * 18 / t / 1e9
+    t = min(R.time_vec_dot(W, q8, 0, 1) for W in Ws + Ws)
+    out["vec_dot_q_1thread_memory_GBps"] = M * (K // 32) * 18 / t / 1e9
+    hs = [R.Handle(R, W, 1) for W in Ws]
+    for h in hs:
+        h.set_x(x)
+    best = {}
+    for th in threads_list:
+        for h in hs:
+            h.compute(th)
+        ts = []
+        for _ in range(3):
+            for h in hs:
+                t0 = time.perf_counter()
+                h.compute(th)
+                ts.append(time.perf_counter() - t0)
+        best[str(th)] = algo_bytes(M, K) / float(np.mean(ts)) / 1e9
+    for h in hs:
+        h.close()
+    out["ggml_graph_compute_GBps_by_threads"] = best
+    return out
+
+
 PREFILL_SHAPES = [(4096, 4096, 4), (11008, 4096, 2), (4096, 11008, 1), (32000, 4096, 1)]   # LLaMA-7B layer + output, n = 512
 
 
-def prefill_leg(mod, stream, rng, steps, warmup, n=512):
+FALCON_PREFILL_SHAPES = [(4672, 4544, 1), (18176, 4544, 1), (4544, 4544, 1), (4544, 18176, 1)]
+FALCON_PREFILL_GROUPS = ["ln_out", "ln_out", "attn_out", "ffn_mid"]
+LLAMA_PREFILL_GROUPS = ["attn_in", "attn_in", "attn_in", "attn_out", "ffn_in", "ffn_in", "ffn_mid", "out_in"]
+_INT8_PEAK = {}
+
+
+def int8_peak():
+    """a cuBLASLt int8 GEMM (8192^3, int32 accumulate) on this box as the empirical dense-int8 ceiling
+    (torch._int_mm is that call).  Best of 10 after 3 warm-ups, CUDA events.  None when the call is unavailable."""
+    if "v" in _INT8_PEAK:
+        return _INT8_PEAK["v"]
+    v = None
+    try:
+        import torch
+        N = 8192
+        a = torch.randint(-127, 127, (N, N), dtype=torch.int8, device="cuda")
+        b = torch.randint(-127, 127, (N, N), dtype=torch.int8, device="cuda").t()      # column-major B, as cuBLASLt wants it
+        for _ in range(3):
+            torch._int_mm(a, b)
+        torch.cuda.synchronize()
+        best = 1e30
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            torch._int_mm(a, b)
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        v = 2.0 * N * N * N / (best * 1e-3) / 1e12
+        del a, b
+        torch.cuda.empty_cache()
+    except Exception as e:   # noqa: BLE001
+        print(f"[bench] cuBLASLt int8 peak not measured ({e})", file=sys.stderr)
+    _INT8_PEAK["v"] = v
+    return v
+
+
+def prefill_leg(mod, stream, rng, steps, warmup, n=512, shapes=None, groups=None, name="llama7b_prefill_n512", host_leg=True):
     """BASELINE configs[2]: LLaMA-7B Q4_0 prefill, n = 512 tokens, tensor-core GEMM path (kernel 1 + kernel 3).
     One pass = the 7 matmuls of a layer + the output matmul; int8 TOPS = 2*M*K*n / time, CUDA events on the
     launching stream.  Also the same pass through the host-buffer call (H2D of x, D2H of y inside the timing)."""
     import torch
     L_ = mod.lib()
     handles, ops = [], 0.0
-    for (M, K, c) in PREFILL_SHAPES:
+    shapes = shapes or PREFILL_SHAPES
+    for (M, K, c) in shapes:
         blk = random_q4_0(rng, M, K)
         for _ in range(c):
             h = L_.ggml_b200_upload_q4_0(blk.ctypes.data_as(C.c_void_p), M, K, (K // 32) * 18, 0, M)
@@ -304,7 +515,7 @@ def prefill_leg(mod, stream, rng, steps, warmup, n=512):
     ys = {M: torch.zeros(n, M, device="cuda") for M in Ms}
     # device-resident leg: buffers as the model graph has them (wq, wk, wv share the normed rows; w3, w1 too; every
     # matmul has its own dst), so same-src1 ops may reuse the quantized activations and overlap (overlap_same_src)
-    groups = ["attn_in", "attn_in", "attn_in", "attn_out", "ffn_in", "ffn_in", "ffn_mid", "out_in"]
+    groups = groups or LLAMA_PREFILL_GROUPS
     assert len(handles) == len(groups)
     xg, dev_ops = {}, []
     for (h, M, K), grp in zip(handles, groups):
@@ -340,6 +551,34 @@ def prefill_leg(mod, stream, rng, steps, warmup, n=512):
     stream.synchronize()
     mod.set_tuning("skip_quantize", 0)
     ms_gemm = e0.elapsed_time(e1) / steps
+    peak_m = int8_peak()
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            pk = json.load(f)
+        bf16, src = float(pk["bf16_tflops"]), "2 x MEASURED_PEAKS.json bf16_tflops (cuBLAS bf16 burst; dense int8 runs at twice the bf16 rate)"
+    except Exception:
+        bf16, src = 1590.0, "2 x fallback 1.59 PFLOP/s bf16 (B200_PROFILING.md)"
+    tops, tops_gemm = ops / (ms * 1e-3) / 1e12, ops / (ms_gemm * 1e-3) / 1e12
+    res = {
+        "metric": "q4_0_mul_mat_n512_int8_TOPS", "value": tops, "unit": "TOPS", "ms_per_pass": ms,
+        "config": {"workload": name, "n": n, "matmuls_per_pass": len(handles),
+                   "shapes": [[M, K, c] for (M, K, c) in shapes], "ops_per_pass": ops,
+                   "timed": "kernel 1 (quantize_row_q8_0) + kernel 3 (tcgen05 kind::i8 GEMM) per matmul, x/y resident in HBM"},
+        "gpu_launches_per_pass": int(launches),
+        "roofline": {"kernel": "gemm_q4_0_tc_kernel (TMA + nibble unpack + tcgen05.mma kind::i8 + TMEM + scale epilogue)",
+                     "bound": "tensor", "achieved": tops_gemm, "peak": 2 * bf16, "unit": "TOP/s", "frac": tops_gemm / (2 * bf16),
+                     "frac_of_nominal_4500": tops_gemm / 4500.0, "peak_source": src,
+                     "measured_cublaslt_int8_8192cubed_TOPS": peak_m, "frac_of_measured_cublaslt_int8": (tops_gemm / peak_m) if peak_m else None,
+                     "traffic": gemm_traffic(), "traffic_source": "profiles/traffic.json (committed ncu capture, not this run)",
+                     "ms_per_pass_kernel3": ms_gemm,
+                     "note": "the per-block fp16 x fp16 scale epilogue bounds this formulation at 25% of the tensor rate: every 128x128 int32 "
+                             "tile (one Q4_0 block) costs 256 clk of FP32 FMAs AND 256 clk of TMEM reads against 64 clk of MMA "
+                             "(profiles/r02_ubench_epi_rate.log); see DESIGN.md kernel 3"},
+    }
+    if not host_leg:
+        for (h, _, _) in handles:
+            L_.ggml_b200_free_weight(h)
+        return res
     # host buffers
     xh = {K: PinnedArray(mod, (n, K)) for K in Ks}
     yh = {M: PinnedArray(mod, (n, M)) for M in Ms}
@@ -363,30 +602,109 @@ def prefill_leg(mod, stream, rng, steps, warmup, n=512):
         p.free()
     for (h, _, _) in handles:
         L_.ggml_b200_free_weight(h)
+    res["e2e"] = {"value": ops / (ms_host * 1e-3) / 1e12, "unit": "TOPS", "ms_per_pass": ms_host,
+                  "h2d_bytes_per_pass": sum(4 * K * n for (_, _, K) in handles), "d2h_bytes_per_pass": sum(4 * M * n for (_, M, _) in handles),
+                  "api": "ggml_b200_mul_mat_q4_0_host (pinned host x/y)"}
+    return res
+
+
+def prefill_sharded_leg(mod, stream, rng, rank, world, dist, steps, warmup, n=512):
+    """BASELINE metric "int8 TOPS (n = 512) at 2/4/8 GPUs": one LLaMA-65B layer + output at n = 512, every weight row-sharded
+    (ggml_b200_mul_mat_q4_0_sharded: kernel 1 + kernel 3 on the shard, ncclAllGather of the slabs over NVLink, scatter into
+    dst).  Timed three ways with CUDA events, max over ranks: the whole op; the shard GEMMs alone (no gather); the op with
+    pinned host x / y around it (e2e).  SURVEY 8(e) predicts the gather, not the GEMM, bounds it."""
+    import torch
+    L_ = mod.lib()
+    shapes = [(8192, 8192, 4), (22016, 8192, 2), (8192, 22016, 1), (32000, 8192, 1)]
+    handles, ops_total = [], 0.0
+    gathered = 0
+    for (M, K, c) in shapes:
+        lo, hi = mod.shard_rows(M, rank, world)
+        blk = random_q4_0(rng, max(hi - lo, 1), K)
+        nb1 = (K // 32) * 18
+        for _ in range(c):
+            h = L_.ggml_b200_upload_q4_0(C.c_void_p(blk.ctypes.data - lo * nb1), M, K, nb1, lo, hi)
+            if not h:
+                raise RuntimeError(L_.ggml_b200_last_error().decode())
+            handles.append((h, M, K))
+            ops_total += 2.0 * M * K * n
+            gathered += 4 * n * M
+    xs = {K: torch.randn(n, K, device="cuda") for K in sorted({K for (_, _, K) in handles})}
+    for K in xs:
+        dist.broadcast(xs[K], src=0)
+    ys = {M: torch.zeros(n, M, device="cuda") for M in sorted({M for (_, M, _) in handles})}
+
+    def run(fn):
+        def one():
+            for (h, M, K) in handles:
+                rc = fn(h, C.c_void_p(xs[K].data_ptr()), n, K * 4, C.c_void_p(ys[M].data_ptr()), M * 4)
+                if rc:
+                    raise RuntimeError(L_.ggml_b200_last_error().decode())
+        with torch.cuda.stream(stream):
+            for _ in range(max(3, warmup)):
+                one()
+        stream.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            for _ in range(steps):
+                one()
+            e1.record(stream)
+        stream.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    ms_op = run(L_.ggml_b200_mul_mat_q4_0_sharded)
+    ms_gemm = run(L_.ggml_b200_mul_mat_q4_0)               # the shard's rows only: kernel 1 + kernel 3, no exchange
+    # e2e: x from pinned host, full y back to pinned host, per matmul (what a host-resident graph pays)
+    xh = {K: torch.empty((n, K), dtype=torch.float32).pin_memory() for K in xs}
+    yh = {M: torch.empty((n, M), dtype=torch.float32).pin_memory() for M in ys}
+    for K in xs:
+        xh[K].copy_(xs[K].cpu())
+
+    def e2e_pass():
+        for (h, M, K) in handles:
+            xs[K].copy_(xh[K], non_blocking=True)
+            rc = L_.ggml_b200_mul_mat_q4_0_sharded(h, C.c_void_p(xs[K].data_ptr()), n, K * 4, C.c_void_p(ys[M].data_ptr()), M * 4)
+            if rc:
+                raise RuntimeError(L_.ggml_b200_last_error().decode())
+            yh[M].copy_(ys[M], non_blocking=True)
+            stream.synchronize()
+    with torch.cuda.stream(stream):
+        e2e_pass()
+        dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(max(2, steps // 2)):
+            e2e_pass()
+    dist.barrier()
+    t = torch.tensor([(time.perf_counter() - t0) * 1e3 / max(2, steps // 2)], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_e2e = float(t.item())
+    for (h, _, _) in handles:
+        L_.ggml_b200_free_weight(h)
+    tops = lambda ms: ops_total / (ms * 1e-3) / 1e12      # noqa: E731
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            pk = json.load(f)
-        bf16, src = float(pk["bf16_tflops"]), "2 x MEASURED_PEAKS.json bf16_tflops (cuBLAS bf16 burst; dense int8 runs at twice the bf16 rate)"
+            bf16 = float(json.load(f)["bf16_tflops"])
     except Exception:
-        bf16, src = 1590.0, "2 x fallback 1.59 PFLOP/s bf16 (B200_PROFILING.md)"
-    tops, tops_gemm = ops / (ms * 1e-3) / 1e12, ops / (ms_gemm * 1e-3) / 1e12
-    return {
-        "metric": "q4_0_mul_mat_n512_int8_TOPS", "value": tops, "unit": "TOPS", "ms_per_pass": ms,
-        "config": {"workload": "llama7b_prefill_n512", "n": n, "matmuls_per_pass": len(handles),
-                   "shapes": [[M, K, c] for (M, K, c) in PREFILL_SHAPES], "ops_per_pass": ops,
-                   "timed": "kernel 1 (quantize_row_q8_0) + kernel 3 (tcgen05 kind::i8 GEMM) per matmul, x/y resident in HBM"},
-        "gpu_launches_per_pass": int(launches),
-        "e2e": {"value": ops / (ms_host * 1e-3) / 1e12, "unit": "TOPS", "ms_per_pass": ms_host,
-                "h2d_bytes_per_pass": sum(4 * K * n for (_, _, K) in handles), "d2h_bytes_per_pass": sum(4 * M * n for (_, M, _) in handles),
-                "api": "ggml_b200_mul_mat_q4_0_host (pinned host x/y)"},
-        "roofline": {"kernel": "gemm_q4_0_tc_kernel (TMA + nibble unpack + tcgen05.mma kind::i8 + TMEM + scale epilogue)",
-                     "bound": "tensor", "achieved": tops_gemm, "peak": 2 * bf16, "unit": "TOP/s", "frac": tops_gemm / (2 * bf16),
-                     "frac_of_nominal_4500": tops_gemm / 4500.0, "peak_source": src, "traffic": gemm_traffic(),
-                     "ms_per_pass_kernel3": ms_gemm,
-                     "note": "the per-block fp16 x fp16 scale epilogue (2 fp32 FMA per int32 S_b on the CUDA cores) bounds this "
-                             "formulation at 64/256 = 25% of the tensor rate with 128x128 tiles; see DESIGN.md kernel 3"},
-    }
+        bf16 = 1590.0
+    return {"metric": "q4_0_mul_mat_n512_int8_TOPS", "value": tops(ms_op), "unit": "TOPS (aggregate over the ranks)", "ms_per_pass": ms_op,
+            "config": {"workload": "llama65b_layer_prefill_n512_rowsharded", "n": n, "matmuls_per_pass": len(handles), "shapes": [list(t_) for t_ in shapes],
+                       "ops_per_pass": ops_total, "ranks": world},
+            "kernels_only": {"value": tops(ms_gemm), "ms_per_pass": ms_gemm, "what": "kernel 1 + kernel 3 on every rank's shards, no exchange"},
+            "gather": {"ms_per_pass": ms_op - ms_gemm, "bytes_received_per_rank_per_pass": int(gathered * (world - 1) / world),
+                       "GBps_per_rank": gathered * (world - 1) / world / max(ms_op - ms_gemm, 1e-6) / 1e6,
+                       "what": "ncclAllGather of the [n][rows] slabs + scatter kernel (op time minus kernels-only time)"},
+            "e2e": {"value": tops(ms_e2e), "unit": "TOPS", "ms_per_pass": ms_e2e, "h2d_bytes_per_pass": sum(4 * K * n for (_, _, K) in handles) * world,
+                    "d2h_bytes_per_pass": gathered * world, "api": "pinned host x -> HBM on every rank, ggml_b200_mul_mat_q4_0_sharded, full y -> pinned host"},
+            "roofline": {"bound": "tensor", "achieved": tops(ms_gemm) / world, "peak": 2 * bf16, "unit": "TOP/s per rank", "frac": tops(ms_gemm) / world / (2 * bf16),
+                         "kernel": "gemm_q4_0_tc_kernel on the rank's row shards"}}
 
+
+def thread_counts():
+    c = os.cpu_count() or 1
+    return sorted({t for t in (8, 16, 32, c) if t <= c} or {c})
 
 
 def run_gpu_arm(args, workload, rank, world, local_rank):
@@ -495,7 +813,7 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
     # every dst buffer must be bit-identical to the per-op path's; otherwise the per-op kernels are timed instead.
     opset = None
     set_note = None
-    if world == 1 and not args.no_set and not args.unfused:
+    if not args.no_set and not args.unfused:
         try:
             with torch.cuda.stream(stream):
                 one_step_per_op()
@@ -504,7 +822,11 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
             for y in yg.values():
                 y.zero_()
             torch.cuda.synchronize()
-            opset = mod.OpSet([(h, xp, yp) for (h, M, K, xp, yp) in ops])
+            # world > 1: collective -- one persistent launch per rank on its row shards, the exchange inside the launch
+            # (ggml_b200_set_create_sharded: tagged words into every rank's arena over NVLink, a gather warp per CTA)
+            opset = mod.OpSet([(h, xp, yp) for (h, M, K, xp, yp) in ops], sharded=world > 1)
+            if world > 1:
+                dist.barrier()
             with torch.cuda.stream(stream):
                 opset.run()
             stream.synchronize()
@@ -522,13 +844,79 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
                         raise RuntimeError(f"dst buffer {pos} (K = {K_pos}) differs from the per-op path: max|dY|/max|Y| = {err:.3e}")
                 return exact
             n_exact = set_check()
-            set_note = {"ops": opset.n_ops, "dependency_barriers": opset.barriers, "ring_slots": opset.slots,
+            gate = None
+            if world == 1:
+                # the gate of the headline number (advisor r1): (1) every op its OWN dst, all results against the per-op
+                # path (on the timed list the layers overwrite each other's dst); (2) the first two layers + output
+                # CHAINED like the model (x of an op = dst of an earlier one: tagged-word dependencies inside the launch)
+                def cmp_lists(lst, label):
+                    refs = [torch.zeros((1, M), dtype=torch.float32, device="cuda") for (h, M, K, xp) in lst]
+                    outs = [torch.zeros((1, M), dtype=torch.float32, device="cuda") for (h, M, K, xp) in lst]
+                    def ptr(xp, table):
+                        return table[xp[1]].data_ptr() if isinstance(xp, tuple) else xp
+                    with torch.cuda.stream(stream):
+                        for i, (h, M, K, xp) in enumerate(lst):
+                            rc = L_.ggml_b200_mul_mat_q4_0(h, C.c_void_p(ptr(xp, refs)), 1, K * 4, C.c_void_p(refs[i].data_ptr()), M * 4)
+                            assert rc == 0, L_.ggml_b200_last_error().decode()
+                    stream.synchronize()
+                    s2 = mod.OpSet([(h, ptr(xp, outs), outs[i].data_ptr()) for i, (h, M, K, xp) in enumerate(lst)])
+                    with torch.cuda.stream(stream):
+                        s2.run()
+                    stream.synchronize()
+                    worst, nex = 0.0, 0
+                    for i, (h, M, K, xp) in enumerate(lst):
+                        a, b = outs[i].cpu().numpy(), refs[i].cpu().numpy()
+                        if np.array_equal(a, b):
+                            nex += 1
+                            continue
+                        err = float(np.max(np.abs(a - b)) / max(float(np.max(np.abs(b))), 1e-30))
+                        worst = max(worst, err)
+                        if K <= 4096 or not err <= 1e-5:
+                            raise RuntimeError(f"{label}: op {i} ({M}x{K}) differs from the per-op path: {err:.3e}")
+                    info = (len(lst), nex, worst, s2.linked_runs)
+                    s2.free()
+                    return info
+                own = cmp_lists([(h, M, K, xp) for (h, M, K, xp, yp) in ops], "own-dst list")
+                nl = len(layer_shapes)
+                sub = [ops[i] for i in range(min(2, L) * nl)] + [ops[-1]]
+                chain = []
+                for i, (h, M, K, xp, yp) in enumerate(sub):
+                    pos = i % nl if i < len(sub) - 1 else nl
+                    lay0 = (i // nl) * nl
+                    src = xp
+                    if workload.startswith("llama"):
+                        if pos == 3:
+                            src = ("dst", lay0 + 0)
+                        elif pos in (4, 5):
+                            src = ("dst", lay0 + 3)
+                        elif pos == 6:
+                            src = ("dst", lay0 + 5)
+                        elif pos in (0, 1, 2) and i >= nl:
+                            src = ("dst", lay0 - 1)
+                        elif pos == nl and len(sub) > 1 and sub[-2][1] == K:
+                            src = ("dst", len(sub) - 2)
+                    chain.append((h, M, K, src))
+                ch = cmp_lists(chain, "chained list")
+                gate = {"own_dst_list": f"{own[0]} ops, {own[1]} bit-identical to the per-op path, worst of the others {own[2]:.1e} (K > 4096: fixed-order four-warp sums)",
+                        "chained_list": f"{ch[0]} ops, {ch[3]} runs read their x from an earlier op's tagged rows, {ch[1]} bit-identical, worst of the others {ch[2]:.1e}"}
+            set_note = {"ops": opset.n_ops, "gate": gate, "dependency_barriers": opset.barriers, "ring_slots": opset.slots,
                         "checked": f"{n_exact}/{len(yg)} dst buffers bit-identical to ggml_b200_mul_mat_q4_0 per op (all with K <= 4096), "
                                    "the others within 1e-5 of max|y| (fixed-order four-warp sums)"}
         except Exception as e:   # noqa: BLE001
-            print(f"[bench] persistent multi-op launch unavailable ({e}); timing one launch per mul_mat", file=sys.stderr)
-            opset = None
-            torch.cuda.synchronize()      # a trapped kernel leaves a sticky error: fail here, loudly
+            print(f"[bench] rank {rank}: persistent multi-op launch unavailable ({e}); timing one launch per mul_mat", file=sys.stderr)
+            if world > 1 and opset is not None:
+                set_note = None
+            else:
+                opset = None
+            if world == 1:
+                torch.cuda.synchronize()      # a trapped kernel leaves a sticky error: fail here, loudly
+        if world > 1:
+            # every rank must take the same path: the launch waits for its peers
+            okf = torch.tensor([1 if (opset is not None and set_note is not None) else 0], device="cuda")
+            dist.all_reduce(okf, op=dist.ReduceOp.MIN)
+            if int(okf.item()) == 0 and opset is not None:
+                opset.free()
+                opset = None
     if args.probe_set:
         # child process of main(): is the persistent launch healthy on this box (parity above, then graph replays)?
         ok = opset is not None
@@ -559,9 +947,54 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
         else:
             one_step_per_op()
 
-    # ---- sanity (outside any timed region): the last matmul of the set against the oracle
+    # ---- sanity (outside any timed region): EVERY rank's shard of one matmul per distinct shape against the oracle, on
+    # the dst buffers the timed path just wrote (the persistent launch where it is used, else one launch per mul_mat)
+    parity_shapes = None
+    if not args.no_check:
+        import oracle
+        R_, P_ = oracle.ref(), oracle.port()
+        with torch.cuda.stream(stream):
+            one_step()
+        stream.synchronize()
+        mine = {}
+        seen = set()
+        n_lay = len(layer_shapes)
+        for idx in range(len(handles) - 1, -1, -1):            # the last writer of every dst buffer
+            (h, M, K, xp, yp) = ops[idx]
+            if (M, K) in seen:
+                continue
+            seen.add((M, K))
+            key = ("L", idx % n_lay) if idx < L * n_lay else ("O", idx - L * n_lay)
+            lo, hi = mod.shard_rows(M, rank, world)
+            if hi <= lo:
+                continue
+            pos = idx % n_lay if idx < L * n_lay else n_lay + (idx - L * n_lay)
+            grp = src_group[pos] if pos < len(src_group) else "out_in"
+            xn = xg[grp].cpu().numpy()
+            Wh = host_blocks[key][: hi - lo]
+            Yo = R_.mul_mat(Wh, xn, n_threads=min(8, os.cpu_count() or 1)) if R_ is not None else P_.mul_mat(Wh, xn, avx2_order=True)
+            Yfull = yg[pos].cpu().numpy()
+            mine[f"{M}x{K}"] = float(np.max(np.abs(Yfull[:, lo:hi] - Yo)) / max(float(np.max(np.abs(Yo))), 1e-30))
+            if world > 1:
+                # and the peers' rows as gathered here must be what the peers computed: checksum of the whole dst
+                mine[f"{M}x{K}_dst_checksum"] = float(np.sum(Yfull.astype(np.float64)))
+        allm = [mine]
+        if world > 1:
+            allm = [None] * world
+            dist.all_gather_object(allm, mine)
+        parity_shapes = {}
+        for k in mine:
+            if k.endswith("_dst_checksum"):
+                vals = [m.get(k) for m in allm if k in m]
+                if max(vals) != min(vals):
+                    raise RuntimeError(f"bench sanity check failed: ranks disagree on the gathered dst of {k}: {vals}")
+            else:
+                parity_shapes[k] = [m.get(k) for m in allm]
+                worst = max(v for v in parity_shapes[k] if v is not None)
+                if not worst <= 1e-4:
+                    raise RuntimeError(f"bench sanity check failed on {k}: max|dY|/max|Y| per rank = {parity_shapes[k]}")
     parity = None
-    if rank == 0 and not args.no_check:
+    if rank == 0 and not args.no_check and world == 1:
         import oracle
         P = oracle.port()
         hW, M, K = handles[0]
@@ -608,7 +1041,16 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
             mod.set_stream(torch.cuda.current_stream().cuda_stream)
             one_step_per_op()
         mod.set_stream(stream.cuda_stream)
-        ms_po, ms_set = quick(g_po.replay), quick(opset.run)
+        if world > 1:
+            dist.barrier()
+        ms_po = quick(g_po.replay)
+        if world > 1:
+            dist.barrier()
+        ms_set = quick(opset.run)
+        if world > 1:
+            tt = torch.tensor([ms_po, ms_set], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ms_po, ms_set = float(tt[0].item()), float(tt[1].item())
         del g_po
         set_note["ms_per_step_one_launch_per_step"] = ms_set
         set_note["ms_per_step_one_launch_per_mul_mat"] = ms_po
@@ -675,6 +1117,15 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
     # kernel launch, so its average launch duration is the step time / launches; with --unfused
     # (kernel 1 + kernel 2) the GEMV is re-timed alone on pre-quantized activations.
     roof = None
+    if world > 1:
+        peak, peak_src = peaks()
+        per_rank = total_bytes / world / (ms_per_step * 1e-3) / 1e9
+        roof = {"kernel": ("gemv_q4_0_set_kernel<GATHER> (persistent, one launch per rank and step; rows exchanged as tagged words over NVLink inside the launch)"
+                           if opset is not None else "gemv_q4_0_fused_p2p_kernel (one launch + one NVLink exchange per mul_mat)"),
+                "bound": "hbm", "achieved": per_rank, "peak": peak, "unit": "GB/s per rank", "frac": per_rank / peak,
+                "peak_source": peak_src, "traffic": None,
+                "nvlink_bytes_per_step_per_rank": int(sum(8 * (mod.shard_rows(M, rank, world)[1] - mod.shard_rows(M, rank, world)[0]) * (world - 1) for (_, M, K) in handles)),
+                "note": "per-rank algorithmic bytes (its row shards) / step time (max over ranks) against one GPU's measured HBM copy peak"}
     if world == 1:
         peak, peak_src = peaks()
         n_launch = len(handles)
@@ -783,21 +1234,48 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
                "ms_per_step": e2e_ms, "steps": e2e_steps,
                "api": "pinned host x -> HBM on every rank, ggml_b200_mul_mat_q4_0_sharded, y -> pinned host, per matmul"}
     prefill = None
+    extra = None
+    n_matmuls = len(handles)
     if world == 1 and not args.no_prefill:
         prefill = prefill_leg(mod, stream, rng, max(5, min(args.steps // 10, 20)), args.warmup)
+    if world > 1 and not args.no_prefill:
+        prefill = prefill_sharded_leg(mod, stream, rng, rank, world, dist, max(3, min(args.steps // 20, 10)), args.warmup)
+    if world == 1 and not args.no_extra:
+        # the other BASELINE configs (each freed again before the next): [0] one 4096x4096 op, [3] Falcon-7B n = 1 and
+        # n = 512, and the 65B set on ONE GPU = the base of the 1 -> 8 scaling run
+        for (h, _, _) in handles:
+            L_.ggml_b200_free_weight(h)
+        handles = []
+        torch.cuda.empty_cache()
+        est = max(5, min(args.steps // 4, 50))
+        extra = {}
+        try:
+            extra["single_4096"] = decode_list_leg(mod, stream, rng, "single_4096_n1", est * 2, args.warmup)
+            extra["falcon7b"] = {"decode_n1": decode_list_leg(mod, stream, rng, "falcon7b_decode_n1", est, args.warmup),
+                                 "prefill_n512": prefill_leg(mod, stream, rng, max(5, min(args.steps // 10, 20)), args.warmup, shapes=FALCON_PREFILL_SHAPES,
+                                                             groups=FALCON_PREFILL_GROUPS, name="falcon7b_prefill_n512", host_leg=False)}
+            extra["scaling_base"] = decode_list_leg(mod, stream, rng, "llama65b_decode_n1_rowsharded", max(3, est // 4), args.warmup)
+            extra["scaling_base"]["note"] = "the workload of --gpus 2/4/8 on ONE GPU, same step definition: divide the N-GPU values by this GB/s for the strong-scaling efficiency"
+        except Exception as e:   # noqa: BLE001
+            extra["error"] = str(e)
     t_clock1 = time.time()
     clocks = sampler.stop(t_clock0, t_clock1) if sampler else None
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        cpu = cpu_reference_arm(workload, 10, 1, budget_s=20.0)
+        cpu = cpu_reference_arm(workload, 10, 1, budget_s=20.0, sample_layers=2)
+        if extra is not None and "single_4096" in extra:
+            try:
+                extra["single_4096"]["cpu_reference"] = single_4096_cpu(thread_counts())
+            except Exception as e:   # noqa: BLE001
+                extra["single_4096"]["cpu_reference"] = {"error": str(e)}
 
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
             "vs_baseline": None, "dtype": "int8 dot (q4_0 x q8_0, dp4a), fp32 scale+accumulate", "data": "synthetic",
-            "config": {"workload": workload, "n": 1, "layers": L, "matmuls_per_step": len(handles),
+            "config": {"workload": workload, "n": 1, "layers": L, "matmuls_per_step": n_matmuls,
                        "weight_bytes_per_step": weight_bytes, "algorithmic_bytes_per_step": total_bytes,
                        "l2": "inputs larger than L2: the set's weights (%.2f GB per rank) are streamed once per step" % (weight_bytes / world / 1e9),
                        "weights": "random-init Q4_0 blocks (one layer generated on the host, a separate HBM copy per layer)",
@@ -806,7 +1284,8 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
                        "same_src1_overlap": not args.no_overlap, "tune": args.tune,
                        "one_launch_per_step": set_note,
                        "parallelism": ("row-sharded x%d + peer-to-peer gather kernel per matmul (NVLink stores + flags; NCCL only for n > 1)" % world) if world > 1 else "single GPU",
-                       "setup_s": round(setup_s, 2), "sanity_max_rel_err": parity},
+                       "setup_s": round(setup_s, 2), "sanity_max_rel_err": parity,
+                       "sanity_max_rel_err_per_shape_and_rank": parity_shapes},
             "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps), "gpu_launches_per_step": int(launches_per_step),
             "clocks": clocks,
         }
@@ -814,6 +1293,8 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
             line["roofline"] = roof
         if prefill:
             line["prefill"] = prefill
+        if extra:
+            line["configs"] = extra
         if cpu:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
@@ -856,6 +1337,7 @@ def main():
     ap.add_argument("--no-check", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-prefill", action="store_true", help="skip the n = 512 tensor-core leg")
+    ap.add_argument("--no-extra", action="store_true", help="skip the other BASELINE configs (single 4096x4096, Falcon-7B, 65B on one GPU)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
@@ -875,7 +1357,7 @@ def main():
         # The persistent launch spins on device-side barriers: prove it healthy in a CHILD process first (a trapped
         # kernel poisons its CUDA context), and time one launch per mul_mat if it is not.
         cmd = [sys.executable, os.path.abspath(__file__), "--probe-set", "--set", "--layers", "2", "--workload", workload,
-               "--no-cpu", "--no-prefill", "--no-check"] + [a for kv in args.tune for a in ("--tune", kv)]
+               "--no-cpu", "--no-prefill", "--no-check", "--no-extra"] + [a for kv in args.tune for a in ("--tune", kv)]
         try:
             pr = subprocess.run(cmd, timeout=600, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
             healthy = pr.returncode == 0

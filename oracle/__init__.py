@@ -196,6 +196,9 @@ class Ref:
         L.ref_dequantize_row_q4_0.argtypes = [_vp, _vp, C.c_int]
         L.ref_vec_dot_q4_0_q8_0.restype = C.c_float
         L.ref_vec_dot_q4_0_q8_0.argtypes = [C.c_int, _vp, _vp]
+        if hasattr(L, "ref_time_vec_dot_q4_0_q8_0"):
+            L.ref_time_vec_dot_q4_0_q8_0.restype = C.c_int64
+            L.ref_time_vec_dot_q4_0_q8_0.argtypes = [C.c_int, _vp, C.c_int64, _vp, C.c_int, C.c_int, _vp]
         L.ref_quantize_q4_0.restype = C.c_size_t
         L.ref_quantize_q4_0.argtypes = [_vp, _vp, C.c_int, C.c_int]
         L.ref_mm_create.restype = _vp
@@ -262,6 +265,16 @@ class Ref:
         q8_row = np.ascontiguousarray(q8_row, dtype=np.uint8)
         k = (w_row.size // Q4_0_BYTES) * QK
         return float(self.L.ref_vec_dot_q4_0_q8_0(k, _ptr(w_row), _ptr(q8_row)))
+
+    def time_vec_dot(self, W: np.ndarray, q8_row: np.ndarray, warmup: int = 5, iters: int = 10) -> float:
+        """best-of-`iters` seconds of one single-thread pass of vec_dot_q over all rows of W (test-quantize-perf method)"""
+        W = np.ascontiguousarray(W, dtype=np.uint8)
+        q8_row = np.ascontiguousarray(q8_row, dtype=np.uint8)
+        rows = W.shape[0]
+        k = (W.size // rows // Q4_0_BYTES) * QK
+        sink = C.c_float(0)
+        us = self.L.ref_time_vec_dot_q4_0_q8_0(k, _ptr(W), rows, _ptr(q8_row), warmup, iters, C.byref(sink))
+        return max(us, 1) * 1e-6
 
     def mul_mat(self, W: np.ndarray, X: np.ndarray, n_threads: int = 1) -> np.ndarray:
         """The whole op through ggml_graph_compute (ref_shim.c)."""

@@ -54,6 +54,29 @@ float ref_vec_dot_q4_0_q8_0(int k, const void * x, const void * y) {
     return s;
 }
 
+/* single-thread vec_dot_q throughput, the method of tests/test-quantize-perf.cpp:85-108 (warm-up passes, then the
+ * best of `iters` timed passes): one pass = vec_dot of every row of W [rows][k/32 blocks] against one q8_0 row.
+ * Returns the best pass in microseconds; *sink keeps the sums alive. */
+int64_t ref_time_vec_dot_q4_0_q8_0(int k, const void * W, int64_t rows, const void * y, int warmup, int iters, float * sink) {
+    ref_init();
+    quantize_fns_t f = ggml_internal_get_quantize_fn(GGML_TYPE_Q4_0);
+    const size_t row_bytes = (size_t)(k / 32) * 18;
+    float acc = 0.0f;
+    int64_t best = -1;
+    for (int it = 0; it < warmup + iters; it++) {
+        const int64_t t0 = ggml_time_us();
+        for (int64_t r = 0; r < rows; r++) {
+            float s = 0.0f;
+            f.vec_dot_q(k, &s, (const char *)W + r * row_bytes, y);
+            acc += s;
+        }
+        const int64_t dt = ggml_time_us() - t0;
+        if (it >= warmup && (best < 0 || dt < best)) best = dt;
+    }
+    if (sink) *sink = acc;
+    return best;
+}
+
 /* bulk weight quantizer, ggml.c:19157-19178 */
 size_t ref_quantize_q4_0(const float * src, void * dst, int n, int k) {
     ref_init();
