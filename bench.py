@@ -347,6 +347,8 @@ def decode_list_leg(mod, stream, rng, workload, steps, warmup, layers=None, chec
         grp = groups[pos] if pos < len(groups) else "out_in"
         if grp not in xg:
             xg[grp] = torch.from_numpy(rng.standard_normal((1, K), dtype=np.float32)).cuda()
+        if workload.startswith("single"):
+            pos = idx                  # "one op", repeated on cold weights: every repetition has its own dst (no hazards between them)
         if pos not in yg:
             yg[pos] = torch.zeros((1, M), dtype=torch.float32, device="cuda")
         ops.append((h, M, K, xg[grp], yg[pos]))
@@ -713,6 +715,9 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
 
     if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
         os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line (the version banner goes to stdout)
+    # stdout carries exactly ONE JSON line: anything a library prints there (the NCCL version banner does) goes to stderr
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     mod = load_binding()
     torch.cuda.set_device(local_rank)
     mod.init(local_rank)
@@ -1283,7 +1288,8 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
                        "fused_quantize": not args.unfused, "pdl": not args.no_pdl,
                        "same_src1_overlap": not args.no_overlap, "tune": args.tune,
                        "one_launch_per_step": set_note,
-                       "parallelism": ("row-sharded x%d + peer-to-peer gather kernel per matmul (NVLink stores + flags; NCCL only for n > 1)" % world) if world > 1 else "single GPU",
+                       "parallelism": (("row-sharded x%d, " % world) + ("one persistent launch per rank and step with the row exchange inside it (tagged words over NVLink, no collective call)" if opset is not None
+                                                                           else "peer-to-peer gather fused into one GEMV launch per matmul (NVLink stores; NCCL only for n > 1)")) if world > 1 else "single GPU",
                        "setup_s": round(setup_s, 2), "sanity_max_rel_err": parity,
                        "sanity_max_rel_err_per_shape_and_rank": parity_shapes},
             "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps), "gpu_launches_per_step": int(launches_per_step),
@@ -1297,7 +1303,8 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
             line["configs"] = extra
         if cpu:
             line["cpu_baseline"] = cpu
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
 
     if world > 1:
         # the captured graph holds NCCL kernels of the library's communicator: tearing the communicator down under

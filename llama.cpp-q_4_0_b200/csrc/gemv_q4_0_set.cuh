@@ -44,8 +44,14 @@ namespace b200 {
 constexpr int SET_WPG = 4;            // consumer warps per group
 constexpr int SET_XWARPS = 2;         // warps that quantize the NEXT run's x while the consumers work on this one
 constexpr int SET_EXTRA_THREADS = 32 /* producer */ + 32 /* sentinel */ + 32 * SET_XWARPS;
-// multi-GPU lists: the second x warp becomes the gather warp (copies the peers' rows into dst), so the CTA keeps its
-// 512 threads / 128 registers (one more warp would round the register budget down to 96 and spill the tile loop)
+// Multi-GPU lists (GATHER): every rank quantizes the whole replicated x of every run itself while it streams only 1/N
+// of the weights, so the x warps, not the weight stream, become the limiter as N grows (measured at N = 2 with one x
+// warp: 4.48 ms per 65B step against 2.98 ms of HBM time).  The gather build therefore runs 8 consumer warps, 5 x warps
+// and 1 gather warp: still 512 threads / 128 registers.
+constexpr int SET_XWARPS_GATHER = 5;
+constexpr int SET_GATHER_WARPS_CONSUMER = 8;
+template <bool GATHER> __host__ __device__ constexpr int set_xwarps() { return GATHER ? SET_XWARPS_GATHER : SET_XWARPS; }
+template <int W, bool GATHER> __host__ __device__ constexpr int set_threads() { return W * 32 + 64 + 32 * set_xwarps<GATHER>() + (GATHER ? 32 : 0); }
 constexpr int SET_MAX_SLOTS = 16;
 constexpr int SET_MAX_GROUPS = 6;
 constexpr int SET_RED_BYTES = 2 * SET_MAX_GROUPS * 16 * 4;   // cross-warp partials: [parity][group][row 4][warp 4] floats
@@ -493,7 +499,7 @@ __device__ __forceinline__ int set_consume_run(const SetCtx & c, const GemvSmem<
 // {whole kernel, consumer warp 0 waiting for full slots, in dependency barriers, quantizing x, producer waiting for empty slots}
 // BIG: also the 6-blocks-per-lane plan (K > 16384); the kernel without it needs fewer registers
 template <int W, bool DUMP, bool PROF, bool BIG, bool GATHER>
-__global__ void __launch_bounds__(W * 32 + SET_EXTRA_THREADS, 1)
+__global__ void __launch_bounds__(set_threads<W, GATHER>(), 1)
 gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restrict__ sync, int nslots, int slot_bytes,
                      int x_bytes, int x_bufs, int tbl_bytes, int max_fly, unsigned seq, long long * __restrict__ prof,
                      const __grid_constant__ SetGather gth) {
@@ -646,7 +652,7 @@ gemv_q4_0_set_kernel(const SetOp * __restrict__ ops, int nops, SetSync * __restr
         }
         return;
     }
-    constexpr int XW = GATHER ? SET_XWARPS - 1 : SET_XWARPS;
+    constexpr int XW = set_xwarps<GATHER>();
     if (warp > W + 1 && warp < W + 2 + XW) {
         // ===== x warps: kernel 1 (quantize_row_q8_0) of every run, one run AHEAD of the consumers =====
         // The consumers keep a run's x in registers, so the planes are free as soon as every warp has copied them: the

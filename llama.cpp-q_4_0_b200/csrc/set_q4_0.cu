@@ -45,7 +45,7 @@ static int set_launch_tb(const ggml_b200_set * s, const SetOp * table, long long
     auto kern = gemv_q4_0_set_kernel<W, DUMP, PROF, BIG, GATHER>;
     B200_SET_SMEM_ATTR(kern, MAX_DYN_SMEM - 1024);
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)s->grid); cfg.blockDim = dim3(W * 32 + SET_EXTRA_THREADS); cfg.dynamicSmemBytes = s->smem; cfg.stream = g.stream;
+    cfg.gridDim = dim3((unsigned)s->grid); cfg.blockDim = dim3(set_threads<W, GATHER>()); cfg.dynamicSmemBytes = s->smem; cfg.stream = g.stream;
     // every CTA of the grid must be resident at once (dependency barriers spin on peers): cooperative launch makes
     // the driver check that instead of trusting it
     cudaLaunchAttribute attr[1];
@@ -59,10 +59,10 @@ static int set_launch_tb(const ggml_b200_set * s, const SetOp * table, long long
 
 template <int W, bool DUMP, bool PROF>
 static int set_launch_t(const ggml_b200_set * s, const SetOp * table, long long * prof) {
-    if constexpr (!DUMP && !PROF) {
+    if constexpr (!DUMP && !PROF && W == SET_GATHER_WARPS_CONSUMER) {
         if (s->gathered) return s->big ? set_launch_tb<W, false, false, true, true>(s, table, prof) : set_launch_tb<W, false, false, false, true>(s, table, prof);
     }
-    if (s->gathered) { set_error("checkpoint / profile launches are single-GPU only"); return GGML_B200_ERR_ARG; }
+    if (s->gathered) { set_error("multi-GPU lists run %d consumer warps; checkpoint / profile launches are single-GPU only", SET_GATHER_WARPS_CONSUMER); return GGML_B200_ERR_ARG; }
     return s->big ? set_launch_tb<W, DUMP, PROF, true>(s, table, prof) : set_launch_tb<W, DUMP, PROF, false>(s, table, prof);
 }
 
@@ -208,7 +208,7 @@ static ggml_b200_set * set_create_impl(const ggml_b200_set_op * ops, int n_ops, 
     if (!ops || n_ops <= 0) { set_error("empty op list"); return nullptr; }
     ggml_b200_set * s = new ggml_b200_set();
     s->grid = g.sm_count;
-    s->warps = g.tune.set_warps;
+    s->warps = gathered ? SET_GATHER_WARPS_CONSUMER : g.tune.set_warps;
     int NG = s->warps / SET_WPG;
     int nbk_max = 0;
     long long tiles = 0;
