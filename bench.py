@@ -704,6 +704,51 @@ def prefill_sharded_leg(mod, stream, rng, rank, world, dist, steps, warmup, n=51
                          "kernel": "gemm_q4_0_tc_kernel on the rank's row shards"}}
 
 
+def glue_e2e_leg(steps, warmup):
+    """e2e through the reference's own offload seam: ggml_graph_compute over a LLaMA-7B decode graph built with the
+    reference's graph API as llama.cpp builds it (tests/glue/layer_driver.c: 32 layers of rms_norm, mul, wq/wk/wv, wo, add,
+    rms_norm, mul, w3, w1, silu, mul, w2, add + final norm + output matmul = the 225 Q4_0 matmuls of the set; the attention
+    core is one CPU node), weights uploaded by ggml_cuda_transform_tensor, results of the offloaded nodes placed by
+    ggml_cuda_assign_buffers, every node entering through ggml_cuda_compute_forward (ggml-b200-glue.c).  HOST input row,
+    HOST logits; wall clock per eval including the graph build."""
+    so = os.path.join(PKG, "ggml_glue", "_build", "libggml_b200_glue_ref.so")
+    if not os.path.exists(so):
+        return None
+    G = C.CDLL(so)
+    if not hasattr(G, "glue_model_create"):
+        return None
+    G.glue_model_create.restype = C.c_void_p
+    G.glue_model_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint]
+    G.glue_model_eval.restype = C.c_double
+    G.glue_model_eval.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]
+    G.glue_model_free.restype = None
+    G.glue_model_free.argtypes = [C.c_void_p]
+    n_layer, n_embd, n_ff, n_vocab = 32, 4096, 11008, 32000
+    m = G.glue_model_create(n_layer, n_embd, n_ff, n_vocab, 1, 11)
+    if not m:
+        return None
+    x = np.random.default_rng(9).standard_normal(n_embd).astype(np.float32)
+    logits = np.zeros(n_vocab, np.float32)
+    xp, lp = x.ctypes.data_as(C.c_void_p), logits.ctypes.data_as(C.c_void_p)
+    out = {}
+    for name, acts in (("device_resident", 1), ("host_activations", 0)):
+        G.glue_model_eval(m, xp, lp, 1, max(3, warmup), acts)
+        sec = G.glue_model_eval(m, xp, lp, 1, steps, acts)
+        out[name] = sec
+        if not np.isfinite(logits).all():
+            raise RuntimeError("glue e2e: non-finite logits")
+    G.glue_model_free(m)
+    nbytes = sum(algo_bytes(M, K) for (M, K) in matmul_list("llama7b_decode_n1"))
+    return {"value": nbytes / out["device_resident"] / 1e9, "unit": UNIT, "ms_per_step": out["device_resident"] * 1e3, "steps": steps,
+            "h2d_bytes_per_step": 4 * n_embd * (1 + n_layer), "d2h_bytes_per_step": 4 * n_embd * 3 * n_layer + 4 * n_vocab,
+            "api": "ggml_graph_compute (reference, -DGGML_USE_CUBLAS) over a LLaMA-7B decode graph; offload through ggml_cuda_transform_tensor / "
+                   "ggml_cuda_assign_buffers / ggml_cuda_compute_forward of ggml-b200-glue.c; host input row, host logits, n_threads = 1",
+            "graph": "tests/glue/layer_driver.c: llama.cpp's layer (llama.cpp:1290-1540) with the attention core replaced by one CPU node; "
+                     "per eval 1 + 32 activation rows go up, 96 rows + the logits come back, the other activations stay in HBM",
+            "same_graph_with_host_activations": {"value": nbytes / out["host_activations"] / 1e9, "ms_per_step": out["host_activations"] * 1e3,
+                                                 "what": "no ggml_cuda_assign_buffers: every offloaded matmul takes and returns host rows (round 1's seam)"}}
+
+
 def thread_counts():
     c = os.cpu_count() or 1
     return sorted({t for t in (8, 16, 32, c) if t <= c} or {c})
@@ -1196,6 +1241,15 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
                "d2h_bytes_per_step": sum(4 * M for (_, M, _) in handles),
                "ms_per_step": e2e_ms, "steps": e2e_steps,
                "api": "ggml_b200_mul_mat_q4_0_host (pinned host x/y, synchronous per matmul like the ggml hook)"}
+        if workload == "llama7b_decode_n1" and not args.layers and not args.no_glue:
+            try:
+                ge = glue_e2e_leg(e2e_steps, args.warmup)
+            except Exception as e:   # noqa: BLE001
+                print(f"[bench] glue e2e leg failed: {e}", file=sys.stderr)
+                ge = None
+            if ge is not None:
+                ge["per_matmul_host_call"] = e2e      # the raw C call with host x / y per matmul, as round 1 reported it
+                e2e = ge
         # the D2H result of the last matmul must equal the resident path's
         if not args.no_check:
             hW, M, K = handles[-1]
@@ -1344,6 +1398,7 @@ def main():
     ap.add_argument("--no-check", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-prefill", action="store_true", help="skip the n = 512 tensor-core leg")
+    ap.add_argument("--no-glue", action="store_true", help="e2e: only the per-matmul host call, not the graph through the reference's seam")
     ap.add_argument("--no-extra", action="store_true", help="skip the other BASELINE configs (single 4096x4096, Falcon-7B, 65B on one GPU)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

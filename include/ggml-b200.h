@@ -143,6 +143,21 @@ int          ggml_b200_mul_mat_q4_0_static(const ggml_b200_weight * w, const flo
                                            size_t nb11, float * y_dev, size_t nb1);
 size_t       ggml_b200_static_max_elems(void);
 
+/* ---- the op's element-wise neighbours in a LLaMA layer ----------------------------
+ * so that activations stay in HBM between consecutive Q4_0 mul_mats (what ggml_cuda_assign_buffers,
+ * ggml-cuda.cu:2830-2892, achieves in the reference).  Device pointers, asynchronous on the current stream, results
+ * follow the reference's CPU code:
+ *   rms_norm : ggml_compute_forward_rms_norm_f32 (ggml.c:10400-10450; sum of squares in double, eps 1e-6 by the caller)
+ *   mul, add : ggml_compute_forward_mul_f32 / _add_f32 (ggml.c:9160-9240, :8480-8560); src1 has nb elements and is
+ *              repeated along src0 (nb == n, or one row broadcast over the rows: the norm weights)
+ *   silu     : ggml_vec_silu_f32 with GGML_SILU_FP16 (ggml.c:3530-3538): y = fp16(silu(fp16(x)))
+ *   silu_mul : silu(x) * b in one kernel (llama.cpp:1492-1498, the FFN gate) */
+int          ggml_b200_rms_norm_f32(const float * x_dev, float * y_dev, int64_t ncols, int64_t nrows, float eps);
+int          ggml_b200_mul_f32(const float * a_dev, const float * b_dev, float * y_dev, int64_t n, int64_t nb);
+int          ggml_b200_add_f32(const float * a_dev, const float * b_dev, float * y_dev, int64_t n, int64_t nb);
+int          ggml_b200_silu_f32(const float * x_dev, float * y_dev, int64_t n);
+int          ggml_b200_silu_mul_f32(const float * x_dev, const float * b_dev, float * y_dev, int64_t n);
+
 /* ---- a list of n = 1 ops in ONE launch ----------------------------------------
  * replaces, for the run of GGML_OP_MUL_MAT nodes of a decode step, the per-node loop of
  * ggml_graph_compute (ggml.c:17541-17720) entering ggml_compute_forward_mul_mat_q_f32
@@ -255,6 +270,9 @@ void         ggml_b200_dev_free(void * ptr);
 int          ggml_b200_memcpy_h2d(void * dst_dev, const void * src_host, size_t size);
 int          ggml_b200_memcpy_d2h(void * dst_host, const void * src_dev, size_t size);
 int          ggml_b200_synchronize(void);
+/* the same copies without the stream sync (the glue keeps activations on the device and syncs once per CPU node) */
+int          ggml_b200_memcpy_h2d_async(void * dst_dev, const void * src_host, size_t size);
+int          ggml_b200_memcpy_d2h_async(void * dst_host, const void * src_dev, size_t size);
 
 #ifdef __cplusplus
 }

@@ -28,6 +28,7 @@
 #include "quantize_q8_0.cuh"
 #include "repack.cuh"
 #include "codec_q4_0.cuh"
+#include "elementwise.cuh"
 #include "state.h"
 
 namespace b200 {
@@ -618,6 +619,58 @@ int ggml_b200_get_rows_q4_0(const ggml_b200_weight * w, const int32_t * ids_dev,
     if (h_bad) { set_error("get_rows: a row id is outside this shard [%lld,%lld)", (long long)w->row_lo, (long long)w->row_hi); return GGML_B200_ERR_ARG; }
     return GGML_B200_OK;
 }
+
+// ---- the element-wise neighbours of the op (elementwise.cuh) ----------------------------------------
+static int eltwise_check(const void * a, const void * y, int64_t n) {
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    if (!a || !y || n < 0) { set_error("bad element-wise arguments"); return GGML_B200_ERR_ARG; }
+    return GGML_B200_OK;
+}
+static unsigned eltwise_grid(int64_t n) {
+    const int64_t b = (n + 255) / 256;
+    return (unsigned)(b < 1 ? 1 : b > (int64_t)g.sm_count * 8 ? (int64_t)g.sm_count * 8 : b);
+}
+int ggml_b200_rms_norm_f32(const float * x_dev, float * y_dev, int64_t ncols, int64_t nrows, float eps) {
+    B200_API_LOCK;
+    int rc = eltwise_check(x_dev, y_dev, ncols);
+    if (rc) return rc;
+    if (nrows <= 0 || ncols == 0) return GGML_B200_OK;
+    if (ncols > INT32_MAX || nrows > INT32_MAX) { set_error("rms_norm: shape too large"); return GGML_B200_ERR_ARG; }
+    return launch_k(rms_norm_f32_kernel, dim3((unsigned)nrows), dim3(256), 0, x_dev, y_dev, (int)ncols, eps);
+}
+int ggml_b200_mul_f32(const float * a_dev, const float * b_dev, float * y_dev, int64_t n, int64_t nb) {
+    B200_API_LOCK;
+    int rc = eltwise_check(a_dev, y_dev, n);
+    if (rc) return rc;
+    if (!b_dev || nb <= 0 || n % nb) { set_error("mul: src1 must tile src0"); return GGML_B200_ERR_ARG; }
+    if (n == 0) return GGML_B200_OK;
+    return launch_k(eltwise_f32_kernel<0>, dim3(eltwise_grid(n)), dim3(256), 0, a_dev, b_dev, y_dev, (long long)n, (long long)nb);
+}
+int ggml_b200_add_f32(const float * a_dev, const float * b_dev, float * y_dev, int64_t n, int64_t nb) {
+    B200_API_LOCK;
+    int rc = eltwise_check(a_dev, y_dev, n);
+    if (rc) return rc;
+    if (!b_dev || nb <= 0 || n % nb) { set_error("add: src1 must tile src0"); return GGML_B200_ERR_ARG; }
+    if (n == 0) return GGML_B200_OK;
+    return launch_k(eltwise_f32_kernel<1>, dim3(eltwise_grid(n)), dim3(256), 0, a_dev, b_dev, y_dev, (long long)n, (long long)nb);
+}
+int ggml_b200_silu_f32(const float * x_dev, float * y_dev, int64_t n) {
+    B200_API_LOCK;
+    int rc = eltwise_check(x_dev, y_dev, n);
+    if (rc) return rc;
+    if (n == 0) return GGML_B200_OK;
+    return launch_k(eltwise_f32_kernel<2>, dim3(eltwise_grid(n)), dim3(256), 0, x_dev, (const float *)nullptr, y_dev, (long long)n, (long long)n);
+}
+int ggml_b200_silu_mul_f32(const float * x_dev, const float * b_dev, float * y_dev, int64_t n) {
+    B200_API_LOCK;
+    int rc = eltwise_check(x_dev, y_dev, n);
+    if (rc) return rc;
+    if (!b_dev) { set_error("silu_mul: null src1"); return GGML_B200_ERR_ARG; }
+    if (n == 0) return GGML_B200_OK;
+    return launch_k(eltwise_f32_kernel<3>, dim3(eltwise_grid(n)), dim3(256), 0, x_dev, b_dev, y_dev, (long long)n, (long long)n);
+}
+int ggml_b200_memcpy_h2d_async(void * d, const void * s, size_t n) { CK(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, g.stream)); return GGML_B200_OK; }
+int ggml_b200_memcpy_d2h_async(void * d, const void * s, size_t n) { CK(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, g.stream)); return GGML_B200_OK; }
 
 // ---- kernel 1 ---------------------------------------------------------------------------------
 int ggml_b200_quantize_q8_0(const float * x_dev, int64_t n, int64_t K, size_t nb11, void * blocks34_dev) {

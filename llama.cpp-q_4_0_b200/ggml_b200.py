@@ -107,6 +107,13 @@ def _load() -> C.CDLL:
         "ggml_b200_memcpy_h2d": (C.c_int, [_vp, _vp, _sz]),
         "ggml_b200_memcpy_d2h": (C.c_int, [_vp, _vp, _sz]),
         "ggml_b200_synchronize": (C.c_int, []),
+        "ggml_b200_memcpy_h2d_async": (C.c_int, [_vp, _vp, _sz]),
+        "ggml_b200_memcpy_d2h_async": (C.c_int, [_vp, _vp, _sz]),
+        "ggml_b200_rms_norm_f32": (C.c_int, [_vp, _vp, _i64, _i64, C.c_float]),
+        "ggml_b200_mul_f32": (C.c_int, [_vp, _vp, _vp, _i64, _i64]),
+        "ggml_b200_add_f32": (C.c_int, [_vp, _vp, _vp, _i64, _i64]),
+        "ggml_b200_silu_f32": (C.c_int, [_vp, _vp, _i64]),
+        "ggml_b200_silu_mul_f32": (C.c_int, [_vp, _vp, _vp, _i64]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)

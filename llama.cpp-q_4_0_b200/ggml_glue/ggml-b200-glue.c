@@ -11,12 +11,16 @@
  * ggml.c / llama.cpp built with -DGGML_USE_CUBLAS links against this object + libggml_b200.so
  * instead of ggml-cuda.o: zero source changes on the reference side.
  *
- * Scope: only GGML_OP_MUL_MAT with a GGML_TYPE_Q4_0 src0 that was uploaded through
- * ggml_cuda_transform_tensor and an F32 src1 is taken; every other node returns false from the hook
- * and runs on the reference's CPU code unchanged.  Tensors of any other type that a loader tags
- * GGML_BACKEND_GPU are kept on the host (copied, re-tagged GGML_BACKEND_CPU) so real model graphs
- * keep working.  There is no CPU fallback for the taken op: a failing device call prints and aborts
- * like the reference's CUDA_CHECK (ggml-cuda.cu:22-30).
+ * Scope: GGML_OP_MUL_MAT with a GGML_TYPE_Q4_0 src0 that was uploaded through
+ * ggml_cuda_transform_tensor and an F32 src1, plus the element-wise nodes that sit between consecutive Q4_0 matmuls of
+ * a LLaMA layer (RMS_NORM, MUL by the norm weights, ADD of the residual, SILU) when the graph builder asked for their
+ * results to live on the device (ggml_cuda_assign_buffers, llama.cpp:1307-1313): activations then stay in HBM from
+ * one matmul to the next, launches are asynchronous and the stream is synchronised once per CPU node instead of once
+ * per offloaded node.  Every other node returns false from the hook and runs on the reference's CPU code unchanged;
+ * a device-resident tensor it reads (directly or through reshape/view/permute/transpose) is copied to its host
+ * buffer first.  Q4_0 matrices and F32 vectors (norm weights) tagged GGML_BACKEND_GPU are uploaded; tensors of other
+ * types are kept on the host (copied, re-tagged GGML_BACKEND_CPU) so real model graphs keep working.  There is no CPU
+ * fallback for a taken op: a failing device call prints and aborts like the reference's CUDA_CHECK (ggml-cuda.cu:22-30).
  *
  * Built only where the reference headers exist (ggml_glue/Makefile, -I$(REF)); plain C.
  */
@@ -31,6 +35,8 @@
 
 #define B200_MAGIC_WEIGHT ((void *)(uintptr_t)0xB200B200u)   /* extra->data_device[1]: data_device[0] is a ggml_b200_weight */
 #define B200_MAGIC_HOST   ((void *)(uintptr_t)0xB200C0DEu)   /* extra->data_device[1]: data_device[0] is our host copy */
+#define B200_MAGIC_DEVF32 ((void *)(uintptr_t)0xB200F320u)   /* ... data_device[0] = device copy of an F32 weight, [2] = our host copy (tensor->data) */
+#define B200_MAGIC_ACT    ((void *)(uintptr_t)0xB200AC70u)   /* ... data_device[0] = device buffer of an activation, [2] != NULL: tensor->data holds the same values */
 
 static int    g_ready = 0;          /* ggml_b200_init succeeded */
 static int    g_main_device = 0;
@@ -67,14 +73,104 @@ void ggml_cuda_set_main_device(int main_device) {
 
 /* ggml_cuda_set_tensor_split (ggml-cuda.cu:1863-1882): the row split is fixed by (rank, world) of the NCCL
  * communicator (ggml_b200_shard_rows); fractions from the command line are not used */
-void ggml_cuda_set_tensor_split(const float * tensor_split) { (void)tensor_split; }
-void ggml_cuda_set_scratch_size(size_t scratch_size) { (void)scratch_size; }   /* activations stay on the host */
-void ggml_cuda_free_scratch(void) {}
+void ggml_cuda_set_tensor_split(const float * tensor_split) {
+    static int warned = 0;
+    if (tensor_split != NULL && !warned) {
+        for (int i = 0; i < GGML_CUDA_MAX_DEVICES; i++) if (tensor_split[i] != 0.0f && !warned) {
+            fprintf(stderr, "ggml-b200: tensor_split is ignored: rows are split evenly over the ranks of the communicator (ggml_b200_shard_rows)\n");
+            warned = 1;
+        }
+    }
+}
 
-/* activations are not kept device-resident by this back-end: leave the tensor on the CPU (ggml-cuda.cu:2830-2935) */
-void ggml_cuda_assign_buffers(struct ggml_tensor * tensor) { (void)tensor; }
-void ggml_cuda_assign_buffers_no_scratch(struct ggml_tensor * tensor) { (void)tensor; }
-void ggml_cuda_assign_buffers_force_inplace(struct ggml_tensor * tensor) { (void)tensor; }
+/* ---- device-resident activations (ggml-cuda.cu:2830-2935) -------------------------------------------------------
+ * ggml_cuda_set_scratch_size gives the size of a VRAM ring (llama.cpp:1115-1116: n_batch MB); ggml_cuda_assign_buffers,
+ * called by the graph builder on the RESULT tensor of a node, takes the next slice of the ring and tags the tensor
+ * GGML_BACKEND_GPU.  Only nodes this back-end computes are taken (the others stay on the CPU and read device-resident
+ * sources through ensure_host below): RMS_NORM, MUL, ADD, SILU on contiguous F32 and MUL_MAT with an uploaded Q4_0
+ * weight.  The extra structs come from a ring too (the reference leaks one per call). */
+static size_t g_scratch_size = 0, g_scratch_off = 0;
+static char * g_scratch = NULL;
+#define B200_EXTRA_POOL 16384
+static struct ggml_tensor_extra_gpu g_extra_pool[B200_EXTRA_POOL];
+static size_t g_extra_next = 0;
+static int    g_pending = 0;        /* asynchronous copies in flight that a CPU node must wait for */
+
+void ggml_cuda_set_scratch_size(size_t scratch_size) {
+    if (scratch_size != g_scratch_size && g_scratch != NULL) { ggml_b200_synchronize(); ggml_b200_dev_free(g_scratch); g_scratch = NULL; }
+    g_scratch_size = scratch_size;
+    g_scratch_off = 0;
+}
+void ggml_cuda_free_scratch(void) {
+    if (g_scratch == NULL) return;
+    ggml_b200_synchronize();
+    ggml_b200_dev_free(g_scratch);
+    g_scratch = NULL;
+}
+
+static ggml_b200_weight * weight_of(const struct ggml_tensor * t);
+static int is_act(const struct ggml_tensor * t) {     /* (by the extra alone: the backend tag flips to CPU once the host buffer holds the values too) */
+    return t != NULL && t->extra != NULL && ((const struct ggml_tensor_extra_gpu *)t->extra)->data_device[1] == B200_MAGIC_ACT;
+}
+static int is_devf32(const struct ggml_tensor * t) {
+    return t != NULL && t->extra != NULL && ((const struct ggml_tensor_extra_gpu *)t->extra)->data_device[1] == B200_MAGIC_DEVF32;
+}
+static float * dev_ptr(const struct ggml_tensor * t) { return (float *)((struct ggml_tensor_extra_gpu *)t->extra)->data_device[0]; }
+static int f32_contig(const struct ggml_tensor * t) { return t != NULL && t->type == GGML_TYPE_F32 && ggml_is_contiguous(t); }
+
+/* can this node run on the device?  (shape rules of the kernels in csrc/elementwise.cuh and of the op) */
+static int node_supported(const struct ggml_tensor * t) {
+    if (!g_ready || t == NULL || !f32_contig(t)) return 0;
+    switch (t->op) {
+        case GGML_OP_RMS_NORM:
+        case GGML_OP_SILU:
+            return f32_contig(t->src0);
+        case GGML_OP_MUL:
+        case GGML_OP_ADD:
+            /* src1 = src0's shape, or one row repeated over src0's rows (norm weights: ggml.c:9199-9210) */
+            return f32_contig(t->src0) && f32_contig(t->src1) && t->src0->ne[0] == t->src1->ne[0] &&
+                   (ggml_nelements(t->src1) == ggml_nelements(t->src0) || ggml_nelements(t->src1) == t->src1->ne[0]);
+        case GGML_OP_MUL_MAT:
+            return weight_of(t->src0) != NULL && t->src0->type == GGML_TYPE_Q4_0 && f32_contig(t->src1) &&
+                   t->src0->ne[2] == 1 && t->src0->ne[3] == 1 && t->src1->ne[2] == 1 && t->src1->ne[3] == 1 && t->src0->ne[0] % 64 == 0;
+        default:
+            return 0;
+    }
+}
+
+static void assign_buffers_impl(struct ggml_tensor * tensor, int scratch, int force_inplace) {
+    if (!g_ready || tensor == NULL) return;
+    if (scratch && g_scratch_size == 0) return;                 /* llama.cpp low_vram: ggml_cuda_set_scratch_size(0) */
+    if (!node_supported(tensor)) return;                        /* stays on the CPU */
+    const size_t size = (ggml_nbytes(tensor) + 255) & ~(size_t)255;
+    struct ggml_tensor_extra_gpu * extra = &g_extra_pool[g_extra_next++ % B200_EXTRA_POOL];
+    memset(extra, 0, sizeof(*extra));
+    const int inplace = force_inplace || (tensor->src0 != NULL && tensor->src0->data == tensor->data);
+    if (inplace && is_act(tensor->src0)) {
+        extra->data_device[0] = dev_ptr(tensor->src0);          /* an _inplace node writes its src0's buffer */
+    } else if (scratch) {
+        GGML_ASSERT(size <= g_scratch_size);
+        if (g_scratch == NULL) {
+            g_scratch = (char *)ggml_b200_dev_malloc(g_scratch_size);
+            if (g_scratch == NULL) { fprintf(stderr, "ggml-b200: %s\n", ggml_b200_last_error()); exit(1); }
+            g_scratch_off = 0;
+        }
+        if (g_scratch_off + size > g_scratch_size) g_scratch_off = 0;     /* ring: older tensors are dead by now (as in the reference) */
+        extra->data_device[0] = g_scratch + g_scratch_off;
+        g_scratch_off += size;
+    } else {
+        void * p = ggml_b200_dev_malloc(size);                  /* (never freed by the reference either: ggml-cuda.cu:2878-2882) */
+        if (p == NULL) { fprintf(stderr, "ggml-b200: %s\n", ggml_b200_last_error()); exit(1); }
+        extra->data_device[0] = p;
+    }
+    extra->data_device[1] = B200_MAGIC_ACT;
+    extra->data_device[2] = NULL;                               /* the host buffer does not hold the values */
+    tensor->backend = GGML_BACKEND_GPU;
+    tensor->extra = extra;
+}
+void ggml_cuda_assign_buffers(struct ggml_tensor * tensor) { assign_buffers_impl(tensor, 1, 0); }
+void ggml_cuda_assign_buffers_no_scratch(struct ggml_tensor * tensor) { assign_buffers_impl(tensor, 0, 0); }
+void ggml_cuda_assign_buffers_force_inplace(struct ggml_tensor * tensor) { assign_buffers_impl(tensor, 0, 1); }
 
 /* pinned host memory (ggml-cuda.cu:1884-1905); NULL makes the caller fall back to malloc */
 void * ggml_cuda_host_malloc(size_t size) { return g_ready ? ggml_b200_host_malloc(size) : NULL; }
@@ -108,11 +204,25 @@ void ggml_cuda_transform_tensor(void * data, struct ggml_tensor * tensor) {
         tensor->extra = extra;
         return;
     }
-    /* not on this back-end's path: keep it for the CPU code */
     const size_t nbytes = ggml_nbytes(tensor);
     void * copy = malloc(nbytes ? nbytes : 1);
     GGML_ASSERT(copy != NULL);
     memcpy(copy, data, nbytes);
+    if (g_ready && tensor->type == GGML_TYPE_F32 && nbytes > 0 && nbytes <= ((size_t)1 << 24)) {
+        /* norm weights (llama.cpp:1048-1070 tags them with the layer's backend): a device copy for MUL nodes that run on
+         * the device, and the host copy stays readable for nodes that run on the CPU */
+        void * d = ggml_b200_dev_malloc(nbytes);
+        if (d == NULL) { fprintf(stderr, "ggml-b200: %s\n", ggml_b200_last_error()); exit(1); }
+        B200_CHECK(ggml_b200_memcpy_h2d(d, copy, nbytes));
+        extra->data_device[0] = d;
+        extra->data_device[1] = B200_MAGIC_DEVF32;
+        extra->data_device[2] = copy;
+        tensor->extra = extra;
+        tensor->data = copy;
+        tensor->backend = GGML_BACKEND_CPU;      /* nodes that run on the CPU may read it (ggml.c:15650-15651 asserts CPU sources) */
+        return;
+    }
+    /* not on this back-end's path: keep it for the CPU code */
     extra->data_device[0] = copy;
     extra->data_device[1] = B200_MAGIC_HOST;
     tensor->extra = extra;
@@ -126,6 +236,7 @@ void ggml_cuda_free_data(struct ggml_tensor * tensor) {
     struct ggml_tensor_extra_gpu * e = (struct ggml_tensor_extra_gpu *)tensor->extra;
     if (e->data_device[1] == B200_MAGIC_WEIGHT) ggml_b200_free_weight((ggml_b200_weight *)e->data_device[0]);
     else if (e->data_device[1] == B200_MAGIC_HOST) { free(e->data_device[0]); if (tensor->data == e->data_device[0]) tensor->data = NULL; }
+    else if (e->data_device[1] == B200_MAGIC_DEVF32) { ggml_b200_dev_free(e->data_device[0]); free(e->data_device[2]); if (tensor->data == e->data_device[2]) tensor->data = NULL; }
     else return;   /* not ours */
     free(e);
     tensor->extra = NULL;
@@ -138,7 +249,7 @@ bool ggml_cuda_can_mul_mat(const struct ggml_tensor * src0, const struct ggml_te
     /* 2-D only (every Q4_0 weight of the models is; a batched src1 falls through to the CPU code instead of aborting),
      * K a multiple of 64 (ggml.c:2343-2344) */
     return g_ready && weight_of(src0) != NULL && src0->type == GGML_TYPE_Q4_0 && src1->type == GGML_TYPE_F32 &&
-           dst->type == GGML_TYPE_F32 && src1->backend == GGML_BACKEND_CPU && dst->backend == GGML_BACKEND_CPU &&
+           dst->type == GGML_TYPE_F32 && (src1->backend == GGML_BACKEND_CPU || is_act(src1)) && (dst->backend == GGML_BACKEND_CPU || is_act(dst)) &&
            src0->ne[2] == 1 && src0->ne[3] == 1 && src1->ne[2] == 1 && src1->ne[3] == 1 && src0->ne[0] % 64 == 0;
 }
 
@@ -188,15 +299,125 @@ void ggml_cuda_mul(const struct ggml_tensor * src0, const struct ggml_tensor * s
     abort();
 }
 
+/* ---- nodes on the device ----------------------------------------------------------------------------------------- */
+static float *g_stage_in[2] = {NULL, NULL}, *g_stage_out = NULL;
+static size_t g_stage_in_cap[2] = {0, 0}, g_stage_out_cap = 0;
+
+/* the values of `t` on the device: its own buffer, the device copy of a norm weight, or a staged upload of its host data */
+static const float * src_on_device(const struct ggml_tensor * t, int slot) {
+    if (is_act(t) || is_devf32(t)) return dev_ptr(t);
+    const size_t nbytes = ggml_nbytes(t);
+    if (nbytes > g_stage_in_cap[slot]) ggml_b200_synchronize();      /* the old block may still be read by a queued kernel */
+    ensure_dev(&g_stage_in[slot], &g_stage_in_cap[slot], nbytes);
+    B200_CHECK(ggml_b200_memcpy_h2d_async(g_stage_in[slot], t->data, nbytes));
+    g_pending = 1;                                                   /* the host buffer must not change before the copy has run */
+    return g_stage_in[slot];
+}
+static float * dst_on_device(struct ggml_tensor * t) {
+    if (is_act(t)) {
+        struct ggml_tensor_extra_gpu * e = (struct ggml_tensor_extra_gpu *)t->extra;
+        e->data_device[2] = NULL;                                    /* rewritten: the host buffer is stale */
+        return (float *)e->data_device[0];
+    }
+    const size_t nbytes = ggml_nbytes(t);
+    if (nbytes > g_stage_out_cap) ggml_b200_synchronize();
+    ensure_dev(&g_stage_out, &g_stage_out_cap, nbytes);
+    return g_stage_out;
+}
+/* a result whose tensor lives on the host: copy it back; the wait happens at the next node that runs on the CPU */
+static void dst_to_host(struct ggml_tensor * t, const float * y_dev) {
+    if (is_act(t)) return;
+    B200_CHECK(ggml_b200_memcpy_d2h_async(t->data, y_dev, ggml_nbytes(t)));
+    g_pending = 1;
+}
+static void wait_pending(void) {
+    if (g_pending) { B200_CHECK(ggml_b200_synchronize()); g_pending = 0; }
+}
+/* a node that runs on the CPU reads `t`: if its values live on the device only (t itself, or the tensor a chain of
+ * reshape / view / permute / transpose nodes looks into), bring them to the host buffer and tag the tensor CPU */
+static void ensure_host(struct ggml_tensor * t) {
+    for (int depth = 0; t != NULL && depth < 8; depth++) {
+        if (is_act(t)) {
+            struct ggml_tensor_extra_gpu * e = (struct ggml_tensor_extra_gpu *)t->extra;
+            if (e->data_device[2] == NULL) {
+                B200_CHECK(ggml_b200_memcpy_d2h_async(t->data, e->data_device[0], ggml_nbytes(t)));
+                g_pending = 1;
+                e->data_device[2] = t->data;
+            }
+            t->backend = GGML_BACKEND_CPU;
+            return;
+        }
+        if (t->op != GGML_OP_RESHAPE && t->op != GGML_OP_VIEW && t->op != GGML_OP_PERMUTE && t->op != GGML_OP_TRANSPOSE) return;
+        t = t->src0;
+    }
+}
+
+static void device_node(struct ggml_tensor * t) {
+    const int64_t n = ggml_nelements(t);
+    switch (t->op) {
+        case GGML_OP_MUL_MAT: {
+            ggml_b200_weight * w = weight_of(t->src0);
+            const int64_t K = t->src0->ne[0], M = t->src0->ne[1], cols = t->src1->ne[1];
+            GGML_ASSERT(t->src1->ne[0] == K && t->ne[0] == M && t->ne[1] == cols);
+            const float * x = src_on_device(t->src1, 0);
+            float * y = dst_on_device(t);
+            if (ggml_b200_comm_world() > 1 && ggml_b200_weight_rows(w) != M)
+                B200_CHECK(ggml_b200_mul_mat_q4_0_sharded(w, x, cols, (size_t)K * sizeof(float), y, (size_t)M * sizeof(float)));
+            else
+                B200_CHECK(ggml_b200_mul_mat_q4_0(w, x, cols, (size_t)K * sizeof(float), y, (size_t)M * sizeof(float)));
+            dst_to_host(t, y);
+        } break;
+        case GGML_OP_RMS_NORM: {
+            const float * x = src_on_device(t->src0, 0);
+            float * y = dst_on_device(t);
+            B200_CHECK(ggml_b200_rms_norm_f32(x, y, t->src0->ne[0], ggml_nrows(t->src0), 1e-6f));     /* eps: ggml.c:10417 */
+            dst_to_host(t, y);
+        } break;
+        case GGML_OP_MUL:
+        case GGML_OP_ADD: {
+            const float * a = src_on_device(t->src0, 0);
+            const float * b = src_on_device(t->src1, 1);
+            float * y = dst_on_device(t);
+            if (t->op == GGML_OP_MUL) B200_CHECK(ggml_b200_mul_f32(a, b, y, n, ggml_nelements(t->src1)));
+            else                      B200_CHECK(ggml_b200_add_f32(a, b, y, n, ggml_nelements(t->src1)));
+            dst_to_host(t, y);
+        } break;
+        case GGML_OP_SILU: {
+            const float * x = src_on_device(t->src0, 0);
+            float * y = dst_on_device(t);
+            B200_CHECK(ggml_b200_silu_f32(x, y, n));
+            dst_to_host(t, y);
+        } break;
+        default:
+            GGML_ASSERT(!"device_node: unsupported op");
+    }
+}
+
 /* ggml_cuda_compute_forward (ggml-cuda.cu:2966-3082): the pre-hook of ggml_compute_forward (ggml.c:15645-15649).
- * Called by every worker thread for every phase; exactly one thread launches, in COMPUTE
- * (ggml-cuda.cu:3013-3020).  Returns true iff the CPU code must be skipped. */
+ * Called by every worker thread for every phase; the INIT phase always runs first and on one thread
+ * (ggml.c:17114-17117), exactly one thread launches, in COMPUTE (ggml-cuda.cu:3013-3020).  Returns true iff the CPU
+ * code must be skipped.  A node runs on the device when this back-end has a kernel for it AND its result or one of its
+ * sources lives there; a Q4_0 mul_mat with everything on the host takes the one-launch host path. */
 bool ggml_cuda_compute_forward(struct ggml_compute_params * params, struct ggml_tensor * tensor) {
-    if (tensor->op != GGML_OP_MUL_MAT || !ggml_cuda_can_mul_mat(tensor->src0, tensor->src1, tensor)) return false;
-    if (params->ith != 0) return true;
-    if (params->type == GGML_TASK_INIT || params->type == GGML_TASK_FINALIZE) return true;
-    ggml_cuda_mul_mat(tensor->src0, tensor->src1, tensor, params->wdata, params->wsize);
-    return true;
+    if (!g_ready) return false;
+    const int on_device = is_act(tensor) || is_act(tensor->src0) || is_act(tensor->src1);
+    const int host_mul_mat = tensor->op == GGML_OP_MUL_MAT && !on_device && ggml_cuda_can_mul_mat(tensor->src0, tensor->src1, tensor);
+    if ((on_device && node_supported(tensor)) || host_mul_mat) {
+        if (params->ith != 0) return true;
+        if (params->type == GGML_TASK_INIT || params->type == GGML_TASK_FINALIZE) return true;
+        if (host_mul_mat) { wait_pending(); ggml_cuda_mul_mat(tensor->src0, tensor->src1, tensor, params->wdata, params->wsize); }
+        else device_node(tensor);
+        return true;
+    }
+    /* the reference's CPU code runs this node: before any thread starts on it (INIT), bring device-resident sources home
+     * and wait for the copies in flight */
+    if (params->ith == 0 && params->type == GGML_TASK_INIT) {
+        ensure_host(tensor->src0);
+        ensure_host(tensor->src1);
+        for (int i = 0; i < GGML_MAX_OPT; i++) ensure_host(tensor->opt[i]);
+        wait_pending();
+    }
+    return false;
 }
 
 /* spelled-out aliases under this back-end's own name */

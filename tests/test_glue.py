@@ -176,3 +176,60 @@ def test_shallow_llama_offloaded_to_b200_is_tight(tmp_path):
         err = float(np.abs(cpu[i] - gpu[i]).max()) / float(np.abs(cpu[i]).max())
         assert err <= 1e-3, f"eval {i}: max|dlogit|/max|logit| = {err:.3e}"
         assert int(cpu[i].argmax()) == int(gpu[i].argmax())
+
+
+# ---------------------------------------------------------------------------- device-resident activations
+def _layer_lib():
+    G = _glue()
+    G.glue_model_create.restype = C.c_void_p
+    G.glue_model_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint]
+    G.glue_model_eval.restype = C.c_double
+    G.glue_model_eval.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]
+    G.glue_model_free.restype = None
+    G.glue_model_free.argtypes = [C.c_void_p]
+    return G
+
+
+def _layer_logits(G, dims, offload, device_acts, x, threads=4):
+    n_layer, n_embd, n_ff, n_vocab = dims
+    m = G.glue_model_create(n_layer, n_embd, n_ff, n_vocab, offload, 7)
+    assert m
+    logits = np.zeros(n_vocab, np.float32)
+    xs = np.ascontiguousarray(x, dtype=np.float32)
+    t = G.glue_model_eval(m, xs.ctypes.data_as(C.c_void_p), logits.ctypes.data_as(C.c_void_p), threads, 2, device_acts)
+    assert t > 0
+    G.glue_model_free(m)
+    return logits
+
+
+def test_layer_graph_driver_on_the_cpu_is_deterministic():
+    """tests/glue/layer_driver.c (a LLaMA decode graph built with the reference's API) on the plain CPU path."""
+    G = _layer_lib()
+    x = np.random.default_rng(3).standard_normal(256).astype(np.float32)
+    a = _layer_logits(G, (3, 256, 704, 512), 0, 0, x)
+    b = _layer_logits(G, (3, 256, 704, 512), 0, 0, x, threads=1)
+    assert np.isfinite(a).all() and float(np.abs(a).max()) > 1e-3
+    assert np.array_equal(a, b)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dims", [(3, 256, 704, 512), (6, 1024, 2752, 4000)])
+def test_device_resident_activations_through_the_seam(b200, dims):
+    """ggml_cuda_assign_buffers is live: rms_norm / mul / add / silu and the Q4_0 matmuls of the offloaded layers run
+    on the device with their results kept in HBM (launches counted), q/k/v come back for the CPU node, wo's input goes
+    up.  Logits vs the same graph on the reference CPU path, and vs the seam with host-resident activations."""
+    G = _layer_lib()
+    x = np.random.default_rng(4).standard_normal(dims[1]).astype(np.float32)
+    cpu = _layer_logits(G, dims, 0, 0, x)
+    c0 = b200.launch_count()
+    host_acts = _layer_logits(G, dims, 1, 0, x)
+    c1 = b200.launch_count()
+    dev_acts = _layer_logits(G, dims, 1, 1, x)
+    c2 = b200.launch_count()
+    n_layer = dims[0]
+    assert c2 - c1 >= (c1 - c0) + 2 * 8 * n_layer          # two evals x >= 8 element-wise kernels per layer more than the matmul-only path
+    scale = float(np.abs(cpu).max())
+    for got in (host_acts, dev_acts):
+        err = float(np.abs(got - cpu).max()) / scale
+        assert err <= 2e-3, f"max|dlogit|/max|logit| = {err:.3e}"
+        assert int(got.argmax()) == int(cpu.argmax())
