@@ -156,7 +156,19 @@ int          ggml_b200_rms_norm_f32(const float * x_dev, float * y_dev, int64_t 
 int          ggml_b200_mul_f32(const float * a_dev, const float * b_dev, float * y_dev, int64_t n, int64_t nb);
 int          ggml_b200_add_f32(const float * a_dev, const float * b_dev, float * y_dev, int64_t n, int64_t nb);
 int          ggml_b200_silu_f32(const float * x_dev, float * y_dev, int64_t n);
-int          ggml_b200_silu_mul_f32(const float * x_dev, const float * b_dev, float * y_dev, int64_t n);
+int          ggml_b200_silu_mul_f32(const float * x_dev, const float * b_dev, float * y_dev, int64_t n,
+                                    float * silu_dev /* NULL, or also receives silu(x) */);
+/* rms_norm and the MUL by the norm weights that follows it in every layer, one kernel; both results are written */
+int          ggml_b200_rms_norm_mul_f32(const float * x_dev, float * y_norm_dev, const float * w_dev, float * y_dev,
+                                        int64_t ncols, int64_t nrows, int64_t nw, float eps);
+/* A sequence of this library's asynchronous calls (ops, element-wise kernels, async copies) recorded once and submitted
+ * as one CUDA graph launch afterwards: begin ... calls ... end -> handle; launch runs it on the current stream.  The
+ * glue uses it for the device nodes between two CPU nodes of a ggml graph (same pointers every eval).  No allocation
+ * may happen between begin and end. */
+int          ggml_b200_graph_begin(void);
+int          ggml_b200_graph_end(void ** exec_out);
+int          ggml_b200_graph_launch(void * exec);
+void         ggml_b200_graph_free(void * exec);
 
 /* ---- a list of n = 1 ops in ONE launch ----------------------------------------
  * replaces, for the run of GGML_OP_MUL_MAT nodes of a decode step, the per-node loop of

@@ -11,8 +11,11 @@
 
 namespace b200 {
 
-// one CTA per row; sum of squares in double like the reference (ggml_float), mean = (float)(sum / ncols)
-__global__ void __launch_bounds__(256) rms_norm_f32_kernel(const float * __restrict__ x, float * __restrict__ y, int ncols, float eps) {
+// one CTA per row; sum of squares in double like the reference (ggml_float), mean = (float)(sum / ncols).
+// w != nullptr: the MUL by the norm weights that follows in every LLaMA layer fused in (y2 = y * w[i % nw]); both
+// results are written, so whoever else reads the norm's own result still finds it.
+__global__ void __launch_bounds__(256) rms_norm_f32_kernel(const float * __restrict__ x, float * __restrict__ y, int ncols, float eps,
+                                                           const float * __restrict__ w, float * __restrict__ y2, int nw) {
     pdl_wait();
     pdl_launch_dependents();
     const float * xr = x + (size_t)blockIdx.x * ncols;
@@ -32,13 +35,18 @@ __global__ void __launch_bounds__(256) rms_norm_f32_kernel(const float * __restr
     }
     __syncthreads();
     const float scale = s_scale;
-    for (int i = threadIdx.x; i < ncols; i += blockDim.x) yr[i] = __fmul_rn(__ldcg(xr + i), scale);
+    for (int i = threadIdx.x; i < ncols; i += blockDim.x) {
+        const float v = __fmul_rn(__ldcg(xr + i), scale);
+        yr[i] = v;
+        if (w != nullptr) y2[(size_t)blockIdx.x * ncols + i] = __fmul_rn(v, __ldcg(w + (((size_t)blockIdx.x * ncols + i) % nw)));
+    }
 }
 
-// OP 0: y = a * b[i % nb]   1: y = a + b[i % nb]   2: y = silu(a) (fp16 table semantics)   3: y = silu(a) * b (fused pair)
+// OP 0: y = a * b[i % nb]   1: y = a + b[i % nb]   2: y = silu(a) (fp16 table semantics)   3: y = silu(a) * b (fused pair;
+// s != nullptr also receives silu(a))
 template <int OP>
 __global__ void __launch_bounds__(256) eltwise_f32_kernel(const float * __restrict__ a, const float * __restrict__ b, float * __restrict__ y,
-                                                          long long n, long long nb) {
+                                                          long long n, long long nb, float * __restrict__ s = nullptr) {
     pdl_wait();
     pdl_launch_dependents();
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
@@ -50,6 +58,7 @@ __global__ void __launch_bounds__(256) eltwise_f32_kernel(const float * __restri
             const float xf = __half2float(__float2half_rn(av));
             const float sv = __half2float(__float2half_rn(__fdiv_rn(xf, 1.0f + expf(-xf))));
             r = OP == 2 ? sv : __fmul_rn(sv, __ldcg(b + i));
+            if (OP == 3 && s != nullptr) s[i] = sv;
         }
         y[i] = r;
     }

@@ -636,7 +636,16 @@ int ggml_b200_rms_norm_f32(const float * x_dev, float * y_dev, int64_t ncols, in
     if (rc) return rc;
     if (nrows <= 0 || ncols == 0) return GGML_B200_OK;
     if (ncols > INT32_MAX || nrows > INT32_MAX) { set_error("rms_norm: shape too large"); return GGML_B200_ERR_ARG; }
-    return launch_k(rms_norm_f32_kernel, dim3((unsigned)nrows), dim3(256), 0, x_dev, y_dev, (int)ncols, eps);
+    return launch_k(rms_norm_f32_kernel, dim3((unsigned)nrows), dim3(256), 0, x_dev, y_dev, (int)ncols, eps, (const float *)nullptr, (float *)nullptr, 1);
+}
+int ggml_b200_rms_norm_mul_f32(const float * x_dev, float * y_norm_dev, const float * w_dev, float * y_dev, int64_t ncols, int64_t nrows, int64_t nw, float eps) {
+    B200_API_LOCK;
+    int rc = eltwise_check(x_dev, y_dev, ncols);
+    if (rc) return rc;
+    if (!y_norm_dev || !w_dev || nw <= 0 || (ncols * nrows) % nw) { set_error("rms_norm_mul: bad arguments"); return GGML_B200_ERR_ARG; }
+    if (nrows <= 0 || ncols == 0) return GGML_B200_OK;
+    if (ncols > INT32_MAX || nrows > INT32_MAX || nw > INT32_MAX) { set_error("rms_norm_mul: shape too large"); return GGML_B200_ERR_ARG; }
+    return launch_k(rms_norm_f32_kernel, dim3((unsigned)nrows), dim3(256), 0, x_dev, y_norm_dev, (int)ncols, eps, w_dev, y_dev, (int)nw);
 }
 int ggml_b200_mul_f32(const float * a_dev, const float * b_dev, float * y_dev, int64_t n, int64_t nb) {
     B200_API_LOCK;
@@ -644,7 +653,7 @@ int ggml_b200_mul_f32(const float * a_dev, const float * b_dev, float * y_dev, i
     if (rc) return rc;
     if (!b_dev || nb <= 0 || n % nb) { set_error("mul: src1 must tile src0"); return GGML_B200_ERR_ARG; }
     if (n == 0) return GGML_B200_OK;
-    return launch_k(eltwise_f32_kernel<0>, dim3(eltwise_grid(n)), dim3(256), 0, a_dev, b_dev, y_dev, (long long)n, (long long)nb);
+    return launch_k(eltwise_f32_kernel<0>, dim3(eltwise_grid(n)), dim3(256), 0, a_dev, b_dev, y_dev, (long long)n, (long long)nb, (float *)nullptr);
 }
 int ggml_b200_add_f32(const float * a_dev, const float * b_dev, float * y_dev, int64_t n, int64_t nb) {
     B200_API_LOCK;
@@ -652,22 +661,61 @@ int ggml_b200_add_f32(const float * a_dev, const float * b_dev, float * y_dev, i
     if (rc) return rc;
     if (!b_dev || nb <= 0 || n % nb) { set_error("add: src1 must tile src0"); return GGML_B200_ERR_ARG; }
     if (n == 0) return GGML_B200_OK;
-    return launch_k(eltwise_f32_kernel<1>, dim3(eltwise_grid(n)), dim3(256), 0, a_dev, b_dev, y_dev, (long long)n, (long long)nb);
+    return launch_k(eltwise_f32_kernel<1>, dim3(eltwise_grid(n)), dim3(256), 0, a_dev, b_dev, y_dev, (long long)n, (long long)nb, (float *)nullptr);
 }
 int ggml_b200_silu_f32(const float * x_dev, float * y_dev, int64_t n) {
     B200_API_LOCK;
     int rc = eltwise_check(x_dev, y_dev, n);
     if (rc) return rc;
     if (n == 0) return GGML_B200_OK;
-    return launch_k(eltwise_f32_kernel<2>, dim3(eltwise_grid(n)), dim3(256), 0, x_dev, (const float *)nullptr, y_dev, (long long)n, (long long)n);
+    return launch_k(eltwise_f32_kernel<2>, dim3(eltwise_grid(n)), dim3(256), 0, x_dev, (const float *)nullptr, y_dev, (long long)n, (long long)n, (float *)nullptr);
 }
-int ggml_b200_silu_mul_f32(const float * x_dev, const float * b_dev, float * y_dev, int64_t n) {
+int ggml_b200_silu_mul_f32(const float * x_dev, const float * b_dev, float * y_dev, int64_t n, float * silu_dev) {
     B200_API_LOCK;
     int rc = eltwise_check(x_dev, y_dev, n);
     if (rc) return rc;
     if (!b_dev) { set_error("silu_mul: null src1"); return GGML_B200_ERR_ARG; }
     if (n == 0) return GGML_B200_OK;
-    return launch_k(eltwise_f32_kernel<3>, dim3(eltwise_grid(n)), dim3(256), 0, x_dev, b_dev, y_dev, (long long)n, (long long)n);
+    return launch_k(eltwise_f32_kernel<3>, dim3(eltwise_grid(n)), dim3(256), 0, x_dev, b_dev, y_dev, (long long)n, (long long)n, silu_dev);
+}
+
+// ---- a recorded sequence of this library's launches and copies as ONE submission (the glue replays the device nodes
+// between two CPU nodes of a ggml graph this way: the host then pays one call instead of one per node) -------------
+struct GraphExec { cudaGraphExec_t exec; uint64_t kernels; };
+static uint64_t g_capture_launches0 = 0;
+int ggml_b200_graph_begin(void) {
+    B200_API_LOCK;
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    g_capture_launches0 = g.launches;
+    CK(cudaStreamBeginCapture(g.stream, cudaStreamCaptureModeThreadLocal));
+    return GGML_B200_OK;
+}
+int ggml_b200_graph_end(void ** exec_out) {
+    B200_API_LOCK;
+    cudaGraph_t graph = nullptr;
+    CK(cudaStreamEndCapture(g.stream, &graph));
+    GraphExec * ge = new GraphExec();
+    ge->kernels = g.launches - g_capture_launches0;
+    g.launches = g_capture_launches0;                 /* counted when the sequence actually runs */
+    cudaError_t e = cudaGraphInstantiate(&ge->exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) { delete ge; return cuda_fail(e, "cudaGraphInstantiate", __FILE__, __LINE__); }
+    *exec_out = ge;
+    return GGML_B200_OK;
+}
+int ggml_b200_graph_launch(void * exec) {
+    B200_API_LOCK;
+    GraphExec * ge = (GraphExec *)exec;
+    if (!ge) { set_error("null graph"); return GGML_B200_ERR_ARG; }
+    CK(cudaGraphLaunch(ge->exec, g.stream));
+    g.launches += ge->kernels;
+    return GGML_B200_OK;
+}
+void ggml_b200_graph_free(void * exec) {
+    GraphExec * ge = (GraphExec *)exec;
+    if (!ge) return;
+    cudaGraphExecDestroy(ge->exec);
+    delete ge;
 }
 int ggml_b200_memcpy_h2d_async(void * d, const void * s, size_t n) { CK(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, g.stream)); return GGML_B200_OK; }
 int ggml_b200_memcpy_d2h_async(void * d, const void * s, size_t n) { CK(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, g.stream)); return GGML_B200_OK; }

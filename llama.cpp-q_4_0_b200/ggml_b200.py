@@ -113,7 +113,12 @@ def _load() -> C.CDLL:
         "ggml_b200_mul_f32": (C.c_int, [_vp, _vp, _vp, _i64, _i64]),
         "ggml_b200_add_f32": (C.c_int, [_vp, _vp, _vp, _i64, _i64]),
         "ggml_b200_silu_f32": (C.c_int, [_vp, _vp, _i64]),
-        "ggml_b200_silu_mul_f32": (C.c_int, [_vp, _vp, _vp, _i64]),
+        "ggml_b200_silu_mul_f32": (C.c_int, [_vp, _vp, _vp, _i64, _vp]),
+        "ggml_b200_rms_norm_mul_f32": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, C.c_float]),
+        "ggml_b200_graph_begin": (C.c_int, []),
+        "ggml_b200_graph_end": (C.c_int, [C.POINTER(_vp)]),
+        "ggml_b200_graph_launch": (C.c_int, [_vp]),
+        "ggml_b200_graph_free": (None, [_vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)

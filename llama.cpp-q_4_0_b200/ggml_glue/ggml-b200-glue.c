@@ -138,8 +138,16 @@ static int node_supported(const struct ggml_tensor * t) {
     }
 }
 
+static int g_computed_since_assign = 0;   /* a node has run since the last ggml_cuda_assign_buffers: the next call belongs to a NEW graph */
 static void assign_buffers_impl(struct ggml_tensor * tensor, int scratch, int force_inplace) {
     if (!g_ready || tensor == NULL) return;
+    if (g_computed_since_assign) {
+        /* a graph builder assigns all its buffers before it computes: this is the first call of the next graph.  Start the
+         * ring over, so that a graph that repeats (every decode step) gets the same device addresses -- what lets the
+         * segments below be replayed as recorded CUDA graphs.  Tensors of the previous graph are dead. */
+        g_computed_since_assign = 0;
+        g_scratch_off = 0;
+    }
     if (scratch && g_scratch_size == 0) return;                 /* llama.cpp low_vram: ggml_cuda_set_scratch_size(0) */
     if (!node_supported(tensor)) return;                        /* stays on the CPU */
     const size_t size = (ggml_nbytes(tensor) + 255) & ~(size_t)255;
@@ -299,40 +307,137 @@ void ggml_cuda_mul(const struct ggml_tensor * src0, const struct ggml_tensor * s
     abort();
 }
 
-/* ---- nodes on the device ----------------------------------------------------------------------------------------- */
-static float *g_stage_in[2] = {NULL, NULL}, *g_stage_out = NULL;
-static size_t g_stage_in_cap[2] = {0, 0}, g_stage_out_cap = 0;
+/* ---- nodes on the device -----------------------------------------------------------------------------------------
+ * A node that runs on the device is first turned into a PLAN (which kernel, which pointers, which copies) and appended
+ * to the current SEGMENT: the device nodes between two CPU nodes of the graph.  A segment is submitted when a CPU node
+ * needs its results, or as soon as a node with a host-resident result has been recorded.  Submitting = the plans' calls
+ * in order; a segment that was seen before with the very same plans (llama.cpp's graphs and buffers repeat every
+ * eval: same scratch addresses, same compute buffer) is replayed as ONE CUDA graph launch instead, so the host pays one
+ * call per segment instead of one per node and copy.  Two peephole fusions at record time: RMS_NORM followed by the MUL
+ * that reads it, and SILU followed by the MUL that reads it, become one kernel each (both results are still written). */
+enum { PL_MUL_MAT, PL_RMS_NORM, PL_RMS_NORM_MUL, PL_MUL, PL_ADD, PL_SILU, PL_SILU_MUL };
+struct plan {
+    int kind;
+    ggml_b200_weight * w;
+    const float * a, * b;           /* device sources */
+    float * y, * y2;                /* device results (y2: the second result of a fused pair) */
+    int64_t n, nb, ncols, nrows, K, M;
+    const void * h2d_src[2]; void * h2d_dst[2]; size_t h2d_bytes[2];     /* staged uploads of host-resident sources */
+    void * d2h_dst; const void * d2h_src; size_t d2h_bytes;                /* result back to a host-resident tensor */
+    int sharded;
+};
+#define SEG_MAX 64
+#define SEG_CACHE 192
+static struct plan g_seg[SEG_MAX];
+static int g_seg_n = 0;
+static struct ggml_tensor * g_seg_last = NULL;       /* the tensor the last plan computes (for the peephole) */
+static struct { struct plan * plans; int n; void * exec; int seen; } g_cache[SEG_CACHE];
+static int g_cache_n = 0, g_cache_cursor = 0;
+static int g_use_graphs = -1;
 
+static float *g_stage_in[2] = {NULL, NULL}, *g_stage_out[4] = {NULL, NULL, NULL, NULL};
+static size_t g_stage_in_cap[2] = {0, 0}, g_stage_out_cap[4] = {0, 0, 0, 0};
+static int g_stage_out_next = 0;
+
+static void wait_pending(void) {
+    if (g_pending) { B200_CHECK(ggml_b200_synchronize()); g_pending = 0; }
+}
+
+static void issue(const struct plan * p) {
+    for (int i = 0; i < 2; i++) if (p->h2d_bytes[i]) B200_CHECK(ggml_b200_memcpy_h2d_async(p->h2d_dst[i], p->h2d_src[i], p->h2d_bytes[i]));
+    switch (p->kind) {
+        case PL_MUL_MAT:
+            if (p->sharded) B200_CHECK(ggml_b200_mul_mat_q4_0_sharded(p->w, p->a, p->n, (size_t)p->K * sizeof(float), p->y, (size_t)p->M * sizeof(float)));
+            else            B200_CHECK(ggml_b200_mul_mat_q4_0(p->w, p->a, p->n, (size_t)p->K * sizeof(float), p->y, (size_t)p->M * sizeof(float)));
+            break;
+        case PL_RMS_NORM:     B200_CHECK(ggml_b200_rms_norm_f32(p->a, p->y, p->ncols, p->nrows, 1e-6f)); break;      /* eps: ggml.c:10417 */
+        case PL_RMS_NORM_MUL: B200_CHECK(ggml_b200_rms_norm_mul_f32(p->a, p->y, p->b, p->y2, p->ncols, p->nrows, p->nb, 1e-6f)); break;
+        case PL_MUL:          B200_CHECK(ggml_b200_mul_f32(p->a, p->b, p->y, p->n, p->nb)); break;
+        case PL_ADD:          B200_CHECK(ggml_b200_add_f32(p->a, p->b, p->y, p->n, p->nb)); break;
+        case PL_SILU:         B200_CHECK(ggml_b200_silu_f32(p->a, p->y, p->n)); break;
+        case PL_SILU_MUL:     B200_CHECK(ggml_b200_silu_mul_f32(p->a, p->b, p->y2, p->n, p->y)); break;
+    }
+    if (p->d2h_bytes) B200_CHECK(ggml_b200_memcpy_d2h_async(p->d2h_dst, p->d2h_src, p->d2h_bytes));
+}
+
+/* submit the current segment (asynchronous; copies in it make g_pending) */
+static void flush_segment(void) {
+    if (g_seg_n == 0) return;
+    if (g_use_graphs < 0) { const char * e = getenv("GGML_B200_GLUE_GRAPHS"); g_use_graphs = e ? atoi(e) : 1; }
+    int hit = -1;
+    /* only decode segments are replayed: an n > 1 matmul goes through the library's activation workspace, which may
+     * move when a larger batch comes by (a recorded launch would keep the old address); there the launches are not
+     * the bottleneck anyway */
+    int graphable = g_use_graphs;
+    for (int i = 0; i < g_seg_n; i++) if (g_seg[i].kind == PL_MUL_MAT && g_seg[i].n != 1) graphable = 0;
+    if (graphable) {
+        for (int k = 0; k < g_cache_n && hit < 0; k++) {
+            const int c = (g_cache_cursor + k) % g_cache_n;
+            if (g_cache[c].n == g_seg_n && memcmp(g_cache[c].plans, g_seg, sizeof(struct plan) * (size_t)g_seg_n) == 0) hit = c;
+        }
+    }
+    if (hit >= 0 && g_cache[hit].exec != NULL) {
+        B200_CHECK(ggml_b200_graph_launch(g_cache[hit].exec));
+        g_cache_cursor = (hit + 1) % g_cache_n;
+    } else if (hit >= 0) {
+        /* second time this very segment comes by: record it while submitting it */
+        void * exec = NULL;
+        B200_CHECK(ggml_b200_graph_begin());
+        for (int i = 0; i < g_seg_n; i++) issue(&g_seg[i]);
+        B200_CHECK(ggml_b200_graph_end(&exec));
+        g_cache[hit].exec = exec;
+        B200_CHECK(ggml_b200_graph_launch(exec));
+        g_cache_cursor = (hit + 1) % g_cache_n;
+    } else {
+        for (int i = 0; i < g_seg_n; i++) issue(&g_seg[i]);
+        if (graphable) {
+            if (g_cache_n == SEG_CACHE) {       /* the graphs changed (another model / batch size): start over */
+                for (int c = 0; c < g_cache_n; c++) { free(g_cache[c].plans); ggml_b200_graph_free(g_cache[c].exec); }
+                g_cache_n = 0;
+            }
+            g_cache[g_cache_n].plans = (struct plan *)malloc(sizeof(struct plan) * (size_t)g_seg_n);
+            memcpy(g_cache[g_cache_n].plans, g_seg, sizeof(struct plan) * (size_t)g_seg_n);
+            g_cache[g_cache_n].n = g_seg_n;
+            g_cache[g_cache_n].exec = NULL;
+            g_cache_n++;
+        }
+    }
+    for (int i = 0; i < g_seg_n; i++) if (g_seg[i].d2h_bytes || g_seg[i].h2d_bytes[0] || g_seg[i].h2d_bytes[1]) g_pending = 1;
+    g_seg_n = 0;
+    g_seg_last = NULL;
+}
+
+/* growing a staging block: everything queued may still use the old one */
+static void stage_grow(float ** p, size_t * cap, size_t need) {
+    if (need <= *cap) return;
+    flush_segment();
+    B200_CHECK(ggml_b200_synchronize());
+    g_pending = 0;
+    ensure_dev(p, cap, (need + 4095) & ~(size_t)4095);
+}
 /* the values of `t` on the device: its own buffer, the device copy of a norm weight, or a staged upload of its host data */
-static const float * src_on_device(const struct ggml_tensor * t, int slot) {
+static const float * plan_src(struct plan * p, const struct ggml_tensor * t, int slot) {
     if (is_act(t) || is_devf32(t)) return dev_ptr(t);
     const size_t nbytes = ggml_nbytes(t);
-    if (nbytes > g_stage_in_cap[slot]) ggml_b200_synchronize();      /* the old block may still be read by a queued kernel */
-    ensure_dev(&g_stage_in[slot], &g_stage_in_cap[slot], nbytes);
-    B200_CHECK(ggml_b200_memcpy_h2d_async(g_stage_in[slot], t->data, nbytes));
-    g_pending = 1;                                                   /* the host buffer must not change before the copy has run */
+    stage_grow(&g_stage_in[slot], &g_stage_in_cap[slot], nbytes);
+    p->h2d_src[slot] = t->data; p->h2d_dst[slot] = g_stage_in[slot]; p->h2d_bytes[slot] = nbytes;
     return g_stage_in[slot];
 }
-static float * dst_on_device(struct ggml_tensor * t) {
+static float * plan_dst(struct plan * p, struct ggml_tensor * t) {
     if (is_act(t)) {
         struct ggml_tensor_extra_gpu * e = (struct ggml_tensor_extra_gpu *)t->extra;
         e->data_device[2] = NULL;                                    /* rewritten: the host buffer is stale */
         return (float *)e->data_device[0];
     }
+    /* result of a host-resident tensor: a staging block (a few in rotation, so that wq/wk/wv do not wait for each
+     * other's copy), then back to the tensor's host buffer */
+    const int k = g_stage_out_next++ % 4;
     const size_t nbytes = ggml_nbytes(t);
-    if (nbytes > g_stage_out_cap) ggml_b200_synchronize();
-    ensure_dev(&g_stage_out, &g_stage_out_cap, nbytes);
-    return g_stage_out;
+    stage_grow(&g_stage_out[k], &g_stage_out_cap[k], nbytes);
+    p->d2h_dst = t->data; p->d2h_src = g_stage_out[k]; p->d2h_bytes = nbytes;
+    return g_stage_out[k];
 }
-/* a result whose tensor lives on the host: copy it back; the wait happens at the next node that runs on the CPU */
-static void dst_to_host(struct ggml_tensor * t, const float * y_dev) {
-    if (is_act(t)) return;
-    B200_CHECK(ggml_b200_memcpy_d2h_async(t->data, y_dev, ggml_nbytes(t)));
-    g_pending = 1;
-}
-static void wait_pending(void) {
-    if (g_pending) { B200_CHECK(ggml_b200_synchronize()); g_pending = 0; }
-}
+
 /* a node that runs on the CPU reads `t`: if its values live on the device only (t itself, or the tensor a chain of
  * reshape / view / permute / transpose nodes looks into), bring them to the host buffer and tag the tensor CPU */
 static void ensure_host(struct ggml_tensor * t) {
@@ -340,6 +445,7 @@ static void ensure_host(struct ggml_tensor * t) {
         if (is_act(t)) {
             struct ggml_tensor_extra_gpu * e = (struct ggml_tensor_extra_gpu *)t->extra;
             if (e->data_device[2] == NULL) {
+                flush_segment();
                 B200_CHECK(ggml_b200_memcpy_d2h_async(t->data, e->data_device[0], ggml_nbytes(t)));
                 g_pending = 1;
                 e->data_device[2] = t->data;
@@ -353,65 +459,79 @@ static void ensure_host(struct ggml_tensor * t) {
 }
 
 static void device_node(struct ggml_tensor * t) {
-    const int64_t n = ggml_nelements(t);
+    if (g_seg_n == SEG_MAX) flush_segment();
+    struct plan * p = &g_seg[g_seg_n];
+    memset(p, 0, sizeof(*p));
+    p->n = ggml_nelements(t);
+    const int fuse = g_use_graphs != 0 && g_seg_n > 0 && g_seg_last != NULL && t->op == GGML_OP_MUL && t->src0 == g_seg_last && is_act(t) &&
+                     !g_seg[g_seg_n - 1].d2h_bytes && (is_act(t->src1) || is_devf32(t->src1));
+    if (fuse && g_seg[g_seg_n - 1].kind == PL_RMS_NORM) {
+        struct plan * q = &g_seg[g_seg_n - 1];                   /* y = rms_norm(a); y2 = y * w: one kernel */
+        q->kind = PL_RMS_NORM_MUL; q->b = dev_ptr(t->src1); q->nb = ggml_nelements(t->src1); q->y2 = plan_dst(q, t);
+        g_seg_last = t;
+        return;
+    }
+    if (fuse && g_seg[g_seg_n - 1].kind == PL_SILU && ggml_nelements(t->src1) == p->n) {
+        struct plan * q = &g_seg[g_seg_n - 1];                   /* y = silu(a); y2 = y * b */
+        q->kind = PL_SILU_MUL; q->b = dev_ptr(t->src1); q->y2 = plan_dst(q, t);
+        g_seg_last = t;
+        return;
+    }
     switch (t->op) {
         case GGML_OP_MUL_MAT: {
-            ggml_b200_weight * w = weight_of(t->src0);
-            const int64_t K = t->src0->ne[0], M = t->src0->ne[1], cols = t->src1->ne[1];
-            GGML_ASSERT(t->src1->ne[0] == K && t->ne[0] == M && t->ne[1] == cols);
-            const float * x = src_on_device(t->src1, 0);
-            float * y = dst_on_device(t);
-            if (ggml_b200_comm_world() > 1 && ggml_b200_weight_rows(w) != M)
-                B200_CHECK(ggml_b200_mul_mat_q4_0_sharded(w, x, cols, (size_t)K * sizeof(float), y, (size_t)M * sizeof(float)));
-            else
-                B200_CHECK(ggml_b200_mul_mat_q4_0(w, x, cols, (size_t)K * sizeof(float), y, (size_t)M * sizeof(float)));
-            dst_to_host(t, y);
+            p->kind = PL_MUL_MAT;
+            p->w = weight_of(t->src0);
+            p->K = t->src0->ne[0]; p->M = t->src0->ne[1]; p->n = t->src1->ne[1];
+            GGML_ASSERT(t->src1->ne[0] == p->K && t->ne[0] == p->M && t->ne[1] == p->n);
+            p->a = plan_src(p, t->src1, 0);
+            p->y = plan_dst(p, t);
+            p->sharded = ggml_b200_comm_world() > 1 && ggml_b200_weight_rows(p->w) != p->M;
         } break;
-        case GGML_OP_RMS_NORM: {
-            const float * x = src_on_device(t->src0, 0);
-            float * y = dst_on_device(t);
-            B200_CHECK(ggml_b200_rms_norm_f32(x, y, t->src0->ne[0], ggml_nrows(t->src0), 1e-6f));     /* eps: ggml.c:10417 */
-            dst_to_host(t, y);
-        } break;
+        case GGML_OP_RMS_NORM:
+            p->kind = PL_RMS_NORM; p->ncols = t->src0->ne[0]; p->nrows = ggml_nrows(t->src0);
+            p->a = plan_src(p, t->src0, 0); p->y = plan_dst(p, t);
+            break;
         case GGML_OP_MUL:
-        case GGML_OP_ADD: {
-            const float * a = src_on_device(t->src0, 0);
-            const float * b = src_on_device(t->src1, 1);
-            float * y = dst_on_device(t);
-            if (t->op == GGML_OP_MUL) B200_CHECK(ggml_b200_mul_f32(a, b, y, n, ggml_nelements(t->src1)));
-            else                      B200_CHECK(ggml_b200_add_f32(a, b, y, n, ggml_nelements(t->src1)));
-            dst_to_host(t, y);
-        } break;
-        case GGML_OP_SILU: {
-            const float * x = src_on_device(t->src0, 0);
-            float * y = dst_on_device(t);
-            B200_CHECK(ggml_b200_silu_f32(x, y, n));
-            dst_to_host(t, y);
-        } break;
+        case GGML_OP_ADD:
+            p->kind = t->op == GGML_OP_MUL ? PL_MUL : PL_ADD; p->nb = ggml_nelements(t->src1);
+            p->a = plan_src(p, t->src0, 0); p->b = plan_src(p, t->src1, 1); p->y = plan_dst(p, t);
+            break;
+        case GGML_OP_SILU:
+            p->kind = PL_SILU; p->a = plan_src(p, t->src0, 0); p->y = plan_dst(p, t);
+            break;
         default:
             GGML_ASSERT(!"device_node: unsupported op");
     }
+    /* (plan_src / plan_dst may have flushed the segment to grow a staging block: append at the current end) */
+    if (p != &g_seg[g_seg_n]) g_seg[g_seg_n] = *p;
+    g_seg_n++;
+    g_seg_last = t;
+    if (g_seg[g_seg_n - 1].d2h_bytes) flush_segment();     /* a host-resident result: get it on its way now */
 }
 
 /* ggml_cuda_compute_forward (ggml-cuda.cu:2966-3082): the pre-hook of ggml_compute_forward (ggml.c:15645-15649).
  * Called by every worker thread for every phase; the INIT phase always runs first and on one thread
  * (ggml.c:17114-17117), exactly one thread launches, in COMPUTE (ggml-cuda.cu:3013-3020).  Returns true iff the CPU
  * code must be skipped.  A node runs on the device when this back-end has a kernel for it AND its result or one of its
- * sources lives there; a Q4_0 mul_mat with everything on the host takes the one-launch host path. */
+ * sources lives there; a Q4_0 mul_mat with everything on the host takes the one-launch host path.
+ * A graph must not END on a device node whose result lives on the host (nothing would wait for its copy); llama.cpp's
+ * graphs end on the output matmul, whose sources and result are on the host: the synchronous host path. */
 bool ggml_cuda_compute_forward(struct ggml_compute_params * params, struct ggml_tensor * tensor) {
     if (!g_ready) return false;
+    g_computed_since_assign = 1;
     const int on_device = is_act(tensor) || is_act(tensor->src0) || is_act(tensor->src1);
     const int host_mul_mat = tensor->op == GGML_OP_MUL_MAT && !on_device && ggml_cuda_can_mul_mat(tensor->src0, tensor->src1, tensor);
     if ((on_device && node_supported(tensor)) || host_mul_mat) {
         if (params->ith != 0) return true;
         if (params->type == GGML_TASK_INIT || params->type == GGML_TASK_FINALIZE) return true;
-        if (host_mul_mat) { wait_pending(); ggml_cuda_mul_mat(tensor->src0, tensor->src1, tensor, params->wdata, params->wsize); }
+        if (host_mul_mat) { flush_segment(); wait_pending(); ggml_cuda_mul_mat(tensor->src0, tensor->src1, tensor, params->wdata, params->wsize); }
         else device_node(tensor);
         return true;
     }
-    /* the reference's CPU code runs this node: before any thread starts on it (INIT), bring device-resident sources home
-     * and wait for the copies in flight */
+    /* the reference's CPU code runs this node: before any thread starts on it (INIT), submit what is recorded, bring
+     * device-resident sources home and wait for the copies in flight */
     if (params->ith == 0 && params->type == GGML_TASK_INIT) {
+        flush_segment();
         ensure_host(tensor->src0);
         ensure_host(tensor->src1);
         for (int i = 0; i < GGML_MAX_OPT; i++) ensure_host(tensor->opt[i]);
