@@ -138,6 +138,7 @@ static int node_supported(const struct ggml_tensor * t) {
     }
 }
 
+static int g_stage_out_next = 0;
 static int g_computed_since_assign = 0;   /* a node has run since the last ggml_cuda_assign_buffers: the next call belongs to a NEW graph */
 static void assign_buffers_impl(struct ggml_tensor * tensor, int scratch, int force_inplace) {
     if (!g_ready || tensor == NULL) return;
@@ -147,6 +148,7 @@ static void assign_buffers_impl(struct ggml_tensor * tensor, int scratch, int fo
          * segments below be replayed as recorded CUDA graphs.  Tensors of the previous graph are dead. */
         g_computed_since_assign = 0;
         g_scratch_off = 0;
+        g_stage_out_next = 0;
     }
     if (scratch && g_scratch_size == 0) return;                 /* llama.cpp low_vram: ggml_cuda_set_scratch_size(0) */
     if (!node_supported(tensor)) return;                        /* stays on the CPU */
@@ -337,10 +339,25 @@ static int g_use_graphs = -1;
 
 static float *g_stage_in[2] = {NULL, NULL}, *g_stage_out[4] = {NULL, NULL, NULL, NULL};
 static size_t g_stage_in_cap[2] = {0, 0}, g_stage_out_cap[4] = {0, 0, 0, 0};
-static int g_stage_out_next = 0;
 
+/* GGML_B200_GLUE_PROFILE=1: where the host's time goes (printed by ggml_b200_glue_profile_dump / at scratch free) */
+#include <time.h>
+static struct { double flush_s, wait_s; long flushes, replays, captures, direct, waits, nodes; } g_prof;
+static int g_prof_on = -1;
+static double now_s(void) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec; }
+void ggml_b200_glue_profile_dump(void) {
+    if (g_prof_on > 0 && g_prof.nodes)
+        fprintf(stderr, "ggml-b200 glue: %ld device nodes, %ld segments (%ld replayed, %ld recorded, %ld direct) %.3f ms submitting, %ld waits %.3f ms\n",
+                g_prof.nodes, g_prof.flushes, g_prof.replays, g_prof.captures, g_prof.direct, g_prof.flush_s * 1e3, g_prof.waits, g_prof.wait_s * 1e3);
+    memset(&g_prof, 0, sizeof(g_prof));
+}
 static void wait_pending(void) {
-    if (g_pending) { B200_CHECK(ggml_b200_synchronize()); g_pending = 0; }
+    if (g_pending) {
+        const double t0 = g_prof_on > 0 ? now_s() : 0.0;
+        B200_CHECK(ggml_b200_synchronize());
+        g_pending = 0;
+        if (g_prof_on > 0) { g_prof.wait_s += now_s() - t0; g_prof.waits++; }
+    }
 }
 
 static void issue(const struct plan * p) {
@@ -363,6 +380,9 @@ static void issue(const struct plan * p) {
 /* submit the current segment (asynchronous; copies in it make g_pending) */
 static void flush_segment(void) {
     if (g_seg_n == 0) return;
+    if (g_prof_on < 0) g_prof_on = getenv("GGML_B200_GLUE_PROFILE") != NULL;
+    const double t0 = g_prof_on > 0 ? now_s() : 0.0;
+    if (g_prof_on > 0) { g_prof.flushes++; g_prof.nodes += g_seg_n; }
     if (g_use_graphs < 0) { const char * e = getenv("GGML_B200_GLUE_GRAPHS"); g_use_graphs = e ? atoi(e) : 1; }
     int hit = -1;
     /* only decode segments are replayed: an n > 1 matmul goes through the library's activation workspace, which may
@@ -379,7 +399,9 @@ static void flush_segment(void) {
     if (hit >= 0 && g_cache[hit].exec != NULL) {
         B200_CHECK(ggml_b200_graph_launch(g_cache[hit].exec));
         g_cache_cursor = (hit + 1) % g_cache_n;
+        g_prof.replays++;
     } else if (hit >= 0) {
+        g_prof.captures++;
         /* second time this very segment comes by: record it while submitting it */
         void * exec = NULL;
         B200_CHECK(ggml_b200_graph_begin());
@@ -389,6 +411,7 @@ static void flush_segment(void) {
         B200_CHECK(ggml_b200_graph_launch(exec));
         g_cache_cursor = (hit + 1) % g_cache_n;
     } else {
+        g_prof.direct++;
         for (int i = 0; i < g_seg_n; i++) issue(&g_seg[i]);
         if (graphable) {
             if (g_cache_n == SEG_CACHE) {       /* the graphs changed (another model / batch size): start over */
@@ -405,6 +428,7 @@ static void flush_segment(void) {
     for (int i = 0; i < g_seg_n; i++) if (g_seg[i].d2h_bytes || g_seg[i].h2d_bytes[0] || g_seg[i].h2d_bytes[1]) g_pending = 1;
     g_seg_n = 0;
     g_seg_last = NULL;
+    if (g_prof_on > 0) g_prof.flush_s += now_s() - t0;
 }
 
 /* growing a staging block: everything queued may still use the old one */
