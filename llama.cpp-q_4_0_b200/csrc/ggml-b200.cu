@@ -109,7 +109,8 @@ int launch_quantize(const float * x_dev, int64_t n, int64_t K, size_t nb11, void
     const long long nn = n;
     // the GEMM path also wants the scales block-major ([K/32][n_pad] floats)
     float * xdT = nullptr;
-    const long long n_pad = (n + 3) & ~3ll;
+    const int perm = gemm_xd_perm();
+    const long long n_pad = perm ? (n + 63) & ~63ll : (n + 3) & ~3ll;
     if (n >= 2 && g.path != GGML_B200_PATH_GEMV) {
         const size_t need = (size_t)(K / QK) * n_pad * sizeof(float);
         if (need > g.xdT_cap) {
@@ -122,11 +123,11 @@ int launch_quantize(const float * x_dev, int64_t n, int64_t K, size_t nb11, void
     }
     g.xdT_n_pad = n_pad;
     if (aligned) {
-        if (b34) return launch_k(quantize_q8_0_kernel<true, true>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34, xdT, n_pad);
-        return launch_k(quantize_q8_0_kernel<true, false>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34, xdT, n_pad);
+        if (b34) return launch_k(quantize_q8_0_kernel<true, true>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34, xdT, n_pad, perm);
+        return launch_k(quantize_q8_0_kernel<true, false>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34, xdT, n_pad, perm);
     }
-    if (b34) return launch_k(quantize_q8_0_kernel<false, true>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34, xdT, n_pad);
-    return launch_k(quantize_q8_0_kernel<false, false>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34, xdT, n_pad);
+    if (b34) return launch_k(quantize_q8_0_kernel<false, true>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34, xdT, n_pad, perm);
+    return launch_k(quantize_q8_0_kernel<false, false>, blocks, threads, 0, x_dev, nn, (int)K, nb11, g.xq, g.xds, b34, xdT, n_pad, perm);
 }
 
 // ---- kernel 2 launch ------------------------------------------------------------------------
@@ -746,7 +747,7 @@ int ggml_b200_mul_mat_q4_0(const ggml_b200_weight * w, const float * x_dev, int6
 constexpr size_t STATIC_MAX_ELEMS = (size_t)4 << 20;                  // n * K of one call
 constexpr size_t STATIC_XQ_BYTES = STATIC_MAX_ELEMS;                  // int8 [n][K]
 constexpr size_t STATIC_XDS_BYTES = STATIC_MAX_ELEMS / 4;             // int2 [n][K/32]
-constexpr size_t STATIC_XDT_BYTES = (size_t)1 << 20;                  // float [K/32][n_pad], n_pad <= n + 3
+constexpr size_t STATIC_XDT_BYTES = (size_t)1 << 20;                  // float [K/32][n_pad], n_pad <= n + 63
 static __device__ __align__(256) unsigned char g_static_scratch[STATIC_XQ_BYTES + STATIC_XDS_BYTES + STATIC_XDT_BYTES];
 static unsigned char * g_static_ptr = nullptr;        // DEVICE address of the array on g.device (the symbol's name is only a host-side stand-in)
 static unsigned g_static_epoch = 0;
@@ -880,7 +881,7 @@ int ggml_b200_mul_mat_q4_0_static(const ggml_b200_weight * w, const float * x_de
     if (rc) return rc;
     if (n == 0 || w->rows() == 0) return GGML_B200_OK;
     const uint64_t elems = (uint64_t)n * (uint64_t)w->K;
-    const uint64_t n_pad = ((uint64_t)n + 3) & ~3ull;
+    const uint64_t n_pad = ((uint64_t)n + 63) & ~63ull;
     if (elems > STATIC_MAX_ELEMS || (uint64_t)(w->K / QK) * n_pad * 4 > STATIC_XDT_BYTES) {
         set_error("ggml_b200_mul_mat_q4_0_static: n * K = %llu activations exceed the static scratch (max %llu); use ggml_b200_mul_mat_q4_0",
                   (unsigned long long)elems, (unsigned long long)STATIC_MAX_ELEMS);

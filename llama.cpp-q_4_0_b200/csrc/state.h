@@ -130,6 +130,7 @@ int mul_mat_dev(const ggml_b200_weight * w, const float * x_dev, int64_t n, size
 int  gemm_init();
 void gemm_shutdown();
 int  gemm_set_tuning(const char * key, int value);
+int  gemm_xd_perm();   // 1: kernel 1 writes the block-major activation scales in kernel 3's (v3) column order
 bool gemm_available(const ggml_b200_weight * w);
 int  gemm_prepare_weight(ggml_b200_weight * w);
 void gemm_release_weight(ggml_b200_weight * w);
