@@ -44,12 +44,12 @@ def main():
         v = rel(t[1, b])
         if b < 24 or b % 16 == 0 or b > nbk - 6:
             e = [rel(t[2, 8 * b + k]) for k in range(6)]
-            print(f"  blk {b:3d}  t={v:8d}  d={v - prev:6d}   epi0: wait_start={e[0]:8d} +d_full={e[1]-e[0]:5d} +ld0={e[2]-e[1]:5d} +fma0={e[3]-e[2]:5d} +ld1={e[4]-e[3]:5d} +fma1={e[5]-e[4]:5d}")
+            print(f"  blk {b:3d}  t={v:8d}  d={v - prev:6d}   epi0: wait_start={e[0]:8d} +d_full={e[1]-e[0]:5d} +ld0={e[2]-e[1]:5d} +fma0={e[3]-e[2]:5d} +ld1={e[4]-e[3]:5d} +fma1={e[5]-e[4]:5d} | warp3 start {rel(t[2, 8*b+6]):8d} warp5 start {rel(t[2, 8*b+7]):8d}")
         prev = v
     print("per stage: MMA got op_full | TMA after raw_empty, op_empty, x_empty | unpack(t0): start, raw_full, waits done, stored")
     for s in range(0, nbk // 4):
-        if s < 10 or s % 8 == 0:
-            print(f"  st {s:3d}  mma_op_full={rel(t[1, 512+s]):8d} | tma {rel(t[0, 3*s]):8d} {rel(t[0, 3*s+1]):8d} {rel(t[0, 3*s+2]):8d} | "
+        if s < 16 or s % 8 == 0:
+            print(f"  st {s:3d}  mma wait_op_full from {rel(t[1, 1024+s]):8d} to {rel(t[1, 512+s]):8d} | tma {rel(t[0, 3*s]):8d} {rel(t[0, 3*s+1]):8d} {rel(t[0, 3*s+2]):8d} | "
                   f"unp {rel(t[3, 4*s]):8d} {rel(t[3, 4*s+1]):8d} {rel(t[3, 4*s+2]):8d} {rel(t[3, 4*s+3]):8d}")
     tot = rel(max(t[1, :nbk]))
     print(f"MMA issue span {tot} cycles = {tot / nbk:.0f} per block")

@@ -66,11 +66,37 @@ __global__ void __launch_bounds__(256, 1) ldtm_kernel(long long * cyc, unsigned 
     tmem_teardown(base, warp);
 }
 
-// (2) two FMAs per element, S from TMEM, scales from registers; half a block (32 registers) double buffered
-__global__ void __launch_bounds__(256, 1) twofma_kernel(long long * cyc, float * y, int nbk) {
+// (2) two FMAs per element, S from TMEM, scales from registers; half a block (32 registers) double buffered.
+// mma_gap >= 0: a ninth warp issues kernel 3's MMA pair (128x128x32 int8, data + constant tile) into the buffers being read,
+// one pair every max(128, mma_gap) clocks -- does the tensor core's accumulator traffic slow tcgen05.ld down?
+__global__ void __launch_bounds__(288, 1) twofma_kernel(long long * cyc, float * y, int nbk, int mma_gap) {
+    extern __shared__ __align__(1024) unsigned char opsmem[];
     __shared__ uint32_t slot;
+    __shared__ volatile int done;
     const int warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) done = 0;
+    if (mma_gap >= 0) {
+        for (int i = threadIdx.x; i < 32768 / 16; i += 288) reinterpret_cast<uint4 *>(opsmem)[i] = make_uint4(i, 0x80808080u, ~i, 0x01020304u);
+        fence_proxy_async_smem();
+    }
     const uint32_t base = tmem_setup(&slot, warp);
+    if (warp == 8) {
+        if (mma_gap >= 0) {
+            const uint32_t idesc = umma_idesc_i8(128, 128);
+            const uint64_t ad = umma_desc_k_sw128(smem_u32(opsmem)), bd = umma_desc_k_sw128(smem_u32(opsmem) + 16384);
+            int i = 0;
+            while (!done) {
+                const long long t = clock64();
+                if (elect_one()) {
+                    mma_i8_ss(base + (i & 3) * 128, ad + 2 * (i & 3), bd + 2 * (i & 3), idesc, 0u);
+                    mma_i8_ss(base + (i & 3) * 128, ad, ad, idesc, 1u);
+                }
+                __syncwarp();
+                i++;
+                while (clock64() - t < mma_gap && !done) { }
+            }
+        }
+    } else {
     const uint32_t t_lane = base + ((uint32_t)((warp & 3) * 32) << 16) + (warp >> 2) * 64;
     uint64_t acc[32];
 #pragma unroll
@@ -110,6 +136,9 @@ __global__ void __launch_bounds__(256, 1) twofma_kernel(long long * cyc, float *
     for (int i = 0; i < 32; i++) { float a, b; unpack_f32x2(acc[i], a, b); s += a + b; }
     y[blockIdx.x * 256 + threadIdx.x] = s + (float)ra[0];
     if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
+    asm volatile("bar.sync 1, 256;" ::: "memory");     // the 8 reading warps
+    if (threadIdx.x == 0) done = 1;
+    }
     tmem_teardown(base, warp);
 }
 
@@ -160,7 +189,8 @@ template <int MODE>   // 0: d = a*s + s' (pair, scalar, scalar)   1: d = a*b + d
 __global__ void __launch_bounds__(256, 1) ffma2_kernel(long long * cyc, float * out, int iters, float seed) {
     uint64_t a[16], b[16];
     for (int i = 0; i < 16; i++) { a[i] = pack_f32x2(seed + i + threadIdx.x, seed * 0.5f + i); b[i] = pack_f32x2(1.0f + 1e-7f * i, 1.0f - 1e-7f * i); }
-    const float s0 = 1.0000001f, s1 = 1e-9f;
+    if (MODE == 4) for (int i = 0; i < 16; i++) b[i] = pack_u32x2((1u << 19) + 16u * (threadIdx.x + i), (1u << 19) - 16u * (threadIdx.x + 3 * i));   // denormals
+    const float s0 = MODE >= 3 ? seed * 5e28f : 1.0000001f, s1 = 1e-9f;
     const uint64_t m2 = pack_f32x2(s0, s0), c2 = pack_f32x2(s1, s1);
     __syncthreads();
     long long t0 = clock64();
@@ -169,7 +199,9 @@ __global__ void __launch_bounds__(256, 1) ffma2_kernel(long long * cyc, float * 
         for (int i = 0; i < 16; i++) {
             if (MODE == 0) a[i] = fma_f32x2(a[i], m2, c2);
             else if (MODE == 1) fma_acc_f32x2(a[i], b[i], b[(i + 5) & 15]);
-            else { const uint64_t t = fma_f32x2(b[i], m2, c2); fma_acc_f32x2(a[i], t, b[(i + 3) & 15]); }
+            else if (MODE == 2) { const uint64_t t = fma_f32x2(b[i], m2, c2); fma_acc_f32x2(a[i], t, b[(i + 3) & 15]); }
+            else fma_acc_f32x2(a[i], b[i], m2);      // modes 3 / 4: b normal / denormal
+
         }
     }
     long long t1 = clock64();
@@ -208,10 +240,14 @@ int main() {
         }
     }
     printf("== (2) two-FMA formulation (kernel 3): S from TMEM, 8 warps, per Q4_0 block of a 128x128 tile  (FMA-pipe floor 256 clk, MMA 64 clk)\n");
-    for (int nbk = 128; nbk <= 512; nbk *= 4) {
-        for (int rep = 0; rep < 2; rep++) { twofma_kernel<<<G, 256>>>(cyc, y, nbk); CHECK(); }
+    cudaFuncSetAttribute(twofma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 33792);
+    const int gaps[5] = {-1, 1000, 500, 250, 0};
+    for (int gi = 0; gi < 5; gi++) {
+        const int nbk = 512;
+        for (int rep = 0; rep < 2; rep++) { twofma_kernel<<<G, 288, 33792>>>(cyc, y, nbk, gaps[gi]); CHECK(); }
         const double c = mean_cycles(cyc, G);
-        printf("  nbk %4d: %9.0f clk total, %6.1f clk per block\n", nbk, c, c / nbk);
+        if (gaps[gi] < 0) printf("  nbk %4d, tensor core idle:                        %9.0f clk total, %6.1f clk per block\n", nbk, c, c / nbk);
+        else printf("  nbk %4d, an MMA pair every max(128, %4d) clk:     %9.0f clk total, %6.1f clk per block\n", nbk, gaps[gi], c, c / nbk);
     }
     printf("== (3) one-FMA formulation: S and D = dw x dx both from TMEM, 8 warps  (FMA-pipe floor 128 clk, TMEM-read floor 512 clk)\n");
     for (int nbk = 128; nbk <= 512; nbk *= 4) {
@@ -220,13 +256,16 @@ int main() {
         printf("  nbk %4d: %9.0f clk total, %6.1f clk per block\n", nbk, c, c / nbk);
     }
     printf("== (4) FFMA2 operand shapes, 8 warps per SM, 16 chains per thread\n");
-    const char * names[3] = {"d = a * s + s' (pair, scalar, scalar)", "d = a * b + d  (three pairs)", "t = b*s+s'; d = t*b'+d (the epilogue's two)"};
-    for (int mode = 0; mode < 3; mode++) {
+    const char * names[5] = {"d = a * s + s' (pair, scalar, scalar)", "d = a * b + d  (three pairs)", "t = b*s+s'; d = t*b'+d (t is loop invariant)",
+                             "d = b * s + d, b normal", "d = b * s + d, b DENORMAL (the S_b + 2^19 bits)"};
+    for (int mode = 0; mode < 5; mode++) {
         const int it2 = 20000;
         for (int rep = 0; rep < 2; rep++) {
             if (mode == 0) ffma2_kernel<0><<<G, 256>>>(cyc, y, it2, 1.5f);
             if (mode == 1) ffma2_kernel<1><<<G, 256>>>(cyc, y, it2, 1.5f);
             if (mode == 2) ffma2_kernel<2><<<G, 256>>>(cyc, y, it2, 1.5f);
+            if (mode == 3) ffma2_kernel<3><<<G, 256>>>(cyc, y, it2, 1.5f);
+            if (mode == 4) ffma2_kernel<4><<<G, 256>>>(cyc, y, it2, 1.5f);
             CHECK();
         }
         const double c = mean_cycles(cyc, G);
