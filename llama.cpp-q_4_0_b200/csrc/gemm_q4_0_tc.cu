@@ -65,13 +65,15 @@ void gemm_shutdown() { g_gemm_ready = false; }
 // "gemm_bias": 1 = the constant-tile MMA + denormal-read epilogue (no int->float instruction), 0 = the
 // 1.5*2^23 integer-add epilogue (gemm_q4_0_tc.cuh)
 static int g_gemm_bias = 1;
-static int g_gemm_dbg = 0;    // "gemm_dbg": timing experiments of the v3 kernel (wrong results), never set by the product
-static int g_gemm_v3 = 1;     // "gemm_v3": 1 = gemm_q4_0_tc3.cuh (round 2), 0 = the round-1 kernel
+// "gemm_v3": 0 = gemm_q4_0_tc.cuh (default), 1 = gemm_q4_0_tc3.cuh, the round-2 rewrite with 40 % fewer epilogue instructions.
+// Both are parity green; measured on the nine prefill shapes the rewrite is 3-4 % SLOWER (profiles/r02_bench_gemm_v1.log,
+// r02_bench_gemm_v3.log): what paces both is the per-warp serial chain TMEM load -> FMA -> barrier hand-off, not the
+// instruction count (kernel 3).
+static int g_gemm_v3 = 0;
 int gemm_xd_perm() { return g_gemm_v3; }
 long long * g_gemm_trace = nullptr;   // debug timeline buffer (tools/trace_gemm.py)
 int gemm_set_tuning(const char * key, int value) {
     if (!strcmp(key, "gemm_bias")) { g_gemm_bias = value != 0; return GGML_B200_OK; }
-    if (!strcmp(key, "gemm_dbg")) { g_gemm_dbg = value; return GGML_B200_OK; }
     if (!strcmp(key, "gemm_v3")) { g_gemm_v3 = value != 0; g.runN.count = 0; return GGML_B200_OK; }
     if (!strcmp(key, "gemm_trace")) {   // value != 0: allocate and arm the 4 x 2048 clock64 timeline buffer
         if (g_gemm_trace) { cudaFree(g_gemm_trace); g_gemm_trace = nullptr; }
@@ -126,9 +128,9 @@ int launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int
     const int rows = (int)w->rows(), nbk_i = (int)nbk;
     if (g_gemm_v3) {
         cfg.dynamicSmemBytes = g3::SMEM_BYTES;
-        if (g_gemm_trace && !S) CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, true>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent | (g_gemm_dbg << 8)));
-        else if (S)             CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<true, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent | (g_gemm_dbg << 8)));
-        else                    CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent | (g_gemm_dbg << 8)));
+        if (g_gemm_trace && !S) CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, true>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
+        else if (S)             CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<true, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
+        else                    CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
     } else if (g_gemm_trace && !S) {
         CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<false, true, true>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
     } else if (g_gemm_bias) {

@@ -56,7 +56,6 @@ constexpr int NS_X = 6;                 // scale ring (the epilogue trails the M
 constexpr int NS_D = 4;                 // TMEM accumulator ring (4 x 128 columns = 512)
 constexpr int THREADS = 384;
 constexpr int EPI_WARPS = 8, TMA_WARP = 8, MMA_WARP = 9, UNPACK_WARP0 = 10, UNPACK_WARPS = 2;
-constexpr int EPI_REGS = 224, SVC_REGS = 56;              // setmaxnreg: 256 * 224 + 128 * 56 == 384 * 168 (the launch pool)
 constexpr int UNPACK_ROWS = BM / (UNPACK_WARPS * 8);      // (row, block) items per unpack thread and k-stage (8)
 static_assert(KB == NS_D, "block j of a k-stage uses TMEM buffer j");
 
@@ -142,7 +141,7 @@ __device__ __forceinline__ float4 lds_f4(uint32_t addr) { return lds_f32x4(addr)
 // The epilogue of one warp over the whole K loop.
 template <bool DUMP, bool TRACE>
 __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int ew, int lane, int m0, int c0, int rows, int n, int nbk,
-                                         float * __restrict__ y, long long ldy, int * S_out, long long * trc, int dbg) {
+                                         float * __restrict__ y, long long ldy, int * S_out, long long * trc) {
 #define G3_TR(idx) do { if (TRACE && trc != nullptr && ew == 0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0) trc[2 * 2048 + (idx)] = clock64(); } while (0)
     const uint32_t bars = sbase + SMEM_BAR;
     const int quad = ew & 3;                        // TMEM lane quadrant (== warp % 4)
@@ -195,27 +194,26 @@ __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int
                     }
                     G3_TR(8 * blk);
                     if (TRACE && trc != nullptr && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && (ew == 3 || ew == 5)) trc[2 * 2048 + 8 * blk + (ew == 3 ? 6 : 7)] = clock64();
-                    float dw[4] = {1.f, 1.f, 1.f, 1.f}, nc[4] = {0.f, 0.f, 0.f, 0.f};
-                    if (!(dbg & 8)) {
+                    float dw[4], nc[4];
+                    {
                         const float4 w4 = lds_f4(da + jj * (BM * 4));
                         dw[0] = w4.x; dw[1] = w4.y; dw[2] = w4.z; dw[3] = w4.w;
 #pragma unroll
                         for (int j = 0; j < 4; j++) nc[j] = NEG_OFFSET * dw[j];      // exact: dw has 11 significant bits
                     }
-                    uint64_t dx2[8] = {1, 1, 1, 1, 1, 1, 1, 1};
-                    if (!(dbg & 8))
+                    uint64_t dx2[8];
 #pragma unroll
                     for (int q = 0; q < 4; q++) {
                         const float4 v = lds_f4(xa + jj * (BN * 4) + 16 * q);
                         dx2[2 * q] = pack_f32x2(v.x, v.y);
                         dx2[2 * q + 1] = pack_f32x2(v.z, v.w);
                     }
-                    if (!(dbg & 4)) tmem_ld_wait();                                       // ra = rows r0, r0 + 8
+                    tmem_ld_wait();                                       // ra = rows r0, r0 + 8
                     G3_TR(8 * blk + 1);
-                    if (!(dbg & 4)) tmem_ld_16x256b_x8(t_lane + jj * BN + (16u << 16), rb);
-                    if (!(dbg & 1)) epi_half<0, DUMP>(ra, acc, dx2, dw, nc, dump, blk, lane);
+                    tmem_ld_16x256b_x8(t_lane + jj * BN + (16u << 16), rb);
+                    epi_half<0, DUMP>(ra, acc, dx2, dw, nc, dump, blk, lane);
                     G3_TR(8 * blk + 2);
-                    if (!(dbg & 4)) tmem_ld_wait();                                       // rb = rows r0 + 16, r0 + 24
+                    tmem_ld_wait();                                       // rb = rows r0 + 16, r0 + 24
                     G3_TR(8 * blk + 3);
                     // this warp's slice of the TMEM buffer is in registers: hand it back to the MMA issuer
                     tc_fence_before_sync();
@@ -225,10 +223,10 @@ __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int
                         if (!ok_x) mbar_wait(x_bar, xph1);                // next stage's scales have landed
                         if (!ok_d) mbar_wait(d_bar, d_par);
                         tc_fence_after_sync();
-                        if (!(dbg & 4)) tmem_ld_16x256b_x8(t_lane + j1 * BN, ra);
+                        tmem_ld_16x256b_x8(t_lane + j1 * BN, ra);
                     }
                     G3_TR(8 * blk + 4);
-                    if (!(dbg & 1)) epi_half<1, DUMP>(rb, acc, dx2, dw, nc, dump, blk, lane);
+                    epi_half<1, DUMP>(rb, acc, dx2, dw, nc, dump, blk, lane);
                     G3_TR(8 * blk + 5);
                 }
             }
@@ -283,8 +281,7 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
                      const __half * __restrict__ wd,               // weight scales [rows][nbk]
                      float * __restrict__ y, long long ldy, int rows, int n, int nbk,
                      int * __restrict__ S_out, long long * __restrict__ trc,
-                     int independent_dbg /* bit 0: reads the activations its predecessor read, writes its own dst: no wait at the top */) {
-    const int independent = independent_dbg & 1, dbg = independent_dbg >> 8;   // dbg: timing experiments only (tools/bench_gemm.py gemm_dbg=)
+                     int independent /* reads the activations its predecessor read, writes its own dst: no wait at the top */) {
 #define G3K_TR(role, idx) do { if (TRACE && trc != nullptr && blockIdx.x == 0 && blockIdx.y == 0) trc[(role) * 2048 + (idx)] = clock64(); } while (0)
     // no static shared memory in this kernel: the dynamic window starts 1024-byte aligned (checked below), which the
     // 128-byte swizzle atoms need
@@ -325,25 +322,20 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
     pdl_launch_dependents();   // after the wait: see gemv_q4_0_fused.cuh (independent ops)
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(smem + SMEM_BAR + Bars::tmem_slot);
 
-    // register budget (setmaxnreg at the top of each role's branch; the branches only meet again at the final barrier)
     if (warp < EPI_WARPS) {
-        setmaxnreg_inc<EPI_REGS>();
-        epilogue<DUMP, TRACE>(sbase, tmem_base, warp, lane, m0, c0, rows, n, nbk, y, ldy, S_out, trc, dbg);
+        epilogue<DUMP, TRACE>(sbase, tmem_base, warp, lane, m0, c0, rows, n, nbk, y, ldy, S_out, trc);
     } else if (warp == TMA_WARP) {
-        setmaxnreg_dec<SVC_REGS>();
         if (lane == 0) {
             for (int s = 0; s < nstages; s++) {
                 const int sr = s % NS_RAW, so = s % NS_OP, sx = s % NS_X;
                 if (s >= NS_RAW) mbar_wait(bars + Bars::raw_empty + 8 * sr, ((s / NS_RAW) - 1) & 1);
                 G3K_TR(0, 3 * s);
-                if (dbg & 32) mbar_arrive(bars + Bars::raw_full + 8 * sr); else {
                 mbar_expect_tx(bars + Bars::raw_full + 8 * sr, RAW_BYTES);
-                tma_load_2d(sbase + SMEM_RAW + sr * RAW_BYTES, &tm_nib, s * KB * 16, m0, bars + Bars::raw_full + 8 * sr); }
+                tma_load_2d(sbase + SMEM_RAW + sr * RAW_BYTES, &tm_nib, s * KB * 16, m0, bars + Bars::raw_full + 8 * sr);
                 if (s >= NS_OP) mbar_wait(bars + Bars::op_empty + 8 * so, ((s / NS_OP) - 1) & 1);
                 G3K_TR(0, 3 * s + 1);
-                if (dbg & 16) mbar_arrive(bars + Bars::op_full + 8 * so); else {
                 mbar_expect_tx(bars + Bars::op_full + 8 * so, B_BYTES);
-                tma_load_2d(sbase + SMEM_OP + so * (A_BYTES + B_BYTES) + A_BYTES, &tm_xq, s * KB * 32, c0, bars + Bars::op_full + 8 * so); }
+                tma_load_2d(sbase + SMEM_OP + so * (A_BYTES + B_BYTES) + A_BYTES, &tm_xq, s * KB * 32, c0, bars + Bars::op_full + 8 * so);
                 if (s >= NS_X) mbar_wait(bars + Bars::x_empty + 8 * sx, ((s / NS_X) - 1) & 1);
                 G3K_TR(0, 3 * s + 2);
                 mbar_expect_tx(bars + Bars::x_full + 8 * sx, XD_BYTES);
@@ -351,7 +343,6 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
             }
         }
     } else if (warp == MMA_WARP) {
-        setmaxnreg_dec<SVC_REGS>();
         // The whole warp walks the loop converged and one elected lane issues: every operand stays in uniform registers.
         // (Inside `if (lane == 0) { loop }` ptxas wraps each UTCIMMA in an ELECT / BRA.U.ANY loop; the issuing thread's own
         // scalar instructions are what paces this pipeline -- tools/ubench/mma_rate.cu: the MMA pair itself takes 128 clk.)
@@ -386,7 +377,6 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
             __syncwarp();
         }
     } else {
-        setmaxnreg_dec<SVC_REGS>();
         // ===== unpack: nibble tile -> K-major signed-byte A tile (16 * (q - 8)) with the 128-byte swizzle =====
         // 64 threads x 8 (row, block) items per k-stage, in two batches of 4 with the shared-memory loads of a batch
         // issued before its first expansion.
@@ -423,7 +413,6 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
             if (t == 0) G3K_TR(3, 4 * s + 2);
             const uint32_t a = sbase + SMEM_OP + so * (A_BYTES + B_BYTES);
             const uint32_t dws = sbase + SMEM_X + sx * X_BYTES + XD_BYTES;
-            if (!(dbg & 2)) {
 #pragma unroll
             for (int jb = 0; jb < KB; jb++) {
                 const unsigned short ha = (unsigned short)(p0[jb >> 1] >> (16 * (jb & 1)));
@@ -454,7 +443,6 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
 #pragma unroll
                     for (int i = 0; i < HALF; i++) q[i] = lds_u32x4(raw + RSTEP * (HALF + i) * 64);
                 }
-            }
             }
             fence_proxy_async_smem();      // generic-proxy stores -> tensor-core (async proxy) reads
             __syncwarp();

@@ -142,6 +142,127 @@ __global__ void __launch_bounds__(288, 1) twofma_kernel(long long * cyc, float *
     tmem_teardown(base, warp);
 }
 
+// (2b) the same epilogue plus, one at a time, what kernel 3 has around it (flags F):
+//   1: the block's scales come from shared memory (5 LDS.128 per thread and block)
+//   2: tcgen05 fences + __syncwarp + one mbarrier.arrive per warp and block
+//   4: two mbarrier.test_wait per block (a completed phase), looked at after the first half
+//   8: two more warps run an unpack-like loop (LDS.128, 24 logic ops, 2 STS.128 per item) flat out
+template <int F>
+__global__ void __launch_bounds__(320, 1) epi_plus_kernel(long long * cyc, float * y, int nbk) {
+    extern __shared__ __align__(1024) unsigned char sm[];
+    __shared__ uint32_t slot;
+    __shared__ __align__(8) unsigned long long bar[2];
+    __shared__ volatile int done;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t sb = smem_u32(sm);
+    if (threadIdx.x == 0) { done = 0; mbar_init(smem_u32(&bar[0]), 8); mbar_init(smem_u32(&bar[1]), 1); mbar_fence_init(); }
+    for (int i = threadIdx.x; i < 49152 / 4; i += 320) reinterpret_cast<float *>(sm)[i] = 1.0f + 1e-3f * (i & 63);
+    const uint32_t base = tmem_setup(&slot, warp);
+    if (threadIdx.x == 0) mbar_arrive(smem_u32(&bar[1]));
+    __syncthreads();
+    if (warp >= 8) {
+        if (F & 8) {
+            const uint32_t src = sb + 16384 + (warp - 8) * 8192 + lane * 16, dst = sb + 32768 + (warp - 8) * 8192 + lane * 32;
+            int i = 0;
+            while (!done) {
+                const uint4 q = lds_u32x4(src + (i & 7) * 512);
+                uint4 lo, hi;
+                lo.x = ((q.x << 4) & 0xF0F0F0F0u) ^ 0x80808080u; hi.x = (q.x & 0xF0F0F0F0u) ^ 0x80808080u;
+                lo.y = ((q.y << 4) & 0xF0F0F0F0u) ^ 0x80808080u; hi.y = (q.y & 0xF0F0F0F0u) ^ 0x80808080u;
+                lo.z = ((q.z << 4) & 0xF0F0F0F0u) ^ 0x80808080u; hi.z = (q.z & 0xF0F0F0F0u) ^ 0x80808080u;
+                lo.w = ((q.w << 4) & 0xF0F0F0F0u) ^ 0x80808080u; hi.w = (q.w & 0xF0F0F0F0u) ^ 0x80808080u;
+                sts_u32x4(dst + (i & 7) * 1024, lo);
+                sts_u32x4(dst + (i & 7) * 1024 + 16, hi);
+                i++;
+            }
+        }
+    } else {
+    const uint32_t t_lane = base + ((uint32_t)((warp & 3) * 32) << 16) + (warp >> 2) * 64;
+    uint32_t xa = sb + ((warp >> 2) * 64 + 16 * (lane & 3)) * 4, da = sb + 2048 + ((warp & 3) * 32 + (lane >> 2) * 4) * 4;
+    asm volatile("" : "+r"(xa), "+r"(da));
+    uint64_t acc[32];
+#pragma unroll
+    for (int i = 0; i < 32; i++) acc[i] = 0ull;
+    float dw[4], nc[4];
+    uint64_t dx2[8];
+    for (int i = 0; i < 4; i++) { dw[i] = 1.0f + i + threadIdx.x; nc[i] = -1e-30f * i; }
+    for (int i = 0; i < 8; i++) dx2[i] = pack_f32x2(0.5f + i, 0.25f + i);
+    uint32_t ra[32], rb[32];
+    unsigned int misses = 0;
+    long long t0 = clock64();
+    ld_x8(t_lane, ra);
+#pragma unroll 1
+    for (int blk = 0; blk < nbk; blk++) {
+        const uint32_t tb = t_lane + (blk & 3) * 128;
+        bool ok0 = true, ok1 = true;
+        if (F & 4) { ok0 = mbar_test_wait(smem_u32(&bar[1]), 0); ok1 = mbar_test_wait(smem_u32(&bar[1]), 0); }
+        if (F & 1) {
+            const float4 w4 = lds_f32x4(da + (blk & 3) * 512);
+            dw[0] = w4.x; dw[1] = w4.y; dw[2] = w4.z; dw[3] = w4.w;
+#pragma unroll
+            for (int j = 0; j < 4; j++) nc[j] = -7.3e-40f * dw[j];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const float4 v = lds_f32x4(xa + (blk & 3) * 512 + 16 * q);
+                dx2[2 * q] = pack_f32x2(v.x, v.y);
+                dx2[2 * q + 1] = pack_f32x2(v.z, v.w);
+            }
+        }
+        tmem_ld_wait();
+        ld_x8(tb + (16u << 16), rb);
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+#pragma unroll
+            for (int jj = 0; jj < 2; jj++) {
+                const uint64_t t = fma_f32x2(pack_u32x2(ra[4 * k + 2 * jj], ra[4 * k + 2 * jj + 1]), pack_f32x2(dw[jj], dw[jj]), pack_f32x2(nc[jj], nc[jj]));
+                fma_acc_f32x2(acc[k * 4 + jj], t, dx2[k]);
+            }
+        tmem_ld_wait();
+        if (F & 2) {
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&bar[0]));
+        }
+        if (F & 4) { if (!ok0 || !ok1) misses++; }
+        if (F & 2) tc_fence_after_sync();
+        ld_x8(t_lane + ((blk + 1) & 3) * 128, ra);
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+#pragma unroll
+            for (int jj = 0; jj < 2; jj++) {
+                const uint64_t t = fma_f32x2(pack_u32x2(rb[4 * k + 2 * jj], rb[4 * k + 2 * jj + 1]), pack_f32x2(dw[2 + jj], dw[2 + jj]), pack_f32x2(nc[2 + jj], nc[2 + jj]));
+                fma_acc_f32x2(acc[k * 4 + 2 + jj], t, dx2[k]);
+            }
+    }
+    tmem_ld_wait();
+    long long t1 = clock64();
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; i++) { float a, b; unpack_f32x2(acc[i], a, b); s += a + b; }
+    y[blockIdx.x * 256 + threadIdx.x] = s + (float)ra[0] + (float)misses;
+    if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (threadIdx.x == 0) done = 1;
+    }
+    tmem_teardown(base, warp);
+}
+
+template <int F>
+static void run_plus(long long * cyc, float * y, const char * what) {
+    const int G = 148, nbk = 512;
+    cudaFuncSetAttribute(epi_plus_kernel<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, 50176);
+    for (int rep = 0; rep < 2; rep++) {
+        epi_plus_kernel<F><<<G, 320, 50176>>>(cyc, y, nbk);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("CUDA error: %s (%s)\n", cudaGetErrorString(e), what); return; }
+    }
+    static long long h[148];
+    cudaMemcpy(h, cyc, sizeof(h), cudaMemcpyDeviceToHost);
+    double c = 0;
+    for (int i = 0; i < G; i++) c += (double)h[i];
+    printf("  %-72s %6.1f clk per block\n", what, c / G / nbk);
+}
+
 // (3) one FMA per element: S and D both from TMEM
 __global__ void __launch_bounds__(256, 1) onefma_kernel(long long * cyc, float * y, int nbk) {
     __shared__ uint32_t slot;
@@ -249,6 +370,14 @@ int main() {
         if (gaps[gi] < 0) printf("  nbk %4d, tensor core idle:                        %9.0f clk total, %6.1f clk per block\n", nbk, c, c / nbk);
         else printf("  nbk %4d, an MMA pair every max(128, %4d) clk:     %9.0f clk total, %6.1f clk per block\n", nbk, gaps[gi], c, c / nbk);
     }
+    printf("== (2b) the two-FMA epilogue plus what kernel 3 has around it\n");
+    run_plus<0>(cyc, y, "nothing added");
+    run_plus<1>(cyc, y, "+ scales from shared memory (5 LDS.128 per thread and block)");
+    run_plus<2>(cyc, y, "+ fences, __syncwarp, mbarrier.arrive per warp and block");
+    run_plus<4>(cyc, y, "+ two mbarrier.test_wait per block");
+    run_plus<7>(cyc, y, "+ all three");
+    run_plus<8>(cyc, y, "+ two unpack-like warps (LDS.128 / logic / STS.128) flat out");
+    run_plus<15>(cyc, y, "+ everything");
     printf("== (3) one-FMA formulation: S and D = dw x dx both from TMEM, 8 warps  (FMA-pipe floor 128 clk, TMEM-read floor 512 clk)\n");
     for (int nbk = 128; nbk <= 512; nbk *= 4) {
         for (int rep = 0; rep < 2; rep++) { onefma_kernel<<<G, 256>>>(cyc, y, nbk); CHECK(); }

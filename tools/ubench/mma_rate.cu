@@ -111,10 +111,11 @@ __global__ void __launch_bounds__(128, 1) mma_kernel(long long * cyc, int nblk) 
 
 int main_proto(long long * cyc);
 void main_prim(long long * cyc);
+void main_after(long long * cyc);
 int main() {
     const int G = 148;
     long long * cyc;
-    cudaMalloc(&cyc, 8192);
+    cudaMalloc(&cyc, 32768);
     typedef void (*kern_t)(long long *, int);
 #define K2(m) {mma_kernel<0, m>, mma_kernel<1, m>}
     kern_t kerns[12][2] = {K2(0), K2(1), K2(2), K2(3), K2(4), K2(5), K2(6), K2(7), K2(8), K2(9), K2(10), K2(11)};
@@ -146,6 +147,7 @@ int main() {
     }
     main_proto(cyc);
     main_prim(cyc);
+    main_after(cyc);
     return 0;
 }
 
@@ -155,7 +157,7 @@ int main() {
 //   V = 0: waits by mbarrier.try_wait loops (ptx.cuh mbar_wait)      V = 1: waits spin on mbarrier.test_wait
 //   V = 2: as 0, epilogue warps probe the NEXT block's barrier with test_wait before waiting (kernel 3)
 template <int V, int NBUF>
-__global__ void __launch_bounds__(288, 1) proto_kernel(long long * cyc, int nblk) {
+__global__ void __launch_bounds__(384, 1) proto_kernel(long long * cyc, int nblk) {
     extern __shared__ __align__(1024) unsigned char smem[];
     __shared__ uint32_t slot;
     __shared__ __align__(8) unsigned long long bar[2 * NBUF];
@@ -163,7 +165,7 @@ __global__ void __launch_bounds__(288, 1) proto_kernel(long long * cyc, int nblk
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t sbase = smem_u32(smem);
     if (threadIdx.x < NBUF) freed[threadIdx.x] = 0;
-    for (int i = threadIdx.x; i < 3 * 32768 / 16; i += 288) reinterpret_cast<uint4 *>(smem)[i] = make_uint4(0x01020304u * (i & 7), 0x80808080u, i, ~i);
+    for (int i = threadIdx.x; i < 3 * 32768 / 16; i += blockDim.x) reinterpret_cast<uint4 *>(smem)[i] = make_uint4(0x01020304u * (i & 7), 0x80808080u, i, ~i);
     fence_proxy_async_smem();
     const uint32_t d_full = smem_u32(&bar[0]), d_empty = smem_u32(&bar[NBUF]);
     if (threadIdx.x == 0) { for (int i = 0; i < NBUF; i++) { mbar_init(d_full + 8 * i, 1); mbar_init(d_empty + 8 * i, 8); } mbar_fence_init(); }
@@ -174,27 +176,39 @@ __global__ void __launch_bounds__(288, 1) proto_kernel(long long * cyc, int nblk
     const uint32_t tm = *reinterpret_cast<volatile uint32_t *>(&slot);
     constexpr int N = 512 / NBUF;
     auto wait = [&](uint32_t b, uint32_t par) {
-        if (V == 1) { while (!mbar_test_wait(b, par)) { } } else mbar_wait(b, par);
+        if (V == 1) { while (!mbar_test_wait(b, par)) { } }
+        else if (V == 16) { while (!mbar_test_wait(b, par)) __nanosleep(40); }
+        else if (V == 17) { while (!mbar_test_wait(b, par)) __nanosleep(200); }
+        else mbar_wait(b, par);
     };
     const long long t0 = clock64();
-    if (warp == 8) {
+    if (warp > 8 && V != 13) {
+        // only V = 13 uses warps 9..11
+    } else if (warp >= 8) {
         const uint32_t idesc = umma_idesc_i8(128, N);
         const uint64_t ad = umma_desc_k_sw128(sbase), bd = umma_desc_k_sw128(sbase + 32768), cd = umma_desc_k_sw128(sbase + 65536);
         bool ok_next = true;
-        for (int blk = 0; blk < nblk; blk++) {
+        // V = 13: FOUR issuing warps, warp 8 + j owns TMEM buffer j (blocks j, j + 4, ...): what a warp loses after its commit
+        // (its next wait only returns once that commit has retired) overlaps the other three warps' issues
+        for (int blk = (V == 13 ? warp - 8 : 0); blk < nblk; blk += (V == 13 ? 4 : 1)) {
             const int j = blk % NBUF, r = blk / NBUF;
             if (V == 3) {
                 // the probe of block blk was issued one iteration ago: its latency ran under the previous block's issue
                 if (!ok_next) mbar_wait(d_empty + 8 * j, (r - 1) & 1);
                 const int b1 = blk + 1;
                 ok_next = b1 / NBUF == 0 ? true : mbar_test_wait(d_empty + 8 * (b1 % NBUF), (b1 / NBUF - 1) & 1);
-            } else if (V == 6) {
+            } else if (V == 6 || V == 12) {
                 if (r > 0) {
                     unsigned int v;
-                    do { asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(smem_u32(&freed[j])) : "memory"); } while (v < 8u * r);
+                    if (V == 6) do { asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(smem_u32(&freed[j])) : "memory"); } while (v < 8u * r);
+                    else        do { asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(v) : "r"(smem_u32(&freed[j])) : "memory"); } while (v < 8u * r);
                 }
-            } else
+            } else if (V == 14) {
+                // no wait at all: does a WAITED-ON d_full alone slow the pipe down?
+            } else {
+            if (V == 0 && blockIdx.x == 0 && lane == 0 && blk >= 256 && blk < 272) cyc[512 + 4 * (blk - 256) + 3] = clock64() - t0;
             if (r > 0) wait(d_empty + 8 * j, (r - 1) & 1);
+            }
             if (V != 7 && V != 9) tc_fence_after_sync();
             if (V == 0 && blockIdx.x == 0 && lane == 0 && blk >= 256 && blk < 272) cyc[512 + 4 * (blk - 256)] = clock64() - t0;
             if (V == 8 || V == 9) {
@@ -228,7 +242,7 @@ __global__ void __launch_bounds__(288, 1) proto_kernel(long long * cyc, int nblk
             if (V >= 2 && blk + 1 < nblk) ok = mbar_test_wait(d_full + 8 * ((blk + 1) % NBUF), ((blk + 1) / NBUF) & 1);
             tc_fence_before_sync();
             __syncwarp();
-            if (V == 6) { if (lane == 0) asm volatile("red.release.cta.shared.add.u32 [%0], 1;" ::"r"(smem_u32(&freed[j])) : "memory"); }
+            if (V == 6 || V == 12) { if (lane == 0) asm volatile("red.release.cta.shared.add.u32 [%0], 1;" ::"r"(smem_u32(&freed[j])) : "memory"); }
             else if (lane == 0) mbar_arrive(d_empty + 8 * j);
         }
     }
@@ -245,7 +259,7 @@ static void run_proto(long long * cyc, const char * what) {
     static long long h[2 * G];
     cudaFuncSetAttribute(proto_kernel<V, NBUF>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * 32768 + 1024);
     for (int rep = 0; rep < 2; rep++) {
-        proto_kernel<V, NBUF><<<G, 288, 3 * 32768 + 1024>>>(cyc, nblk);
+        proto_kernel<V, NBUF><<<G, V == 13 ? 384 : 288, 3 * 32768 + 1024>>>(cyc, nblk);
         cudaError_t e = cudaDeviceSynchronize();
         if (e != cudaSuccess) { printf("CUDA error: %s (%s)\n", cudaGetErrorString(e), what); return; }
     }
@@ -256,8 +270,8 @@ static void run_proto(long long * cyc, const char * what) {
     if (V == 0 && NBUF == 4) {
         static long long tr[64];
         cudaMemcpy(tr, cyc + 512, sizeof(tr), cudaMemcpyDeviceToHost);
-        for (int b = 0; b < 16; b++) printf("      blk %d: MMA warp passes d_empty wait at %lld, issued (3 tcgen05 instr.) +%lld, epilogue warp 0 sees d_full +%lld after the issue began\n",
-                                            256 + b, tr[4 * b], tr[4 * b + 1] - tr[4 * b], tr[4 * b + 2] - tr[4 * b]);
+        for (int b = 0; b < 16; b++) printf("      blk %d: MMA warp reaches the d_empty wait at %lld, passes it +%lld, has issued (3 tcgen05 instr.) +%lld; epilogue warp 0 sees d_full at %lld\n",
+                                            256 + b, tr[4 * b + 3], tr[4 * b] - tr[4 * b + 3], tr[4 * b + 1] - tr[4 * b], tr[4 * b + 2]);
     }
 }
 
@@ -271,6 +285,10 @@ int main_proto(long long * cyc) {
     run_proto<7, 4>(cyc, "try_wait loops, NO tcgen05.fence::after_thread_sync in the MMA warp");
     run_proto<8, 4>(cyc, "try_wait loops, lane 0 predicate instead of elect.sync");
     run_proto<9, 4>(cyc, "try_wait loops, lane 0 predicate, no fence");
+    run_proto<16, 4>(cyc, "test_wait polls with __nanosleep(40) between them");
+    run_proto<17, 4>(cyc, "test_wait polls with __nanosleep(200) between them");
+    run_proto<13, 4>(cyc, "FOUR issuing warps, one per TMEM buffer (try_wait loops)");
+    run_proto<12, 4>(cyc, "d_empty as a shared-memory counter polled with ld.volatile (no acquire)");
     run_proto<10, 4>(cyc, "only lane 0 of each epilogue warp polls d_full");
     run_proto<11, 4>(cyc, "only epilogue warp 0 polls d_full, bar.sync releases the other seven");
     run_proto<3, 4>(cyc, "both sides probe the next block early (test_wait), try_wait only on a miss");
@@ -320,4 +338,107 @@ void main_prim(long long * cyc) {
                              "__syncwarp + arrive + try_wait for that phase"};
     printf("== (C) one warp, back to back, clk per iteration\n");
     for (int k = 0; k < 6; k++) printf("  %-60s %7.1f\n", names[k], (double)h[k] / iters);
+}
+
+
+// ---- (D) one warp issues kernel 3's MMA pair + commit per step and, after the commit, does ONE more thing: what stalls?
+// W = 6 / 7: eight more warps issue back-to-back conflict-free LDS.128 (W = 6: one per ~64 clk per warp, W = 7: flat out)
+// while warp 0 issues: the MMA's operands come out of the same shared memory
+template <int W>
+__global__ void __launch_bounds__(384, 1) after_commit_kernel(long long * cyc, int nblk) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    __shared__ uint32_t slot;
+    __shared__ __align__(8) unsigned long long bar[8];
+    __shared__ volatile unsigned int word;
+    __shared__ volatile int done;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t sbase = smem_u32(smem);
+    if (threadIdx.x == 0) done = 0;
+    for (int i = threadIdx.x; i < 3 * 32768 / 16; i += blockDim.x) reinterpret_cast<uint4 *>(smem)[i] = make_uint4(0x01020304u * (i & 7), 0x80808080u, i, ~i);
+    fence_proxy_async_smem();
+    if (threadIdx.x == 0) { for (int i = 0; i < 8; i++) mbar_init(smem_u32(&bar[i]), 1); mbar_fence_init(); word = 0; }
+    if (warp == 0) { tmem_alloc(smem_u32(&slot), 512); tmem_relinquish(); }
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tm = *reinterpret_cast<volatile uint32_t *>(&slot);
+    if (threadIdx.x == 0) mbar_arrive(smem_u32(&bar[6]));      // bar[6]: phase 0 complete, never touched again
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t idesc = umma_idesc_i8(128, 128);
+        const uint64_t ad = umma_desc_k_sw128(sbase), bd = umma_desc_k_sw128(sbase + 32768), cd = umma_desc_k_sw128(sbase + 65536);
+        unsigned int acc = 0;
+        const long long t0 = clock64();
+        for (int blk = 0; blk < nblk; blk++) {
+            const int j = blk & 3;
+            if (elect_one()) {
+                mma_i8_ss(tm + j * 128, ad + 2 * j, bd + 2 * j, idesc, 0u);
+                mma_i8_ss(tm + j * 128, cd, cd, idesc, 1u);
+                mma_commit(smem_u32(&bar[j]));
+            }
+            __syncwarp();
+            if (W == 1) acc += mbar_test_wait(smem_u32(&bar[6]), 0) ? 1 : 2;
+            if (W == 2) acc += word;
+            if (W == 3) tc_fence_after_sync();
+            if (W == 4) { if (lane == 0) mbar_arrive(smem_u32(&bar[5])); }
+            if (W == 5) acc += mbar_test_wait(smem_u32(&bar[(j + 2) & 3]), 0) ? 1 : 2;     // a barrier commits DO arrive on
+        }
+        const long long t1 = clock64();
+        if (elect_one()) mma_commit(smem_u32(&bar[7]));
+        __syncwarp();
+        mbar_wait(smem_u32(&bar[7]), 0);
+        const long long t2 = clock64();
+        if (threadIdx.x == 0) { cyc[2 * blockIdx.x] = t1 - t0; cyc[2 * blockIdx.x + 1] = t2 - t0 + (acc == 12345u); done = 1; }
+    } else if (warp >= 4 && (W == 6 || W == 7)) {
+        uint4 a = make_uint4(0, 0, 0, 0);
+        unsigned long long n = 0;
+        while (!done) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const uint4 v = lds_u32x4(sbase + 65536 + 16384 + ((warp * 8 + k) & 31) * 512 + lane * 16);
+                a.x ^= v.x; a.y += v.y; a.z ^= v.z; a.w += v.w;
+                if (W == 6) { const long long t = clock64(); while (clock64() - t < 56) { } }
+            }
+            n += 8;
+        }
+        if (lane == 0) cyc[1024 + blockIdx.x * 8 + (warp - 4)] = (long long)n + (a.x + a.y + a.z + a.w == 77u);
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 0) { tc_fence_after_sync(); tmem_dealloc(tm, 512); }
+}
+
+template <int W>
+static void run_after(long long * cyc, const char * what) {
+    const int G = 148, nblk = 2048;
+    static long long h[2 * G];
+    cudaFuncSetAttribute(after_commit_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * 32768 + 1024);
+    for (int rep = 0; rep < 2; rep++) {
+        after_commit_kernel<W><<<G, (W == 6 || W == 7) ? 384 : 128, 3 * 32768 + 1024>>>(cyc, nblk);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("CUDA error: %s (%s)\n", cudaGetErrorString(e), what); return; }
+    }
+    cudaMemcpy(h, cyc, sizeof(h), cudaMemcpyDeviceToHost);
+    double a = 0, b = 0;
+    for (int i = 0; i < G; i++) { a += (double)h[2 * i]; b += (double)h[2 * i + 1]; }
+    printf("  after the commit: %-58s issue %7.1f, complete %7.1f clk per block", what, a / G / nblk, b / G / nblk);
+    if (W == 6 || W == 7) {
+        static long long c8[8];
+        cudaMemcpy(c8, cyc + 1024, sizeof(c8), cudaMemcpyDeviceToHost);
+        double n = 0; for (int i = 0; i < 8; i++) n += (double)c8[i];
+        printf("   (%.1f LDS.128 warp instructions per block = %.0f B/clk of shared-memory reads beside the MMA's 128)", n / nblk, n * 512 / (h[1]));
+    }
+    printf("\n");
+}
+
+void main_after(long long * cyc) {
+    printf("== (D) one warp: MMA pair + commit per block, then one more instruction\n");
+    run_after<0>(cyc, "nothing");
+    run_after<1>(cyc, "mbarrier.test_wait on an unrelated, completed barrier");
+    run_after<2>(cyc, "a volatile shared-memory load");
+    run_after<3>(cyc, "tcgen05.fence::after_thread_sync");
+    run_after<4>(cyc, "mbarrier.arrive on an unrelated barrier");
+    run_after<5>(cyc, "mbarrier.test_wait on a barrier the commits arrive on");
+    run_after<6>(cyc, "nothing; 8 other warps: one LDS.128 per ~64 clk each");
+    run_after<7>(cyc, "nothing; 8 other warps: LDS.128 flat out");
 }
