@@ -495,6 +495,93 @@ def int8_peak():
     return v
 
 
+def siblings_leg(mod, stream, rng, steps, warmup):
+    """Q8_0 and Q4_1 weights through the same op, n = 1 -- a single 4096x4096 op (48 / 32 HBM copies cycled,
+    more than 2x L2) and the LLaMA-7B decode list, one launch per mul_mat (CUDA graph).  One op of every shape is checked
+    against the oracle (oracle/siblings.py, rows 0..255) first.  GB/s = algorithmic bytes (34 or 20 B per block + 4K in, 4M out)."""
+    import torch
+    from oracle import siblings as sib
+    L_ = mod.lib()
+    peak, peak_src = peaks()
+    out = {"hbm_peak_GBps": peak, "hbm_peak_source": peak_src,
+           "kernel": "sib_gemv_kernel (dp4a, activation quantizer fused, one launch per mul_mat)", "timing": "CUDA events on the launching stream"}
+    Lp, per_layer, once = WORKLOADS["llama7b_decode_n1"]
+    for qtype, name in ((sib.TYPE_Q8_0, "q8_0"), (sib.TYPE_Q4_1, "q4_1")):
+        bs = sib.BLOCK_BYTES[qtype]
+
+        def host_blocks(M, K):
+            W = rng.integers(0, 256, size=(M, K // 32, bs), dtype=np.uint8)
+            d = rng.uniform(0.002, 0.02, size=(M, K // 32)).astype(np.float16)
+            W[..., 0:2] = d.view(np.uint8).reshape(M, K // 32, 2)
+            if qtype == sib.TYPE_Q4_1:
+                W[..., 2:4] = rng.uniform(-0.1, 0.1, size=(M, K // 32)).astype(np.float16).view(np.uint8).reshape(M, K // 32, 2)
+            return W
+
+        def leg(shapes, copies):
+            """shapes: [(M, K)] of one layer; copies layers; returns (ms per step, bytes per step, max err)"""
+            host = {sh: host_blocks(*sh) for sh in set(shapes)}
+            ws, total = [], 0
+            for _ in range(copies):
+                for (M, K) in shapes:
+                    W = host[(M, K)]
+                    h = L_.ggml_b200_upload_quant(qtype, W.ctypes.data_as(C.c_void_p), M, K, 0)
+                    if not h:
+                        raise RuntimeError(L_.ggml_b200_last_error().decode())
+                    ws.append((h, M, K))
+                    total += M * (K // 32) * bs + 4 * K + 4 * M
+            xs = {K: torch.randn(K, device="cuda", dtype=torch.float32) for K in {K for (_, K) in shapes}}
+            ys = {M: torch.empty(M, device="cuda", dtype=torch.float32) for M in {M for (M, _) in shapes}}
+            errs = {}
+            for (h, M, K) in ws[:len(shapes)]:
+                rc = L_.ggml_b200_mul_mat_quant(h, C.c_void_p(xs[K].data_ptr()), 1, K * 4, C.c_void_p(ys[M].data_ptr()), M * 4)
+                assert rc == 0, L_.ggml_b200_last_error()
+                stream.synchronize()
+                rows = min(M, 256)
+                want = sib.mul_mat(qtype, host[(M, K)][:rows], xs[K].cpu().numpy()[None, :])[0]
+                got = ys[M].cpu().numpy()[:rows]
+                e = float(np.max(np.abs(got - want)) / max(float(np.max(np.abs(want))), 1e-30))
+                errs[f"{M}x{K}"] = e
+                if not e <= 1e-4:
+                    raise RuntimeError(f"siblings {name}: {M}x{K} differs from the oracle: {e:.3e}")
+
+            def per_op():
+                for (h, M, K) in ws:
+                    L_.ggml_b200_mul_mat_quant(h, C.c_void_p(xs[K].data_ptr()), 1, K * 4, C.c_void_p(ys[M].data_ptr()), M * 4)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=stream):
+                mod.set_stream(torch.cuda.current_stream().cuda_stream)
+                per_op()
+            mod.set_stream(stream.cuda_stream)
+            with torch.cuda.stream(stream):
+                for _ in range(max(3, warmup)):
+                    g.replay()
+            stream.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            with torch.cuda.stream(stream):
+                e0.record(stream)
+                for _ in range(steps):
+                    g.replay()
+                e1.record(stream)
+            stream.synchronize()
+            ms = e0.elapsed_time(e1) / steps
+            del g
+            for (h, _, _) in ws:
+                L_.ggml_b200_free_quant(h)
+            torch.cuda.empty_cache()
+            return ms, total, errs, len(ws)
+
+        ms1, b1, e1_, n1 = leg([(4096, 4096)], 48 if qtype == sib.TYPE_Q4_1 else 32)
+        layer = [(M, K) for (M, K, c) in per_layer for _ in range(c)]
+        ms7, b7, e7_, n7 = leg(layer, Lp)
+        out[name] = {"single_4096_n1": {"GBps": b1 / (ms1 * 1e-3) / 1e9, "frac_of_measured_hbm_peak": b1 / (ms1 * 1e-3) / 1e9 / peak, "us_per_mul_mat": ms1 * 1e3 / n1,
+                                        "hbm_copies_cycled": n1, "oracle_max_rel_err": e1_},
+                     "llama7b_layers_n1": {"GBps": b7 / (ms7 * 1e-3) / 1e9, "frac_of_measured_hbm_peak": b7 / (ms7 * 1e-3) / 1e9 / peak, "ms_per_step": ms7,
+                                           "matmuls_per_step": n7, "algorithmic_bytes_per_step": b7, "oracle_max_rel_err": e7_,
+                                           "note": "the 32 layers' 7 matmuls (the 32000x4096 output op is left out)"},
+                     "bytes_per_block": bs}
+    return out
+
+
 def prefill_leg(mod, stream, rng, steps, warmup, n=512, shapes=None, groups=None, name="llama7b_prefill_n512", host_leg=True):
     """BASELINE configs[2]: LLaMA-7B Q4_0 prefill, n = 512 tokens, tensor-core GEMM path (kernel 1 + kernel 3).
     One pass = the 7 matmuls of a layer + the output matmul; int8 TOPS = 2*M*K*n / time, CUDA events on the
@@ -1314,6 +1401,7 @@ def run_gpu_arm(args, workload, rank, world, local_rank):
                                  "prefill_n512": prefill_leg(mod, stream, rng, max(5, min(args.steps // 10, 20)), args.warmup, shapes=FALCON_PREFILL_SHAPES,
                                                              groups=FALCON_PREFILL_GROUPS, name="falcon7b_prefill_n512", host_leg=False)}
             extra["scaling_base"] = decode_list_leg(mod, stream, rng, "llama65b_decode_n1_rowsharded", max(3, est // 4), args.warmup)
+            extra["siblings"] = siblings_leg(mod, stream, rng, est, args.warmup)
             extra["scaling_base"]["note"] = "the workload of --gpus 2/4/8 on ONE GPU, same step definition: divide the N-GPU values by this GB/s for the strong-scaling efficiency"
         except Exception as e:   # noqa: BLE001
             extra["error"] = str(e)

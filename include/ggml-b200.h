@@ -244,6 +244,31 @@ int          ggml_b200_block_dots_q4_0(const ggml_b200_weight * w, const float *
 int          ggml_b200_fused_checkpoint_q4_0(const ggml_b200_weight * w, const float * x_dev,
                                              int32_t * S_dev, void * blocks34_dev);
 
+/* ---- sibling weight formats: Q8_0 and Q4_1 through the same op ----------------------------
+ * The reference's operator is format blind (ggml_compute_forward_mul_mat_q_f32, ggml.c:11268-11411); quantize_fns[]
+ * (ggml.c:1619-1670) binds per type the activation quantizer and the block dot:
+ *   GGML_TYPE_Q8_0 (8): block_q8_0 weights (ggml.c:902-907) x quantize_row_q8_0 activations, ggml_vec_dot_q8_0_q8_0 (ggml.c:3231-3330)
+ *   GGML_TYPE_Q4_1 (3): block_q4_1 weights (ggml.c:877-883) x quantize_row_q8_1 activations (ggml.c:1318-1480),
+ *                       ggml_vec_dot_q4_1_q8_1 (ggml.c:2609-2734)
+ * `type` takes the reference's enum values (ggml.h:230-242).  Decode path (dp4a GEMV, the activation quantizer fused into
+ * the kernel, passes of 4 columns); no tensor-core path for these formats. */
+#define GGML_B200_TYPE_Q4_1 3
+#define GGML_B200_TYPE_Q8_0 8
+typedef struct ggml_b200_qweight ggml_b200_qweight;
+/* blocks: M rows of K/32 reference-format blocks (34 B / 20 B), row stride nb1 bytes (0 = contiguous); host memory */
+ggml_b200_qweight * ggml_b200_upload_quant(int type, const void * blocks, int64_t M, int64_t K, size_t nb1);
+void         ggml_b200_free_quant(ggml_b200_qweight * w);
+int          ggml_b200_quant_type(const ggml_b200_qweight * w);
+size_t       ggml_b200_quant_bytes(const ggml_b200_qweight * w);      /* device bytes of the planes */
+/* dst[c][m] = row m of w . column c of x: same argument meaning as ggml_b200_mul_mat_q4_0 (device pointers, byte strides) */
+int          ggml_b200_mul_mat_quant(const ggml_b200_qweight * w, const float * x_dev, int64_t n, size_t nb11,
+                                     float * y_dev, size_t nb1);
+/* parity checkpoints: the same kernel with the S_b store enabled (S_dev: [n][M][K/32] int32), and the activation blocks
+ * the fused quantizer forms, in the reference's format (block_q8_0 34 B for Q8_0, block_q8_1 40 B for Q4_1) */
+int          ggml_b200_block_dots_quant(const ggml_b200_qweight * w, const float * x_dev, int64_t n, size_t nb11,
+                                        int32_t * S_dev, float * y_dev, size_t nb1);
+int          ggml_b200_quantize_dot_blocks(int type, const float * x_dev, int64_t n, int64_t K, size_t nb11, void * blocks_dev);
+
 /* ---- multi-GPU: row shards + all-gather ---------------------------------------------------
  * replaces the row-split placement and gather of GGML_BACKEND_GPU_SPLIT (ggml_cuda_set_tensor_split
  * ggml-cuda.cu:1863-1882, slices :2780-2797, gather by cudaMemcpyAsync :2514-2540) with one

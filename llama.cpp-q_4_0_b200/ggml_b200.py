@@ -75,6 +75,13 @@ def _load() -> C.CDLL:
         "ggml_b200_mul_mat_q4_0": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
         "ggml_b200_mul_mat_q4_0_host": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
         "ggml_b200_mul_mat_q4_0_static": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
+        "ggml_b200_upload_quant": (_vp, [C.c_int, _vp, _i64, _i64, _sz]),
+        "ggml_b200_free_quant": (None, [_vp]),
+        "ggml_b200_quant_type": (C.c_int, [_vp]),
+        "ggml_b200_quant_bytes": (_sz, [_vp]),
+        "ggml_b200_mul_mat_quant": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _sz]),
+        "ggml_b200_block_dots_quant": (C.c_int, [_vp, _vp, _i64, _sz, _vp, _vp, _sz]),
+        "ggml_b200_quantize_dot_blocks": (C.c_int, [C.c_int, _vp, _i64, _i64, _sz, _vp]),
         "ggml_b200_static_max_elems": (_sz, []),
         "ggml_b200_block_dots_q4_0": (C.c_int, [_vp, _vp, _i64, _sz, _vp, C.c_int]),
         "ggml_b200_fused_checkpoint_q4_0": (C.c_int, [_vp, _vp, _vp, _vp]),
@@ -270,6 +277,65 @@ class Weight:
             self.free()
         except Exception:
             pass
+
+
+TYPE_Q4_1, TYPE_Q8_0 = 3, 8          # the reference's ggml_type values (ggml.h:230-242)
+QUANT_BLOCK_BYTES = {TYPE_Q4_1: 20, TYPE_Q8_0: 34}
+DOT_BLOCK_BYTES = {TYPE_Q4_1: 40, TYPE_Q8_0: 34}     # block_q8_1 / block_q8_0
+
+
+class QuantWeight:
+    """A device-resident Q8_0 or Q4_1 weight (ggml_b200_upload_quant): the op's sibling formats."""
+
+    def __init__(self, qtype: int, blocks: np.ndarray):
+        blocks = np.ascontiguousarray(blocks, dtype=np.uint8)
+        assert blocks.ndim == 3 and blocks.shape[2] == QUANT_BLOCK_BYTES[qtype]
+        self.type, self.M, self.K = qtype, blocks.shape[0], blocks.shape[1] * QK
+        self.h = lib().ggml_b200_upload_quant(qtype, blocks.ctypes.data_as(_vp), self.M, self.K, blocks.shape[1] * blocks.shape[2])
+        if not self.h:
+            raise B200Error(ERR_ARG, lib().ggml_b200_last_error().decode(errors="replace"))
+
+    @property
+    def device_bytes(self) -> int:
+        return int(lib().ggml_b200_quant_bytes(self.h))
+
+    def mul_mat(self, X: np.ndarray, checkpoint: bool = False):
+        """X [n][K] f32 -> Y [n][M] f32 (and S [n][M][K/32] int32 with checkpoint=True)."""
+        X = np.ascontiguousarray(X, dtype=np.float32)
+        n = X.shape[0]
+        assert X.shape[1] == self.K
+        xd = DevBuf.from_numpy(X) if n else DevBuf(16)
+        yd = DevBuf(max(16, n * self.M * 4))
+        if checkpoint:
+            sd = DevBuf(max(16, n * self.M * (self.K // QK) * 4))
+            _check(lib().ggml_b200_block_dots_quant(self.h, xd.ptr, n, self.K * 4, sd.ptr, yd.ptr, self.M * 4))
+            synchronize()
+            return yd.to_numpy(np.float32, (n, self.M)), sd.to_numpy(np.int32, (n, self.M, self.K // QK))
+        _check(lib().ggml_b200_mul_mat_quant(self.h, xd.ptr, n, self.K * 4, yd.ptr, self.M * 4))
+        synchronize()
+        return yd.to_numpy(np.float32, (n, self.M))
+
+    def free(self) -> None:
+        if self.h:
+            lib().ggml_b200_free_quant(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def quantize_dot_blocks(qtype: int, x: np.ndarray) -> np.ndarray:
+    """The activation blocks the sibling kernels' fused quantizer forms, reference format: uint8 [n][K/32][34 | 40]."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    n, K = x.shape
+    xd = DevBuf.from_numpy(x)
+    out = DevBuf(n * (K // QK) * DOT_BLOCK_BYTES[qtype])
+    _check(lib().ggml_b200_quantize_dot_blocks(qtype, xd.ptr, n, K, K * 4, out.ptr))
+    synchronize()
+    return out.to_numpy(np.uint8, (n, K // QK, DOT_BLOCK_BYTES[qtype]))
 
 
 def quantize_q8_0(x: np.ndarray) -> np.ndarray:

@@ -213,7 +213,56 @@ class Ref:
         L.ref_mm_y.argtypes = [_vp]
         L.ref_mm_free.restype = None
         L.ref_mm_free.argtypes = [_vp]
+        if hasattr(L, "ref_type_vec_dot"):          # sibling formats (ref_shim.c, second half)
+            L.ref_type_block_bytes.restype = C.c_int
+            L.ref_type_block_bytes.argtypes = [C.c_int]
+            L.ref_type_dot_block_bytes.restype = C.c_int
+            L.ref_type_dot_block_bytes.argtypes = [C.c_int]
+            for name in ("ref_type_quantize_row", "ref_type_dequantize_row", "ref_type_quantize_row_dot"):
+                getattr(L, name).restype = None
+                getattr(L, name).argtypes = [C.c_int, _vp, _vp, C.c_int]
+            L.ref_type_vec_dot.restype = C.c_float
+            L.ref_type_vec_dot.argtypes = [C.c_int, C.c_int, _vp, _vp]
+            L.ref_mm_create_type.restype = _vp
+            L.ref_mm_create_type.argtypes = [C.c_int, C.c_int64, C.c_int64, C.c_int64, _vp]
         L.ref_init()
+
+    # -- sibling formats: the reference's own functions by ggml_type (3 = Q4_1, 8 = Q8_0)
+    def type_quantize(self, qtype: int, x: np.ndarray) -> np.ndarray:
+        """quantize_row_q of the type (the weight-side codec): [..., K] f32 -> uint8 [..., K/32, block bytes]."""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        bs = int(self.L.ref_type_block_bytes(qtype))
+        out = np.empty(x.shape[:-1] + (x.shape[-1] // QK, bs), dtype=np.uint8)
+        self.L.ref_type_quantize_row(qtype, _ptr(x), _ptr(out), x.size)
+        return out
+
+    def type_quantize_dot(self, qtype: int, x: np.ndarray) -> np.ndarray:
+        """quantize_row_q_dot of the type (q8_0 for Q8_0, q8_1 for Q4_1), the build host's SIMD branch."""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        bs = int(self.L.ref_type_dot_block_bytes(qtype))
+        out = np.empty(x.shape[:-1] + (x.shape[-1] // QK, bs), dtype=np.uint8)
+        self.L.ref_type_quantize_row_dot(qtype, _ptr(x), _ptr(out), x.size)
+        return out
+
+    def type_vec_dot(self, qtype: int, w_row: np.ndarray, q_row: np.ndarray) -> float:
+        w_row = np.ascontiguousarray(w_row, dtype=np.uint8)
+        q_row = np.ascontiguousarray(q_row, dtype=np.uint8)
+        k = w_row.shape[0] * QK
+        return float(self.L.ref_type_vec_dot(qtype, k, _ptr(w_row), _ptr(q_row)))
+
+    def type_mul_mat(self, qtype: int, W: np.ndarray, X: np.ndarray, n_threads: int = 1) -> np.ndarray:
+        """The whole operator through the reference's graph API for a weight of `qtype`."""
+        W = np.ascontiguousarray(W, dtype=np.uint8)
+        X = np.ascontiguousarray(X, dtype=np.float32)
+        M, nbk = W.shape[0], W.shape[1]
+        n, K = X.shape
+        assert K == nbk * QK
+        h = self.L.ref_mm_create_type(qtype, M, K, n, _ptr(W))
+        assert h
+        Y = np.empty((n, M), dtype=np.float32)
+        self.L.ref_mm_run(h, _ptr(X), _ptr(Y), n_threads)
+        self.L.ref_mm_free(h)
+        return Y
 
     def fp16_to_fp32(self, h: int) -> float:
         return float(self.L.ref_fp16_to_fp32(h))

@@ -137,3 +137,47 @@ void ref_mm_free(struct ref_mm * h) {
 }
 
 int64_t ref_time_us(void) { ref_init(); return ggml_time_us(); }
+
+/* ---- sibling formats: the same hooks by type ------------------------------------------------
+ * quantize_fns[] (ggml.c:1619-1670): Q4_1 -> quantize_row_q_dot = quantize_row_q8_1, vec_dot_q = ggml_vec_dot_q4_1_q8_1;
+ * Q8_0 -> quantize_row_q8_0, ggml_vec_dot_q8_0_q8_0. */
+int ref_type_block_bytes(int type) { ref_init(); return (int)ggml_type_size((enum ggml_type)type); }
+int ref_type_dot_block_bytes(int type) {
+    ref_init();
+    return (int)ggml_type_size(ggml_internal_get_quantize_fn((size_t)type).vec_dot_type);
+}
+void ref_type_quantize_row(int type, const float * x, void * y, int k) {
+    ref_init();
+    ggml_internal_get_quantize_fn((size_t)type).quantize_row_q(x, y, k);
+}
+void ref_type_dequantize_row(int type, const void * x, float * y, int k) {
+    ref_init();
+    ggml_internal_get_quantize_fn((size_t)type).dequantize_row_q(x, y, k);
+}
+void ref_type_quantize_row_dot(int type, const float * x, void * y, int k) {
+    ref_init();
+    ggml_internal_get_quantize_fn((size_t)type).quantize_row_q_dot(x, y, k);
+}
+float ref_type_vec_dot(int type, int k, const void * x, const void * y) {
+    ref_init();
+    float s = 0.0f;
+    ggml_internal_get_quantize_fn((size_t)type).vec_dot_q(k, &s, x, y);
+    return s;
+}
+/* the whole operator for a weight of `type` (W: M * K/32 blocks of that type, contiguous) */
+struct ref_mm * ref_mm_create_type(int type, int64_t M, int64_t K, int64_t n, const void * W) {
+    ref_init();
+    struct ref_mm * h = (struct ref_mm *)calloc(1, sizeof(*h));
+    const size_t wbytes = (size_t)M * (K / 32) * ggml_type_size((enum ggml_type)type);
+    size_t ctx_size = wbytes + (size_t)n * K * 4 + (size_t)n * M * 4 + (size_t)n * (K / 32) * 40 + (16u << 20);
+    struct ggml_init_params p = { ctx_size, NULL, false };
+    h->ctx = ggml_init(p);
+    if (!h->ctx) { free(h); return NULL; }
+    h->M = M; h->K = K; h->n = n;
+    h->w = ggml_new_tensor_2d(h->ctx, (enum ggml_type)type, K, M);
+    memcpy(h->w->data, W, wbytes);
+    h->x = ggml_new_tensor_2d(h->ctx, GGML_TYPE_F32, K, n);
+    h->y = ggml_mul_mat(h->ctx, h->w, h->x);
+    h->gf = ggml_build_forward(h->y);
+    return h;
+}

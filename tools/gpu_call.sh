@@ -1,6 +1,12 @@
-test llama.cpp-q_4_0_b200/lib/libggml_b200.so -nt llama.cpp-q_4_0_b200/csrc/gemm_q4_0_tc3.cuh || { echo STALE LIB; exit 9; }
+test llama.cpp-q_4_0_b200/lib/libggml_b200.so -nt llama.cpp-q_4_0_b200/csrc/siblings.cu || { echo STALE LIB; exit 9; }
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_zz_no_alloc.py -x -q -m gpu -k "gemm or auto_dispatch or same_src1_batched or static" > gpurun_out/r02_pytest_gemm_v3.log 2>&1; tail -3 gpurun_out/r02_pytest_gemm_v3.log
-timeout 600 python tools/bench_gemm.py > gpurun_out/r02_bench_gemm_v3.log 2>&1; cat gpurun_out/r02_bench_gemm_v3.log; cp gpurun_out/bench_gemm.json gpurun_out/r02_bench_gemm_v3.json
-timeout 600 python tools/bench_gemm.py gemm_v3=0 > gpurun_out/r02_bench_gemm_v1.log 2>&1; cat gpurun_out/r02_bench_gemm_v1.log
-timeout 120 python tools/trace_gemm.py > gpurun_out/r02_trace_gemm_v3.log 2>&1
+timeout 900 python -m pytest tests/test_gpu_siblings.py -x -q -m gpu > gpurun_out/r02_pytest_siblings.log 2>&1; tail -2 gpurun_out/r02_pytest_siblings.log
+for c in 1 2; do
+GGML_B200_SIB_CTAS=$c timeout 600 python - > gpurun_out/r02_bench_siblings_c$c.log 2>&1 <<'PY'
+import json, numpy as np, torch, bench
+mod = bench.load_binding(); mod.init(0)
+stream = torch.cuda.Stream(); mod.set_stream(stream.cuda_stream)
+print(json.dumps(bench.siblings_leg(mod, stream, np.random.default_rng(1), 20, 3), indent=1))
+PY
+echo "== ctas $c"; grep "GBps\|us_per\|ms_per\|q8_0\|q4_1\|Error" gpurun_out/r02_bench_siblings_c$c.log
+done
