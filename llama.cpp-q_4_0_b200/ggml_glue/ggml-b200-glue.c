@@ -34,6 +34,7 @@
 #include "../../include/ggml-b200.h"
 
 #define B200_MAGIC_WEIGHT ((void *)(uintptr_t)0xB200B200u)   /* extra->data_device[1]: data_device[0] is a ggml_b200_weight */
+#define B200_MAGIC_QWEIGHT ((void *)(uintptr_t)0xB200B208u)  /* extra->data_device[1]: data_device[0] is a ggml_b200_qweight (Q8_0 / Q4_1) */
 #define B200_MAGIC_HOST   ((void *)(uintptr_t)0xB200C0DEu)   /* extra->data_device[1]: data_device[0] is our host copy */
 #define B200_MAGIC_DEVF32 ((void *)(uintptr_t)0xB200F320u)   /* ... data_device[0] = device copy of an F32 weight, [2] = our host copy (tensor->data) */
 #define B200_MAGIC_ACT    ((void *)(uintptr_t)0xB200AC70u)   /* ... data_device[0] = device buffer of an activation, [2] != NULL: tensor->data holds the same values */
@@ -109,6 +110,7 @@ void ggml_cuda_free_scratch(void) {
 }
 
 static ggml_b200_weight * weight_of(const struct ggml_tensor * t);
+static ggml_b200_qweight * qweight_of(const struct ggml_tensor * t);
 static int is_act(const struct ggml_tensor * t) {     /* (by the extra alone: the backend tag flips to CPU once the host buffer holds the values too) */
     return t != NULL && t->extra != NULL && ((const struct ggml_tensor_extra_gpu *)t->extra)->data_device[1] == B200_MAGIC_ACT;
 }
@@ -131,7 +133,7 @@ static int node_supported(const struct ggml_tensor * t) {
             return f32_contig(t->src0) && f32_contig(t->src1) && t->src0->ne[0] == t->src1->ne[0] &&
                    (ggml_nelements(t->src1) == ggml_nelements(t->src0) || ggml_nelements(t->src1) == t->src1->ne[0]);
         case GGML_OP_MUL_MAT:
-            return weight_of(t->src0) != NULL && t->src0->type == GGML_TYPE_Q4_0 && f32_contig(t->src1) &&
+            return ((weight_of(t->src0) != NULL && t->src0->type == GGML_TYPE_Q4_0) || qweight_of(t->src0) != NULL) && f32_contig(t->src1) &&
                    t->src0->ne[2] == 1 && t->src0->ne[3] == 1 && t->src1->ne[2] == 1 && t->src1->ne[3] == 1 && t->src0->ne[0] % 64 == 0;
         default:
             return 0;
@@ -193,6 +195,14 @@ static ggml_b200_weight * weight_of(const struct ggml_tensor * t) {
     return e->data_device[1] == B200_MAGIC_WEIGHT ? (ggml_b200_weight *)e->data_device[0] : NULL;
 }
 
+/* the sibling formats: Q8_0 and Q4_1 weights, single GPU */
+static ggml_b200_qweight * qweight_of(const struct ggml_tensor * t) {
+    if (t == NULL || t->extra == NULL) return NULL;
+    if (t->backend != GGML_BACKEND_GPU && t->backend != GGML_BACKEND_GPU_SPLIT) return NULL;
+    const struct ggml_tensor_extra_gpu * e = (const struct ggml_tensor_extra_gpu *)t->extra;
+    return e->data_device[1] == B200_MAGIC_QWEIGHT ? (ggml_b200_qweight *)e->data_device[0] : NULL;
+}
+
 /* ggml_cuda_transform_tensor (ggml-cuda.cu:2766-2809): the loader hands over the host bytes of a tensor it
  * tagged GPU / GPU_SPLIT.  The callee must copy: the caller frees `data` right after (llama.cpp:682-684). */
 void ggml_cuda_transform_tensor(void * data, struct ggml_tensor * tensor) {
@@ -211,6 +221,19 @@ void ggml_cuda_transform_tensor(void * data, struct ggml_tensor * tensor) {
         }
         extra->data_device[0] = w;
         extra->data_device[1] = B200_MAGIC_WEIGHT;
+        tensor->extra = extra;
+        return;
+    }
+    const int sib_2d = (tensor->type == GGML_TYPE_Q8_0 || tensor->type == GGML_TYPE_Q4_1) && tensor->ne[2] == 1 && tensor->ne[3] == 1 &&
+                       (tensor->ne[0] % 64) == 0 && ggml_b200_comm_world() <= 1;
+    if (g_ready && sib_2d) {
+        ggml_b200_qweight * w = ggml_b200_upload_quant((int)tensor->type, data, tensor->ne[1], tensor->ne[0], tensor->nb[1]);
+        if (w == NULL) {
+            fprintf(stderr, "ggml-b200: upload of %s failed: %s\n", tensor->name, ggml_b200_last_error());
+            exit(1);
+        }
+        extra->data_device[0] = w;
+        extra->data_device[1] = B200_MAGIC_QWEIGHT;
         tensor->extra = extra;
         return;
     }
@@ -245,6 +268,7 @@ void ggml_cuda_free_data(struct ggml_tensor * tensor) {
     if (tensor == NULL || tensor->extra == NULL) return;
     struct ggml_tensor_extra_gpu * e = (struct ggml_tensor_extra_gpu *)tensor->extra;
     if (e->data_device[1] == B200_MAGIC_WEIGHT) ggml_b200_free_weight((ggml_b200_weight *)e->data_device[0]);
+    else if (e->data_device[1] == B200_MAGIC_QWEIGHT) ggml_b200_free_quant((ggml_b200_qweight *)e->data_device[0]);
     else if (e->data_device[1] == B200_MAGIC_HOST) { free(e->data_device[0]); if (tensor->data == e->data_device[0]) tensor->data = NULL; }
     else if (e->data_device[1] == B200_MAGIC_DEVF32) { ggml_b200_dev_free(e->data_device[0]); free(e->data_device[2]); if (tensor->data == e->data_device[2]) tensor->data = NULL; }
     else return;   /* not ours */
@@ -258,7 +282,7 @@ void ggml_cuda_free_data(struct ggml_tensor * tensor) {
 bool ggml_cuda_can_mul_mat(const struct ggml_tensor * src0, const struct ggml_tensor * src1, struct ggml_tensor * dst) {
     /* 2-D only (every Q4_0 weight of the models is; a batched src1 falls through to the CPU code instead of aborting),
      * K a multiple of 64 (ggml.c:2343-2344) */
-    return g_ready && weight_of(src0) != NULL && src0->type == GGML_TYPE_Q4_0 && src1->type == GGML_TYPE_F32 &&
+    return g_ready && ((weight_of(src0) != NULL && src0->type == GGML_TYPE_Q4_0) || qweight_of(src0) != NULL) && src1->type == GGML_TYPE_F32 &&
            dst->type == GGML_TYPE_F32 && (src1->backend == GGML_BACKEND_CPU || is_act(src1)) && (dst->backend == GGML_BACKEND_CPU || is_act(dst)) &&
            src0->ne[2] == 1 && src0->ne[3] == 1 && src1->ne[2] == 1 && src1->ne[3] == 1 && src0->ne[0] % 64 == 0;
 }
@@ -281,12 +305,25 @@ static void ensure_dev(float ** p, size_t * cap, size_t need) {
 void ggml_cuda_mul_mat(const struct ggml_tensor * src0, const struct ggml_tensor * src1, struct ggml_tensor * dst, void * wdata, size_t wsize) {
     (void)wdata; (void)wsize;
     ggml_b200_weight * w = weight_of(src0);
-    GGML_ASSERT(w != NULL);
+    ggml_b200_qweight * qw = qweight_of(src0);
+    GGML_ASSERT(w != NULL || qw != NULL);
     /* the asserts of the CPU op (ggml.c:11267-11290) that matter here */
     GGML_ASSERT(src1->nb[0] == sizeof(float) && dst->nb[0] == sizeof(float));
     GGML_ASSERT(src1->ne[2] == 1 && src1->ne[3] == 1 && dst->ne[2] == 1 && dst->ne[3] == 1);
     GGML_ASSERT(src1->ne[0] == src0->ne[0] && dst->ne[0] == src0->ne[1] && dst->ne[1] == src1->ne[1]);
     const int64_t n = src1->ne[1], K = src0->ne[0], M = src0->ne[1];
+    if (qw != NULL) {
+        /* Q8_0 / Q4_1: activations to the device, the op, dst back (no host-pointer entry point for the siblings) */
+        ensure_dev(&g_x_dev, &g_x_cap, (size_t)n * K * sizeof(float));
+        ensure_dev(&g_y_dev, &g_y_cap, (size_t)n * M * sizeof(float));
+        for (int64_t c = 0; c < n; c++)
+            B200_CHECK(ggml_b200_memcpy_h2d(g_x_dev + c * K, (const char *)src1->data + c * src1->nb[1], (size_t)K * sizeof(float)));
+        B200_CHECK(ggml_b200_mul_mat_quant(qw, g_x_dev, n, (size_t)K * sizeof(float), g_y_dev, (size_t)M * sizeof(float)));
+        B200_CHECK(ggml_b200_synchronize());
+        for (int64_t c = 0; c < n; c++)
+            B200_CHECK(ggml_b200_memcpy_d2h((char *)dst->data + c * dst->nb[1], g_y_dev + c * M, (size_t)M * sizeof(float)));
+        return;
+    }
     if (ggml_b200_comm_world() > 1 && ggml_b200_weight_rows(w) != M) {
         /* row shard: replicate x on the device, sharded op + NCCL all-gather, full dst back to the host */
         ensure_dev(&g_x_dev, &g_x_cap, (size_t)n * K * sizeof(float));
@@ -321,6 +358,7 @@ enum { PL_MUL_MAT, PL_RMS_NORM, PL_RMS_NORM_MUL, PL_MUL, PL_ADD, PL_SILU, PL_SIL
 struct plan {
     int kind;
     ggml_b200_weight * w;
+    ggml_b200_qweight * qw;          /* a Q8_0 / Q4_1 weight instead of w */
     const float * a, * b;           /* device sources */
     float * y, * y2;                /* device results (y2: the second result of a fused pair) */
     int64_t n, nb, ncols, nrows, K, M;
@@ -364,7 +402,8 @@ static void issue(const struct plan * p) {
     for (int i = 0; i < 2; i++) if (p->h2d_bytes[i]) B200_CHECK(ggml_b200_memcpy_h2d_async(p->h2d_dst[i], p->h2d_src[i], p->h2d_bytes[i]));
     switch (p->kind) {
         case PL_MUL_MAT:
-            if (p->sharded) B200_CHECK(ggml_b200_mul_mat_q4_0_sharded(p->w, p->a, p->n, (size_t)p->K * sizeof(float), p->y, (size_t)p->M * sizeof(float)));
+            if (p->qw)      B200_CHECK(ggml_b200_mul_mat_quant(p->qw, p->a, p->n, (size_t)p->K * sizeof(float), p->y, (size_t)p->M * sizeof(float)));
+            else if (p->sharded) B200_CHECK(ggml_b200_mul_mat_q4_0_sharded(p->w, p->a, p->n, (size_t)p->K * sizeof(float), p->y, (size_t)p->M * sizeof(float)));
             else            B200_CHECK(ggml_b200_mul_mat_q4_0(p->w, p->a, p->n, (size_t)p->K * sizeof(float), p->y, (size_t)p->M * sizeof(float)));
             break;
         case PL_RMS_NORM:     B200_CHECK(ggml_b200_rms_norm_f32(p->a, p->y, p->ncols, p->nrows, 1e-6f)); break;      /* eps: ggml.c:10417 */
@@ -505,11 +544,12 @@ static void device_node(struct ggml_tensor * t) {
         case GGML_OP_MUL_MAT: {
             p->kind = PL_MUL_MAT;
             p->w = weight_of(t->src0);
+            p->qw = qweight_of(t->src0);
             p->K = t->src0->ne[0]; p->M = t->src0->ne[1]; p->n = t->src1->ne[1];
             GGML_ASSERT(t->src1->ne[0] == p->K && t->ne[0] == p->M && t->ne[1] == p->n);
             p->a = plan_src(p, t->src1, 0);
             p->y = plan_dst(p, t);
-            p->sharded = ggml_b200_comm_world() > 1 && ggml_b200_weight_rows(p->w) != p->M;
+            p->sharded = p->w != NULL && ggml_b200_comm_world() > 1 && ggml_b200_weight_rows(p->w) != p->M;
         } break;
         case GGML_OP_RMS_NORM:
             p->kind = PL_RMS_NORM; p->ncols = t->src0->ne[0]; p->nrows = ggml_nrows(t->src0);

@@ -101,6 +101,25 @@ def test_reference_graph_runs_the_op_on_the_gpu(b200, port, ref, M, K, n, offloa
     assert float(np.max(d / colmax)) <= 1e-4
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("qtype", [8, 3])
+@pytest.mark.parametrize("M,K,n", [(512, 1024, 1), (4096, 4544 - 4544 % 64 + 64, 1), (300, 1088, 7)])
+def test_reference_graph_runs_the_sibling_formats_on_the_gpu(b200, ref, qtype, M, K, n):
+    """SURVEY 8f-4 through the seam: a Q8_0 / Q4_1 weight uploaded by ggml_cuda_transform_tensor, the op taken by the hook
+    inside the reference's ggml_graph_compute; against the same build's CPU path (the reference's own vec_dot)."""
+    G = _glue()
+    rng = np.random.default_rng(900 + M + qtype)
+    W = ref.type_quantize(qtype, rng.standard_normal((M, K), dtype=np.float32) * np.float32(0.05))
+    X = rng.standard_normal((n, K), dtype=np.float32)
+    before = b200.launch_count()
+    Yg = _run(G, W, qtype, M, K, X, offload=1)
+    assert b200.launch_count() - before >= 2, "the op did not reach the CUDA kernels"
+    Yc = _run(G, W, qtype, M, K, X, offload=0, threads=4)
+    d = np.abs(Yg.astype(np.float64) - Yc)
+    colmax = np.max(np.abs(Yc), axis=1, keepdims=True)
+    assert float(np.max(d / colmax)) <= 1e-4
+
+
 # ---------------------------------------------------------------------------- whole model through the seam (SURVEY 8f-1)
 LLAMA_CPU_SO = os.path.join(PKG, "ggml_glue", "_build", "libllama_ref_cpu.so")
 LLAMA_B200_SO = os.path.join(PKG, "ggml_glue", "_build", "libllama_b200.so")
