@@ -1,0 +1,26 @@
+"""Runs tests/glue/falcon_driver.cpp's tiny_falcon_run from one of the two builds of the reference's arch/falcon/falcon.cpp
+(ggml_glue/_build/libfalcon_ref_cpu.so = plain CPU reference, libfalcon_b200.so = the same source with the loader tag,
+-DGGML_USE_CUBLAS over ggml-b200-glue.c + libggml_b200.so) in its own process and saves the prompt / decode logits.
+usage: run_tiny_falcon.py <lib.so> <model.bin> <n_prompt> <out.npy> [n_threads]"""
+import ctypes as C
+import sys
+
+import numpy as np
+
+lib, model, n_prompt, out = sys.argv[1], sys.argv[2], int(sys.argv[3]), sys.argv[4]
+threads = int(sys.argv[5]) if len(sys.argv) > 5 else 4
+L = C.CDLL(lib)
+L.tiny_falcon_run.restype = C.c_int
+NV = 512
+toks = [(7 * i + 3) % NV for i in range(n_prompt)]
+arr = (C.c_int * n_prompt)(*toks)
+lp, ld = np.zeros(NV, np.float32), np.zeros(NV, np.float32)
+rc = L.tiny_falcon_run(model.encode(), arr, n_prompt, 11, threads, lp.ctypes.data_as(C.c_void_p), ld.ctypes.data_as(C.c_void_p), NV)
+if rc != 0:
+    sys.exit("tiny_falcon_run failed: %d" % rc)
+np.save(out, np.stack([lp, ld]))
+try:                                   # the drop-in build links libggml_b200.so: how many of its kernels ran in this process
+    L.ggml_b200_launch_count.restype = C.c_uint64
+    print("b200_kernel_launches=%d" % L.ggml_b200_launch_count(), file=sys.stderr)
+except AttributeError:
+    pass

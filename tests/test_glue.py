@@ -221,6 +221,97 @@ def _layer_logits(G, dims, offload, device_acts, x, threads=4):
     return logits
 
 
+# ---------------------------------------------------------------------------- arch/falcon through the seam
+FALCON_CPU_SO = os.path.join(PKG, "ggml_glue", "_build", "libfalcon_ref_cpu.so")
+FALCON_B200_SO = os.path.join(PKG, "ggml_glue", "_build", "libfalcon_b200.so")
+
+
+def _falcon_model(tmp_path, size="tiny"):
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests", "glue"))
+    import make_tiny_falcon
+    if not (os.path.exists(FALCON_CPU_SO) and os.path.exists(FALCON_B200_SO)):
+        pytest.skip("ggml_glue/_build/libfalcon_*.so not built (needs /root/reference at build time)")
+    hp = dict(make_tiny_falcon.HP)
+    if size == "7b":
+        hp.update(n_embd=4544, n_head=71)        # Falcon-7B's own shapes: 4672x4544, 4544x4544, 18176x4544, 4544x18176
+    return make_tiny_falcon.write_model(str(tmp_path / ("falcon_%s_q4_0.bin" % size)), hp=hp)
+
+
+def _falcon_logits(tmp_path, lib, n_prompt, model, threads=4, timeout=1800):
+    import subprocess
+    import sys
+    out = str(tmp_path / (os.path.basename(lib) + ".%d.npy" % n_prompt))
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "glue", "run_tiny_falcon.py"), lib, model, str(n_prompt), out, str(threads)],
+                       capture_output=True, text=True, timeout=timeout)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    return np.load(out), r.stderr
+
+
+def test_tiny_falcon_through_the_seam_without_a_gpu_is_the_cpu_reference(tmp_path):
+    """arch/falcon/falcon.cpp (loader + graph builder, falcon_eval) built -DGGML_USE_CUBLAS over the glue with the loader
+    tag applied (tests/glue/patch_falcon.py): on a host without a B200 nothing is offloaded (ggml_cuda_transform_tensor
+    hands the bytes back to the CPU code) and the logits are bit-identical to the plain CPU build."""
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("GPU present: covered by the gpu-marked twin")
+    except ImportError:
+        pass
+    model = _falcon_model(tmp_path)
+    cpu, _ = _falcon_logits(tmp_path, FALCON_CPU_SO, 9, model)
+    seam, _ = _falcon_logits(tmp_path, FALCON_B200_SO, 9, model)
+    assert np.isfinite(cpu).all() and np.abs(cpu).max() > 1.0
+    assert np.array_equal(cpu, seam)
+
+
+def _launches(log):
+    import re
+    m = re.search(r"b200_kernel_launches=(\d+)", log)
+    return int(m.group(1)) if m else 0
+
+
+def _compare_logits(cpu, gpu, bar):
+    for i in range(2):
+        scale = float(np.abs(cpu[i]).max())
+        err = float(np.abs(cpu[i] - gpu[i]).max()) / scale
+        cos = float(np.dot(cpu[i], gpu[i]) / (np.linalg.norm(cpu[i]) * np.linalg.norm(gpu[i])))
+        assert err <= bar and cos >= 0.9995, f"eval {i}: max|dlogit|/max|logit| = {err:.3e}, cosine = {cos:.6f}"
+        assert int(cpu[i].argmax()) == int(gpu[i].argmax())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_prompt", [6, 40])
+def test_tiny_falcon_offloaded_to_b200_matches_cpu_reference(b200, tmp_path, n_prompt):
+    """Drop-in for an arch/* model: a 32-layer multi-query Falcon (Q4_0, the reference's file format) through the
+    reference's own loader and falcon_eval; the 4 matrices of every layer and lm_head are uploaded by the loader tag and
+    all 129 Q4_0 matmuls per eval run on the B200 (n = 6: GEMV columns, n = 40: tcgen05 GEMM, decode n = 1: the one-launch
+    host path).  Same bar as the LLaMA twin (the activations are re-quantized before every matmul)."""
+    model = _falcon_model(tmp_path)
+    cpu, _ = _falcon_logits(tmp_path, FALCON_CPU_SO, n_prompt, model)
+    gpu, log = _falcon_logits(tmp_path, FALCON_B200_SO, n_prompt, model)
+    assert np.isfinite(gpu).all()
+    _compare_logits(cpu, gpu, 3e-2)
+    assert _launches(log) >= 129 + 2 * 129, log[-500:]     # 129 uploads (repack) + two evals of 129 matmuls
+
+
+@pytest.mark.gpu
+def test_falcon_7b_shapes_offloaded_to_b200_match_cpu_reference(tmp_path):
+    """The same with Falcon-7B's own dimensions (n_embd 4544, 71 heads, 32 layers, random Q4_0 blocks, 3.9 GB file):
+    K = 4544 (142 blocks: not a multiple of the 128-block chunks) and K = 18176 through the GEMV, the tcgen05 GEMM
+    (prompt of 40) and the n = 1 host path, from a real graph."""
+    import shutil
+    if shutil.disk_usage(str(tmp_path)).free < 6 * (1 << 30):
+        pytest.skip("needs 6 GB of scratch disk for the model file")
+    model = _falcon_model(tmp_path, "7b")
+    cpu, _ = _falcon_logits(tmp_path, FALCON_CPU_SO, 40, model, threads=16)
+    gpu, log = _falcon_logits(tmp_path, FALCON_B200_SO, 40, model, threads=16)
+    os.remove(model)
+    assert np.isfinite(gpu).all()
+    _compare_logits(cpu, gpu, 3e-2)
+    assert _launches(log) >= 129 + 2 * 129, log[-500:]
+
+
 def test_layer_graph_driver_on_the_cpu_is_deterministic():
     """tests/glue/layer_driver.c (a LLaMA decode graph built with the reference's API) on the plain CPU path."""
     G = _layer_lib()
