@@ -55,18 +55,27 @@ def main():
         return L.ggml_b200_last_error().decode()
 
     # (M, K): even shards, a ragged last shard, a shard-less last rank at world 8, vocabulary sized
-    shapes = [(4096, 4096), (11008, 4096), (4544, 4544 // 64 * 64), (32000, 4096), (384, 256), (1000, 512)]
+    # + the LLaMA-65B matmuls of the scaling run (BASELINE configs[4])
+    shapes = [(4096, 4096), (11008, 4096), (4544, 4544 // 64 * 64), (32000, 4096), (384, 256), (1000, 512),
+              (8192, 8192), (22016, 8192), (8192, 22016)]
+    import oracle
+    try:
+        R = oracle.ref()
+    except Exception:   # noqa: BLE001
+        R = None
+    P = oracle.port() if R is None else None
+    oracle_err = {}
     failures = []
     rng = np.random.default_rng(1234)                       # same stream on every rank: identical tensors
     weights = []
     for (M, K) in shapes:
         blk = random_q4_0(rng, M, K)
         lo, hi = mod.shard_rows(M, rank, world)
-        weights.append((mod.Weight(blk), mod.Weight(blk, lo, hi), M, K))
+        weights.append((mod.Weight(blk), mod.Weight(blk, lo, hi), M, K, blk))
 
     def run_case(n, p2p, label):
         mod.set_tuning("p2p_gather", p2p)
-        for (wf, ws, M, K) in weights:
+        for (wf, ws, M, K, blk) in weights:
             x = torch.from_numpy(np.random.default_rng(M + K + n).standard_normal((n, K), dtype=np.float32)).cuda()
             y_ref = torch.zeros((n, M), dtype=torch.float32, device="cuda")
             y = torch.full((n, M), float("nan"), dtype=torch.float32, device="cuda")
@@ -79,6 +88,14 @@ def main():
             if not torch.equal(y, y_ref):
                 bad = int((y != y_ref).sum().item())
                 failures.append(f"rank {rank} {label} M={M} K={K} n={n}: {bad} of {n * M} differ")
+            if n == 1 and label == "p2p-fused":
+                # every rank: its gathered result against the ORACLE (the reference itself, else the C port)
+                xn = x.cpu().numpy()
+                want = R.mul_mat(blk, xn, n_threads=4) if R is not None else P.mul_mat(blk, xn, avx2_order=True)
+                e = float(np.max(np.abs(y.cpu().numpy() - want)) / max(float(np.max(np.abs(want))), 1e-30))
+                oracle_err[f"{M}x{K}"] = e
+                if not e <= 1e-4:
+                    failures.append(f"rank {rank} {label} M={M} K={K}: differs from the oracle by {e:.3e}")
 
     run_case(1, 1, "p2p-fused")
     run_case(1, 5, "p2p-gather")
@@ -88,7 +105,7 @@ def main():
 
     # ---- protocol stress: a chain y1 = W1 x, then many ops queued with no host sync, results kept per op
     mod.set_tuning("p2p_gather", 1)
-    wf, ws, M, K = weights[0]                                # 4096 x 4096: y feeds the next op's x
+    wf, ws, M, K, _ = weights[0]                             # 4096 x 4096: y feeds the next op's x
     reps = 300
     x0 = torch.from_numpy(np.random.default_rng(99).standard_normal((1, K), dtype=np.float32)).cuda()
     bufs_ref = [x0] + [torch.zeros((1, M), dtype=torch.float32, device="cuda") for _ in range(reps)]
@@ -233,6 +250,8 @@ def main():
         print(f"CHECK_SHARDED {'OK' if not flat else 'FAILED'} world={world} shapes={len(shapes)} "
               f"chain_us_per_op p2p={dt:.1f} (graph {graph_us if graph_us is None else round(graph_us, 2)}) nccl={dt_nccl:.1f} "
               f"same-src-runs graph us/op={run_us if run_us is None else round(run_us, 2)}")
+        print("oracle (%s) max|dY|/max|Y| of rank 0's gathered n = 1 results: %s" % ("reference" if R is not None else "C port",
+              " ".join("%s=%.2e" % kv for kv in oracle_err.items())))
     sys.stdout.flush()
     dist.barrier()
     torch.cuda.synchronize()
