@@ -165,7 +165,7 @@ def main():
     # for each other's exchange; a consumer of their results must still see all of them.  60 rounds back to back,
     # eagerly and from a CUDA graph, against the same sequence on the unsharded weights.
     run_us = None
-    (wf0, ws0, M0, K0), (wf1, ws1, M1, K1) = weights[0], weights[1]          # 4096x4096 and 11008x4096
+    (wf0, ws0, M0, K0, _b0), (wf1, ws1, M1, K1, _b1) = weights[0], weights[1]          # 4096x4096 and 11008x4096
     rounds = 60
 
     def make_bufs():
