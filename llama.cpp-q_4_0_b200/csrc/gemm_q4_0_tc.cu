@@ -3,6 +3,7 @@
 // cuTensorMapEncodeTiled is fetched through cudaGetDriverEntryPoint so the library keeps no
 // link-time dependency on libcuda (it must load, and export its ABI, on a GPU-less build host).
 #include <cuda.h>
+#include <stdlib.h>
 #include <cuda_runtime.h>
 #include <string.h>
 
@@ -69,7 +70,7 @@ static int g_gemm_bias = 1;
 // Both are parity green; measured on the nine prefill shapes the rewrite is 3-4 % SLOWER (profiles/r02_bench_gemm_v1.log,
 // r02_bench_gemm_v3.log): what paces both is the per-warp serial chain TMEM load -> FMA -> barrier hand-off, not the
 // instruction count (kernel 3).
-static int g_gemm_v3 = 0;
+static int g_gemm_v3 = 1;
 int gemm_xd_perm() { return g_gemm_v3; }
 long long * g_gemm_trace = nullptr;   // debug timeline buffer (tools/trace_gemm.py)
 int gemm_set_tuning(const char * key, int value) {
@@ -128,6 +129,7 @@ int launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int
     const int rows = (int)w->rows(), nbk_i = (int)nbk;
     if (g_gemm_v3) {
         cfg.dynamicSmemBytes = g3::SMEM_BYTES;
+        cfg.blockDim = dim3(g3::THREADS);
         if (g_gemm_trace && !S) CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, true>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
         else if (S)             CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<true, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
         else                    CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));

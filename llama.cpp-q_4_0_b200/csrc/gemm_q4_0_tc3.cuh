@@ -54,8 +54,11 @@ constexpr int NS_RAW = 4;               // nibble-tile ring
 constexpr int NS_OP = 4;                // int8 operand ring (A unpacked + B)
 constexpr int NS_X = 6;                 // scale ring (the epilogue trails the MMA by up to one stage, the unpack warps lead it by NS_OP)
 constexpr int NS_D = 4;                 // TMEM accumulator ring (4 x 128 columns = 512)
-constexpr int THREADS = 384;
-constexpr int EPI_WARPS = 8, TMA_WARP = 8, MMA_WARP = 9, UNPACK_WARP0 = 10, UNPACK_WARPS = 2;
+constexpr int THREADS = 640;
+constexpr int EPI_WARPS = 16, TMA_WARP = 16, MMA_WARP = 17, UNPACK_WARP0 = 18, UNPACK_WARPS = 2;
+constexpr int WCOLS = BN / (EPI_WARPS / 4);                // tile columns per epilogue warp (32)
+constexpr int NKG = WCOLS / 8;                             // 8-column groups per warp = the .xN of its TMEM loads (4)
+constexpr int EPI_REGS = 104, SVC_REGS = 56;              // setmaxnreg: 512 * 104 + 128 * 56 <= 640 * 96 (the launch pool)
 constexpr int UNPACK_ROWS = BM / (UNPACK_WARPS * 8);      // (row, block) items per unpack thread and k-stage (8)
 static_assert(KB == NS_D, "block j of a k-stage uses TMEM buffer j");
 
@@ -88,20 +91,18 @@ constexpr int S_BIAS = 1 << 19;                  // constant-tile MMA: 32 * (-12
 // where kernel 1 puts the scale of activation column c inside a row of xdT (gemm_xd_perm in quantize_q8_0.cuh is the
 // same formula): within every group of 64 columns, the 16 columns {8k + 2t, 8k + 2t + 1 : k = 0..7} that epilogue
 // thread t (= lane % 4) owns become contiguous
-__host__ __device__ constexpr int xd_perm(int c) { return (c & ~63) + (((c & 7) >> 1) << 4) + (((c & 63) >> 3) << 1) + (c & 1); }
+__host__ __device__ constexpr int xd_perm(int c) { return (c & ~31) + (((c & 7) >> 1) << 3) + (((c & 31) >> 3) << 1) + (c & 1); }
 
 // 16 TMEM lanes x 64 columns in the accumulator-fragment layout (16x256b.x8): thread i gets, for column group
 // k = 0..7: r[4k+0], r[4k+1] = lane (i/4),     columns 8k + 2(i%4), +1
 //           r[4k+2], r[4k+3] = lane (i/4) + 8, the same two columns.
-__device__ __forceinline__ void tmem_ld_16x256b_x8(uint32_t taddr, uint32_t (&r)[32]) {
+__device__ __forceinline__ void tmem_ld_frag(uint32_t taddr, uint32_t (&r)[4 * NKG]) {
+    static_assert(NKG == 4, "one tcgen05.ld.16x256b.x4 per half block and warp");
     asm volatile(
-        "tcgen05.ld.sync.aligned.16x256b.x8.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        "tcgen05.ld.sync.aligned.16x256b.x4.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
         : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
         : "r"(taddr) : "memory");
 }
 
@@ -113,10 +114,10 @@ struct Dump {
 // One half block: H = 0 -> the thread's rows r0, r0 + 8 (TMEM lanes 0..15 of the quadrant), H = 1 -> rows r0 + 16, r0 + 24;
 // 8 column pairs each.  acc[k * 4 + j] = (column pair k, row j).
 template <int H, bool DUMP>
-__device__ __forceinline__ void epi_half(const uint32_t (&r)[32], uint64_t (&acc)[32], const uint64_t (&dx2)[8],
+__device__ __forceinline__ void epi_half(const uint32_t (&r)[4 * NKG], uint64_t (&acc)[4 * NKG], const uint64_t (&dx2)[NKG],
                                          const float (&dw)[4], const float (&nc)[4], const Dump & dp, int blk, int lane) {
 #pragma unroll
-    for (int k = 0; k < 8; k++) {
+    for (int k = 0; k < NKG; k++) {
 #pragma unroll
         for (int jj = 0; jj < 2; jj++) {
             const int j = 2 * H + jj;
@@ -145,28 +146,28 @@ __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int
 #define G3_TR(idx) do { if (TRACE && trc != nullptr && ew == 0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0) trc[2 * 2048 + (idx)] = clock64(); } while (0)
     const uint32_t bars = sbase + SMEM_BAR;
     const int quad = ew & 3;                        // TMEM lane quadrant (== warp % 4)
-    const int col0 = (ew >> 2) * 64;                // first tile column of this warp
+    const int col0 = (ew >> 2) * WCOLS;             // first tile column of this warp
     const int r0 = quad * 32 + (lane >> 2);         // this thread's tile rows: r0 + 8j, j = 0..3
     const int m = m0 + r0;
     const bool cols_live = c0 + col0 < n;           // warp-uniform: any real column in this half?
     uint32_t t_lane = tmem_base + ((uint32_t)(quad * 32) << 16) + col0;
     // per-thread base addresses, made opaque: ptxas otherwise re-derives them from %tid in every unrolled block
-    uint32_t xa0 = sbase + SMEM_X + (col0 + 16 * (lane & 3)) * 4;                       // this thread's 16 (permuted) column scales of block 0
+    uint32_t xa0 = sbase + SMEM_X + (col0 + 2 * NKG * (lane & 3)) * 4;                       // this thread's 16 (permuted) column scales of block 0
     uint32_t da0 = sbase + SMEM_X + XD_BYTES + (quad * 32 + (lane >> 2) * 4) * 4;       // its 4 row scales of block 0
     asm volatile("" : "+r"(t_lane), "+r"(xa0), "+r"(da0));
     const int nstages = (nbk + KB - 1) / KB;
     const float NEG_OFFSET = -__int_as_float(S_BIAS);    // -(2^19 * 2^-149) = -2^-130
-    uint64_t acc[32];
+    uint64_t acc[4 * NKG];
 #pragma unroll
-    for (int i = 0; i < 32; i++) acc[i] = 0ull;
+    for (int i = 0; i < 4 * NKG; i++) acc[i] = 0ull;
     const Dump dump = {S_out, rows, n, nbk, m, c0 + col0};
 
     if (cols_live) {
-        uint32_t ra[32], rb[32];                    // the two half blocks (TMEM lanes 0..15 / 16..31 of the quadrant)
+        uint32_t ra[4 * NKG], rb[4 * NKG];                    // the two half blocks (TMEM lanes 0..15 / 16..31 of the quadrant)
         mbar_wait(bars + Bars::x_full, 0);
         mbar_wait(bars + Bars::d_full, 0);
         tc_fence_after_sync();
-        tmem_ld_16x256b_x8(t_lane, ra);
+        tmem_ld_frag(t_lane, ra);
         int sx = 0;
         uint32_t xph = 0;
 #pragma unroll 1
@@ -201,16 +202,16 @@ __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int
 #pragma unroll
                         for (int j = 0; j < 4; j++) nc[j] = NEG_OFFSET * dw[j];      // exact: dw has 11 significant bits
                     }
-                    uint64_t dx2[8];
+                    uint64_t dx2[NKG];
 #pragma unroll
-                    for (int q = 0; q < 4; q++) {
+                    for (int q = 0; q < NKG / 2; q++) {
                         const float4 v = lds_f4(xa + jj * (BN * 4) + 16 * q);
                         dx2[2 * q] = pack_f32x2(v.x, v.y);
                         dx2[2 * q + 1] = pack_f32x2(v.z, v.w);
                     }
                     tmem_ld_wait();                                       // ra = rows r0, r0 + 8
                     G3_TR(8 * blk + 1);
-                    tmem_ld_16x256b_x8(t_lane + jj * BN + (16u << 16), rb);
+                    tmem_ld_frag(t_lane + jj * BN + (16u << 16), rb);
                     epi_half<0, DUMP>(ra, acc, dx2, dw, nc, dump, blk, lane);
                     G3_TR(8 * blk + 2);
                     tmem_ld_wait();                                       // rb = rows r0 + 16, r0 + 24
@@ -223,7 +224,7 @@ __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int
                         if (!ok_x) mbar_wait(x_bar, xph1);                // next stage's scales have landed
                         if (!ok_d) mbar_wait(d_bar, d_par);
                         tc_fence_after_sync();
-                        tmem_ld_16x256b_x8(t_lane + j1 * BN, ra);
+                        tmem_ld_frag(t_lane + j1 * BN, ra);
                     }
                     G3_TR(8 * blk + 4);
                     epi_half<1, DUMP>(rb, acc, dx2, dw, nc, dump, blk, lane);
@@ -257,7 +258,7 @@ __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int
     if (cols_live) {
         const float rescale = 562949953421312.0f;   // 2^49
 #pragma unroll
-        for (int q = 0; q < 32; q++) {
+        for (int q = 0; q < 4 * NKG; q++) {
             const int j = q & 3, k = q >> 2;
             float v0, v1;
             unpack_f32x2(acc[q], v0, v1);
@@ -322,9 +323,12 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
     pdl_launch_dependents();   // after the wait: see gemv_q4_0_fused.cuh (independent ops)
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(smem + SMEM_BAR + Bars::tmem_slot);
 
+    // register budget: setmaxnreg at the top of each role's branch (the branches only meet again at the final barrier)
     if (warp < EPI_WARPS) {
+        setmaxnreg_inc<EPI_REGS>();
         epilogue<DUMP, TRACE>(sbase, tmem_base, warp, lane, m0, c0, rows, n, nbk, y, ldy, S_out, trc);
     } else if (warp == TMA_WARP) {
+        setmaxnreg_dec<SVC_REGS>();
         if (lane == 0) {
             for (int s = 0; s < nstages; s++) {
                 const int sr = s % NS_RAW, so = s % NS_OP, sx = s % NS_X;
@@ -343,6 +347,7 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
             }
         }
     } else if (warp == MMA_WARP) {
+        setmaxnreg_dec<SVC_REGS>();
         // The whole warp walks the loop converged and one elected lane issues: every operand stays in uniform registers.
         // (Inside `if (lane == 0) { loop }` ptxas wraps each UTCIMMA in an ELECT / BRA.U.ANY loop; the issuing thread's own
         // scalar instructions are what paces this pipeline -- tools/ubench/mma_rate.cu: the MMA pair itself takes 128 clk.)
@@ -377,6 +382,7 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
             __syncwarp();
         }
     } else {
+        setmaxnreg_dec<SVC_REGS>();
         // ===== unpack: nibble tile -> K-major signed-byte A tile (16 * (q - 8)) with the 128-byte swizzle =====
         // 64 threads x 8 (row, block) items per k-stage, in two batches of 4 with the shared-memory loads of a batch
         // issued before its first expansion.

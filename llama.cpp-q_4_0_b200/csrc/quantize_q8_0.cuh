@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(256)
 quantize_q8_0_kernel(const float * __restrict__ x, long long n, int K, size_t nb11,
                      int8_t * __restrict__ xq, int2 * __restrict__ xds,
                      unsigned char * __restrict__ blocks34,
-                     float * __restrict__ xdT, long long n_pad, int xd_perm /* kernel 3's column order inside every 64-group (gemm_q4_0_tc3.cuh xd_perm) */) {
+                     float * __restrict__ xdT, long long n_pad, int xd_perm /* kernel 3's (tc3) column order inside every 32-group (gemm_q4_0_tc3.cuh xd_perm) */) {
     pdl_wait();   // x may be produced, and xq/xds still be read, by the previous kernel
     pdl_launch_dependents();   // after the wait: see gemv_q4_0_fused.cuh (independent ops)
     const int per_row = K >> 3;
@@ -83,7 +83,7 @@ quantize_q8_0_kernel(const float * __restrict__ x, long long n, int K, size_t nb
         // block-major copy of the scales for the tensor-core GEMM's epilogue: xdT[b][row]
         if (xdT != nullptr) {
             const long long c = row;
-            const long long pos = xd_perm ? (c & ~63ll) + (((c & 7) >> 1) << 4) + (((c & 63) >> 3) << 1) + (c & 1) : c;
+            const long long pos = xd_perm ? (c & ~31ll) + (((c & 7) >> 1) << 3) + (((c & 31) >> 3) << 1) + (c & 1) : c;
             xdT[(long long)b * n_pad + pos] = __half2float(dh);
         }
     }
