@@ -654,15 +654,16 @@ def prefill_leg(mod, stream, rng, steps, warmup, n=512, shapes=None, groups=None
                    "shapes": [[M, K, c] for (M, K, c) in shapes], "ops_per_pass": ops,
                    "timed": "kernel 1 (quantize_row_q8_0) + kernel 3 (tcgen05 kind::i8 GEMM) per matmul, x/y resident in HBM"},
         "gpu_launches_per_pass": int(launches),
-        "roofline": {"kernel": "gemm_q4_0_tc_kernel (TMA + nibble unpack + tcgen05.mma kind::i8 + TMEM + scale epilogue)",
+        "roofline": {"kernel": "gemm_q4_0_tc3_kernel (TMA + nibble unpack + tcgen05.mma kind::i8 + TMEM + 16-warp scale epilogue)",
                      "bound": "tensor", "achieved": tops_gemm, "peak": 2 * bf16, "unit": "TOP/s", "frac": tops_gemm / (2 * bf16),
                      "frac_of_nominal_4500": tops_gemm / 4500.0, "peak_source": src,
                      "measured_cublaslt_int8_8192cubed_TOPS": peak_m, "frac_of_measured_cublaslt_int8": (tops_gemm / peak_m) if peak_m else None,
                      "traffic": gemm_traffic(), "traffic_source": "profiles/traffic.json (committed ncu capture, not this run)",
                      "ms_per_pass_kernel3": ms_gemm,
-                     "note": "the per-block fp16 x fp16 scale epilogue bounds this formulation at 25% of the tensor rate: every 128x128 int32 "
-                             "tile (one Q4_0 block) costs 256 clk of FP32 FMAs AND 256 clk of TMEM reads against 64 clk of MMA "
-                             "(profiles/r02_ubench_epi_rate.log); see DESIGN.md kernel 3"},
+                     "note": "the per-block fp16 x fp16 scale epilogue bounds this formulation at ~25% of the tensor rate: every 128x128 int32 "
+                             "tile (one Q4_0 block) costs 300 clk of FP32 FMAs overlapped with 257 clk of TMEM reads against 64 clk of data MMA "
+                             "(profiles/r02_ubench_epi_rate.log, r02_ubench_mma_rate.log); the kernel itself is latency bound on the per-warp chain "
+                             "TMEM load -> FMA -> hand-off (profiles/r02_ncu_gemm_full_summary.txt): 16 epilogue warps; see DESIGN.md kernel 3"},
     }
     if not host_leg:
         for (h, _, _) in handles:
@@ -788,7 +789,7 @@ def prefill_sharded_leg(mod, stream, rng, rank, world, dist, steps, warmup, n=51
             "e2e": {"value": tops(ms_e2e), "unit": "TOPS", "ms_per_pass": ms_e2e, "h2d_bytes_per_pass": sum(4 * K * n for (_, _, K) in handles) * world,
                     "d2h_bytes_per_pass": gathered * world, "api": "pinned host x -> HBM on every rank, ggml_b200_mul_mat_q4_0_sharded, full y -> pinned host"},
             "roofline": {"bound": "tensor", "achieved": tops(ms_gemm) / world, "peak": 2 * bf16, "unit": "TOP/s per rank", "frac": tops(ms_gemm) / world / (2 * bf16),
-                         "kernel": "gemm_q4_0_tc_kernel on the rank's row shards"}}
+                         "kernel": "gemm_q4_0_tc3_kernel on the rank's row shards"}}
 
 
 def glue_e2e_leg(steps, warmup):

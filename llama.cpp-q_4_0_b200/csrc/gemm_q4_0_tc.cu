@@ -1,4 +1,4 @@
-// gemm_q4_0_tc.cu -- host side of kernel 3 (gemm_q4_0_tc.cuh): TMA tensor maps, launch, tuning.
+// gemm_q4_0_tc.cu -- host side of kernel 3 (gemm_q4_0_tc3.cuh): TMA tensor maps, launch, tuning.
 //
 // cuTensorMapEncodeTiled is fetched through cudaGetDriverEntryPoint so the library keeps no
 // link-time dependency on libcuda (it must load, and export its ABI, on a GPU-less build host).
@@ -7,7 +7,6 @@
 #include <cuda_runtime.h>
 #include <string.h>
 
-#include "gemm_q4_0_tc.cuh"
 #include "gemm_q4_0_tc3.cuh"
 #include "state.h"
 
@@ -49,11 +48,6 @@ int gemm_init() {
         return GGML_B200_ERR_CUDA;
     }
     g_encode = (EncodeTiledFn)fn;
-    CK(cudaFuncSetAttribute(gemm_q4_0_tc_kernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
-    CK(cudaFuncSetAttribute(gemm_q4_0_tc_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
-    CK(cudaFuncSetAttribute(gemm_q4_0_tc_kernel<false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
-    CK(cudaFuncSetAttribute(gemm_q4_0_tc_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
-    CK(cudaFuncSetAttribute(gemm_q4_0_tc_kernel<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
     CK(cudaFuncSetAttribute(g3::gemm_q4_0_tc3_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, g3::SMEM_BYTES));
     CK(cudaFuncSetAttribute(g3::gemm_q4_0_tc3_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, g3::SMEM_BYTES));
     CK(cudaFuncSetAttribute(g3::gemm_q4_0_tc3_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, g3::SMEM_BYTES));
@@ -63,19 +57,10 @@ int gemm_init() {
 
 void gemm_shutdown() { g_gemm_ready = false; }
 
-// "gemm_bias": 1 = the constant-tile MMA + denormal-read epilogue (no int->float instruction), 0 = the
-// 1.5*2^23 integer-add epilogue (gemm_q4_0_tc.cuh)
-static int g_gemm_bias = 1;
-// "gemm_v3": 0 = gemm_q4_0_tc.cuh (default), 1 = gemm_q4_0_tc3.cuh, the round-2 rewrite with 40 % fewer epilogue instructions.
-// Both are parity green; measured on the nine prefill shapes the rewrite is 3-4 % SLOWER (profiles/r02_bench_gemm_v1.log,
-// r02_bench_gemm_v3.log): what paces both is the per-warp serial chain TMEM load -> FMA -> barrier hand-off, not the
-// instruction count (kernel 3).
-static int g_gemm_v3 = 1;
-int gemm_xd_perm() { return g_gemm_v3; }
+// kernel 1 writes the block-major activation scales in kernel 3's column order (gemm_q4_0_tc3.cuh xd_perm)
+int gemm_xd_perm() { return 1; }
 long long * g_gemm_trace = nullptr;   // debug timeline buffer (tools/trace_gemm.py)
 int gemm_set_tuning(const char * key, int value) {
-    if (!strcmp(key, "gemm_bias")) { g_gemm_bias = value != 0; return GGML_B200_OK; }
-    if (!strcmp(key, "gemm_v3")) { g_gemm_v3 = value != 0; g.runN.count = 0; return GGML_B200_OK; }
     if (!strcmp(key, "gemm_trace")) {   // value != 0: allocate and arm the 4 x 2048 clock64 timeline buffer
         if (g_gemm_trace) { cudaFree(g_gemm_trace); g_gemm_trace = nullptr; }
         if (value) { CK(cudaMalloc(&g_gemm_trace, 4 * 2048 * 8)); CK(cudaMemset(g_gemm_trace, 0, 4 * 2048 * 8)); }
@@ -94,7 +79,7 @@ int gemm_prepare_weight(ggml_b200_weight * w) {
     const uint64_t nbk = (uint64_t)(w->K / QK);
     // nibble plane as bytes: [rows][nbk * 16], box = 4 blocks (64 B) x 128 rows, no swizzle
     int rc = encode_2d(&gw->tm_nib, CU_TENSOR_MAP_DATA_TYPE_UINT8, w->wq, nbk * 16, (uint64_t)w->rows(), nbk * 16,
-                       GEMM_KB * 16, GEMM_BM, CU_TENSOR_MAP_SWIZZLE_NONE);
+                       g3::KB * 16, g3::BM, CU_TENSOR_MAP_SWIZZLE_NONE);
     if (rc) { delete gw; return rc; }
     w->gemm = gw;
     return GGML_B200_OK;
@@ -111,37 +96,25 @@ int launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int
     const uint64_t K = (uint64_t)w->K, nbk = K / QK;
     CUtensorMap tm_xq, tm_xd;
     // activations int8 [n][K], box = 128 K-bytes x 128 columns, 128-byte swizzle (UMMA K-major SW128)
-    int rc = encode_2d(&tm_xq, CU_TENSOR_MAP_DATA_TYPE_UINT8, g.xq, K, (uint64_t)n, K, GEMM_KB * 32, GEMM_BN, CU_TENSOR_MAP_SWIZZLE_128B);
+    int rc = encode_2d(&tm_xq, CU_TENSOR_MAP_DATA_TYPE_UINT8, g.xq, K, (uint64_t)n, K, g3::KB * 32, g3::BN, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
     // activation scales block-major [nbk][n_pad] f32, box = 128 columns x 4 blocks
     rc = encode_2d(&tm_xd, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, g.xdT, (uint64_t)g.xdT_n_pad, nbk, (uint64_t)g.xdT_n_pad * 4,
-                   GEMM_BN, GEMM_KB, CU_TENSOR_MAP_SWIZZLE_NONE);
+                   g3::BN, g3::KB, CU_TENSOR_MAP_SWIZZLE_NONE);
     if (rc) return rc;
 
-    const dim3 grid((unsigned)((w->rows() + GEMM_BM - 1) / GEMM_BM), (unsigned)((n + GEMM_BN - 1) / GEMM_BN));
+    const dim3 grid((unsigned)((w->rows() + g3::BM - 1) / g3::BM), (unsigned)((n + g3::BN - 1) / g3::BN));
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = grid; cfg.blockDim = dim3(GEMM_THREADS); cfg.dynamicSmemBytes = GEMM_SMEM_BYTES; cfg.stream = g.stream;
+    cfg.gridDim = grid; cfg.blockDim = dim3(g3::THREADS); cfg.dynamicSmemBytes = g3::SMEM_BYTES; cfg.stream = g.stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = g.tune.pdl ? 1 : 0;
     const __half * wd = w->wd;
     const int rows = (int)w->rows(), nbk_i = (int)nbk;
-    if (g_gemm_v3) {
-        cfg.dynamicSmemBytes = g3::SMEM_BYTES;
-        cfg.blockDim = dim3(g3::THREADS);
-        if (g_gemm_trace && !S) CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, true>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
-        else if (S)             CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<true, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
-        else                    CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
-    } else if (g_gemm_trace && !S) {
-        CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<false, true, true>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
-    } else if (g_gemm_bias) {
-        if (S) CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<true, true, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
-        else   CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<false, true, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
-    } else {
-        if (S) CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<true, false, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
-        else   CK(cudaLaunchKernelEx(&cfg, gemm_q4_0_tc_kernel<false, false, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
-    }
+    if (g_gemm_trace && !S) CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, true>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
+    else if (S)             CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<true, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
+    else                    CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
     g.launches++;
     return GGML_B200_OK;
 }

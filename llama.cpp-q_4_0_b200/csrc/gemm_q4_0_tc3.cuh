@@ -1,43 +1,51 @@
-// gemm_q4_0_tc3.cuh -- kernel 3: prefill GEMM, Q4_0 weights x q8_0 activations on tcgen05 (round-2 rewrite).
+// gemm_q4_0_tc3.cuh -- kernel 3: prefill GEMM, Q4_0 weights x q8_0 activations on tcgen05.
 //
 // Device replacement of the COMPUTE phase of ggml_compute_forward_mul_mat_q_f32 for many columns (reference
 // ggml.c:11373-11411, a loop of ggml_vec_dot_q4_0_q8_0 per column; ggml.c:2339-2607):
 //     Y[c][m] = sum_b fp32(dw[m,b]) * fp32(dx[c,b]) * S_b[m,c],  S_b = sum_j (q4_j - 8) * q8_j
 // One `tcgen05.mma.kind::i8` (M = 128 weight rows, N = 128 activation columns, K = 32 = one Q4_0 block) forms a
 // 128x128 int32 tile exactly in TMEM; every block has its own fp16 x fp16 scale pair, so the int32 accumulator cannot
-// run across blocks: each block's MMA targets a fresh TMEM buffer (4-deep ring) and 8 epilogue warps fold
-// S_b * dw * dx into fp32 registers.  What bounds this formulation, measured (profiles/r02_ubench_epi_rate.log):
-//   * the CUDA cores: 2 FP32 FMAs per S_b = 32768 per block at 128 FMA/clk/SM = 256 clk,
+// run across blocks: each block's MMA targets a fresh TMEM buffer (4-deep ring) and the epilogue warps fold
+// S_b * dw * dx into fp32 registers.  What bounds this formulation, measured (profiles/r02_ubench_epi_rate.log,
+// r02_ubench_mma_rate.log):
+//   * the CUDA cores: 2 FP32 FMAs per S_b = 32768 per block; FFMA2 runs at 98-124 fp32 FMA/clk/SM depending on operand
+//     shapes: 300 clk per block together with
 //   * the TMEM read port: 255 B/clk/SM -> 64 KB of S_b per block = 257 clk,
-//   against 64 clk of MMA: at most 25 % of the int8 tensor rate; both together, with nothing else in the way, take
-//   300 clk per block.  (One FMA per S_b with the rank-1 scale tile dw x dx formed by an extra MMA needs the scale tile
-//   from TMEM too: 532 clk per block, measured -- rejected.)
-// The round-1 kernel needed 646-780 clk per block: ~1600 warp instructions per block and a serial chain per epilogue warp
-// of TMEM-load wait -> mbarrier arrive -> mbarrier wait (~200 clk even when complete) -> 16 FFMA2.  What changed:
+//   against 128 clk for the block's MMA pair (64 clk per 128x128x32 MMA at any N <= 128): at most ~40 % of the int8 rate
+//   for the MMA pair, 25 % counting the data MMA alone.  (One FMA per S_b with the rank-1 scale tile dw x dx formed by an
+//   extra MMA needs the scale tile from TMEM too: 532 clk per block, measured -- rejected.)  With the kernel's scale loads
+//   from shared memory, barrier arrivals and the unpack warps beside it the same epilogue takes 463 clk per block in
+//   isolation; the kernel runs at ~640: ncu shows no saturated pipe (tensor 17 %, FMA 28 %, issue 53 % with 8 epilogue
+//   warps) -- it is latency bound on the per-warp chain TMEM load -> FMA -> hand-off, and tcgen05.wait::ld waits for ALL of
+//   a warp's loads, so only more warps hide it.  Hence:
+//   * 16 epilogue warps (4 per SM sub-partition), each 32 lanes x 32 columns, half blocks of 16 registers
+//     (tcgen05.ld.16x256b.x4), the load of the next half in flight under the 16 FFMA2 pairs of this one; 96 registers per
+//     thread at launch, setmaxnreg 104 (epilogue) / 56 (service warps).  +11-13 % over 8 warps of 64 columns.
 //   * A operand = 16 * (q - 8): a nibble moved to the HIGH half of its byte with the top bit flipped IS that signed byte, so
 //     the nibble -> int8 expansion is 3 instructions per 8 weights instead of 7; the MMA yields 16 * S_b
 //     (|16 S_b| <= 520192 < 2^23) and the factor 2^-4 goes into the weight scale for free.
 //   * int -> float costs no instruction: a constant-tile MMA (every byte -128: 32 * 128 * 128 = 2^19) makes the
 //     accumulator 16 S_b + 2^19 >= 0, whose bits read as fp32 are the DENORMAL (16 S_b + 2^19) * 2^-149, exactly;
 //     t = fma(f, dw * 2^96, -2^-130 * dw * 2^96) = rn(S_b * dw) * 2^-49 in ONE rounding; the accumulators run scaled by
-//     2^-49 and are rescaled once.  fp32 operation order: y = sum_b rn(rn(S_b * dw) * dx + acc).
-//   * scales arrive in the epilogue's own order: kernel 1 writes the activation scales with the columns of every 64-group
-//     permuted so that a thread's 16 scales of a block are contiguous (4 LDS.128), the unpack warps stage the weight
-//     scales so that a thread's 4 rows are contiguous (1 LDS.128): 5 shared-memory loads per block and thread, was 20;
-//   * TMEM is read with tcgen05.ld.16x256b.x8 (16 lanes x 64 columns, 32 registers per instruction) in half blocks, the
-//     load of the next half in flight under the 32 FFMA2 of this one; the mbarrier tests for the NEXT block are issued
-//     at the top of a block and only looked at after its math;
-//   * the service warps have the highest warp ids (the schedulers prefer them): the MMA issuer never queues behind FFMA2;
-//     the unpack warps fetch their rows' weight scales three k-stages ahead (consumed one stage after issue, those loads
-//     made the unpack warps the bottleneck of the whole kernel: 1800-2800 clk per stage).
+//     2^-49 and are rescaled once.  fp32 operation order: y = sum_b rn(rn(S_b * dw) * dx + acc).  (Resetting the
+//     accumulators to a float magic number with tcgen05.st instead of the second MMA was measured: the stores contend with
+//     the loads, 307 TOPS against 364 -- profiles/r02_bench_gemm_v3_tmem_reset.log.)
+//   * scales arrive in the epilogue's own order: kernel 1 writes the activation scales with the columns of every 32-group
+//     permuted so that a thread's 8 scales of a block are contiguous (2 LDS.128), the unpack warps stage the weight
+//     scales so that a thread's 4 rows are contiguous (1 LDS.128);
+//   * the mbarrier probes for the NEXT block are non-blocking (test_wait) at the top of a block and only looked at after
+//     its first half; a miss falls back to try_wait;
+//   * the MMA warp walks its loop converged and ONE ELECTED lane issues (elect.sync): inside `if (lane == 0) { loop }` ptxas
+//     wraps every UTCIMMA in an ELECT / BRA.U.ANY loop;
+//   * the service warps have the highest warp ids; the unpack warps fetch their rows' weight scales three k-stages ahead.
 //
-// CTA = one 128 (rows) x 128 (columns) output tile, 12 warps:
-//   warps 0-7   epilogue: warp = (TMEM lane quadrant w % 4, 64-column half w / 4); a thread owns rows r0 + 8j (j = 0..3) x 16
-//               column pairs = 64 fp32 accumulators in the tcgen05 accumulator-fragment layout
-//   warp 8      TMA producer (one thread): per k-stage (4 blocks = 128 K-bytes) the 128x64 B nibble tile (plane layout),
+// CTA = one 128 (rows) x 128 (columns) output tile, 20 warps:
+//   warps 0-15  epilogue: warp = (TMEM lane quadrant w % 4, 32-column slice w / 4); a thread owns rows r0 + 8j (j = 0..3) x 4
+//               column pairs = 32 fp32 accumulators in the tcgen05 accumulator-fragment layout
+//   warp 16     TMA producer (one thread): per k-stage (4 blocks = 128 K-bytes) the 128x64 B nibble tile (plane layout),
 //               the 128x128 B int8 activation tile (SWIZZLE_128B, K-major) and the 4x128 activation scales
-//   warp 9      TMEM allocator + MMA issuer (one thread): per block one MMA + the constant-tile MMA, commit per block
-//   warps 10-11 unpack: nibbles -> 16 * (q - 8), K-major with the 128-byte swizzle of the UMMA descriptor; weight scales
+//   warp 17     TMEM allocator + MMA issuer: per block one MMA + the constant-tile MMA, commit per block
+//   warps 18-19 unpack: nibbles -> 16 * (q - 8), K-major with the 128-byte swizzle of the UMMA descriptor; weight scales
 #pragma once
 #include <cuda.h>
 
@@ -88,9 +96,9 @@ static_assert(Bars::tmem_slot + 8 <= 512, "barrier block too small");
 constexpr int S_SHIFT = 4;                       // the MMA forms 16 * S_b
 constexpr int S_BIAS = 1 << 19;                  // constant-tile MMA: 32 * (-128) * (-128)
 
-// where kernel 1 puts the scale of activation column c inside a row of xdT (gemm_xd_perm in quantize_q8_0.cuh is the
-// same formula): within every group of 64 columns, the 16 columns {8k + 2t, 8k + 2t + 1 : k = 0..7} that epilogue
-// thread t (= lane % 4) owns become contiguous
+// where kernel 1 puts the scale of activation column c inside a row of xdT (quantize_q8_0.cuh has the same formula):
+// within every group of 32 columns, the 8 columns {8k + 2t, 8k + 2t + 1 : k = 0..3} that epilogue thread t (= lane % 4)
+// owns become contiguous
 __host__ __device__ constexpr int xd_perm(int c) { return (c & ~31) + (((c & 7) >> 1) << 3) + (((c & 31) >> 3) << 1) + (c & 1); }
 
 // 16 TMEM lanes x 64 columns in the accumulator-fragment layout (16x256b.x8): thread i gets, for column group
