@@ -496,9 +496,9 @@ def int8_peak():
 
 
 def siblings_leg(mod, stream, rng, steps, warmup):
-    """Q8_0 and Q4_1 weights through the same op, n = 1 -- a single 4096x4096 op (48 / 32 HBM copies cycled,
+    """Q8_0, Q4_1, Q5_0 and Q5_1 weights through the same op, n = 1 -- a single 4096x4096 op (48 / 32 HBM copies cycled,
     more than 2x L2) and the LLaMA-7B decode list, one launch per mul_mat (CUDA graph).  One op of every shape is checked
-    against the oracle (oracle/siblings.py, rows 0..255) first.  GB/s = algorithmic bytes (34 or 20 B per block + 4K in, 4M out)."""
+    against the oracle (oracle/siblings.py, rows 0..255) first.  GB/s = algorithmic bytes (34 / 20 / 22 / 24 B per block as stored by the reference + 4K in, 4M out)."""
     import torch
     from oracle import siblings as sib
     L_ = mod.lib()
@@ -506,14 +506,14 @@ def siblings_leg(mod, stream, rng, steps, warmup):
     out = {"hbm_peak_GBps": peak, "hbm_peak_source": peak_src,
            "kernel": "sib_gemv_kernel (dp4a, activation quantizer fused, one launch per mul_mat)", "timing": "CUDA events on the launching stream"}
     Lp, per_layer, once = WORKLOADS["llama7b_decode_n1"]
-    for qtype, name in ((sib.TYPE_Q8_0, "q8_0"), (sib.TYPE_Q4_1, "q4_1")):
+    for qtype, name in ((sib.TYPE_Q8_0, "q8_0"), (sib.TYPE_Q4_1, "q4_1"), (sib.TYPE_Q5_0, "q5_0"), (sib.TYPE_Q5_1, "q5_1")):
         bs = sib.BLOCK_BYTES[qtype]
 
         def host_blocks(M, K):
             W = rng.integers(0, 256, size=(M, K // 32, bs), dtype=np.uint8)
             d = rng.uniform(0.002, 0.02, size=(M, K // 32)).astype(np.float16)
             W[..., 0:2] = d.view(np.uint8).reshape(M, K // 32, 2)
-            if qtype == sib.TYPE_Q4_1:
+            if qtype in sib.Q8_1_ACT:
                 W[..., 2:4] = rng.uniform(-0.1, 0.1, size=(M, K // 32)).astype(np.float16).view(np.uint8).reshape(M, K // 32, 2)
             return W
 
@@ -570,7 +570,7 @@ def siblings_leg(mod, stream, rng, steps, warmup):
             torch.cuda.empty_cache()
             return ms, total, errs, len(ws)
 
-        ms1, b1, e1_, n1 = leg([(4096, 4096)], 48 if qtype == sib.TYPE_Q4_1 else 32)
+        ms1, b1, e1_, n1 = leg([(4096, 4096)], 32 if qtype == sib.TYPE_Q8_0 else 48)
         layer = [(M, K) for (M, K, c) in per_layer for _ in range(c)]
         ms7, b7, e7_, n7 = leg(layer, Lp)
         out[name] = {"single_4096_n1": {"GBps": b1 / (ms1 * 1e-3) / 1e9, "frac_of_measured_hbm_peak": b1 / (ms1 * 1e-3) / 1e9 / peak, "us_per_mul_mat": ms1 * 1e3 / n1,

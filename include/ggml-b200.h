@@ -244,18 +244,22 @@ int          ggml_b200_block_dots_q4_0(const ggml_b200_weight * w, const float *
 int          ggml_b200_fused_checkpoint_q4_0(const ggml_b200_weight * w, const float * x_dev,
                                              int32_t * S_dev, void * blocks34_dev);
 
-/* ---- sibling weight formats: Q8_0 and Q4_1 through the same op ----------------------------
+/* ---- sibling weight formats: Q8_0, Q4_1, Q5_0 and Q5_1 through the same op ----------------------------
  * The reference's operator is format blind (ggml_compute_forward_mul_mat_q_f32, ggml.c:11268-11411); quantize_fns[]
  * (ggml.c:1619-1670) binds per type the activation quantizer and the block dot:
  *   GGML_TYPE_Q8_0 (8): block_q8_0 weights (ggml.c:902-907) x quantize_row_q8_0 activations, ggml_vec_dot_q8_0_q8_0 (ggml.c:3231-3330)
  *   GGML_TYPE_Q4_1 (3): block_q4_1 weights (ggml.c:877-883) x quantize_row_q8_1 activations (ggml.c:1318-1480),
  *                       ggml_vec_dot_q4_1_q8_1 (ggml.c:2609-2734)
+ *   GGML_TYPE_Q5_0 (6): block_q5_0 (ggml.c:885-891) x q8_0 activations, ggml_vec_dot_q5_0_q8_0 (ggml.c:2735-2973)
+ *   GGML_TYPE_Q5_1 (7): block_q5_1 (ggml.c:893-900) x q8_1 activations, ggml_vec_dot_q5_1_q8_1 (ggml.c:2975-3229)
  * `type` takes the reference's enum values (ggml.h:230-242).  Decode path (dp4a GEMV, the activation quantizer fused into
  * the kernel, passes of 4 columns); no tensor-core path for these formats. */
 #define GGML_B200_TYPE_Q4_1 3
+#define GGML_B200_TYPE_Q5_0 6
+#define GGML_B200_TYPE_Q5_1 7
 #define GGML_B200_TYPE_Q8_0 8
 typedef struct ggml_b200_qweight ggml_b200_qweight;
-/* blocks: M rows of K/32 reference-format blocks (34 B / 20 B), row stride nb1 bytes (0 = contiguous); host memory */
+/* blocks: M rows of K/32 reference-format blocks (34 / 20 / 22 / 24 B), row stride nb1 bytes (0 = contiguous); host memory */
 ggml_b200_qweight * ggml_b200_upload_quant(int type, const void * blocks, int64_t M, int64_t K, size_t nb1);
 void         ggml_b200_free_quant(ggml_b200_qweight * w);
 int          ggml_b200_quant_type(const ggml_b200_qweight * w);

@@ -1,4 +1,4 @@
-// siblings.cu -- SURVEY 8(f) row 4: the op's sibling weight formats, Q8_0 and Q4_1, through the same design as Q4_0.
+// siblings.cu -- SURVEY 8(f) row 4: the op's sibling weight formats, Q8_0, Q4_1, Q5_0 and Q5_1, through the same design as Q4_0.
 //
 // What the reference does for them (ggml_compute_forward_mul_mat_q_f32, ggml.c:11268-11411, is format blind; the table
 // quantize_fns[], ggml.c:1619-1670, binds the per-format pieces):
@@ -7,6 +7,9 @@
 //   Q4_1 weights (block_q4_1, 20 B: fp16 d, fp16 m + 16 nibble bytes, ggml.c:877-883) x Q8_1 activations
 //   (block_q8_1: FLOAT d = amax / 127, s = d * sum_j x_j, ggml.c:909-915, quantize_row_q8_1 ggml.c:1318-1480):
 //       y = sum_b (d_w * d_x) * S_b + m_w * s_x,  S_b = sum_j q_j * x_j  (q unsigned 0..15) ggml_vec_dot_q4_1_q8_1, ggml.c:2609-2734
+//   Q5_0 (block_q5_0, 22 B: fp16 d, 32 fifth bits qh, 16 nibble bytes, ggml.c:885-891) x Q8_0: as Q8_0 with w_j = (nibble | bit << 4) - 16
+//                                                                                 ggml_vec_dot_q5_0_q8_0, ggml.c:2735-2973
+//   Q5_1 (block_q5_1, 24 B: + fp16 m, ggml.c:893-900) x Q8_1: as Q4_1 with q = nibble | bit << 4 (0..31)   ggml_vec_dot_q5_1_q8_1, ggml.c:2975-3229
 // The activation quantizer is kernel 1's arithmetic (the AVX2 contract: two IEEE divides, round-half-even); Q8_1 keeps
 // the scale in fp32 and adds s.
 //
@@ -40,7 +43,12 @@ namespace sib {
 constexpr int SIB_NC = 4;          // activation columns per pass
 constexpr int THREADS = 512;
 
-__host__ __device__ constexpr int block_bytes(int type) { return type == GGML_B200_TYPE_Q8_0 ? 34 : 20; }
+__host__ __device__ constexpr int block_bytes(int type) {
+    return type == GGML_B200_TYPE_Q8_0 ? 34 : type == GGML_B200_TYPE_Q4_1 ? 20 : type == GGML_B200_TYPE_Q5_0 ? 22 : 24;
+}
+// activations: q8_1 (fp32 d, s = d * sum) for the formats with a min term, q8_0 (fp16 d) otherwise (quantize_fns[].vec_dot_type)
+__host__ __device__ constexpr bool act_q8_1(int type) { return type == GGML_B200_TYPE_Q4_1 || type == GGML_B200_TYPE_Q5_1; }
+__host__ __device__ constexpr bool is_q5(int type) { return type == GGML_B200_TYPE_Q5_0 || type == GGML_B200_TYPE_Q5_1; }
 
 // raw reference blocks (row stride nb1) -> planes.  One thread per block.
 template <int TYPE>
@@ -58,11 +66,21 @@ __global__ void __launch_bounds__(256) repack_kernel(const unsigned char * __res
         for (int i = 0; i < 8; i++) w[i] = (uint32_t)src[1 + 2 * i] | ((uint32_t)src[2 + 2 * i] << 16);
         wq[2 * t]     = make_uint4(w[0], w[1], w[2], w[3]);
         wq[2 * t + 1] = make_uint4(w[4], w[5], w[6], w[7]);
-    } else {
+    } else if (TYPE == GGML_B200_TYPE_Q4_1) {
         reinterpret_cast<uint32_t *>(wd)[t] = (uint32_t)src[0] | ((uint32_t)src[1] << 16);      // {d, m}
         uint32_t w[4];
 #pragma unroll
         for (int i = 0; i < 4; i++) w[i] = (uint32_t)src[2 + 2 * i] | ((uint32_t)src[3 + 2 * i] << 16);
+        wq[t] = make_uint4(w[0], w[1], w[2], w[3]);
+    } else {
+        // Q5_0: {d, qh[4], qs[16]} (ggml.c:885-891); Q5_1: {d, m, qh[4], qs[16]} (ggml.c:893-900) -> scale plane {d | m << 16, qh}
+        const int o = TYPE == GGML_B200_TYPE_Q5_1 ? 2 : 1;                                       // halves before qh
+        const uint32_t dm = (uint32_t)src[0] | (TYPE == GGML_B200_TYPE_Q5_1 ? (uint32_t)src[1] << 16 : 0u);
+        const uint32_t qh = (uint32_t)src[o] | ((uint32_t)src[o + 1] << 16);
+        reinterpret_cast<uint2 *>(wd)[t] = make_uint2(dm, qh);
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) w[i] = (uint32_t)src[o + 2 + 2 * i] | ((uint32_t)src[o + 3 + 2 * i] << 16);
         wq[t] = make_uint4(w[0], w[1], w[2], w[3]);
     }
 }
@@ -81,7 +99,7 @@ __device__ __forceinline__ void quantize_block(float v, int lane, int8_t * xq_bl
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
     if (lane == 0) {
-        if (TYPE == GGML_B200_TYPE_Q8_0) *xd = __half2float(__float2half_rn(d));       // block_q8_0.d is fp16 (ggml.c:1214-1215)
+        if (!act_q8_1(TYPE)) *xd = __half2float(__float2half_rn(d));                  // block_q8_0.d is fp16 (ggml.c:1214-1215)
         else { *xd = d; *xs = __fmul_rn(d, (float)sum); }                             // block_q8_1: float d, s = d * sum (ggml.c:1419,1449)
     }
 }
@@ -93,6 +111,27 @@ __device__ __forceinline__ int block_dot(const uint4 & w0, const uint4 & w1, con
     if (TYPE == GGML_B200_TYPE_Q8_0) {
         s = __dp4a((int)w0.x, (int)x0.x, s); s = __dp4a((int)w0.y, (int)x0.y, s); s = __dp4a((int)w0.z, (int)x0.z, s); s = __dp4a((int)w0.w, (int)x0.w, s);
         s = __dp4a((int)w1.x, (int)x1.x, s); s = __dp4a((int)w1.y, (int)x1.y, s); s = __dp4a((int)w1.z, (int)x1.z, s); s = __dp4a((int)w1.w, (int)x1.w, s);
+    } else if (is_q5(TYPE)) {
+        // element j = nibble | bit j of qh << 4 (low nibbles: elements 0..15, high: 16..31; ggml.c:1024-1038).  Four bits of qh
+        // go to bit 0 of four bytes by one multiply (bit m of x lands on bit 8m of x * 0x00204081).  Q5_1 uses the unsigned
+        // 0..31 (ggml.c:3156-3159); Q5_0 the value - 16 = nibble | (bit ? 0 : 0xF0) as a signed byte (ggml.c:2903-2906).
+        const uint32_t qh = w1.x;
+        const uint32_t w[4] = {w0.x, w0.y, w0.z, w0.w};
+        const uint32_t xl[4] = {x0.x, x0.y, x0.z, x0.w}, xh[4] = {x1.x, x1.y, x1.z, x1.w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint32_t bl = (qh >> (4 * i)) & 0xFu, bh = (qh >> (16 + 4 * i)) & 0xFu;
+            uint32_t lo = w[i] & 0x0F0F0F0Fu, hi = (w[i] >> 4) & 0x0F0F0F0Fu;
+            if (TYPE == GGML_B200_TYPE_Q5_1) {
+                lo |= ((bl * 0x00204081u) & 0x01010101u) << 4;
+                hi |= ((bh * 0x00204081u) & 0x01010101u) << 4;
+            } else {
+                lo |= (((bl ^ 0xFu) * 0x00204081u) & 0x01010101u) * 0xF0u;
+                hi |= (((bh ^ 0xFu) * 0x00204081u) & 0x01010101u) * 0xF0u;
+            }
+            s = __dp4a((int)lo, (int)xl[i], s);
+            s = __dp4a((int)hi, (int)xh[i], s);
+        }
     } else {
         // byte j of the 16 = elements j (low nibble) and j + 16 (high nibble), unsigned 0..15 (ggml.c:2722-2726)
         s = __dp4a((int)(w0.x & 0x0F0F0F0Fu), (int)x0.x, s); s = __dp4a((int)((w0.x >> 4) & 0x0F0F0F0Fu), (int)x1.x, s);
@@ -131,7 +170,7 @@ __device__ __forceinline__ void quantize_column(const float * __restrict__ xc, i
             const uint32_t w1 = (uint32_t)(q[4] & 0xFF) | ((uint32_t)(q[5] & 0xFF) << 8) | ((uint32_t)(q[6] & 0xFF) << 16) | ((uint32_t)(q[7] & 0xFF) << 24);
             *reinterpret_cast<uint2 *>(xq + 8 * j) = make_uint2(w0, w1);
             if ((j & 3) == 0) {
-                if (TYPE == GGML_B200_TYPE_Q8_0) xd[j >> 2] = __half2float(__float2half_rn(d));      // block_q8_0.d is fp16 (ggml.c:1214-1215)
+                if (!act_q8_1(TYPE)) xd[j >> 2] = __half2float(__float2half_rn(d));                  // block_q8_0.d is fp16 (ggml.c:1214-1215)
                 else { xd[j >> 2] = d; xs[j >> 2] = __fmul_rn(d, (float)sum); }                      // block_q8_1: float d, s = d * sum (ggml.c:1419,1449)
             }
         }
@@ -150,6 +189,12 @@ __device__ __forceinline__ void load_blocks(const uint4 * __restrict__ wq, const
                 w1[u] = ldg_stream_u4(wq + 2 * (rb + b) + 1);
                 dw[u] = __half2float(__ushort_as_half(ldg_stream_u16(reinterpret_cast<const unsigned short *>(wd) + rb + b)));
                 mw[u] = 0.0f;
+            } else if (is_q5(TYPE)) {
+                w0[u] = ldg_stream_u4(wq + rb + b);
+                const uint32_t dm = ldg_stream_u32(reinterpret_cast<const uint32_t *>(wd) + 2 * (rb + b));
+                w1[u] = make_uint4(ldg_stream_u32(reinterpret_cast<const uint32_t *>(wd) + 2 * (rb + b) + 1), 0u, 0u, 0u);    // qh
+                dw[u] = __half2float(__ushort_as_half((unsigned short)(dm & 0xFFFF)));
+                mw[u] = __half2float(__ushort_as_half((unsigned short)(dm >> 16)));
             } else {
                 w0[u] = ldg_stream_u4(wq + rb + b);
                 w1[u] = w0[u];
@@ -209,7 +254,7 @@ sib_gemv_kernel(const uint4 * __restrict__ wq, const void * __restrict__ wd, con
                             if (DUMP) S_out[((c0 + c) * M + row) * nbk + b] = S;
                             // d = d_w * d_x rounded, then acc = fma(d, float(S), acc): ggml.c:3305-3313 / :2692-2706
                             acc[c] = fmaf(__fmul_rn(dw[u], xd[c * nbk + b]), (float)S, acc[c]);
-                            if (TYPE == GGML_B200_TYPE_Q4_1) mins[c] = __fadd_rn(mins[c], __fmul_rn(mw[u], xs[c * nbk + b]));   // summs += m * s, ggml.c:2688
+                            if (act_q8_1(TYPE)) mins[c] = __fadd_rn(mins[c], __fmul_rn(mw[u], xs[c * nbk + b]));   // summs += m * s, ggml.c:2688 / :3153
                         }
                     }
                 }
@@ -222,7 +267,7 @@ sib_gemv_kernel(const uint4 * __restrict__ wq, const void * __restrict__ wd, con
                 acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], o);
                 mins[c] += __shfl_xor_sync(0xffffffffu, mins[c], o);
             }
-            if (lane == 0 && c < nc) y[(size_t)c * ldy + row] = TYPE == GGML_B200_TYPE_Q4_1 ? __fadd_rn(acc[c], mins[c]) : acc[c];   // hsum(acc) + summs
+            if (lane == 0 && c < nc) y[(size_t)c * ldy + row] = act_q8_1(TYPE) ? __fadd_rn(acc[c], mins[c]) : acc[c];   // hsum(acc) + summs
         }
     }
     (void)n_total;
@@ -243,7 +288,7 @@ __global__ void __launch_bounds__(256) sib_quantize_blocks_kernel(const float * 
     const int w = threadIdx.x >> 5;
     quantize_block<TYPE>(v, lane, q[w], &d[w], &s[w]);
     __syncwarp();
-    if (TYPE == GGML_B200_TYPE_Q8_0) {
+    if (!act_q8_1(TYPE)) {
         unsigned char * blk = out + (size_t)gw * 34;
         if (lane == 0) *reinterpret_cast<unsigned short *>(blk) = __half_as_ushort(__float2half_rn(d[w]));
         blk[2 + lane] = (unsigned char)q[w][lane];
@@ -260,12 +305,12 @@ __global__ void __launch_bounds__(256) sib_quantize_blocks_kernel(const float * 
 // ================================= C ABI =================================
 using namespace b200;
 
-static bool sib_type_ok(int type) { return type == GGML_B200_TYPE_Q8_0 || type == GGML_B200_TYPE_Q4_1; }
+static bool sib_type_ok(int type) { return type == GGML_B200_TYPE_Q8_0 || type == GGML_B200_TYPE_Q4_1 || type == GGML_B200_TYPE_Q5_0 || type == GGML_B200_TYPE_Q5_1; }
 
 extern "C" ggml_b200_qweight * ggml_b200_upload_quant(int type, const void * blocks, int64_t M, int64_t K, size_t nb1) {
     B200_API_LOCK;
     if (!g.inited) { set_error("ggml_b200_upload_quant: library not initialised"); return nullptr; }
-    if (!sib_type_ok(type)) { set_error("ggml_b200_upload_quant: type %d is not Q8_0 (8) or Q4_1 (3)", type); return nullptr; }
+    if (!sib_type_ok(type)) { set_error("ggml_b200_upload_quant: type %d is not Q8_0 (8), Q4_1 (3), Q5_0 (6) or Q5_1 (7)", type); return nullptr; }
     if (!blocks || M <= 0 || K <= 0 || K % 32 != 0) { set_error("ggml_b200_upload_quant: bad shape M=%lld K=%lld", (long long)M, (long long)K); return nullptr; }
     const int64_t nbk = K / 32;
     const size_t row_bytes = (size_t)nbk * sib::block_bytes(type);
@@ -274,7 +319,7 @@ extern "C" ggml_b200_qweight * ggml_b200_upload_quant(int type, const void * blo
     ggml_b200_qweight * w = new ggml_b200_qweight();
     w->type = type; w->M = M; w->K = K;
     const size_t q_bytes = (size_t)M * nbk * (type == GGML_B200_TYPE_Q8_0 ? 32 : 16);
-    const size_t d_bytes = (size_t)M * nbk * (type == GGML_B200_TYPE_Q8_0 ? 2 : 4);
+    const size_t d_bytes = (size_t)M * nbk * (type == GGML_B200_TYPE_Q8_0 ? 2 : type == GGML_B200_TYPE_Q4_1 ? 4 : 8);
     unsigned char * raw = nullptr;
     cudaError_t e = cudaMalloc(&w->wq, q_bytes + 16);
     if (e == cudaSuccess) e = cudaMalloc(&w->wd, d_bytes + 16);
@@ -283,8 +328,10 @@ extern "C" ggml_b200_qweight * ggml_b200_upload_quant(int type, const void * blo
     if (e == cudaSuccess) {
         const long long total = (long long)M * nbk;
         const unsigned grid = (unsigned)((total + 255) / 256);
-        if (type == GGML_B200_TYPE_Q8_0) sib::repack_kernel<GGML_B200_TYPE_Q8_0><<<grid, 256, 0, g.stream>>>(raw, nb1, M, (int)nbk, w->wq, w->wd);
-        else                             sib::repack_kernel<GGML_B200_TYPE_Q4_1><<<grid, 256, 0, g.stream>>>(raw, nb1, M, (int)nbk, w->wq, w->wd);
+        if (type == GGML_B200_TYPE_Q8_0)      sib::repack_kernel<GGML_B200_TYPE_Q8_0><<<grid, 256, 0, g.stream>>>(raw, nb1, M, (int)nbk, w->wq, w->wd);
+        else if (type == GGML_B200_TYPE_Q4_1) sib::repack_kernel<GGML_B200_TYPE_Q4_1><<<grid, 256, 0, g.stream>>>(raw, nb1, M, (int)nbk, w->wq, w->wd);
+        else if (type == GGML_B200_TYPE_Q5_0) sib::repack_kernel<GGML_B200_TYPE_Q5_0><<<grid, 256, 0, g.stream>>>(raw, nb1, M, (int)nbk, w->wq, w->wd);
+        else                                  sib::repack_kernel<GGML_B200_TYPE_Q5_1><<<grid, 256, 0, g.stream>>>(raw, nb1, M, (int)nbk, w->wq, w->wd);
         e = cudaGetLastError();
         g.launches++;
     }
@@ -356,15 +403,17 @@ static int sib_mul_mat(const ggml_b200_qweight * w, const float * x_dev, int64_t
         const float * xc = reinterpret_cast<const float *>(reinterpret_cast<const char *>(x_dev) + (size_t)c0 * nb11);
         float * yc = y_dev + (size_t)c0 * ldy;
         int rc;
-        if (w->type == GGML_B200_TYPE_Q8_0) {
-            if (S_dev)        rc = sib_launch<GGML_B200_TYPE_Q8_0, true, sib::SIB_NC>(w, xc, nb11, yc, ldy, nc, S_dev, n, c0);
-            else if (nc == 1) rc = sib_launch<GGML_B200_TYPE_Q8_0, false, 1>(w, xc, nb11, yc, ldy, nc, nullptr, n, c0);       // decode: one column
-            else              rc = sib_launch<GGML_B200_TYPE_Q8_0, false, sib::SIB_NC>(w, xc, nb11, yc, ldy, nc, nullptr, n, c0);
-        } else {
-            if (S_dev)        rc = sib_launch<GGML_B200_TYPE_Q4_1, true, sib::SIB_NC>(w, xc, nb11, yc, ldy, nc, S_dev, n, c0);
-            else if (nc == 1) rc = sib_launch<GGML_B200_TYPE_Q4_1, false, 1>(w, xc, nb11, yc, ldy, nc, nullptr, n, c0);
-            else              rc = sib_launch<GGML_B200_TYPE_Q4_1, false, sib::SIB_NC>(w, xc, nb11, yc, ldy, nc, nullptr, n, c0);
-        }
+#define SIB_DISPATCH(T)                                                                                                   \
+        do {                                                                                                              \
+            if (S_dev)        rc = sib_launch<T, true, sib::SIB_NC>(w, xc, nb11, yc, ldy, nc, S_dev, n, c0);              \
+            else if (nc == 1) rc = sib_launch<T, false, 1>(w, xc, nb11, yc, ldy, nc, nullptr, n, c0); /* decode */        \
+            else              rc = sib_launch<T, false, sib::SIB_NC>(w, xc, nb11, yc, ldy, nc, nullptr, n, c0);           \
+        } while (0)
+        if (w->type == GGML_B200_TYPE_Q8_0)      SIB_DISPATCH(GGML_B200_TYPE_Q8_0);
+        else if (w->type == GGML_B200_TYPE_Q4_1) SIB_DISPATCH(GGML_B200_TYPE_Q4_1);
+        else if (w->type == GGML_B200_TYPE_Q5_0) SIB_DISPATCH(GGML_B200_TYPE_Q5_0);
+        else                                     SIB_DISPATCH(GGML_B200_TYPE_Q5_1);
+#undef SIB_DISPATCH
         if (rc != GGML_B200_OK) return rc;
     }
     return GGML_B200_OK;
@@ -389,8 +438,9 @@ extern "C" int ggml_b200_quantize_dot_blocks(int type, const float * x_dev, int6
     if (nb11 == 0) nb11 = (size_t)K * 4;
     const long long warps = (long long)n * (K / 32);
     const unsigned grid = (unsigned)((warps * 32 + 255) / 256);
-    if (type == GGML_B200_TYPE_Q8_0) sib::sib_quantize_blocks_kernel<GGML_B200_TYPE_Q8_0><<<grid, 256, 0, g.stream>>>(x_dev, nb11, n, (int)K, (unsigned char *)blocks_dev);
-    else                             sib::sib_quantize_blocks_kernel<GGML_B200_TYPE_Q4_1><<<grid, 256, 0, g.stream>>>(x_dev, nb11, n, (int)K, (unsigned char *)blocks_dev);
+    // the activation format of the weight type: q8_0 for Q8_0 / Q5_0, q8_1 for Q4_1 / Q5_1
+    if (!sib::act_q8_1(type)) sib::sib_quantize_blocks_kernel<GGML_B200_TYPE_Q8_0><<<grid, 256, 0, g.stream>>>(x_dev, nb11, n, (int)K, (unsigned char *)blocks_dev);
+    else                      sib::sib_quantize_blocks_kernel<GGML_B200_TYPE_Q4_1><<<grid, 256, 0, g.stream>>>(x_dev, nb11, n, (int)K, (unsigned char *)blocks_dev);
     CK(cudaGetLastError());
     g.launches++;
     return GGML_B200_OK;

@@ -279,13 +279,13 @@ class Weight:
             pass
 
 
-TYPE_Q4_1, TYPE_Q8_0 = 3, 8          # the reference's ggml_type values (ggml.h:230-242)
-QUANT_BLOCK_BYTES = {TYPE_Q4_1: 20, TYPE_Q8_0: 34}
-DOT_BLOCK_BYTES = {TYPE_Q4_1: 40, TYPE_Q8_0: 34}     # block_q8_1 / block_q8_0
+TYPE_Q4_1, TYPE_Q5_0, TYPE_Q5_1, TYPE_Q8_0 = 3, 6, 7, 8          # the reference's ggml_type values (ggml.h:230-242)
+QUANT_BLOCK_BYTES = {TYPE_Q4_1: 20, TYPE_Q5_0: 22, TYPE_Q5_1: 24, TYPE_Q8_0: 34}
+DOT_BLOCK_BYTES = {TYPE_Q4_1: 40, TYPE_Q5_0: 34, TYPE_Q5_1: 40, TYPE_Q8_0: 34}     # block_q8_1 (formats with a min term) / block_q8_0
 
 
 class QuantWeight:
-    """A device-resident Q8_0 or Q4_1 weight (ggml_b200_upload_quant): the op's sibling formats."""
+    """A device-resident Q8_0 / Q4_1 / Q5_0 / Q5_1 weight (ggml_b200_upload_quant): the op's sibling formats."""
 
     def __init__(self, qtype: int, blocks: np.ndarray):
         blocks = np.ascontiguousarray(blocks, dtype=np.uint8)

@@ -195,7 +195,7 @@ static ggml_b200_weight * weight_of(const struct ggml_tensor * t) {
     return e->data_device[1] == B200_MAGIC_WEIGHT ? (ggml_b200_weight *)e->data_device[0] : NULL;
 }
 
-/* the sibling formats: Q8_0 and Q4_1 weights, single GPU */
+/* the sibling formats: Q8_0, Q4_1, Q5_0 and Q5_1 weights, single GPU */
 static ggml_b200_qweight * qweight_of(const struct ggml_tensor * t) {
     if (t == NULL || t->extra == NULL) return NULL;
     if (t->backend != GGML_BACKEND_GPU && t->backend != GGML_BACKEND_GPU_SPLIT) return NULL;
@@ -224,7 +224,7 @@ void ggml_cuda_transform_tensor(void * data, struct ggml_tensor * tensor) {
         tensor->extra = extra;
         return;
     }
-    const int sib_2d = (tensor->type == GGML_TYPE_Q8_0 || tensor->type == GGML_TYPE_Q4_1) && tensor->ne[2] == 1 && tensor->ne[3] == 1 &&
+    const int sib_2d = (tensor->type == GGML_TYPE_Q8_0 || tensor->type == GGML_TYPE_Q4_1 || tensor->type == GGML_TYPE_Q5_0 || tensor->type == GGML_TYPE_Q5_1) && tensor->ne[2] == 1 && tensor->ne[3] == 1 &&
                        (tensor->ne[0] % 64) == 0 && ggml_b200_comm_world() <= 1;
     if (g_ready && sib_2d) {
         ggml_b200_qweight * w = ggml_b200_upload_quant((int)tensor->type, data, tensor->ne[1], tensor->ne[0], tensor->nb[1]);

@@ -12,11 +12,11 @@
 
 int ggml_b200_glue_ready(void);
 
-/* wtype: 0 = Q4_0 blocks [M][K/32][18], 1 = F32 [M][K], 3 = Q4_1 blocks (20 B), 8 = Q8_0 blocks (34 B).  offload: 0 = CPU, 1 = GGML_BACKEND_GPU, 2 = GPU_SPLIT.
+/* wtype: 0 = Q4_0 blocks [M][K/32][18], 1 = F32 [M][K], 3 / 6 / 7 / 8 = Q4_1 / Q5_0 / Q5_1 / Q8_0 blocks (the reference's type values).  offload: 0 = CPU, 1 = GGML_BACKEND_GPU, 2 = GPU_SPLIT.
  * Returns 0, or -1 when the context could not be created. */
 int glue_graph_mul_mat(const void * wdata, int wtype, int64_t M, int64_t K, const float * x, int64_t n, float * y,
                        int n_threads, int offload) {
-    const enum ggml_type t = wtype == 0 ? GGML_TYPE_Q4_0 : wtype == 3 ? GGML_TYPE_Q4_1 : wtype == 8 ? GGML_TYPE_Q8_0 : GGML_TYPE_F32;
+    const enum ggml_type t = wtype == 0 ? GGML_TYPE_Q4_0 : wtype == 1 ? GGML_TYPE_F32 : (enum ggml_type)wtype;
     const size_t wbytes = wtype == 1 ? (size_t)M * K * 4 : (size_t)M * (K / 32) * ggml_type_size(t);
     size_t mem = wbytes + (size_t)n * K * 4 + (size_t)n * M * 4 + (size_t)n * (K / 32) * 40 * 2 + (64u << 20);
     struct ggml_init_params ip = { mem, NULL, false };

@@ -102,7 +102,7 @@ def test_reference_graph_runs_the_op_on_the_gpu(b200, port, ref, M, K, n, offloa
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("qtype", [8, 3])
+@pytest.mark.parametrize("qtype", [8, 3, 6, 7])
 @pytest.mark.parametrize("M,K,n", [(512, 1024, 1), (4096, 4544 - 4544 % 64 + 64, 1), (300, 1088, 7)])
 def test_reference_graph_runs_the_sibling_formats_on_the_gpu(b200, ref, qtype, M, K, n):
     """SURVEY 8f-4 through the seam: a Q8_0 / Q4_1 weight uploaded by ggml_cuda_transform_tensor, the op taken by the hook

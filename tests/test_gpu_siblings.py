@@ -1,4 +1,4 @@
-"""Sibling formats Q8_0 and Q4_1 on the GPU against the oracle: the activation blocks the kernel's
+"""Sibling formats Q8_0, Q4_1, Q5_0 and Q5_1 on the GPU against the oracle: the activation blocks the kernel's
 fused quantizer forms and the int32 block dots bit-exact, the fp32 result within 1e-4 (north_star's tolerance,
 relative to the largest |y| of the column)."""
 import numpy as np
@@ -7,7 +7,7 @@ import pytest
 from oracle import siblings as sib
 
 pytestmark = pytest.mark.gpu
-TYPES = [sib.TYPE_Q8_0, sib.TYPE_Q4_1]
+TYPES = [sib.TYPE_Q8_0, sib.TYPE_Q4_1, sib.TYPE_Q5_0, sib.TYPE_Q5_1]
 TOL = 1e-4
 
 
@@ -19,7 +19,7 @@ def _weights(qtype, seed, M, K):
     d = (rng.uniform(0.002, 0.02, size=(M, nbk)) * rng.choice([-1.0, 1.0], size=(M, nbk))).astype(np.float16)
     W[..., 0:2] = d.view(np.uint8).reshape(M, nbk, 2)
     off = 2
-    if qtype == sib.TYPE_Q4_1:
+    if qtype in (sib.TYPE_Q4_1, sib.TYPE_Q5_1):
         m = rng.uniform(-0.2, 0.2, size=(M, nbk)).astype(np.float16)
         W[..., 2:4] = m.view(np.uint8).reshape(M, nbk, 2)
         off = 4

@@ -5,7 +5,7 @@ import pytest
 
 from oracle import siblings as sib
 
-TYPES = [sib.TYPE_Q8_0, sib.TYPE_Q4_1]
+TYPES = [sib.TYPE_Q8_0, sib.TYPE_Q4_1, sib.TYPE_Q5_0, sib.TYPE_Q5_1]
 
 
 def _rows(seed, n, K, scale=1.0, huge=1e30):
@@ -28,6 +28,8 @@ def test_activation_blocks_bit_exact(ref, qtype):
 def test_weight_codecs_bit_exact(ref):
     x = _rows(7, 6, 4096)
     assert np.array_equal(sib.quantize_q4_1_reference(x), ref.type_quantize(sib.TYPE_Q4_1, x))
+    assert np.array_equal(sib.quantize_q5_0_reference(x), ref.type_quantize(sib.TYPE_Q5_0, x))
+    assert np.array_equal(sib.quantize_q5_1_reference(x), ref.type_quantize(sib.TYPE_Q5_1, x))
     # quantize_row_q of Q8_0 is the SIMD quantize_row_q8_0 (ggml.c:1660-1666): the activation contract
     assert np.array_equal(sib.quantize_dot(sib.TYPE_Q8_0, x), ref.type_quantize(sib.TYPE_Q8_0, x))
 
@@ -61,7 +63,7 @@ def test_block_dots_are_the_integer_part_of_vec_dot(ref, qtype):
     W = np.zeros((4, 2, sib.BLOCK_BYTES[qtype]), dtype=np.uint8)
     one = np.array([1.0], dtype=np.float16).view(np.uint8)
     W[..., 0:2] = one
-    off = 2 if qtype == sib.TYPE_Q8_0 else 4
+    off = {sib.TYPE_Q8_0: 2, sib.TYPE_Q4_1: 4, sib.TYPE_Q5_0: 2, sib.TYPE_Q5_1: 4}[qtype]     # after d (and m = 0): quants, or qh + quants
     W[..., off:] = rng.integers(0, 256, size=W[..., off:].shape, dtype=np.uint8)
     X = np.rint(rng.standard_normal((2, 64)) * 40).astype(np.float32)
     X[:, 0] = 127.0                                            # amax = 127 -> d = 1, the quants are the values
