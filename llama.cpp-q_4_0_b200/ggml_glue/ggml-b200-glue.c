@@ -370,6 +370,15 @@ struct plan {
 #define SEG_CACHE 192
 static struct plan g_seg[SEG_MAX];
 static int g_seg_n = 0;
+/* beside the plans (not part of the replay key): the tensors a plan computes and whether a later plan of the segment
+ * reads them.  Results nothing in the segment reads (wq/wk/wv of a layer whose attention runs on the CPU) are what the
+ * next CPU nodes will ask for: their copies to the host are queued right behind the segment instead of one by one, each
+ * with its own wait (flush_segment). */
+static struct ggml_tensor * g_seg_out[SEG_MAX][2];
+static unsigned char g_seg_read[SEG_MAX][2];
+static void seg_mark_read(const struct ggml_tensor * t) {
+    for (int i = 0; i < g_seg_n; i++) for (int o = 0; o < 2; o++) if (g_seg_out[i][o] == t) g_seg_read[i][o] = 1;
+}
 static struct ggml_tensor * g_seg_last = NULL;       /* the tensor the last plan computes (for the peephole) */
 static struct { struct plan * plans; int n; void * exec; int seen; } g_cache[SEG_CACHE];
 static int g_cache_n = 0, g_cache_cursor = 0;
@@ -465,6 +474,15 @@ static void flush_segment(void) {
         }
     }
     for (int i = 0; i < g_seg_n; i++) if (g_seg[i].d2h_bytes || g_seg[i].h2d_bytes[0] || g_seg[i].h2d_bytes[1]) g_pending = 1;
+    for (int i = 0; i < g_seg_n; i++) for (int o = 0; o < 2; o++) {
+        struct ggml_tensor * t = g_seg_out[i][o];
+        if (t == NULL || g_seg_read[i][o] || !is_act(t) || t->data == NULL) continue;
+        struct ggml_tensor_extra_gpu * e = (struct ggml_tensor_extra_gpu *)t->extra;
+        if (e->data_device[2] != NULL) continue;
+        B200_CHECK(ggml_b200_memcpy_d2h_async(t->data, e->data_device[0], ggml_nbytes(t)));     /* in graph order: t's node is behind us */
+        e->data_device[2] = t->data;
+        g_pending = 1;
+    }
     g_seg_n = 0;
     g_seg_last = NULL;
     if (g_prof_on > 0) g_prof.flush_s += now_s() - t0;
@@ -531,12 +549,16 @@ static void device_node(struct ggml_tensor * t) {
     if (fuse && g_seg[g_seg_n - 1].kind == PL_RMS_NORM) {
         struct plan * q = &g_seg[g_seg_n - 1];                   /* y = rms_norm(a); y2 = y * w: one kernel */
         q->kind = PL_RMS_NORM_MUL; q->b = dev_ptr(t->src1); q->nb = ggml_nelements(t->src1); q->y2 = plan_dst(q, t);
+        seg_mark_read(t->src0); seg_mark_read(t->src1);
+        g_seg_out[g_seg_n - 1][1] = t; g_seg_read[g_seg_n - 1][1] = 0;
         g_seg_last = t;
         return;
     }
     if (fuse && g_seg[g_seg_n - 1].kind == PL_SILU && ggml_nelements(t->src1) == p->n) {
         struct plan * q = &g_seg[g_seg_n - 1];                   /* y = silu(a); y2 = y * b */
         q->kind = PL_SILU_MUL; q->b = dev_ptr(t->src1); q->y2 = plan_dst(q, t);
+        seg_mark_read(t->src0); seg_mark_read(t->src1);
+        g_seg_out[g_seg_n - 1][1] = t; g_seg_read[g_seg_n - 1][1] = 0;
         g_seg_last = t;
         return;
     }
@@ -568,9 +590,12 @@ static void device_node(struct ggml_tensor * t) {
     }
     /* (plan_src / plan_dst may have flushed the segment to grow a staging block: append at the current end) */
     if (p != &g_seg[g_seg_n]) g_seg[g_seg_n] = *p;
+    seg_mark_read(t->src0); seg_mark_read(t->src1);
+    g_seg_out[g_seg_n][0] = t; g_seg_out[g_seg_n][1] = NULL; g_seg_read[g_seg_n][0] = 0; g_seg_read[g_seg_n][1] = 0;
     g_seg_n++;
     g_seg_last = t;
-    if (g_seg[g_seg_n - 1].d2h_bytes) flush_segment();     /* a host-resident result: get it on its way now */
+    /* a host-resident result is copied back inside the segment (stream order); the segment is submitted when a CPU node
+     * needs something (the hook below).  Submitting here, per result, cost two extra graph launches and waits per layer. */
 }
 
 /* ggml_cuda_compute_forward (ggml-cuda.cu:2966-3082): the pre-hook of ggml_compute_forward (ggml.c:15645-15649).
