@@ -312,6 +312,49 @@ def test_falcon_7b_shapes_offloaded_to_b200_match_cpu_reference(tmp_path):
     assert _launches(log) >= 129 + 2 * 129, log[-500:]
 
 
+# ---------------------------------------------------------------------------- arch/gptneox through the seam
+NEOX_CPU_SO = os.path.join(PKG, "ggml_glue", "_build", "libgptneox_ref_cpu.so")
+NEOX_B200_SO = os.path.join(PKG, "ggml_glue", "_build", "libgptneox_b200.so")
+
+
+def _neox_model(tmp_path):
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests", "glue"))
+    import make_tiny_gptneox
+    if not (os.path.exists(NEOX_CPU_SO) and os.path.exists(NEOX_B200_SO)):
+        pytest.skip("ggml_glue/_build/libgptneox_*.so not built (needs /root/reference at build time)")
+    return make_tiny_gptneox.write_model(str(tmp_path / "gptneox_tiny_q4_0.bin"))
+
+
+def test_tiny_gptneox_through_the_seam_without_a_gpu_is_the_cpu_reference(tmp_path):
+    """arch/gptneox/gptneox.cpp with the loader tag over the glue: bit-identical to the plain CPU build without a B200."""
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("GPU present: covered by the gpu-marked twin")
+    except ImportError:
+        pass
+    model = _neox_model(tmp_path)
+    cpu, _ = _falcon_logits(tmp_path, NEOX_CPU_SO, 9, model)
+    seam, _ = _falcon_logits(tmp_path, NEOX_B200_SO, 9, model)
+    assert np.isfinite(cpu).all() and np.abs(cpu).max() > 1.0
+    assert np.array_equal(cpu, seam)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_prompt", [6, 40])
+def test_tiny_gptneox_offloaded_to_b200_matches_cpu_reference(tmp_path, n_prompt):
+    """A 16-layer GPT-NeoX (fused QKV + biases, parallel residual; Q4_0) through the reference's own gptneox loader and
+    gptneox_eval: the 4 matrices of every layer and embed_out run on the B200 (65 matmuls per eval), the bias adds and
+    everything else on the reference CPU code."""
+    model = _neox_model(tmp_path)
+    cpu, _ = _falcon_logits(tmp_path, NEOX_CPU_SO, n_prompt, model)
+    gpu, log = _falcon_logits(tmp_path, NEOX_B200_SO, n_prompt, model)
+    assert np.isfinite(gpu).all()
+    _compare_logits(cpu, gpu, 3e-2)
+    assert _launches(log) >= 65 + 2 * 65, log[-500:]
+
+
 def test_layer_graph_driver_on_the_cpu_is_deterministic():
     """tests/glue/layer_driver.c (a LLaMA decode graph built with the reference's API) on the plain CPU path."""
     G = _layer_lib()
