@@ -2,7 +2,7 @@
 // falcon_eval, falcon_get_logits; falcon.cpp:2189-2260, :2848-2870): loads a model file with the reference's loader,
 // evaluates a prompt (n > 1) and then one more token (n = 1), returns both logit vectors.  Built twice by
 // ggml_glue/Makefile: against the plain CPU reference (the truth) and against the reference compiled -DGGML_USE_CUBLAS
-// with the loader tag (tests/glue/patch_falcon.py) + ggml-b200-glue.c + libggml_b200.so.  Test infrastructure only.
+// with the loader tag (tests/glue/patch_arch.py) + ggml-b200-glue.c + libggml_b200.so.  Test infrastructure only.
 #include <cstdio>
 #include <cstring>
 #include <vector>

@@ -250,7 +250,7 @@ def _falcon_logits(tmp_path, lib, n_prompt, model, threads=4, timeout=1800):
 
 def test_tiny_falcon_through_the_seam_without_a_gpu_is_the_cpu_reference(tmp_path):
     """arch/falcon/falcon.cpp (loader + graph builder, falcon_eval) built -DGGML_USE_CUBLAS over the glue with the loader
-    tag applied (tests/glue/patch_falcon.py): on a host without a B200 nothing is offloaded (ggml_cuda_transform_tensor
+    tag applied (tests/glue/patch_arch.py): on a host without a B200 nothing is offloaded (ggml_cuda_transform_tensor
     hands the bytes back to the CPU code) and the logits are bit-identical to the plain CPU build."""
     try:
         import torch
