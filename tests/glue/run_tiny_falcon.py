@@ -11,7 +11,7 @@ import numpy as np
 lib, model, n_prompt, out = sys.argv[1], sys.argv[2], int(sys.argv[3]), sys.argv[4]
 threads = int(sys.argv[5]) if len(sys.argv) > 5 else 4
 L = C.CDLL(lib)
-run = L.tiny_gptneox_run if "gptneox" in lib else L.tiny_falcon_run
+run = L.tiny_gptneox_run if "gptneox" in lib else L.tiny_rwkv_run if "rwkv" in lib else L.tiny_falcon_run
 run.restype = C.c_int
 NV = 512
 toks = [(7 * i + 3) % NV for i in range(n_prompt)]

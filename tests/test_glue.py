@@ -355,6 +355,58 @@ def test_tiny_gptneox_offloaded_to_b200_matches_cpu_reference(tmp_path, n_prompt
     assert _launches(log) >= 65 + 2 * 65, log[-500:]
 
 
+# ---------------------------------------------------------------------------- arch/rwkv through the seam
+RWKV_CPU_SO = os.path.join(PKG, "ggml_glue", "_build", "librwkv_ref_cpu.so")
+RWKV_B200_SO = os.path.join(PKG, "ggml_glue", "_build", "librwkv_b200.so")
+
+
+def _rwkv_model(tmp_path):
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests", "glue"))
+    import make_tiny_rwkv
+    if not (os.path.exists(RWKV_CPU_SO) and os.path.exists(RWKV_B200_SO)):
+        pytest.skip("ggml_glue/_build/librwkv_*.so not built (needs /root/reference at build time)")
+    return make_tiny_rwkv.write_model(str(tmp_path / "rwkv_tiny_q4_0.bin"))
+
+
+def test_tiny_rwkv_through_the_seam_without_a_gpu_is_the_cpu_reference(tmp_path):
+    """arch/rwkv/rwkv.cpp with the loader tag over the glue: bit-identical to the plain CPU build without a B200."""
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("GPU present: covered by the gpu-marked twin")
+    except ImportError:
+        pass
+    model = _rwkv_model(tmp_path)
+    cpu, _ = _falcon_logits(tmp_path, RWKV_CPU_SO, 9, model)
+    seam, _ = _falcon_logits(tmp_path, RWKV_B200_SO, 9, model)
+    assert np.isfinite(cpu).all() and 0.05 < np.abs(cpu).max() < 0.9       # soft-max probabilities (rwkv.cpp:1667), not saturated
+    assert np.array_equal(cpu, seam)
+
+
+@pytest.mark.gpu
+def test_tiny_rwkv_offloaded_to_b200_matches_cpu_reference(tmp_path):
+    """A 12-block RWKV (Q4_0) through the reference's own rwkv loader and rwkv_eval -- one token per call over a graph the
+    reference builds ONCE and re-runs (rwkv.cpp:1682-1760): the 7 matrices of every block and the head run on the B200
+    (85 n = 1 matmuls per token, 10 tokens), the recurrence and everything else on the reference CPU code.  rwkv_get_logits returns soft-max probabilities
+    (rwkv.cpp:1667); the tiny model's head is scaled so that they are not saturated."""
+    model = _rwkv_model(tmp_path)
+    cpu, _ = _falcon_logits(tmp_path, RWKV_CPU_SO, 9, model)
+    gpu, log = _falcon_logits(tmp_path, RWKV_B200_SO, 9, model)
+    assert np.isfinite(gpu).all()
+    # what comes back are soft-max probabilities through ggml's fp16 exp table (tiny ones are quantised, many exactly 0):
+    # d log p = d logit, so the bar of the other models' logits becomes a bar on log p of the tokens that matter
+    for i in range(2):
+        big = cpu[i] >= 1e-2 * cpu[i].max()
+        assert big.sum() >= 3
+        dlog = np.abs(np.log(gpu[i][big].astype(np.float64)) - np.log(cpu[i][big].astype(np.float64)))
+        cos = float(np.dot(cpu[i], gpu[i]) / (np.linalg.norm(cpu[i]) * np.linalg.norm(gpu[i])))
+        span = float(np.log(cpu[i].max()) - np.log(cpu[i][cpu[i] > 0].min()))          # the logits' range seen through the soft-max
+        assert float(dlog.max()) <= 3e-2 * span and cos >= 0.999, f"eval {i}: max|dlog p| = {dlog.max():.3e} of span {span:.1f}, cosine = {cos:.6f}"
+        assert int(cpu[i].argmax()) == int(gpu[i].argmax())
+    assert _launches(log) >= 85 + 10 * 85, log[-500:]
+
+
 def test_layer_graph_driver_on_the_cpu_is_deterministic():
     """tests/glue/layer_driver.c (a LLaMA decode graph built with the reference's API) on the plain CPU path."""
     G = _layer_lib()
