@@ -124,6 +124,10 @@ struct Dump {
 template <int H, bool DUMP>
 __device__ __forceinline__ void epi_half(const uint32_t (&r)[4 * NKG], uint64_t (&acc)[4 * NKG], const uint64_t (&dx2)[NKG],
                                          const float (&dw)[4], const float (&nc)[4], const Dump & dp, int blk, int lane) {
+    // The products rn(S_b * dw) are formed IN PLACE in the fragment's own register pairs, all of them before the first
+    // accumulation: with a separate temporary per product ptxas parks the temporaries in the OTHER fragment's (dead)
+    // registers and then has to sink that fragment's tcgen05.ld below these FMAs -- its latency lands on the critical path.
+    uint64_t t[2 * NKG];
 #pragma unroll
     for (int k = 0; k < NKG; k++) {
 #pragma unroll
@@ -139,9 +143,14 @@ __device__ __forceinline__ void epi_half(const uint32_t (&r)[4 * NKG], uint64_t 
                     if (c + 1 < dp.n) dst[(size_t)dp.rows * dp.nbk] = ((int)f1 - S_BIAS) >> S_SHIFT;
                 }
             }
-            const uint64_t t = fma_f32x2(pack_u32x2(f0, f1), pack_f32x2(dw[j], dw[j]), pack_f32x2(nc[j], nc[j]));   // == rn(S_b * dw) * 2^-49
-            fma_acc_f32x2(acc[k * 4 + j], t, dx2[k]);
+            t[2 * k + jj] = pack_u32x2(f0, f1);
+            fma_inplace_f32x2(t[2 * k + jj], pack_f32x2(dw[j], dw[j]), pack_f32x2(nc[j], nc[j]));   // == rn(S_b * dw) * 2^-49
         }
+    }
+#pragma unroll
+    for (int k = 0; k < NKG; k++) {
+#pragma unroll
+        for (int jj = 0; jj < 2; jj++) fma_acc_f32x2(acc[k * 4 + 2 * H + jj], t[2 * k + jj], dx2[k]);
     }
 }
 

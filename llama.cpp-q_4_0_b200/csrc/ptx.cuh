@@ -204,6 +204,10 @@ __device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c
     asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
     return d;
 }
+// a = a * b + c IN PLACE (the product replaces its packed operand: no third register pair)
+__device__ __forceinline__ void fma_inplace_f32x2(uint64_t & a, uint64_t b, uint64_t c) {
+    asm("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(a) : "l"(b), "l"(c));
+}
 // acc = a * b + acc with the accumulator pinned to one register pair (no copy after the FMA)
 __device__ __forceinline__ void fma_acc_f32x2(uint64_t & acc, uint64_t a, uint64_t b) {
     asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
