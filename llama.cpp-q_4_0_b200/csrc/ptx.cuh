@@ -208,6 +208,11 @@ __device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c
 __device__ __forceinline__ void fma_inplace_f32x2(uint64_t & a, uint64_t b, uint64_t c) {
     asm("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(a) : "l"(b), "l"(c));
 }
+// the same on a pair of 32-bit registers (the two halves of a tcgen05.ld fragment pair): the result lands in the very
+// registers the operand came in, whatever the register allocator would have preferred
+__device__ __forceinline__ void fma_inplace_pair_f32x2(uint32_t & lo, uint32_t & hi, uint64_t b, uint64_t c) {
+    asm("{\n\t.reg .b64 t;\n\tmov.b64 t, {%0, %1};\n\tfma.rn.f32x2 t, t, %2, %3;\n\tmov.b64 {%0, %1}, t;\n\t}" : "+r"(lo), "+r"(hi) : "l"(b), "l"(c));
+}
 // acc = a * b + acc with the accumulator pinned to one register pair (no copy after the FMA)
 __device__ __forceinline__ void fma_acc_f32x2(uint64_t & acc, uint64_t a, uint64_t b) {
     asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
