@@ -161,6 +161,21 @@ int          ggml_b200_silu_mul_f32(const float * x_dev, const float * b_dev, fl
 /* rms_norm and the MUL by the norm weights that follows it in every layer, one kernel; both results are written */
 int          ggml_b200_rms_norm_mul_f32(const float * x_dev, float * y_norm_dev, const float * w_dev, float * y_dev,
                                         int64_t ncols, int64_t nrows, int64_t nw, float eps);
+/* The decode (n = 1) op with the element-wise node BEHIND it folded into the kernel's store: no launch and no trip of
+ * the row through L2 for that node (the old back-end ran them as kernels of their own,
+ * ggml-cuda.cu:2830-2892).  Every result the graph names is still written; y / y1 / y3 are bit-identical to
+ * ggml_b200_mul_mat_q4_0, the fused result applies the same single fp32 operation as ggml_b200_add_f32 / _silu_mul_f32.
+ *   _add    : y = W x;  y2 = y + r                       residual add behind wo / w2 (llama.cpp:1462, :1504)
+ *   _swiglu : y1 = W1 x; y3 = W3 x; silu = silu(y1); y2 = silu * y3     the FFN gate (llama.cpp:1479-1497): x is read
+ *             once, row i of both weights streams through the same warp
+ * Device pointers, asynchronous; n = 1 only, the whole weight on this GPU in the plane layout (ggml_b200_neigh_ok
+ * returns 1), GGML_B200_ERR_ARG otherwise. */
+int          ggml_b200_neigh_ok(const ggml_b200_weight * w);
+int          ggml_b200_mul_mat_q4_0_add(const ggml_b200_weight * w, const float * x_dev, float * y_dev,
+                                        const float * r_dev, float * y2_dev);
+int          ggml_b200_mul_mat_q4_0_swiglu(const ggml_b200_weight * w1, const ggml_b200_weight * w3, const float * x_dev,
+                                           float * y1_dev, float * y3_dev, float * silu_dev /* may be NULL */,
+                                           float * y2_dev);
 /* A sequence of this library's asynchronous calls (ops, element-wise kernels, async copies) recorded once and submitted
  * as one CUDA graph launch afterwards: begin ... calls ... end -> handle; launch runs it on the current stream.  The
  * glue uses it for the device nodes between two CPU nodes of a ggml graph (same pointers every eval).  No allocation

@@ -25,6 +25,7 @@
 #include "gemv_q4_0_fused.cuh"
 #include "gemv_q4_0_p2p.cuh"
 #include "gemv_q4_0_hostio.cuh"
+#include "gemv_q4_0_neigh.cuh"
 #include "quantize_q8_0.cuh"
 #include "repack.cuh"
 #include "codec_q4_0.cuh"
@@ -440,6 +441,7 @@ int ggml_b200_set_tuning(const char * key, int value) {
     else if (!strcmp(key, "gemv_fused"))   { g.tune.gemv_fused = value != 0; }
     else if (!strcmp(key, "pdl"))          { g.tune.pdl = value != 0; }
     else if (!strcmp(key, "fused_threads")) { if (value < 32 || value > 1024 || (value & 31)) return GGML_B200_ERR_ARG; g.tune.fused_threads = value; }
+    else if (!strcmp(key, "small_copy"))   { g.tune.small_copy = value != 0; }
     else if (!strcmp(key, "fused_ctas_per_sm")) { if (value < 1 || value > 16) return GGML_B200_ERR_ARG; g.tune.fused_ctas_per_sm = value; }
     else if (!strcmp(key, "skip_quantize")) { g.tune.skip_quantize = value != 0; }
     else if (!strcmp(key, "host_fast"))    { g.tune.host_fast = value != 0; }
@@ -459,12 +461,33 @@ int ggml_b200_set_tuning(const char * key, int value) {
     return GGML_B200_OK;
 }
 
+// pinned blocks handed out here are mapped into the device's address space (unified addressing): the asynchronous
+// copies below move small rows to / from them with a kernel instead of a copy-engine transfer (see small_copy)
+struct PinnedRange { const char * base; size_t size; };
+static PinnedRange g_pinned[64];
+static int g_pinned_n = 0;
+static std::mutex g_pinned_mu;
 void * ggml_b200_host_malloc(size_t size) {
     void * p = nullptr;
     if (cudaMallocHost(&p, size) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    std::lock_guard<std::mutex> lk(g_pinned_mu);
+    if (g_pinned_n < 64) g_pinned[g_pinned_n++] = { (const char *)p, size };
     return p;
 }
-void ggml_b200_host_free(void * p) { if (p) cudaFreeHost(p); }
+void ggml_b200_host_free(void * p) {
+    if (!p) return;
+    {
+        std::lock_guard<std::mutex> lk(g_pinned_mu);
+        for (int i = 0; i < g_pinned_n; i++) if (g_pinned[i].base == (const char *)p) { g_pinned[i] = g_pinned[--g_pinned_n]; break; }
+    }
+    cudaFreeHost(p);
+}
+static bool in_pinned_block(const void * p, size_t n) {
+    std::lock_guard<std::mutex> lk(g_pinned_mu);
+    for (int i = 0; i < g_pinned_n; i++)
+        if ((const char *)p >= g_pinned[i].base && (const char *)p + n <= g_pinned[i].base + g_pinned[i].size) return true;
+    return false;
+}
 
 void * ggml_b200_dev_malloc(size_t size) {
     void * p = nullptr;
@@ -631,13 +654,27 @@ static unsigned eltwise_grid(int64_t n) {
     const int64_t b = (n + 255) / 256;
     return (unsigned)(b < 1 ? 1 : b > (int64_t)g.sm_count * 8 ? (int64_t)g.sm_count * 8 : b);
 }
+// rows of up to 16384 floats, everything 16-byte aligned, weights one row or one per element: the register-resident kernel
+static int rms_norm_launch(const float * x, float * y, int64_t ncols, int64_t nrows, float eps, const float * w, float * y2, int64_t nw) {
+    const int wmode = w == nullptr ? 0 : nw == ncols ? 1 : nw == ncols * nrows ? 2 : -1;
+    const bool aligned = ((((uintptr_t)x) | ((uintptr_t)y) | ((uintptr_t)w) | ((uintptr_t)y2)) & 15) == 0;
+    if (wmode >= 0 && aligned && (ncols & 3) == 0 && ncols <= 16384) {
+        const int threads = (int)(((ncols / 4) + 31) / 32 * 32 > 1024 ? 1024 : ((ncols / 4) + 31) / 32 * 32);
+        if (ncols <= 4096)
+            return launch_k(rms_norm_f32_row_kernel<1>, dim3((unsigned)nrows), dim3(threads), 0, x, y, (int)ncols, eps, w, y2, wmode, (unsigned)g.launches);
+        if (ncols <= 8192)
+            return launch_k(rms_norm_f32_row_kernel<2>, dim3((unsigned)nrows), dim3(threads), 0, x, y, (int)ncols, eps, w, y2, wmode, (unsigned)g.launches);
+        return launch_k(rms_norm_f32_row_kernel<4>, dim3((unsigned)nrows), dim3(threads), 0, x, y, (int)ncols, eps, w, y2, wmode, (unsigned)g.launches);
+    }
+    return launch_k(rms_norm_f32_kernel, dim3((unsigned)nrows), dim3(256), 0, x, y, (int)ncols, eps, w, y2, (int)(w ? nw : 1), (unsigned)g.launches);
+}
 int ggml_b200_rms_norm_f32(const float * x_dev, float * y_dev, int64_t ncols, int64_t nrows, float eps) {
     B200_API_LOCK;
     int rc = eltwise_check(x_dev, y_dev, ncols);
     if (rc) return rc;
     if (nrows <= 0 || ncols == 0) return GGML_B200_OK;
     if (ncols > INT32_MAX || nrows > INT32_MAX) { set_error("rms_norm: shape too large"); return GGML_B200_ERR_ARG; }
-    return launch_k(rms_norm_f32_kernel, dim3((unsigned)nrows), dim3(256), 0, x_dev, y_dev, (int)ncols, eps, (const float *)nullptr, (float *)nullptr, 1);
+    return rms_norm_launch(x_dev, y_dev, ncols, nrows, eps, nullptr, nullptr, 1);
 }
 int ggml_b200_rms_norm_mul_f32(const float * x_dev, float * y_norm_dev, const float * w_dev, float * y_dev, int64_t ncols, int64_t nrows, int64_t nw, float eps) {
     B200_API_LOCK;
@@ -646,7 +683,7 @@ int ggml_b200_rms_norm_mul_f32(const float * x_dev, float * y_norm_dev, const fl
     if (!y_norm_dev || !w_dev || nw <= 0 || (ncols * nrows) % nw) { set_error("rms_norm_mul: bad arguments"); return GGML_B200_ERR_ARG; }
     if (nrows <= 0 || ncols == 0) return GGML_B200_OK;
     if (ncols > INT32_MAX || nrows > INT32_MAX || nw > INT32_MAX) { set_error("rms_norm_mul: shape too large"); return GGML_B200_ERR_ARG; }
-    return launch_k(rms_norm_f32_kernel, dim3((unsigned)nrows), dim3(256), 0, x_dev, y_norm_dev, (int)ncols, eps, w_dev, y_dev, (int)nw);
+    return rms_norm_launch(x_dev, y_norm_dev, ncols, nrows, eps, w_dev, y_dev, nw);
 }
 int ggml_b200_mul_f32(const float * a_dev, const float * b_dev, float * y_dev, int64_t n, int64_t nb) {
     B200_API_LOCK;
@@ -654,7 +691,7 @@ int ggml_b200_mul_f32(const float * a_dev, const float * b_dev, float * y_dev, i
     if (rc) return rc;
     if (!b_dev || nb <= 0 || n % nb) { set_error("mul: src1 must tile src0"); return GGML_B200_ERR_ARG; }
     if (n == 0) return GGML_B200_OK;
-    return launch_k(eltwise_f32_kernel<0>, dim3(eltwise_grid(n)), dim3(256), 0, a_dev, b_dev, y_dev, (long long)n, (long long)nb, (float *)nullptr);
+    return launch_k(eltwise_f32_kernel<0>, dim3(eltwise_grid(n)), dim3(256), 0, a_dev, b_dev, y_dev, (long long)n, (long long)nb, (float *)nullptr, (unsigned)g.launches);
 }
 int ggml_b200_add_f32(const float * a_dev, const float * b_dev, float * y_dev, int64_t n, int64_t nb) {
     B200_API_LOCK;
@@ -662,14 +699,14 @@ int ggml_b200_add_f32(const float * a_dev, const float * b_dev, float * y_dev, i
     if (rc) return rc;
     if (!b_dev || nb <= 0 || n % nb) { set_error("add: src1 must tile src0"); return GGML_B200_ERR_ARG; }
     if (n == 0) return GGML_B200_OK;
-    return launch_k(eltwise_f32_kernel<1>, dim3(eltwise_grid(n)), dim3(256), 0, a_dev, b_dev, y_dev, (long long)n, (long long)nb, (float *)nullptr);
+    return launch_k(eltwise_f32_kernel<1>, dim3(eltwise_grid(n)), dim3(256), 0, a_dev, b_dev, y_dev, (long long)n, (long long)nb, (float *)nullptr, (unsigned)g.launches);
 }
 int ggml_b200_silu_f32(const float * x_dev, float * y_dev, int64_t n) {
     B200_API_LOCK;
     int rc = eltwise_check(x_dev, y_dev, n);
     if (rc) return rc;
     if (n == 0) return GGML_B200_OK;
-    return launch_k(eltwise_f32_kernel<2>, dim3(eltwise_grid(n)), dim3(256), 0, x_dev, (const float *)nullptr, y_dev, (long long)n, (long long)n, (float *)nullptr);
+    return launch_k(eltwise_f32_kernel<2>, dim3(eltwise_grid(n)), dim3(256), 0, x_dev, (const float *)nullptr, y_dev, (long long)n, (long long)n, (float *)nullptr, (unsigned)g.launches);
 }
 int ggml_b200_silu_mul_f32(const float * x_dev, const float * b_dev, float * y_dev, int64_t n, float * silu_dev) {
     B200_API_LOCK;
@@ -677,7 +714,7 @@ int ggml_b200_silu_mul_f32(const float * x_dev, const float * b_dev, float * y_d
     if (rc) return rc;
     if (!b_dev) { set_error("silu_mul: null src1"); return GGML_B200_ERR_ARG; }
     if (n == 0) return GGML_B200_OK;
-    return launch_k(eltwise_f32_kernel<3>, dim3(eltwise_grid(n)), dim3(256), 0, x_dev, b_dev, y_dev, (long long)n, (long long)n, silu_dev);
+    return launch_k(eltwise_f32_kernel<3>, dim3(eltwise_grid(n)), dim3(256), 0, x_dev, b_dev, y_dev, (long long)n, (long long)n, silu_dev, (unsigned)g.launches);
 }
 
 // ---- a recorded sequence of this library's launches and copies as ONE submission (the glue replays the device nodes
@@ -718,8 +755,30 @@ void ggml_b200_graph_free(void * exec) {
     cudaGraphExecDestroy(ge->exec);
     delete ge;
 }
-int ggml_b200_memcpy_h2d_async(void * d, const void * s, size_t n) { CK(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, g.stream)); return GGML_B200_OK; }
-int ggml_b200_memcpy_d2h_async(void * d, const void * s, size_t n) { CK(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, g.stream)); return GGML_B200_OK; }
+// A decode graph moves rows of 16-64 KB between the host's compute buffer and HBM at every CPU node (q/k/v down, the
+// attention result up).  As copy-engine transfers each costs 8-11 us on the stream's critical path
+// (profiles/r02_trace_seam.log: the idle time between wq and wk); when the host side lies in a block from
+// ggml_b200_host_malloc (pinned AND mapped) a kernel moves the row over PCIe with 16-byte accesses instead -- posted
+// writes on the way down, a handful of read round trips on the way up -- and takes the programmatic launch edge like
+// every other kernel here.  Larger or unaligned copies, and pageable host memory, take cudaMemcpyAsync.
+constexpr size_t SMALL_COPY_MAX = (size_t)256 << 10;
+static bool small_copy_ok(const void * host, const void * dev, size_t n) {
+    return g.tune.small_copy && n > 0 && n <= SMALL_COPY_MAX && (n & 15) == 0 && ((((uintptr_t)host) | ((uintptr_t)dev)) & 15) == 0 && in_pinned_block(host, n);
+}
+static int small_copy(void * d, const void * s, size_t n) {
+    const int n16 = (int)(n / 16);
+    return launch_k(copy_rows_kernel, dim3((unsigned)((n16 + 127) / 128)), dim3(128), 0, (uint4 *)d, (const uint4 *)s, n16, (unsigned)g.launches);
+}
+int ggml_b200_memcpy_h2d_async(void * d, const void * s, size_t n) {
+    B200_API_LOCK;
+    if (small_copy_ok(s, d, n)) return small_copy(d, s, n);
+    CK(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, g.stream)); return GGML_B200_OK;
+}
+int ggml_b200_memcpy_d2h_async(void * d, const void * s, size_t n) {
+    B200_API_LOCK;
+    if (small_copy_ok(d, s, n)) return small_copy(d, s, n);
+    CK(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, g.stream)); return GGML_B200_OK;
+}
 
 // ---- kernel 1 ---------------------------------------------------------------------------------
 int ggml_b200_quantize_q8_0(const float * x_dev, int64_t n, int64_t K, size_t nb11, void * blocks34_dev) {
@@ -735,6 +794,53 @@ int ggml_b200_mul_mat_q4_0(const ggml_b200_weight * w, const float * x_dev, int6
     int rc = check_op_args(w, x_dev, n, nb11, y_dev, nb1);
     if (rc) return rc;
     return mul_mat_dev(w, x_dev, n, nb11, y_dev, nb1);
+}
+
+// ---- the op with its immediate neighbour folded into the store (gemv_q4_0_neigh.cuh) -------------
+// n = 1, this GPU holds every row of the weight, plane layout; anything else is GGML_B200_ERR_ARG (callers ask
+// ggml_b200_neigh_ok first and issue the nodes one by one otherwise).
+int ggml_b200_neigh_ok(const ggml_b200_weight * w) {
+    B200_API_LOCK;
+    return g.inited && w != nullptr && w->rows() == w->M && fused_ok(w, 1) ? 1 : 0;
+}
+
+static int launch_neigh(int EPI, NeighArgs & a, const ggml_b200_weight * w) {
+    a.nbk = (int)(w->K / QK); a.rows = (int)w->M; a.x_aligned = (((uintptr_t)a.x) & 15) == 0; a.seq = (unsigned)g.launches;
+    g.run.count = 0; g.run.x = nullptr;                 // reads more than x: never a member of a same-src1 run
+    const size_t smem = gemv_smem_bytes(a.nbk, 1);
+    if (EPI == NEIGH_ADD) {
+        auto kern = gemv_q4_0_neigh_kernel<4, 1024, NEIGH_ADD>;
+        B200_SET_SMEM_ATTR(kern, MAX_DYN_SMEM);
+        return launch_k(kern, g.sm_count, 1024, smem, a);
+    }
+    auto kern = gemv_q4_0_neigh_kernel<4, 512, NEIGH_SWIGLU>;
+    B200_SET_SMEM_ATTR(kern, MAX_DYN_SMEM);
+    return launch_k(kern, 2 * g.sm_count, 512, smem, a);
+}
+
+int ggml_b200_mul_mat_q4_0_add(const ggml_b200_weight * w, const float * x_dev, float * y_dev, const float * r_dev, float * y2_dev) {
+    B200_API_LOCK;
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    if (!w || !x_dev || !y_dev || !r_dev || !y2_dev) { set_error("mul_mat_q4_0_add: null argument"); return GGML_B200_ERR_ARG; }
+    if (w->rows() != w->M || !fused_ok(w, 1)) { set_error("mul_mat_q4_0_add: needs the whole weight on this GPU in the plane layout"); return GGML_B200_ERR_ARG; }
+    NeighArgs a{};
+    a.wq[0] = (const uint4 *)w->wq; a.wd[0] = (const __half *)w->wd; a.x = x_dev; a.r = r_dev; a.y = y_dev; a.y2 = y2_dev;
+    return launch_neigh(NEIGH_ADD, a, w);
+}
+
+int ggml_b200_mul_mat_q4_0_swiglu(const ggml_b200_weight * w1, const ggml_b200_weight * w3, const float * x_dev, float * y1_dev, float * y3_dev,
+                                  float * silu_dev, float * y2_dev) {
+    B200_API_LOCK;
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    if (!w1 || !w3 || !x_dev || !y1_dev || !y3_dev || !y2_dev) { set_error("mul_mat_q4_0_swiglu: null argument"); return GGML_B200_ERR_ARG; }
+    if (w1->K != w3->K || w1->M != w3->M) { set_error("mul_mat_q4_0_swiglu: the two weights differ in shape"); return GGML_B200_ERR_ARG; }
+    if (w1->rows() != w1->M || w3->rows() != w3->M || !fused_ok(w1, 1) || !fused_ok(w3, 1)) {
+        set_error("mul_mat_q4_0_swiglu: needs both whole weights on this GPU in the plane layout"); return GGML_B200_ERR_ARG;
+    }
+    NeighArgs a{};
+    a.wq[0] = (const uint4 *)w1->wq; a.wd[0] = (const __half *)w1->wd; a.wq[1] = (const uint4 *)w3->wq; a.wd[1] = (const __half *)w3->wd;
+    a.x = x_dev; a.y = y1_dev; a.yb = y3_dev; a.ys = silu_dev; a.y2 = y2_dev;
+    return launch_neigh(NEIGH_SWIGLU, a, w1);
 }
 
 // ---- the op without any allocation (no counterpart in the reference) ----------------------

@@ -36,6 +36,7 @@ struct Tune {
     int gemv_fused = 1;          // n == 1: quantize inside the GEMV kernel (one launch per op)
     int fused_threads = 1024;    // threads per CTA of the fused kernel
     int fused_ctas_per_sm = 1;
+    int small_copy = 1;          // rows <= 256 KB to / from mapped pinned host memory move with a kernel, not the copy engine
     int pdl = 1;                 // programmatic dependent launch between consecutive kernels
     int overlap_same_src = 0;    // n == 1: an op that reads the same x as the previous one does not wait for it (caller owns the stream)
     int host_fast = 1;           // n == 1 host entry: single-launch path with mapped staging rows and a completion word

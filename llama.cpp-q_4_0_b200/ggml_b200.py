@@ -122,6 +122,9 @@ def _load() -> C.CDLL:
         "ggml_b200_silu_f32": (C.c_int, [_vp, _vp, _i64]),
         "ggml_b200_silu_mul_f32": (C.c_int, [_vp, _vp, _vp, _i64, _vp]),
         "ggml_b200_rms_norm_mul_f32": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, C.c_float]),
+        "ggml_b200_neigh_ok": (C.c_int, [_vp]),
+        "ggml_b200_mul_mat_q4_0_add": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
+        "ggml_b200_mul_mat_q4_0_swiglu": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
         "ggml_b200_graph_begin": (C.c_int, []),
         "ggml_b200_graph_end": (C.c_int, [C.POINTER(_vp)]),
         "ggml_b200_graph_launch": (C.c_int, [_vp]),
@@ -408,6 +411,45 @@ def mul_mat_host(w: Weight, x: np.ndarray, y: np.ndarray | None = None) -> np.nd
 def mul_mat_dev(w: Weight, x_dev_ptr: int, n: int, y_dev_ptr: int, nb11: int | None = None,
                 nb1: int | None = None) -> None:
     _check(lib().ggml_b200_mul_mat_q4_0(w.h, _vp(x_dev_ptr), n, nb11 or w.K * 4, _vp(y_dev_ptr), nb1 or w.M * 4))
+
+
+def mul_mat_add(w: Weight, x: np.ndarray, r: np.ndarray):
+    """n = 1: (W x, W x + r) from ONE kernel (ggml_b200_mul_mat_q4_0_add; the residual add behind wo / w2)."""
+    xd, rd = DevBuf.from_numpy(np.ascontiguousarray(x, np.float32)), DevBuf.from_numpy(np.ascontiguousarray(r, np.float32))
+    yd, y2d = DevBuf(w.M * 4), DevBuf(w.M * 4)
+    _check(lib().ggml_b200_mul_mat_q4_0_add(w.h, xd.ptr, yd.ptr, rd.ptr, y2d.ptr))
+    synchronize()
+    return yd.to_numpy(np.float32, (w.M,)), y2d.to_numpy(np.float32, (w.M,))
+
+
+def mul_mat_swiglu(w1: Weight, w3: Weight, x: np.ndarray, want_silu: bool = True):
+    """n = 1: (W1 x, W3 x, silu(W1 x), silu(W1 x) * W3 x) from ONE kernel (ggml_b200_mul_mat_q4_0_swiglu; the FFN gate)."""
+    xd = DevBuf.from_numpy(np.ascontiguousarray(x, np.float32))
+    y1, y3, ys, y2 = (DevBuf(w1.M * 4) for _ in range(4))
+    _check(lib().ggml_b200_mul_mat_q4_0_swiglu(w1.h, w3.h, xd.ptr, y1.ptr, y3.ptr, ys.ptr if want_silu else None, y2.ptr))
+    synchronize()
+    out = (y1.to_numpy(np.float32, (w1.M,)), y3.to_numpy(np.float32, (w3.M,)), ys.to_numpy(np.float32, (w1.M,)) if want_silu else None,
+           y2.to_numpy(np.float32, (w1.M,)))
+    return out
+
+
+def eltwise(op: str, a: np.ndarray, b: np.ndarray | None = None):
+    """The stand-alone element-wise kernels (add | mul | silu | silu_mul) on host arrays: the unfused twins in the tests."""
+    a = np.ascontiguousarray(a, np.float32)
+    ad, yd = DevBuf.from_numpy(a), DevBuf(a.size * 4)
+    bd = DevBuf.from_numpy(np.ascontiguousarray(b, np.float32)) if b is not None else None
+    if op == "add":
+        _check(lib().ggml_b200_add_f32(ad.ptr, bd.ptr, yd.ptr, a.size, b.size))
+    elif op == "mul":
+        _check(lib().ggml_b200_mul_f32(ad.ptr, bd.ptr, yd.ptr, a.size, b.size))
+    elif op == "silu":
+        _check(lib().ggml_b200_silu_f32(ad.ptr, yd.ptr, a.size))
+    elif op == "silu_mul":
+        _check(lib().ggml_b200_silu_mul_f32(ad.ptr, bd.ptr, yd.ptr, a.size, None))
+    else:
+        raise ValueError(op)
+    synchronize()
+    return yd.to_numpy(np.float32, a.shape)
 
 
 def mul_mat_sharded_dev(w: Weight, x_dev_ptr: int, n: int, y_dev_ptr: int) -> None:

@@ -354,10 +354,11 @@ void ggml_cuda_mul(const struct ggml_tensor * src0, const struct ggml_tensor * s
  * eval: same scratch addresses, same compute buffer) is replayed as ONE CUDA graph launch instead, so the host pays one
  * call per segment instead of one per node and copy.  Two peephole fusions at record time: RMS_NORM followed by the MUL
  * that reads it, and SILU followed by the MUL that reads it, become one kernel each (both results are still written). */
-enum { PL_MUL_MAT, PL_RMS_NORM, PL_RMS_NORM_MUL, PL_MUL, PL_ADD, PL_SILU, PL_SILU_MUL };
+enum { PL_MUL_MAT, PL_RMS_NORM, PL_RMS_NORM_MUL, PL_MUL, PL_ADD, PL_SILU, PL_SILU_MUL, PL_MUL_MAT_ADD, PL_SWIGLU };
 struct plan {
     int kind;
-    ggml_b200_weight * w;
+    ggml_b200_weight * w, * w3;      /* w3: the second weight of PL_SWIGLU */
+    float * y3, * ys;                /* PL_SWIGLU: W3 x and silu(W1 x) */
     ggml_b200_qweight * qw;          /* a Q8_0 / Q4_1 weight instead of w */
     const float * a, * b;           /* device sources */
     float * y, * y2;                /* device results (y2: the second result of a fused pair) */
@@ -383,19 +384,40 @@ static struct ggml_tensor * g_seg_last = NULL;       /* the tensor the last plan
 static struct { struct plan * plans; int n; void * exec; int seen; } g_cache[SEG_CACHE];
 static int g_cache_n = 0, g_cache_cursor = 0;
 static int g_use_graphs = -1;
+static int g_fuse_neigh = 1;           /* GGML_B200_GLUE_FUSE=0: a matmul's ADD / SiLU*MUL neighbours stay kernels of their own */
+/* tests and benches: override the two environment switches in-process (-1 leaves a switch alone).  Takes effect at the
+ * next recorded node; cached segments of the other setting simply stop matching. */
+void ggml_b200_glue_configure(int graphs, int fuse);
+static void glue_env(void);
+void ggml_b200_glue_configure(int graphs, int fuse) {
+    glue_env();
+    if (graphs >= 0) g_use_graphs = graphs;
+    if (fuse >= 0) g_fuse_neigh = fuse;
+}
+static void glue_env(void) {
+    if (g_use_graphs >= 0) return;
+    const char * e = getenv("GGML_B200_GLUE_GRAPHS"); g_use_graphs = e ? atoi(e) : 1;
+    e = getenv("GGML_B200_GLUE_FUSE"); g_fuse_neigh = e ? atoi(e) : 1;
+}
 
 static float *g_stage_in[2] = {NULL, NULL}, *g_stage_out[4] = {NULL, NULL, NULL, NULL};
 static size_t g_stage_in_cap[2] = {0, 0}, g_stage_out_cap[4] = {0, 0, 0, 0};
 
 /* GGML_B200_GLUE_PROFILE=1: where the host's time goes (printed by ggml_b200_glue_profile_dump / at scratch free) */
 #include <time.h>
-static struct { double flush_s, wait_s; long flushes, replays, captures, direct, waits, nodes; } g_prof;
+static struct { double flush_s, wait_s; long flushes, replays, captures, direct, waits, nodes; double wait_by_n[SEG_MAX + 1]; long waits_by_n[SEG_MAX + 1]; } g_prof;
+static int g_last_flush_n = 0;         /* plans in the segment submitted last (profile: waits by segment length) */
 static int g_prof_on = -1;
 static double now_s(void) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec; }
 void ggml_b200_glue_profile_dump(void) {
     if (g_prof_on > 0 && g_prof.nodes)
         fprintf(stderr, "ggml-b200 glue: %ld device nodes, %ld segments (%ld replayed, %ld recorded, %ld direct) %.3f ms submitting, %ld waits %.3f ms\n",
                 g_prof.nodes, g_prof.flushes, g_prof.replays, g_prof.captures, g_prof.direct, g_prof.flush_s * 1e3, g_prof.waits, g_prof.wait_s * 1e3);
+    if (g_prof_on > 0 && g_prof.nodes) {
+        fprintf(stderr, "ggml-b200 glue: waits by kernels in the segment before them (kernels: count x mean us):");
+        for (int i = 0; i <= SEG_MAX; i++) if (g_prof.waits_by_n[i]) fprintf(stderr, "  %d: %ld x %.1f", i, g_prof.waits_by_n[i], g_prof.wait_by_n[i] * 1e6 / (double)g_prof.waits_by_n[i]);
+        fprintf(stderr, "\n");
+    }
     memset(&g_prof, 0, sizeof(g_prof));
 }
 static void wait_pending(void) {
@@ -403,10 +425,31 @@ static void wait_pending(void) {
         const double t0 = g_prof_on > 0 ? now_s() : 0.0;
         B200_CHECK(ggml_b200_synchronize());
         g_pending = 0;
-        if (g_prof_on > 0) { g_prof.wait_s += now_s() - t0; g_prof.waits++; }
+        if (g_prof_on > 0) { const double dt = now_s() - t0; g_prof.wait_s += dt; g_prof.waits++; g_prof.wait_by_n[g_last_flush_n] += dt; g_prof.waits_by_n[g_last_flush_n]++; }
     }
 }
 
+static void issue_d2h(const struct plan * p) {
+    if (p->d2h_bytes) B200_CHECK(ggml_b200_memcpy_d2h_async(p->d2h_dst, p->d2h_src, p->d2h_bytes));
+}
+/* The copies of host-resident results (wq / wk / wv of a layer whose attention runs on the CPU) can wait for the end of
+ * the segment -- the CPU only looks after the flush -- so that the matmuls ahead of them run back to back (and, sharing
+ * src1, side by side).  Not when a staging block would come round again first (4 in rotation), nor when a later plan of
+ * the segment uploads from a host buffer such a copy fills. */
+static int d2h_deferrable(void) {
+    int copies = 0;
+    for (int i = 0; i < g_seg_n; i++) if (g_seg[i].d2h_bytes) copies++;
+    if (copies == 0 || copies > 4) return 0;
+    for (int i = 0; i < g_seg_n; i++) {
+        if (!g_seg[i].d2h_bytes) continue;
+        const char * lo = (const char *)g_seg[i].d2h_dst, * hi = lo + g_seg[i].d2h_bytes;
+        for (int k = i + 1; k < g_seg_n; k++) for (int j = 0; j < 2; j++) {
+            const char * a = (const char *)g_seg[k].h2d_src[j];
+            if (g_seg[k].h2d_bytes[j] && a < hi && a + g_seg[k].h2d_bytes[j] > lo) return 0;
+        }
+    }
+    return 1;
+}
 static void issue(const struct plan * p) {
     for (int i = 0; i < 2; i++) if (p->h2d_bytes[i]) B200_CHECK(ggml_b200_memcpy_h2d_async(p->h2d_dst[i], p->h2d_src[i], p->h2d_bytes[i]));
     switch (p->kind) {
@@ -421,8 +464,14 @@ static void issue(const struct plan * p) {
         case PL_ADD:          B200_CHECK(ggml_b200_add_f32(p->a, p->b, p->y, p->n, p->nb)); break;
         case PL_SILU:         B200_CHECK(ggml_b200_silu_f32(p->a, p->y, p->n)); break;
         case PL_SILU_MUL:     B200_CHECK(ggml_b200_silu_mul_f32(p->a, p->b, p->y2, p->n, p->y)); break;
+        case PL_MUL_MAT_ADD:  B200_CHECK(ggml_b200_mul_mat_q4_0_add(p->w, p->a, p->y, p->b, p->y2)); break;
+        case PL_SWIGLU:       B200_CHECK(ggml_b200_mul_mat_q4_0_swiglu(p->w, p->w3, p->a, p->y, p->y3, p->ys, p->y2)); break;
     }
-    if (p->d2h_bytes) B200_CHECK(ggml_b200_memcpy_d2h_async(p->d2h_dst, p->d2h_src, p->d2h_bytes));
+}
+static void issue_segment(void) {
+    const int defer = d2h_deferrable();
+    for (int i = 0; i < g_seg_n; i++) { issue(&g_seg[i]); if (!defer) issue_d2h(&g_seg[i]); }
+    if (defer) for (int i = 0; i < g_seg_n; i++) issue_d2h(&g_seg[i]);
 }
 
 /* submit the current segment (asynchronous; copies in it make g_pending) */
@@ -431,7 +480,8 @@ static void flush_segment(void) {
     if (g_prof_on < 0) g_prof_on = getenv("GGML_B200_GLUE_PROFILE") != NULL;
     const double t0 = g_prof_on > 0 ? now_s() : 0.0;
     if (g_prof_on > 0) { g_prof.flushes++; g_prof.nodes += g_seg_n; }
-    if (g_use_graphs < 0) { const char * e = getenv("GGML_B200_GLUE_GRAPHS"); g_use_graphs = e ? atoi(e) : 1; }
+    g_last_flush_n = g_seg_n;
+    glue_env();
     int hit = -1;
     /* only decode segments are replayed: an n > 1 matmul goes through the library's activation workspace, which may
      * move when a larger batch comes by (a recorded launch would keep the old address); there the launches are not
@@ -453,14 +503,14 @@ static void flush_segment(void) {
         /* second time this very segment comes by: record it while submitting it */
         void * exec = NULL;
         B200_CHECK(ggml_b200_graph_begin());
-        for (int i = 0; i < g_seg_n; i++) issue(&g_seg[i]);
+        issue_segment();
         B200_CHECK(ggml_b200_graph_end(&exec));
         g_cache[hit].exec = exec;
         B200_CHECK(ggml_b200_graph_launch(exec));
         g_cache_cursor = (hit + 1) % g_cache_n;
     } else {
         g_prof.direct++;
-        for (int i = 0; i < g_seg_n; i++) issue(&g_seg[i]);
+        issue_segment();
         if (graphable) {
             if (g_cache_n == SEG_CACHE) {       /* the graphs changed (another model / batch size): start over */
                 for (int c = 0; c < g_cache_n; c++) { free(g_cache[c].plans); ggml_b200_graph_free(g_cache[c].exec); }
@@ -540,6 +590,7 @@ static void ensure_host(struct ggml_tensor * t) {
 }
 
 static void device_node(struct ggml_tensor * t) {
+    glue_env();
     if (g_seg_n == SEG_MAX) flush_segment();
     struct plan * p = &g_seg[g_seg_n];
     memset(p, 0, sizeof(*p));
@@ -560,7 +611,64 @@ static void device_node(struct ggml_tensor * t) {
         seg_mark_read(t->src0); seg_mark_read(t->src1);
         g_seg_out[g_seg_n - 1][1] = t; g_seg_read[g_seg_n - 1][1] = 0;
         g_seg_last = t;
+        /* ... and when a and b are the results of the two decode matmuls right before it, over the same x (the LLaMA FFN
+         * gate, llama.cpp:1479-1497): all three become ONE kernel that streams both weights */
+        if (g_fuse_neigh && g_seg_n >= 3) {
+            struct plan * m1 = &g_seg[g_seg_n - 3], * m2 = &g_seg[g_seg_n - 2];
+            const int pair = m1->kind == PL_MUL_MAT && m2->kind == PL_MUL_MAT && m1->w && m2->w && m1->n == 1 && m2->n == 1 &&
+                             !m1->sharded && !m2->sharded && m1->a == m2->a && m1->K == m2->K && m1->M == m2->M &&
+                             !m1->d2h_bytes && !m2->d2h_bytes && !m1->h2d_bytes[0] && !m2->h2d_bytes[0] && !q->h2d_bytes[0] && !q->h2d_bytes[1] && !q->d2h_bytes &&
+                             ggml_b200_neigh_ok(m1->w) && ggml_b200_neigh_ok(m2->w);
+            struct plan * gate = NULL, * up = NULL;
+            if (pair && m1->y == q->a && m2->y == q->b) { gate = m1; up = m2; }
+            if (pair && m2->y == q->a && m1->y == q->b) { gate = m2; up = m1; }
+            if (gate != NULL) {
+                struct plan f;
+                memset(&f, 0, sizeof(f));
+                f.kind = PL_SWIGLU; f.w = gate->w; f.w3 = up->w; f.a = gate->a; f.y = gate->y; f.y3 = up->y; f.ys = q->y; f.y2 = q->y2;
+                f.n = 1; f.K = gate->K; f.M = gate->M;
+                *m1 = f;
+                g_seg_out[g_seg_n - 3][0] = t; g_seg_out[g_seg_n - 3][1] = NULL; g_seg_read[g_seg_n - 3][0] = 0; g_seg_read[g_seg_n - 3][1] = 0;
+                g_seg_n -= 2;
+            }
+        }
         return;
+    }
+    /* the same gate in the order ggml_build_forward_expand gives llama.cpp's graph (src0 first): w1, silu, w3, mul */
+    if (g_fuse_neigh && g_use_graphs != 0 && t->op == GGML_OP_MUL && is_act(t) && g_seg_n >= 3 && is_act(t->src0) && is_act(t->src1) &&
+        ggml_nelements(t->src0) == p->n && ggml_nelements(t->src1) == p->n) {
+        struct plan * gate = &g_seg[g_seg_n - 3], * sl = &g_seg[g_seg_n - 2], * up = &g_seg[g_seg_n - 1];
+        const float * s0 = dev_ptr(t->src0), * s1 = dev_ptr(t->src1);
+        if (gate->kind == PL_MUL_MAT && sl->kind == PL_SILU && up->kind == PL_MUL_MAT && gate->w && up->w && gate->n == 1 && up->n == 1 &&
+            !gate->sharded && !up->sharded && sl->a == gate->y && gate->a == up->a && gate->K == up->K && gate->M == up->M && gate->M == p->n &&
+            ((s0 == sl->y && s1 == up->y) || (s1 == sl->y && s0 == up->y)) &&
+            !gate->d2h_bytes && !up->d2h_bytes && !sl->d2h_bytes && !gate->h2d_bytes[0] && !up->h2d_bytes[0] && !sl->h2d_bytes[0] &&
+            ggml_b200_neigh_ok(gate->w) && ggml_b200_neigh_ok(up->w)) {
+            struct plan f;
+            memset(&f, 0, sizeof(f));
+            f.kind = PL_SWIGLU; f.w = gate->w; f.w3 = up->w; f.a = gate->a; f.y = gate->y; f.y3 = up->y; f.ys = sl->y; f.y2 = plan_dst(&f, t);
+            f.n = 1; f.K = gate->K; f.M = gate->M;
+            *gate = f;
+            seg_mark_read(t->src0); seg_mark_read(t->src1);
+            g_seg_out[g_seg_n - 3][0] = t; g_seg_out[g_seg_n - 3][1] = NULL; g_seg_read[g_seg_n - 3][0] = 0; g_seg_read[g_seg_n - 3][1] = 0;
+            g_seg_n -= 2;
+            g_seg_last = t;
+            return;
+        }
+    }
+    /* a decode matmul and the ADD that reads its result (residual behind wo / w2, llama.cpp:1462, :1504): one kernel */
+    if (g_fuse_neigh && g_use_graphs != 0 && g_seg_n > 0 && g_seg_last != NULL && t->op == GGML_OP_ADD && is_act(t) &&
+        (t->src0 == g_seg_last || t->src1 == g_seg_last) && t->src0 != t->src1) {
+        struct plan * q = &g_seg[g_seg_n - 1];
+        const struct ggml_tensor * other = t->src0 == g_seg_last ? t->src1 : t->src0;
+        if (q->kind == PL_MUL_MAT && q->w != NULL && q->n == 1 && !q->sharded && !q->d2h_bytes && (is_act(other) || is_devf32(other)) &&
+            ggml_nelements(other) == q->M && ggml_nelements(t) == q->M && ggml_b200_neigh_ok(q->w)) {
+            q->kind = PL_MUL_MAT_ADD; q->b = dev_ptr(other); q->y2 = plan_dst(q, t);
+            seg_mark_read(t->src0); seg_mark_read(t->src1);
+            g_seg_out[g_seg_n - 1][1] = t; g_seg_read[g_seg_n - 1][1] = 0;
+            g_seg_last = t;
+            return;
+        }
     }
     switch (t->op) {
         case GGML_OP_MUL_MAT: {

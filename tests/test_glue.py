@@ -429,12 +429,23 @@ def test_device_resident_activations_through_the_seam(b200, dims):
     c0 = b200.launch_count()
     host_acts = _layer_logits(G, dims, 1, 0, x)
     c1 = b200.launch_count()
-    dev_acts = _layer_logits(G, dims, 1, 1, x)
+    G.ggml_b200_glue_configure.argtypes = [C.c_int, C.c_int]
+    G.ggml_b200_glue_configure.restype = None
+    G.ggml_b200_glue_configure(-1, 0)                       # every node a kernel of its own (but rms_norm+mul, silu+mul)
+    try:
+        dev_acts = _layer_logits(G, dims, 1, 1, x)
+    finally:
+        G.ggml_b200_glue_configure(-1, 1)
     c2 = b200.launch_count()
+    # the matmul's neighbours folded into its store (8f-2): wo + residual, w1/w3 + silu*mul, w2 + residual
+    fused_acts = _layer_logits(G, dims, 1, 1, x)
+    c3 = b200.launch_count()
     n_layer = dims[0]
     assert c2 - c1 >= (c1 - c0) + 2 * 5 * n_layer          # two evals x >= 5 element-wise kernels per layer (rms_norm+mul and silu+mul fused) on top of the matmuls
+    assert c3 - c2 <= (c2 - c1) - 2 * 4 * n_layer          # two evals x 4 launches fewer per layer: 2 adds, silu*mul, one of w1/w3
+    assert np.array_equal(fused_acts, dev_acts)             # the folded neighbours apply the same fp32 operations: same bits
     scale = float(np.abs(cpu).max())
-    for got in (host_acts, dev_acts):
+    for got in (host_acts, dev_acts, fused_acts):
         err = float(np.abs(got - cpu).max()) / scale
         assert err <= 2e-3, f"max|dlogit|/max|logit| = {err:.3e}"
         assert int(got.argmax()) == int(cpu.argmax())

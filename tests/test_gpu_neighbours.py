@@ -1,0 +1,71 @@
+"""The decode op with its neighbour folded into the store (gemv_q4_0_neigh.cuh) through the C ABI:
+the matmul results bit-identical to ggml_b200_mul_mat_q4_0, the fused result bit-identical to the stand-alone element-wise
+kernel applied to it, and both within the bars against the oracle."""
+import numpy as np
+import pytest
+
+from oracle import neighbours as nb
+from test_gpu_parity import make_weights, make_x, oracle_Y, assert_close
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(256, 64), (4096, 4096), (1000, 4544), (11008, 4096), (4096, 11008)]
+
+
+@pytest.mark.parametrize("M,K", SHAPES)
+def test_mul_mat_add(b200, port, ref, M, K):
+    W = make_weights(port, ref, M, K)
+    x = make_x(port, 1, K)
+    r = port.synthetic(M, 0xADD + M, 1.0).astype(np.float32)
+    w = b200.Weight(W)
+    y_plain = b200.mul_mat_host(w, x)[0]
+    y, y2 = b200.mul_mat_add(w, x[0], r)
+    assert np.array_equal(y.view(np.uint32), y_plain.view(np.uint32))
+    assert np.array_equal(y2.view(np.uint32), b200.eltwise("add", y_plain, r).view(np.uint32))
+    assert np.array_equal(y2.view(np.uint32), nb.add(y_plain, r).view(np.uint32))
+    assert_close(y[None], oracle_Y(port, ref, W, x))
+    # in place over the residual row, as ggml_add_inplace would ask for
+    rd = b200.DevBuf.from_numpy(r)
+    xd = b200.DevBuf.from_numpy(x[0])
+    yd = b200.DevBuf(M * 4)
+    b200._check(b200.lib().ggml_b200_mul_mat_q4_0_add(w.h, xd.ptr, yd.ptr, rd.ptr, rd.ptr))
+    b200.synchronize()
+    assert np.array_equal(rd.to_numpy(np.float32, (M,)).view(np.uint32), y2.view(np.uint32))
+    w.free()
+
+
+@pytest.mark.parametrize("M,K", SHAPES)
+def test_mul_mat_swiglu(b200, port, ref, M, K):
+    W1 = make_weights(port, ref, M, K, seed=0x5EED0011)
+    W3 = make_weights(port, ref, M, K, seed=0x5EED0033)
+    x = make_x(port, 1, K)
+    w1, w3 = b200.Weight(W1), b200.Weight(W3)
+    g_plain, u_plain = b200.mul_mat_host(w1, x)[0], b200.mul_mat_host(w3, x)[0]
+    g, u, s, y2 = b200.mul_mat_swiglu(w1, w3, x[0])
+    assert np.array_equal(g.view(np.uint32), g_plain.view(np.uint32))
+    assert np.array_equal(u.view(np.uint32), u_plain.view(np.uint32))
+    assert np.array_equal(s.view(np.uint32), b200.eltwise("silu", g_plain).view(np.uint32))
+    assert np.array_equal(y2.view(np.uint32), b200.eltwise("silu_mul", g_plain, u_plain).view(np.uint32))
+    # the oracle's restatement of the table look-up: at most one fp16 ulp apart (expf), mostly equal
+    s_ref = nb.silu(g_plain)
+    ulp = np.maximum(np.abs(s_ref), 2.0 ** -14) * 2.0 ** -10
+    assert np.all(np.abs(s - s_ref) <= ulp)
+    assert np.mean(s == s_ref) > 0.99
+    assert_close(g[None], oracle_Y(port, ref, W1, x))
+    assert_close(u[None], oracle_Y(port, ref, W3, x))
+    _, _, s_none, y2b = b200.mul_mat_swiglu(w1, w3, x[0], want_silu=False)
+    assert s_none is None and np.array_equal(y2b.view(np.uint32), y2.view(np.uint32))
+    w1.free(); w3.free()
+
+
+def test_contract(b200, port, ref):
+    W = make_weights(port, ref, 128, 64)
+    W2 = make_weights(port, ref, 256, 64)
+    w, w2 = b200.Weight(W), b200.Weight(W2)
+    assert b200.lib().ggml_b200_neigh_ok(w.h) == 1
+    d = b200.DevBuf(4096)
+    with pytest.raises(b200.B200Error):
+        b200._check(b200.lib().ggml_b200_mul_mat_q4_0_add(w.h, d.ptr, d.ptr, None, d.ptr))
+    with pytest.raises(b200.B200Error):
+        b200._check(b200.lib().ggml_b200_mul_mat_q4_0_swiglu(w.h, w2.h, d.ptr, d.ptr, d.ptr, None, d.ptr))
+    w.free(); w2.free()

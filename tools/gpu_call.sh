@@ -1,4 +1,7 @@
-test llama.cpp-q_4_0_b200/lib/libggml_b200.so -nt llama.cpp-q_4_0_b200/csrc/gemm_q4_0_tc3.cuh || { echo STALE LIB; exit 9; }
+#!/bin/bash
+# scratch: one GPU call
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_parity.py tests/test_gpu_fullsize.py -x -q -m gpu -k "gemm or prefill or auto_dispatch" > gpurun_out/t.log 2>&1; tail -2 gpurun_out/t.log
-timeout 600 python tools/bench_gemm.py > gpurun_out/r02_bench_gemm_v3_16w_c.log 2>&1; cat gpurun_out/r02_bench_gemm_v3_16w_c.log
+timeout 600 python -m pytest tests/test_gpu_neighbours.py tests/test_glue.py -m gpu -x -q > gpurun_out/r02_pytest_neigh.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r02_pytest_neigh.log
+timeout 300 python tools/trace_seam.py > gpurun_out/r02_trace_seam.log 2>&1; echo "trace rc=$?" >> gpurun_out/r02_trace_seam.log
+GGML_B200_GLUE_PROFILE=1 timeout 300 python tools/probe_glue_e2e.py > gpurun_out/r02_probe_glue_e2e_b.log 2>&1; echo "probe rc=$?" >> gpurun_out/r02_probe_glue_e2e_b.log
+tail -5 gpurun_out/r02_pytest_neigh.log; grep "device_acts" gpurun_out/r02_probe_glue_e2e_b.log
