@@ -176,6 +176,12 @@ int          ggml_b200_mul_mat_q4_0_add(const ggml_b200_weight * w, const float 
 int          ggml_b200_mul_mat_q4_0_swiglu(const ggml_b200_weight * w1, const ggml_b200_weight * w3, const float * x_dev,
                                            float * y1_dev, float * y3_dev, float * silu_dev /* may be NULL */,
                                            float * y2_dev);
+/* Marks on the current stream: ggml_b200_wait_mark(slot) returns when everything queued before ggml_b200_mark(slot) has
+ * finished, whatever was queued behind it (the glue submits the next segment of a decode graph ahead of the CPU node in
+ * front of it and waits for the one before; the reference waits for whole streams, ggml-cuda.cu:2514-2552). */
+#define GGML_B200_MARKS 8
+int          ggml_b200_mark(int slot);
+int          ggml_b200_wait_mark(int slot);
 /* A sequence of this library's asynchronous calls (ops, element-wise kernels, async copies) recorded once and submitted
  * as one CUDA graph launch afterwards: begin ... calls ... end -> handle; launch runs it on the current stream.  The
  * glue uses it for the device nodes between two CPU nodes of a ggml graph (same pointers every eval).  No allocation

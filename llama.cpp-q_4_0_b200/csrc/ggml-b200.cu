@@ -498,6 +498,21 @@ void ggml_b200_dev_free(void * p) { if (p) cudaFree(p); }
 int ggml_b200_memcpy_h2d(void * d, const void * s, size_t n) { CK(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, g.stream)); CK(cudaStreamSynchronize(g.stream)); return GGML_B200_OK; }
 int ggml_b200_memcpy_d2h(void * d, const void * s, size_t n) { CK(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, g.stream)); CK(cudaStreamSynchronize(g.stream)); return GGML_B200_OK; }
 int ggml_b200_synchronize(void) { CK(cudaStreamSynchronize(g.stream)); return GGML_B200_OK; }
+// a few marks on the stream: wait for what was queued up to a mark although more has been queued behind it
+static cudaEvent_t g_marks[GGML_B200_MARKS] = {};
+int ggml_b200_mark(int slot) {
+    B200_API_LOCK;
+    if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
+    if (slot < 0 || slot >= GGML_B200_MARKS) { set_error("mark: bad slot"); return GGML_B200_ERR_ARG; }
+    if (!g_marks[slot]) CK(cudaEventCreateWithFlags(&g_marks[slot], cudaEventDisableTiming));
+    CK(cudaEventRecord(g_marks[slot], g.stream));
+    return GGML_B200_OK;
+}
+int ggml_b200_wait_mark(int slot) {
+    if (slot < 0 || slot >= GGML_B200_MARKS || !g_marks[slot]) { set_error("wait_mark: no such mark"); return GGML_B200_ERR_ARG; }
+    CK(cudaEventSynchronize(g_marks[slot]));
+    return GGML_B200_OK;
+}
 
 // ---- upload -----------------------------------------------------------------------------------
 ggml_b200_weight * ggml_b200_upload_q4_0(const void * blocks, int64_t M, int64_t K, size_t nb1, int64_t row_lo, int64_t row_hi) {

@@ -135,6 +135,20 @@ def _tiny_llama_logits(tmp_path, lib, ngl, n_prompt, model):
     return np.load(out), r.stderr
 
 
+def _tiny_llama_decode(tmp_path, lib, ngl, n_prompt, n_decode, model, env=None, tag=""):
+    import subprocess
+    import sys
+    out = str(tmp_path / (os.path.basename(lib) + ".dec%s.%d.%d.npy" % (tag, ngl, n_decode)))
+    e = dict(os.environ)
+    e.update(env or {})
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "glue", "run_tiny_llama.py"), lib, model, str(ngl), str(n_prompt), out, str(n_decode)],
+                       capture_output=True, text=True, timeout=900, env=e)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    line = [ln for ln in r.stdout.splitlines() if ln.startswith("decode_ms_per_step=")][-1]
+    stats = {kv.split("=")[0]: float(kv.split("=")[1]) for kv in line.split()}
+    return np.load(out), stats
+
+
 def _tiny_model(tmp_path, n_layer=26):
     import sys
     sys.path.insert(0, os.path.join(ROOT, "tests", "glue"))
@@ -185,6 +199,38 @@ def test_tiny_llama_offloaded_to_b200_matches_cpu_reference(tmp_path, n_prompt):
 
 
 @pytest.mark.gpu
+def test_tiny_llama_decode_loop_replays_and_runs_ahead(tmp_path):
+    """The decode loop of the reference's own llama_eval (n_past grows, so the graph's host buffers move from token to
+    token): the glue keeps replaying its recorded segments (rows cross PCIe through its own pinned arenas) and submits
+    wq / wv ahead of the CPU nodes in front of them.  Every step's logits against the CPU build, and bit-identical
+    with segment replay, speculation and neighbour fusion switched off one by one."""
+    model = _tiny_model(tmp_path)
+    n_prompt, n_decode = 5, 24
+    cpu, _ = _tiny_llama_decode(tmp_path, LLAMA_CPU_SO, 0, n_prompt, n_decode, model)
+    gpu, st = _tiny_llama_decode(tmp_path, LLAMA_B200_SO, 99, n_prompt, n_decode, model)
+    assert st["replays"] >= 10 * 26, st                      # most segments of most steps came from a recorded graph
+    assert st["ahead"] >= 10 * 26, st
+    # (bar: the single-eval test above; over a decode loop the f16 KV cache carries every step's last-bit differences
+    # into the next ones, so the worst of 24 steps gets twice the room and the median has to meet the single-eval bar)
+    same, errs = 0, []
+    for i in range(n_decode):
+        scale = float(np.abs(cpu[i]).max())
+        err = float(np.abs(cpu[i] - gpu[i]).max()) / scale
+        cos = float(np.dot(cpu[i], gpu[i]) / (np.linalg.norm(cpu[i]) * np.linalg.norm(gpu[i])))
+        assert err <= 6e-2 and cos >= 0.999, f"step {i}: max|dlogit|/max|logit| = {err:.3e}, cosine = {cos:.6f}"
+        errs.append(err)
+        same += int(cpu[i].argmax()) == int(gpu[i].argmax())
+    assert float(np.median(errs)) <= 3e-2 and same >= n_decode - 2
+    for tag, env in (("nospec", {"GGML_B200_GLUE_SPECULATE": "0"}), ("nograph", {"GGML_B200_GLUE_GRAPHS": "0"}), ("nofuse", {"GGML_B200_GLUE_FUSE": "0"})):
+        other, st2 = _tiny_llama_decode(tmp_path, LLAMA_B200_SO, 99, n_prompt, n_decode, model, env=env, tag=tag)
+        assert np.array_equal(other, gpu), tag
+        if tag == "nospec":
+            assert st2["ahead"] == 0 and st2["replays"] >= 10 * 26
+        if tag == "nograph":
+            assert st2["replays"] == 0
+
+
+@pytest.mark.gpu
 def test_shallow_llama_offloaded_to_b200_is_tight(tmp_path):
     """The same through a 1-layer model, where no error has room to be re-quantized and amplified: 8 offloaded
     matmuls per eval; logits within 1e-3 of the largest logit of the CPU reference."""
@@ -209,13 +255,13 @@ def _layer_lib():
     return G
 
 
-def _layer_logits(G, dims, offload, device_acts, x, threads=4):
+def _layer_logits(G, dims, offload, device_acts, x, threads=4, steps=2):
     n_layer, n_embd, n_ff, n_vocab = dims
     m = G.glue_model_create(n_layer, n_embd, n_ff, n_vocab, offload, 7)
     assert m
     logits = np.zeros(n_vocab, np.float32)
     xs = np.ascontiguousarray(x, dtype=np.float32)
-    t = G.glue_model_eval(m, xs.ctypes.data_as(C.c_void_p), logits.ctypes.data_as(C.c_void_p), threads, 2, device_acts)
+    t = G.glue_model_eval(m, xs.ctypes.data_as(C.c_void_p), logits.ctypes.data_as(C.c_void_p), threads, steps, device_acts)
     assert t > 0
     G.glue_model_free(m)
     return logits
@@ -440,6 +486,21 @@ def test_device_resident_activations_through_the_seam(b200, dims):
     # the matmul's neighbours folded into its store (8f-2): wo + residual, w1/w3 + silu*mul, w2 + residual
     fused_acts = _layer_logits(G, dims, 1, 1, x)
     c3 = b200.launch_count()
+    # ... and the same again without submitting segments ahead of the CPU node in front of them
+    G.ggml_b200_glue_set_speculate.argtypes = [C.c_int]
+    G.ggml_b200_glue_set_speculate.restype = None
+    G.ggml_b200_glue_speculation_hits.restype = C.c_long
+    h0 = G.ggml_b200_glue_speculation_hits()
+    many = _layer_logits(G, dims, 1, 1, x, steps=6)
+    h1 = G.ggml_b200_glue_speculation_hits()
+    G.ggml_b200_glue_set_speculate(0)
+    try:
+        plain = _layer_logits(G, dims, 1, 1, x, steps=6)
+    finally:
+        G.ggml_b200_glue_set_speculate(1)
+    assert h1 - h0 >= 2 * dims[0]                           # wv of every layer went ahead in the later evals
+    assert G.ggml_b200_glue_speculation_hits() == h1
+    assert np.array_equal(many, plain) and np.array_equal(many, fused_acts)
     n_layer = dims[0]
     assert c2 - c1 >= (c1 - c0) + 2 * 5 * n_layer          # two evals x >= 5 element-wise kernels per layer (rms_norm+mul and silu+mul fused) on top of the matmuls
     assert c3 - c2 <= (c2 - c1) - 2 * 4 * n_layer          # two evals x 4 launches fewer per layer: 2 adds, silu*mul, one of w1/w3

@@ -20,11 +20,14 @@ x = np.random.default_rng(9).standard_normal(4096).astype(np.float32)
 lg = np.zeros(32000, np.float32)
 G.ggml_b200_glue_configure.argtypes = [C.c_int, C.c_int]
 G.ggml_b200_glue_configure.restype = None
-for acts, fuse in ((1, 0), (0, 1), (1, 1), (1, 0), (1, 1)):
+G.ggml_b200_glue_set_speculate.argtypes = [C.c_int]
+G.ggml_b200_glue_speculation_hits.restype = C.c_long
+for acts, fuse, spec in ((1, 0, 0), (0, 1, 0), (1, 1, 0), (1, 1, 1), (1, 0, 0), (1, 1, 0), (1, 1, 1)):
     G.ggml_b200_glue_configure(-1, fuse)
+    G.ggml_b200_glue_set_speculate(spec)
     G.glue_model_eval(m, x.ctypes.data_as(C.c_void_p), lg.ctypes.data_as(C.c_void_p), 1, 3, acts)
     G.ggml_b200_glue_profile_dump()
     t = G.glue_model_eval(m, x.ctypes.data_as(C.c_void_p), lg.ctypes.data_as(C.c_void_p), 1, 20, acts)
-    print(f"device_acts={acts} fuse_neighbours={fuse}: {t * 1e3:.3f} ms per eval, launches so far {mod.launch_count()}", flush=True)
+    print(f"device_acts={acts} fuse_neighbours={fuse} ahead={spec}: {t * 1e3:.3f} ms per eval, launches so far {mod.launch_count()}, segments run ahead so far {G.ggml_b200_glue_speculation_hits()}", flush=True)
     G.ggml_b200_glue_profile_dump()
 G.glue_model_free(m)
