@@ -579,7 +579,69 @@ def siblings_leg(mod, stream, rng, steps, warmup):
                                            "matmuls_per_step": n7, "algorithmic_bytes_per_step": b7, "oracle_max_rel_err": e7_,
                                            "note": "the 32 layers' 7 matmuls (the 32000x4096 output op is left out)"},
                      "bytes_per_block": bs}
+        if qtype == sib.TYPE_Q8_0:
+            out[name]["prefill_n512"] = siblings_q8_prefill(mod, stream, L_, host_blocks, steps, warmup)
     return out
+
+
+def siblings_q8_prefill(mod, stream, L_, host_blocks, steps, warmup, n=512):
+    """Q8_0 weights, n = 512: kernel 1 + kernel 3 with the weight's int8 plane as the A operand (gemm_q4_0_tc3.cuh, WFMT = 8).
+    One pass = the LLaMA-7B layer shapes once each; int8 TOPS = 2 M K n / time; one column checked against the oracle."""
+    import torch
+    from oracle import siblings as sib
+    shapes = [(4096, 4096), (11008, 4096), (4096, 11008)]
+    hs, ops = [], 0.0
+    xs = {K: torch.randn(n, K, device="cuda", dtype=torch.float32) for K in {K for (_, K) in shapes}}
+    ys = {M: torch.empty(n, M, device="cuda", dtype=torch.float32) for M in {M for (M, _) in shapes}}
+    errs = {}
+    for (M, K) in shapes:
+        W = host_blocks(M, K)
+        h = L_.ggml_b200_upload_quant(sib.TYPE_Q8_0, W.ctypes.data_as(C.c_void_p), M, K, 0)
+        if not h:
+            raise RuntimeError(L_.ggml_b200_last_error().decode())
+        hs.append((h, M, K))
+        ops += 2.0 * M * K * n
+        rc = L_.ggml_b200_mul_mat_quant(h, C.c_void_p(xs[K].data_ptr()), n, K * 4, C.c_void_p(ys[M].data_ptr()), M * 4)
+        assert rc == 0, L_.ggml_b200_last_error()
+        stream.synchronize()
+        rows, col = min(M, 128), n - 1
+        want = sib.mul_mat(sib.TYPE_Q8_0, W[:rows], xs[K][col:col + 1].cpu().numpy())[0]
+        got = ys[M][col, :rows].cpu().numpy()
+        e = float(np.max(np.abs(got - want)) / max(float(np.max(np.abs(want))), 1e-30))
+        errs[f"{M}x{K}"] = e
+        if not e <= 1e-4:
+            raise RuntimeError(f"siblings q8_0 prefill: {M}x{K} differs from the oracle: {e:.3e}")
+
+    def one_pass():
+        for (h, M, K) in hs:
+            L_.ggml_b200_mul_mat_quant(h, C.c_void_p(xs[K].data_ptr()), n, K * 4, C.c_void_p(ys[M].data_ptr()), M * 4)
+    c0 = mod.launch_count()
+    with torch.cuda.stream(stream):
+        for _ in range(max(3, warmup)):
+            one_pass()
+    stream.synchronize()
+    launches = (mod.launch_count() - c0) / max(3, warmup)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+        for _ in range(steps):
+            one_pass()
+        e1.record(stream)
+    stream.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    for (h, _, _) in hs:
+        L_.ggml_b200_free_quant(h)
+    torch.cuda.empty_cache()
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            bf16 = float(json.load(f)["bf16_tflops"])
+    except Exception:
+        bf16 = 1590.0
+    tops = ops / (ms * 1e-3) / 1e12
+    return {"int8_TOPS": tops, "frac_of_2x_bf16_peak": tops / (2 * bf16), "ms_per_pass": ms, "n": n, "shapes": [list(sh) for sh in shapes],
+            "gpu_launches_per_pass": int(launches), "oracle_max_rel_err": errs,
+            "kernel": "kernel 1 + gemm_q4_0_tc3_kernel<WFMT = 8> (the int8 plane is the MMA's A operand, no unpack)",
+            "l2": "weights 9-45 MB per op, activations 8-23 MB: the pass (277 MB) is larger than L2"}
 
 
 def prefill_leg(mod, stream, rng, steps, warmup, n=512, shapes=None, groups=None, name="llama7b_prefill_n512", host_leg=True):

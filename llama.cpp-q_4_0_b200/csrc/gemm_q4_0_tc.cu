@@ -51,6 +51,8 @@ int gemm_init() {
     CK(cudaFuncSetAttribute(g3::gemm_q4_0_tc3_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, g3::SMEM_BYTES));
     CK(cudaFuncSetAttribute(g3::gemm_q4_0_tc3_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, g3::SMEM_BYTES));
     CK(cudaFuncSetAttribute(g3::gemm_q4_0_tc3_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, g3::SMEM_BYTES));
+    CK(cudaFuncSetAttribute(g3::gemm_q4_0_tc3_kernel<false, false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, g3::SMEM_BYTES));
+    CK(cudaFuncSetAttribute(g3::gemm_q4_0_tc3_kernel<true, false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, g3::SMEM_BYTES));
     g_gemm_ready = true;
     return GGML_B200_OK;
 }
@@ -89,11 +91,31 @@ void gemm_release_weight(ggml_b200_weight * w) {
     if (w->gemm) { delete (GemmWeight *)w->gemm; w->gemm = nullptr; }
 }
 
+// Q8_0 weights (siblings.cu): the int8 plane [M][K] is the A operand as it lies -- box = 128 K-bytes x 128 rows, SW128
+void * gemm_prepare_q8(const void * wq, int64_t M, int64_t K) {
+    if (!g_gemm_ready || M <= 0) return nullptr;
+    GemmWeight * gw = new GemmWeight();
+    if (encode_2d(&gw->tm_nib, CU_TENSOR_MAP_DATA_TYPE_UINT8, const_cast<void *>(wq), (uint64_t)K, (uint64_t)M, (uint64_t)K, g3::KB * 32, g3::BM,
+                  CU_TENSOR_MAP_SWIZZLE_128B)) { delete gw; return nullptr; }
+    return gw;
+}
+void gemm_release_q8(void * h) { delete (GemmWeight *)h; }
+
+static int launch_gemm_any(const CUtensorMap & tm_w, const __half * wd, int64_t M, int64_t Kw, int wfmt, float * y, long long ldy, int n, int * S, int independent);
+
+int launch_gemm_q8(const void * h, const void * wd, int64_t M, int64_t K, float * y, long long ldy, int n, int * S) {
+    if (!g_gemm_ready || !h) { set_error("tensor-core GEMM path not available for this weight"); return GGML_B200_ERR_STATE; }
+    return launch_gemm_any(((const GemmWeight *)h)->tm_nib, (const __half *)wd, M, K, 8, y, ldy, n, S, 0);
+}
+
 int launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int * S, int independent) {
     if (!gemm_available(w)) { set_error("tensor-core GEMM path not available for this weight"); return GGML_B200_ERR_STATE; }
+    return launch_gemm_any(((const GemmWeight *)w->gemm)->tm_nib, w->wd, w->rows(), w->K, 4, y, ldy, n, S, independent);
+}
+
+static int launch_gemm_any(const CUtensorMap & tm_w, const __half * wd, int64_t M, int64_t Kw, int wfmt, float * y, long long ldy, int n, int * S, int independent) {
     if (!g.xdT || g.xdT_n_pad < n) { set_error("activation scales were not laid out for the GEMM path"); return GGML_B200_ERR_STATE; }
-    const GemmWeight * gw = (const GemmWeight *)w->gemm;
-    const uint64_t K = (uint64_t)w->K, nbk = K / QK;
+    const uint64_t K = (uint64_t)Kw, nbk = K / QK;
     CUtensorMap tm_xq, tm_xd;
     // activations int8 [n][K], box = 128 K-bytes x 128 columns, 128-byte swizzle (UMMA K-major SW128)
     int rc = encode_2d(&tm_xq, CU_TENSOR_MAP_DATA_TYPE_UINT8, g.xq, K, (uint64_t)n, K, g3::KB * 32, g3::BN, CU_TENSOR_MAP_SWIZZLE_128B);
@@ -103,18 +125,21 @@ int launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int
                    g3::BN, g3::KB, CU_TENSOR_MAP_SWIZZLE_NONE);
     if (rc) return rc;
 
-    const dim3 grid((unsigned)((w->rows() + g3::BM - 1) / g3::BM), (unsigned)((n + g3::BN - 1) / g3::BN));
+    const dim3 grid((unsigned)((M + g3::BM - 1) / g3::BM), (unsigned)((n + g3::BN - 1) / g3::BN));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = dim3(g3::THREADS); cfg.dynamicSmemBytes = g3::SMEM_BYTES; cfg.stream = g.stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = g.tune.pdl ? 1 : 0;
-    const __half * wd = w->wd;
-    const int rows = (int)w->rows(), nbk_i = (int)nbk;
-    if (g_gemm_trace && !S) CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, true>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
-    else if (S)             CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<true, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
-    else                    CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, false>, gw->tm_nib, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
+    const int rows = (int)M, nbk_i = (int)nbk;
+    if (wfmt == 8) {
+        if (S) CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<true, false, 8>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
+        else   CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, false, 8>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
+    }
+    else if (g_gemm_trace && !S) CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, true>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
+    else if (S)             CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<true, false>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
+    else                    CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, false>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
     g.launches++;
     return GGML_B200_OK;
 }

@@ -122,7 +122,7 @@ struct Dump {
 
 // One half block: H = 0 -> the thread's rows r0, r0 + 8 (TMEM lanes 0..15 of the quadrant), H = 1 -> rows r0 + 16, r0 + 24;
 // 8 column pairs each.  acc[k * 4 + j] = (column pair k, row j).
-template <int H, bool DUMP>
+template <int H, bool DUMP, int WFMT>
 __device__ __forceinline__ void epi_half(uint32_t (&r)[4 * NKG], uint64_t (&acc)[4 * NKG], const uint64_t (&dx2)[NKG],
                                          const float (&dw)[4], const float (&nc)[4], const Dump & dp, int blk, int lane) {
     // The products rn(S_b * dw) are formed IN PLACE in the fragment's own register pairs, all of them before the first
@@ -139,8 +139,8 @@ __device__ __forceinline__ void epi_half(uint32_t (&r)[4 * NKG], uint64_t (&acc)
                 const int mm = dp.m + 8 * j;
                 if (mm < dp.rows) {
                     int * dst = dp.S + ((size_t)c * dp.rows + mm) * dp.nbk + blk;
-                    if (c < dp.n)     dst[0] = ((int)f0 - S_BIAS) >> S_SHIFT;
-                    if (c + 1 < dp.n) dst[(size_t)dp.rows * dp.nbk] = ((int)f1 - S_BIAS) >> S_SHIFT;
+                    if (c < dp.n)     dst[0] = ((int)f0 - S_BIAS) >> (WFMT == 8 ? 0 : S_SHIFT);
+                    if (c + 1 < dp.n) dst[(size_t)dp.rows * dp.nbk] = ((int)f1 - S_BIAS) >> (WFMT == 8 ? 0 : S_SHIFT);
                 }
             }
             fma_inplace_pair_f32x2(r[4 * k + 2 * jj], r[4 * k + 2 * jj + 1], pack_f32x2(dw[j], dw[j]), pack_f32x2(nc[j], nc[j]));   // == rn(S_b * dw) * 2^-49
@@ -156,7 +156,7 @@ __device__ __forceinline__ void epi_half(uint32_t (&r)[4 * NKG], uint64_t (&acc)
 __device__ __forceinline__ float4 lds_f4(uint32_t addr) { return lds_f32x4(addr); }
 
 // The epilogue of one warp over the whole K loop.
-template <bool DUMP, bool TRACE>
+template <bool DUMP, bool TRACE, int WFMT>
 __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int ew, int lane, int m0, int c0, int rows, int n, int nbk,
                                          float * __restrict__ y, long long ldy, int * S_out, long long * trc) {
 #define G3_TR(idx) do { if (TRACE && trc != nullptr && ew == 0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0) trc[2 * 2048 + (idx)] = clock64(); } while (0)
@@ -228,7 +228,7 @@ __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int
                     tmem_ld_wait();                                       // ra = rows r0, r0 + 8
                     G3_TR(8 * blk + 1);
                     tmem_ld_frag(t_lane + jj * BN + (16u << 16), rb);
-                    epi_half<0, DUMP>(ra, acc, dx2, dw, nc, dump, blk, lane);
+                    epi_half<0, DUMP, WFMT>(ra, acc, dx2, dw, nc, dump, blk, lane);
                     G3_TR(8 * blk + 2);
                     tmem_ld_wait();                                       // rb = rows r0 + 16, r0 + 24
                     G3_TR(8 * blk + 3);
@@ -243,7 +243,7 @@ __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int
                         tmem_ld_frag(t_lane + j1 * BN, ra);
                     }
                     G3_TR(8 * blk + 4);
-                    epi_half<1, DUMP>(rb, acc, dx2, dw, nc, dump, blk, lane);
+                    epi_half<1, DUMP, WFMT>(rb, acc, dx2, dw, nc, dump, blk, lane);
                     G3_TR(8 * blk + 5);
                 }
             }
@@ -290,9 +290,13 @@ __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int
 }
 
 // TRACE: CTA (0,0) stamps clock64 at its pipeline hand-offs into trc (tools/trace_gemm.py); compiled out otherwise
-template <bool DUMP, bool TRACE>
+// WFMT = 4: Q4_0 weights (nibble plane, unpacked by warps 18-19).  WFMT = 8: Q8_0 weights (a sibling format
+// through the same kernel): the int8 plane [rows][K] IS the A operand, so the TMA warp drops the 128 x 128 B tile straight
+// into the operand ring (SWIZZLE_128B, like the activations), the MMA forms S_b itself (no factor 16: the staged weight scale
+// carries 2^4 instead) and warps 18-19 only stage the weight scales.  |S_b| <= 32 * 128 * 127 < 2^19 as before.
+template <bool DUMP, bool TRACE, int WFMT = 4>
 __global__ void __launch_bounds__(THREADS, 1)
-gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble plane  [rows][nbk*16 B], box 64 B x 128
+gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble plane  [rows][nbk*16 B], box 64 B x 128   (WFMT 8: int8 plane [rows][K], box 128 B x 128, SW128)
                      const __grid_constant__ CUtensorMap tm_xq,    // activations   [n][K] int8,      box 128 B x 128, SW128
                      const __grid_constant__ CUtensorMap tm_xd,    // act. scales   [nbk][n_pad] f32 (columns permuted: xd_perm), box 128 x 4
                      const __half * __restrict__ wd,               // weight scales [rows][nbk]
@@ -313,7 +317,7 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < NS_RAW; i++) { mbar_init(bars + Bars::raw_full + 8 * i, 1); mbar_init(bars + Bars::raw_empty + 8 * i, UNPACK_WARPS); }
-        for (int i = 0; i < NS_OP; i++)  { mbar_init(bars + Bars::op_full + 8 * i, 1 + UNPACK_WARPS); mbar_init(bars + Bars::op_empty + 8 * i, 1); }
+        for (int i = 0; i < NS_OP; i++)  { mbar_init(bars + Bars::op_full + 8 * i, WFMT == 8 ? 1 : 1 + UNPACK_WARPS); mbar_init(bars + Bars::op_empty + 8 * i, 1); }
         for (int i = 0; i < NS_X; i++)   { mbar_init(bars + Bars::x_full + 8 * i, 1 + UNPACK_WARPS); mbar_init(bars + Bars::x_empty + 8 * i, EPI_WARPS); }
         for (int i = 0; i < NS_D; i++)   { mbar_init(bars + Bars::d_full + 8 * i, 1); mbar_init(bars + Bars::d_empty + 8 * i, EPI_WARPS); }
         mbar_fence_init();
@@ -342,12 +346,20 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
     // register budget: setmaxnreg at the top of each role's branch (the branches only meet again at the final barrier)
     if (warp < EPI_WARPS) {
         setmaxnreg_inc<EPI_REGS>();
-        epilogue<DUMP, TRACE>(sbase, tmem_base, warp, lane, m0, c0, rows, n, nbk, y, ldy, S_out, trc);
+        epilogue<DUMP, TRACE, WFMT>(sbase, tmem_base, warp, lane, m0, c0, rows, n, nbk, y, ldy, S_out, trc);
     } else if (warp == TMA_WARP) {
         setmaxnreg_dec<SVC_REGS>();
         if (lane == 0) {
             for (int s = 0; s < nstages; s++) {
                 const int sr = s % NS_RAW, so = s % NS_OP, sx = s % NS_X;
+                if (WFMT == 8) {
+                    (void)sr;
+                    if (s >= NS_OP) mbar_wait(bars + Bars::op_empty + 8 * so, ((s / NS_OP) - 1) & 1);
+                    G3K_TR(0, 3 * s + 1);
+                    mbar_expect_tx(bars + Bars::op_full + 8 * so, A_BYTES + B_BYTES);
+                    tma_load_2d(sbase + SMEM_OP + so * (A_BYTES + B_BYTES), &tm_nib, s * KB * 32, m0, bars + Bars::op_full + 8 * so);
+                    tma_load_2d(sbase + SMEM_OP + so * (A_BYTES + B_BYTES) + A_BYTES, &tm_xq, s * KB * 32, c0, bars + Bars::op_full + 8 * so);
+                } else {
                 if (s >= NS_RAW) mbar_wait(bars + Bars::raw_empty + 8 * sr, ((s / NS_RAW) - 1) & 1);
                 G3K_TR(0, 3 * s);
                 mbar_expect_tx(bars + Bars::raw_full + 8 * sr, RAW_BYTES);
@@ -356,6 +368,7 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
                 G3K_TR(0, 3 * s + 1);
                 mbar_expect_tx(bars + Bars::op_full + 8 * so, B_BYTES);
                 tma_load_2d(sbase + SMEM_OP + so * (A_BYTES + B_BYTES) + A_BYTES, &tm_xq, s * KB * 32, c0, bars + Bars::op_full + 8 * so);
+                }
                 if (s >= NS_X) mbar_wait(bars + Bars::x_empty + 8 * sx, ((s / NS_X) - 1) & 1);
                 G3K_TR(0, 3 * s + 2);
                 mbar_expect_tx(bars + Bars::x_full + 8 * sx, XD_BYTES);
@@ -405,7 +418,7 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
         const int t = threadIdx.x - UNPACK_WARP0 * 32;      // 0..63
         const int j = t & 3;                                  // block within the stage
         constexpr int RSTEP = UNPACK_WARPS * 8;              // tile rows between this thread's items (16)
-        const float DSCALE = 7.922816251426434e28f;          // 2^96
+        const float DSCALE = WFMT == 8 ? 1.2676506002282294e30f : 7.922816251426434e28f;          // 2^96 (x 2^4 when the MMA forms S_b, not 16 S_b)
         // Weight scales: thread t owns tile rows t and t + 64 and fetches their 4 fp16 scales of a k-stage as two
         // 32-bit words per row, THREE stages ahead.  Reads past a row's last block (tail stage) land in the next row or
         // in the plane's 16 bytes of slack and are never used.
@@ -423,14 +436,16 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
         for (int s = 0; s < nstages; s++) {
             const int sr = s % NS_RAW, so = s % NS_OP, sx = s % NS_X;
             if (t == 0) G3K_TR(3, 4 * s);
-            mbar_wait(bars + Bars::raw_full + 8 * sr, (s / NS_RAW) & 1);
+            if (WFMT != 8) mbar_wait(bars + Bars::raw_full + 8 * sr, (s / NS_RAW) & 1);
             if (t == 0) G3K_TR(3, 4 * s + 1);
             const uint32_t raw = sbase + SMEM_RAW + sr * RAW_BYTES + (t >> 2) * 64 + j * 16;
             constexpr int HALF = UNPACK_ROWS / 2;
             uint4 q[HALF];
+            if (WFMT != 8) {
 #pragma unroll
             for (int i = 0; i < HALF; i++) q[i] = lds_u32x4(raw + RSTEP * i * 64);
             if (s >= NS_OP) mbar_wait(bars + Bars::op_empty + 8 * so, ((s / NS_OP) - 1) & 1);
+            }
             if (s >= NS_X) mbar_wait(bars + Bars::x_empty + 8 * sx, ((s / NS_X) - 1) & 1);
             if (t == 0) G3K_TR(3, 4 * s + 2);
             const uint32_t a = sbase + SMEM_OP + so * (A_BYTES + B_BYTES);
@@ -445,6 +460,7 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
 #pragma unroll
             for (int i = 0; i < 4; i++) { p0[i] = p1[i]; p1[i] = p2[i]; }
             G3_LOAD_SCALES(s + 3, p2);
+            if (WFMT != 8) {
 #pragma unroll
             for (int h = 0; h < 2; h++) {
 #pragma unroll
@@ -467,10 +483,13 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
                 }
             }
             fence_proxy_async_smem();      // generic-proxy stores -> tensor-core (async proxy) reads
+            }
             __syncwarp();
             if (lane == 0) {
-                mbar_arrive(bars + Bars::op_full + 8 * so);
-                mbar_arrive(bars + Bars::raw_empty + 8 * sr);
+                if (WFMT != 8) {
+                    mbar_arrive(bars + Bars::op_full + 8 * so);
+                    mbar_arrive(bars + Bars::raw_empty + 8 * sr);
+                }
                 mbar_arrive(bars + Bars::x_full + 8 * sx);
             }
             if (t == 0) G3K_TR(3, 4 * s + 3);

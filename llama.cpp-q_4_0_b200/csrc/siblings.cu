@@ -35,6 +35,7 @@ struct ggml_b200_qweight {
     uint4 * wq = nullptr;          // [M][nbk] (Q4_1) or [M][nbk][2] (Q8_0)
     void *  wd = nullptr;          // [M][nbk] half (Q8_0) or half2 {d, m} (Q4_1)
     size_t  dev_bytes = 0;
+    void *  gemm = nullptr;        // Q8_0: TMA descriptor of the int8 plane for the tensor-core prefill kernel (gemm_q4_0_tc.cu)
 };
 
 namespace b200 {
@@ -345,6 +346,7 @@ extern "C" ggml_b200_qweight * ggml_b200_upload_quant(int type, const void * blo
         return nullptr;
     }
     w->dev_bytes = q_bytes + d_bytes;
+    if (type == GGML_B200_TYPE_Q8_0) w->gemm = gemm_prepare_q8(w->wq, M, K);      // (nullptr: no tensor-core path, column passes instead)
     return w;
 }
 
@@ -352,6 +354,7 @@ extern "C" void ggml_b200_free_quant(ggml_b200_qweight * w) {
     B200_API_LOCK;
     if (!w) return;
     if (g.inited) cudaStreamSynchronize(g.stream);
+    if (w->gemm) gemm_release_q8(w->gemm);
     if (w->wq) cudaFree(w->wq);
     if (w->wd) cudaFree(w->wd);
     delete w;
@@ -398,6 +401,14 @@ static int sib_mul_mat(const ggml_b200_qweight * w, const float * x_dev, int64_t
     if (nb11 % 16 != 0 || ((uintptr_t)x_dev & 15) != 0) { set_error("sibling formats: activation rows must be 16-byte aligned (every ggml tensor is: GGML_MEM_ALIGN)"); return GGML_B200_ERR_ARG; }
     if (nb11 % 4 != 0 || nb1 % 4 != 0 || nb11 < (size_t)w->K * 4 || nb1 < (size_t)w->M * 4) { set_error("sibling formats: bad strides nb11=%zu nb1=%zu", nb11, nb1); return GGML_B200_ERR_ARG; }
     const long long ldy = (long long)(nb1 / 4);
+    // prefill on the tensor cores: Q8_0's int8 plane is kernel 3's A operand as it lies (gemm_q4_0_tc3.cuh, WFMT = 8);
+    // kernel 1 of the Q4_0 path quantizes the activations (the same q8_0 blocks) into kernel 3's layout
+    if (w->type == GGML_B200_TYPE_Q8_0 && w->gemm != nullptr && n <= INT32_MAX && g.path != GGML_B200_PATH_GEMV &&
+        (g.path == GGML_B200_PATH_GEMM || n >= g.gemm_min_n)) {
+        int rc = launch_quantize(x_dev, n, w->K, nb11, nullptr);
+        if (rc) return rc;
+        return launch_gemm_q8(w->gemm, w->wd, w->M, w->K, y_dev, ldy, (int)n, S_dev);
+    }
     for (int64_t c0 = 0; c0 < n; c0 += sib::SIB_NC) {
         const int nc = (int)(n - c0 < sib::SIB_NC ? n - c0 : sib::SIB_NC);
         const float * xc = reinterpret_cast<const float *>(reinterpret_cast<const char *>(x_dev) + (size_t)c0 * nb11);

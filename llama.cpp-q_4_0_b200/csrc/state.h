@@ -137,6 +137,10 @@ int  gemm_prepare_weight(ggml_b200_weight * w);
 void gemm_release_weight(ggml_b200_weight * w);
 // y: first output element of this shard (column 0), ldy in floats; S != nullptr: also dump S_b
 int  launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int * S, int independent = 0);
+// the same kernel over a Q8_0 weight's int8 plane (siblings.cu); handle = its TMA descriptor
+void * gemm_prepare_q8(const void * wq, int64_t M, int64_t K);
+void gemm_release_q8(void * handle);
+int  launch_gemm_q8(const void * handle, const void * wd, int64_t M, int64_t K, float * y, long long ldy, int n, int * S);
 
 }  // namespace b200
 

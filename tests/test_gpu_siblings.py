@@ -65,6 +65,33 @@ def test_block_dots_bit_exact_and_result_within_tolerance(b200, qtype, M, K, n):
     w.free()
 
 
+@pytest.mark.parametrize("M,K,n", [(128, 128, 32), (200, 4096, 33), (257, 4544, 130), (130, 11008, 64), (512, 4096, 160)])
+def test_q8_0_prefill_on_the_tensor_cores(b200, M, K, n):
+    """n >= gemm_min_n: Q8_0's int8 plane is kernel 3's A operand as it lies (tcgen05 kind::i8, WFMT = 8).  Block dots
+    bit-exact, result within 1e-4, the column-pass kernel (forced with set_path) agrees; ragged rows / columns / K tail."""
+    qtype = sib.TYPE_Q8_0
+    W = _weights(qtype, 40 + M, M, K)
+    X = _x(50 + n, n, K)
+    w = b200.QuantWeight(qtype, W)
+    c0 = b200.launch_count()
+    Y, S = w.mul_mat(X, checkpoint=True)
+    assert b200.launch_count() - c0 == 2                     # kernel 1 + kernel 3, not n / 4 column passes
+    Q = sib.quantize_dot(qtype, X)
+    assert np.array_equal(S, sib.block_dots(qtype, W, Q))
+    Yo = sib.mul_mat(qtype, W, X)
+    err = np.max(np.abs(Y - Yo), axis=1) / np.maximum(np.max(np.abs(Yo), axis=1), 1e-30)
+    assert np.all(err <= TOL), err
+    assert np.array_equal(w.mul_mat(X), Y)
+    b200.set_path(b200.PATH_GEMV)
+    try:
+        Yc = w.mul_mat(X)
+    finally:
+        b200.set_path(b200.PATH_AUTO)
+    errc = np.max(np.abs(Y - Yc), axis=1) / np.maximum(np.max(np.abs(Yo), axis=1), 1e-30)
+    assert np.all(errc <= 1e-5), errc
+    w.free()
+
+
 @pytest.mark.parametrize("qtype", TYPES)
 def test_against_the_reference_itself(b200, ref, qtype):
     """Where oracle/_ref is present: weights quantized by the reference's own quantize_row_q, the op through its graph."""
