@@ -158,6 +158,12 @@ int          ggml_b200_add_f32(const float * a_dev, const float * b_dev, float *
 int          ggml_b200_silu_f32(const float * x_dev, float * y_dev, int64_t n);
 int          ggml_b200_silu_mul_f32(const float * x_dev, const float * b_dev, float * y_dev, int64_t n,
                                     float * silu_dev /* NULL, or also receives silu(x) */);
+/* rope, mode 0 (ggml_compute_forward_rope_f32, ggml.c:12714-12850; behind wq / wk in llama.cpp:1342-1347): x_dev is
+ * [npos][rows_per_pos][ne0], adjacent pairs (2k, 2k+1) of every row are rotated by cos_sin_dev[pos][k] = {cos, sin}; the
+ * caller supplies the angles (the glue runs the reference's float recurrence theta_k = p * scale^k on the host, so they are
+ * the reference's bit for bit).  y_dev may be x_dev (rope_inplace). */
+int          ggml_b200_rope_f32(const float * x_dev, float * y_dev, const float * cos_sin_dev, int64_t ne0,
+                                int64_t rows_per_pos, int64_t npos);
 /* rms_norm and the MUL by the norm weights that follows it in every layer, one kernel; both results are written */
 int          ggml_b200_rms_norm_mul_f32(const float * x_dev, float * y_norm_dev, const float * w_dev, float * y_dev,
                                         int64_t ncols, int64_t nrows, int64_t nw, float eps);

@@ -140,6 +140,33 @@ __global__ void __launch_bounds__(256) eltwise_f32_kernel(const float * __restri
     if (threadIdx.x == 0) tr.mark(3);
 }
 
+// rope, mode 0 (ggml_compute_forward_rope_f32, ggml.c:12714-12850, the `!is_neox` branch): adjacent pairs of every row
+// are rotated by the angle of the row's position; tab[pos][k] = {cos, sin} of theta_k comes from the HOST (the glue runs
+// the reference's own float recurrence through the host's libm, so the angles are the reference's bit for bit).  The node
+// sits right behind wq / wk in the graph (llama.cpp:1342-1347); on the CPU it costs 4096 cosf + sinf per layer and token.
+// x: [npos][rows_per_pos][ne0]; one thread per pair; y may alias x (rope_inplace).
+__global__ void __launch_bounds__(256) rope_f32_kernel(const float * __restrict__ x, float * __restrict__ y, const float2 * __restrict__ tab,
+                                                       int ne0, int rows_per_pos, long long npairs, unsigned seq) {
+    CtaTrace tr;
+    if (threadIdx.x == 0) tr.begin(seq | 0x80000000u);
+    pdl_wait();
+    pdl_launch_dependents();
+    if (threadIdx.x == 0) tr.mark(1);
+    const int half = ne0 >> 1;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < npairs; i += (long long)gridDim.x * blockDim.x) {
+        const int k = (int)(i % half);
+        const long long row = i / half;
+        const long long pos = row / rows_per_pos;
+        const float2 cs = __ldcg(tab + pos * half + k);
+        const float2 v = __ldcg(reinterpret_cast<const float2 *>(x) + i);
+        float2 o;
+        o.x = __fsub_rn(__fmul_rn(v.x, cs.x), __fmul_rn(v.y, cs.y));
+        o.y = __fadd_rn(__fmul_rn(v.x, cs.y), __fmul_rn(v.y, cs.x));
+        reinterpret_cast<float2 *>(y)[i] = o;
+    }
+    if (threadIdx.x == 0) tr.mark(3);
+}
+
 // a small row between HBM and MAPPED pinned host memory (either direction), 16 bytes per thread (ggml-b200.cu: small_copy)
 __global__ void __launch_bounds__(128) copy_rows_kernel(uint4 * __restrict__ dst, const uint4 * __restrict__ src, int n16, unsigned seq) {
     CtaTrace tr;

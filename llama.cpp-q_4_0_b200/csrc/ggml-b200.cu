@@ -700,6 +700,17 @@ int ggml_b200_rms_norm_mul_f32(const float * x_dev, float * y_norm_dev, const fl
     if (ncols > INT32_MAX || nrows > INT32_MAX || nw > INT32_MAX) { set_error("rms_norm_mul: shape too large"); return GGML_B200_ERR_ARG; }
     return rms_norm_launch(x_dev, y_norm_dev, ncols, nrows, eps, w_dev, y_dev, nw);
 }
+int ggml_b200_rope_f32(const float * x_dev, float * y_dev, const float * cos_sin_dev, int64_t ne0, int64_t rows_per_pos, int64_t npos) {
+    B200_API_LOCK;
+    const int64_t n = ne0 * rows_per_pos * npos;
+    int rc = eltwise_check(x_dev, y_dev, n);
+    if (rc) return rc;
+    if (!cos_sin_dev || ne0 <= 0 || (ne0 & 1) || rows_per_pos <= 0 || npos < 0 || ne0 > INT32_MAX || rows_per_pos > INT32_MAX ||
+        ((((uintptr_t)x_dev) | ((uintptr_t)y_dev) | ((uintptr_t)cos_sin_dev)) & 7)) { set_error("rope: bad arguments"); return GGML_B200_ERR_ARG; }
+    if (n == 0) return GGML_B200_OK;
+    return launch_k(rope_f32_kernel, dim3(eltwise_grid(n / 2)), dim3(256), 0, x_dev, y_dev, (const float2 *)cos_sin_dev, (int)ne0, (int)rows_per_pos, (long long)(n / 2),
+                    (unsigned)g.launches);
+}
 int ggml_b200_mul_f32(const float * a_dev, const float * b_dev, float * y_dev, int64_t n, int64_t nb) {
     B200_API_LOCK;
     int rc = eltwise_check(a_dev, y_dev, n);

@@ -124,6 +124,7 @@ def _load() -> C.CDLL:
         "ggml_b200_rms_norm_mul_f32": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, C.c_float]),
         "ggml_b200_mark": (C.c_int, [C.c_int]),
         "ggml_b200_wait_mark": (C.c_int, [C.c_int]),
+        "ggml_b200_rope_f32": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64]),
         "ggml_b200_neigh_ok": (C.c_int, [_vp]),
         "ggml_b200_mul_mat_q4_0_add": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
         "ggml_b200_mul_mat_q4_0_swiglu": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),

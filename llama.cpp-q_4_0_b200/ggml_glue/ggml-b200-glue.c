@@ -102,7 +102,9 @@ void ggml_cuda_set_scratch_size(size_t scratch_size) {
     g_scratch_size = scratch_size;
     g_scratch_off = 0;
 }
+void ggml_b200_glue_profile_dump(void);
 void ggml_cuda_free_scratch(void) {
+    ggml_b200_glue_profile_dump();
     if (g_scratch == NULL) return;
     ggml_b200_synchronize();
     ggml_b200_dev_free(g_scratch);
@@ -120,6 +122,7 @@ static int is_devf32(const struct ggml_tensor * t) {
 static float * dev_ptr(const struct ggml_tensor * t) { return (float *)((struct ggml_tensor_extra_gpu *)t->extra)->data_device[0]; }
 static int f32_contig(const struct ggml_tensor * t) { return t != NULL && t->type == GGML_TYPE_F32 && ggml_is_contiguous(t); }
 
+#define ROPE_TAB_BYTES ((size_t)256 << 10)
 /* can this node run on the device?  (shape rules of the kernels in csrc/elementwise.cuh and of the op) */
 static int node_supported(const struct ggml_tensor * t) {
     if (!g_ready || t == NULL || !f32_contig(t)) return 0;
@@ -132,6 +135,16 @@ static int node_supported(const struct ggml_tensor * t) {
             /* src1 = src0's shape, or one row repeated over src0's rows (norm weights: ggml.c:9199-9210) */
             return f32_contig(t->src0) && f32_contig(t->src1) && t->src0->ne[0] == t->src1->ne[0] &&
                    (ggml_nelements(t->src1) == ggml_nelements(t->src0) || ggml_nelements(t->src1) == t->src1->ne[0]);
+        case GGML_OP_RESHAPE:
+            /* a contiguous reshape of a device-resident tensor is the same buffer under another shape */
+            return f32_contig(t->src0) && is_act(t->src0);
+        case GGML_OP_ROPE: {
+            /* mode 0 over whole rows (llama.cpp:1342-1347); tables of up to 256 KB (N * ne0 floats) */
+            if (!f32_contig(t->src0) || t->src1 == NULL || t->src1->type != GGML_TYPE_I32 || ggml_nelements(t->src1) != 4 || t->src1->data == NULL) return 0;
+            const int32_t * pr = (const int32_t *)t->src1->data;
+            return pr[2] == 0 && pr[1] == t->ne[0] && (t->ne[0] & 1) == 0 && t->ne[3] == 1 && pr[0] >= 0 &&
+                   (size_t)t->ne[2] * (size_t)t->ne[0] * sizeof(float) <= ROPE_TAB_BYTES;
+        }
         case GGML_OP_MUL_MAT:
             return ((weight_of(t->src0) != NULL && t->src0->type == GGML_TYPE_Q4_0) || qweight_of(t->src0) != NULL) && f32_contig(t->src1) &&
                    t->src0->ne[2] == 1 && t->src0->ne[3] == 1 && t->src1->ne[2] == 1 && t->src1->ne[3] == 1 && t->src0->ne[0] % 64 == 0;
@@ -161,11 +174,14 @@ static void assign_buffers_impl(struct ggml_tensor * tensor, int scratch, int fo
         g_stage_out_next = 0;
     }
     if (scratch && g_scratch_size == 0) return;                 /* llama.cpp low_vram: ggml_cuda_set_scratch_size(0) */
+    /* like the reference (ggml-cuda.cu:2835-2841): a reshape between this node and a device-resident tensor comes along */
+    if (tensor->op == GGML_OP_ROPE && tensor->src0 != NULL && tensor->src0->op == GGML_OP_RESHAPE && !is_act(tensor->src0))
+        assign_buffers_impl(tensor->src0, scratch, force_inplace);
     if (!node_supported(tensor)) return;                        /* stays on the CPU */
     const size_t size = (ggml_nbytes(tensor) + 255) & ~(size_t)255;
     struct ggml_tensor_extra_gpu * extra = &g_extra_pool[g_extra_next++ % B200_EXTRA_POOL];
     memset(extra, 0, sizeof(*extra));
-    const int inplace = force_inplace || (tensor->src0 != NULL && tensor->src0->data == tensor->data);
+    const int inplace = force_inplace || tensor->op == GGML_OP_RESHAPE || (tensor->src0 != NULL && tensor->src0->data == tensor->data);
     if (inplace && is_act(tensor->src0)) {
         extra->data_device[0] = dev_ptr(tensor->src0);          /* an _inplace node writes its src0's buffer */
     } else if (scratch) {
@@ -368,7 +384,7 @@ void ggml_cuda_mul(const struct ggml_tensor * src0, const struct ggml_tensor * s
  * eval: same scratch addresses, same compute buffer) is replayed as ONE CUDA graph launch instead, so the host pays one
  * call per segment instead of one per node and copy.  Two peephole fusions at record time: RMS_NORM followed by the MUL
  * that reads it, and SILU followed by the MUL that reads it, become one kernel each (both results are still written). */
-enum { PL_MUL_MAT, PL_RMS_NORM, PL_RMS_NORM_MUL, PL_MUL, PL_ADD, PL_SILU, PL_SILU_MUL, PL_MUL_MAT_ADD, PL_SWIGLU };
+enum { PL_MUL_MAT, PL_RMS_NORM, PL_RMS_NORM_MUL, PL_MUL, PL_ADD, PL_SILU, PL_SILU_MUL, PL_MUL_MAT_ADD, PL_SWIGLU, PL_ROPE };
 struct plan {
     int kind;
     ggml_b200_weight * w, * w3;      /* w3: the second weight of PL_SWIGLU */
@@ -449,18 +465,27 @@ static int arenas_ready(void) {
 
 /* GGML_B200_GLUE_PROFILE=1: where the host's time goes (printed by ggml_b200_glue_profile_dump / at scratch free) */
 #include <time.h>
-static struct { double flush_s, wait_s; long flushes, replays, captures, direct, waits, nodes; double wait_by_n[SEG_MAX + 1]; long waits_by_n[SEG_MAX + 1]; } g_prof;
+static struct { double flush_s, wait_s, record_s; long flushes, replays, captures, direct, waits, nodes; double wait_by_n[SEG_MAX + 1]; long waits_by_n[SEG_MAX + 1]; } g_prof;
 static int g_last_flush_n = 0;         /* plans in the segment submitted last (profile: waits by segment length) */
 static int g_prof_on = -1;
+static double g_prof_cpu_by_op[GGML_OP_COUNT], g_prof_last_t = 0.0;
+static int g_prof_last_op = -1;
+static long g_spec_hits = 0, g_spec_misses = 0;      /* segments submitted ahead that came / did not come (flush_segment) */
 static double now_s(void) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec; }
 void ggml_b200_glue_profile_dump(void) {
     if (g_prof_on > 0 && g_prof.nodes)
-        fprintf(stderr, "ggml-b200 glue: %ld device nodes, %ld segments (%ld replayed, %ld recorded, %ld direct) %.3f ms submitting, %ld waits %.3f ms\n",
-                g_prof.nodes, g_prof.flushes, g_prof.replays, g_prof.captures, g_prof.direct, g_prof.flush_s * 1e3, g_prof.waits, g_prof.wait_s * 1e3);
+        fprintf(stderr, "ggml-b200 glue: %ld device nodes, %ld segments (%ld replayed, %ld recorded, %ld direct) %.3f ms submitting, %ld waits %.3f ms, %.3f ms recording, %ld run ahead\n",
+                g_prof.nodes, g_prof.flushes, g_prof.replays, g_prof.captures, g_prof.direct, g_prof.flush_s * 1e3, g_prof.waits, g_prof.wait_s * 1e3, g_prof.record_s * 1e3, g_spec_hits);
     if (g_prof_on > 0 && g_prof.nodes) {
         fprintf(stderr, "ggml-b200 glue: waits by kernels in the segment before them (kernels: count x mean us):");
         for (int i = 0; i <= SEG_MAX; i++) if (g_prof.waits_by_n[i]) fprintf(stderr, "  %d: %ld x %.1f", i, g_prof.waits_by_n[i], g_prof.wait_by_n[i] * 1e6 / (double)g_prof.waits_by_n[i]);
         fprintf(stderr, "\n");
+    }
+    if (g_prof_on > 0 && g_prof.nodes) {
+        fprintf(stderr, "ggml-b200 glue: host time between hook calls by the op the CPU ran (ms):");
+        for (int i = 0; i < GGML_OP_COUNT; i++) if (g_prof_cpu_by_op[i] > 1e-4) fprintf(stderr, "  op%d %.2f", i, g_prof_cpu_by_op[i] * 1e3);
+        fprintf(stderr, "\n");
+        memset(g_prof_cpu_by_op, 0, sizeof(g_prof_cpu_by_op));
     }
     memset(&g_prof, 0, sizeof(g_prof));
 }
@@ -512,6 +537,7 @@ static void issue(const struct plan * p) {
         case PL_SILU:         B200_CHECK(ggml_b200_silu_f32(p->a, p->y, p->n)); break;
         case PL_SILU_MUL:     B200_CHECK(ggml_b200_silu_mul_f32(p->a, p->b, p->y2, p->n, p->y)); break;
         case PL_MUL_MAT_ADD:  B200_CHECK(ggml_b200_mul_mat_q4_0_add(p->w, p->a, p->y, p->b, p->y2)); break;
+        case PL_ROPE:         B200_CHECK(ggml_b200_rope_f32(p->a, p->y, p->b, p->ncols, p->nrows, p->n)); break;
         case PL_SWIGLU:       B200_CHECK(ggml_b200_mul_mat_q4_0_swiglu(p->w, p->w3, p->a, p->y, p->y3, p->ys, p->y2)); break;
     }
 }
@@ -527,7 +553,7 @@ static void issue_segment(void) {
  * (12-15 us against 3 us of work, profiles/r02_trace_seam_after.log).  So when a recorded segment is submitted, the
  * segment that followed it last time is submitted right behind it if
  *   - this graph has the same fingerprint as the previous one (same device nodes in the same order: a decode loop),
- *   - it is recorded (replayable) and consists of n = 1 matmuls only, every source in HBM, every result going either
+ *   - it is recorded (replayable) and consists of n = 1 matmuls (and the rope behind one) only, every source in HBM, every result going either
  *     down to the host through a staging block and the down arena, or into its tensor's own device buffer while the
  *     scratch ring has not come round within this graph (no other tensor of the graph shares that buffer): it writes
  *     nothing a CPU node in between could read.
@@ -539,7 +565,6 @@ static int g_spec_ok = 0;               /* fingerprint of this graph == fingerpr
 static int g_spec_inflight = -1;        /* cache index of the segment submitted ahead, -1: none */
 static int g_last_hit = -1;             /* cache index of the segment submitted last in this graph (for the successor links) */
 static int g_mark_next = 0, g_spec_mark = -1;
-static long g_spec_hits = 0, g_spec_misses = 0;
 static void new_graph_reset(void) {
     /* (called at the first ggml_cuda_assign_buffers of a graph: the previous graph has been computed) */
     if (g_spec_inflight >= 0) { B200_CHECK(ggml_b200_synchronize()); g_spec_inflight = -1; }
@@ -553,7 +578,9 @@ static int speculatable(int c) {
     if (c < 0 || g_cache[c].exec == NULL) return 0;
     for (int i = 0; i < g_cache[c].n; i++) {
         const struct plan * p = &g_cache[c].plans[i];
-        if (p->kind != PL_MUL_MAT || p->n != 1 || p->sharded || p->h2d_bytes[0] || p->h2d_bytes[1]) return 0;
+        if (p->h2d_bytes[0] || p->h2d_bytes[1]) return 0;
+        if (p->kind == PL_ROPE && p->n == 1 && !p->d2h_bytes) continue;      /* rope(wq x) in place on the matmul's own result; its table is in HBM before any segment of the eval */
+        if (p->kind != PL_MUL_MAT || p->n != 1 || p->sharded) return 0;
         if (p->d2h_bytes && ((const char *)p->d2h_dst < g_down || (const char *)p->d2h_dst >= g_down + ARENA_BYTES)) return 0;
     }
     return 1;
@@ -741,6 +768,38 @@ static void ensure_host(struct ggml_tensor * t) {
     }
 }
 
+/* The angles of a rope node, computed as the reference computes them (ggml.c:12771-12813: theta = p, then theta *= theta_scale
+ * per pair, cosf / sinf of the host's libm) and kept in ONE device block whose address the recorded segments hold: it is
+ * refilled when the position changes (once per token: q and k of every layer share it), by a copy queued on the stream
+ * ahead of the segments that read it. */
+#include <math.h>
+static float * g_rope_dev = NULL;
+static float * g_rope_pin[2] = {NULL, NULL};
+static int g_rope_flip = 0;
+static struct { int n_past, n_dims, ne0, npos, valid; } g_rope_key;
+static const float * rope_table(int n_past, int n_dims, int ne0, int npos) {
+    if (g_rope_dev == NULL) {
+        g_rope_dev = (float *)ggml_b200_dev_malloc(ROPE_TAB_BYTES);
+        g_rope_pin[0] = (float *)ggml_b200_host_malloc(ROPE_TAB_BYTES);
+        g_rope_pin[1] = (float *)ggml_b200_host_malloc(ROPE_TAB_BYTES);
+        if (g_rope_dev == NULL || g_rope_pin[0] == NULL || g_rope_pin[1] == NULL) { fprintf(stderr, "ggml-b200: %s\n", ggml_b200_last_error()); exit(1); }
+    }
+    if (g_rope_key.valid && g_rope_key.n_past == n_past && g_rope_key.n_dims == n_dims && g_rope_key.ne0 == ne0 && g_rope_key.npos == npos) return g_rope_dev;
+    float * tab = g_rope_pin[g_rope_flip ^= 1];
+    const float theta_scale = powf(10000.0, -2.0f / n_dims);
+    for (int i2 = 0; i2 < npos; i2++) {
+        float theta = (float)(n_past + i2);
+        for (int k = 0; k < ne0 / 2; k++) {
+            tab[((size_t)i2 * (ne0 / 2) + k) * 2] = cosf(theta);
+            tab[((size_t)i2 * (ne0 / 2) + k) * 2 + 1] = sinf(theta);
+            theta *= theta_scale;
+        }
+    }
+    B200_CHECK(ggml_b200_memcpy_h2d_async(g_rope_dev, tab, (size_t)npos * (size_t)ne0 * sizeof(float)));
+    g_rope_key.n_past = n_past; g_rope_key.n_dims = n_dims; g_rope_key.ne0 = ne0; g_rope_key.npos = npos; g_rope_key.valid = 1;
+    return g_rope_dev;
+}
+
 static void device_node(struct ggml_tensor * t) {
     glue_env();
     if (g_seg_n == SEG_MAX) flush_segment();
@@ -845,6 +904,15 @@ static void device_node(struct ggml_tensor * t) {
         case GGML_OP_SILU:
             p->kind = PL_SILU; p->a = plan_src(p, t->src0, 0); p->y = plan_dst(p, t);
             break;
+        case GGML_OP_RESHAPE:
+            ((struct ggml_tensor_extra_gpu *)t->extra)->data_device[2] = NULL;      /* same buffer as src0: nothing to run */
+            return;
+        case GGML_OP_ROPE: {
+            const int32_t * pr = (const int32_t *)t->src1->data;
+            p->kind = PL_ROPE; p->ncols = t->ne[0]; p->nrows = t->ne[1]; p->n = t->ne[2];
+            p->b = rope_table(pr[0], pr[1], (int)t->ne[0], (int)t->ne[2]);
+            p->a = plan_src(p, t->src0, 0); p->y = plan_dst(p, t);
+        } break;
         default:
             GGML_ASSERT(!"device_node: unsupported op");
     }
@@ -867,6 +935,12 @@ static void device_node(struct ggml_tensor * t) {
  * graphs end on the output matmul, whose sources and result are on the host: the synchronous host path. */
 bool ggml_cuda_compute_forward(struct ggml_compute_params * params, struct ggml_tensor * tensor) {
     if (!g_ready) return false;
+    if (g_prof_on > 0 && params->ith == 0) {                  /* profile: wall time between hook calls, by the op the CPU ran */
+        const double t = now_s();
+        if (g_prof_last_op >= 0 && g_prof_last_op < GGML_OP_COUNT) g_prof_cpu_by_op[g_prof_last_op] += t - g_prof_last_t;
+        g_prof_last_t = t;
+        g_prof_last_op = -1;
+    }
     if (!g_computed_since_assign && params->ith == 0) {       /* first node of a graph: its fingerprint is complete */
         g_fp_previous = g_fp_running; g_fp_running = g_fp_build;
         g_spec_ok = g_fp_running != 0 && g_fp_running == g_fp_previous && !g_ring_wrapped;
@@ -874,15 +948,18 @@ bool ggml_cuda_compute_forward(struct ggml_compute_params * params, struct ggml_
     g_computed_since_assign = 1;
     const int on_device = is_act(tensor) || is_act(tensor->src0) || is_act(tensor->src1);
     const int host_mul_mat = tensor->op == GGML_OP_MUL_MAT && !on_device && ggml_cuda_can_mul_mat(tensor->src0, tensor->src1, tensor);
-    if ((on_device && node_supported(tensor)) || host_mul_mat) {
+    /* (a reshape is a device node only where assign_buffers made it an alias of its source's buffer) */
+    if ((on_device && node_supported(tensor) && (tensor->op != GGML_OP_RESHAPE || is_act(tensor))) || host_mul_mat) {
         if (params->ith != 0) return true;
         if (params->type == GGML_TASK_INIT || params->type == GGML_TASK_FINALIZE) return true;
         if (host_mul_mat) { flush_segment(); wait_pending(); ggml_cuda_mul_mat(tensor->src0, tensor->src1, tensor, params->wdata, params->wsize); }
+        else if (g_prof_on > 0) { const double t0 = now_s(); device_node(tensor); g_prof.record_s += now_s() - t0; }
         else device_node(tensor);
         return true;
     }
     /* the reference's CPU code runs this node: before any thread starts on it (INIT), submit what is recorded, bring
      * device-resident sources home and wait for the copies in flight */
+    if (g_prof_on > 0 && params->ith == 0) g_prof_last_op = (int)tensor->op;
     if (params->ith == 0 && params->type == GGML_TASK_INIT) {
         flush_segment();
         ensure_host(tensor->src0);

@@ -27,3 +27,29 @@ def silu(x):
 
 def silu_mul(a, b):
     return (silu(a) * np.asarray(b, np.float32)).astype(np.float32)
+
+
+def rope_table(n_past, n_dims, ne0, npos):
+    """cos / sin of the angles ggml_compute_forward_rope_f32 walks through (ggml.c:12771-12813, mode 0): theta = p, then
+    theta *= theta_scale per pair, all in float32.  (numpy's float32 cos / sin stand in for the host's cosf / sinf: equal
+    or one ulp apart; the product gets its table from the host's libm through the glue.)  -> [npos][ne0 / 2][2]"""
+    scale = np.float32(np.power(np.float32(10000.0), np.float32(-2.0) / np.float32(n_dims), dtype=np.float32))
+    tab = np.zeros((npos, ne0 // 2, 2), np.float32)
+    for i2 in range(npos):
+        theta = np.float32(n_past + i2)
+        for k in range(ne0 // 2):
+            tab[i2, k, 0] = np.cos(theta, dtype=np.float32)
+            tab[i2, k, 1] = np.sin(theta, dtype=np.float32)
+            theta = np.float32(theta * scale)
+    return tab
+
+
+def rope(x, tab):
+    """x [npos][rows][ne0]: adjacent pairs rotated, four float32 products and two sums per pair, no fused multiply-add."""
+    x = np.asarray(x, np.float32)
+    x0, x1 = x[..., 0::2], x[..., 1::2]
+    c, s = tab[:, None, :, 0], tab[:, None, :, 1]
+    y = np.empty_like(x)
+    y[..., 0::2] = (x0 * c).astype(np.float32) - (x1 * s).astype(np.float32)
+    y[..., 1::2] = (x0 * s).astype(np.float32) + (x1 * c).astype(np.float32)
+    return y

@@ -22,7 +22,12 @@ def n_ff(hp=HP):
     return ((2 * (4 * hp["n_embd"]) // 3 + hp["n_mult"] - 1) // hp["n_mult"]) * hp["n_mult"]    # llama.cpp:930
 
 
-def write_model(path, seed=1234, hp=HP):
+HP_7B = dict(n_vocab=32000, n_embd=4096, n_mult=256, n_head=32, n_layer=32, n_rot=128, ftype=2)     # LLaMA-7B's own dimensions
+
+
+def write_model(path, seed=1234, hp=HP, direct_blocks=False):
+    """direct_blocks: the Q4_0 blocks are drawn directly (random nibbles, fp16 scale ~ scale / 4.6) instead of quantizing
+    random floats -- what makes a 7B-sized file (3.9 GB) a matter of seconds."""
     import oracle
     P = oracle.port()
     rng = np.random.default_rng(seed)
@@ -39,6 +44,11 @@ def write_model(path, seed=1234, hp=HP):
         f.write(np.ascontiguousarray(data).tobytes())
 
     def q4(rows, cols, scale):
+        if direct_blocks:
+            blk = rng.integers(0, 256, size=(rows, cols // 32, 18), dtype=np.uint8)
+            d = (scale / 4.6 * rng.uniform(0.7, 1.3, size=(rows, cols // 32))).astype(np.float16)
+            blk[..., 0:2] = d.view(np.uint8).reshape(rows, cols // 32, 2)
+            return blk
         w = (rng.standard_normal((rows, cols)) * scale).astype(np.float32)
         return P.quantize_q4_0(w)                                                                # [rows][cols/32][18]
 

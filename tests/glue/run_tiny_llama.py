@@ -12,7 +12,8 @@ import numpy as np
 lib, model, ngl, n_prompt, out = sys.argv[1], sys.argv[2], int(sys.argv[3]), int(sys.argv[4]), sys.argv[5]
 L = C.CDLL(lib)
 L.tiny_llama_run.restype = C.c_int
-NV = 512
+import os
+NV = int(os.environ.get("TINY_LLAMA_N_VOCAB", "512"))
 toks = [1] + [(7 * i + 3) % NV for i in range(n_prompt - 1)]          # BOS first (llama.cpp:1336)
 arr = (C.c_int * n_prompt)(*toks)
 if len(sys.argv) > 6:
@@ -21,7 +22,7 @@ if len(sys.argv) > 6:
     steps = np.zeros((n_decode, NV), np.float32)
     ms = C.c_double(0.0)
     cnt = (C.c_long * 2)(0, 0)
-    rc = L.tiny_llama_decode(model.encode(), ngl, arr, n_prompt, n_decode, 4, steps.ctypes.data_as(C.c_void_p), C.byref(ms), cnt, NV)
+    rc = L.tiny_llama_decode(model.encode(), ngl, arr, n_prompt, n_decode, int(os.environ.get("TINY_LLAMA_THREADS", "4")), steps.ctypes.data_as(C.c_void_p), C.byref(ms), cnt, NV)
     if rc != 0:
         sys.exit("tiny_llama_decode failed: %d" % rc)
     print(f"decode_ms_per_step={ms.value:.4f} replays={cnt[0]} ahead={cnt[1]}", flush=True)

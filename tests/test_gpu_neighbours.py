@@ -69,3 +69,22 @@ def test_contract(b200, port, ref):
     with pytest.raises(b200.B200Error):
         b200._check(b200.lib().ggml_b200_mul_mat_q4_0_swiglu(w.h, w2.h, d.ptr, d.ptr, d.ptr, None, d.ptr))
     w.free(); w2.free()
+
+
+@pytest.mark.parametrize("npos,rows,ne0", [(1, 32, 128), (7, 32, 128), (1, 71, 64), (3, 5, 2)])
+def test_rope_mode0(b200, npos, rows, ne0):
+    """ggml_b200_rope_f32 against the oracle's restatement on the same angle table: bit-exact (the same four products and
+    two sums per pair), in place and out of place."""
+    rng = np.random.default_rng(npos * 1000 + ne0)
+    x = rng.standard_normal((npos, rows, ne0), dtype=np.float32)
+    tab = nb.rope_table(13, ne0, ne0, npos)
+    want = nb.rope(x, tab)
+    xd, td = b200.DevBuf.from_numpy(x), b200.DevBuf.from_numpy(tab)
+    yd = b200.DevBuf(x.nbytes)
+    b200._check(b200.lib().ggml_b200_rope_f32(xd.ptr, yd.ptr, td.ptr, ne0, rows, npos))
+    b200.synchronize()
+    assert np.array_equal(yd.to_numpy(np.float32, x.shape).view(np.uint32), want.view(np.uint32))
+    b200._check(b200.lib().ggml_b200_rope_f32(xd.ptr, xd.ptr, td.ptr, ne0, rows, npos))
+    b200.synchronize()
+    assert np.array_equal(xd.to_numpy(np.float32, x.shape).view(np.uint32), want.view(np.uint32))
+    assert np.allclose(np.linalg.norm(want, axis=-1), np.linalg.norm(x, axis=-1), rtol=1e-5)      # a rotation
