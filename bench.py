@@ -762,8 +762,8 @@ def prefill_leg(mod, stream, rng, steps, warmup, n=512, shapes=None, groups=None
 
 def prefill_sharded_leg(mod, stream, rng, rank, world, dist, steps, warmup, n=512):
     """BASELINE metric "int8 TOPS (n = 512) at 2/4/8 GPUs": one LLaMA-65B layer + output at n = 512, every weight row-sharded
-    (ggml_b200_mul_mat_q4_0_sharded: kernel 1 + kernel 3 on the shard, ncclAllGather of the slabs over NVLink, scatter into
-    dst).  Timed three ways with CUDA events, max over ranks: the whole op; the shard GEMMs alone (no gather); the op with
+    (ggml_b200_mul_mat_q4_0_sharded: kernel 1 + kernel 3 on the shard; kernel 3 stores every finished tile into the peers'
+    landing buffers over NVLink and a collect kernel moves the peers' rows into dst -- no collective call).  Timed three ways with CUDA events, max over ranks: the whole op; the shard GEMMs alone (no gather); the op with
     pinned host x / y around it (e2e).  SURVEY 8(e) predicts the gather, not the GEMM, bounds it."""
     import torch
     L_ = mod.lib()
@@ -847,7 +847,7 @@ def prefill_sharded_leg(mod, stream, rng, rank, world, dist, steps, warmup, n=51
             "kernels_only": {"value": tops(ms_gemm), "ms_per_pass": ms_gemm, "what": "kernel 1 + kernel 3 on every rank's shards, no exchange"},
             "gather": {"ms_per_pass": ms_op - ms_gemm, "bytes_received_per_rank_per_pass": int(gathered * (world - 1) / world),
                        "GBps_per_rank": gathered * (world - 1) / world / max(ms_op - ms_gemm, 1e-6) / 1e6,
-                       "what": "ncclAllGather of the [n][rows] slabs + scatter kernel (op time minus kernels-only time)"},
+                       "what": "exchange fused into kernel 3 (peer stores of finished tiles over NVLink) + collect kernel: op time minus kernels-only time"},
             "e2e": {"value": tops(ms_e2e), "unit": "TOPS", "ms_per_pass": ms_e2e, "h2d_bytes_per_pass": sum(4 * K * n for (_, _, K) in handles) * world,
                     "d2h_bytes_per_pass": gathered * world, "api": "pinned host x -> HBM on every rank, ggml_b200_mul_mat_q4_0_sharded, full y -> pinned host"},
             "roofline": {"bound": "tensor", "achieved": tops(ms_gemm) / world, "peak": 2 * bf16, "unit": "TOP/s per rank", "frac": tops(ms_gemm) / world / (2 * bf16),

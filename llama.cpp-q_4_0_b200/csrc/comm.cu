@@ -12,6 +12,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include "common.cuh"
 #include "p2p.cuh"
 #include "state.h"
 
@@ -57,7 +58,14 @@ struct Nccl {
     unsigned char * arena = nullptr;                       // this rank's IPC-exported arena
     P2PPeers peers;                                        // every rank's arena as mapped in this process
     bool p2p_ok = false;
+    // prefill exchange (n >= gemm_min_n): kernel 3 stores its tiles straight into the peers' landing buffers
+    float * pf_local = nullptr;                            // [2 regions][pf_cap floats] + PF_SLOTS arrival counters, IPC-exported
+    void * pf_mapped[P2P_MAX_WORLD] = {};                  // the same block of every rank as mapped here
+    size_t pf_cap = 0;
+    unsigned long long pf_seq = 0;                         // sharded prefill ops so far (identical on every rank)
+    unsigned pf_target[64] = {};                           // arrivals a counter slot must have seen once its current op is complete
 };
+constexpr int PF_SLOTS = 64;
 static Nccl nc;
 static int g_p2p_enabled = 1;   // tuning key "p2p_gather"
 
@@ -94,6 +102,44 @@ __global__ void scatter_slabs_kernel(const float * __restrict__ gbuf, float * __
         if (r >= world) r = world - 1;
         const long long j = m - r * per;
         y[c * ldy + m] = gbuf[(r * n + c) * rows_max + j];
+    }
+}
+
+// Prefill exchange, receiving side: wait until every peer's tiles of this op have landed in this rank's region (one
+// release-add per tile on the op's counter slot, gemm_q4_0_tc3.cuh), then move the peers' rows into dst.  The peers are
+// other GPUs driven by other processes: the poll cannot starve what it waits for.
+__global__ void __launch_bounds__(512) pf_collect_kernel(const float * __restrict__ region, const unsigned * __restrict__ ctr, unsigned target,
+                                                          float * __restrict__ y, long long ldy, int n, int M, int world, int me, int per) {
+    pdl_wait();
+    pdl_launch_dependents();
+    if (threadIdx.x == 0) {
+        const unsigned long long t0 = p2p_now();
+        unsigned v;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+            if (p2p_now() - t0 > P2P_TIMEOUT_NS) __trap();
+        } while ((int)(v - target) < 0);
+    }
+    __syncthreads();
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nthr = (long long)gridDim.x * blockDim.x;
+    for (int r = 0; r < world; r++) {
+        if (r == me) continue;
+        const int lo = min(r * per, M), width = min(lo + per, M) - lo;
+        if (width <= 0) continue;
+        const bool vec = (width & 3) == 0 && (lo & 3) == 0 && (M & 3) == 0 && (ldy & 3) == 0 &&
+                         ((reinterpret_cast<uintptr_t>(region) | reinterpret_cast<uintptr_t>(y)) & 15) == 0;
+        if (vec) {
+            const int w4 = width >> 2;
+            for (long long i = tid; i < (long long)n * w4; i += nthr) {
+                const long long c = i / w4; const int j = (int)(i - c * w4) * 4;
+                *reinterpret_cast<float4 *>(y + c * ldy + lo + j) = __ldcg(reinterpret_cast<const float4 *>(region + c * M + lo + j));
+            }
+        } else {
+            for (long long i = tid; i < (long long)n * width; i += nthr) {
+                const long long c = i / width; const int j = (int)(i - c * width);
+                y[c * ldy + lo + j] = __ldcg(region + c * M + lo + j);
+            }
+        }
     }
 }
 
@@ -188,7 +234,27 @@ void comm_unshare(void ** mapped) {
     }
 }
 
+// the landing block of the prefill exchange: grown collectively (every rank sees the same shapes in the same order)
+static int pf_ensure(size_t need_floats) {
+    if (need_floats <= nc.pf_cap) return GGML_B200_OK;
+    CK(cudaStreamSynchronize(g.stream));                       // this rank's tiles for the old block are out
+    if (nc.pf_local) { comm_unshare(nc.pf_mapped); CK(cudaFree(nc.pf_local)); nc.pf_local = nullptr; nc.pf_cap = 0; }
+    size_t cap = (size_t)8 << 20;                              // floats per region
+    while (cap < need_floats) cap *= 2;
+    const size_t bytes = 2 * cap * sizeof(float) + PF_SLOTS * sizeof(unsigned);
+    CK(cudaMalloc(&nc.pf_local, bytes));
+    CK(cudaMemsetAsync(reinterpret_cast<unsigned char *>(nc.pf_local) + 2 * cap * sizeof(float), 0, PF_SLOTS * sizeof(unsigned), g.stream));
+    CK(cudaStreamSynchronize(g.stream));
+    int rc = comm_share(nc.pf_local, nc.pf_mapped);            // (all-gather of the handles: also the barrier behind the old block)
+    if (rc) return rc;
+    nc.pf_cap = cap;
+    nc.pf_seq = 0;
+    memset(nc.pf_target, 0, sizeof(nc.pf_target));
+    return GGML_B200_OK;
+}
+
 static void p2p_teardown() {
+    if (nc.pf_local) { comm_unshare(nc.pf_mapped); cudaFree(nc.pf_local); nc.pf_local = nullptr; nc.pf_cap = 0; nc.pf_seq = 0; }
     for (int r = 0; r < P2P_MAX_WORLD; r++) {
         if (nc.peers.arena[r] && r != nc.rank) cudaIpcCloseMemHandle(nc.peers.arena[r]);
         nc.peers.arena[r] = nullptr;
@@ -283,6 +349,50 @@ int ggml_b200_mul_mat_q4_0_sharded(const ggml_b200_weight * w, const float * x_d
         attr[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = attr; cfg.numAttrs = g.tune.pdl ? 1 : 0;
         CK(cudaLaunchKernelEx(&cfg, p2p_gather_kernel, ex, y_dev, g_p2p_enabled == 5 ? 1 : g_p2p_enabled));
+        g.launches++;
+        return GGML_B200_OK;
+    }
+
+    // n >= gemm_min_n: kernel 3 delivers its tiles to every peer itself and a collect kernel picks up theirs -- no
+    // collective call, the exchange rides under the tiles still being computed (tuning key p2p_gather = 0: NCCL below)
+    cudaStreamCaptureStatus cap_st = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(g.stream, &cap_st);
+    if (n > 1 && nc.p2p_ok && g_p2p_enabled == 1 && cap_st == cudaStreamCaptureStatusNone && g.path != GGML_B200_PATH_GEMV &&
+        (g.path == GGML_B200_PATH_GEMM || n >= g.gemm_min_n) && (w->rows() == 0 || gemm_available(w)) && !g.tune.skip_quantize) {
+        int rc = pf_ensure((size_t)n * (size_t)w->M);
+        if (rc) return rc;
+        const unsigned long long seq = nc.pf_seq++;
+        const int region = (int)(seq & 1), slot = (int)(seq % PF_SLOTS);
+        const int ctiles = (int)((n + 127) / 128);
+        unsigned expected = 0;
+        float * dst[P2P_MAX_WORLD]; unsigned * ctr[P2P_MAX_WORLD];
+        int nd = 0;
+        for (int r = 0; r < nc.world; r++) {
+            if (r == nc.rank) continue;
+            int64_t rl, rh;
+            ggml_b200_shard_rows(w->M, r, nc.world, &rl, &rh);
+            expected += (unsigned)(((rh - rl) + 127) / 128) * (unsigned)ctiles;
+            float * blk = (float *)nc.pf_mapped[r];
+            dst[nd] = blk + (size_t)region * nc.pf_cap + lo;       // my rows inside r's landing region ([n][M])
+            ctr[nd] = reinterpret_cast<unsigned *>(blk + 2 * nc.pf_cap) + slot;
+            nd++;
+        }
+        const unsigned target = (nc.pf_target[slot] += expected);
+        if (w->rows() > 0) {
+            rc = launch_quantize(x_dev, n, w->K, nb11, nullptr);
+            if (rc) return rc;
+            rc = launch_gemm_peers(w, y_dev + lo, (long long)(nb1 / 4), (int)n, dst, ctr, nd, (long long)w->M);
+            if (rc) return rc;
+        }
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = (unsigned)(2 * g.sm_count); cfg.blockDim = 512; cfg.stream = g.stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr; cfg.numAttrs = g.tune.pdl ? 1 : 0;
+        CK(cudaLaunchKernelEx(&cfg, pf_collect_kernel, (const float *)(nc.pf_local + (size_t)region * nc.pf_cap),
+                              (const unsigned *)(reinterpret_cast<unsigned *>(nc.pf_local + 2 * nc.pf_cap) + slot), target, y_dev, (long long)(nb1 / 4), (int)n, (int)w->M,
+                              nc.world, nc.rank, (int)rows_max));
         g.launches++;
         return GGML_B200_OK;
     }

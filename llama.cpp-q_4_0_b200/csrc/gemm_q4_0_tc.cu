@@ -101,11 +101,22 @@ void * gemm_prepare_q8(const void * wq, int64_t M, int64_t K) {
 }
 void gemm_release_q8(void * h) { delete (GemmWeight *)h; }
 
-static int launch_gemm_any(const CUtensorMap & tm_w, const __half * wd, int64_t M, int64_t Kw, int wfmt, float * y, long long ldy, int n, int * S, int independent);
+static int launch_gemm_any(const CUtensorMap & tm_w, const __half * wd, int64_t M, int64_t Kw, int wfmt, float * y, long long ldy, int n, int * S, int independent,
+                           const g3::PeerOut * peers = nullptr);
 
 int launch_gemm_q8(const void * h, const void * wd, int64_t M, int64_t K, float * y, long long ldy, int n, int * S) {
     if (!g_gemm_ready || !h) { set_error("tensor-core GEMM path not available for this weight"); return GGML_B200_ERR_STATE; }
     return launch_gemm_any(((const GemmWeight *)h)->tm_nib, (const __half *)wd, M, K, 8, y, ldy, n, S, 0);
+}
+
+// multi-GPU prefill: the tiles also go to the peers' landing buffers (comm.cu); dst[i] / ctr[i] for the ndst peers
+int launch_gemm_peers(const ggml_b200_weight * w, float * y, long long ldy, int n, float * const * dst, unsigned * const * ctr, int ndst, long long ld) {
+    if (!gemm_available(w)) { set_error("tensor-core GEMM path not available for this weight"); return GGML_B200_ERR_STATE; }
+    g3::PeerOut po = {};
+    if (ndst > 8) { set_error("too many peers"); return GGML_B200_ERR_ARG; }
+    for (int i = 0; i < ndst; i++) { po.dst[i] = dst[i]; po.ctr[i] = ctr[i]; }
+    po.ndst = ndst; po.ld = ld;
+    return launch_gemm_any(((const GemmWeight *)w->gemm)->tm_nib, w->wd, w->rows(), w->K, 4, y, ldy, n, nullptr, 0, &po);
 }
 
 int launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int * S, int independent) {
@@ -113,7 +124,8 @@ int launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int
     return launch_gemm_any(((const GemmWeight *)w->gemm)->tm_nib, w->wd, w->rows(), w->K, 4, y, ldy, n, S, independent);
 }
 
-static int launch_gemm_any(const CUtensorMap & tm_w, const __half * wd, int64_t M, int64_t Kw, int wfmt, float * y, long long ldy, int n, int * S, int independent) {
+static int launch_gemm_any(const CUtensorMap & tm_w, const __half * wd, int64_t M, int64_t Kw, int wfmt, float * y, long long ldy, int n, int * S, int independent,
+                           const g3::PeerOut * peers) {
     if (!g.xdT || g.xdT_n_pad < n) { set_error("activation scales were not laid out for the GEMM path"); return GGML_B200_ERR_STATE; }
     const uint64_t K = (uint64_t)Kw, nbk = K / QK;
     CUtensorMap tm_xq, tm_xd;
@@ -133,13 +145,15 @@ static int launch_gemm_any(const CUtensorMap & tm_w, const __half * wd, int64_t 
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = g.tune.pdl ? 1 : 0;
     const int rows = (int)M, nbk_i = (int)nbk;
+    g3::PeerOut po = {};
+    if (peers) po = *peers;
     if (wfmt == 8) {
-        if (S) CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<true, false, 8>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
-        else   CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, false, 8>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
+        if (S) CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<true, false, 8>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent, po));
+        else   CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, false, 8>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent, po));
     }
-    else if (g_gemm_trace && !S) CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, true>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
-    else if (S)             CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<true, false>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
-    else                    CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, false>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent));
+    else if (g_gemm_trace && !S) CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, true>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent, po));
+    else if (S)             CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<true, false>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent, po));
+    else                    CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, false>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent, po));
     g.launches++;
     return GGML_B200_OK;
 }

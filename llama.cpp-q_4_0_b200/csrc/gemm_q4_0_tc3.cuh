@@ -120,6 +120,18 @@ struct Dump {
     int * S; int rows, n, nbk, m, c_first;
 };
 
+// Multi-GPU prefill (row shards): the finished tile also goes to every peer's copy of dst over NVLink, straight from this
+// kernel (comm.cu: "prefill exchange") -- the all-gather that used to follow the GEMM rides under the tiles still being
+// computed.  dst[p] = the peer's landing buffer for THIS rank's rows (column stride ld floats); when the CTA is done, one
+// release-add per peer on ctr[p] tells the peer's collect kernel that one more tile has landed.
+struct PeerOut {
+    float * dst[8];
+    unsigned * ctr[8];
+    long long ld;
+    int ndst;
+};
+constexpr int T_STRIDE = BM + 4;        // words between two columns of the staged tile: 8 rows x 4 column pairs hit 32 banks
+
 // One half block: H = 0 -> the thread's rows r0, r0 + 8 (TMEM lanes 0..15 of the quadrant), H = 1 -> rows r0 + 16, r0 + 24;
 // 8 column pairs each.  acc[k * 4 + j] = (column pair k, row j).
 template <int H, bool DUMP, int WFMT>
@@ -158,7 +170,7 @@ __device__ __forceinline__ float4 lds_f4(uint32_t addr) { return lds_f32x4(addr)
 // The epilogue of one warp over the whole K loop.
 template <bool DUMP, bool TRACE, int WFMT>
 __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int ew, int lane, int m0, int c0, int rows, int n, int nbk,
-                                         float * __restrict__ y, long long ldy, int * S_out, long long * trc) {
+                                         float * __restrict__ y, long long ldy, int * S_out, long long * trc, const PeerOut & po) {
 #define G3_TR(idx) do { if (TRACE && trc != nullptr && ew == 0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0) trc[2 * 2048 + (idx)] = clock64(); } while (0)
     const uint32_t bars = sbase + SMEM_BAR;
     const int quad = ew & 3;                        // TMEM lane quadrant (== warp % 4)
@@ -269,8 +281,11 @@ __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int
             if (++sx == NS_X) { sx = 0; xph ^= 1; }
         }
     }
-    // store: a thread holds rows m + 8j and column pairs; for one (j, pair) the 8 threads with equal i%4 cover 8 consecutive
-    // rows = one 32-byte sector per column
+    // store: the tile goes through shared memory (the operand rings are idle now: the last block's commit has arrived),
+    // [column][row] with a padded column stride, so that every destination receives whole 512-byte column segments --
+    // 16-byte stores, 4 x 128 B per column -- instead of 32-byte pieces: what NVLink wants for the peers' copies, and no
+    // worse for the local dst.
+    const uint32_t tbase = sbase + SMEM_OP;
     if (cols_live) {
         const float rescale = 562949953421312.0f;   // 2^49
 #pragma unroll
@@ -278,13 +293,35 @@ __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int
             const int j = q & 3, k = q >> 2;
             float v0, v1;
             unpack_f32x2(acc[q], v0, v1);
-            const int c = c0 + col0 + 8 * k + 2 * (lane & 3);
-            const int mm = m + 8 * j;
-            if (mm < rows) {
-                if (c < n)     y[(size_t)c * ldy + mm] = v0 * rescale;
-                if (c + 1 < n) y[(size_t)(c + 1) * ldy + mm] = v1 * rescale;
+            const int cl = col0 + 8 * k + 2 * (lane & 3);
+            const int rl = r0 + 8 * j;
+            sts_f32(tbase + (cl * T_STRIDE + rl) * 4, v0 * rescale);
+            sts_f32(tbase + ((cl + 1) * T_STRIDE + rl) * 4, v1 * rescale);
+        }
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");      // the 16 epilogue warps
+    {
+        const int te = ew * 32 + lane;
+        for (int d = -1; d < po.ndst; d++) {
+            float * __restrict__ base = d < 0 ? y : po.dst[d];
+            const long long ld = d < 0 ? ldy : po.ld;
+            const bool vec = ((ld & 3) == 0) && ((reinterpret_cast<uintptr_t>(base + m0) & 15) == 0);
+            for (int idx = te; idx < BN * (BM / 4); idx += EPI_WARPS * 32) {
+                const int cl = idx >> 5, r4 = (idx & 31) * 4;
+                const int c = c0 + cl, mm = m0 + r4;
+                if (c >= n || mm >= rows) continue;
+                const float4 v = lds_f32x4(tbase + (cl * T_STRIDE + r4) * 4);
+                float * out = base + (size_t)c * ld + mm;
+                if (vec && mm + 3 < rows) *reinterpret_cast<float4 *>(out) = v;
+                else {
+                    out[0] = v.x;
+                    if (mm + 1 < rows) out[1] = v.y;
+                    if (mm + 2 < rows) out[2] = v.z;
+                    if (mm + 3 < rows) out[3] = v.w;
+                }
             }
         }
+        if (po.ndst > 0) __threadfence_system();      // this thread's peer stores are out before the CTA signals (kernel end)
     }
 #undef G3_TR
 }
@@ -302,7 +339,8 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
                      const __half * __restrict__ wd,               // weight scales [rows][nbk]
                      float * __restrict__ y, long long ldy, int rows, int n, int nbk,
                      int * __restrict__ S_out, long long * __restrict__ trc,
-                     int independent /* reads the activations its predecessor read, writes its own dst: no wait at the top */) {
+                     int independent /* reads the activations its predecessor read, writes its own dst: no wait at the top */,
+                     const __grid_constant__ PeerOut po /* ndst = 0: single GPU */) {
 #define G3K_TR(role, idx) do { if (TRACE && trc != nullptr && blockIdx.x == 0 && blockIdx.y == 0) trc[(role) * 2048 + (idx)] = clock64(); } while (0)
     // no static shared memory in this kernel: the dynamic window starts 1024-byte aligned (checked below), which the
     // 128-byte swizzle atoms need
@@ -346,7 +384,7 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
     // register budget: setmaxnreg at the top of each role's branch (the branches only meet again at the final barrier)
     if (warp < EPI_WARPS) {
         setmaxnreg_inc<EPI_REGS>();
-        epilogue<DUMP, TRACE, WFMT>(sbase, tmem_base, warp, lane, m0, c0, rows, n, nbk, y, ldy, S_out, trc);
+        epilogue<DUMP, TRACE, WFMT>(sbase, tmem_base, warp, lane, m0, c0, rows, n, nbk, y, ldy, S_out, trc, po);
     } else if (warp == TMA_WARP) {
         setmaxnreg_dec<SVC_REGS>();
         if (lane == 0) {
@@ -503,6 +541,7 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
         tc_fence_after_sync();
         tmem_dealloc(tmem_base, 512);
     }
+    if ((int)threadIdx.x < po.ndst) asm volatile("red.release.sys.global.add.u32 [%0], 1;" ::"l"(po.ctr[threadIdx.x]) : "memory");   // this tile has landed at peer threadIdx.x
     if (independent) pdl_wait();
 #undef G3K_TR
 }

@@ -137,6 +137,9 @@ int  gemm_prepare_weight(ggml_b200_weight * w);
 void gemm_release_weight(ggml_b200_weight * w);
 // y: first output element of this shard (column 0), ldy in floats; S != nullptr: also dump S_b
 int  launch_gemm(const ggml_b200_weight * w, float * y, long long ldy, int n, int * S, int independent = 0);
+// multi-GPU prefill: kernel 3 also stores every finished tile into the ndst peers' landing buffers (column stride ld) and
+// release-adds 1 to ctr[i] per tile (comm.cu: prefill exchange)
+int  launch_gemm_peers(const ggml_b200_weight * w, float * y, long long ldy, int n, float * const * dst, unsigned * const * ctr, int ndst, long long ld);
 // the same kernel over a Q8_0 weight's int8 plane (siblings.cu); handle = its TMA descriptor
 void * gemm_prepare_q8(const void * wq, int64_t M, int64_t K);
 void gemm_release_q8(void * handle);
