@@ -302,7 +302,10 @@ __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int
     asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");      // the 16 epilogue warps
     {
         const int te = ew * 32 + lane;
-        for (int d = -1; d < po.ndst; d++) {
+        // (every CTA starts its round of the peers somewhere else, so that no peer is everybody's first target)
+        const int rot = po.ndst > 0 ? (int)((blockIdx.x + blockIdx.y) % (unsigned)po.ndst) : 0;
+        for (int dd = -1; dd < po.ndst; dd++) {
+            const int d = dd < 0 ? -1 : (dd + rot) % po.ndst;
             float * __restrict__ base = d < 0 ? y : po.dst[d];
             const long long ld = d < 0 ? ldy : po.ld;
             const bool vec = ((ld & 3) == 0) && ((reinterpret_cast<uintptr_t>(base + m0) & 15) == 0);
