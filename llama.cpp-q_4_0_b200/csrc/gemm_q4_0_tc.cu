@@ -52,6 +52,7 @@ int gemm_init() {
     CK(cudaFuncSetAttribute(g3::gemm_q4_0_tc3_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, g3::SMEM_BYTES));
     CK(cudaFuncSetAttribute(g3::gemm_q4_0_tc3_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, g3::SMEM_BYTES));
     CK(cudaFuncSetAttribute(g3::gemm_q4_0_tc3_kernel<false, false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, g3::SMEM_BYTES));
+    CK(cudaFuncSetAttribute(g3::gemm_q4_0_tc3_kernel<false, false, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, g3::SMEM_BYTES));
     CK(cudaFuncSetAttribute(g3::gemm_q4_0_tc3_kernel<true, false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, g3::SMEM_BYTES));
     g_gemm_ready = true;
     return GGML_B200_OK;
@@ -147,7 +148,10 @@ static int launch_gemm_any(const CUtensorMap & tm_w, const __half * wd, int64_t 
     const int rows = (int)M, nbk_i = (int)nbk;
     g3::PeerOut po = {};
     if (peers) po = *peers;
-    if (wfmt == 8) {
+    if (peers && peers->ndst > 0 && wfmt == 4 && !S) {
+        CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, false, 4, true>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent, po));
+    }
+    else if (wfmt == 8) {
         if (S) CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<true, false, 8>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent, po));
         else   CK(cudaLaunchKernelEx(&cfg, g3::gemm_q4_0_tc3_kernel<false, false, 8>, tm_w, tm_xq, tm_xd, wd, y, ldy, rows, n, nbk_i, S, g_gemm_trace, independent, po));
     }

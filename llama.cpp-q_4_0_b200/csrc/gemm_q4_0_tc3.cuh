@@ -168,7 +168,7 @@ __device__ __forceinline__ void epi_half(uint32_t (&r)[4 * NKG], uint64_t (&acc)
 __device__ __forceinline__ float4 lds_f4(uint32_t addr) { return lds_f32x4(addr); }
 
 // The epilogue of one warp over the whole K loop.
-template <bool DUMP, bool TRACE, int WFMT>
+template <bool DUMP, bool TRACE, int WFMT, bool PEERS>
 __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int ew, int lane, int m0, int c0, int rows, int n, int nbk,
                                          float * __restrict__ y, long long ldy, int * S_out, long long * trc, const PeerOut & po) {
 #define G3_TR(idx) do { if (TRACE && trc != nullptr && ew == 0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0) trc[2 * 2048 + (idx)] = clock64(); } while (0)
@@ -281,10 +281,30 @@ __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int
             if (++sx == NS_X) { sx = 0; xph ^= 1; }
         }
     }
-    // store: the tile goes through shared memory (the operand rings are idle now: the last block's commit has arrived),
+    // store, multi-GPU: the tile goes through shared memory (the operand rings are idle now: the last block's commit has arrived),
     // [column][row] with a padded column stride, so that every destination receives whole 512-byte column segments --
-    // 16-byte stores, 4 x 128 B per column -- instead of 32-byte pieces: what NVLink wants for the peers' copies, and no
-    // worse for the local dst.
+    // 16-byte stores, 4 x 128 B per column -- instead of 32-byte pieces: what NVLink wants for the peers' copies.
+    if (!PEERS) {
+        // single GPU: straight from the registers -- a thread holds rows m + 8j and column pairs; for one (j, pair) the 8
+        // threads with equal i%4 cover 8 consecutive rows = one 32-byte sector per column (the staged path below costs 2-6 %
+        // when there is nobody to send to: profiles/r02_bench_gemm_staged.log)
+        if (cols_live) {
+            const float rescale = 562949953421312.0f;   // 2^49
+#pragma unroll
+            for (int q = 0; q < 4 * NKG; q++) {
+                const int j = q & 3, k = q >> 2;
+                float v0, v1;
+                unpack_f32x2(acc[q], v0, v1);
+                const int c = c0 + col0 + 8 * k + 2 * (lane & 3);
+                const int mm = m + 8 * j;
+                if (mm < rows) {
+                    if (c < n)     y[(size_t)c * ldy + mm] = v0 * rescale;
+                    if (c + 1 < n) y[(size_t)(c + 1) * ldy + mm] = v1 * rescale;
+                }
+            }
+        }
+        return;
+    }
     const uint32_t tbase = sbase + SMEM_OP;
     if (cols_live) {
         const float rescale = 562949953421312.0f;   // 2^49
@@ -334,7 +354,10 @@ __device__ __forceinline__ void epilogue(uint32_t sbase, uint32_t tmem_base, int
 // through the same kernel): the int8 plane [rows][K] IS the A operand, so the TMA warp drops the 128 x 128 B tile straight
 // into the operand ring (SWIZZLE_128B, like the activations), the MMA forms S_b itself (no factor 16: the staged weight scale
 // carries 2^4 instead) and warps 18-19 only stage the weight scales.  |S_b| <= 32 * 128 * 127 < 2^19 as before.
-template <bool DUMP, bool TRACE, int WFMT = 4>
+// PEERS: the multi-GPU instantiation (tile staged in shared memory, peer stores, arrival signal).  A template parameter and not
+// a run-time branch: with both store paths in one kernel ptxas schedules the K loop 2-7 % slower (A/B on one box, 394 -> 378 TOPS
+// at 4096^2), which the single-GPU kernel must not pay.
+template <bool DUMP, bool TRACE, int WFMT = 4, bool PEERS = false>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble plane  [rows][nbk*16 B], box 64 B x 128   (WFMT 8: int8 plane [rows][K], box 128 B x 128, SW128)
                      const __grid_constant__ CUtensorMap tm_xq,    // activations   [n][K] int8,      box 128 B x 128, SW128
@@ -387,7 +410,7 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
     // register budget: setmaxnreg at the top of each role's branch (the branches only meet again at the final barrier)
     if (warp < EPI_WARPS) {
         setmaxnreg_inc<EPI_REGS>();
-        epilogue<DUMP, TRACE, WFMT>(sbase, tmem_base, warp, lane, m0, c0, rows, n, nbk, y, ldy, S_out, trc, po);
+        epilogue<DUMP, TRACE, WFMT, PEERS>(sbase, tmem_base, warp, lane, m0, c0, rows, n, nbk, y, ldy, S_out, trc, po);
     } else if (warp == TMA_WARP) {
         setmaxnreg_dec<SVC_REGS>();
         if (lane == 0) {
@@ -544,7 +567,7 @@ gemm_q4_0_tc3_kernel(const __grid_constant__ CUtensorMap tm_nib,   // nibble pla
         tc_fence_after_sync();
         tmem_dealloc(tmem_base, 512);
     }
-    if ((int)threadIdx.x < po.ndst) asm volatile("red.release.sys.global.add.u32 [%0], 1;" ::"l"(po.ctr[threadIdx.x]) : "memory");   // this tile has landed at peer threadIdx.x
+    if (PEERS && (int)threadIdx.x < po.ndst) asm volatile("red.release.sys.global.add.u32 [%0], 1;" ::"l"(po.ctr[threadIdx.x]) : "memory");   // this tile has landed at peer threadIdx.x
     if (independent) pdl_wait();
 #undef G3K_TR
 }
