@@ -225,7 +225,24 @@ class Ref:
             L.ref_type_vec_dot.argtypes = [C.c_int, C.c_int, _vp, _vp]
             L.ref_mm_create_type.restype = _vp
             L.ref_mm_create_type.argtypes = [C.c_int, C.c_int64, C.c_int64, C.c_int64, _vp]
+        if hasattr(L, "ref_neighbour_op"):          # element-wise nodes next to the op (ref_shim.c, last part)
+            L.ref_neighbour_op.restype = C.c_int
+            L.ref_neighbour_op.argtypes = [C.c_int, _vp, _vp, _vp, C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_int]
         L.ref_init()
+
+    # -- the element-wise nodes next to the op, by the reference's own graph compute
+    NEIGHBOUR_OPS = {"add": 0, "mul": 1, "silu": 2, "rms_norm": 3, "rope": 4}
+
+    def neighbour(self, op: str, a: np.ndarray, b: np.ndarray | None = None, n_past: int = 0, n_threads: int = 1) -> np.ndarray:
+        """a: f32 [ne2][ne1][ne0] (any leading dims are padded to three); rope: mode 0 over whole rows, positions n_past + i2."""
+        a = np.ascontiguousarray(a, dtype=np.float32)
+        sh = (1,) * (3 - a.ndim) + a.shape
+        y = np.empty_like(a)
+        bb = np.ascontiguousarray(b, dtype=np.float32) if b is not None else a
+        rc = self.L.ref_neighbour_op(self.NEIGHBOUR_OPS[op], _ptr(a), _ptr(bb), _ptr(y), sh[2], sh[1], sh[0], n_past, n_threads)
+        if rc != 0:
+            raise RuntimeError("ref_neighbour_op failed: %d" % rc)
+        return y
 
     # -- sibling formats: the reference's own functions by ggml_type (3 = Q4_1, 8 = Q8_0)
     def type_quantize(self, qtype: int, x: np.ndarray) -> np.ndarray:

@@ -181,3 +181,32 @@ struct ref_mm * ref_mm_create_type(int type, int64_t M, int64_t K, int64_t n, co
     h->gf = ggml_build_forward(h->y);
     return h;
 }
+
+/* ---- the element-wise nodes next to the op, run by the reference's own ggml_graph_compute: what
+ * oracle/neighbours.py is pinned against.  op: 0 add(a, b)  1 mul(a, b)  2 silu(a)  3 rms_norm(a) (rows of ne0)
+ * 4 rope(a, n_past, n_dims = ne0, mode 0) with a = [ne0][ne1][ne2].  Result into y (same element count as a). */
+int ref_neighbour_op(int op, const float * a, const float * b, float * y, int64_t ne0, int64_t ne1, int64_t ne2, int n_past, int n_threads) {
+    ref_init();
+    const size_t n = (size_t)ne0 * ne1 * ne2;
+    struct ggml_init_params p = { n * 4 * 4 + (8u << 20), NULL, false };
+    struct ggml_context * ctx = ggml_init(p);
+    if (!ctx) return -1;
+    struct ggml_tensor * ta = ggml_new_tensor_3d(ctx, GGML_TYPE_F32, ne0, ne1, ne2);
+    memcpy(ta->data, a, n * 4);
+    struct ggml_tensor * tb = NULL, * r = NULL;
+    if (op == 0 || op == 1) { tb = ggml_new_tensor_3d(ctx, GGML_TYPE_F32, ne0, ne1, ne2); memcpy(tb->data, b, n * 4); }
+    switch (op) {
+        case 0: r = ggml_add(ctx, ta, tb); break;
+        case 1: r = ggml_mul(ctx, ta, tb); break;
+        case 2: r = ggml_silu(ctx, ta); break;
+        case 3: r = ggml_rms_norm(ctx, ta); break;
+        case 4: r = ggml_rope(ctx, ta, n_past, (int)ne0, 0, 0); break;
+        default: ggml_free(ctx); return -2;
+    }
+    struct ggml_cgraph gf = ggml_build_forward(r);
+    gf.n_threads = n_threads;
+    ggml_graph_compute(ctx, &gf);
+    memcpy(y, r->data, n * 4);
+    ggml_free(ctx);
+    return 0;
+}
