@@ -436,6 +436,23 @@ def mul_mat_swiglu(w1: Weight, w3: Weight, x: np.ndarray, want_silu: bool = True
     return out
 
 
+def rms_norm(x: np.ndarray, w: np.ndarray | None = None, eps: float = 1e-6):
+    """rows of x normalised (ggml_b200_rms_norm_f32); with w also the product with the norm weights (…_rms_norm_mul_f32).
+    Returns y, or (y, y * w)."""
+    x = np.ascontiguousarray(x, np.float32)
+    ncols, nrows = x.shape[-1], x.size // x.shape[-1]
+    xd, yd = DevBuf.from_numpy(x), DevBuf(x.nbytes)
+    if w is None:
+        _check(lib().ggml_b200_rms_norm_f32(xd.ptr, yd.ptr, ncols, nrows, C.c_float(eps)))
+        synchronize()
+        return yd.to_numpy(np.float32, x.shape)
+    w = np.ascontiguousarray(w, np.float32)
+    wd, y2d = DevBuf.from_numpy(w), DevBuf(x.nbytes)
+    _check(lib().ggml_b200_rms_norm_mul_f32(xd.ptr, yd.ptr, wd.ptr, y2d.ptr, ncols, nrows, w.size, C.c_float(eps)))
+    synchronize()
+    return yd.to_numpy(np.float32, x.shape), y2d.to_numpy(np.float32, x.shape)
+
+
 def eltwise(op: str, a: np.ndarray, b: np.ndarray | None = None):
     """The stand-alone element-wise kernels (add | mul | silu | silu_mul) on host arrays: the unfused twins in the tests."""
     a = np.ascontiguousarray(a, np.float32)

@@ -88,3 +88,20 @@ def test_rope_mode0(b200, npos, rows, ne0):
     b200.synchronize()
     assert np.array_equal(xd.to_numpy(np.float32, x.shape).view(np.uint32), want.view(np.uint32))
     assert np.allclose(np.linalg.norm(want, axis=-1), np.linalg.norm(x, axis=-1), rtol=1e-5)      # a rotation
+
+
+@pytest.mark.parametrize("nrows,ncols", [(1, 4096), (1, 4544), (3, 8192), (2, 11008), (1, 64), (5, 100), (1, 20000)])
+def test_rms_norm_kernels(b200, nrows, ncols):
+    """Both rms_norm kernels (rows held in registers up to 16384 aligned floats, the strided one otherwise) against the oracle's
+    restatement of ggml_compute_forward_rms_norm_f32: the double-precision sum is a tree here and a serial loop there, which
+    moves the float mean by at most its last bit -- one ulp on the result; with the norm weights the product is exact on top."""
+    rng = np.random.default_rng(nrows * 7 + ncols)
+    x = rng.standard_normal((nrows, ncols), dtype=np.float32) * np.float32(2.5)
+    w = (1.0 + 0.1 * rng.standard_normal(ncols)).astype(np.float32)
+    want = nb.rms_norm(x)
+    y = b200.rms_norm(x)
+    assert np.all(np.abs(y - want) <= np.spacing(np.abs(want)))
+    assert np.mean(y == want) > 0.5
+    y1, y2 = b200.rms_norm(x, w)
+    assert np.array_equal(y1.view(np.uint32), y.view(np.uint32))
+    assert np.array_equal(y2.view(np.uint32), (y1 * w[None, :]).astype(np.float32).view(np.uint32))
