@@ -783,7 +783,7 @@ void ggml_b200_graph_free(void * exec) {
 }
 // A decode graph moves rows of 16-64 KB between the host's compute buffer and HBM at every CPU node (q/k/v down, the
 // attention result up).  As copy-engine transfers each costs 8-11 us on the stream's critical path
-// (profiles/r02_trace_seam.log: the idle time between wq and wk); when the host side lies in a block from
+// (profiles/r02_trace_seam_before.log: the idle time between wq and wk); when the host side lies in a block from
 // ggml_b200_host_malloc (pinned AND mapped) a kernel moves the row over PCIe with 16-byte accesses instead -- posted
 // writes on the way down, a handful of read round trips on the way up -- and takes the programmatic launch edge like
 // every other kernel here.  Larger or unaligned copies, and pageable host memory, take cudaMemcpyAsync.
