@@ -55,7 +55,9 @@ static struct ggml_tensor * make_weight(struct glue_model * m, enum ggml_type ty
     if (own) m->host[m->n_host++] = data;
     if (m->offload) {
         /* llama.cpp:678-685: the loader tags the tensor and hands the bytes over; the callee copies */
-        t->backend = GGML_BACKEND_GPU;
+        /* GLUE_DRIVER_SPLIT=1: matrices tagged like llama.cpp's LLAMA_BACKEND_OFFLOAD_SPLIT -- row-sharded when a communicator is up */
+        const char * split = getenv("GLUE_DRIVER_SPLIT");
+        t->backend = (split && atoi(split) && ne1 > 0 && type != GGML_TYPE_F32) ? GGML_BACKEND_GPU_SPLIT : GGML_BACKEND_GPU;
         ggml_cuda_transform_tensor(data, t);
     }
     return t;

@@ -44,3 +44,20 @@ def test_sharded_persistent_list_equals_single_gpu(world):
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "CHECK_SHARDED_SET OK" in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2])
+def test_seam_with_row_sharded_weights(world):
+    """The reference's graph compute over the seam with a communicator up (tools/check_glue_multi_rank.py): the layer graph's
+    matrices tagged GGML_BACKEND_GPU_SPLIT are row-sharded by ggml_cuda_transform_tensor, every matmul node is a sharded op
+    (host-resident and device-resident activations, recorded segments included); every rank's logits against the CPU path."""
+    if _gpus() < world:
+        pytest.skip(f"needs {world} GPUs")
+    if not os.path.exists(os.path.join(ROOT, "llama.cpp-q_4_0_b200", "ggml_glue", "_build", "libggml_b200_glue_ref.so")):
+        pytest.skip("ggml_glue/_build/libggml_b200_glue_ref.so not built (needs /root/reference at build time)")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29800 + world), os.path.join(ROOT, "tools", "check_glue_multi_rank.py")]
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("ALL OK") == world and "MISMATCH" not in r.stdout
