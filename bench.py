@@ -725,7 +725,7 @@ def prefill_leg(mod, stream, rng, steps, warmup, n=512, shapes=None, groups=None
                      "note": "the per-block fp16 x fp16 scale epilogue bounds this formulation at ~25% of the tensor rate: every 128x128 int32 "
                              "tile (one Q4_0 block) costs 300 clk of FP32 FMAs overlapped with 257 clk of TMEM reads against 64 clk of data MMA "
                              "(profiles/r02_ubench_epi_rate.log, r02_ubench_mma_rate.log); the kernel itself is latency bound on the per-warp chain "
-                             "TMEM load -> FMA -> hand-off (profiles/r02_ncu_gemm_full_summary.txt): 16 epilogue warps; see DESIGN.md kernel 3"},
+                             "TMEM load -> FMA -> hand-off (profiles/r02_ncu_gemm3_full_summary.txt: issue slots 57 % busy, tensor pipe 19.6 %): 16 epilogue warps; see DESIGN.md kernel 3"},
     }
     if not host_leg:
         for (h, _, _) in handles:
