@@ -395,6 +395,7 @@ int ggml_b200_init(int device) {
 static struct { uint64_t ops, copy_in, launch, spin, copy_out; } g_hio_stats = {};
 static void hostio_release();
 
+static cudaEvent_t g_marks[GGML_B200_MARKS] = {};      // ggml_b200_mark / _wait_mark
 void ggml_b200_shutdown(void) {
     std::lock_guard<std::mutex> lk(g_mu);
     if (!g.inited) return;
@@ -414,6 +415,7 @@ void ggml_b200_shutdown(void) {
         fprintf(stderr, "ggml_b200: host path, %llu ops: copy-in %.2f us, launch %.2f us, wait for the first 4 rows %.2f us, rest of the copy-out %.2f us per op\n",
                 (unsigned long long)g_hio_stats.ops, g_hio_stats.copy_in / n, g_hio_stats.launch / n, g_hio_stats.spin / n, g_hio_stats.copy_out / n);
     }
+    for (int i = 0; i < GGML_B200_MARKS; i++) if (g_marks[i]) { cudaEventDestroy(g_marks[i]); g_marks[i] = nullptr; }
     hostio_release();
     gemm_shutdown();
     if (g.own_stream) cudaStreamDestroy(g.own_stream);
@@ -499,7 +501,6 @@ int ggml_b200_memcpy_h2d(void * d, const void * s, size_t n) { CK(cudaMemcpyAsyn
 int ggml_b200_memcpy_d2h(void * d, const void * s, size_t n) { CK(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, g.stream)); CK(cudaStreamSynchronize(g.stream)); return GGML_B200_OK; }
 int ggml_b200_synchronize(void) { CK(cudaStreamSynchronize(g.stream)); return GGML_B200_OK; }
 // a few marks on the stream: wait for what was queued up to a mark although more has been queued behind it
-static cudaEvent_t g_marks[GGML_B200_MARKS] = {};
 int ggml_b200_mark(int slot) {
     B200_API_LOCK;
     if (!g.inited) { set_error("ggml_b200_init was not called"); return GGML_B200_ERR_STATE; }
